@@ -1,0 +1,294 @@
+#!/usr/bin/env python
+"""bench.py — input bases/s for k-mer count + DBG build on B200 (BASELINE.json metric).
+
+A step = one pass of the hot path (K1 extract_count → K2 histogram_filter →
+K3..K6 graph + unitigs) over one synthetic read set of the named shape.
+
+  value : device-resident packed reads in → device-resident filtered k-mers +
+          unitigs out (shk_run), CUDA events on the launching stream.
+  e2e   : the reference-facing C-ABI calls with HOST (pinned) seq/qual buffers:
+          shk_asm_preprocess_reads (H2D + K0 pack + K1 + K2 + info JSON) and
+          shk_asm_assemble (K3..K6 + D2H of the unitig graph + text writers).
+  roofline    : K1 extract_count alone (shk_stats.ms_extract), algorithmic bytes
+                ALG(k, L) per input base over MEASURED_PEAKS hbm_gbs.
+  cpu_baseline: the CPU oracle (a port; the reference crate is absent) on a
+                bounded sample of the same reads, all host threads.
+
+N > 1: one process per GPU, each rank assembles its own genome of the same shape
+(BASELINE config 4 style batch: independent replicas, no collective) — weak scaling.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: genome length, coverage, error, k, min_count   
+    "A": dict(G=2_000_000, cov=30.0, err=0.005, k=31, min_count=3, desc="2 Mb genome, 30x 150bp PE, 0.5% error, k=31"),
+    "B": dict(G=5_000_000, cov=100.0, err=0.005, k=31, min_count=5, desc="5 Mb genome, 100x 150bp PE, 0.5% error, k=31"),
+    "C": dict(G=5_000_000, cov=100.0, err=0.01, k=63, min_count=5, desc="5 Mb genome, 100x 150bp PE, 1% error, k=63"),
+    "S": dict(G=200_000, cov=30.0, err=0.005, k=31, min_count=3, desc="smoke: 200 kb genome, 30x"),
+}
+L = 150
+MIN_QUAL = 20
+
+
+def alg_bytes_per_base(k):
+    slot = 16 if k <= 31 else 32
+    return 0.375 + (L - k + 1) / L * 2 * slot
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.p = None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                       "-lms", "100", "-i", str(index)], stdout=subprocess.PIPE,
+                                      stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.p = None
+
+    def stop(self):
+        if not self.p:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.p.terminate()
+        try:
+            out, _ = self.p.communicate(timeout=5)
+        except Exception:
+            self.p.kill()
+            out = ""
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in out.splitlines():
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def reference_arm(args, w, rank, world):
+    """--impl reference: the CPU implementation of the path on the host cores.
+    The reference's own crate is absent, so this times the oracle
+    port (kind "port") with all host threads on a bounded sample per step."""
+    if rank != 0:
+        return
+    from oracle import Oracle
+    from sparrowhawk_b200 import synth
+    cores = os.cpu_count() or 1
+    npairs = synth.num_pairs(w["G"], w["cov"], L)
+    frac = args.cpu_sample_frac
+    sp = max(1, int(npairs * frac))
+    seq, qual = synth.reads(w["seed"], w["G"], w["cov"], w["err"], L, pair_range=(0, sp))
+    bases = sp * 2 * L
+    times = []
+    for it in range(args.warmup + args.steps):
+        t0 = time.perf_counter()
+        o = Oracle(w["k"], w["min_count"], MIN_QUAL, cores)
+        o.add_reads(seq, qual); o.finish_count(); o.build_graph()
+        dt = time.perf_counter() - t0
+        if it >= args.warmup:
+            times.append(dt)
+        del o
+    ms = 1e3 * sum(times) / len(times)
+    v = bases / (ms * 1e-3)
+    sample = f"first {sp} of {npairs} read pairs ({bases/1e6:.1f} Mbase) of workload {args.workload}"
+    print(json.dumps({
+        "impl": "reference", "metric": "input bases/s, k-mer count + DBG build", "value": v, "unit": "bases/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64" if w["k"] <= 31 else "u128",
+        "data": "synthetic", "config": {"workload": f"{args.workload}: {w['desc']}", "min_qual": MIN_QUAL,
+                                        "min_count": w["min_count"], "bases_per_step": bases},
+        "cpu_baseline": {"value": v, "unit": "bases/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": "bases/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+        "note": "CPU oracle (restatement of the path); sparrowhawk-asm native CPU: unavailable on this box",
+    }))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="B", choices=sorted(WORKLOADS))
+    ap.add_argument("--cpu-sample-frac", type=float, default=0.05)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--table-slots", type=int, default=0)
+    args = ap.parse_args()
+    if args.warmup < 1:
+        args.warmup = 1
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    w = dict(WORKLOADS[args.workload])
+    w["seed"] = 2 + rank          # every rank assembles its own genome (replicas)
+
+    if args.impl == "reference":
+        reference_arm(args, w, rank, world)
+        return
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from sparrowhawk_b200 import AssemblyHelper, synth
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    # ---- synthetic reads into pinned host memory --------------------------
+    npairs = synth.num_pairs(w["G"], w["cov"], L)
+    nbytes = npairs * 2 * (L + 1)
+    pin_seq = torch.empty(nbytes, dtype=torch.uint8, pin_memory=True)
+    pin_qual = torch.empty(nbytes, dtype=torch.uint8, pin_memory=True)
+    t0 = time.perf_counter()
+    seq, qual = synth.reads(w["seed"], w["G"], w["cov"], w["err"], L, out=(pin_seq.numpy(), pin_qual.numpy()))
+    t_gen = time.perf_counter() - t0
+    bases = npairs * 2 * L
+
+    stream = torch.cuda.current_stream()
+    h = AssemblyHelper.new(w["k"], False, w["min_count"], MIN_QUAL, 0, False, False, False, False, device=local,
+                           table_slots=args.table_slots)
+    h.set_stream(stream.cuda_stream)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident arm ------------------------------------------------
+    h.load_reads_ptr(pin_seq.data_ptr(), pin_qual.data_ptr(), nbytes)     # resident packed reads (untimed)
+    torch.cuda.synchronize()
+    for _ in range(args.warmup):
+        h.run()
+    launches0 = h.stats()["gpu_launches"]
+    sampler = ClockSampler(local)
+    barrier()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ms_extract = []
+    ms_parts = {"count": [], "filter": [], "graph": []}
+    ev0.record(stream)
+    for _ in range(args.steps):
+        h.run()
+        st = h.stats()
+        ms_extract.append(st["ms_extract"])
+        for kname in ms_parts:
+            ms_parts[kname].append(st["ms_" + kname])
+    ev1.record(stream)
+    barrier()
+    clocks = sampler.stop()
+    ms_total = ev0.elapsed_time(ev1)
+    st = h.stats()
+    launches = st["gpu_launches"] - launches0
+    t = torch.tensor([ms_total], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_step = float(t.item()) / args.steps
+    value = bases * world / (ms_step * 1e-3)
+
+    # ---- end-to-end arm: host buffers through the reference-facing calls ----
+    e2e = None
+    if not args.no_e2e:
+        for _ in range(1):
+            h.preprocess_reads(seq, qual); h.assemble()
+        barrier()
+        t0 = time.perf_counter()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(args.steps):
+            h.preprocess_reads(seq, qual)
+            info = h.get_preprocessing_info()
+            h.assemble()
+            res = h.get_assembly()
+        e1.record(stream)
+        barrier()
+        wall = (time.perf_counter() - t0) * 1e3
+        t = torch.tensor([max(wall, e0.elapsed_time(e1))], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_e2e = float(t.item()) / args.steps
+        s2 = h.stats()
+        d2h = int(s2["unitig_bases"] + s2["n_unitigs"] * 25 + s2["n_links"] * 8 + 3 * 4200 + 128)
+        e2e = {"value": bases * world / (ms_e2e * 1e-3), "unit": "bases/s", "h2d_bytes_per_step": int(2 * nbytes),
+               "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e,
+               "calls": "shk_asm_preprocess_reads + shk_asm_preprocessing_info + shk_asm_assemble + shk_asm_get_assembly",
+               "ncontigs": json.loads(res)["ncontigs"], "nkmers": json.loads(info)["nkmers"]}
+
+    # ---- roofline of the dominant kernel (K1 extract_count) -----------------
+    peak, peak_src = peaks()
+    ms_k1 = sum(ms_extract) / len(ms_extract)
+    alg = alg_bytes_per_base(w["k"]) * bases
+    achieved = alg / (ms_k1 * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": "k_extract_count", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                "alg_bytes_per_base": alg_bytes_per_base(w["k"]), "kernel_ms": ms_k1,
+                "whole_step_frac": (alg / (ms_step * 1e-3) / 1e9) / peak,
+                "stage_ms": {kname: sum(v) / len(v) for kname, v in ms_parts.items()}}
+
+    # ---- CPU baseline (rank 0, N = 1 only) -----------------------------------
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        from oracle import Oracle
+        cores = os.cpu_count() or 1
+        sp = max(1, int(npairs * args.cpu_sample_frac))
+        sb = sp * 2 * (L + 1)
+        t0 = time.perf_counter()
+        o = Oracle(w["k"], w["min_count"], MIN_QUAL, cores)
+        o.add_reads(seq[:sb], qual[:sb]); o.finish_count(); o.build_graph()
+        dt = time.perf_counter() - t0
+        cpu = {"value": sp * 2 * L / dt, "unit": "bases/s", "cores": cores, "kind": "port",
+               "sample": f"first {sp} of {npairs} read pairs ({sp*2*L/1e6:.1f} Mbase) of workload {args.workload}, "
+                         f"{dt:.1f} s; sparrowhawk-asm native CPU: unavailable on this box"}
+
+    if rank == 0:
+        print(json.dumps({
+            "metric": "input bases/s, k-mer count + DBG build", "value": value, "unit": "bases/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u64" if w["k"] <= 31 else "u128", "data": "synthetic",
+            "config": {"workload": f"{args.workload}: {w['desc']}", "min_qual": MIN_QUAL, "min_count": w["min_count"],
+                       "bases_per_step_per_gpu": bases, "read_pairs": npairs,
+                       "multi_gpu": "independent genome per rank (replicas, no collective)" if world > 1 else "single GPU",
+                       "l2": "inputs larger than L2: packed reads %.0f MB + table %.0f MB vs 126 MB L2"
+                             % (st["n_positions"] * 0.375 / 1e6, st["table_slots"] * (16 if w["k"] <= 31 else 32) / 1e6),
+                       "n_distinct": st["n_distinct"], "n_nodes": st["n_nodes"], "n_unitigs": st["n_unitigs"],
+                       "table_slots": st["table_slots"], "gen_seconds": round(t_gen, 2)},
+            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
+            "clocks": clocks,
+        }))
+    h.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,198 @@
+/* shk.h — C ABI of the B200-native sparrowhawk-asm front end (libshk_b200.so).
+ *
+ * Drop-in boundary for the path named by BASELINE.json `north_star`:
+ *   FASTQ → 2-bit canonical k-mers → exact counts + min-count filter + 500-bin
+ *   spectrum → node-based de Bruijn graph (read-evidenced edges) → unitigs.
+ *
+ * The reference side of this boundary is the wasm-bindgen class `AssemblyHelper`
+ * of the (unfetched) crate rust/sparrowhawk-asm, whose complete consumed surface
+ * is in the reference tree at
+ *   www/src/workers/Assembler.ts:15-39   (constructor + 4 methods)
+ *   www/src/workers/Assembler.ts:1-13    (result JSON schemas)
+ *   SKILLS.md:620-636                    (post_state progress hook)
+ * Every entry point below cites the reference interface it replaces.
+ *
+ * Conventions: plain pointers and sizes only; every call returns shk_status
+ * (0 = ok); no exception crosses the ABI; a failed handle stays freeable
+ * (reference: a wasm panic poisons the module, Assembler.ts:101-106 — here the
+ * error is a return code + shk_last_error()).  Handles are not thread-safe;
+ * distinct handles may run concurrently.  There is NO CPU fallback: without a
+ * CUDA device every compute entry returns SHK_ERR_NO_DEVICE.
+ */
+#ifndef SHK_H
+#define SHK_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SHK_ABI_VERSION 1
+#define SHK_HISTO_BINS 500 /* www/src/components/KmerHistogram.vue:45 */
+
+typedef enum shk_status {
+  SHK_OK = 0,
+  SHK_ERR_BAD_ARG = 1,     /* k even / out of range, null pointer, >2 files … */
+  SHK_ERR_NO_DEVICE = 2,   /* no CUDA device / wrong arch: there is no CPU path */
+  SHK_ERR_CUDA = 3,        /* CUDA runtime error (message in shk_last_error) */
+  SHK_ERR_OOM = 4,         /* host or device allocation failed */
+  SHK_ERR_TABLE_FULL = 5,  /* k-mer table overflow after all growth retries */
+  SHK_ERR_IO = 6,          /* file unreadable */
+  SHK_ERR_FORMAT = 7,      /* malformed FASTQ / gzip */
+  SHK_ERR_STATE = 8        /* call order violated (assemble before preprocess …) */
+} shk_status;
+
+/* Parameters = the 9 positional constructor arguments of AssemblyHelper.new
+ * (Assembler.ts:17-27, order kept) followed by GPU-only knobs (0 = default). */
+typedef struct shk_params {
+  int32_t k;                   /* odd, 3..63 (UI default 31, AssemblyPage.vue:313) */
+  int32_t verbose;
+  int32_t min_count;           /* k-mer kept iff count > min_count */
+  int32_t min_qual;            /* base valid iff phred33 >= min_qual (S3) */
+  int64_t chunk_size;          /* reads per batch; 0 = bulk. Result-independent (S8) */
+  int32_t do_bloom;            /* accepted, ignored: counting is exact (S8) */
+  int32_t do_fit;              /* host spectrum fit of min_count (S11) */
+  int32_t no_bubble_collapse;  /* host cleaning flags (docs/src/assembly.md:19-20) */
+  int32_t no_dead_end_removal;
+  /* --- GPU-only knobs --- */
+  int32_t device;              /* CUDA ordinal; -1 = current device */
+  int32_t reserved0;
+  uint64_t table_slots;        /* initial hash-table capacity; 0 = auto */
+  uint64_t reserved1;
+} shk_params;
+
+typedef struct shk_asm shk_asm; /* opaque; owns all host + device memory */
+
+typedef void (*shk_progress_fn)(const char *state, void *user);
+
+/* ------------------------------------------------------------------ */
+/* Reference-facing entry points (AssemblyHelper mirror)               */
+/* ------------------------------------------------------------------ */
+
+/* AssemblyHelper.new(k, verbose, min_count, min_qual, chunk_size, do_bloom,
+ * do_fit, no_bubble_collapse, no_dead_end_removal) — Assembler.ts:94-99 */
+shk_status shk_asm_new(const shk_params *params, shk_asm **out);
+
+/* `helper = null` / resetAll() — Assembler.ts:141-143 */
+void shk_asm_free(shk_asm *h);
+
+/* post_state(&str) → postMessage({assemblyState}) — SKILLS.md:620-636.
+ * Called on the calling thread with the vocabulary of AssemblyPage.vue:451-619. */
+shk_status shk_asm_set_progress_cb(shk_asm *h, shk_progress_fn fn, void *user);
+
+/* AssemblyHelper.preprocess(file1, file2|null) — Assembler.ts:35,100.
+ * FASTQ, plain or gzip (magic 1F 8B, sketchlib.rust/src/fastx_wasm.rs:42-47). */
+shk_status shk_asm_preprocess_files(shk_asm *h, const char *path1,
+                                    const char *path2_or_null);
+
+/* Streaming form of preprocess for hosts that hold bytes, not paths (model:
+ * deacon-bridge/src/lib.rs:112-206 push_chunk/finish).  `bytes` is decompressed
+ * FASTQ text; chunks may split records anywhere. */
+shk_status shk_asm_preprocess_push(shk_asm *h, const uint8_t *bytes, size_t n);
+shk_status shk_asm_preprocess_finish(shk_asm *h);
+
+/* preprocess for hosts that already parsed the FASTQ (what a Rust host holding
+ * needletail records would pass): two HOST byte streams of equal length n,
+ * reads separated by '\n' in `seq`; `qual` holds the phred+33 byte of the base
+ * at the same index (any byte under a separator).  qual may be NULL (FASTA). */
+shk_status shk_asm_preprocess_reads(shk_asm *h, const uint8_t *seq,
+                                    const uint8_t *qual, size_t n);
+
+/* AssemblyHelper.get_preprocessing_info() -> JSON {nkmers, histo[500],
+ * used_min_count} — Assembler.ts:1-5,110.  Pointer valid until the next call
+ * on the handle. */
+shk_status shk_asm_preprocessing_info(shk_asm *h, const char **json, size_t *len);
+
+/* AssemblyHelper.assemble() — Assembler.ts:124 */
+shk_status shk_asm_assemble(shk_asm *h);
+
+/* AssemblyHelper.get_assembly() -> JSON {outfasta, ncontigs, outdot, outgfa,
+ * outgfav2} — Assembler.ts:7-13,127 */
+shk_status shk_asm_get_assembly(shk_asm *h, const char **json, size_t *len);
+
+/* Thread-local message of the last failing call (reference: panic text). */
+const char *shk_last_error(void);
+int shk_abi_version(void);
+
+/* ------------------------------------------------------------------ */
+/* Low-level path API (what a Rust host that keeps its own cleaning /  */
+/* writer code binds; internal to the crate in the reference, SURVEY   */
+/* §8b row 2).  All arrays are plain SoA, caller-allocated after a     */
+/* size query through shk_get_stats().                                 */
+/* ------------------------------------------------------------------ */
+
+typedef struct shk_stats {
+  uint64_t n_bases;        /* sequence characters loaded (unit of the metric) */
+  uint64_t n_positions;    /* stream positions incl. separators / padding */
+  uint64_t n_instances;    /* valid k-mer instances counted */
+  uint64_t n_distinct;     /* distinct canonical k-mers before the filter */
+  uint64_t n_nodes;        /* survivors of count > min_count (== nkmers) */
+  uint64_t n_unitigs;
+  uint64_t unitig_bases;   /* total length of all unitig sequences */
+  uint64_t n_links;        /* unitig-level links (directed, both directions) */
+  uint64_t table_slots;    /* hash-table capacity finally used */
+  uint64_t gpu_launches;   /* kernels launched by this handle so far */
+  int32_t used_min_count;
+  int32_t table_retries;
+  float ms_pack, ms_count, ms_filter, ms_graph; /* CUDA-event time of last run */
+  float ms_extract, reserved_f;                 /* K1 extract_count kernel alone */
+} shk_stats;
+
+/* Use `stream` (a cudaStream_t passed as void*) for all work of this handle;
+ * NULL restores the handle's own stream.  shk_get_stream returns the current one
+ * so the caller can bracket calls with its own CUDA events. */
+shk_status shk_set_stream(shk_asm *h, void *stream);
+void *shk_get_stream(shk_asm *h);
+
+/* HOST seq/qual streams (same meaning as shk_asm_preprocess_reads) → H2D →
+ * K0 pack_reads.  Replaces (append=0) or extends (append=1) the resident reads. */
+shk_status shk_load_reads(shk_asm *h, const uint8_t *seq, const uint8_t *qual,
+                          size_t n, int append);
+/* Same, but seq/qual are DEVICE pointers (already in HBM). */
+shk_status shk_load_reads_device(shk_asm *h, const void *d_seq, const void *d_qual,
+                                 size_t n, int append);
+
+/* K1 extract_count over the resident packed reads.  reset=1 clears the table
+ * first (memset inside the timed region); reset=0 accumulates (chunked mode). */
+shk_status shk_count(shk_asm *h, int reset);
+/* K2 histogram + min-count filter + compaction into dense node arrays. */
+shk_status shk_filter(shk_asm *h);
+/* K3..K6 edge validation, unitig links, list ranking, unitig emission. */
+shk_status shk_build_graph(shk_asm *h);
+/* shk_count(reset=1) + shk_filter + shk_build_graph: the device-resident timed
+ * region of the metric. No host synchronisation except the few
+ * scalar read-backs that size later stages. */
+shk_status shk_run(shk_asm *h);
+
+shk_status shk_get_stats(shk_asm *h, shk_stats *out);
+/* 500-bin spectrum, histo[i] = #distinct k-mers with min(count,500) == i+1. */
+shk_status shk_get_histogram(shk_asm *h, uint64_t *histo /*[SHK_HISTO_BINS]*/);
+
+/* Filtered k-mers (nodes), unsorted.  key_hi may be NULL when k <= 31.
+ * counts saturate at 65535 (S7); edges: bits 0-3 right extension one-hot by
+ * base code, bits 4-7 left extension, relative to the canonical k-mer (A=0,
+ * C=1, T=2, G=3).  raw_edges = read-evidenced bits before neighbour validation,
+ * edges = validated (both endpoints survive; valid after shk_build_graph). */
+shk_status shk_export_kmers(shk_asm *h, uint64_t *key_lo, uint64_t *key_hi,
+                            uint16_t *counts, uint8_t *raw_edges, uint8_t *edges,
+                            size_t cap, size_t *n);
+/* All distinct k-mers before the filter (test/diagnostic; may be large). */
+shk_status shk_export_table(shk_asm *h, uint64_t *key_lo, uint64_t *key_hi,
+                            uint32_t *counts, uint8_t *raw_edges, size_t cap,
+                            size_t *n);
+/* Unitigs: ASCII sequences concatenated in `seq` (no separators), offsets has
+ * n_unitigs+1 entries, mean_cov = mean k-mer count, circular = 1 for a cycle. */
+shk_status shk_export_unitigs(shk_asm *h, char *seq, size_t seq_cap,
+                              uint64_t *offsets, float *mean_cov,
+                              uint8_t *circular, size_t unitig_cap);
+/* Unitig links, one per (unitig end, validated edge): from/to = unitig id * 2 +
+ * orientation (0 = forward as exported, 1 = reverse-complement); overlap k-1. */
+shk_status shk_export_links(shk_asm *h, uint32_t *from, uint32_t *to, size_t cap,
+                            size_t *n);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SHK_H */

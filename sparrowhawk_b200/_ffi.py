@@ -1,0 +1,123 @@
+"""ctypes binding of include/shk.h (libshk_b200.so) and of the read generator.
+
+The library is the product: if it is missing this module raises — there is no
+Python / CPU implementation to fall back to.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libshk_b200.so")
+GEN_PATH = os.path.join(_HERE, "libshk_gen.so")
+
+HISTO_BINS = 500
+
+STATUS_NAMES = {
+    0: "SHK_OK", 1: "SHK_ERR_BAD_ARG", 2: "SHK_ERR_NO_DEVICE", 3: "SHK_ERR_CUDA", 4: "SHK_ERR_OOM",
+    5: "SHK_ERR_TABLE_FULL", 6: "SHK_ERR_IO", 7: "SHK_ERR_FORMAT", 8: "SHK_ERR_STATE",
+}
+
+
+class ShkParams(C.Structure):
+    _fields_ = [
+        ("k", C.c_int32), ("verbose", C.c_int32), ("min_count", C.c_int32), ("min_qual", C.c_int32),
+        ("chunk_size", C.c_int64), ("do_bloom", C.c_int32), ("do_fit", C.c_int32),
+        ("no_bubble_collapse", C.c_int32), ("no_dead_end_removal", C.c_int32),
+        ("device", C.c_int32), ("reserved0", C.c_int32), ("table_slots", C.c_uint64), ("reserved1", C.c_uint64),
+    ]
+
+
+class ShkStats(C.Structure):
+    _fields_ = [
+        ("n_bases", C.c_uint64), ("n_positions", C.c_uint64), ("n_instances", C.c_uint64),
+        ("n_distinct", C.c_uint64), ("n_nodes", C.c_uint64), ("n_unitigs", C.c_uint64),
+        ("unitig_bases", C.c_uint64), ("n_links", C.c_uint64), ("table_slots", C.c_uint64),
+        ("gpu_launches", C.c_uint64), ("used_min_count", C.c_int32), ("table_retries", C.c_int32),
+        ("ms_pack", C.c_float), ("ms_count", C.c_float), ("ms_filter", C.c_float), ("ms_graph", C.c_float),
+        ("ms_extract", C.c_float), ("reserved_f", C.c_float),
+    ]
+
+
+PROGRESS_FN = C.CFUNCTYPE(None, C.c_char_p, C.c_void_p)
+
+# every symbol include/shk.h declares: name -> (restype, argtypes)
+_H = C.c_void_p
+_U8P = C.c_void_p
+SYMBOLS = {
+    "shk_asm_new": (C.c_int, [C.POINTER(ShkParams), C.POINTER(_H)]),
+    "shk_asm_free": (None, [_H]),
+    "shk_asm_set_progress_cb": (C.c_int, [_H, PROGRESS_FN, C.c_void_p]),
+    "shk_asm_preprocess_files": (C.c_int, [_H, C.c_char_p, C.c_char_p]),
+    "shk_asm_preprocess_push": (C.c_int, [_H, _U8P, C.c_size_t]),
+    "shk_asm_preprocess_finish": (C.c_int, [_H]),
+    "shk_asm_preprocess_reads": (C.c_int, [_H, _U8P, _U8P, C.c_size_t]),
+    "shk_asm_preprocessing_info": (C.c_int, [_H, C.POINTER(C.c_char_p), C.POINTER(C.c_size_t)]),
+    "shk_asm_assemble": (C.c_int, [_H]),
+    "shk_asm_get_assembly": (C.c_int, [_H, C.POINTER(C.c_char_p), C.POINTER(C.c_size_t)]),
+    "shk_last_error": (C.c_char_p, []),
+    "shk_abi_version": (C.c_int, []),
+    "shk_set_stream": (C.c_int, [_H, C.c_void_p]),
+    "shk_get_stream": (C.c_void_p, [_H]),
+    "shk_load_reads": (C.c_int, [_H, _U8P, _U8P, C.c_size_t, C.c_int]),
+    "shk_load_reads_device": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_size_t, C.c_int]),
+    "shk_count": (C.c_int, [_H, C.c_int]),
+    "shk_filter": (C.c_int, [_H]),
+    "shk_build_graph": (C.c_int, [_H]),
+    "shk_run": (C.c_int, [_H]),
+    "shk_get_stats": (C.c_int, [_H, C.POINTER(ShkStats)]),
+    "shk_get_histogram": (C.c_int, [_H, C.c_void_p]),
+    "shk_export_kmers": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t,
+                                   C.POINTER(C.c_size_t)]),
+    "shk_export_table": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t,
+                                   C.POINTER(C.c_size_t)]),
+    "shk_export_unitigs": (C.c_int, [_H, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]),
+    "shk_export_links": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]),
+}
+
+_lib = None
+_gen = None
+
+
+class ShkError(RuntimeError):
+    def __init__(self, status, message):
+        self.status = status
+        super().__init__(f"{STATUS_NAMES.get(status, status)}: {message}")
+
+
+def lib():
+    """The product library. Raises if it was not built (run __graft_entry__.build())."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(
+                f"{LIB_PATH} is missing: build it with `make -C sparrowhawk_b200/csrc` "
+                "(there is no CPU fallback for the CUDA path)")
+        L = C.CDLL(LIB_PATH)
+        for name, (res, args) in SYMBOLS.items():
+            fn = getattr(L, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = L
+    return _lib
+
+
+def check(status):
+    if status != 0:
+        raise ShkError(status, (lib().shk_last_error() or b"").decode(errors="replace"))
+
+
+def gen():
+    global _gen
+    if _gen is None:
+        if not os.path.exists(GEN_PATH):
+            raise ImportError(f"{GEN_PATH} is missing: build it with `make -C sparrowhawk_b200/csrc`")
+        G = C.CDLL(GEN_PATH)
+        G.shk_gen_num_pairs.restype = C.c_uint64
+        G.shk_gen_num_pairs.argtypes = [C.c_uint64, C.c_double, C.c_int]
+        G.shk_gen_genome.restype = None
+        G.shk_gen_genome.argtypes = [C.c_uint64, C.c_uint64, C.c_void_p]
+        G.shk_gen_reads.restype = C.c_uint64
+        G.shk_gen_reads.argtypes = [C.c_uint64, C.c_uint64, C.c_int, C.c_double, C.c_void_p, C.c_uint64,
+                                    C.c_uint64, C.c_void_p, C.c_void_p, C.c_int]
+        _gen = G
+    return _gen

@@ -1,0 +1,686 @@
+// shk_api.cu — the C ABI of include/shk.h over the sm_100a kernels.
+// Host orchestration only: buffer ownership, stage ordering, the handful of
+// scalar read-backs that size later stages, CUDA-event timing.  There is no
+// CPU implementation of any stage here: without a device every entry fails
+// with SHK_ERR_NO_DEVICE.
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <cmath>
+#include <algorithm>
+
+#include "shk_handle.h"
+
+namespace shk {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char *fmt, ...) {
+  va_list ap; va_start(ap, fmt);
+  vsnprintf(g_err, sizeof g_err, fmt, ap);
+  va_end(ap);
+}
+shk_status cuda_fail(cudaError_t e, const char *what) {
+  set_error("CUDA error %d (%s) at %s", (int)e, cudaGetErrorString(e), what);
+  cudaGetLastError();
+  return e == cudaErrorMemoryAllocation ? SHK_ERR_OOM : SHK_ERR_CUDA;
+}
+
+shk_status DevBuf::ensure(size_t bytes) {
+  if (bytes <= cap) return SHK_OK;
+  release();
+  size_t want = bytes + bytes / 8 + 256;
+  cudaError_t e = cudaMalloc(&p, want);
+  if (e != cudaSuccess) { p = nullptr; return cuda_fail(e, "cudaMalloc"); }
+  cap = want;
+  return SHK_OK;
+}
+void DevBuf::release() {
+  if (p) cudaFree(p);
+  p = nullptr; cap = 0;
+}
+
+void progress(shk_asm *h, const char *state) {
+  if (h->cb) h->cb(state, h->cb_user);
+  else if (h->p.verbose > 1) fprintf(stderr, "[shk] %s\n", state);
+}
+
+shk_status require_device(shk_asm *h) {
+  if (!h) { set_error("null handle"); return SHK_ERR_BAD_ARG; }
+  if (h->dev < 0) { set_error("no CUDA device: this library has no CPU path"); return SHK_ERR_NO_DEVICE; }
+  SHK_CUDA(cudaSetDevice(h->dev));
+  return SHK_OK;
+}
+
+#define SHK_TRY(x) do { shk_status s__ = (x); if (s__ != SHK_OK) return s__; } while (0)
+
+static shk_status read_scalars(shk_asm *h) {
+  SHK_CUDA(cudaMemcpyAsync(h->h_pinned, h->dscal.p, DSCAL_BYTES, cudaMemcpyDeviceToHost, h->stream));
+  SHK_CUDA(cudaStreamSynchronize(h->stream));
+  return SHK_OK;
+}
+
+// ---- K0: load + pack -------------------------------------------------
+static shk_status pack_from_device(shk_asm *h, const uint8_t *d_seq, const uint8_t *d_qual, size_t n, int append) {
+  uint64_t base_word = append ? h->nwords : 0;
+  uint64_t add_words = (n + 31) / 32;
+  uint64_t total = base_word + add_words;
+  // layout: [1 zero word][total words][4 zero words]
+  size_t need_b = (total + 5) * 8, need_m = (total + 5) * 4;
+  if (need_b > h->bases.cap) {
+    DevBuf nb, nm;
+    SHK_TRY(nb.ensure(need_b + (append ? need_b / 2 : 0)));
+    SHK_TRY(nm.ensure(need_m + (append ? need_m / 2 : 0)));
+    if (append && base_word) {
+      SHK_CUDA(cudaMemcpyAsync(nb.p, h->bases.p, (base_word + 1) * 8, cudaMemcpyDeviceToDevice, h->stream));
+      SHK_CUDA(cudaMemcpyAsync(nm.p, h->mask.p, (base_word + 1) * 4, cudaMemcpyDeviceToDevice, h->stream));
+      SHK_CUDA(cudaStreamSynchronize(h->stream));
+    }
+    h->bases.release(); h->mask.release();
+    h->bases = nb; h->mask = nm;
+  }
+  uint64_t *b = h->bases.as<uint64_t>() + 1;
+  uint32_t *m = h->mask.as<uint32_t>() + 1;
+  if (!append || base_word == 0) {
+    SHK_CUDA(cudaMemsetAsync(h->bases.p, 0, 8, h->stream));
+    SHK_CUDA(cudaMemsetAsync(h->mask.p, 0, 4, h->stream));
+    SHK_CUDA(cudaMemsetAsync(d_counters(h) + 3, 0, 8, h->stream));   // bases of the resident reads
+    h->n_positions = 0;
+  }
+  SHK_CUDA(cudaMemsetAsync(b + total, 0, 4 * 8, h->stream));
+  SHK_CUDA(cudaMemsetAsync(m + total, 0, 4 * 4, h->stream));
+  h->st.gpu_launches += launch_pack_reads(d_seq, d_qual, n, add_words, h->p.min_qual, b + base_word, m + base_word,
+                                          d_counters(h) + 3, h->stream);
+  SHK_CUDA(cudaGetLastError());
+  h->nwords = total;
+  h->n_positions += n;
+  h->counted = h->filtered = h->graphed = false;
+  return SHK_OK;
+}
+
+static shk_status load_reads_host(shk_asm *h, const uint8_t *seq, const uint8_t *qual, size_t n, int append) {
+  SHK_TRY(require_device(h));
+  if (!seq && n) { set_error("seq is null"); return SHK_ERR_BAD_ARG; }
+  SHK_CUDA(cudaEventRecord(h->ev[0], h->stream));
+  SHK_TRY(h->ascii_seq.ensure(n + 64));
+  if (qual) SHK_TRY(h->ascii_qual.ensure(n + 64));
+  // H2D in slices so that a pinned caller buffer streams at link rate and the
+  // pack kernel of slice i overlaps the copy of slice i+1 is left to the
+  // copy engine; one stream keeps ordering trivial.
+  if (n) {
+    SHK_CUDA(cudaMemcpyAsync(h->ascii_seq.p, seq, n, cudaMemcpyHostToDevice, h->stream));
+    if (qual) SHK_CUDA(cudaMemcpyAsync(h->ascii_qual.p, qual, n, cudaMemcpyHostToDevice, h->stream));
+  }
+  SHK_TRY(pack_from_device(h, h->ascii_seq.as<uint8_t>(), qual ? h->ascii_qual.as<uint8_t>() : nullptr, n, append));
+  SHK_CUDA(cudaEventRecord(h->ev[1], h->stream));
+  return SHK_OK;
+}
+
+// ---- K1: count ---------------------------------------------------------
+static uint64_t auto_table_slots(shk_asm *h, uint64_t positions) {
+  if (h->p.table_slots) return std::max<uint64_t>(h->p.table_slots, 64);
+  // distinct k-mers <= instances <= positions; sequencing reads at >= 20x carry
+  // ~0.1-0.5 distinct k-mers per base: start at 0.30 slots per
+  // position and grow on overflow.
+  return std::max<uint64_t>(1024, (uint64_t)((double)positions * 0.30));
+}
+
+static shk_status table_alloc_fill(shk_asm *h, DevBuf &buf, uint64_t cap) {
+  SHK_TRY(buf.ensure(cap * slot_bytes(h->kw)));
+  h->st.gpu_launches += launch_table_fill(buf.p, cap, h->kw, h->stream);
+  SHK_CUDA(cudaGetLastError());
+  return SHK_OK;
+}
+
+static shk_status grow_table(shk_asm *h, uint64_t new_cap) {
+  for (int attempt = 0; attempt < 4; ++attempt, new_cap *= 2) {
+    DevBuf nb;
+    SHK_TRY(nb.ensure(new_cap * slot_bytes(h->kw)));
+    h->st.gpu_launches += launch_table_fill(nb.p, new_cap, h->kw, h->stream);
+    SHK_CUDA(cudaMemsetAsync(d_flags(h), 0, 4, h->stream));
+    h->st.gpu_launches += launch_rehash(h->kw, h->slots.p, h->cap, nb.p, new_cap, d_flags(h), h->stream);
+    SHK_CUDA(cudaGetLastError());
+    SHK_TRY(read_scalars(h));
+    uint32_t ovf = *(uint32_t *)(h->h_pinned + 8 + SHK_HISTO_BINS);
+    if (!ovf) {
+      h->slots.release();
+      h->slots = nb; h->cap = new_cap;
+      return SHK_OK;
+    }
+    nb.release();
+  }
+  set_error("k-mer table overflow while growing");
+  return SHK_ERR_TABLE_FULL;
+}
+
+static shk_status count_impl(shk_asm *h, int reset) {
+  SHK_TRY(require_device(h));
+  if (!h->nwords && reset) { /* empty input is legal: zero k-mers */ }
+  if (!reset && !h->table_live) reset = 1;
+  SHK_CUDA(cudaEventRecord(h->ev[2], h->stream));
+  const uint64_t *b = h->bases.as<uint64_t>() + 1;
+  const uint32_t *m = h->mask.as<uint32_t>() + 1;
+  if (reset) {
+    uint64_t cap = auto_table_slots(h, h->nwords * 32);
+    h->st.table_retries = 0;
+    for (;;) {
+      h->cap = cap;
+      SHK_TRY(table_alloc_fill(h, h->slots, cap));
+      SHK_CUDA(cudaMemsetAsync(d_counters(h) + 1, 0, 16, h->stream));   // n_instances, n_distinct
+      SHK_CUDA(cudaMemsetAsync(d_flags(h), 0, 4, h->stream));
+      SHK_CUDA(cudaEventRecord(h->ev[8], h->stream));
+      if (h->nwords)
+        h->st.gpu_launches += launch_extract_count(h->kw, b, m, h->nwords, h->p.k, h->slots.p, h->cap,
+                                                   d_counters(h), d_flags(h), h->stream);
+      SHK_CUDA(cudaGetLastError());
+      SHK_CUDA(cudaEventRecord(h->ev[9], h->stream));
+      SHK_CUDA(cudaEventRecord(h->ev[3], h->stream));
+      SHK_TRY(read_scalars(h));
+      uint32_t ovf = *(uint32_t *)(h->h_pinned + 8 + SHK_HISTO_BINS);
+      uint64_t distinct = h->h_pinned[2];
+      // a table above 90 % load has degenerate probe lengths even if it fitted
+      if (!ovf && distinct * 10 <= cap * 9) break;
+      if (++h->st.table_retries > 8) { set_error("k-mer table overflow (cap %llu)", (unsigned long long)cap); return SHK_ERR_TABLE_FULL; }
+      cap = std::max<uint64_t>(cap * 2, distinct * 2);
+    }
+  } else {
+    // chunked accumulation: keep load <= 0.7 assuming every new position is a new k-mer
+    SHK_TRY(read_scalars(h));
+    uint64_t distinct = h->h_pinned[2];
+    uint64_t worst = distinct + h->nwords * 32;
+    if (worst * 10 > h->cap * 7) SHK_TRY(grow_table(h, std::max<uint64_t>(h->cap * 2, worst * 2)));
+    SHK_CUDA(cudaMemsetAsync(d_flags(h), 0, 4, h->stream));
+    SHK_CUDA(cudaEventRecord(h->ev[8], h->stream));
+    if (h->nwords)
+      h->st.gpu_launches += launch_extract_count(h->kw, b, m, h->nwords, h->p.k, h->slots.p, h->cap, d_counters(h),
+                                                 d_flags(h), h->stream);
+    SHK_CUDA(cudaGetLastError());
+    SHK_CUDA(cudaEventRecord(h->ev[9], h->stream));
+    SHK_CUDA(cudaEventRecord(h->ev[3], h->stream));
+    SHK_TRY(read_scalars(h));
+    if (*(uint32_t *)(h->h_pinned + 8 + SHK_HISTO_BINS)) { set_error("k-mer table overflow in chunked mode"); return SHK_ERR_TABLE_FULL; }
+  }
+  // totals over everything counted into the live table (chunked mode adds up)
+  h->n_bases = (reset ? 0 : h->n_bases) + h->h_pinned[3];
+  h->counted_positions = (reset ? 0 : h->counted_positions) + h->n_positions;
+  h->st.n_bases = h->n_bases;
+  h->st.n_positions = h->counted_positions;
+  h->st.n_instances = h->h_pinned[1];
+  h->st.n_distinct = h->h_pinned[2];
+  h->st.table_slots = h->cap;
+  h->table_live = true; h->counted = true; h->filtered = h->graphed = false;
+  return SHK_OK;
+}
+
+// ---- K2: histogram + filter + compaction ---------------------------------
+static shk_status histogram_impl(shk_asm *h) {
+  SHK_CUDA(cudaMemsetAsync(d_histo(h), 0, SHK_HISTO_BINS * 8, h->stream));
+  h->st.gpu_launches += launch_histogram_only(h->kw, h->slots.p, h->cap, d_histo(h), h->stream);
+  SHK_CUDA(cudaGetLastError());
+  SHK_TRY(read_scalars(h));
+  memcpy(h->histo, h->h_pinned + 8, sizeof h->histo);
+  return SHK_OK;
+}
+
+static shk_status filter_impl(shk_asm *h, int min_count) {
+  SHK_TRY(require_device(h));
+  if (!h->counted || !h->table_live) { set_error("filter before count"); return SHK_ERR_STATE; }
+  SHK_CUDA(cudaEventRecord(h->ev[4], h->stream));
+  uint64_t nd = h->st.n_distinct;
+  if (nd > 0xFFFFFFF0ull) { set_error("more than 2^32 distinct k-mers"); return SHK_ERR_BAD_ARG; }
+  uint32_t node_cap = (uint32_t)std::max<uint64_t>(nd, 1);
+  SHK_TRY(h->node_lo.ensure((size_t)node_cap * 8));
+  if (h->kw == 2) SHK_TRY(h->node_hi.ensure((size_t)node_cap * 8));
+  SHK_TRY(h->node_count.ensure((size_t)node_cap * 2));
+  SHK_TRY(h->node_raw.ensure((size_t)node_cap));
+  h->node_cap = node_cap;
+  SHK_CUDA(cudaMemsetAsync(d_histo(h), 0, SHK_HISTO_BINS * 8, h->stream));
+  SHK_CUDA(cudaMemsetAsync(d_flags(h) + 1, 0, 4, h->stream));   // n_nodes
+  h->st.gpu_launches += launch_histogram_filter(h->kw, h->slots.p, h->cap, min_count, d_histo(h),
+                                                h->node_lo.as<uint64_t>(), h->node_hi.as<uint64_t>(),
+                                                h->node_count.as<uint16_t>(), h->node_raw.as<uint8_t>(), node_cap,
+                                                d_flags(h) + 1, h->stream);
+  SHK_CUDA(cudaGetLastError());
+  SHK_CUDA(cudaEventRecord(h->ev[5], h->stream));
+  SHK_TRY(read_scalars(h));
+  memcpy(h->histo, h->h_pinned + 8, sizeof h->histo);
+  h->st.n_nodes = ((uint32_t *)(h->h_pinned + 8 + SHK_HISTO_BINS))[1];
+  h->st.used_min_count = min_count;
+  h->table_live = false;      // count words now hold node ids
+  h->filtered = true; h->graphed = false;
+  h->hu.valid = false;
+  return SHK_OK;
+}
+
+// ---- K3..K6: graph ---------------------------------------------------------
+static shk_status graph_impl(shk_asm *h) {
+  SHK_TRY(require_device(h));
+  if (!h->filtered) { set_error("build_graph before filter"); return SHK_ERR_STATE; }
+  SHK_CUDA(cudaEventRecord(h->ev[6], h->stream));
+  const uint32_t N = (uint32_t)h->st.n_nodes;
+  const size_t ne = 2 * (size_t)N;
+  const int k = h->p.k;
+  h->st.n_unitigs = 0; h->st.unitig_bases = 0; h->st.n_links = 0;
+  if (N == 0) {
+    SHK_CUDA(cudaEventRecord(h->ev[7], h->stream));
+    SHK_CUDA(cudaStreamSynchronize(h->stream));
+    h->graphed = true;
+    return SHK_OK;
+  }
+  if (N > 0x7FFFFFF0u) { set_error("too many nodes"); return SHK_ERR_BAD_ARG; }
+  SHK_TRY(h->node_edges.ensure(N));
+  SHK_TRY(h->uniq.ensure(ne * 4)); SHK_TRY(h->succ.ensure(ne * 4));
+  SHK_TRY(h->tail_of.ensure(ne * 4)); SHK_TRY(h->len_of.ensure(ne * 4));
+  SHK_TRY(h->unitig_of_head.ensure(ne * 4)); SHK_TRY(h->elem_unitig.ensure(ne * 4));
+  SHK_TRY(h->pd.ensure(ne * 8));
+  SHK_TRY(h->recs.ensure((size_t)N * unitig_rec_bytes()));
+  SHK_TRY(h->ucirc.ensure(N)); SHK_TRY(h->cov_sum.ensure((size_t)N * 8));
+  SHK_TRY(h->useq.ensure((size_t)N * (size_t)k));
+  uint32_t link_cap = (uint32_t)std::min<uint64_t>(4ull * N + 64, 0x7FFFFFFFull);
+  SHK_TRY(h->link_from.ensure((size_t)link_cap * 4)); SHK_TRY(h->link_to.ensure((size_t)link_cap * 4));
+  SHK_TRY(h->gscal.ensure(64));
+  SHK_CUDA(cudaMemsetAsync(h->gscal.p, 0, 64, h->stream));
+  SHK_CUDA(cudaMemsetAsync(h->tail_of.p, 0xFF, ne * 4, h->stream));
+  SHK_CUDA(cudaMemsetAsync(h->cov_sum.p, 0, (size_t)N * 8, h->stream));
+
+  GraphBuffers g{};
+  g.node_lo = h->node_lo.as<uint64_t>(); g.node_hi = h->kw == 2 ? h->node_hi.as<uint64_t>() : nullptr;
+  g.node_count = h->node_count.as<uint16_t>(); g.node_raw = h->node_raw.as<uint8_t>();
+  g.node_edges = h->node_edges.as<uint8_t>(); g.n_nodes = N;
+  g.uniq = h->uniq.as<uint32_t>(); g.succ = h->succ.as<uint32_t>(); g.tail_of = h->tail_of.as<uint32_t>();
+  g.len_of = h->len_of.as<uint32_t>(); g.unitig_of_head = h->unitig_of_head.as<uint32_t>();
+  g.elem_unitig = h->elem_unitig.as<uint32_t>(); g.pd = h->pd.as<uint64_t>();
+  g.recs = h->recs.p; g.ucirc = h->ucirc.as<uint8_t>(); g.cov_sum = h->cov_sum.as<uint64_t>();
+  g.seq = h->useq.as<char>(); g.link_from = h->link_from.as<uint32_t>(); g.link_to = h->link_to.as<uint32_t>();
+  g.link_cap = link_cap; g.scal = h->gscal.as<uint32_t>(); g.seq_cursor = (uint64_t *)(h->gscal.as<uint32_t>() + 8);
+  g.cq = nullptr; g.circ = nullptr;
+
+  uint64_t &L = h->st.gpu_launches;
+  L += launch_build_edges(h->kw, h->slots.p, h->cap, k, g, h->stream);
+  L += launch_links_and_rank_init(g, h->stream);
+  // each launch multiplies the resolved distance by >= 5 (4 in-place jumps)
+  int rounds = 2;
+  for (double d = 1; d < (double)ne; d *= 5.0) ++rounds;
+  for (int r = 0; r < rounds; ++r) L += launch_rank_jump(g, h->stream);
+  // cycles: anything not hanging off a true head now
+  SHK_TRY(h->cq.ensure(ne * 8));
+  g.cq = h->cq.as<uint64_t>();
+  L += launch_cycle_init(g, h->stream);
+  SHK_CUDA(cudaGetLastError());
+  uint32_t hs[16];
+  SHK_CUDA(cudaMemcpyAsync(hs, h->gscal.p, 64, cudaMemcpyDeviceToHost, h->stream));
+  SHK_CUDA(cudaStreamSynchronize(h->stream));
+  bool have_circ = hs[1] != 0;
+  if (have_circ) {
+    SHK_TRY(h->circ.ensure(ne));
+    g.circ = h->circ.as<uint8_t>();
+    int cr = 1;
+    for (uint64_t d = 1; d < (uint64_t)hs[1]; d *= 2) ++cr;
+    for (int r = 0; r < cr; ++r) L += launch_cycle_jump(g, h->stream);
+    L += launch_cycle_cut(g, h->stream);
+    for (int r = 0; r < rounds; ++r) L += launch_rank_jump(g, h->stream);
+  }
+  L += launch_unitig_tails_heads(g, k, have_circ, h->stream);
+  L += launch_unitig_emit(h->kw, g, k, h->stream);
+  SHK_CUDA(cudaGetLastError());
+  SHK_CUDA(cudaMemcpyAsync(hs, h->gscal.p, 64, cudaMemcpyDeviceToHost, h->stream));
+  SHK_CUDA(cudaStreamSynchronize(h->stream));
+  uint32_t nu = hs[2];
+  uint64_t seq_len; memcpy(&seq_len, hs + 8, 8);
+  L += launch_unitig_links_out(h->kw, h->slots.p, h->cap, k, g, nu, h->stream);
+  SHK_CUDA(cudaGetLastError());
+  SHK_CUDA(cudaEventRecord(h->ev[7], h->stream));
+  SHK_CUDA(cudaMemcpyAsync(hs, h->gscal.p, 64, cudaMemcpyDeviceToHost, h->stream));
+  SHK_CUDA(cudaStreamSynchronize(h->stream));
+  if (hs[3] > link_cap) { set_error("unitig link buffer overflow (%u > %u)", hs[3], link_cap); return SHK_ERR_OOM; }
+  h->st.n_unitigs = nu; h->st.unitig_bases = seq_len; h->st.n_links = hs[3];
+  h->graphed = true; h->hu.valid = false;
+  return SHK_OK;
+}
+
+static void collect_timing(shk_asm *h) {
+  auto el = [&](int a, int b) { float ms = 0; if (cudaEventElapsedTime(&ms, h->ev[a], h->ev[b]) != cudaSuccess) { cudaGetLastError(); ms = 0; } return ms; };
+  h->st.ms_pack = el(0, 1); h->st.ms_count = el(2, 3); h->st.ms_extract = el(8, 9); h->st.ms_filter = el(4, 5); h->st.ms_graph = el(6, 7);
+}
+
+}  // namespace shk
+
+using namespace shk;
+
+extern "C" {
+
+int shk_abi_version(void) { return SHK_ABI_VERSION; }
+const char *shk_last_error(void) { return g_err; }
+
+shk_status shk_asm_new(const shk_params *params, shk_asm **out) {
+  if (!params || !out) { set_error("null argument"); return SHK_ERR_BAD_ARG; }
+  *out = nullptr;
+  if (params->k < 3 || params->k > 63 || !(params->k & 1)) {
+    set_error("k must be odd and in [3, 63] (got %d)", params->k);
+    return SHK_ERR_BAD_ARG;
+  }
+  if (params->min_count < 0 || params->min_qual < 0 || params->chunk_size < 0) { set_error("negative parameter"); return SHK_ERR_BAD_ARG; }
+  shk_asm *h = new (std::nothrow) shk_asm();
+  if (!h) { set_error("out of host memory"); return SHK_ERR_OOM; }
+  h->p = *params;
+  h->kw = params->k <= 31 ? 1 : 2;
+  memset(&h->st, 0, sizeof h->st);
+  memset(h->histo, 0, sizeof h->histo);
+  h->st.used_min_count = params->min_count;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+    cudaGetLastError();
+    h->dev = -1;               // handle exists (parameters were valid) but cannot compute
+    *out = h;
+    progress(h, "initialised");
+    return SHK_OK;
+  }
+  int dev = params->device;
+  if (dev < 0) { if (cudaGetDevice(&dev) != cudaSuccess) dev = 0; }
+  if (dev >= ndev) { delete h; set_error("device %d out of range", dev); return SHK_ERR_BAD_ARG; }
+  h->dev = dev;
+  cudaDeviceProp prop;
+  if (cudaSetDevice(dev) != cudaSuccess || cudaGetDeviceProperties(&prop, dev) != cudaSuccess) {
+    delete h; return cuda_fail(cudaGetLastError(), "cudaSetDevice");
+  }
+  if (prop.major < 10) {
+    delete h; set_error("device %d is sm_%d%d; this library is built for sm_100a only", dev, prop.major, prop.minor);
+    return SHK_ERR_NO_DEVICE;
+  }
+  if (cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking) != cudaSuccess) { delete h; return cuda_fail(cudaGetLastError(), "cudaStreamCreate"); }
+  h->stream = h->own_stream;
+  for (auto &e : h->ev) cudaEventCreate(&e);
+  if (h->dscal.ensure(DSCAL_BYTES) != SHK_OK || cudaMallocHost((void **)&h->h_pinned, DSCAL_BYTES) != cudaSuccess) {
+    shk_asm_free(h); set_error("scalar buffer allocation failed"); return SHK_ERR_OOM;
+  }
+  cudaMemsetAsync(h->dscal.p, 0, DSCAL_BYTES, h->stream);
+  memset(h->h_pinned, 0, DSCAL_BYTES);
+  *out = h;
+  progress(h, "initialised");
+  return SHK_OK;
+}
+
+void shk_asm_free(shk_asm *h) {
+  if (!h) return;
+  if (h->dev >= 0) {
+    cudaSetDevice(h->dev);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    DevBuf *bufs[] = {&h->bases, &h->mask, &h->ascii_seq, &h->ascii_qual, &h->slots, &h->dscal, &h->node_lo, &h->node_hi,
+                      &h->node_count, &h->node_raw, &h->node_edges, &h->uniq, &h->succ, &h->tail_of, &h->len_of,
+                      &h->unitig_of_head, &h->elem_unitig, &h->pd, &h->cq, &h->circ, &h->recs, &h->ucirc, &h->cov_sum,
+                      &h->useq, &h->link_from, &h->link_to, &h->gscal};
+    for (auto b : bufs) b->release();
+    if (h->h_pinned) cudaFreeHost(h->h_pinned);
+    for (auto &e : h->ev) if (e) cudaEventDestroy(e);
+    if (h->own_stream) cudaStreamDestroy(h->own_stream);
+  }
+  delete h;
+}
+
+shk_status shk_asm_set_progress_cb(shk_asm *h, shk_progress_fn fn, void *user) {
+  if (!h) { set_error("null handle"); return SHK_ERR_BAD_ARG; }
+  h->cb = fn; h->cb_user = user;
+  return SHK_OK;
+}
+
+shk_status shk_set_stream(shk_asm *h, void *stream) {
+  if (!h) { set_error("null handle"); return SHK_ERR_BAD_ARG; }
+  h->stream = stream ? (cudaStream_t)stream : h->own_stream;
+  return SHK_OK;
+}
+void *shk_get_stream(shk_asm *h) { return h ? (void *)h->stream : nullptr; }
+
+shk_status shk_load_reads(shk_asm *h, const uint8_t *seq, const uint8_t *qual, size_t n, int append) {
+  return load_reads_host(h, seq, qual, n, append);
+}
+shk_status shk_load_reads_device(shk_asm *h, const void *d_seq, const void *d_qual, size_t n, int append) {
+  SHK_TRY(require_device(h));
+  SHK_CUDA(cudaEventRecord(h->ev[0], h->stream));
+  SHK_TRY(pack_from_device(h, (const uint8_t *)d_seq, (const uint8_t *)d_qual, n, append));
+  SHK_CUDA(cudaEventRecord(h->ev[1], h->stream));
+  return SHK_OK;
+}
+shk_status shk_count(shk_asm *h, int reset) { return count_impl(h, reset); }
+shk_status shk_filter(shk_asm *h) { if (!h) { set_error("null handle"); return SHK_ERR_BAD_ARG; } return filter_impl(h, h->p.min_count); }
+shk_status shk_build_graph(shk_asm *h) { return graph_impl(h); }
+shk_status shk_run(shk_asm *h) {
+  SHK_TRY(count_impl(h, 1));
+  SHK_TRY(filter_impl(h, h->p.min_count));
+  return graph_impl(h);
+}
+shk_status shk_get_stats(shk_asm *h, shk_stats *out) {
+  if (!h || !out) { set_error("null argument"); return SHK_ERR_BAD_ARG; }
+  if (h->dev >= 0) collect_timing(h);
+  *out = h->st;
+  return SHK_OK;
+}
+shk_status shk_get_histogram(shk_asm *h, uint64_t *histo) {
+  if (!h || !histo) { set_error("null argument"); return SHK_ERR_BAD_ARG; }
+  if (h->counted && !h->filtered && h->table_live) SHK_TRY(histogram_impl(h));
+  memcpy(histo, h->histo, sizeof h->histo);
+  return SHK_OK;
+}
+
+// ---- exports ---------------------------------------------------------------
+shk_status shk_export_kmers(shk_asm *h, uint64_t *key_lo, uint64_t *key_hi, uint16_t *counts, uint8_t *raw_edges,
+                            uint8_t *edges, size_t cap, size_t *n) {
+  SHK_TRY(require_device(h));
+  if (!h->filtered) { set_error("export_kmers before filter"); return SHK_ERR_STATE; }
+  size_t N = h->st.n_nodes;
+  if (n) *n = N;
+  if (cap < N) { set_error("export buffer too small (%zu < %zu)", cap, N); return SHK_ERR_BAD_ARG; }
+  if (!N) return SHK_OK;
+  if (key_lo) SHK_CUDA(cudaMemcpyAsync(key_lo, h->node_lo.p, N * 8, cudaMemcpyDeviceToHost, h->stream));
+  if (key_hi) {
+    if (h->kw == 2) SHK_CUDA(cudaMemcpyAsync(key_hi, h->node_hi.p, N * 8, cudaMemcpyDeviceToHost, h->stream));
+    else memset(key_hi, 0, N * 8);
+  }
+  if (counts) SHK_CUDA(cudaMemcpyAsync(counts, h->node_count.p, N * 2, cudaMemcpyDeviceToHost, h->stream));
+  if (raw_edges) SHK_CUDA(cudaMemcpyAsync(raw_edges, h->node_raw.p, N, cudaMemcpyDeviceToHost, h->stream));
+  if (edges) {
+    if (!h->graphed) { set_error("validated edges need build_graph"); return SHK_ERR_STATE; }
+    SHK_CUDA(cudaMemcpyAsync(edges, h->node_edges.p, N, cudaMemcpyDeviceToHost, h->stream));
+  }
+  SHK_CUDA(cudaStreamSynchronize(h->stream));
+  return SHK_OK;
+}
+
+shk_status shk_export_table(shk_asm *h, uint64_t *key_lo, uint64_t *key_hi, uint32_t *counts, uint8_t *raw_edges,
+                            size_t cap, size_t *n) {
+  SHK_TRY(require_device(h));
+  if (!h->counted || !h->table_live) { set_error("export_table needs a live table (after count, before filter)"); return SHK_ERR_STATE; }
+  size_t nd = h->st.n_distinct;
+  if (n) *n = nd;
+  if (cap < nd) { set_error("export buffer too small"); return SHK_ERR_BAD_ARG; }
+  // diagnostic path: slot array to host in slices, compaction on the host
+  const size_t sb = slot_bytes(h->kw), slice = (size_t)1 << 22;
+  std::vector<uint8_t> buf(slice * sb);
+  size_t o = 0;
+  for (uint64_t s0 = 0; s0 < h->cap; s0 += slice) {
+    size_t cnt = (size_t)std::min<uint64_t>(slice, h->cap - s0);
+    SHK_CUDA(cudaMemcpyAsync(buf.data(), (const uint8_t *)h->slots.p + s0 * sb, cnt * sb, cudaMemcpyDeviceToHost, h->stream));
+    SHK_CUDA(cudaStreamSynchronize(h->stream));
+    for (size_t i = 0; i < cnt; ++i) {
+      const uint64_t *w = (const uint64_t *)(buf.data() + i * sb);
+      uint64_t lo = w[0], hi = h->kw == 2 ? w[1] : 0;
+      bool empty = h->kw == 2 ? (hi == ~0ull) : (lo == ~0ull);
+      if (empty) continue;
+      const uint32_t *cv = (const uint32_t *)(w + (h->kw == 2 ? 2 : 1));
+      if (o >= cap) { set_error("table holds more live slots than n_distinct"); return SHK_ERR_STATE; }
+      if (key_lo) key_lo[o] = lo;
+      if (key_hi) key_hi[o] = hi;
+      if (counts) counts[o] = cv[0];
+      if (raw_edges) raw_edges[o] = (uint8_t)cv[1];
+      ++o;
+    }
+  }
+  if (n) *n = o;
+  return SHK_OK;
+}
+
+}  // extern "C"
+namespace shk {
+// device unitigs → host, reordered by unitig id
+shk_status fetch_unitigs(shk_asm *h) {
+  if (h->hu.valid) return SHK_OK;
+  SHK_TRY(require_device(h));
+  if (!h->graphed) { set_error("unitigs need build_graph"); return SHK_ERR_STATE; }
+  HostUnitigs &u = h->hu;
+  size_t nu = h->st.n_unitigs, k = (size_t)h->p.k;
+  u.seq.assign(h->st.unitig_bases, 0); u.off.assign(nu + 1, 0); u.cov.assign(nu, 0.f); u.circ.assign(nu, 0);
+  u.link_from.assign(h->st.n_links, 0); u.link_to.assign(h->st.n_links, 0);
+  if (nu) {
+    struct Rec { uint32_t head, len; uint64_t off; };
+    std::vector<Rec> recs(nu); std::vector<uint64_t> cs(nu); std::vector<char> raw(h->st.unitig_bases);
+    SHK_CUDA(cudaMemcpyAsync(recs.data(), h->recs.p, nu * sizeof(Rec), cudaMemcpyDeviceToHost, h->stream));
+    SHK_CUDA(cudaMemcpyAsync(cs.data(), h->cov_sum.p, nu * 8, cudaMemcpyDeviceToHost, h->stream));
+    SHK_CUDA(cudaMemcpyAsync(u.circ.data(), h->ucirc.p, nu, cudaMemcpyDeviceToHost, h->stream));
+    SHK_CUDA(cudaMemcpyAsync(raw.data(), h->useq.p, raw.size(), cudaMemcpyDeviceToHost, h->stream));
+    if (h->st.n_links) {
+      SHK_CUDA(cudaMemcpyAsync(u.link_from.data(), h->link_from.p, h->st.n_links * 4, cudaMemcpyDeviceToHost, h->stream));
+      SHK_CUDA(cudaMemcpyAsync(u.link_to.data(), h->link_to.p, h->st.n_links * 4, cudaMemcpyDeviceToHost, h->stream));
+    }
+    SHK_CUDA(cudaStreamSynchronize(h->stream));
+    uint64_t p = 0;
+    for (size_t i = 0; i < nu; ++i) {
+      size_t len = recs[i].len + k - 1;
+      u.off[i] = p;
+      memcpy(u.seq.data() + p, raw.data() + recs[i].off, len);
+      u.cov[i] = (float)((double)cs[i] / (double)recs[i].len);
+      p += len;
+    }
+    u.off[nu] = p;
+  }
+  u.valid = true;
+  return SHK_OK;
+}
+}  // namespace shk
+extern "C" {
+
+shk_status shk_export_unitigs(shk_asm *h, char *seq, size_t seq_cap, uint64_t *offsets, float *mean_cov,
+                              uint8_t *circular, size_t unitig_cap) {
+  SHK_TRY(fetch_unitigs(h));
+  const HostUnitigs &u = h->hu;
+  size_t nu = u.cov.size();
+  if (seq_cap < u.seq.size() || unitig_cap < nu) { set_error("export buffer too small"); return SHK_ERR_BAD_ARG; }
+  if (seq && !u.seq.empty()) memcpy(seq, u.seq.data(), u.seq.size());
+  if (offsets) memcpy(offsets, u.off.data(), (nu + 1) * 8);
+  if (mean_cov && nu) memcpy(mean_cov, u.cov.data(), nu * 4);
+  if (circular && nu) memcpy(circular, u.circ.data(), nu);
+  return SHK_OK;
+}
+
+shk_status shk_export_links(shk_asm *h, uint32_t *from, uint32_t *to, size_t cap, size_t *n) {
+  SHK_TRY(fetch_unitigs(h));
+  size_t nl = h->hu.link_from.size();
+  if (n) *n = nl;
+  if (cap < nl) { set_error("export buffer too small"); return SHK_ERR_BAD_ARG; }
+  if (nl && from) memcpy(from, h->hu.link_from.data(), nl * 4);
+  if (nl && to) memcpy(to, h->hu.link_to.data(), nl * 4);
+  return SHK_OK;
+}
+
+// ---- reference-facing entry points -------------------------------------------
+shk_status shk_internal_finish_preprocess(shk_asm *h, const char *mode) {
+  char st[96];
+  int mc = h->p.min_count;
+  if (h->p.do_fit) {
+    snprintf(st, sizeof st, "preprocess:%s:fitting", mode); progress(h, st);
+    SHK_TRY(histogram_impl(h));
+    mc = shk::fit_min_count(h->histo, h->p.min_count);
+  }
+  snprintf(st, sizeof st, "preprocess:%s:filtering", mode); progress(h, st);
+  SHK_TRY(filter_impl(h, mc));
+  progress(h, "preprocess:saving");
+  std::string &j = h->json_pre;
+  j.clear(); j.reserve(4096);
+  j += "{\"nkmers\":" + std::to_string(h->st.n_nodes) + ",\"histo\":[";
+  for (int i = 0; i < SHK_HISTO_BINS; ++i) { if (i) j += ','; j += std::to_string(h->histo[i]); }
+  j += "],\"used_min_count\":" + std::to_string(h->st.used_min_count) + "}";
+  progress(h, "preprocess:end");
+  return SHK_OK;
+}
+
+shk_status shk_asm_preprocess_reads(shk_asm *h, const uint8_t *seq, const uint8_t *qual, size_t n) {
+  SHK_TRY(require_device(h));
+  progress(h, "preprocess:start");
+  progress(h, "preprocess:bulk:start");
+  progress(h, "preprocess:bulk:loop:start");
+  SHK_TRY(load_reads_host(h, seq, qual, n, 0));
+  progress(h, "preprocess:bulk:loop:end");
+  progress(h, "preprocess:bulk:sorting");   // the counting step (reference bulk mode sorts; we hash)
+  SHK_TRY(count_impl(h, 1));
+  return shk_internal_finish_preprocess(h, "bulk");
+}
+
+shk_status shk_asm_preprocessing_info(shk_asm *h, const char **json, size_t *len) {
+  if (!h || !json) { set_error("null argument"); return SHK_ERR_BAD_ARG; }
+  if (!h->filtered) { set_error("get_preprocessing_info before preprocess"); return SHK_ERR_STATE; }
+  *json = h->json_pre.c_str();
+  if (len) *len = h->json_pre.size();
+  return SHK_OK;
+}
+
+shk_status shk_asm_assemble(shk_asm *h) {
+  SHK_TRY(require_device(h));
+  if (!h->filtered) { set_error("assemble before preprocess"); return SHK_ERR_STATE; }
+  progress(h, "assembly:start");
+  progress(h, "assembly:create_graph");
+  if (!h->graphed) SHK_TRY(graph_impl(h));
+  SHK_TRY(fetch_unitigs(h));
+  SHK_TRY(shk::build_assembly_json(h));     // correct_graph / collapse_graph / saving states inside
+  progress(h, "assembly:end");
+  return SHK_OK;
+}
+
+shk_status shk_asm_get_assembly(shk_asm *h, const char **json, size_t *len) {
+  if (!h || !json) { set_error("null argument"); return SHK_ERR_BAD_ARG; }
+  if (h->json_asm.empty()) { set_error("get_assembly before assemble"); return SHK_ERR_STATE; }
+  *json = h->json_asm.c_str();
+  if (len) *len = h->json_asm.size();
+  return SHK_OK;
+}
+
+// Batch boundary of the streaming / file forms: counts the reads parsed so far.
+shk_status shk_internal_flush_batch(shk_asm *h, bool final_batch) {
+  if (h->hseq.empty() && !(final_batch && !h->any_batch_counted)) return SHK_OK;
+  SHK_TRY(load_reads_host(h, h->hseq.data(), h->hqual.data(), h->hseq.size(), 0));
+  SHK_TRY(count_impl(h, h->any_batch_counted ? 0 : 1));
+  h->any_batch_counted = true;
+  h->hseq.clear(); h->hqual.clear(); h->batch_reads = 0;
+  return SHK_OK;
+}
+
+shk_status shk_asm_preprocess_push(shk_asm *h, const uint8_t *bytes, size_t n) {
+  SHK_TRY(require_device(h));
+  if (!bytes && n) { set_error("null bytes"); return SHK_ERR_BAD_ARG; }
+  if (!h->streaming) {
+    h->streaming = true; h->any_batch_counted = false; h->total_reads = 0; h->batch_reads = 0; h->line_in_rec = 0;
+    h->pend.clear(); h->hseq.clear(); h->hqual.clear();
+    progress(h, "preprocess:start");
+    progress(h, h->p.chunk_size > 0 ? "preprocess:chunked:start" : "preprocess:bulk:start");
+    if (h->p.chunk_size == 0) progress(h, "preprocess:bulk:loop:start");
+  }
+  return shk::fastq_feed(h, bytes, n);
+}
+
+shk_status shk_asm_preprocess_finish(shk_asm *h) {
+  SHK_TRY(require_device(h));
+  if (!h->streaming) { set_error("preprocess_finish without push"); return SHK_ERR_STATE; }
+  SHK_TRY(shk::fastq_feed(h, (const uint8_t *)"\n", 1));   // terminate a last line without newline
+  h->streaming = false;
+  if (h->line_in_rec != 0 || !h->pend.empty()) { set_error("truncated FASTQ record at end of input"); return SHK_ERR_FORMAT; }
+  const char *mode = h->p.chunk_size > 0 ? "chunked" : "bulk";
+  if (h->p.chunk_size == 0) { progress(h, "preprocess:bulk:loop:end"); progress(h, "preprocess:bulk:sorting"); }
+  SHK_TRY(shk_internal_flush_batch(h, true));
+  return shk_internal_finish_preprocess(h, mode);
+}
+
+shk_status shk_asm_preprocess_files(shk_asm *h, const char *path1, const char *path2_or_null) {
+  SHK_TRY(require_device(h));
+  if (!path1) { set_error("path1 is null"); return SHK_ERR_BAD_ARG; }
+  h->streaming = false;
+  return shk::parse_fastq_files(h, path1, path2_or_null);
+}
+
+}  // extern "C"

@@ -1,0 +1,100 @@
+// shk_handle.h — the opaque handle behind include/shk.h: owns the device-resident
+// packed reads, the k-mer table, the node/graph buffers and the host-side
+// results between preprocess() and assemble() (reference: the stateful
+// AssemblyHelper, Assembler.ts:92-100 + "preprocess:saving", AssemblyPage.vue:582).
+#pragma once
+#include <cuda_runtime.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/shk.h"
+#include "shk_kernels.h"
+
+namespace shk {
+
+void set_error(const char *fmt, ...);
+shk_status cuda_fail(cudaError_t e, const char *what);
+
+#define SHK_CUDA(call)                                          \
+  do {                                                          \
+    cudaError_t e__ = (call);                                   \
+    if (e__ != cudaSuccess) return shk::cuda_fail(e__, #call);  \
+  } while (0)
+
+// grow-only device buffer
+struct DevBuf {
+  void *p = nullptr;
+  size_t cap = 0;
+  shk_status ensure(size_t bytes);
+  void release();
+  template <class T> T *as() const { return (T *)p; }
+};
+
+struct HostUnitigs {
+  std::vector<char> seq;              // concatenated, as emitted by the device
+  std::vector<uint64_t> off;          // n+1
+  std::vector<float> cov;
+  std::vector<uint8_t> circ;
+  std::vector<uint32_t> link_from, link_to;
+  bool valid = false;
+};
+
+}  // namespace shk
+
+struct shk_asm {
+  shk_params p;
+  int kw = 1, dev = 0;
+  cudaStream_t own_stream = nullptr, stream = nullptr;
+  cudaEvent_t ev[10] = {};
+  shk_progress_fn cb = nullptr;
+  void *cb_user = nullptr;
+
+  // ---- device-resident packed reads (1 zero word in front, 4 behind) ----
+  shk::DevBuf bases, mask, ascii_seq, ascii_qual;
+  uint64_t nwords = 0;          // words in use (excluding pads)
+  uint64_t n_positions = 0, n_bases = 0, counted_positions = 0;
+  // ---- table ----
+  shk::DevBuf slots;
+  uint64_t cap = 0;
+  bool table_live = false;      // holds counts (before K2 rewrote count words)
+  // ---- device scalars: counters[0]=n_bases [1]=n_instances [2]=n_distinct ; histo[500]
+  shk::DevBuf dscal;            // u64 counters[8] | u64 histo[500] | u32 flags[8]
+  uint64_t *h_pinned = nullptr; // pinned mirror of dscal
+  // ---- nodes + graph ----
+  shk::DevBuf node_lo, node_hi, node_count, node_raw, node_edges;
+  shk::DevBuf uniq, succ, tail_of, len_of, unitig_of_head, elem_unitig, pd, cq, circ;
+  shk::DevBuf recs, ucirc, cov_sum, useq, link_from, link_to, gscal;
+  uint32_t node_cap = 0;
+
+  // ---- results / state ----
+  shk_stats st;
+  uint64_t histo[SHK_HISTO_BINS];
+  bool counted = false, filtered = false, graphed = false;
+  shk::HostUnitigs hu;
+  std::string json_pre, json_asm;
+
+  // ---- FASTQ streaming parser (shk_asm_preprocess_push) ----
+  std::vector<uint8_t> pend;          // bytes of an incomplete record
+  std::vector<uint8_t> hseq, hqual;   // parsed reads of the current batch
+  uint64_t batch_reads = 0, total_reads = 0;
+  int line_in_rec = 0;                // 0..3
+  bool streaming = false, any_batch_counted = false;
+};
+
+namespace shk {
+inline uint64_t *d_counters(shk_asm *h) { return h->dscal.as<uint64_t>(); }
+inline uint64_t *d_histo(shk_asm *h) { return h->dscal.as<uint64_t>() + 8; }
+inline uint32_t *d_flags(shk_asm *h) { return (uint32_t *)(h->dscal.as<uint64_t>() + 8 + SHK_HISTO_BINS); }
+static const size_t DSCAL_BYTES = (8 + SHK_HISTO_BINS) * 8 + 8 * 4;
+void progress(shk_asm *h, const char *state);
+shk_status require_device(shk_asm *h);
+// host side (shk_host.cpp)
+shk_status build_assembly_json(shk_asm *h);
+shk_status parse_fastq_files(shk_asm *h, const char *p1, const char *p2);
+shk_status fastq_feed(shk_asm *h, const uint8_t *bytes, size_t n);
+int fit_min_count(const uint64_t *histo, int fallback);
+shk_status fetch_unitigs(shk_asm *h);
+}  // namespace shk
+extern "C" shk_status shk_internal_flush_batch(shk_asm *h, bool final_batch);
+extern "C" shk_status shk_internal_finish_preprocess(shk_asm *h, const char *mode);

@@ -1,0 +1,767 @@
+// shk_kernels.cu — hand-written sm_100a kernels of the sparrowhawk-asm front end
+// (SURVEY.md §2.2 K0..K6).  Integer / byte work bound by HBM and L2 atomics; no
+// tensor cores (nothing here is a dense contraction).  Launch wrappers at the
+// bottom are the only symbols other translation units use (shk_kernels.h).
+#include "shk_device.cuh"
+#include "shk_kernels.h"
+
+namespace shk {
+
+// =====================================================================
+// K0 pack_reads: ASCII seq (+ phred33 qual) → 2-bit words + validity words.
+// One thread per 32 positions: 2 x 128-bit loads from each stream, one 64-bit
+// and one 32-bit coalesced store.  Replaces the per-base masking/packing loop
+// of the reference front end (analogue: sketchlib nthash_iterator.rs:206-252).
+// =====================================================================
+__global__ void __launch_bounds__(256)
+k_pack_reads(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual, u64 n,
+             u64 nwords, int min_qual, u64 *__restrict__ bases, u32 *__restrict__ mask,
+             u64 *__restrict__ counters /* [0]=n_bases */) {
+  u64 w = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+  u64 nb = 0;
+  if (w < nwords) {
+    u64 p0 = w * 32;
+    uint4 s[2], q[2];
+    if (p0 + 32 <= n && ((((uintptr_t)seq | (uintptr_t)(qual ? qual : seq)) & 15) == 0)) {
+      const uint4 *sp = reinterpret_cast<const uint4 *>(seq + p0);
+      s[0] = __ldg(sp); s[1] = __ldg(sp + 1);
+      if (qual) {
+        const uint4 *qp = reinterpret_cast<const uint4 *>(qual + p0);
+        q[0] = __ldg(qp); q[1] = __ldg(qp + 1);
+      }
+    } else {  // ragged tail / unaligned input: byte loads
+      uint8_t *sb = reinterpret_cast<uint8_t *>(s), *qb = reinterpret_cast<uint8_t *>(q);
+      for (int j = 0; j < 32; ++j) {
+        u64 p = p0 + j;
+        sb[j] = p < n ? seq[p] : (uint8_t)'\n';
+        qb[j] = (p < n && qual) ? qual[p] : (uint8_t)'\n';
+      }
+    }
+    const uint8_t *sb = reinterpret_cast<const uint8_t *>(s);
+    const uint8_t *qb = reinterpret_cast<const uint8_t *>(q);
+    u64 bw = 0; u32 mw = 0;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+      uint8_t c = sb[j];
+      bool ok = shk_valid_base(c) && (!qual || shk_qual_ok(qb[j], min_qual));
+      bw = (bw << 2) | (u64)shk_encode_base(c);
+      mw |= (ok ? 1u : 0u) << j;
+      nb += (c != '\n') ? 1 : 0;   // unit of the metric: every sequence character
+    }
+    bases[w] = bw;
+    mask[w] = mw;
+  }
+  // block-level count of bases
+  for (int o = 16; o; o >>= 1) nb += __shfl_xor_sync(0xffffffffu, nb, o);
+  if ((threadIdx.x & 31) == 0 && nb) atomicAdd(&counters[0], nb);
+}
+
+// =====================================================================
+// K1 extract_count.  A warp takes 32 consecutive stream words (1024 positions);
+// lane i owns word i and gets its neighbours by warp shuffle (the halo words
+// come from the two edge lanes).  Every lane materialises the forward k-mer at
+// each of its 32 offsets by a funnel shift of (w, w+1[, w+2]) and the reverse
+// complement by the mirrored funnel shift of the revcomp'ed words, takes the
+// minimum (canonical, S6), builds the read-evidenced edge code (S13 / D.3) and
+// inserts into the open-addressing table: 128-bit slot load, CAS claim on the
+// key, RED.ADD on the count, RED.OR on the edge byte only when it adds bits.
+// =====================================================================
+template <int KW> struct Table {
+  typename SlotOf<KW>::type *slots;
+  u64 cap;
+  u32 max_probe;
+};
+
+__device__ __forceinline__ bool table_insert(const Table<1> &t, u64 key, u32 e, u32 add, u32 *overflow) {
+  u64 i = slot_of(hash_key(key), t.cap);
+  for (u32 probe = 0; probe < t.max_probe; ++probe) {
+    Slot1 *sp = t.slots + i;
+    uint4 v = __ldcg(reinterpret_cast<const uint4 *>(sp));
+    u64 cur = ((u64)v.y << 32) | v.x;
+    u32 seen = v.w;
+    bool claimed = false;
+    if (cur == SHK_EMPTY64) {
+      cur = atomicCAS(&sp->key, SHK_EMPTY64, key);
+      if (cur == SHK_EMPTY64) { cur = key; seen = 0; claimed = true; }
+    }
+    if (cur == key) {
+      atomicAdd(&sp->count, add);                      // RED.ADD (result unused)
+      if ((seen & e) != e) atomicOr(&sp->edges, e);    // RED.OR only when new bits
+      return claimed;
+    }
+    if (++i == t.cap) i = 0;
+  }
+  atomicExch(overflow, 1u);
+  return false;
+}
+
+__device__ __forceinline__ bool table_insert(const Table<2> &t, u128 key, u32 e, u32 add, u32 *overflow) {
+  u64 i = slot_of(hash_key(key), t.cap);
+  const u64 klo = (u64)key, khi = (u64)(key >> 64);
+  for (u32 probe = 0; probe < t.max_probe; ++probe) {
+    Slot2 *sp = t.slots + i;
+    const uint4 *p4 = reinterpret_cast<const uint4 *>(sp);
+    uint4 v = __ldcg(p4);
+    uint2 cv = __ldcg(reinterpret_cast<const uint2 *>(p4 + 1));
+    u64 lo = ((u64)v.y << 32) | v.x, hi = ((u64)v.w << 32) | v.z;
+    u32 seen = cv.y;
+    bool claimed = false;
+    if (hi == SHK_EMPTY64) {
+      U128Pair expect{SHK_EMPTY64, SHK_EMPTY64}, want{klo, khi};
+      U128Pair old = atomicCAS(reinterpret_cast<U128Pair *>(sp), expect, want);
+      lo = old.lo; hi = old.hi;
+      if (hi == SHK_EMPTY64) { lo = klo; hi = khi; seen = 0; claimed = true; }
+    }
+    if (lo == klo && hi == khi) {
+      atomicAdd(&sp->count, add);
+      if ((seen & e) != e) atomicOr(&sp->edges, e);
+      return claimed;
+    }
+    if (++i == t.cap) i = 0;
+  }
+  atomicExch(overflow, 1u);
+  return false;
+}
+
+template <int KW>
+__global__ void __launch_bounds__(256)
+k_extract_count(const u64 *__restrict__ bases, const u32 *__restrict__ mask, u64 nwords, int k,
+                Table<KW> tbl, u64 *__restrict__ counters /* [1]=n_instances [2]=n_distinct */,
+                u32 *__restrict__ overflow) {
+  typedef typename KeyOf<KW>::type K;
+  const int lane = threadIdx.x & 31;
+  const u64 warp0 = ((u64)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const u64 nwarps = ((u64)gridDim.x * blockDim.x) >> 5;
+  const u64 nchunks = (nwords + 31) >> 5;
+  const K km = kmask_of(k, (K)0);
+  u64 ninst = 0; u32 nclaim = 0;
+  for (u64 c = warp0; c < nchunks; c += nwarps) {
+    const u64 w = c * 32 + lane;
+    // arrays carry one zero word before index 0 and >= 4 after nwords-1
+    u64 b0 = w < nwords ? __ldg(bases + w) : 0;
+    u32 m0 = w < nwords ? __ldg(mask + w) : 0;
+    u64 b1 = __shfl_down_sync(0xffffffffu, b0, 1);
+    u32 m1 = __shfl_down_sync(0xffffffffu, m0, 1);
+    u64 bp = __shfl_up_sync(0xffffffffu, b0, 1);
+    u32 mp = __shfl_up_sync(0xffffffffu, m0, 1);
+    u64 b2 = 0; u32 m2 = 0;
+    if (KW == 2) {
+      b2 = __shfl_down_sync(0xffffffffu, b0, 2);
+      m2 = __shfl_down_sync(0xffffffffu, m0, 2);
+    }
+    if (lane == 31) {
+      b1 = w + 1 < nwords ? __ldg(bases + w + 1) : 0; m1 = w + 1 < nwords ? __ldg(mask + w + 1) : 0;
+    }
+    if (KW == 2 && lane >= 30) {
+      b2 = w + 2 < nwords ? __ldg(bases + w + 2) : 0; m2 = w + 2 < nwords ? __ldg(mask + w + 2) : 0;
+    }
+    if (lane == 0) {
+      bp = c ? __ldg(bases + w - 1) : 0; mp = c ? __ldg(mask + w - 1) : 0;
+    }
+    if (m0 == 0) continue;  // no window can start in this word
+    const u64 r0 = revcomp_word(b0), r1 = revcomp_word(b1);
+    const u64 r2 = KW == 2 ? revcomp_word(b2) : 0;
+    const u64 mm = (u64)m0 | ((u64)m1 << 32);
+#pragma unroll 4
+    for (int o = 0; o < 32; ++o) {
+      // validity of window [o, o+k): k mask bits all set
+      bool ok;
+      if (KW == 1) {
+        const u64 vm = (1ull << k) - 1;
+        ok = ((mm >> o) & vm) == vm;
+      } else {
+        u128 m128 = (u128)mm | ((u128)m2 << 64);
+        const u128 vm = (((u128)1) << k) - 1;
+        ok = ((m128 >> o) & vm) == vm;
+      }
+      if (!ok) continue;
+      ++ninst;
+      K fwd, rc; u32 bnext;
+      if (KW == 1) {
+        u64 H = o ? ((b0 << (2 * o)) | (b1 >> (64 - 2 * o))) : b0;      // stream << 2o, top word
+        u64 t = H >> (62 - 2 * k);
+        bnext = (u32)t & 3u; fwd = (K)(t >> 2);
+        u64 L = o ? ((r0 >> (2 * o)) | (r1 << (64 - 2 * o))) : r0;      // (r1:r0) >> 2o, low word
+        rc = (K)(L & (u64)km);
+      } else {
+        u128 S01 = ((u128)b0 << 64) | b1;
+        u128 H = o ? ((S01 << (2 * o)) | (u128)(b2 >> (64 - 2 * o))) : S01;
+        u128 t = H >> (126 - 2 * k);
+        bnext = (u32)t & 3u; fwd = (K)(t >> 2);
+        u128 R10 = ((u128)r1 << 64) | r0;
+        u128 L = o ? ((R10 >> (2 * o)) | ((u128)r2 << (128 - 2 * o))) : R10;
+        rc = (K)(L & (u128)km);
+      }
+      // neighbours in the read: previous / next window valid too?
+      const bool has_l = o ? ((m0 >> (o - 1)) & 1u) : ((mp >> 31) & 1u);
+      bool has_r;
+      if (KW == 1) has_r = (mm >> (o + k)) & 1ull;
+      else has_r = (o + k < 64) ? ((mm >> (o + k)) & 1ull) : ((m2 >> (o + k - 64)) & 1u);
+      const u32 a = o ? (u32)(b0 >> (64 - 2 * o)) & 3u : (u32)bp & 3u;
+      u32 e; K key;
+      if (fwd < rc) {
+        key = fwd;
+        e = (has_r ? (1u << bnext) : 0u) | (has_l ? (16u << a) : 0u);
+      } else {
+        key = rc;
+        e = (has_l ? (1u << (a ^ 2u)) : 0u) | (has_r ? (16u << (bnext ^ 2u)) : 0u);
+      }
+      nclaim += table_insert(tbl, key, e, 1u, overflow) ? 1u : 0u;
+    }
+  }
+  for (int o = 16; o; o >>= 1) ninst += __shfl_xor_sync(0xffffffffu, ninst, o);
+  if (lane == 0 && ninst) atomicAdd(&counters[1], ninst);
+  for (int o = 16; o; o >>= 1) nclaim += __shfl_xor_sync(0xffffffffu, nclaim, o);
+  if (lane == 0 && nclaim) atomicAdd(&counters[2], (u64)nclaim);
+}
+
+// =====================================================================
+// K2 histogram_filter: one sweep over the table.  500-bin spectrum in shared
+// memory (S9), survivors of count > min_count (S10) compacted into dense node
+// arrays with warp-aggregated cursor bumps; the slot's count word is replaced
+// by the node id (SHK_NONE for non-survivors) so K3 can translate neighbour
+// key → node id with the same table.
+// =====================================================================
+template <int KW> __device__ __forceinline__ bool slot_load(const typename SlotOf<KW>::type *sp,
+                                                            typename KeyOf<KW>::type &key, u32 &count, u32 &edges);
+template <> __device__ __forceinline__ bool slot_load<1>(const Slot1 *sp, u64 &key, u32 &count, u32 &edges) {
+  uint4 v = *reinterpret_cast<const uint4 *>(sp);
+  key = ((u64)v.y << 32) | v.x; count = v.z; edges = v.w;
+  return key != SHK_EMPTY64;
+}
+template <> __device__ __forceinline__ bool slot_load<2>(const Slot2 *sp, u128 &key, u32 &count, u32 &edges) {
+  const uint4 *p4 = reinterpret_cast<const uint4 *>(sp);
+  uint4 v = p4[0]; uint2 c = *reinterpret_cast<const uint2 *>(p4 + 1);
+  u64 lo = ((u64)v.y << 32) | v.x, hi = ((u64)v.w << 32) | v.z;
+  key = ((u128)hi << 64) | lo; count = c.x; edges = c.y;
+  return hi != SHK_EMPTY64;
+}
+
+template <int KW>
+__global__ void __launch_bounds__(256)
+k_histogram_filter(Table<KW> tbl, int min_count, u64 *__restrict__ histo /*[500]*/,
+                   u64 *__restrict__ node_lo, u64 *__restrict__ node_hi, uint16_t *__restrict__ node_count,
+                   uint8_t *__restrict__ node_raw, u32 node_cap, u32 *__restrict__ n_nodes) {
+  typedef typename KeyOf<KW>::type K;
+  __shared__ u32 sh[SHK_NBINS];
+  for (int i = threadIdx.x; i < SHK_NBINS; i += blockDim.x) sh[i] = 0;
+  __syncthreads();
+  const int lane = threadIdx.x & 31;
+  // all lanes of a warp iterate together (ballot below): pad the bound to 32
+  const u64 stride = (u64)gridDim.x * blockDim.x;
+  for (u64 base = (u64)blockIdx.x * blockDim.x; base < tbl.cap; base += stride) {
+    u64 i = base + threadIdx.x;
+    bool surv = false; K key = 0; u32 cnt = 0, e = 0;
+    if (i < tbl.cap && slot_load<KW>(tbl.slots + i, key, cnt, e)) {
+      u32 c = cnt > SHK_COUNT_MAX ? SHK_COUNT_MAX : cnt;   // S7 saturation
+      atomicAdd(&sh[shk_histo_bin(c)], 1u);
+      surv = shk_passes(c, min_count);
+      cnt = c;
+      if (!surv) tbl.slots[i].count = SHK_NONE;
+    }
+    u32 ball = __ballot_sync(0xffffffffu, surv);
+    if (ball) {
+      u32 basei = 0;
+      if (lane == 0) basei = atomicAdd(n_nodes, (u32)__popc(ball));
+      basei = __shfl_sync(0xffffffffu, basei, 0);
+      if (surv) {
+        u32 id = basei + __popc(ball & ((1u << lane) - 1));
+        if (id < node_cap) {
+          node_lo[id] = (u64)key;
+          if (KW == 2) node_hi[id] = (u64)((u128)key >> 64);
+          node_count[id] = (uint16_t)cnt;
+          node_raw[id] = (uint8_t)e;
+          tbl.slots[i].count = id;
+        }
+      }
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < SHK_NBINS; i += blockDim.x)
+    if (sh[i]) atomicAdd(&histo[i], (u64)sh[i]);
+}
+
+// Table growth (chunked mode only): re-insert every live slot of `old` into `neu`.
+template <int KW>
+__global__ void __launch_bounds__(256)
+k_rehash(Table<KW> old, Table<KW> neu, u32 *__restrict__ overflow) {
+  typedef typename KeyOf<KW>::type K;
+  const u64 stride = (u64)gridDim.x * blockDim.x;
+  for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < old.cap; i += stride) {
+    K key; u32 cnt, e;
+    if (slot_load<KW>(old.slots + i, key, cnt, e)) table_insert(neu, key, e, cnt, overflow);
+  }
+}
+
+// Count-only variant of the sweep (sizes the node arrays before compaction).
+template <int KW>
+__global__ void __launch_bounds__(256)
+k_histogram_only(Table<KW> tbl, u64 *__restrict__ histo) {
+  typedef typename KeyOf<KW>::type K;
+  __shared__ u32 sh[SHK_NBINS];
+  for (int i = threadIdx.x; i < SHK_NBINS; i += blockDim.x) sh[i] = 0;
+  __syncthreads();
+  const u64 stride = (u64)gridDim.x * blockDim.x;
+  for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < tbl.cap; i += stride) {
+    K key; u32 cnt, e;
+    if (slot_load<KW>(tbl.slots + i, key, cnt, e)) {
+      u32 c = cnt > SHK_COUNT_MAX ? SHK_COUNT_MAX : cnt;
+      atomicAdd(&sh[shk_histo_bin(c)], 1u);
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < SHK_NBINS; i += blockDim.x)
+    if (sh[i]) atomicAdd(&histo[i], (u64)sh[i]);
+}
+
+// =====================================================================
+// K3 build_edges: per node, validate each read-evidenced edge bit against the
+// presence of the neighbour node (S13) by a table lookup; record, per side,
+// the unique neighbour (node id << 1 | arrival side) when exactly one edge
+// survives.
+// =====================================================================
+template <int KW>
+__device__ __forceinline__ u32 table_find(const Table<KW> &t, typename KeyOf<KW>::type key) {
+  typedef typename KeyOf<KW>::type K;
+  u64 i = slot_of(hash_key(key), t.cap);
+  for (u32 probe = 0; probe < t.max_probe; ++probe) {
+    K cur; u32 cnt, e;
+    if (!slot_load<KW>(t.slots + i, cur, cnt, e)) return SHK_NONE;  // empty: absent
+    if (cur == key) return cnt;                                     // node id or SHK_NONE
+    if (++i == t.cap) i = 0;
+  }
+  return SHK_NONE;
+}
+
+template <int KW>
+__global__ void __launch_bounds__(256)
+k_build_edges(Table<KW> tbl, int k, const u64 *__restrict__ node_lo, const u64 *__restrict__ node_hi,
+              const uint8_t *__restrict__ node_raw, u32 n_nodes, uint8_t *__restrict__ node_edges,
+              u32 *__restrict__ uniq /* [2*n_nodes] */) {
+  typedef typename KeyOf<KW>::type K;
+  u32 n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= n_nodes) return;
+  K X = (K)node_lo[n];
+  if (KW == 2) X |= (K)((u128)node_hi[n] << 64);
+  u32 raw = node_raw[n], valid = 0;
+  u32 un[2] = {SHK_NONE, SHK_NONE};
+  for (int bit = 0; bit < 8; ++bit) {
+    if (!((raw >> bit) & 1u)) continue;
+    int s_in; K Y = neighbour_key(X, k, bit >> 2, (u32)(bit & 3), s_in);
+    u32 id = table_find<KW>(tbl, Y);
+    if (id != SHK_NONE) { valid |= 1u << bit; un[bit >> 2] = (id << 1) | (u32)s_in; }
+  }
+  node_edges[n] = (uint8_t)valid;
+  uniq[2 * n + 0] = __popc(valid & 15u) == 1 ? un[0] : SHK_NONE;
+  uniq[2 * n + 1] = __popc(valid >> 4) == 1 ? un[1] : SHK_NONE;
+}
+
+// =====================================================================
+// K4 unitig_links over directed elements e = 2*node + dir (dir 0 = canonical
+// orientation, leaves through the right side; dir 1 leaves through the left).
+// succ[e] = f iff the edge is the only one on the facing side of both nodes and
+// does not return to the same node (D.6).  Then the ranking state is seeded:
+// pd[e] = (pred, 1) or (e, 0) for heads, packed (ptr << 32 | dist).
+// =====================================================================
+__global__ void __launch_bounds__(256)
+k_unitig_links(const uint8_t *__restrict__ node_edges, const u32 *__restrict__ uniq, u32 n_elems,
+               u32 *__restrict__ succ) {
+  u32 e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= n_elems) return;
+  u32 u = uniq[e], out = SHK_NONE;   // out side of e == dir == e & 1
+  if (u != SHK_NONE) {
+    u32 w = u >> 1, s = u & 1u;
+    if (w != (e >> 1) && __popc(side_bits(node_edges[w], (int)s)) == 1) out = 2 * w + (s ^ 1u);
+  }
+  succ[e] = out;
+}
+
+__global__ void __launch_bounds__(256)
+k_rank_init(const u32 *__restrict__ succ, u32 n_elems, u64 *__restrict__ pd) {
+  u32 e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= n_elems) return;
+  u32 sr = succ[e ^ 1u];                       // pred(e) = rev(succ(rev e))
+  pd[e] = sr == SHK_NONE ? ((u64)e << 32) : (((u64)(sr ^ 1u) << 32) | 1ull);
+}
+
+// =====================================================================
+// K5 list_rank: Wyllie pointer jumping, in place.  pd[e] = (ancestor, distance)
+// is read as one 64-bit word, so a racing reader always sees a consistent pair
+// and the jump stays exact.  Heads are fixed points (ptr == self, dist 0).
+// =====================================================================
+__global__ void __launch_bounds__(256)
+k_rank_jump(u64 *__restrict__ pd, u32 n_elems, u32 *__restrict__ changed) {
+  u32 e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= n_elems) return;
+  u64 v = pd[e];
+  u32 p = (u32)(v >> 32);
+  if (p == e) return;                          // head (dist 0) or closed cycle (dist > 0)
+  bool ch = false;
+  // a few jumps per launch: chains are long, launches are not free
+  for (int it = 0; it < 4; ++it) {
+    u64 vp = __ldcg(pd + p);
+    u32 pp = (u32)(vp >> 32);
+    if (pp == p) break;                        // p is a head (or a closed cycle): stop
+    v = ((u64)pp << 32) | (u32)((u32)v + (u32)vp);
+    p = pp; ch = true;
+    if (p == e) break;                         // cycle closed on itself (dist > 0 marks it)
+  }
+  if (ch) { pd[e] = v; *changed = 1u; }
+}
+
+// ---- cycles (S14): elements whose ancestor is not a true head (ptr==self,
+// dist 0) after ceil(log2 n) rounds lie on unbranched cycles.  Doubling on
+// (pred pointer, argmin element by node key) finds the minimum canonical k-mer
+// of each directed cycle; the cycle is cut there and re-ranked.  Of the two
+// mirror cycles the one that holds the minimum node in dir 0 is kept.
+__device__ __forceinline__ bool is_true_head(const u64 *pd, u32 p) { return __ldcg(pd + p) == ((u64)p << 32); }
+
+__device__ __forceinline__ bool elem_key_less(const u64 *lo, const u64 *hi, u32 a, u32 b) {
+  u32 na = a >> 1, nb = b >> 1;
+  if (hi) { u64 ha = hi[na], hb = hi[nb]; if (ha != hb) return ha < hb; }
+  return lo[na] < lo[nb];
+}
+
+__global__ void __launch_bounds__(256)
+k_cycle_init(const u64 *__restrict__ pd, const u32 *__restrict__ succ, u32 n_elems,
+             u64 *__restrict__ cq /* (pred ptr << 32 | argmin elem), or ~0 when acyclic */,
+             u32 *__restrict__ n_cyclic) {
+  u32 e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= n_elems) return;
+  u32 p = (u32)(pd[e] >> 32);
+  if (is_true_head(pd, p)) { cq[e] = ~0ull; return; }
+  u32 pred = succ[e ^ 1u] ^ 1u;                // exists on a cycle
+  cq[e] = ((u64)pred << 32) | e;
+  atomicAdd(n_cyclic, 1u);
+}
+
+__global__ void __launch_bounds__(256)
+k_cycle_jump(u64 *__restrict__ cq, u32 n_elems, const u64 *__restrict__ node_lo,
+             const u64 *__restrict__ node_hi) {
+  u32 e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= n_elems) return;
+  u64 v = cq[e];
+  if (v == ~0ull) return;
+  u32 q = (u32)(v >> 32), m = (u32)v;
+  u64 vq = __ldcg(cq + q);
+  u32 qq = (u32)(vq >> 32), mq = (u32)vq;
+  if (elem_key_less(node_lo, node_hi, mq, m)) m = mq;
+  cq[e] = ((u64)qq << 32) | m;
+}
+
+__global__ void __launch_bounds__(256)
+k_cycle_cut(const u64 *__restrict__ cq, const u32 *__restrict__ succ, u32 n_elems,
+            u64 *__restrict__ pd, uint8_t *__restrict__ circ /* per element */) {
+  u32 e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= n_elems) return;
+  u64 v = cq[e];
+  if (v == ~0ull) { circ[e] = 0; return; }
+  u32 m = (u32)v;
+  circ[e] = 1;
+  pd[e] = (e == m) ? ((u64)e << 32) : (((u64)(succ[e ^ 1u] ^ 1u) << 32) | 1ull);
+}
+
+// =====================================================================
+// K6 emit_unitigs.
+//  tails : the last element of every directed list tells its head the length.
+//  heads : one list of each mirror pair is kept (smaller end-node key first;
+//          a single node in dir 0; a cycle through its minimum node in dir 0)
+//          and gets a unitig id + an output range from two cursors.
+//  emit  : element of rank r writes its oriented last base at off + k-1 + r
+//          (rank 0 writes the whole k-mer) and adds its count to the unitig.
+// =====================================================================
+struct UnitigRec { u32 head, len; u64 off; };
+
+__global__ void __launch_bounds__(256)
+k_unitig_tails(const u64 *__restrict__ pd, const u32 *__restrict__ succ, const uint8_t *__restrict__ circ,
+               u32 n_elems, u32 *__restrict__ tail_of /* by head elem */, u32 *__restrict__ len_of) {
+  u32 e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= n_elems) return;
+  u64 v = pd[e];
+  u32 h = (u32)(v >> 32), d = (u32)v;
+  u32 s = succ[e];
+  bool tail = (s == SHK_NONE) || (circ && circ[e] && s == h);
+  if (tail) { tail_of[h] = e; len_of[h] = d + 1; }
+}
+
+__global__ void __launch_bounds__(256)
+k_unitig_heads(const u64 *__restrict__ pd, const uint8_t *__restrict__ circ, const u32 *__restrict__ tail_of,
+               const u32 *__restrict__ len_of, const u64 *__restrict__ node_lo,
+               const u64 *__restrict__ node_hi, u32 n_elems, int k, u32 *__restrict__ unitig_of_head,
+               UnitigRec *__restrict__ recs, uint8_t *__restrict__ ucirc, u32 *__restrict__ n_unitigs,
+               u64 *__restrict__ seq_cursor) {
+  u32 e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= n_elems) return;
+  unitig_of_head[e] = SHK_NONE;
+  if (pd[e] != ((u64)e << 32)) return;         // not a head
+  u32 t = tail_of[e];
+  bool cyc = circ && circ[e];
+  bool keep;
+  if (cyc) keep = (e & 1u) == 0;
+  else if ((t >> 1) == (e >> 1)) keep = (e & 1u) == 0;
+  else keep = elem_key_less(node_lo, node_hi, e, t);
+  if (!keep) return;
+  u32 len = len_of[e];
+  u32 uid = atomicAdd(n_unitigs, 1u);
+  u64 off = atomicAdd(seq_cursor, (u64)len + (u64)k - 1);
+  unitig_of_head[e] = uid;
+  recs[uid] = UnitigRec{e, len, off};
+  ucirc[uid] = cyc ? 1 : 0;
+}
+
+template <int KW>
+__global__ void __launch_bounds__(256)
+k_unitig_emit(const u64 *__restrict__ pd, const u32 *__restrict__ unitig_of_head,
+              const UnitigRec *__restrict__ recs, const u64 *__restrict__ node_lo,
+              const u64 *__restrict__ node_hi, const uint16_t *__restrict__ node_count, u32 n_elems, int k,
+              char *__restrict__ seq, u64 *__restrict__ cov_sum, u32 *__restrict__ elem_unitig) {
+  typedef typename KeyOf<KW>::type K;
+  u32 e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= n_elems) return;
+  u64 v = pd[e];
+  u32 h = (u32)(v >> 32), r = (u32)v;
+  u32 uid = unitig_of_head[h];
+  if (elem_unitig) elem_unitig[e] = uid;
+  if (uid == SHK_NONE) return;
+  u32 n = e >> 1;
+  K X = (K)node_lo[n];
+  if (KW == 2) X |= (K)((u128)node_hi[n] << 64);
+  if (e & 1u) X = revcomp_key(X, k);
+  u64 off = recs[uid].off;
+  if (r == 0) {
+    for (int i = 0; i < k; ++i) seq[off + i] = SHK_CODE2ASCII_DEV((u32)(X >> (2 * (k - 1 - i))) & 3u);
+  } else {
+    seq[off + k - 1 + r] = SHK_CODE2ASCII_DEV((u32)X & 3u);
+  }
+  atomicAdd(cov_sum + uid, (u64)node_count[n]);
+}
+
+// Unitig-level links: for every kept unitig and both of its exits (tail
+// element, and the reverse of its head) one link per validated edge.  The
+// entered element is always the head of its directed list; if that list is
+// the dropped mirror, the kept one is entered in reverse through its tail.
+template <int KW>
+__global__ void __launch_bounds__(256)
+k_unitig_links_out(Table<KW> tbl, int k, const UnitigRec *__restrict__ recs, u32 n_unitigs,
+                   const u32 *__restrict__ tail_of, const u32 *__restrict__ unitig_of_head,
+                   const u64 *__restrict__ node_lo, const u64 *__restrict__ node_hi,
+                   const uint8_t *__restrict__ node_edges, const uint8_t *__restrict__ ucirc,
+                   u32 *__restrict__ from, u32 *__restrict__ to,
+                   u32 link_cap, u32 *__restrict__ n_links) {
+  typedef typename KeyOf<KW>::type K;
+  u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= 2 * n_unitigs) return;
+  u32 uid = i >> 1, orient = i & 1u;
+  u32 head = recs[uid].head;
+  u32 x = orient == 0 ? tail_of[head] : (head ^ 1u);     // exit element
+  u32 n = x >> 1; int side = (int)(x & 1u);
+  u32 bits = (u32)side_bits(node_edges[n], side);
+  if (!bits) return;
+  if (ucirc[uid]) {                            // unbranched cycle: closes on itself
+    u32 slot = atomicAdd(n_links, 1u);
+    if (slot < link_cap) { from[slot] = i; to[slot] = i; }
+    return;
+  }
+  K X = (K)node_lo[n];
+  if (KW == 2) X |= (K)((u128)node_hi[n] << 64);
+  for (u32 b = 0; b < 4; ++b) {
+    if (!((bits >> b) & 1u)) continue;
+    int s_in; K Y = neighbour_key(X, k, side, b, s_in);
+    u32 w = table_find<KW>(tbl, Y);
+    if (w == SHK_NONE) continue;               // cannot happen after validation
+    u32 f = 2 * w + ((u32)s_in ^ 1u);          // entered element: head of its list
+    u32 target = unitig_of_head[f];
+    u32 tor = 0;
+    if (target == SHK_NONE) {
+      u32 tf = tail_of[f];
+      if (tf == SHK_NONE) continue;            // f not a head: cannot happen (D.6)
+      target = unitig_of_head[tf ^ 1u]; tor = 1;
+    }
+    if (target == SHK_NONE) continue;
+    u32 slot = atomicAdd(n_links, 1u);
+    if (slot < link_cap) { from[slot] = 2 * uid + orient; to[slot] = 2 * target + tor; }
+  }
+}
+
+// =====================================================================
+// launch wrappers
+// =====================================================================
+static int g_sms = 0;
+int sm_count() {
+  if (!g_sms) {
+    int dev = 0; cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&g_sms, cudaDevAttrMultiProcessorCount, dev);
+    if (g_sms <= 0) g_sms = 148;
+  }
+  return g_sms;
+}
+size_t slot_bytes(int kw) { return kw == 1 ? sizeof(Slot1) : sizeof(Slot2); }
+size_t unitig_rec_bytes() { return sizeof(UnitigRec); }
+
+static inline unsigned blocks_for(uint64_t n, unsigned per) { return (unsigned)((n + per - 1) / per); }
+// persistent-style grid: a multiple of the SM count, capped by the work
+static inline unsigned grid_persistent(uint64_t work_items, unsigned threads, unsigned ctas_per_sm) {
+  uint64_t need = (work_items + threads - 1) / threads;
+  uint64_t cap = (uint64_t)sm_count() * ctas_per_sm;
+  return (unsigned)(need < cap ? (need ? need : 1) : cap);
+}
+
+int launch_pack_reads(const uint8_t *seq, const uint8_t *qual, uint64_t n, uint64_t nwords, int min_qual,
+                      uint64_t *bases, uint32_t *mask, uint64_t *counters, cudaStream_t st) {
+  if (!nwords) return 0;
+  k_pack_reads<<<blocks_for(nwords, 256), 256, 0, st>>>(seq, qual, n, nwords, min_qual, (u64 *)bases, mask,
+                                                        (u64 *)counters);
+  return 1;
+}
+
+__global__ void __launch_bounds__(256) k_table_clear1(Slot1 *s, u64 cap) {
+  u64 stride = (u64)gridDim.x * blockDim.x;
+  const uint4 v = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0u, 0u);
+  for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < cap; i += stride)
+    reinterpret_cast<uint4 *>(s)[i] = v;
+}
+__global__ void __launch_bounds__(256) k_table_clear2(Slot2 *s, u64 cap) {
+  u64 stride = (u64)gridDim.x * blockDim.x;
+  const uint4 v0 = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu), v1 = make_uint4(0, 0, 0, 0);
+  for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < 2 * cap; i += stride)
+    reinterpret_cast<uint4 *>(s)[i] = (i & 1) ? v1 : v0;
+}
+
+int launch_table_fill(void *slots, uint64_t cap, int kw, cudaStream_t st) {
+  unsigned g = grid_persistent(cap * (kw == 2 ? 2 : 1), 256, 8);
+  if (kw == 1) k_table_clear1<<<g, 256, 0, st>>>((Slot1 *)slots, cap);
+  else k_table_clear2<<<g, 256, 0, st>>>((Slot2 *)slots, cap);
+  return 1;
+}
+
+int launch_extract_count(int kw, const uint64_t *bases, const uint32_t *mask, uint64_t nwords, int k,
+                         void *slots, uint64_t cap, uint64_t *counters, uint32_t *overflow, cudaStream_t st) {
+  if (!nwords) return 0;
+  unsigned g = grid_persistent(nwords, 256, 8);
+  u32 max_probe = (u32)(cap < 4096 ? cap : 4096);
+  if (kw == 1) {
+    Table<1> t{(Slot1 *)slots, cap, max_probe};
+    k_extract_count<1><<<g, 256, 0, st>>>((const u64 *)bases, mask, nwords, k, t, (u64 *)counters, overflow);
+  } else {
+    Table<2> t{(Slot2 *)slots, cap, max_probe};
+    k_extract_count<2><<<g, 256, 0, st>>>((const u64 *)bases, mask, nwords, k, t, (u64 *)counters, overflow);
+  }
+  return 1;
+}
+
+int launch_rehash(int kw, void *old_slots, uint64_t old_cap, void *new_slots, uint64_t new_cap, uint32_t *overflow,
+                  cudaStream_t st) {
+  unsigned g = grid_persistent(old_cap, 256, 8);
+  u32 mp = (u32)(new_cap < 4096 ? new_cap : 4096);
+  if (kw == 1)
+    k_rehash<1><<<g, 256, 0, st>>>(Table<1>{(Slot1 *)old_slots, old_cap, 0}, Table<1>{(Slot1 *)new_slots, new_cap, mp}, overflow);
+  else
+    k_rehash<2><<<g, 256, 0, st>>>(Table<2>{(Slot2 *)old_slots, old_cap, 0}, Table<2>{(Slot2 *)new_slots, new_cap, mp}, overflow);
+  return 1;
+}
+
+int launch_histogram_only(int kw, void *slots, uint64_t cap, uint64_t *histo, cudaStream_t st) {
+  unsigned g = grid_persistent(cap, 256, 8);
+  if (kw == 1) k_histogram_only<1><<<g, 256, 0, st>>>(Table<1>{(Slot1 *)slots, cap, 0}, (u64 *)histo);
+  else k_histogram_only<2><<<g, 256, 0, st>>>(Table<2>{(Slot2 *)slots, cap, 0}, (u64 *)histo);
+  return 1;
+}
+
+int launch_histogram_filter(int kw, void *slots, uint64_t cap, int min_count, uint64_t *histo,
+                            uint64_t *node_lo, uint64_t *node_hi, uint16_t *node_count, uint8_t *node_raw,
+                            uint32_t node_cap, uint32_t *n_nodes, cudaStream_t st) {
+  unsigned g = grid_persistent(cap, 256, 8);
+  if (kw == 1)
+    k_histogram_filter<1><<<g, 256, 0, st>>>(Table<1>{(Slot1 *)slots, cap, 0}, min_count, (u64 *)histo,
+                                             (u64 *)node_lo, (u64 *)node_hi, node_count, node_raw, node_cap, n_nodes);
+  else
+    k_histogram_filter<2><<<g, 256, 0, st>>>(Table<2>{(Slot2 *)slots, cap, 0}, min_count, (u64 *)histo,
+                                             (u64 *)node_lo, (u64 *)node_hi, node_count, node_raw, node_cap, n_nodes);
+  return 1;
+}
+
+int launch_build_edges(int kw, void *slots, uint64_t cap, int k, const GraphBuffers &g, cudaStream_t st) {
+  if (!g.n_nodes) return 0;
+  u32 max_probe = (u32)(cap < 4096 ? cap : 4096);
+  unsigned b = blocks_for(g.n_nodes, 256);
+  if (kw == 1)
+    k_build_edges<1><<<b, 256, 0, st>>>(Table<1>{(Slot1 *)slots, cap, max_probe}, k, (const u64 *)g.node_lo,
+                                        (const u64 *)g.node_hi, g.node_raw, g.n_nodes, g.node_edges, g.uniq);
+  else
+    k_build_edges<2><<<b, 256, 0, st>>>(Table<2>{(Slot2 *)slots, cap, max_probe}, k, (const u64 *)g.node_lo,
+                                        (const u64 *)g.node_hi, g.node_raw, g.n_nodes, g.node_edges, g.uniq);
+  return 1;
+}
+
+int launch_links_and_rank_init(const GraphBuffers &g, cudaStream_t st) {
+  u32 ne = 2 * g.n_nodes;
+  if (!ne) return 0;
+  k_unitig_links<<<blocks_for(ne, 256), 256, 0, st>>>(g.node_edges, g.uniq, ne, g.succ);
+  k_rank_init<<<blocks_for(ne, 256), 256, 0, st>>>(g.succ, ne, (u64 *)g.pd);
+  return 2;
+}
+int launch_rank_jump(const GraphBuffers &g, cudaStream_t st) {
+  u32 ne = 2 * g.n_nodes;
+  if (!ne) return 0;
+  k_rank_jump<<<blocks_for(ne, 256), 256, 0, st>>>((u64 *)g.pd, ne, g.scal + 0);
+  return 1;
+}
+int launch_cycle_init(const GraphBuffers &g, cudaStream_t st) {
+  u32 ne = 2 * g.n_nodes;
+  if (!ne) return 0;
+  k_cycle_init<<<blocks_for(ne, 256), 256, 0, st>>>((const u64 *)g.pd, g.succ, ne, (u64 *)g.cq, g.scal + 1);
+  return 1;
+}
+int launch_cycle_jump(const GraphBuffers &g, cudaStream_t st) {
+  u32 ne = 2 * g.n_nodes;
+  k_cycle_jump<<<blocks_for(ne, 256), 256, 0, st>>>((u64 *)g.cq, ne, (const u64 *)g.node_lo, (const u64 *)g.node_hi);
+  return 1;
+}
+int launch_cycle_cut(const GraphBuffers &g, cudaStream_t st) {
+  u32 ne = 2 * g.n_nodes;
+  k_cycle_cut<<<blocks_for(ne, 256), 256, 0, st>>>((const u64 *)g.cq, g.succ, ne, (u64 *)g.pd, g.circ);
+  return 1;
+}
+int launch_unitig_tails_heads(const GraphBuffers &g, int k, bool have_circ, cudaStream_t st) {
+  u32 ne = 2 * g.n_nodes;
+  if (!ne) return 0;
+  const uint8_t *circ = have_circ ? g.circ : nullptr;
+  k_unitig_tails<<<blocks_for(ne, 256), 256, 0, st>>>((const u64 *)g.pd, g.succ, circ, ne, g.tail_of, g.len_of);
+  k_unitig_heads<<<blocks_for(ne, 256), 256, 0, st>>>((const u64 *)g.pd, circ, g.tail_of, g.len_of,
+                                                      (const u64 *)g.node_lo, (const u64 *)g.node_hi, ne, k,
+                                                      g.unitig_of_head, (UnitigRec *)g.recs, g.ucirc, g.scal + 2,
+                                                      (u64 *)g.seq_cursor);
+  return 2;
+}
+int launch_unitig_emit(int kw, const GraphBuffers &g, int k, cudaStream_t st) {
+  u32 ne = 2 * g.n_nodes;
+  if (!ne) return 0;
+  if (kw == 1)
+    k_unitig_emit<1><<<blocks_for(ne, 256), 256, 0, st>>>((const u64 *)g.pd, g.unitig_of_head, (const UnitigRec *)g.recs,
+                                                          (const u64 *)g.node_lo, (const u64 *)g.node_hi, g.node_count,
+                                                          ne, k, g.seq, (u64 *)g.cov_sum, g.elem_unitig);
+  else
+    k_unitig_emit<2><<<blocks_for(ne, 256), 256, 0, st>>>((const u64 *)g.pd, g.unitig_of_head, (const UnitigRec *)g.recs,
+                                                          (const u64 *)g.node_lo, (const u64 *)g.node_hi, g.node_count,
+                                                          ne, k, g.seq, (u64 *)g.cov_sum, g.elem_unitig);
+  return 1;
+}
+int launch_unitig_links_out(int kw, void *slots, uint64_t cap, int k, const GraphBuffers &g, uint32_t n_unitigs,
+                            cudaStream_t st) {
+  if (!n_unitigs) return 0;
+  u32 max_probe = (u32)(cap < 4096 ? cap : 4096);
+  unsigned b = blocks_for(2ull * n_unitigs, 256);
+  if (kw == 1)
+    k_unitig_links_out<1><<<b, 256, 0, st>>>(Table<1>{(Slot1 *)slots, cap, max_probe}, k, (const UnitigRec *)g.recs,
+                                             n_unitigs, g.tail_of, g.unitig_of_head, (const u64 *)g.node_lo,
+                                             (const u64 *)g.node_hi, g.node_edges, g.ucirc, g.link_from, g.link_to,
+                                             g.link_cap, g.scal + 3);
+  else
+    k_unitig_links_out<2><<<b, 256, 0, st>>>(Table<2>{(Slot2 *)slots, cap, max_probe}, k, (const UnitigRec *)g.recs,
+                                             n_unitigs, g.tail_of, g.unitig_of_head, (const u64 *)g.node_lo,
+                                             (const u64 *)g.node_hi, g.node_edges, g.ucirc, g.link_from, g.link_to,
+                                             g.link_cap, g.scal + 3);
+  return 1;
+}
+
+}  // namespace shk

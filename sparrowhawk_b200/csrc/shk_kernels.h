@@ -1,0 +1,51 @@
+// shk_kernels.h — launch wrappers of the sm_100a kernels (shk_kernels.cu).
+// kw = 1 for k <= 31 (64-bit keys, 16-byte slots), 2 for k <= 63 (128-bit keys,
+// 32-byte slots).  All pointers are device pointers; every wrapper only
+// enqueues on `st` and returns the number of kernels it launched.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace shk {
+
+struct GraphBuffers {
+  // nodes (dense, after K2)
+  uint64_t *node_lo, *node_hi; uint16_t *node_count; uint8_t *node_raw, *node_edges;
+  uint32_t n_nodes;
+  // per element (2 * n_nodes)
+  uint32_t *uniq, *succ, *tail_of, *len_of, *unitig_of_head, *elem_unitig;
+  uint64_t *pd, *cq; uint8_t *circ;
+  // unitigs
+  void *recs; uint8_t *ucirc; uint64_t *cov_sum; char *seq;
+  uint32_t *link_from, *link_to; uint32_t link_cap;
+  // device scalars: [0] changed, [1] n_cyclic, [2] n_unitigs, [3] n_links ; cursor
+  uint32_t *scal; uint64_t *seq_cursor;
+};
+
+size_t slot_bytes(int kw);
+int sm_count();
+
+int launch_pack_reads(const uint8_t *seq, const uint8_t *qual, uint64_t n, uint64_t nwords, int min_qual,
+                      uint64_t *bases, uint32_t *mask, uint64_t *counters, cudaStream_t st);
+int launch_table_fill(void *slots, uint64_t cap, int kw, cudaStream_t st);
+int launch_extract_count(int kw, const uint64_t *bases, const uint32_t *mask, uint64_t nwords, int k,
+                         void *slots, uint64_t cap, uint64_t *counters, uint32_t *overflow, cudaStream_t st);
+int launch_rehash(int kw, void *old_slots, uint64_t old_cap, void *new_slots, uint64_t new_cap,
+                  uint32_t *overflow, cudaStream_t st);
+int launch_histogram_only(int kw, void *slots, uint64_t cap, uint64_t *histo, cudaStream_t st);
+int launch_histogram_filter(int kw, void *slots, uint64_t cap, int min_count, uint64_t *histo,
+                            uint64_t *node_lo, uint64_t *node_hi, uint16_t *node_count, uint8_t *node_raw,
+                            uint32_t node_cap, uint32_t *n_nodes, cudaStream_t st);
+int launch_build_edges(int kw, void *slots, uint64_t cap, int k, const GraphBuffers &g, cudaStream_t st);
+int launch_links_and_rank_init(const GraphBuffers &g, cudaStream_t st);
+int launch_rank_jump(const GraphBuffers &g, cudaStream_t st);
+int launch_cycle_init(const GraphBuffers &g, cudaStream_t st);
+int launch_cycle_jump(const GraphBuffers &g, cudaStream_t st);
+int launch_cycle_cut(const GraphBuffers &g, cudaStream_t st);
+int launch_unitig_tails_heads(const GraphBuffers &g, int k, bool have_circ, cudaStream_t st);
+int launch_unitig_emit(int kw, const GraphBuffers &g, int k, cudaStream_t st);
+int launch_unitig_links_out(int kw, void *slots, uint64_t cap, int k, const GraphBuffers &g,
+                            uint32_t n_unitigs, cudaStream_t st);
+size_t unitig_rec_bytes();
+
+}  // namespace shk

@@ -1,0 +1,76 @@
+"""Shared checker: CUDA path (through the C ABI) vs the CPU oracle, bit-exact
+in the comparison form of SURVEY.md S15."""
+import numpy as np
+
+from oracle import Oracle
+
+_COMP = str.maketrans("ACGT", "TGCA")
+
+
+def canon_unitig(s):
+    r = s.translate(_COMP)[::-1]
+    return min(s, r)
+
+
+def sort_by_key(lo, hi, *cols):
+    order = np.lexsort((lo, hi))
+    return (lo[order], hi[order]) + tuple(c[order] for c in cols)
+
+
+def run_oracle(seq, qual, k, min_count, min_qual, nthreads=4):
+    o = Oracle(k, min_count, min_qual, nthreads)
+    o.add_reads(seq, qual)
+    o.finish_count()
+    o.build_graph()
+    return o
+
+
+def assert_parity(helper, oracle, check_table=True, check_unitigs=True):
+    """helper: AssemblyHelper after run() (or count+filter+build_graph with the
+    table exported beforehand via `helper._table`)."""
+    so, sg = oracle.stats(), helper.stats()
+    for f in ("n_bases", "n_instances", "n_distinct", "n_nodes"):
+        assert sg[f] == so[f], (f, sg[f], so[f])
+    assert np.array_equal(helper.histogram(), oracle.histogram()), "spectrum differs"
+    if check_table and getattr(helper, "_table", None) is not None:
+        glo, ghi, gc, ge = sort_by_key(*helper._table)
+        olo, ohi, oc, oe = oracle.export_table()          # already sorted
+        assert np.array_equal(glo, olo) and np.array_equal(ghi, ohi), "distinct k-mer sets differ"
+        assert np.array_equal(gc, oc), "counts differ"
+        assert np.array_equal(ge, oe), "read-evidenced edge bits differ"
+    glo, ghi, gc, graw, gval = sort_by_key(*helper.export_kmers())
+    olo, ohi, oc, oraw, oval = oracle.export_kmers()
+    assert np.array_equal(glo, olo) and np.array_equal(ghi, ohi), "filtered k-mer sets differ"
+    assert np.array_equal(gc, oc), "filtered counts differ"
+    assert np.array_equal(graw, oraw), "raw edge bits differ"
+    assert np.array_equal(gval, oval), "validated edge set differs"
+    if check_unitigs:
+        assert sg["n_unitigs"] == so["n_unitigs"], (sg["n_unitigs"], so["n_unitigs"])
+        assert sg["unitig_bases"] == so["unitig_bases"]
+        gu, gcov, gcirc = helper.export_unitigs()
+        ou, ocov, ocirc = oracle.export_unitigs()
+        gs = sorted(zip((canon_unitig(u) for u in gu), (round(float(c), 3) for c in gcov), (int(c) for c in gcirc)))
+        os_ = sorted(zip(ou, (round(float(c), 3) for c in ocov), (int(c) for c in ocirc)))
+        assert [g[0] for g in gs] == [o[0] for o in os_], "unitig multisets differ"
+        assert [g[2] for g in gs] == [o[2] for o in os_], "circular flags differ"
+        assert np.allclose([g[1] for g in gs], [o[1] for o in os_], rtol=1e-5, atol=2e-3), "mean coverage differs"
+
+
+def gpu_pipeline(seq, qual, k, min_count, min_qual, keep_table=True, **kw):
+    from sparrowhawk_b200 import AssemblyHelper
+    h = AssemblyHelper(k, False, min_count, min_qual, 0, False, False, False, False, **kw)
+    h.load_reads(seq, qual)
+    h.count(True)
+    h._table = h.export_table() if keep_table else None
+    h.filter()
+    h.build_graph()
+    return h
+
+
+def make_stream(reads, quals=None):
+    seq = b"".join(r.encode() + b"\n" for r in reads)
+    if quals is None:
+        qual = b"".join(b"I" * len(r) + b"\n" for r in reads)
+    else:
+        qual = b"".join(q.encode() + b"\n" for q in quals)
+    return np.frombuffer(seq, np.uint8).copy(), np.frombuffer(qual, np.uint8).copy()

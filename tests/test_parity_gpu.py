@@ -1,0 +1,182 @@
+"""GPU parity tests proper: the CUDA path, called through the C ABI
+(libshk_b200.so), against the CPU oracle on the same inputs — bit-exact k-mer
+counts, spectrum, filtered nodes, read-evidenced + validated edge bits and the
+unitig multiset."""
+import json
+import os
+import random
+
+import numpy as np
+import pytest
+
+from oracle import Oracle
+from sparrowhawk_b200 import AssemblyHelper, ShkError, synth
+
+from parity import assert_parity, canon_unitig, gpu_pipeline, make_stream, run_oracle
+from test_oracle import GOLD, _rand_case, parse_fastq, stream
+
+pytestmark = pytest.mark.gpu
+
+
+def check(seq, qual, k, min_count, min_qual, **kw):
+    h = gpu_pipeline(seq, qual, k, min_count, min_qual, **kw)
+    o = run_oracle(seq, qual, k, min_count, min_qual)
+    assert_parity(h, o)
+    return h, o
+
+
+def test_micro_cases_golden():
+    cases = json.load(open(os.path.join(GOLD, "micro_cases.json")))["cases"]
+    for c in cases:
+        seq = np.frombuffer((c["seq"] + "\n").encode(), np.uint8).copy()
+        h = gpu_pipeline(seq, None, c["k"], c["min_count"], 0)
+        st = h.stats()
+        assert st["n_bases"] == c["n_bases"] and st["n_instances"] == c["n_instances"]
+        lo, hi, cnt, e = h._table
+        assert sorted([int(a), int(b)] for a, b in zip(lo, cnt)) == c["counts"]
+        lo, hi, cnt, raw, val = h.export_kmers()
+        assert sorted([int(a), int(b), int(v)] for a, b, v in zip(lo, cnt, val)) == c["nodes"]
+        assert sorted(canon_unitig(u) for u in h.export_unitigs()[0]) == c["unitigs"]
+
+
+def test_sketchlib_fastq_kat_through_gpu(tmp_path):
+    """Reference fixtures through the product's own FASTQ(.gz) reader + K0."""
+    import gzip
+    kat = json.load(open(os.path.join(GOLD, "sketchlib_fastq_kat.json")))
+    for name, smp in kat["samples"].items():
+        p1, p2 = tmp_path / f"{name}_fwd.fastq.gz", tmp_path / f"{name}_rev.fastq"
+        with gzip.open(p1, "wt") as f:
+            f.write(smp["fastq"]["fwd"])
+        p2.write_text(smp["fastq"]["rev"])
+        h = AssemblyHelper.new(9, True, 2, 2, 0, False, False, False, False)
+        h.preprocess(p1, p2)
+        st = h.stats()
+        assert st["n_bases"] == sum(smp["acgt"]) + smp["non_acgt"]
+        o = Oracle(9, 2, 2, 1)
+        for mate in ("fwd", "rev"):
+            o.add_reads(*stream(*parse_fastq(smp["fastq"][mate])))
+        o.finish_count(); o.build_graph()
+        h.assemble()
+        assert_parity(h, o, check_table=False)
+
+
+@pytest.mark.parametrize("k", [3, 5, 11, 21, 31, 33, 47, 63])
+def test_random_reads_all_k(k):
+    rng = random.Random(2000 + k)
+    reads, quals = _rand_case(rng, k, 400, 600, 0.01)
+    seq, qual = stream(reads, quals)
+    for min_count in (0, 2):
+        check(seq, qual, k, min_count, 20)
+
+
+def test_edge_cases():
+    # empty input, reads shorter than k, all-N, lower case + U, no trailing newline
+    for reads in ([], ["ACGT"], ["NNNNNNNNNNNNNNNNNNNNNNNNNNNNNNNNNNNNNN"], ["acgtuacgtuacgtuacgtuacgtuacgtuacgtuacgu"],
+                  ["A" * 100], ["ACGTTGCAACGT" * 8]):
+        seq, qual = make_stream(reads)
+        check(seq, qual, 31 if reads and len(reads[0]) > 40 else 5, 0, 0)
+    seq = np.frombuffer(b"ACGTACGGTTACGATCGATTTACG", np.uint8).copy()     # no '\n' at the end
+    check(seq, None, 7, 0, 0)
+    # quality exactly at the threshold (S3): '5' = phred 20 passes, '4' = 19 fails
+    seq, qual = make_stream(["ACGTACGGTTACGATCGATTTACG"], ["IIIIIIIIII5IIIII4IIIIIII"])
+    check(seq, qual, 5, 0, 20)
+
+
+def test_circular_and_hairpin():
+    rng = random.Random(5)
+    for k in (7, 33):
+        g = "".join(rng.choice("ACGT") for _ in range(200))
+        circ = g + g[:k]
+        for reads in ([circ, circ], ["ACGTTGCAACGT" * 6], [circ, "ACGTTGCAACGT" * 6, g[50:150]]):
+            seq, qual = make_stream(reads)
+            h, o = check(seq, qual, k, 0, 0)
+        seq, qual = make_stream([circ, circ])
+        h, _ = check(seq, qual, k, 0, 0)
+        u, cov, c = h.export_unitigs()
+        assert len(u) == 1 and c[0] == 1 and len(u[0]) == 200 + k - 1
+
+
+@pytest.mark.parametrize("cfg", [dict(G=50_000, cov=30.0, err=0.005, k=31, mc=3),
+                                 dict(G=40_000, cov=40.0, err=0.01, k=63, mc=5),
+                                 dict(G=300_000, cov=30.0, err=0.005, k=31, mc=3)])
+def test_synthetic_reads(cfg):
+    seq, qual = synth.reads(3, cfg["G"], cfg["cov"], cfg["err"])
+    h, o = check(seq, qual, cfg["k"], cfg["mc"], 20)
+    # invariants
+    st = h.stats()
+    assert int(h.histogram().sum()) == st["n_distinct"]
+    assert st["unitig_bases"] == st["n_nodes"] + st["n_unitigs"] * (cfg["k"] - 1)
+
+
+def test_invariance_read_order_and_mate_swap():
+    seq, qual = synth.reads(9, 30_000, 20.0, 0.01)
+    L = 151
+    recs = seq.reshape(-1, L); qrecs = qual.reshape(-1, L)
+    perm = np.random.RandomState(0).permutation(len(recs))
+    h1 = gpu_pipeline(seq, qual, 31, 2, 20)
+    h2 = gpu_pipeline(recs[perm].reshape(-1).copy(), qrecs[perm].reshape(-1).copy(), 31, 2, 20)
+    a = sorted(canon_unitig(u) for u in h1.export_unitigs()[0])
+    b = sorted(canon_unitig(u) for u in h2.export_unitigs()[0])
+    assert a == b
+    assert np.array_equal(h1.histogram(), h2.histogram())
+
+
+def test_table_growth_and_tiny_table():
+    seq, qual = synth.reads(5, 20_000, 20.0, 0.01)
+    h = gpu_pipeline(seq, qual, 31, 2, 20, table_slots=1000)     # forces several growth retries
+    assert h.stats()["table_retries"] >= 1
+    assert_parity(h, run_oracle(seq, qual, 31, 2, 20))
+
+
+def test_chunked_equals_bulk(tmp_path):
+    seq, qual = synth.reads(6, 20_000, 20.0, 0.01)
+    p1, p2 = str(tmp_path / "a_1.fastq"), str(tmp_path / "a_2.fastq.gz")
+    synth.write_fastq(p1, p2 + ".tmp", seq, qual)
+    import gzip, shutil
+    with open(p2 + ".tmp", "rb") as fi, gzip.open(p2, "wb") as fo:
+        shutil.copyfileobj(fi, fo)
+    o = run_oracle(seq, qual, 31, 2, 20)
+    states = {}
+    for chunk in (0, 777):
+        st = []
+        h = AssemblyHelper.new(31, True, 2, 20, chunk, False, False, False, False, progress=st.append)
+        h.preprocess(p1, p2)
+        info = h.preprocessing_result()
+        assert info["nkmers"] == o.stats()["n_nodes"] and info["used_min_count"] == 2
+        assert info["histo"] == [int(x) for x in o.histogram()] and len(info["histo"]) == 500
+        h.assemble()
+        assert_parity(h, o, check_table=False)
+        res = h.assembly_result()
+        assert set(res) == {"outfasta", "ncontigs", "outdot", "outgfa", "outgfav2"}
+        assert res["ncontigs"] == o.stats()["n_unitigs"]
+        fa = [l for l in res["outfasta"].splitlines() if not l.startswith(">")]
+        assert sorted(fa) == sorted(o.export_unitigs()[0])
+        states[chunk] = st
+    assert states[0][:4] == ["preprocess:start", "preprocess:bulk:start", "preprocess:bulk:loop:start",
+                             "preprocess:bulk:loop:end"]
+    assert states[0][-6:] == ["assembly:start", "assembly:create_graph", "assembly:correct_graph",
+                              "assembly:collapse_graph", "assembly:saving", "assembly:end"]
+    assert any(s.startswith("preprocess:chunked:loop:") for s in states[777])
+    # streaming push form, ragged chunks
+    h = AssemblyHelper.new(31, False, 2, 20, 0, False, False, False, False)
+    data = open(p1, "rb").read() + gzip.open(p2, "rb").read()
+    rng = random.Random(1)
+    i = 0
+    while i < len(data):
+        n = rng.randint(1, 70_000)
+        h.preprocess_push(data[i:i + n]); i += n
+    h.preprocess_finish(); h.assemble()
+    assert_parity(h, o, check_table=False)
+
+
+def test_errors():
+    h = AssemblyHelper.new(31, False, 2, 20, 0, False, False, False, False)
+    with pytest.raises(ShkError):
+        h.assemble()                       # before preprocess
+    with pytest.raises(ShkError):
+        h.preprocess("/nonexistent/file.fastq")
+    with pytest.raises(ShkError):
+        h.preprocess_push(b"@r1\nACGT\n+\nIII\n"); h.preprocess_finish()   # qual length mismatch
+    h.close()
+    with pytest.raises(ShkError):
+        AssemblyHelper.new(32, False, 2, 20, 0, False, False, False, False)
