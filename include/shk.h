@@ -59,7 +59,7 @@ typedef struct shk_params {
   /* --- GPU-only knobs --- */
   int32_t device;              /* CUDA ordinal; -1 = current device */
   int32_t reserved0;
-  uint64_t table_slots;        /* initial hash-table capacity; 0 = auto */
+  uint64_t table_slots;        /* reserved (was: initial hash-table capacity); 0 */
   uint64_t reserved1;
 } shk_params;
 
@@ -127,17 +127,20 @@ typedef struct shk_stats {
   uint64_t n_bases;        /* sequence characters loaded (unit of the metric) */
   uint64_t n_positions;    /* stream positions incl. separators / padding */
   uint64_t n_instances;    /* valid k-mer instances counted */
-  uint64_t n_distinct;     /* distinct canonical k-mers before the filter */
+  uint64_t n_distinct;     /* distinct canonical k-mers before the filter (after shk_filter) */
   uint64_t n_nodes;        /* survivors of count > min_count (== nkmers) */
   uint64_t n_unitigs;
   uint64_t unitig_bases;   /* total length of all unitig sequences */
   uint64_t n_links;        /* unitig-level links (directed, both directions) */
-  uint64_t table_slots;    /* hash-table capacity finally used */
+  uint64_t table_slots;    /* fine buckets used by the partition pass */
   uint64_t gpu_launches;   /* kernels launched by this handle so far */
   int32_t used_min_count;
   int32_t table_retries;
   float ms_pack, ms_count, ms_filter, ms_graph; /* CUDA-event time of last run */
-  float ms_extract, reserved_f;                 /* K1 extract_count kernel alone */
+  float ms_extract;        /* K1a minimizer_partition kernel alone */
+  float ms_count_kernel;   /* K1b count_buckets main launch alone */
+  uint64_t n_spilled;      /* k-mer instances that went through the global overflow table */
+  uint64_t n_records;      /* super-k-mer records written by K1a */
 } shk_stats;
 
 /* Use `stream` (a cudaStream_t passed as void*) for all work of this handle;
@@ -154,10 +157,14 @@ shk_status shk_load_reads(shk_asm *h, const uint8_t *seq, const uint8_t *qual,
 shk_status shk_load_reads_device(shk_asm *h, const void *d_seq, const void *d_qual,
                                  size_t n, int append);
 
-/* K1 extract_count over the resident packed reads.  reset=1 clears the table
- * first (memset inside the timed region); reset=0 accumulates (chunked mode). */
+/* K1a minimizer_partition over ALL resident packed reads: cuts the stream into
+ * super-k-mer records grouped by minimizer bucket.  `reset` is kept for ABI
+ * stability: reads appended with append=1 are simply part of the resident
+ * stream, so chunked accumulation needs no separate mode. */
 shk_status shk_count(shk_asm *h, int reset);
-/* K2 histogram + min-count filter + compaction into dense node arrays. */
+/* K1b count_buckets (shared-memory hash tables) fused with K2: exact counts,
+ * 500-bin spectrum, min-count filter, compaction into dense node arrays, then
+ * the key -> node index used by the graph stage. */
 shk_status shk_filter(shk_asm *h);
 /* K3..K6 edge validation, unitig links, list ranking, unitig emission. */
 shk_status shk_build_graph(shk_asm *h);
@@ -178,10 +185,6 @@ shk_status shk_get_histogram(shk_asm *h, uint64_t *histo /*[SHK_HISTO_BINS]*/);
 shk_status shk_export_kmers(shk_asm *h, uint64_t *key_lo, uint64_t *key_hi,
                             uint16_t *counts, uint8_t *raw_edges, uint8_t *edges,
                             size_t cap, size_t *n);
-/* All distinct k-mers before the filter (test/diagnostic; may be large). */
-shk_status shk_export_table(shk_asm *h, uint64_t *key_lo, uint64_t *key_hi,
-                            uint32_t *counts, uint8_t *raw_edges, size_t cap,
-                            size_t *n);
 /* Unitigs: ASCII sequences concatenated in `seq` (no separators), offsets has
  * n_unitigs+1 entries, mean_cov = mean k-mer count, circular = 1 for a cycle. */
 shk_status shk_export_unitigs(shk_asm *h, char *seq, size_t seq_cap,

@@ -34,7 +34,7 @@ class ShkStats(C.Structure):
         ("unitig_bases", C.c_uint64), ("n_links", C.c_uint64), ("table_slots", C.c_uint64),
         ("gpu_launches", C.c_uint64), ("used_min_count", C.c_int32), ("table_retries", C.c_int32),
         ("ms_pack", C.c_float), ("ms_count", C.c_float), ("ms_filter", C.c_float), ("ms_graph", C.c_float),
-        ("ms_extract", C.c_float), ("reserved_f", C.c_float),
+        ("ms_extract", C.c_float), ("ms_count_kernel", C.c_float), ("n_spilled", C.c_uint64), ("n_records", C.c_uint64),
     ]
 
 
@@ -67,8 +67,6 @@ SYMBOLS = {
     "shk_get_stats": (C.c_int, [_H, C.POINTER(ShkStats)]),
     "shk_get_histogram": (C.c_int, [_H, C.c_void_p]),
     "shk_export_kmers": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t,
-                                   C.POINTER(C.c_size_t)]),
-    "shk_export_table": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t,
                                    C.POINTER(C.c_size_t)]),
     "shk_export_unitigs": (C.c_int, [_H, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]),
     "shk_export_links": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]),

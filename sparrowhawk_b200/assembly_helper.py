@@ -156,16 +156,6 @@ class AssemblyHelper:
                                          val.ctypes.data if validated else None, n, C.byref(got)))
         return lo, hi, cnt, raw, (val if validated else None)
 
-    def export_table(self):
-        n = self.stats()["n_distinct"]
-        lo = np.zeros(n, np.uint64); hi = np.zeros(n, np.uint64)
-        cnt = np.zeros(n, np.uint32); raw = np.zeros(n, np.uint8)
-        got = C.c_size_t()
-        check(self._lib.shk_export_table(self._h, lo.ctypes.data, hi.ctypes.data, cnt.ctypes.data, raw.ctypes.data,
-                                         n, C.byref(got)))
-        assert got.value == n, (got.value, n)
-        return lo, hi, cnt, raw
-
     def export_unitigs(self):
         st = self.stats()
         nu, nb = st["n_unitigs"], st["unitig_bases"]

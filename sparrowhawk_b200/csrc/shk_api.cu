@@ -8,6 +8,7 @@
 #include <cstring>
 #include <cmath>
 #include <algorithm>
+#include <vector>
 
 #include "shk_handle.h"
 
@@ -37,6 +38,18 @@ shk_status DevBuf::ensure(size_t bytes) {
 }
 void DevBuf::release() {
   if (p) cudaFree(p);
+  p = nullptr; cap = 0;
+}
+shk_status PinBuf::ensure_host(size_t bytes) {
+  if (bytes <= cap) return SHK_OK;
+  release();
+  cudaError_t e = cudaMallocHost(&p, bytes + bytes / 4 + 256);
+  if (e != cudaSuccess) { p = nullptr; return cuda_fail(e, "cudaMallocHost"); }
+  cap = bytes + bytes / 4 + 256;
+  return SHK_OK;
+}
+void PinBuf::release() {
+  if (p) cudaFreeHost(p);
   p = nullptr; cap = 0;
 }
 
@@ -116,141 +129,194 @@ static shk_status load_reads_host(shk_asm *h, const uint8_t *seq, const uint8_t 
   return SHK_OK;
 }
 
-// ---- K1: count ---------------------------------------------------------
-static uint64_t auto_table_slots(shk_asm *h, uint64_t positions) {
-  if (h->p.table_slots) return std::max<uint64_t>(h->p.table_slots, 64);
-  // distinct k-mers <= instances <= positions; sequencing reads at >= 20x carry
-  // ~0.1-0.5 distinct k-mers per base: start at 0.30 slots per
-  // position and grow on overflow.
-  return std::max<uint64_t>(1024, (uint64_t)((double)positions * 0.30));
-}
+// ---- K1a: minimizer partition into super-k-mer records ---------------------
+static uint32_t next_pow2(uint64_t x) { uint32_t p = 1; while (p < x && p < (1u << 30)) p <<= 1; return p; }
 
-static shk_status table_alloc_fill(shk_asm *h, DevBuf &buf, uint64_t cap) {
-  SHK_TRY(buf.ensure(cap * slot_bytes(h->kw)));
-  h->st.gpu_launches += launch_table_fill(buf.p, cap, h->kw, h->stream);
-  SHK_CUDA(cudaGetLastError());
-  return SHK_OK;
-}
+// instances a fine bucket should hold on average: all of them distinct must still
+// fit the shared-memory table of K1b at ~70 % load.
+static uint32_t target_bucket_instances(int kw) { return (uint32_t)(count_table_slots(kw) * 0.70); }
 
-static shk_status grow_table(shk_asm *h, uint64_t new_cap) {
-  for (int attempt = 0; attempt < 4; ++attempt, new_cap *= 2) {
-    DevBuf nb;
-    SHK_TRY(nb.ensure(new_cap * slot_bytes(h->kw)));
-    h->st.gpu_launches += launch_table_fill(nb.p, new_cap, h->kw, h->stream);
-    SHK_CUDA(cudaMemsetAsync(d_flags(h), 0, 4, h->stream));
-    h->st.gpu_launches += launch_rehash(h->kw, h->slots.p, h->cap, nb.p, new_cap, d_flags(h), h->stream);
-    SHK_CUDA(cudaGetLastError());
-    SHK_TRY(read_scalars(h));
-    uint32_t ovf = *(uint32_t *)(h->h_pinned + 8 + SHK_HISTO_BINS);
-    if (!ovf) {
-      h->slots.release();
-      h->slots = nb; h->cap = new_cap;
-      return SHK_OK;
-    }
-    nb.release();
-  }
-  set_error("k-mer table overflow while growing");
-  return SHK_ERR_TABLE_FULL;
-}
-
-static shk_status count_impl(shk_asm *h, int reset) {
+static shk_status count_impl(shk_asm *h, int /*reset*/) {
   SHK_TRY(require_device(h));
-  if (!h->nwords && reset) { /* empty input is legal: zero k-mers */ }
-  if (!reset && !h->table_live) reset = 1;
   SHK_CUDA(cudaEventRecord(h->ev[2], h->stream));
   const uint64_t *b = h->bases.as<uint64_t>() + 1;
   const uint32_t *m = h->mask.as<uint32_t>() + 1;
-  if (reset) {
-    uint64_t cap = auto_table_slots(h, h->nwords * 32);
-    h->st.table_retries = 0;
-    for (;;) {
-      h->cap = cap;
-      SHK_TRY(table_alloc_fill(h, h->slots, cap));
-      SHK_CUDA(cudaMemsetAsync(d_counters(h) + 1, 0, 16, h->stream));   // n_instances, n_distinct
-      SHK_CUDA(cudaMemsetAsync(d_flags(h), 0, 4, h->stream));
-      SHK_CUDA(cudaEventRecord(h->ev[8], h->stream));
-      if (h->nwords)
-        h->st.gpu_launches += launch_extract_count(h->kw, b, m, h->nwords, h->p.k, h->slots.p, h->cap,
-                                                   d_counters(h), d_flags(h), h->stream);
-      SHK_CUDA(cudaGetLastError());
-      SHK_CUDA(cudaEventRecord(h->ev[9], h->stream));
-      SHK_CUDA(cudaEventRecord(h->ev[3], h->stream));
-      SHK_TRY(read_scalars(h));
-      uint32_t ovf = *(uint32_t *)(h->h_pinned + 8 + SHK_HISTO_BINS);
-      uint64_t distinct = h->h_pinned[2];
-      // a table above 90 % load has degenerate probe lengths even if it fitted
-      if (!ovf && distinct * 10 <= cap * 9) break;
-      if (++h->st.table_retries > 8) { set_error("k-mer table overflow (cap %llu)", (unsigned long long)cap); return SHK_ERR_TABLE_FULL; }
-      cap = std::max<uint64_t>(cap * 2, distinct * 2);
-    }
-  } else {
-    // chunked accumulation: keep load <= 0.7 assuming every new position is a new k-mer
-    SHK_TRY(read_scalars(h));
-    uint64_t distinct = h->h_pinned[2];
-    uint64_t worst = distinct + h->nwords * 32;
-    if (worst * 10 > h->cap * 7) SHK_TRY(grow_table(h, std::max<uint64_t>(h->cap * 2, worst * 2)));
-    SHK_CUDA(cudaMemsetAsync(d_flags(h), 0, 4, h->stream));
+  const uint64_t positions = h->nwords * 32;
+  const int k = h->p.k;
+  // fine buckets: power of two, sized from the input alone
+  uint32_t P = next_pow2(std::max<uint64_t>(16, positions / target_bucket_instances(h->kw)));
+  if (P > (1u << 20)) P = 1u << 20;
+  // records per bucket: a run holds ~ (w+1)/2 k-mers for a window of w = k-m+1 m-mers
+  const int mlen = k < 11 ? k : 11, w = k - mlen + 1;
+  double avg_run = std::min<double>(records_max_run(h->kw, k), std::max(1.0, (w + 1) / 2.0 * 0.6));
+  uint64_t rcap64 = (uint64_t)(3.0 * (double)positions / avg_run / (double)P) + 64;
+  h->st.table_retries = 0;
+  for (;;) {
+    if (rcap64 > 0x7FFFFFFFull) { set_error("record region too large"); return SHK_ERR_OOM; }
+    uint32_t rcap = (uint32_t)rcap64;
+    SHK_TRY(h->skrecs.ensure((size_t)P * rcap * record_bytes(h->kw)));
+    SHK_TRY(h->bfill.ensure((size_t)P * 8));
+    SHK_TRY(h->hfill.ensure_host((size_t)P * 8));
+    SHK_CUDA(cudaMemsetAsync(h->bfill.p, 0, (size_t)P * 8, h->stream));
+    SHK_CUDA(cudaMemsetAsync(d_counters(h) + 1, 0, 8, h->stream));    // n_instances
     SHK_CUDA(cudaEventRecord(h->ev[8], h->stream));
-    if (h->nwords)
-      h->st.gpu_launches += launch_extract_count(h->kw, b, m, h->nwords, h->p.k, h->slots.p, h->cap, d_counters(h),
-                                                 d_flags(h), h->stream);
+    uint32_t *fill = h->bfill.as<uint32_t>(), *kcount = fill + P;
+    h->st.gpu_launches += launch_partition(h->kw, b, m, h->nwords, k, P, rcap, h->skrecs.p, fill, kcount, d_counters(h), h->stream);
     SHK_CUDA(cudaGetLastError());
     SHK_CUDA(cudaEventRecord(h->ev[9], h->stream));
+    SHK_CUDA(cudaMemcpyAsync(h->hfill.p, h->bfill.p, (size_t)P * 8, cudaMemcpyDeviceToHost, h->stream));
     SHK_CUDA(cudaEventRecord(h->ev[3], h->stream));
     SHK_TRY(read_scalars(h));
-    if (*(uint32_t *)(h->h_pinned + 8 + SHK_HISTO_BINS)) { set_error("k-mer table overflow in chunked mode"); return SHK_ERR_TABLE_FULL; }
+    const uint32_t *hf = (const uint32_t *)h->hfill.p;
+    uint32_t mx = 0; uint64_t nrec = 0;
+    for (uint32_t i = 0; i < P; ++i) { mx = std::max(mx, hf[i]); nrec += hf[i]; }
+    h->P = P; h->rcap = rcap; h->n_records = nrec;
+    if (mx <= rcap) break;
+    if (++h->st.table_retries > 3) { set_error("record regions overflow after retries"); return SHK_ERR_TABLE_FULL; }
+    rcap64 = (uint64_t)mx + mx / 4 + 64;              // exact need is known now
   }
-  // totals over everything counted into the live table (chunked mode adds up)
-  h->n_bases = (reset ? 0 : h->n_bases) + h->h_pinned[3];
-  h->counted_positions = (reset ? 0 : h->counted_positions) + h->n_positions;
+  h->n_bases = h->h_pinned[3];
+  h->counted_positions = h->n_positions;
   h->st.n_bases = h->n_bases;
   h->st.n_positions = h->counted_positions;
   h->st.n_instances = h->h_pinned[1];
-  h->st.n_distinct = h->h_pinned[2];
-  h->st.table_slots = h->cap;
-  h->table_live = true; h->counted = true; h->filtered = h->graphed = false;
+  h->st.n_distinct = 0;
+  h->st.table_slots = (uint64_t)P;
+  h->counted = true; h->filtered = h->graphed = false;
   return SHK_OK;
 }
 
-// ---- K2: histogram + filter + compaction ---------------------------------
-static shk_status histogram_impl(shk_asm *h) {
-  SHK_CUDA(cudaMemsetAsync(d_histo(h), 0, SHK_HISTO_BINS * 8, h->stream));
-  h->st.gpu_launches += launch_histogram_only(h->kw, h->slots.p, h->cap, d_histo(h), h->stream);
+// ---- K1b + K2: shared-memory count, spectrum, filter, compaction -----------------
+// Groups of consecutive fine buckets whose estimated distinct k-mers fit the
+// shared table at ~55 % load.  `ratio` = distinct / instances estimate.
+static void plan_groups(shk_asm *h, uint32_t first_bucket, double ratio, std::vector<uint32_t> &gs) {
+  const uint32_t *kc = (const uint32_t *)h->hfill.p + h->P;
+  const double budget = count_table_slots(h->kw) * 0.55;
+  const uint32_t maxc = (uint32_t)count_max_group();
+  double acc = 0; uint32_t cnt = 0;
+  for (uint32_t bkt = first_bucket; bkt < h->P; ++bkt) {
+    double est = kc[bkt] * ratio;
+    if (cnt && (acc + est > budget || cnt >= maxc)) { gs.push_back(bkt); acc = 0; cnt = 0; }
+    acc += est; ++cnt;
+  }
+  gs.push_back(h->P);
+}
+
+static shk_status count_groups(shk_asm *h, const std::vector<uint32_t> &gs, uint32_t g_begin, uint32_t g_end,
+                               int min_count, uint32_t node_cap) {
+  uint32_t *fill = h->bfill.as<uint32_t>();
+  SHK_CUDA(cudaMemsetAsync(d_flags(h) + 2, 0, 4, h->stream));       // next_group
+  h->st.gpu_launches += launch_count_buckets(h->kw, h->skrecs.p, fill, h->rcap, h->groups.as<uint32_t>(), g_begin, g_end,
+                                             d_flags(h) + 2, h->p.k, min_count, h->ovf.p, h->ovf_cap, d_flags(h),
+                                             d_histo(h), h->node_lo.as<uint64_t>(), h->node_hi.as<uint64_t>(),
+                                             h->node_count.as<uint16_t>(), h->node_raw.as<uint8_t>(), node_cap,
+                                             d_flags(h) + 1, d_counters(h), h->stream);
   SHK_CUDA(cudaGetLastError());
-  SHK_TRY(read_scalars(h));
-  memcpy(h->histo, h->h_pinned + 8, sizeof h->histo);
+  (void)gs;
   return SHK_OK;
 }
 
-static shk_status filter_impl(shk_asm *h, int min_count) {
+static shk_status filter_impl(shk_asm *h, int min_count, bool histogram_only = false) {
   SHK_TRY(require_device(h));
-  if (!h->counted || !h->table_live) { set_error("filter before count"); return SHK_ERR_STATE; }
+  if (!h->counted) { set_error("filter before count"); return SHK_ERR_STATE; }
   SHK_CUDA(cudaEventRecord(h->ev[4], h->stream));
-  uint64_t nd = h->st.n_distinct;
-  if (nd > 0xFFFFFFF0ull) { set_error("more than 2^32 distinct k-mers"); return SHK_ERR_BAD_ARG; }
-  uint32_t node_cap = (uint32_t)std::max<uint64_t>(nd, 1);
+  const uint64_t ninst = h->st.n_instances;
+  // survivors have count > min_count  =>  n_nodes <= instances / (min_count + 1)
+  uint64_t bound = histogram_only ? 1 : ninst / ((uint64_t)std::max(min_count, 0) + 1) + 1;
+  if (bound > 0xFFFFFFF0ull) { set_error("more than 2^32 k-mers can pass the filter"); return SHK_ERR_BAD_ARG; }
+  uint32_t node_cap = (uint32_t)bound;
   SHK_TRY(h->node_lo.ensure((size_t)node_cap * 8));
   if (h->kw == 2) SHK_TRY(h->node_hi.ensure((size_t)node_cap * 8));
   SHK_TRY(h->node_count.ensure((size_t)node_cap * 2));
   SHK_TRY(h->node_raw.ensure((size_t)node_cap));
   h->node_cap = node_cap;
-  SHK_CUDA(cudaMemsetAsync(d_histo(h), 0, SHK_HISTO_BINS * 8, h->stream));
-  SHK_CUDA(cudaMemsetAsync(d_flags(h) + 1, 0, 4, h->stream));   // n_nodes
-  h->st.gpu_launches += launch_histogram_filter(h->kw, h->slots.p, h->cap, min_count, d_histo(h),
-                                                h->node_lo.as<uint64_t>(), h->node_hi.as<uint64_t>(),
-                                                h->node_count.as<uint16_t>(), h->node_raw.as<uint8_t>(), node_cap,
-                                                d_flags(h) + 1, h->stream);
-  SHK_CUDA(cudaGetLastError());
-  SHK_CUDA(cudaEventRecord(h->ev[5], h->stream));
-  SHK_TRY(read_scalars(h));
+  const int mc_eff = histogram_only ? 0x7FFFFFFF : min_count;
+  double ratio = h->ratio_est;
+  for (int attempt = 0;; ++attempt) {
+    // overflow table: only keys that found no room in a shared table land here
+    uint64_t ovf_cap = std::max<uint64_t>(1u << 16, ninst / (attempt ? 4 : 32));
+    SHK_TRY(h->ovf.ensure(ovf_cap * slot_bytes(h->kw)));
+    h->ovf_cap = ovf_cap;
+    h->st.gpu_launches += launch_table_fill(h->ovf.p, ovf_cap, h->kw, h->stream);
+    SHK_CUDA(cudaMemsetAsync(d_histo(h), 0, SHK_HISTO_BINS * 8, h->stream));
+    SHK_CUDA(cudaMemsetAsync(d_counters(h) + 2, 0, 8, h->stream));       // n_distinct
+    SHK_CUDA(cudaMemsetAsync(d_counters(h) + 4, 0, 16, h->stream));      // spilled, decoded
+    SHK_CUDA(cudaMemsetAsync(d_flags(h), 0, 8, h->stream));              // overflow flag, n_nodes
+    std::vector<uint32_t> gs;
+    gs.push_back(0);
+    uint32_t pilot_groups = 0;
+    if (ratio <= 0 && h->P > 256) {
+      // no estimate yet: count a pilot of single-bucket groups, measure distinct / instances
+      pilot_groups = std::min<uint32_t>(h->P / 8, 2 * (uint32_t)sm_count());
+      for (uint32_t i = 1; i <= pilot_groups; ++i) gs.push_back(i);
+      SHK_TRY(h->groups.ensure((size_t)(pilot_groups + 1) * 4));
+      SHK_CUDA(cudaMemcpyAsync(h->groups.p, gs.data(), (size_t)(pilot_groups + 1) * 4, cudaMemcpyHostToDevice, h->stream));
+      SHK_TRY(count_groups(h, gs, 0, pilot_groups, mc_eff, node_cap));
+      SHK_TRY(read_scalars(h));
+      uint64_t pd = h->h_pinned[2], pi = h->h_pinned[5];
+      ratio = pi ? std::min(1.0, std::max(0.02, 1.15 * (double)pd / (double)pi)) : 0.5;
+    } else if (ratio <= 0) {
+      ratio = 1.0;                                    // tiny input: one bucket per group always fits
+    }
+    plan_groups(h, pilot_groups, ratio, gs);
+    const uint32_t ngroups = (uint32_t)gs.size() - 1;
+    SHK_TRY(h->groups.ensure(gs.size() * 4));
+    SHK_CUDA(cudaMemcpyAsync(h->groups.p, gs.data(), gs.size() * 4, cudaMemcpyHostToDevice, h->stream));
+    SHK_CUDA(cudaEventRecord(h->ev[10], h->stream));
+    SHK_TRY(count_groups(h, gs, pilot_groups, ngroups, mc_eff, node_cap));
+    SHK_CUDA(cudaEventRecord(h->ev[11], h->stream));
+    SHK_TRY(read_scalars(h));
+    uint32_t *fl = (uint32_t *)(h->h_pinned + 8 + SHK_HISTO_BINS);
+    const uint64_t spilled = h->h_pinned[4];
+    h->st.n_spilled = spilled; h->st.n_records = h->n_records;
+    if (fl[0]) {                                      // overflow table itself overflowed: replan denser
+      if (attempt >= 3) { set_error("k-mer overflow table full after retries"); return SHK_ERR_TABLE_FULL; }
+      ratio = std::min(1.0, ratio * 2.0); ++h->st.table_retries;
+      continue;
+    }
+    if (spilled) {
+      // sweep the overflow table into the same spectrum / node arrays
+      h->st.gpu_launches += launch_histogram_filter(h->kw, h->ovf.p, h->ovf_cap, mc_eff, d_histo(h),
+                                                    h->node_lo.as<uint64_t>(), h->node_hi.as<uint64_t>(),
+                                                    h->node_count.as<uint16_t>(), h->node_raw.as<uint8_t>(), node_cap,
+                                                    d_flags(h) + 1, h->stream);
+      SHK_CUDA(cudaGetLastError());
+      SHK_TRY(read_scalars(h));
+    }
+    break;
+  }
   memcpy(h->histo, h->h_pinned + 8, sizeof h->histo);
-  h->st.n_nodes = ((uint32_t *)(h->h_pinned + 8 + SHK_HISTO_BINS))[1];
+  uint64_t nd = 0;
+  for (int i = 0; i < SHK_HISTO_BINS; ++i) nd += h->histo[i];
+  h->st.n_distinct = nd;
+  if (ninst) h->ratio_est = std::min(1.0, 1.10 * (double)nd / (double)ninst + 0.005);
+  uint32_t nn = ((uint32_t *)(h->h_pinned + 8 + SHK_HISTO_BINS))[1];
+  if (nn > node_cap) { set_error("node buffer overflow (%u > %u)", nn, node_cap); return SHK_ERR_STATE; }
+  if (histogram_only) { SHK_CUDA(cudaEventRecord(h->ev[5], h->stream)); return SHK_OK; }
+  h->st.n_nodes = nn;
   h->st.used_min_count = min_count;
-  h->table_live = false;      // count words now hold node ids
+  // node index for the graph stage: key -> node id, 2 slots per node
+  uint64_t icap = std::max<uint64_t>(64, 2ull * nn);
+  for (int attempt = 0;; ++attempt) {
+    SHK_TRY(h->slots.ensure(icap * slot_bytes(h->kw)));
+    h->cap = icap;
+    h->st.gpu_launches += launch_table_fill(h->slots.p, icap, h->kw, h->stream);
+    SHK_CUDA(cudaMemsetAsync(d_flags(h), 0, 4, h->stream));
+    h->st.gpu_launches += launch_index_nodes(h->kw, h->slots.p, icap, h->node_lo.as<uint64_t>(), h->node_hi.as<uint64_t>(), nn,
+                                             d_flags(h), h->stream);
+    SHK_CUDA(cudaGetLastError());
+    SHK_CUDA(cudaEventRecord(h->ev[5], h->stream));
+    SHK_TRY(read_scalars(h));
+    if (!((uint32_t *)(h->h_pinned + 8 + SHK_HISTO_BINS))[0]) break;
+    if (attempt >= 3) { set_error("node index overflow"); return SHK_ERR_TABLE_FULL; }
+    icap *= 2;
+  }
   h->filtered = true; h->graphed = false;
   h->hu.valid = false;
   return SHK_OK;
 }
+
+static shk_status histogram_impl(shk_asm *h) { return filter_impl(h, 0, true); }
 
 // ---- K3..K6: graph ---------------------------------------------------------
 static shk_status graph_impl(shk_asm *h) {
@@ -276,7 +342,9 @@ static shk_status graph_impl(shk_asm *h) {
   SHK_TRY(h->recs.ensure((size_t)N * unitig_rec_bytes()));
   SHK_TRY(h->ucirc.ensure(N)); SHK_TRY(h->cov_sum.ensure((size_t)N * 8));
   SHK_TRY(h->useq.ensure((size_t)N * (size_t)k));
-  uint32_t link_cap = (uint32_t)std::min<uint64_t>(4ull * N + 64, 0x7FFFFFFFull);
+  // links: usually a few per branching unitig; sized small, re-run once with the
+  // exact count if the first pass overflows (the kernel counts past the cap)
+  uint32_t link_cap = (uint32_t)std::min<uint64_t>((uint64_t)N / 2 + 4096, 0x7FFFFFFFull);
   SHK_TRY(h->link_from.ensure((size_t)link_cap * 4)); SHK_TRY(h->link_to.ensure((size_t)link_cap * 4));
   SHK_TRY(h->gscal.ensure(64));
   SHK_CUDA(cudaMemsetAsync(h->gscal.p, 0, 64, h->stream));
@@ -332,7 +400,18 @@ static shk_status graph_impl(shk_asm *h) {
   SHK_CUDA(cudaEventRecord(h->ev[7], h->stream));
   SHK_CUDA(cudaMemcpyAsync(hs, h->gscal.p, 64, cudaMemcpyDeviceToHost, h->stream));
   SHK_CUDA(cudaStreamSynchronize(h->stream));
-  if (hs[3] > link_cap) { set_error("unitig link buffer overflow (%u > %u)", hs[3], link_cap); return SHK_ERR_OOM; }
+  if (hs[3] > link_cap) {
+    link_cap = hs[3];
+    SHK_TRY(h->link_from.ensure((size_t)link_cap * 4)); SHK_TRY(h->link_to.ensure((size_t)link_cap * 4));
+    g.link_from = h->link_from.as<uint32_t>(); g.link_to = h->link_to.as<uint32_t>(); g.link_cap = link_cap;
+    SHK_CUDA(cudaMemsetAsync(g.scal + 3, 0, 4, h->stream));
+    L += launch_unitig_links_out(h->kw, h->slots.p, h->cap, k, g, nu, h->stream);
+    SHK_CUDA(cudaGetLastError());
+    SHK_CUDA(cudaEventRecord(h->ev[7], h->stream));
+    SHK_CUDA(cudaMemcpyAsync(hs, h->gscal.p, 64, cudaMemcpyDeviceToHost, h->stream));
+    SHK_CUDA(cudaStreamSynchronize(h->stream));
+    if (hs[3] > link_cap) { set_error("unitig link buffer overflow (%u > %u)", hs[3], link_cap); return SHK_ERR_OOM; }
+  }
   h->st.n_unitigs = nu; h->st.unitig_bases = seq_len; h->st.n_links = hs[3];
   h->graphed = true; h->hu.valid = false;
   return SHK_OK;
@@ -340,7 +419,7 @@ static shk_status graph_impl(shk_asm *h) {
 
 static void collect_timing(shk_asm *h) {
   auto el = [&](int a, int b) { float ms = 0; if (cudaEventElapsedTime(&ms, h->ev[a], h->ev[b]) != cudaSuccess) { cudaGetLastError(); ms = 0; } return ms; };
-  h->st.ms_pack = el(0, 1); h->st.ms_count = el(2, 3); h->st.ms_extract = el(8, 9); h->st.ms_filter = el(4, 5); h->st.ms_graph = el(6, 7);
+  h->st.ms_pack = el(0, 1); h->st.ms_count = el(2, 3); h->st.ms_extract = el(8, 9); h->st.ms_count_kernel = el(10, 11); h->st.ms_filter = el(4, 5); h->st.ms_graph = el(6, 7);
 }
 
 }  // namespace shk
@@ -408,9 +487,10 @@ void shk_asm_free(shk_asm *h) {
     DevBuf *bufs[] = {&h->bases, &h->mask, &h->ascii_seq, &h->ascii_qual, &h->slots, &h->dscal, &h->node_lo, &h->node_hi,
                       &h->node_count, &h->node_raw, &h->node_edges, &h->uniq, &h->succ, &h->tail_of, &h->len_of,
                       &h->unitig_of_head, &h->elem_unitig, &h->pd, &h->cq, &h->circ, &h->recs, &h->ucirc, &h->cov_sum,
-                      &h->useq, &h->link_from, &h->link_to, &h->gscal};
+                      &h->useq, &h->link_from, &h->link_to, &h->gscal, &h->skrecs, &h->bfill, &h->groups, &h->ovf};
     for (auto b : bufs) b->release();
     if (h->h_pinned) cudaFreeHost(h->h_pinned);
+    h->hfill.release();
     for (auto &e : h->ev) if (e) cudaEventDestroy(e);
     if (h->own_stream) cudaStreamDestroy(h->own_stream);
   }
@@ -456,7 +536,7 @@ shk_status shk_get_stats(shk_asm *h, shk_stats *out) {
 }
 shk_status shk_get_histogram(shk_asm *h, uint64_t *histo) {
   if (!h || !histo) { set_error("null argument"); return SHK_ERR_BAD_ARG; }
-  if (h->counted && !h->filtered && h->table_live) SHK_TRY(histogram_impl(h));
+  if (h->counted && !h->filtered) SHK_TRY(histogram_impl(h));
   memcpy(histo, h->histo, sizeof h->histo);
   return SHK_OK;
 }
@@ -482,39 +562,6 @@ shk_status shk_export_kmers(shk_asm *h, uint64_t *key_lo, uint64_t *key_hi, uint
     SHK_CUDA(cudaMemcpyAsync(edges, h->node_edges.p, N, cudaMemcpyDeviceToHost, h->stream));
   }
   SHK_CUDA(cudaStreamSynchronize(h->stream));
-  return SHK_OK;
-}
-
-shk_status shk_export_table(shk_asm *h, uint64_t *key_lo, uint64_t *key_hi, uint32_t *counts, uint8_t *raw_edges,
-                            size_t cap, size_t *n) {
-  SHK_TRY(require_device(h));
-  if (!h->counted || !h->table_live) { set_error("export_table needs a live table (after count, before filter)"); return SHK_ERR_STATE; }
-  size_t nd = h->st.n_distinct;
-  if (n) *n = nd;
-  if (cap < nd) { set_error("export buffer too small"); return SHK_ERR_BAD_ARG; }
-  // diagnostic path: slot array to host in slices, compaction on the host
-  const size_t sb = slot_bytes(h->kw), slice = (size_t)1 << 22;
-  std::vector<uint8_t> buf(slice * sb);
-  size_t o = 0;
-  for (uint64_t s0 = 0; s0 < h->cap; s0 += slice) {
-    size_t cnt = (size_t)std::min<uint64_t>(slice, h->cap - s0);
-    SHK_CUDA(cudaMemcpyAsync(buf.data(), (const uint8_t *)h->slots.p + s0 * sb, cnt * sb, cudaMemcpyDeviceToHost, h->stream));
-    SHK_CUDA(cudaStreamSynchronize(h->stream));
-    for (size_t i = 0; i < cnt; ++i) {
-      const uint64_t *w = (const uint64_t *)(buf.data() + i * sb);
-      uint64_t lo = w[0], hi = h->kw == 2 ? w[1] : 0;
-      bool empty = h->kw == 2 ? (hi == ~0ull) : (lo == ~0ull);
-      if (empty) continue;
-      const uint32_t *cv = (const uint32_t *)(w + (h->kw == 2 ? 2 : 1));
-      if (o >= cap) { set_error("table holds more live slots than n_distinct"); return SHK_ERR_STATE; }
-      if (key_lo) key_lo[o] = lo;
-      if (key_hi) key_hi[o] = hi;
-      if (counts) counts[o] = cv[0];
-      if (raw_edges) raw_edges[o] = (uint8_t)cv[1];
-      ++o;
-    }
-  }
-  if (n) *n = o;
   return SHK_OK;
 }
 
@@ -644,9 +691,12 @@ shk_status shk_asm_get_assembly(shk_asm *h, const char **json, size_t *len) {
 // Batch boundary of the streaming / file forms: counts the reads parsed so far.
 shk_status shk_internal_flush_batch(shk_asm *h, bool final_batch) {
   if (h->hseq.empty() && !(final_batch && !h->any_batch_counted)) return SHK_OK;
-  SHK_TRY(load_reads_host(h, h->hseq.data(), h->hqual.data(), h->hseq.size(), 0));
-  SHK_TRY(count_impl(h, h->any_batch_counted ? 0 : 1));
+  // chunked mode: batches are packed and appended to the resident stream (0.375
+  // B/base of HBM); counting runs once over all of it at the end — the result is
+  // identical to bulk (S8) and no batch is ever re-read from the host.
+  SHK_TRY(load_reads_host(h, h->hseq.data(), h->hqual.data(), h->hseq.size(), h->any_batch_counted ? 1 : 0));
   h->any_batch_counted = true;
+  if (final_batch) SHK_TRY(count_impl(h, 1));
   h->hseq.clear(); h->hqual.clear(); h->batch_reads = 0;
   return SHK_OK;
 }

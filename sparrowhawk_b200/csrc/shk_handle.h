@@ -31,6 +31,14 @@ struct DevBuf {
   template <class T> T *as() const { return (T *)p; }
 };
 
+// grow-only pinned host buffer
+struct PinBuf {
+  void *p = nullptr;
+  size_t cap = 0;
+  shk_status ensure_host(size_t bytes);
+  void release();
+};
+
 struct HostUnitigs {
   std::vector<char> seq;              // concatenated, as emitted by the device
   std::vector<uint64_t> off;          // n+1
@@ -46,7 +54,7 @@ struct shk_asm {
   shk_params p;
   int kw = 1, dev = 0;
   cudaStream_t own_stream = nullptr, stream = nullptr;
-  cudaEvent_t ev[10] = {};
+  cudaEvent_t ev[12] = {};
   shk_progress_fn cb = nullptr;
   void *cb_user = nullptr;
 
@@ -54,10 +62,16 @@ struct shk_asm {
   shk::DevBuf bases, mask, ascii_seq, ascii_qual;
   uint64_t nwords = 0;          // words in use (excluding pads)
   uint64_t n_positions = 0, n_bases = 0, counted_positions = 0;
-  // ---- table ----
+  // ---- K1a output: super-k-mer records in P fine-bucket regions of rcap records ----
+  shk::DevBuf skrecs, bfill /* u32 fill[P] | u32 kcount[P] */, groups, ovf;
+  shk::PinBuf hfill;
+  uint32_t P = 0, rcap = 0;
+  uint64_t n_records = 0, ovf_cap = 0;
+  double ratio_est = 0;         // distinct / instances, measured by a pilot or the previous run
+  // ---- node index (key -> node id) for the graph stage ----
   shk::DevBuf slots;
   uint64_t cap = 0;
-  bool table_live = false;      // holds counts (before K2 rewrote count words)
+  bool table_live = false;
   // ---- device scalars: counters[0]=n_bases [1]=n_instances [2]=n_distinct ; histo[500]
   shk::DevBuf dscal;            // u64 counters[8] | u64 histo[500] | u32 flags[8]
   uint64_t *h_pinned = nullptr; // pinned mirror of dscal

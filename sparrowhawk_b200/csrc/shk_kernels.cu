@@ -2,8 +2,12 @@
 // (SURVEY.md §2.2 K0..K6).  Integer / byte work bound by HBM and L2 atomics; no
 // tensor cores (nothing here is a dense contraction).  Launch wrappers at the
 // bottom are the only symbols other translation units use (shk_kernels.h).
+#include <type_traits>
+
 #include "shk_device.cuh"
 #include "shk_kernels.h"
+#include "shk_table.cuh"
+#include "shk_count_smem.cuh"
 
 namespace shk {
 
@@ -66,63 +70,6 @@ k_pack_reads(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual, 
 // inserts into the open-addressing table: 128-bit slot load, CAS claim on the
 // key, RED.ADD on the count, RED.OR on the edge byte only when it adds bits.
 // =====================================================================
-template <int KW> struct Table {
-  typename SlotOf<KW>::type *slots;
-  u64 cap;
-  u32 max_probe;
-};
-
-__device__ __forceinline__ bool table_insert(const Table<1> &t, u64 key, u32 e, u32 add, u32 *overflow) {
-  u64 i = slot_of(hash_key(key), t.cap);
-  for (u32 probe = 0; probe < t.max_probe; ++probe) {
-    Slot1 *sp = t.slots + i;
-    uint4 v = __ldcg(reinterpret_cast<const uint4 *>(sp));
-    u64 cur = ((u64)v.y << 32) | v.x;
-    u32 seen = v.w;
-    bool claimed = false;
-    if (cur == SHK_EMPTY64) {
-      cur = atomicCAS(&sp->key, SHK_EMPTY64, key);
-      if (cur == SHK_EMPTY64) { cur = key; seen = 0; claimed = true; }
-    }
-    if (cur == key) {
-      atomicAdd(&sp->count, add);                      // RED.ADD (result unused)
-      if ((seen & e) != e) atomicOr(&sp->edges, e);    // RED.OR only when new bits
-      return claimed;
-    }
-    if (++i == t.cap) i = 0;
-  }
-  atomicExch(overflow, 1u);
-  return false;
-}
-
-__device__ __forceinline__ bool table_insert(const Table<2> &t, u128 key, u32 e, u32 add, u32 *overflow) {
-  u64 i = slot_of(hash_key(key), t.cap);
-  const u64 klo = (u64)key, khi = (u64)(key >> 64);
-  for (u32 probe = 0; probe < t.max_probe; ++probe) {
-    Slot2 *sp = t.slots + i;
-    const uint4 *p4 = reinterpret_cast<const uint4 *>(sp);
-    uint4 v = __ldcg(p4);
-    uint2 cv = __ldcg(reinterpret_cast<const uint2 *>(p4 + 1));
-    u64 lo = ((u64)v.y << 32) | v.x, hi = ((u64)v.w << 32) | v.z;
-    u32 seen = cv.y;
-    bool claimed = false;
-    if (hi == SHK_EMPTY64) {
-      U128Pair expect{SHK_EMPTY64, SHK_EMPTY64}, want{klo, khi};
-      U128Pair old = atomicCAS(reinterpret_cast<U128Pair *>(sp), expect, want);
-      lo = old.lo; hi = old.hi;
-      if (hi == SHK_EMPTY64) { lo = klo; hi = khi; seen = 0; claimed = true; }
-    }
-    if (lo == klo && hi == khi) {
-      atomicAdd(&sp->count, add);
-      if ((seen & e) != e) atomicOr(&sp->edges, e);
-      return claimed;
-    }
-    if (++i == t.cap) i = 0;
-  }
-  atomicExch(overflow, 1u);
-  return false;
-}
-
 template <int KW>
 __global__ void __launch_bounds__(256)
 k_extract_count(const u64 *__restrict__ bases, const u32 *__restrict__ mask, u64 nwords, int k,
@@ -761,6 +708,57 @@ int launch_unitig_links_out(int kw, void *slots, uint64_t cap, int k, const Grap
                                              n_unitigs, g.tail_of, g.unitig_of_head, (const u64 *)g.node_lo,
                                              (const u64 *)g.node_hi, g.node_edges, g.ucirc, g.link_from, g.link_to,
                                              g.link_cap, g.scal + 3);
+  return 1;
+}
+
+// ---- two-pass counting (shk_partition.cuh / shk_count_smem.cuh) ----------------
+size_t record_bytes(int kw) { return kw == 1 ? 16 : 32; }
+int records_max_run(int kw, int k) { return rec_max_run(kw, k); }
+int count_table_slots(int kw) { return kw == 1 ? CbCfg<1>::NS : CbCfg<2>::NS; }
+int count_max_group() { return SHK_CB_MAXC; }
+
+int launch_partition(int kw, const uint64_t *bases, const uint32_t *mask, uint64_t nwords, int k, uint32_t P,
+                     uint32_t rcap, void *recs, uint32_t *fill, uint32_t *kcount, uint64_t *counters, cudaStream_t st) {
+  if (!nwords) return 0;
+  unsigned g = blocks_for(nwords, SHK_PT_WORDS);
+  if (kw == 1)
+    k_minimizer_partition<1><<<g, SHK_PT_THREADS, 0, st>>>((const u64 *)bases, mask, nwords, k, P, rcap, (uint4 *)recs, fill, kcount, (u64 *)counters);
+  else
+    k_minimizer_partition<2><<<g, SHK_PT_THREADS, 0, st>>>((const u64 *)bases, mask, nwords, k, P, rcap, (Rec32 *)recs, fill, kcount, (u64 *)counters);
+  return 1;
+}
+
+int launch_count_buckets(int kw, const void *recs, const uint32_t *fill, uint32_t rcap, const uint32_t *group_start,
+                         uint32_t g_begin, uint32_t g_end, uint32_t *next_group, int k, int min_count, void *ovf_slots,
+                         uint64_t ovf_cap, uint32_t *ovf_flag, uint64_t *histo, uint64_t *node_lo, uint64_t *node_hi,
+                         uint16_t *node_count, uint8_t *node_raw, uint32_t node_cap, uint32_t *n_nodes,
+                         uint64_t *counters, cudaStream_t st) {
+  if (g_end <= g_begin) return 0;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaFuncSetAttribute(k_count_buckets<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cb_smem_bytes<1>());
+    cudaFuncSetAttribute(k_count_buckets<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cb_smem_bytes<2>());
+    attr_set = true;
+  }
+  unsigned grid = (unsigned)sm_count();
+  if (grid > g_end - g_begin) grid = g_end - g_begin;
+  u32 mp = (u32)(ovf_cap < 4096 ? ovf_cap : 4096);
+  CountOut out{(u64 *)histo, (u64 *)node_lo, (u64 *)node_hi, node_count, node_raw, node_cap, n_nodes, (u64 *)counters};
+  if (kw == 1)
+    k_count_buckets<1><<<grid, SHK_CB_THREADS, cb_smem_bytes<1>(), st>>>((const uint4 *)recs, fill, rcap, group_start, g_begin, g_end,
+                                                                      next_group, k, min_count, Table<1>{(Slot1 *)ovf_slots, ovf_cap, mp}, ovf_flag, out);
+  else
+    k_count_buckets<2><<<grid, SHK_CB_THREADS, cb_smem_bytes<2>(), st>>>((const Rec32 *)recs, fill, rcap, group_start, g_begin, g_end,
+                                                                      next_group, k, min_count, Table<2>{(Slot2 *)ovf_slots, ovf_cap, mp}, ovf_flag, out);
+  return 1;
+}
+
+int launch_index_nodes(int kw, void *slots, uint64_t cap, const uint64_t *node_lo, const uint64_t *node_hi, uint32_t n_nodes,
+                       uint32_t *overflow, cudaStream_t st) {
+  if (!n_nodes) return 0;
+  u32 mp = (u32)(cap < 4096 ? cap : 4096);
+  if (kw == 1) k_index_nodes<1><<<blocks_for(n_nodes, 256), 256, 0, st>>>(Table<1>{(Slot1 *)slots, cap, mp}, (const u64 *)node_lo, (const u64 *)node_hi, n_nodes, overflow);
+  else k_index_nodes<2><<<blocks_for(n_nodes, 256), 256, 0, st>>>(Table<2>{(Slot2 *)slots, cap, mp}, (const u64 *)node_lo, (const u64 *)node_hi, n_nodes, overflow);
   return 1;
 }
 
