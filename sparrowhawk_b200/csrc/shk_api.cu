@@ -339,6 +339,7 @@ static shk_status graph_impl(shk_asm *h) {
   SHK_TRY(h->tail_of.ensure(ne * 4)); SHK_TRY(h->len_of.ensure(ne * 4));
   SHK_TRY(h->unitig_of_head.ensure(ne * 4)); SHK_TRY(h->elem_unitig.ensure(ne * 4));
   SHK_TRY(h->pd.ensure(ne * 8));
+  SHK_TRY(h->splitters.ensure(ne * 4)); SHK_TRY(h->sum_of.ensure(ne * 8));
   SHK_TRY(h->recs.ensure((size_t)N * unitig_rec_bytes()));
   SHK_TRY(h->ucirc.ensure(N)); SHK_TRY(h->cov_sum.ensure((size_t)N * 8));
   SHK_TRY(h->useq.ensure((size_t)N * (size_t)k));
@@ -349,7 +350,6 @@ static shk_status graph_impl(shk_asm *h) {
   SHK_TRY(h->gscal.ensure(64));
   SHK_CUDA(cudaMemsetAsync(h->gscal.p, 0, 64, h->stream));
   SHK_CUDA(cudaMemsetAsync(h->tail_of.p, 0xFF, ne * 4, h->stream));
-  SHK_CUDA(cudaMemsetAsync(h->cov_sum.p, 0, (size_t)N * 8, h->stream));
 
   GraphBuffers g{};
   g.node_lo = h->node_lo.as<uint64_t>(); g.node_hi = h->kw == 2 ? h->node_hi.as<uint64_t>() : nullptr;
@@ -362,33 +362,39 @@ static shk_status graph_impl(shk_asm *h) {
   g.seq = h->useq.as<char>(); g.link_from = h->link_from.as<uint32_t>(); g.link_to = h->link_to.as<uint32_t>();
   g.link_cap = link_cap; g.scal = h->gscal.as<uint32_t>(); g.seq_cursor = (uint64_t *)(h->gscal.as<uint32_t>() + 8);
   g.cq = nullptr; g.circ = nullptr;
+  g.splitters = h->splitters.as<uint32_t>(); g.sum_of = h->sum_of.as<uint64_t>();
 
   uint64_t &L = h->st.gpu_launches;
-  L += launch_build_edges(h->kw, h->slots.p, h->cap, k, g, h->stream);
-  L += launch_links_and_rank_init(g, h->stream);
-  // each launch multiplies the resolved distance by >= 5 (4 in-place jumps)
-  int rounds = 2;
-  for (double d = 1; d < (double)ne; d *= 5.0) ++rounds;
-  for (int r = 0; r < rounds; ++r) L += launch_rank_jump(g, h->stream);
-  // cycles: anything not hanging off a true head now
-  SHK_TRY(h->cq.ensure(ne * 8));
-  g.cq = h->cq.as<uint64_t>();
-  L += launch_cycle_init(g, h->stream);
-  SHK_CUDA(cudaGetLastError());
   uint32_t hs[16];
-  SHK_CUDA(cudaMemcpyAsync(hs, h->gscal.p, 64, cudaMemcpyDeviceToHost, h->stream));
-  SHK_CUDA(cudaStreamSynchronize(h->stream));
-  bool have_circ = hs[1] != 0;
-  if (have_circ) {
+  L += launch_build_edges(h->kw, h->slots.p, h->cap, k, g, h->stream);
+  L += launch_unitig_links(g, h->stream);
+  // K5: rank every directed list; a second pass only when unbranched cycles exist
+  bool have_circ = false;
+  for (int pass = 0; pass < 2; ++pass) {
+    const uint8_t *circ = pass ? g.circ : nullptr;
+    SHK_CUDA(cudaMemsetAsync(h->pd.p, 0xFF, ne * 8, h->stream));
+    SHK_CUDA(cudaMemsetAsync(g.scal + 4, 0, 4, h->stream));
+    SHK_CUDA(cudaMemsetAsync(g.scal + 1, 0, 4, h->stream));
+    L += launch_rank_mark(g, circ, h->stream);
+    SHK_CUDA(cudaGetLastError());
+    SHK_CUDA(cudaMemcpyAsync(hs, h->gscal.p, 64, cudaMemcpyDeviceToHost, h->stream));
+    SHK_CUDA(cudaStreamSynchronize(h->stream));
+    const uint32_t ns = hs[4];
+    SHK_TRY(h->rank_work.ensure((size_t)ns * rank_splitter_bytes() + 64));
+    L += launch_rank_lists(g, circ, ns, h->rank_work.p, h->stream);
+    SHK_CUDA(cudaGetLastError());
+    SHK_CUDA(cudaMemcpyAsync(hs, h->gscal.p, 64, cudaMemcpyDeviceToHost, h->stream));
+    SHK_CUDA(cudaStreamSynchronize(h->stream));
+    const uint32_t n_cyclic = hs[1];
+    if (!n_cyclic) break;
+    if (pass == 1) { set_error("list ranking left %u elements unranked", n_cyclic); return SHK_ERR_STATE; }
+    SHK_TRY(h->cq.ensure(2 * ne * 8));
     SHK_TRY(h->circ.ensure(ne));
-    g.circ = h->circ.as<uint8_t>();
-    int cr = 1;
-    for (uint64_t d = 1; d < (uint64_t)hs[1]; d *= 2) ++cr;
-    for (int r = 0; r < cr; ++r) L += launch_cycle_jump(g, h->stream);
-    L += launch_cycle_cut(g, h->stream);
-    for (int r = 0; r < rounds; ++r) L += launch_rank_jump(g, h->stream);
+    g.cq = h->cq.as<uint64_t>(); g.circ = h->circ.as<uint8_t>();
+    L += launch_cycle_cut(g, n_cyclic, h->stream);
+    have_circ = true;
   }
-  L += launch_unitig_tails_heads(g, k, have_circ, h->stream);
+  L += launch_unitig_heads(g, k, have_circ, h->stream);
   L += launch_unitig_emit(h->kw, g, k, h->stream);
   SHK_CUDA(cudaGetLastError());
   SHK_CUDA(cudaMemcpyAsync(hs, h->gscal.p, 64, cudaMemcpyDeviceToHost, h->stream));
@@ -487,7 +493,7 @@ void shk_asm_free(shk_asm *h) {
     DevBuf *bufs[] = {&h->bases, &h->mask, &h->ascii_seq, &h->ascii_qual, &h->slots, &h->dscal, &h->node_lo, &h->node_hi,
                       &h->node_count, &h->node_raw, &h->node_edges, &h->uniq, &h->succ, &h->tail_of, &h->len_of,
                       &h->unitig_of_head, &h->elem_unitig, &h->pd, &h->cq, &h->circ, &h->recs, &h->ucirc, &h->cov_sum,
-                      &h->useq, &h->link_from, &h->link_to, &h->gscal, &h->skrecs, &h->bfill, &h->groups, &h->ovf};
+                      &h->useq, &h->link_from, &h->link_to, &h->gscal, &h->splitters, &h->sum_of, &h->rank_work, &h->skrecs, &h->bfill, &h->groups, &h->ovf};
     for (auto b : bufs) b->release();
     if (h->h_pinned) cudaFreeHost(h->h_pinned);
     h->hfill.release();

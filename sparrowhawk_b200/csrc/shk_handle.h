@@ -78,7 +78,7 @@ struct shk_asm {
   // ---- nodes + graph ----
   shk::DevBuf node_lo, node_hi, node_count, node_raw, node_edges;
   shk::DevBuf uniq, succ, tail_of, len_of, unitig_of_head, elem_unitig, pd, cq, circ;
-  shk::DevBuf recs, ucirc, cov_sum, useq, link_from, link_to, gscal;
+  shk::DevBuf recs, ucirc, cov_sum, useq, link_from, link_to, gscal, splitters, sum_of, rank_work;
   uint32_t node_cap = 0;
 
   // ---- results / state ----

@@ -8,6 +8,7 @@
 #include "shk_kernels.h"
 #include "shk_table.cuh"
 #include "shk_count_smem.cuh"
+#include "shk_rank.cuh"
 
 namespace shk {
 
@@ -323,46 +324,14 @@ k_unitig_links(const uint8_t *__restrict__ node_edges, const u32 *__restrict__ u
   succ[e] = out;
 }
 
-__global__ void __launch_bounds__(256)
-k_rank_init(const u32 *__restrict__ succ, u32 n_elems, u64 *__restrict__ pd) {
-  u32 e = blockIdx.x * blockDim.x + threadIdx.x;
-  if (e >= n_elems) return;
-  u32 sr = succ[e ^ 1u];                       // pred(e) = rev(succ(rev e))
-  pd[e] = sr == SHK_NONE ? ((u64)e << 32) : (((u64)(sr ^ 1u) << 32) | 1ull);
-}
-
 // =====================================================================
-// K5 list_rank: Wyllie pointer jumping, in place.  pd[e] = (ancestor, distance)
-// is read as one 64-bit word, so a racing reader always sees a consistent pair
-// and the jump stays exact.  Heads are fixed points (ptr == self, dist 0).
+// K5 list_rank lives in shk_rank.cuh (sparse ruling set + Wyllie on splitters).
+// Cycles (S14): elements left with pd == ~0 lie on unbranched cycles.  Doubling
+// on (pred pointer, argmin element by node key) finds the minimum canonical
+// k-mer of each directed cycle; the cycle is cut in front of that element
+// (circ = 2, a forced head) and the ranking is run again.  Of the two mirror
+// cycles the one that holds the minimum node in dir 0 is kept.
 // =====================================================================
-__global__ void __launch_bounds__(256)
-k_rank_jump(u64 *__restrict__ pd, u32 n_elems, u32 *__restrict__ changed) {
-  u32 e = blockIdx.x * blockDim.x + threadIdx.x;
-  if (e >= n_elems) return;
-  u64 v = pd[e];
-  u32 p = (u32)(v >> 32);
-  if (p == e) return;                          // head (dist 0) or closed cycle (dist > 0)
-  bool ch = false;
-  // a few jumps per launch: chains are long, launches are not free
-  for (int it = 0; it < 4; ++it) {
-    u64 vp = __ldcg(pd + p);
-    u32 pp = (u32)(vp >> 32);
-    if (pp == p) break;                        // p is a head (or a closed cycle): stop
-    v = ((u64)pp << 32) | (u32)((u32)v + (u32)vp);
-    p = pp; ch = true;
-    if (p == e) break;                         // cycle closed on itself (dist > 0 marks it)
-  }
-  if (ch) { pd[e] = v; *changed = 1u; }
-}
-
-// ---- cycles (S14): elements whose ancestor is not a true head (ptr==self,
-// dist 0) after ceil(log2 n) rounds lie on unbranched cycles.  Doubling on
-// (pred pointer, argmin element by node key) finds the minimum canonical k-mer
-// of each directed cycle; the cycle is cut there and re-ranked.  Of the two
-// mirror cycles the one that holds the minimum node in dir 0 is kept.
-__device__ __forceinline__ bool is_true_head(const u64 *pd, u32 p) { return __ldcg(pd + p) == ((u64)p << 32); }
-
 __device__ __forceinline__ bool elem_key_less(const u64 *lo, const u64 *hi, u32 a, u32 b) {
   u32 na = a >> 1, nb = b >> 1;
   if (hi) { u64 ha = hi[na], hb = hi[nb]; if (ha != hb) return ha < hb; }
@@ -371,46 +340,41 @@ __device__ __forceinline__ bool elem_key_less(const u64 *lo, const u64 *hi, u32 
 
 __global__ void __launch_bounds__(256)
 k_cycle_init(const u64 *__restrict__ pd, const u32 *__restrict__ succ, u32 n_elems,
-             u64 *__restrict__ cq /* (pred ptr << 32 | argmin elem), or ~0 when acyclic */,
-             u32 *__restrict__ n_cyclic) {
+             u64 *__restrict__ cq /* (pred ptr << 32 | argmin elem), or ~0 when acyclic */) {
   u32 e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= n_elems) return;
-  u32 p = (u32)(pd[e] >> 32);
-  if (is_true_head(pd, p)) { cq[e] = ~0ull; return; }
+  if (pd[e] != ~0ull) { cq[e] = ~0ull; return; }
   u32 pred = succ[e ^ 1u] ^ 1u;                // exists on a cycle
   cq[e] = ((u64)pred << 32) | e;
-  atomicAdd(n_cyclic, 1u);
 }
 
 __global__ void __launch_bounds__(256)
-k_cycle_jump(u64 *__restrict__ cq, u32 n_elems, const u64 *__restrict__ node_lo,
+k_cycle_jump(const u64 *__restrict__ cq, u64 *__restrict__ cq_out, u32 n_elems, const u64 *__restrict__ node_lo,
              const u64 *__restrict__ node_hi) {
   u32 e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= n_elems) return;
   u64 v = cq[e];
-  if (v == ~0ull) return;
-  u32 q = (u32)(v >> 32), m = (u32)v;
-  u64 vq = __ldcg(cq + q);
-  u32 qq = (u32)(vq >> 32), mq = (u32)vq;
-  if (elem_key_less(node_lo, node_hi, mq, m)) m = mq;
-  cq[e] = ((u64)qq << 32) | m;
+  if (v != ~0ull) {
+    u32 q = (u32)(v >> 32), m = (u32)v;
+    u64 vq = cq[q];
+    u32 qq = (u32)(vq >> 32), mq = (u32)vq;
+    if (elem_key_less(node_lo, node_hi, mq, m)) m = mq;
+    v = ((u64)qq << 32) | m;
+  }
+  cq_out[e] = v;
 }
 
 __global__ void __launch_bounds__(256)
-k_cycle_cut(const u64 *__restrict__ cq, const u32 *__restrict__ succ, u32 n_elems,
-            u64 *__restrict__ pd, uint8_t *__restrict__ circ /* per element */) {
+k_cycle_cut(const u64 *__restrict__ cq, u32 n_elems, uint8_t *__restrict__ circ /* per element */) {
   u32 e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= n_elems) return;
   u64 v = cq[e];
-  if (v == ~0ull) { circ[e] = 0; return; }
-  u32 m = (u32)v;
-  circ[e] = 1;
-  pd[e] = (e == m) ? ((u64)e << 32) : (((u64)(succ[e ^ 1u] ^ 1u) << 32) | 1ull);
+  circ[e] = v == ~0ull ? 0 : (e == (u32)v ? 2 : 1);
 }
 
 // =====================================================================
 // K6 emit_unitigs.
-//  tails : the last element of every directed list tells its head the length.
+//  tails : k_rank_finish told every head its tail, length and count sum.
 //  heads : one list of each mirror pair is kept (smaller end-node key first;
 //          a single node in dir 0; a cycle through its minimum node in dir 0)
 //          and gets a unitig id + an output range from two cursors.
@@ -420,23 +384,11 @@ k_cycle_cut(const u64 *__restrict__ cq, const u32 *__restrict__ succ, u32 n_elem
 struct UnitigRec { u32 head, len; u64 off; };
 
 __global__ void __launch_bounds__(256)
-k_unitig_tails(const u64 *__restrict__ pd, const u32 *__restrict__ succ, const uint8_t *__restrict__ circ,
-               u32 n_elems, u32 *__restrict__ tail_of /* by head elem */, u32 *__restrict__ len_of) {
-  u32 e = blockIdx.x * blockDim.x + threadIdx.x;
-  if (e >= n_elems) return;
-  u64 v = pd[e];
-  u32 h = (u32)(v >> 32), d = (u32)v;
-  u32 s = succ[e];
-  bool tail = (s == SHK_NONE) || (circ && circ[e] && s == h);
-  if (tail) { tail_of[h] = e; len_of[h] = d + 1; }
-}
-
-__global__ void __launch_bounds__(256)
 k_unitig_heads(const u64 *__restrict__ pd, const uint8_t *__restrict__ circ, const u32 *__restrict__ tail_of,
-               const u32 *__restrict__ len_of, const u64 *__restrict__ node_lo,
+               const u32 *__restrict__ len_of, const u64 *__restrict__ sum_of, const u64 *__restrict__ node_lo,
                const u64 *__restrict__ node_hi, u32 n_elems, int k, u32 *__restrict__ unitig_of_head,
-               UnitigRec *__restrict__ recs, uint8_t *__restrict__ ucirc, u32 *__restrict__ n_unitigs,
-               u64 *__restrict__ seq_cursor) {
+               UnitigRec *__restrict__ recs, uint8_t *__restrict__ ucirc, u64 *__restrict__ cov_sum,
+               u32 *__restrict__ n_unitigs, u64 *__restrict__ seq_cursor) {
   u32 e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= n_elems) return;
   unitig_of_head[e] = SHK_NONE;
@@ -454,14 +406,15 @@ k_unitig_heads(const u64 *__restrict__ pd, const uint8_t *__restrict__ circ, con
   unitig_of_head[e] = uid;
   recs[uid] = UnitigRec{e, len, off};
   ucirc[uid] = cyc ? 1 : 0;
+  cov_sum[uid] = sum_of[e];                    // accumulated by the ranking walk
 }
 
 template <int KW>
 __global__ void __launch_bounds__(256)
 k_unitig_emit(const u64 *__restrict__ pd, const u32 *__restrict__ unitig_of_head,
               const UnitigRec *__restrict__ recs, const u64 *__restrict__ node_lo,
-              const u64 *__restrict__ node_hi, const uint16_t *__restrict__ node_count, u32 n_elems, int k,
-              char *__restrict__ seq, u64 *__restrict__ cov_sum, u32 *__restrict__ elem_unitig) {
+              const u64 *__restrict__ node_hi, u32 n_elems, int k,
+              char *__restrict__ seq, u32 *__restrict__ elem_unitig) {
   typedef typename KeyOf<KW>::type K;
   u32 e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= n_elems) return;
@@ -480,7 +433,6 @@ k_unitig_emit(const u64 *__restrict__ pd, const u32 *__restrict__ unitig_of_head
   } else {
     seq[off + k - 1 + r] = SHK_CODE2ASCII_DEV((u32)X & 3u);
   }
-  atomicAdd(cov_sum + uid, (u64)node_count[n]);
 }
 
 // Unitig-level links: for every kept unitig and both of its exits (tail
@@ -640,57 +592,78 @@ int launch_build_edges(int kw, void *slots, uint64_t cap, int k, const GraphBuff
   return 1;
 }
 
-int launch_links_and_rank_init(const GraphBuffers &g, cudaStream_t st) {
+int launch_unitig_links(const GraphBuffers &g, cudaStream_t st) {
   u32 ne = 2 * g.n_nodes;
   if (!ne) return 0;
   k_unitig_links<<<blocks_for(ne, 256), 256, 0, st>>>(g.node_edges, g.uniq, ne, g.succ);
-  k_rank_init<<<blocks_for(ne, 256), 256, 0, st>>>(g.succ, ne, (u64 *)g.pd);
-  return 2;
+  return 1;
 }
-int launch_rank_jump(const GraphBuffers &g, cudaStream_t st) {
+int launch_rank_mark(const GraphBuffers &g, const uint8_t *circ, cudaStream_t st) {
   u32 ne = 2 * g.n_nodes;
   if (!ne) return 0;
-  k_rank_jump<<<blocks_for(ne, 256), 256, 0, st>>>((u64 *)g.pd, ne, g.scal + 0);
+  k_rank_mark<<<blocks_for(ne, 256), 256, 0, st>>>(g.succ, circ, ne, g.splitters, g.scal + 4);
   return 1;
 }
-int launch_cycle_init(const GraphBuffers &g, cudaStream_t st) {
+size_t rank_splitter_bytes() { return 4 + 8 + 4 + 4 + 2 * sizeof(WyState); }
+int launch_rank_lists(const GraphBuffers &g, const uint8_t *circ, uint32_t ns, void *work, cudaStream_t st) {
+  u32 ne = 2 * g.n_nodes;
+  if (!ne || !ns) return 0;
+  // carve the per-splitter work area (16-byte aligned pieces first)
+  WyState *sa = (WyState *)work, *sb = sa + ns;
+  u64 *sub_sum = (u64 *)(sb + ns);
+  u32 *sub_len = (u32 *)(sub_sum + ns), *last_elem = sub_len + ns, *next_elem = last_elem + ns;
+  int n = 0;
+  k_rank_walk<<<blocks_for(ns, 128), 128, 0, st>>>(g.succ, circ, g.node_count, g.splitters, ns, (u64 *)g.pd, sub_len,
+                                                   sub_sum, last_elem, next_elem); ++n;
+  k_rank_link<<<blocks_for(ns, 256), 256, 0, st>>>(g.succ, circ, g.splitters, ns, (const u64 *)g.pd, sub_len, sub_sum,
+                                                   next_elem, sa); ++n;
+  int rounds = 1;
+  for (u64 d = 1; d < (u64)ns; d *= 2) ++rounds;
+  for (int r = 0; r < rounds; ++r) {
+    k_rank_wyllie<<<blocks_for(ns, 256), 256, 0, st>>>(sa, sb, ns); ++n;
+    WyState *t = sa; sa = sb; sb = t;
+  }
+  k_rank_finish<<<blocks_for(ns, 256), 256, 0, st>>>(sa, g.splitters, ns, sub_len, sub_sum, last_elem, next_elem,
+                                                     g.tail_of, g.len_of, (u64 *)g.sum_of); ++n;
+  k_rank_apply<<<blocks_for(ne, 256), 256, 0, st>>>(sa, g.splitters, ne, (u64 *)g.pd, g.scal + 1); ++n;
+  return n;
+}
+int launch_cycle_cut(const GraphBuffers &g, uint32_t n_cyclic, cudaStream_t st) {
   u32 ne = 2 * g.n_nodes;
   if (!ne) return 0;
-  k_cycle_init<<<blocks_for(ne, 256), 256, 0, st>>>((const u64 *)g.pd, g.succ, ne, (u64 *)g.cq, g.scal + 1);
-  return 1;
+  int n = 0;
+  u64 *a = (u64 *)g.cq, *b = a + ne;
+  k_cycle_init<<<blocks_for(ne, 256), 256, 0, st>>>((const u64 *)g.pd, g.succ, ne, a); ++n;
+  int cr = 1;
+  for (u64 d = 1; d < (u64)n_cyclic; d *= 2) ++cr;
+  for (int r = 0; r < cr; ++r) {
+    k_cycle_jump<<<blocks_for(ne, 256), 256, 0, st>>>(a, b, ne, (const u64 *)g.node_lo, (const u64 *)g.node_hi); ++n;
+    u64 *t = a; a = b; b = t;
+  }
+  k_cycle_cut<<<blocks_for(ne, 256), 256, 0, st>>>(a, ne, g.circ); ++n;
+  return n;
 }
-int launch_cycle_jump(const GraphBuffers &g, cudaStream_t st) {
-  u32 ne = 2 * g.n_nodes;
-  k_cycle_jump<<<blocks_for(ne, 256), 256, 0, st>>>((u64 *)g.cq, ne, (const u64 *)g.node_lo, (const u64 *)g.node_hi);
-  return 1;
-}
-int launch_cycle_cut(const GraphBuffers &g, cudaStream_t st) {
-  u32 ne = 2 * g.n_nodes;
-  k_cycle_cut<<<blocks_for(ne, 256), 256, 0, st>>>((const u64 *)g.cq, g.succ, ne, (u64 *)g.pd, g.circ);
-  return 1;
-}
-int launch_unitig_tails_heads(const GraphBuffers &g, int k, bool have_circ, cudaStream_t st) {
+int launch_unitig_heads(const GraphBuffers &g, int k, bool have_circ, cudaStream_t st) {
   u32 ne = 2 * g.n_nodes;
   if (!ne) return 0;
   const uint8_t *circ = have_circ ? g.circ : nullptr;
-  k_unitig_tails<<<blocks_for(ne, 256), 256, 0, st>>>((const u64 *)g.pd, g.succ, circ, ne, g.tail_of, g.len_of);
-  k_unitig_heads<<<blocks_for(ne, 256), 256, 0, st>>>((const u64 *)g.pd, circ, g.tail_of, g.len_of,
+  k_unitig_heads<<<blocks_for(ne, 256), 256, 0, st>>>((const u64 *)g.pd, circ, g.tail_of, g.len_of, (const u64 *)g.sum_of,
                                                       (const u64 *)g.node_lo, (const u64 *)g.node_hi, ne, k,
-                                                      g.unitig_of_head, (UnitigRec *)g.recs, g.ucirc, g.scal + 2,
-                                                      (u64 *)g.seq_cursor);
-  return 2;
+                                                      g.unitig_of_head, (UnitigRec *)g.recs, g.ucirc, (u64 *)g.cov_sum,
+                                                      g.scal + 2, (u64 *)g.seq_cursor);
+  return 1;
 }
 int launch_unitig_emit(int kw, const GraphBuffers &g, int k, cudaStream_t st) {
   u32 ne = 2 * g.n_nodes;
   if (!ne) return 0;
   if (kw == 1)
     k_unitig_emit<1><<<blocks_for(ne, 256), 256, 0, st>>>((const u64 *)g.pd, g.unitig_of_head, (const UnitigRec *)g.recs,
-                                                          (const u64 *)g.node_lo, (const u64 *)g.node_hi, g.node_count,
-                                                          ne, k, g.seq, (u64 *)g.cov_sum, g.elem_unitig);
+                                                          (const u64 *)g.node_lo, (const u64 *)g.node_hi,
+                                                          ne, k, g.seq, g.elem_unitig);
   else
     k_unitig_emit<2><<<blocks_for(ne, 256), 256, 0, st>>>((const u64 *)g.pd, g.unitig_of_head, (const UnitigRec *)g.recs,
-                                                          (const u64 *)g.node_lo, (const u64 *)g.node_hi, g.node_count,
-                                                          ne, k, g.seq, (u64 *)g.cov_sum, g.elem_unitig);
+                                                          (const u64 *)g.node_lo, (const u64 *)g.node_hi,
+                                                          ne, k, g.seq, g.elem_unitig);
   return 1;
 }
 int launch_unitig_links_out(int kw, void *slots, uint64_t cap, int k, const GraphBuffers &g, uint32_t n_unitigs,

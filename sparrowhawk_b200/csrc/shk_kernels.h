@@ -13,12 +13,12 @@ struct GraphBuffers {
   uint64_t *node_lo, *node_hi; uint16_t *node_count; uint8_t *node_raw, *node_edges;
   uint32_t n_nodes;
   // per element (2 * n_nodes)
-  uint32_t *uniq, *succ, *tail_of, *len_of, *unitig_of_head, *elem_unitig;
-  uint64_t *pd, *cq; uint8_t *circ;
+  uint32_t *uniq, *succ, *tail_of, *len_of, *unitig_of_head, *elem_unitig, *splitters;
+  uint64_t *pd, *cq /* 2 x 2N, ping-pong */, *sum_of; uint8_t *circ;
   // unitigs
   void *recs; uint8_t *ucirc; uint64_t *cov_sum; char *seq;
   uint32_t *link_from, *link_to; uint32_t link_cap;
-  // device scalars: [0] changed, [1] n_cyclic, [2] n_unitigs, [3] n_links ; cursor
+  // device scalars: [1] n_cyclic, [2] n_unitigs, [3] n_links, [4] n_splitters ; [8..9] seq cursor
   uint32_t *scal; uint64_t *seq_cursor;
 };
 
@@ -37,12 +37,14 @@ int launch_histogram_filter(int kw, void *slots, uint64_t cap, int min_count, ui
                             uint64_t *node_lo, uint64_t *node_hi, uint16_t *node_count, uint8_t *node_raw,
                             uint32_t node_cap, uint32_t *n_nodes, cudaStream_t st);
 int launch_build_edges(int kw, void *slots, uint64_t cap, int k, const GraphBuffers &g, cudaStream_t st);
-int launch_links_and_rank_init(const GraphBuffers &g, cudaStream_t st);
-int launch_rank_jump(const GraphBuffers &g, cudaStream_t st);
-int launch_cycle_init(const GraphBuffers &g, cudaStream_t st);
-int launch_cycle_jump(const GraphBuffers &g, cudaStream_t st);
-int launch_cycle_cut(const GraphBuffers &g, cudaStream_t st);
-int launch_unitig_tails_heads(const GraphBuffers &g, int k, bool have_circ, cudaStream_t st);
+int launch_unitig_links(const GraphBuffers &g, cudaStream_t st);
+// K5 (shk_rank.cuh): mark counts the splitters into scal[4]; after reading that number the host sizes
+// `work` (rank_splitter_bytes() per splitter) and launches the rest.  circ may be null (first pass).
+int launch_rank_mark(const GraphBuffers &g, const uint8_t *circ, cudaStream_t st);
+size_t rank_splitter_bytes();
+int launch_rank_lists(const GraphBuffers &g, const uint8_t *circ, uint32_t n_splitters, void *work, cudaStream_t st);
+int launch_cycle_cut(const GraphBuffers &g, uint32_t n_cyclic, cudaStream_t st);
+int launch_unitig_heads(const GraphBuffers &g, int k, bool have_circ, cudaStream_t st);
 int launch_unitig_emit(int kw, const GraphBuffers &g, int k, cudaStream_t st);
 int launch_unitig_links_out(int kw, void *slots, uint64_t cap, int k, const GraphBuffers &g,
                             uint32_t n_unitigs, cudaStream_t st);
