@@ -160,16 +160,15 @@ static shk_status count_impl(shk_asm *h, int /*reset*/) {
     SHK_CUDA(cudaMemsetAsync(h->bfill.p, 0, (size_t)P * 8, h->stream));
     SHK_CUDA(cudaMemsetAsync(d_counters(h) + 1, 0, 8, h->stream));    // n_instances
     SHK_CUDA(cudaEventRecord(h->ev[8], h->stream));
-    uint32_t *fill = h->bfill.as<uint32_t>(), *kcount = fill + P;
-    h->st.gpu_launches += launch_partition(h->kw, b, m, h->nwords, k, P, rcap, h->skrecs.p, fill, kcount, d_counters(h), h->stream);
+    h->st.gpu_launches += launch_partition(h->kw, b, m, h->nwords, k, P, rcap, h->skrecs.p, h->bfill.as<uint64_t>(), d_counters(h), h->stream);
     SHK_CUDA(cudaGetLastError());
     SHK_CUDA(cudaEventRecord(h->ev[9], h->stream));
     SHK_CUDA(cudaMemcpyAsync(h->hfill.p, h->bfill.p, (size_t)P * 8, cudaMemcpyDeviceToHost, h->stream));
     SHK_CUDA(cudaEventRecord(h->ev[3], h->stream));
     SHK_TRY(read_scalars(h));
-    const uint32_t *hf = (const uint32_t *)h->hfill.p;
+    const uint64_t *hf = (const uint64_t *)h->hfill.p;   // records | k-mers << 32 per bucket
     uint32_t mx = 0; uint64_t nrec = 0;
-    for (uint32_t i = 0; i < P; ++i) { mx = std::max(mx, hf[i]); nrec += hf[i]; }
+    for (uint32_t i = 0; i < P; ++i) { mx = std::max(mx, (uint32_t)hf[i]); nrec += (uint32_t)hf[i]; }
     h->P = P; h->rcap = rcap; h->n_records = nrec;
     if (mx <= rcap) break;
     if (++h->st.table_retries > 3) { set_error("record regions overflow after retries"); return SHK_ERR_TABLE_FULL; }
@@ -190,12 +189,12 @@ static shk_status count_impl(shk_asm *h, int /*reset*/) {
 // Groups of consecutive fine buckets whose estimated distinct k-mers fit the
 // shared table at ~55 % load.  `ratio` = distinct / instances estimate.
 static void plan_groups(shk_asm *h, uint32_t first_bucket, double ratio, std::vector<uint32_t> &gs) {
-  const uint32_t *kc = (const uint32_t *)h->hfill.p + h->P;
+  const uint64_t *bst = (const uint64_t *)h->hfill.p;
   const double budget = count_table_slots(h->kw) * 0.55;
   const uint32_t maxc = (uint32_t)count_max_group();
   double acc = 0; uint32_t cnt = 0;
   for (uint32_t bkt = first_bucket; bkt < h->P; ++bkt) {
-    double est = kc[bkt] * ratio;
+    double est = (double)(bst[bkt] >> 32) * ratio;
     if (cnt && (acc + est > budget || cnt >= maxc)) { gs.push_back(bkt); acc = 0; cnt = 0; }
     acc += est; ++cnt;
   }
@@ -204,9 +203,8 @@ static void plan_groups(shk_asm *h, uint32_t first_bucket, double ratio, std::ve
 
 static shk_status count_groups(shk_asm *h, const std::vector<uint32_t> &gs, uint32_t g_begin, uint32_t g_end,
                                int min_count, uint32_t node_cap) {
-  uint32_t *fill = h->bfill.as<uint32_t>();
   SHK_CUDA(cudaMemsetAsync(d_flags(h) + 2, 0, 4, h->stream));       // next_group
-  h->st.gpu_launches += launch_count_buckets(h->kw, h->skrecs.p, fill, h->rcap, h->groups.as<uint32_t>(), g_begin, g_end,
+  h->st.gpu_launches += launch_count_buckets(h->kw, h->skrecs.p, h->bfill.as<uint64_t>(), h->rcap, h->groups.as<uint32_t>(), g_begin, g_end,
                                              d_flags(h) + 2, h->p.k, min_count, h->ovf.p, h->ovf_cap, d_flags(h),
                                              d_histo(h), h->node_lo.as<uint64_t>(), h->node_hi.as<uint64_t>(),
                                              h->node_count.as<uint16_t>(), h->node_raw.as<uint8_t>(), node_cap,

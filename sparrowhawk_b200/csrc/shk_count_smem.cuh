@@ -105,7 +105,7 @@ struct CountOut {
 
 template <int KW>
 __global__ void __launch_bounds__(SHK_CB_THREADS, 1)
-k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u32 *__restrict__ fill, u32 rcap,
+k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__restrict__ bstat, u32 rcap,
                 const u32 *__restrict__ group_start, u32 g_begin, u32 g_end, u32 *__restrict__ next_group, int k,
                 int min_count, Table<KW> ovf, u32 *__restrict__ ovf_flag, CountOut out) {
   typedef typename KeyOf<KW>::type K;
@@ -139,7 +139,7 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u32 *__
     if (warp == 0) {
       u32 run = 0;
       for (u32 base = 0; base < nb; base += 32) {
-        u32 i = base + lane, f = i < nb ? min(fill[b0 + i], rcap) : 0, inc = f;
+        u32 i = base + lane, f = i < nb ? min((u32)bstat[b0 + i], rcap) : 0, inc = f;
         for (int o = 1; o < 32; o <<= 1) { u32 v = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += v; }
         if (i < nb) gpre[i + 1] = run + inc;
         run += __shfl_sync(0xffffffffu, inc, 31);

@@ -691,17 +691,17 @@ int count_table_slots(int kw) { return kw == 1 ? CbCfg<1>::NS : CbCfg<2>::NS; }
 int count_max_group() { return SHK_CB_MAXC; }
 
 int launch_partition(int kw, const uint64_t *bases, const uint32_t *mask, uint64_t nwords, int k, uint32_t P,
-                     uint32_t rcap, void *recs, uint32_t *fill, uint32_t *kcount, uint64_t *counters, cudaStream_t st) {
+                     uint32_t rcap, void *recs, uint64_t *bstat, uint64_t *counters, cudaStream_t st) {
   if (!nwords) return 0;
   unsigned g = blocks_for(nwords, SHK_PT_WORDS);
   if (kw == 1)
-    k_minimizer_partition<1><<<g, SHK_PT_THREADS, 0, st>>>((const u64 *)bases, mask, nwords, k, P, rcap, (uint4 *)recs, fill, kcount, (u64 *)counters);
+    k_minimizer_partition<1><<<g, SHK_PT_THREADS, 0, st>>>((const u64 *)bases, mask, nwords, k, P, rcap, (uint4 *)recs, (u64 *)bstat, (u64 *)counters);
   else
-    k_minimizer_partition<2><<<g, SHK_PT_THREADS, 0, st>>>((const u64 *)bases, mask, nwords, k, P, rcap, (Rec32 *)recs, fill, kcount, (u64 *)counters);
+    k_minimizer_partition<2><<<g, SHK_PT_THREADS, 0, st>>>((const u64 *)bases, mask, nwords, k, P, rcap, (Rec32 *)recs, (u64 *)bstat, (u64 *)counters);
   return 1;
 }
 
-int launch_count_buckets(int kw, const void *recs, const uint32_t *fill, uint32_t rcap, const uint32_t *group_start,
+int launch_count_buckets(int kw, const void *recs, const uint64_t *bstat, uint32_t rcap, const uint32_t *group_start,
                          uint32_t g_begin, uint32_t g_end, uint32_t *next_group, int k, int min_count, void *ovf_slots,
                          uint64_t ovf_cap, uint32_t *ovf_flag, uint64_t *histo, uint64_t *node_lo, uint64_t *node_hi,
                          uint16_t *node_count, uint8_t *node_raw, uint32_t node_cap, uint32_t *n_nodes,
@@ -718,10 +718,10 @@ int launch_count_buckets(int kw, const void *recs, const uint32_t *fill, uint32_
   u32 mp = (u32)(ovf_cap < 4096 ? ovf_cap : 4096);
   CountOut out{(u64 *)histo, (u64 *)node_lo, (u64 *)node_hi, node_count, node_raw, node_cap, n_nodes, (u64 *)counters};
   if (kw == 1)
-    k_count_buckets<1><<<grid, SHK_CB_THREADS, cb_smem_bytes<1>(), st>>>((const uint4 *)recs, fill, rcap, group_start, g_begin, g_end,
+    k_count_buckets<1><<<grid, SHK_CB_THREADS, cb_smem_bytes<1>(), st>>>((const uint4 *)recs, (const u64 *)bstat, rcap, group_start, g_begin, g_end,
                                                                       next_group, k, min_count, Table<1>{(Slot1 *)ovf_slots, ovf_cap, mp}, ovf_flag, out);
   else
-    k_count_buckets<2><<<grid, SHK_CB_THREADS, cb_smem_bytes<2>(), st>>>((const Rec32 *)recs, fill, rcap, group_start, g_begin, g_end,
+    k_count_buckets<2><<<grid, SHK_CB_THREADS, cb_smem_bytes<2>(), st>>>((const Rec32 *)recs, (const u64 *)bstat, rcap, group_start, g_begin, g_end,
                                                                       next_group, k, min_count, Table<2>{(Slot2 *)ovf_slots, ovf_cap, mp}, ovf_flag, out);
   return 1;
 }
