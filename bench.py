@@ -177,7 +177,7 @@ def main():
     stream = torch.cuda.current_stream()
     h = AssemblyHelper.new(w["k"], False, w["min_count"], MIN_QUAL, 0, False, False, False, False, device=local,
                            table_slots=args.table_slots)
-    h.set_stream(stream.cuda_stream)
+    h.set_stream(stream.cuda_stream or 1)   # 0 is the legacy default stream = cudaStreamLegacy (1)
 
     def barrier():
         torch.cuda.synchronize()

@@ -1,0 +1,112 @@
+//! shk_sys.rs — raw `extern "C"` declarations of include/shk.h (libshk_b200.so).
+//!
+//! This is the binding a maintainer of `sparrowhawk-asm` adds to call the
+//! B200 path (BASELINE.json north_star: "Host code stays in Rust, calls CUDA
+//! through a thin extern "C" FFI layer").  It CANNOT be compiled in this
+//! repository's build image (no rustc / cargo); the C++ and ctypes callers in
+//! this repo exercise the same ABI symbol for symbol (tests/test_abi.py checks
+//! that every symbol named here is exported).
+#![allow(non_camel_case_types)]
+use std::os::raw::{c_char, c_int, c_void};
+
+pub const SHK_HISTO_BINS: usize = 500;
+
+#[repr(C)]
+#[derive(Clone, Copy, Debug, PartialEq, Eq)]
+pub enum shk_status {
+    SHK_OK = 0,
+    SHK_ERR_BAD_ARG = 1,
+    SHK_ERR_NO_DEVICE = 2,
+    SHK_ERR_CUDA = 3,
+    SHK_ERR_OOM = 4,
+    SHK_ERR_TABLE_FULL = 5,
+    SHK_ERR_IO = 6,
+    SHK_ERR_FORMAT = 7,
+    SHK_ERR_STATE = 8,
+}
+
+/// AssemblyHelper::new's nine arguments in the reference order
+/// (www/src/workers/Assembler.ts:17-27) followed by the GPU-only knobs.
+#[repr(C)]
+#[derive(Clone, Copy, Debug, Default)]
+pub struct shk_params {
+    pub k: i32,
+    pub verbose: i32,
+    pub min_count: i32,
+    pub min_qual: i32,
+    pub chunk_size: i64,
+    pub do_bloom: i32,
+    pub do_fit: i32,
+    pub no_bubble_collapse: i32,
+    pub no_dead_end_removal: i32,
+    pub device: i32,
+    pub reserved0: i32,
+    pub table_slots: u64,
+    pub reserved1: u64,
+}
+
+#[repr(C)]
+#[derive(Clone, Copy, Debug, Default)]
+pub struct shk_stats {
+    pub n_bases: u64,
+    pub n_positions: u64,
+    pub n_instances: u64,
+    pub n_distinct: u64,
+    pub n_nodes: u64,
+    pub n_unitigs: u64,
+    pub unitig_bases: u64,
+    pub n_links: u64,
+    pub table_slots: u64,
+    pub gpu_launches: u64,
+    pub used_min_count: i32,
+    pub table_retries: i32,
+    pub ms_pack: f32,
+    pub ms_count: f32,
+    pub ms_filter: f32,
+    pub ms_graph: f32,
+    pub ms_extract: f32,
+    pub ms_count_kernel: f32,
+    pub n_spilled: u64,
+    pub n_records: u64,
+}
+
+#[repr(C)]
+pub struct shk_asm {
+    _private: [u8; 0],
+}
+
+pub type shk_progress_fn = Option<unsafe extern "C" fn(state: *const c_char, user: *mut c_void)>;
+
+#[link(name = "shk_b200")]
+extern "C" {
+    // ---- reference-facing entry points (AssemblyHelper mirror) ----
+    pub fn shk_asm_new(params: *const shk_params, out: *mut *mut shk_asm) -> shk_status;
+    pub fn shk_asm_free(h: *mut shk_asm);
+    pub fn shk_asm_set_progress_cb(h: *mut shk_asm, f: shk_progress_fn, user: *mut c_void) -> shk_status;
+    pub fn shk_asm_preprocess_files(h: *mut shk_asm, path1: *const c_char, path2_or_null: *const c_char) -> shk_status;
+    pub fn shk_asm_preprocess_push(h: *mut shk_asm, bytes: *const u8, n: usize) -> shk_status;
+    pub fn shk_asm_preprocess_finish(h: *mut shk_asm) -> shk_status;
+    pub fn shk_asm_preprocess_reads(h: *mut shk_asm, seq: *const u8, qual: *const u8, n: usize) -> shk_status;
+    pub fn shk_asm_preprocessing_info(h: *mut shk_asm, json: *mut *const c_char, len: *mut usize) -> shk_status;
+    pub fn shk_asm_assemble(h: *mut shk_asm) -> shk_status;
+    pub fn shk_asm_get_assembly(h: *mut shk_asm, json: *mut *const c_char, len: *mut usize) -> shk_status;
+    pub fn shk_last_error() -> *const c_char;
+    pub fn shk_abi_version() -> c_int;
+
+    // ---- low-level path API (host keeps its own cleaning / writers) ----
+    pub fn shk_set_stream(h: *mut shk_asm, stream: *mut c_void) -> shk_status;
+    pub fn shk_get_stream(h: *mut shk_asm) -> *mut c_void;
+    pub fn shk_load_reads(h: *mut shk_asm, seq: *const u8, qual: *const u8, n: usize, append: c_int) -> shk_status;
+    pub fn shk_load_reads_device(h: *mut shk_asm, d_seq: *const c_void, d_qual: *const c_void, n: usize, append: c_int) -> shk_status;
+    pub fn shk_count(h: *mut shk_asm, reset: c_int) -> shk_status;
+    pub fn shk_filter(h: *mut shk_asm) -> shk_status;
+    pub fn shk_build_graph(h: *mut shk_asm) -> shk_status;
+    pub fn shk_run(h: *mut shk_asm) -> shk_status;
+    pub fn shk_get_stats(h: *mut shk_asm, out: *mut shk_stats) -> shk_status;
+    pub fn shk_get_histogram(h: *mut shk_asm, histo: *mut u64) -> shk_status;
+    pub fn shk_export_kmers(h: *mut shk_asm, key_lo: *mut u64, key_hi: *mut u64, counts: *mut u16,
+                            raw_edges: *mut u8, edges: *mut u8, cap: usize, n: *mut usize) -> shk_status;
+    pub fn shk_export_unitigs(h: *mut shk_asm, seq: *mut c_char, seq_cap: usize, offsets: *mut u64,
+                              mean_cov: *mut f32, circular: *mut u8, unitig_cap: usize) -> shk_status;
+    pub fn shk_export_links(h: *mut shk_asm, from: *mut u32, to: *mut u32, cap: usize, n: *mut usize) -> shk_status;
+}

@@ -144,7 +144,8 @@ typedef struct shk_stats {
 } shk_stats;
 
 /* Use `stream` (a cudaStream_t passed as void*) for all work of this handle;
- * NULL restores the handle's own stream.  shk_get_stream returns the current one
+ * NULL restores the handle's own stream; to name the legacy default stream pass
+ * cudaStreamLegacy ((void*)1), as CUDA itself does.  shk_get_stream returns the current one
  * so the caller can bracket calls with its own CUDA events. */
 shk_status shk_set_stream(shk_asm *h, void *stream);
 void *shk_get_stream(shk_asm *h);
@@ -194,6 +195,57 @@ shk_status shk_export_unitigs(shk_asm *h, char *seq, size_t seq_cap,
  * orientation (0 = forward as exported, 1 = reverse-complement); overlap k-1. */
 shk_status shk_export_links(shk_asm *h, uint32_t *from, uint32_t *to, size_t cap,
                             size_t *n);
+
+/* ------------------------------------------------------------------ */
+/* Sharded path API (one 8xB200 box; SURVEY §8e, north_star: "reads   */
+/* shard evenly across GPUs and k-mers route to an owner GPU by hash   */
+/* range through an NCCL all-to-all").  One handle per rank / GPU.     */
+/* The library never communicates: between the calls the HOST moves    */
+/* the named device buffers with its collective library (this repo:    */
+/* torch.distributed/NCCL in sparrowhawk_b200/dist.py; a Rust host:    */
+/* ncclSend/ncclRecv).  Reference analogue: none — sparrowhawk-asm is   */
+/* single-threaded wasm (Assembler.worker.ts:31-59).                   */
+/*   1 shk_load_reads*          this rank's share of the read pairs     */
+/*   2 shk_shard_partition      K1a with the GLOBAL bucket count        */
+/*   3 shk_shard_pack           dense send buffer ordered by owner      */
+/*   4 host: all-to-all of per-bucket fills, then of the records        */
+/*   5 shk_shard_count          K1b/K2 over the received records        */
+/*   6 host: all-reduce spectrum, all-gather surviving nodes            */
+/*   7 shk_shard_set_nodes      global node set + index on every rank   */
+/*   8 shk_build_graph          K3..K6                                  */
+/* Bucket b belongs to rank r iff r*P/world <= b < (r+1)*P/world.       */
+/* ------------------------------------------------------------------ */
+
+/* Power-of-two fine-bucket count for a read set of `global_positions` stream
+ * positions (sum of shk_stats.n_positions over ranks). */
+uint32_t shk_shard_buckets(uint64_t global_positions, int k);
+/* Bytes per super-k-mer record: 16 (k <= 31) or 32 (k <= 63). */
+size_t shk_record_bytes(int k);
+/* K1a over the resident reads with n_buckets buckets; send_records[r] = records
+ * this rank holds for owner r (host array of `world` entries). */
+shk_status shk_shard_partition(shk_asm *h, uint32_t n_buckets, uint32_t world,
+                               uint32_t rank, uint64_t *send_records);
+/* d_send (device, sum(send_records) records): records ordered by bucket;
+ * d_send_fill (device, u64[n_buckets]): per bucket records | k-mers << 32. */
+shk_status shk_shard_pack(shk_asm *h, void *d_send, uint64_t *d_send_fill);
+/* d_recv (device): for source 0..world-1 in order, the dense records of this
+ * rank's buckets; recv_fill (HOST, u64[world][n_own]) the matching fills.
+ * histogram_only != 0: spectrum only (for do_fit); min_count < 0: the handle's. */
+shk_status shk_shard_count(shk_asm *h, const void *d_recv, const uint64_t *recv_fill,
+                           int histogram_only, int min_count);
+/* D2D copy of this rank's surviving nodes (shk_stats.n_nodes of them) into
+ * caller-owned device arrays: u64 lo, u64 hi, u16 count, u8 raw edge bits. */
+shk_status shk_shard_local_nodes(shk_asm *h, void *d_lo, void *d_hi, void *d_count,
+                                 void *d_raw, size_t cap);
+/* Install the gathered node set (device arrays of n_total entries, identical on
+ * every rank), the reduced spectrum and totals; builds the node index. */
+shk_status shk_shard_set_nodes(shk_asm *h, const void *d_lo, const void *d_hi,
+                               const void *d_count, const void *d_raw, size_t n_total,
+                               size_t my_offset, const uint64_t *histo_global,
+                               uint64_t n_instances_global, uint64_t n_bases_global,
+                               int used_min_count);
+/* The host-side spectrum fit used by do_fit (docs/src/assembly.md:16). */
+int shk_fit_min_count(const uint64_t *histo /*[SHK_HISTO_BINS]*/, int fallback);
 
 #ifdef __cplusplus
 }

@@ -136,7 +136,7 @@ static uint32_t next_pow2(uint64_t x) { uint32_t p = 1; while (p < x && p < (1u 
 // fit the shared-memory table of K1b at ~70 % load.
 static uint32_t target_bucket_instances(int kw) { return (uint32_t)(count_table_slots(kw) * 0.70); }
 
-static shk_status count_impl(shk_asm *h, int /*reset*/) {
+static shk_status count_impl(shk_asm *h, int /*reset*/, uint32_t P_override = 0) {
   SHK_TRY(require_device(h));
   SHK_CUDA(cudaEventRecord(h->ev[2], h->stream));
   const uint64_t *b = h->bases.as<uint64_t>() + 1;
@@ -146,6 +146,7 @@ static shk_status count_impl(shk_asm *h, int /*reset*/) {
   // fine buckets: power of two, sized from the input alone
   uint32_t P = next_pow2(std::max<uint64_t>(16, positions / target_bucket_instances(h->kw)));
   if (P > (1u << 20)) P = 1u << 20;
+  if (P_override) P = P_override;                    // sharded path: every rank cuts into the same buckets
   // records per bucket: a run holds ~ (w+1)/2 k-mers for a window of w = k-m+1 m-mers
   const int mlen = k < 11 ? k : 11, w = k - mlen + 1;
   double avg_run = std::min<double>(records_max_run(h->kw, k), std::max(1.0, (w + 1) / 2.0 * 0.6));
@@ -181,30 +182,41 @@ static shk_status count_impl(shk_asm *h, int /*reset*/) {
   h->st.n_instances = h->h_pinned[1];
   h->st.n_distinct = 0;
   h->st.table_slots = (uint64_t)P;
-  h->counted = true; h->filtered = h->graphed = false;
+  // K1b input: one segment per local bucket region
+  {
+    const uint64_t *hf = (const uint64_t *)h->hfill.p;
+    h->seg_kmers.resize(P);
+    for (uint32_t i = 0; i < P; ++i) h->seg_kmers[i] = (uint32_t)(hf[i] >> 32);
+    h->seg_per_bucket = 1; h->src_instances = h->st.n_instances; h->shard_src = false;
+  }
+  h->counted = true; h->filtered = h->graphed = false; h->histo_valid = false;
   return SHK_OK;
 }
 
 // ---- K1b + K2: shared-memory count, spectrum, filter, compaction -----------------
 // Groups of consecutive fine buckets whose estimated distinct k-mers fit the
 // shared table at ~55 % load.  `ratio` = distinct / instances estimate.
-static void plan_groups(shk_asm *h, uint32_t first_bucket, double ratio, std::vector<uint32_t> &gs) {
-  const uint64_t *bst = (const uint64_t *)h->hfill.p;
+static void plan_groups(shk_asm *h, uint32_t first_seg, double ratio, std::vector<uint32_t> &gs) {
   const double budget = count_table_slots(h->kw) * 0.55;
-  const uint32_t maxc = (uint32_t)count_max_group();
+  const uint32_t maxc = (uint32_t)count_max_group(), spb = h->seg_per_bucket;
+  const uint32_t nseg = (uint32_t)h->seg_kmers.size();
   double acc = 0; uint32_t cnt = 0;
-  for (uint32_t bkt = first_bucket; bkt < h->P; ++bkt) {
-    double est = (double)(bst[bkt] >> 32) * ratio;
-    if (cnt && (acc + est > budget || cnt >= maxc)) { gs.push_back(bkt); acc = 0; cnt = 0; }
-    acc += est; ++cnt;
+  for (uint32_t sgi = first_seg; sgi < nseg; sgi += spb) {     // all segments of a bucket stay in one group
+    double est = 0;
+    for (uint32_t j = 0; j < spb; ++j) est += (double)h->seg_kmers[sgi + j] * ratio;
+    if (cnt && (acc + est > budget || cnt + spb > maxc)) { gs.push_back(sgi); acc = 0; cnt = 0; }
+    acc += est; cnt += spb;
   }
-  gs.push_back(h->P);
+  gs.push_back(nseg);
 }
 
 static shk_status count_groups(shk_asm *h, const std::vector<uint32_t> &gs, uint32_t g_begin, uint32_t g_end,
                                int min_count, uint32_t node_cap) {
   SHK_CUDA(cudaMemsetAsync(d_flags(h) + 2, 0, 4, h->stream));       // next_group
-  h->st.gpu_launches += launch_count_buckets(h->kw, h->skrecs.p, h->bfill.as<uint64_t>(), h->rcap, h->groups.as<uint32_t>(), g_begin, g_end,
+  const bool sh = h->shard_src;
+  h->st.gpu_launches += launch_count_buckets(h->kw, sh ? h->recv_recs : h->skrecs.p, h->bfill.as<uint64_t>(), h->rcap,
+                                             sh ? h->seg_off.as<uint64_t>() : nullptr, sh ? h->seg_cnt.as<uint32_t>() : nullptr,
+                                             h->groups.as<uint32_t>(), g_begin, g_end,
                                              d_flags(h) + 2, h->p.k, min_count, h->ovf.p, h->ovf_cap, d_flags(h),
                                              d_histo(h), h->node_lo.as<uint64_t>(), h->node_hi.as<uint64_t>(),
                                              h->node_count.as<uint16_t>(), h->node_raw.as<uint8_t>(), node_cap,
@@ -214,11 +226,12 @@ static shk_status count_groups(shk_asm *h, const std::vector<uint32_t> &gs, uint
   return SHK_OK;
 }
 
-static shk_status filter_impl(shk_asm *h, int min_count, bool histogram_only = false) {
+static shk_status index_impl(shk_asm *h);
+static shk_status filter_impl(shk_asm *h, int min_count, bool histogram_only = false, bool build_index = true) {
   SHK_TRY(require_device(h));
   if (!h->counted) { set_error("filter before count"); return SHK_ERR_STATE; }
   SHK_CUDA(cudaEventRecord(h->ev[4], h->stream));
-  const uint64_t ninst = h->st.n_instances;
+  const uint64_t ninst = h->src_instances;
   // survivors have count > min_count  =>  n_nodes <= instances / (min_count + 1)
   uint64_t bound = histogram_only ? 1 : ninst / ((uint64_t)std::max(min_count, 0) + 1) + 1;
   if (bound > 0xFFFFFFF0ull) { set_error("more than 2^32 k-mers can pass the filter"); return SHK_ERR_BAD_ARG; }
@@ -243,10 +256,11 @@ static shk_status filter_impl(shk_asm *h, int min_count, bool histogram_only = f
     std::vector<uint32_t> gs;
     gs.push_back(0);
     uint32_t pilot_groups = 0;
-    if (ratio <= 0 && h->P > 256) {
+    const uint32_t spb = h->seg_per_bucket, nbuckets = (uint32_t)h->seg_kmers.size() / spb;
+    if (ratio <= 0 && nbuckets > 256) {
       // no estimate yet: count a pilot of single-bucket groups, measure distinct / instances
-      pilot_groups = std::min<uint32_t>(h->P / 8, 2 * (uint32_t)sm_count());
-      for (uint32_t i = 1; i <= pilot_groups; ++i) gs.push_back(i);
+      pilot_groups = std::min<uint32_t>(nbuckets / 8, 2 * (uint32_t)sm_count());
+      for (uint32_t i = 1; i <= pilot_groups; ++i) gs.push_back(i * spb);
       SHK_TRY(h->groups.ensure((size_t)(pilot_groups + 1) * 4));
       SHK_CUDA(cudaMemcpyAsync(h->groups.p, gs.data(), (size_t)(pilot_groups + 1) * 4, cudaMemcpyHostToDevice, h->stream));
       SHK_TRY(count_groups(h, gs, 0, pilot_groups, mc_eff, node_cap));
@@ -256,7 +270,7 @@ static shk_status filter_impl(shk_asm *h, int min_count, bool histogram_only = f
     } else if (ratio <= 0) {
       ratio = 1.0;                                    // tiny input: one bucket per group always fits
     }
-    plan_groups(h, pilot_groups, ratio, gs);
+    plan_groups(h, pilot_groups * spb, ratio, gs);
     const uint32_t ngroups = (uint32_t)gs.size() - 1;
     SHK_TRY(h->groups.ensure(gs.size() * 4));
     SHK_CUDA(cudaMemcpyAsync(h->groups.p, gs.data(), gs.size() * 4, cudaMemcpyHostToDevice, h->stream));
@@ -284,6 +298,7 @@ static shk_status filter_impl(shk_asm *h, int min_count, bool histogram_only = f
     break;
   }
   memcpy(h->histo, h->h_pinned + 8, sizeof h->histo);
+  h->histo_valid = true;
   uint64_t nd = 0;
   for (int i = 0; i < SHK_HISTO_BINS; ++i) nd += h->histo[i];
   h->st.n_distinct = nd;
@@ -293,6 +308,17 @@ static shk_status filter_impl(shk_asm *h, int min_count, bool histogram_only = f
   if (histogram_only) { SHK_CUDA(cudaEventRecord(h->ev[5], h->stream)); return SHK_OK; }
   h->st.n_nodes = nn;
   h->st.used_min_count = min_count;
+  if (!build_index) {          // sharded path: the index is built over the gathered node set (shk_shard_set_nodes)
+    SHK_CUDA(cudaEventRecord(h->ev[5], h->stream));
+    h->filtered = false; h->graphed = false; h->hu.valid = false;
+    return SHK_OK;
+  }
+  return index_impl(h);
+}
+
+// node index for the graph stage: key -> node id, 2 slots per node
+static shk_status index_impl(shk_asm *h) {
+  const uint32_t nn = (uint32_t)h->st.n_nodes;
   // node index for the graph stage: key -> node id, 2 slots per node
   uint64_t icap = std::max<uint64_t>(64, 2ull * nn);
   for (int attempt = 0;; ++attempt) {
@@ -509,6 +535,7 @@ shk_status shk_asm_set_progress_cb(shk_asm *h, shk_progress_fn fn, void *user) {
 
 shk_status shk_set_stream(shk_asm *h, void *stream) {
   if (!h) { set_error("null handle"); return SHK_ERR_BAD_ARG; }
+  if (h->dev >= 0 && h->stream) { cudaSetDevice(h->dev); cudaStreamSynchronize(h->stream); }   // work queued so far is ordered before the switch
   h->stream = stream ? (cudaStream_t)stream : h->own_stream;
   return SHK_OK;
 }
@@ -535,12 +562,13 @@ shk_status shk_run(shk_asm *h) {
 shk_status shk_get_stats(shk_asm *h, shk_stats *out) {
   if (!h || !out) { set_error("null argument"); return SHK_ERR_BAD_ARG; }
   if (h->dev >= 0) collect_timing(h);
+  if (!h->counted) h->st.n_positions = h->n_positions;   // known from the load, before any count
   *out = h->st;
   return SHK_OK;
 }
 shk_status shk_get_histogram(shk_asm *h, uint64_t *histo) {
   if (!h || !histo) { set_error("null argument"); return SHK_ERR_BAD_ARG; }
-  if (h->counted && !h->filtered) SHK_TRY(histogram_impl(h));
+  if (h->counted && !h->histo_valid) SHK_TRY(histogram_impl(h));
   memcpy(histo, h->histo, sizeof h->histo);
   return SHK_OK;
 }
@@ -632,6 +660,14 @@ shk_status shk_export_links(shk_asm *h, uint32_t *from, uint32_t *to, size_t cap
 }
 
 // ---- reference-facing entry points -------------------------------------------
+static void build_pre_json(shk_asm *h) {
+  std::string &j = h->json_pre;
+  j.clear(); j.reserve(4096);
+  j += "{\"nkmers\":" + std::to_string(h->st.n_nodes) + ",\"histo\":[";
+  for (int i = 0; i < SHK_HISTO_BINS; ++i) { if (i) j += ','; j += std::to_string(h->histo[i]); }
+  j += "],\"used_min_count\":" + std::to_string(h->st.used_min_count) + "}";
+}
+
 shk_status shk_internal_finish_preprocess(shk_asm *h, const char *mode) {
   char st[96];
   int mc = h->p.min_count;
@@ -643,11 +679,7 @@ shk_status shk_internal_finish_preprocess(shk_asm *h, const char *mode) {
   snprintf(st, sizeof st, "preprocess:%s:filtering", mode); progress(h, st);
   SHK_TRY(filter_impl(h, mc));
   progress(h, "preprocess:saving");
-  std::string &j = h->json_pre;
-  j.clear(); j.reserve(4096);
-  j += "{\"nkmers\":" + std::to_string(h->st.n_nodes) + ",\"histo\":[";
-  for (int i = 0; i < SHK_HISTO_BINS; ++i) { if (i) j += ','; j += std::to_string(h->histo[i]); }
-  j += "],\"used_min_count\":" + std::to_string(h->st.used_min_count) + "}";
+  build_pre_json(h);
   progress(h, "preprocess:end");
   return SHK_OK;
 }
@@ -736,5 +768,129 @@ shk_status shk_asm_preprocess_files(shk_asm *h, const char *path1, const char *p
   h->streaming = false;
   return shk::parse_fastq_files(h, path1, path2_or_null);
 }
+
+
+// ---- sharded path (multi-GPU) ----------------------------------------
+// One handle per rank.  The host's collective library moves the bytes between the
+// calls (NCCL all-to-all / all-gather through torch.distributed in this repo's
+// Python host, ncclSend/ncclRecv from a Rust host); nothing here communicates.
+uint32_t shk_shard_buckets(uint64_t global_positions, int k) {
+  const int kw = k <= 31 ? 1 : 2;
+  uint32_t P = next_pow2(std::max<uint64_t>(16, global_positions / target_bucket_instances(kw)));
+  return std::min<uint32_t>(P, 1u << 20);
+}
+size_t shk_record_bytes(int k) { return record_bytes(k <= 31 ? 1 : 2); }
+
+static inline uint32_t shard_lo(uint32_t P, uint32_t world, uint32_t r) { return (uint32_t)((uint64_t)r * P / world); }
+
+shk_status shk_shard_partition(shk_asm *h, uint32_t n_buckets, uint32_t world, uint32_t rank, uint64_t *send_records) {
+  SHK_TRY(require_device(h));
+  if (!world || rank >= world || !send_records || n_buckets < world || (n_buckets & (n_buckets - 1))) {
+    set_error("shard_partition: need a power-of-two bucket count >= world and rank < world"); return SHK_ERR_BAD_ARG;
+  }
+  SHK_TRY(count_impl(h, 1, n_buckets));
+  h->shard_world = world; h->shard_rank = rank;
+  // dense offsets of every bucket in the send buffer (bucket order = owner order)
+  const uint64_t *hf = (const uint64_t *)h->hfill.p;
+  std::vector<uint64_t> off(n_buckets);
+  uint64_t run = 0;
+  for (uint32_t r = 0, b = 0; r < world; ++r) {
+    const uint32_t hi = shard_lo(n_buckets, world, r + 1);
+    const uint64_t start = run;
+    for (; b < hi; ++b) { off[b] = run; run += (uint32_t)hf[b]; }
+    send_records[r] = run - start;
+  }
+  SHK_TRY(h->pack_off.ensure((size_t)n_buckets * 8));
+  SHK_CUDA(cudaMemcpyAsync(h->pack_off.p, off.data(), (size_t)n_buckets * 8, cudaMemcpyHostToDevice, h->stream));
+  SHK_CUDA(cudaStreamSynchronize(h->stream));       // `off` is pageable and dies here
+  return SHK_OK;
+}
+
+shk_status shk_shard_pack(shk_asm *h, void *d_send, uint64_t *d_send_fill) {
+  SHK_TRY(require_device(h));
+  if (!h->counted || !h->shard_world) { set_error("shard_pack before shard_partition"); return SHK_ERR_STATE; }
+  if (h->n_records && !d_send) { set_error("null send buffer"); return SHK_ERR_BAD_ARG; }
+  if (h->n_records)
+    h->st.gpu_launches += launch_pack_records(h->kw, h->skrecs.p, h->bfill.as<uint64_t>(), h->rcap, h->pack_off.as<uint64_t>(),
+                                              h->P, d_send, h->stream);
+  SHK_CUDA(cudaGetLastError());
+  if (d_send_fill) SHK_CUDA(cudaMemcpyAsync(d_send_fill, h->bfill.p, (size_t)h->P * 8, cudaMemcpyDeviceToDevice, h->stream));
+  return SHK_OK;
+}
+
+shk_status shk_shard_count(shk_asm *h, const void *d_recv, const uint64_t *recv_fill, int histogram_only, int min_count) {
+  SHK_TRY(require_device(h));
+  if (!h->counted || !h->shard_world) { set_error("shard_count before shard_partition"); return SHK_ERR_STATE; }
+  if (!recv_fill) { set_error("null recv_fill"); return SHK_ERR_BAD_ARG; }
+  const uint32_t W = h->shard_world, lo = shard_lo(h->P, W, h->shard_rank), hi = shard_lo(h->P, W, h->shard_rank + 1), nb = hi - lo;
+  // segment (owned bucket j, source s) at index j * W + s
+  std::vector<uint64_t> off((size_t)nb * W); std::vector<uint32_t> cnt((size_t)nb * W);
+  h->seg_kmers.assign((size_t)nb * W, 0);
+  uint64_t run = 0, inst = 0;
+  for (uint32_t s = 0; s < W; ++s)
+    for (uint32_t j = 0; j < nb; ++j) {
+      const uint64_t f = recv_fill[(size_t)s * nb + j];
+      off[(size_t)j * W + s] = run; cnt[(size_t)j * W + s] = (uint32_t)f; h->seg_kmers[(size_t)j * W + s] = (uint32_t)(f >> 32);
+      run += (uint32_t)f; inst += f >> 32;
+    }
+  if (run && !d_recv) { set_error("null receive buffer"); return SHK_ERR_BAD_ARG; }
+  SHK_TRY(h->seg_off.ensure(off.size() * 8 + 8)); SHK_TRY(h->seg_cnt.ensure(cnt.size() * 4 + 4));
+  if (!off.empty()) {
+    SHK_CUDA(cudaMemcpyAsync(h->seg_off.p, off.data(), off.size() * 8, cudaMemcpyHostToDevice, h->stream));
+    SHK_CUDA(cudaMemcpyAsync(h->seg_cnt.p, cnt.data(), cnt.size() * 4, cudaMemcpyHostToDevice, h->stream));
+    SHK_CUDA(cudaStreamSynchronize(h->stream));
+  }
+  h->seg_per_bucket = W; h->src_instances = inst; h->shard_src = true; h->recv_recs = d_recv;
+  h->histo_valid = false;
+  shk_status st = filter_impl(h, min_count < 0 ? h->p.min_count : min_count, histogram_only != 0, false);
+  h->shard_nodes_local = st == SHK_OK && !histogram_only ? h->st.n_nodes : 0;
+  return st;
+}
+
+shk_status shk_shard_local_nodes(shk_asm *h, void *d_lo, void *d_hi, void *d_count, void *d_raw, size_t cap) {
+  SHK_TRY(require_device(h));
+  const size_t n = h->shard_nodes_local;
+  if (cap < n) { set_error("node buffer too small (%zu < %zu)", cap, n); return SHK_ERR_BAD_ARG; }
+  if (!n) return SHK_OK;
+  if (d_lo) SHK_CUDA(cudaMemcpyAsync(d_lo, h->node_lo.p, n * 8, cudaMemcpyDeviceToDevice, h->stream));
+  if (d_hi) {
+    if (h->kw == 2) SHK_CUDA(cudaMemcpyAsync(d_hi, h->node_hi.p, n * 8, cudaMemcpyDeviceToDevice, h->stream));
+    else SHK_CUDA(cudaMemsetAsync(d_hi, 0, n * 8, h->stream));
+  }
+  if (d_count) SHK_CUDA(cudaMemcpyAsync(d_count, h->node_count.p, n * 2, cudaMemcpyDeviceToDevice, h->stream));
+  if (d_raw) SHK_CUDA(cudaMemcpyAsync(d_raw, h->node_raw.p, n, cudaMemcpyDeviceToDevice, h->stream));
+  return SHK_OK;
+}
+
+shk_status shk_shard_set_nodes(shk_asm *h, const void *d_lo, const void *d_hi, const void *d_count, const void *d_raw,
+                               size_t n_total, size_t my_offset, const uint64_t *histo_global, uint64_t n_instances_global,
+                               uint64_t n_bases_global, int used_min_count) {
+  SHK_TRY(require_device(h));
+  if (n_total > 0x7FFFFFF0ull) { set_error("too many nodes"); return SHK_ERR_BAD_ARG; }
+  if (n_total && (!d_lo || !d_count || !d_raw || (h->kw == 2 && !d_hi))) { set_error("null node array"); return SHK_ERR_BAD_ARG; }
+  SHK_TRY(h->node_lo.ensure(n_total * 8 + 8));
+  if (h->kw == 2) SHK_TRY(h->node_hi.ensure(n_total * 8 + 8));
+  SHK_TRY(h->node_count.ensure(n_total * 2 + 2)); SHK_TRY(h->node_raw.ensure(n_total + 1));
+  if (n_total) {
+    SHK_CUDA(cudaMemcpyAsync(h->node_lo.p, d_lo, n_total * 8, cudaMemcpyDeviceToDevice, h->stream));
+    if (h->kw == 2) SHK_CUDA(cudaMemcpyAsync(h->node_hi.p, d_hi, n_total * 8, cudaMemcpyDeviceToDevice, h->stream));
+    SHK_CUDA(cudaMemcpyAsync(h->node_count.p, d_count, n_total * 2, cudaMemcpyDeviceToDevice, h->stream));
+    SHK_CUDA(cudaMemcpyAsync(h->node_raw.p, d_raw, n_total, cudaMemcpyDeviceToDevice, h->stream));
+  }
+  h->node_cap = (uint32_t)n_total; h->st.n_nodes = n_total; h->shard_node_offset = my_offset;
+  if (histo_global) {
+    memcpy(h->histo, histo_global, sizeof h->histo);
+    uint64_t nd = 0;
+    for (int i = 0; i < SHK_HISTO_BINS; ++i) nd += h->histo[i];
+    h->st.n_distinct = nd; h->histo_valid = true;
+  }
+  h->st.n_instances = n_instances_global; h->st.n_bases = n_bases_global; h->n_bases = n_bases_global;
+  if (used_min_count >= 0) h->st.used_min_count = used_min_count;
+  SHK_TRY(index_impl(h));
+  build_pre_json(h);
+  return SHK_OK;
+}
+
+int shk_fit_min_count(const uint64_t *histo, int fallback) { return histo ? shk::fit_min_count(histo, fallback) : fallback; }
 
 }  // extern "C"

@@ -11,7 +11,7 @@ namespace shk {
 
 #define SHK_CB_THREADS 1024
 #define SHK_CB_WARPS (SHK_CB_THREADS / 32)
-#define SHK_CB_MAXC 128           // fine buckets per group (planner splits larger groups)
+#define SHK_CB_MAXC 256           // record segments per group (planner splits larger groups)
 #define SHK_CB_MAXPROBE 96
 
 template <int KW> struct CbCfg;
@@ -106,6 +106,7 @@ struct CountOut {
 template <int KW>
 __global__ void __launch_bounds__(SHK_CB_THREADS, 1)
 k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__restrict__ bstat, u32 rcap,
+                const u64 *__restrict__ seg_off, const u32 *__restrict__ seg_cnt,
                 const u32 *__restrict__ group_start, u32 g_begin, u32 g_end, u32 *__restrict__ next_group, int k,
                 int min_count, Table<KW> ovf, u32 *__restrict__ ovf_flag, CountOut out) {
   typedef typename KeyOf<KW>::type K;
@@ -139,7 +140,11 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
     if (warp == 0) {
       u32 run = 0;
       for (u32 base = 0; base < nb; base += 32) {
-        u32 i = base + lane, f = i < nb ? min((u32)bstat[b0 + i], rcap) : 0, inc = f;
+        // a segment = one dense run of records: fine bucket i of the local regions (seg_off == null), or the
+        // records one source rank sent for an owned bucket (sharded path)
+        u32 i = base + lane, f = 0;
+        if (i < nb) f = seg_off ? seg_cnt[b0 + i] : min((u32)bstat[b0 + i], rcap);
+        u32 inc = f;
         for (int o = 1; o < 32; o <<= 1) { u32 v = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += v; }
         if (i < nb) gpre[i + 1] = run + inc;
         run += __shfl_sync(0xffffffffu, inc, 31);
@@ -155,7 +160,8 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
       if (f < total) {
         u32 lo = 0, hi = nb;                              // bucket bi with gpre[bi] <= f < gpre[bi+1]
         while (hi - lo > 1) { u32 mid = (lo + hi) >> 1; if (gpre[mid] <= f) lo = mid; else hi = mid; }
-        const uint4 *src = reinterpret_cast<const uint4 *>(recs + ((u64)(b0 + lo) * rcap + (f - gpre[lo])));
+        const u64 sbase = seg_off ? seg_off[b0 + lo] : (u64)(b0 + lo) * rcap;
+        const uint4 *src = reinterpret_cast<const uint4 *>(recs + (sbase + (f - gpre[lo])));
         if (KW == 1) {
           uint4 r = __ldcs(src); wst[lane] = r;
           n = r.x & 31u; hasl = (r.x >> 5) & 1u; hasr = (r.x >> 6) & 1u;

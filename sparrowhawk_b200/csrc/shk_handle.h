@@ -68,6 +68,16 @@ struct shk_asm {
   uint32_t P = 0, rcap = 0;
   uint64_t n_records = 0, ovf_cap = 0;
   double ratio_est = 0;         // distinct / instances, measured by a pilot or the previous run
+  // ---- K1b input description: record segments (one per local bucket, or one per (owned bucket, source rank)) ----
+  std::vector<uint32_t> seg_kmers;     // k-mer instances per segment (host)
+  uint32_t seg_per_bucket = 1;         // segments that must share a group (all sources of one bucket)
+  uint64_t src_instances = 0;          // k-mer instances K1b will see
+  // ---- sharded path (include/shk.h "sharded path API") ----
+  uint32_t shard_world = 0, shard_rank = 0;      // 0 = not in a sharded run
+  bool shard_src = false;                        // K1b reads the received records instead of the local regions
+  const void *recv_recs = nullptr;               // caller-owned device buffer (records received from all ranks)
+  shk::DevBuf seg_off, seg_cnt, pack_off;
+  uint64_t shard_node_offset = 0, shard_nodes_local = 0;
   // ---- node index (key -> node id) for the graph stage ----
   shk::DevBuf slots;
   uint64_t cap = 0;
@@ -84,7 +94,7 @@ struct shk_asm {
   // ---- results / state ----
   shk_stats st;
   uint64_t histo[SHK_HISTO_BINS];
-  bool counted = false, filtered = false, graphed = false;
+  bool counted = false, filtered = false, graphed = false, histo_valid = false;
   shk::HostUnitigs hu;
   std::string json_pre, json_asm;
 

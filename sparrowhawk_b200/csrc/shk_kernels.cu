@@ -701,7 +701,8 @@ int launch_partition(int kw, const uint64_t *bases, const uint32_t *mask, uint64
   return 1;
 }
 
-int launch_count_buckets(int kw, const void *recs, const uint64_t *bstat, uint32_t rcap, const uint32_t *group_start,
+int launch_count_buckets(int kw, const void *recs, const uint64_t *bstat, uint32_t rcap, const uint64_t *seg_off,
+                         const uint32_t *seg_cnt, const uint32_t *group_start,
                          uint32_t g_begin, uint32_t g_end, uint32_t *next_group, int k, int min_count, void *ovf_slots,
                          uint64_t ovf_cap, uint32_t *ovf_flag, uint64_t *histo, uint64_t *node_lo, uint64_t *node_hi,
                          uint16_t *node_count, uint8_t *node_raw, uint32_t node_cap, uint32_t *n_nodes,
@@ -718,11 +719,34 @@ int launch_count_buckets(int kw, const void *recs, const uint64_t *bstat, uint32
   u32 mp = (u32)(ovf_cap < 4096 ? ovf_cap : 4096);
   CountOut out{(u64 *)histo, (u64 *)node_lo, (u64 *)node_hi, node_count, node_raw, node_cap, n_nodes, (u64 *)counters};
   if (kw == 1)
-    k_count_buckets<1><<<grid, SHK_CB_THREADS, cb_smem_bytes<1>(), st>>>((const uint4 *)recs, (const u64 *)bstat, rcap, group_start, g_begin, g_end,
+    k_count_buckets<1><<<grid, SHK_CB_THREADS, cb_smem_bytes<1>(), st>>>((const uint4 *)recs, (const u64 *)bstat, rcap, (const u64 *)seg_off, seg_cnt, group_start, g_begin, g_end,
                                                                       next_group, k, min_count, Table<1>{(Slot1 *)ovf_slots, ovf_cap, mp}, ovf_flag, out);
   else
-    k_count_buckets<2><<<grid, SHK_CB_THREADS, cb_smem_bytes<2>(), st>>>((const Rec32 *)recs, (const u64 *)bstat, rcap, group_start, g_begin, g_end,
+    k_count_buckets<2><<<grid, SHK_CB_THREADS, cb_smem_bytes<2>(), st>>>((const Rec32 *)recs, (const u64 *)bstat, rcap, (const u64 *)seg_off, seg_cnt, group_start, g_begin, g_end,
                                                                       next_group, k, min_count, Table<2>{(Slot2 *)ovf_slots, ovf_cap, mp}, ovf_flag, out);
+  return 1;
+}
+
+// Sharded path: compact the fixed-stride bucket regions into one dense buffer ordered
+// by bucket (= ordered by owner rank), the send buffer of the record all-to-all.
+// One warp per bucket, 128-bit copies.
+__global__ void __launch_bounds__(256)
+k_pack_records(const uint4 *__restrict__ recs, const u64 *__restrict__ bstat, u32 rcap, const u64 *__restrict__ dst_off,
+               u32 P, int rw /* uint4s per record */, uint4 *__restrict__ out) {
+  const u32 lane = threadIdx.x & 31;
+  const u32 warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
+  for (u32 b = warp; b < P; b += nwarps) {
+    const u64 n = (u64)min((u32)bstat[b], rcap) * (u64)rw;
+    const uint4 *src = recs + (u64)b * rcap * (u64)rw;
+    uint4 *dst = out + dst_off[b] * (u64)rw;
+    for (u64 i = lane; i < n; i += 32) dst[i] = __ldcs(src + i);
+  }
+}
+int launch_pack_records(int kw, const void *recs, const uint64_t *bstat, uint32_t rcap, const uint64_t *dst_off, uint32_t P,
+                        void *out, cudaStream_t st) {
+  if (!P) return 0;
+  unsigned g = grid_persistent((uint64_t)P * 32, 256, 8);
+  k_pack_records<<<g, 256, 0, st>>>((const uint4 *)recs, (const u64 *)bstat, rcap, (const u64 *)dst_off, P, kw == 1 ? 1 : 2, (uint4 *)out);
   return 1;
 }
 

@@ -1,0 +1,214 @@
+"""Sharded (multi-GPU) run of the path — SURVEY.md §8(e).
+
+One process per GPU (torchrun); `torch.distributed` is the plumbing.  Reads are
+split evenly by pair index (each rank loads its own share); every rank cuts its
+reads into super-k-mer records with the SAME global bucket count; a fine bucket
+b is owned by rank r iff r*P/world <= b < (r+1)*P/world, and a bucket is a
+function of the canonical minimizer, so all instances of a k-mer (with their
+read-evidenced edge bits, S13) meet on one rank:
+
+    partition (K1a) -> pack -> all-to-all(fills) -> all-to-all(records)
+      -> count + spectrum + filter on the owner (K1b/K2)
+      -> all-reduce(spectrum, totals), all-gather(surviving nodes)
+      -> node index + graph stage (K3..K6)
+
+The orchestration is written against a small engine interface so that the
+world_size-2 `gloo` tests on CPU drive exactly this code with a CPU stand-in
+for the device stages; on a GPU box the engine is the C ABI (GpuEngine).
+"""
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from . import _ffi
+from ._ffi import check
+
+
+def shard_range(P, world, r):
+    """Buckets owned by rank r: [lo, hi) — the rule of include/shk.h."""
+    return r * P // world, (r + 1) * P // world
+
+
+def split_pairs(n_pairs, world, r):
+    """Read pairs of rank r: even split by pair index, pairs kept together."""
+    return r * n_pairs // world, (r + 1) * n_pairs // world
+
+
+class GpuEngine:
+    """The device stages of one rank through the C ABI (libshk_b200.so)."""
+
+    def __init__(self, helper, device):
+        self.h = helper
+        self.lib = helper._lib
+        self.k = helper.params.k
+        self.min_count = helper.params.min_count
+        self.do_fit = bool(helper.params.do_fit)
+        self.device = device
+        self.rec_words = _ffi.lib().shk_record_bytes(self.k) // 8
+        # the torch tensors exchanged between the calls live on torch's current stream
+        # (0 = the legacy default stream, which the C ABI spells cudaStreamLegacy = 1; NULL means 'own stream')
+        helper.set_stream(torch.cuda.current_stream(device).cuda_stream or 1)
+
+    def n_positions(self):
+        return self.h.stats()["n_positions"]        # known at load time
+
+    def n_bases(self):
+        return self.h.stats()["n_bases"]            # counted on the device: valid after partition()
+
+    def buckets(self, global_positions):
+        return int(self.lib.shk_shard_buckets(int(global_positions), self.k))
+
+    def partition(self, P, world, rank):
+        out = np.zeros(world, np.uint64)
+        check(self.lib.shk_shard_partition(self.h._h, P, world, rank, out.ctypes.data))
+        return [int(x) for x in out]
+
+    def pack(self, send_buf, send_fill):
+        check(self.lib.shk_shard_pack(self.h._h, send_buf.data_ptr() if send_buf.numel() else None, send_fill.data_ptr()))
+
+    def count(self, recv_buf, recv_fill_host, histogram_only, min_count):
+        rf = np.ascontiguousarray(recv_fill_host, dtype=np.uint64)
+        self._keep = recv_buf          # K1b reads it asynchronously
+        check(self.lib.shk_shard_count(self.h._h, recv_buf.data_ptr() if recv_buf.numel() else None, rf.ctypes.data,
+                                       int(histogram_only), int(min_count)))
+
+    def local_counts(self):
+        st = self.h.stats()
+        return st["n_nodes"], int(self._instances_seen())
+
+    def _instances_seen(self):
+        return self.h.stats()["n_instances"]
+
+    def histogram(self):
+        return self.h.histogram()
+
+    def fit(self, histo, fallback):
+        h = np.ascontiguousarray(histo, dtype=np.uint64)
+        return int(self.lib.shk_fit_min_count(h.ctypes.data, int(fallback)))
+
+    def local_nodes(self, lo, hi, cnt, raw):
+        check(self.lib.shk_shard_local_nodes(self.h._h, lo.data_ptr(), hi.data_ptr(), cnt.data_ptr(), raw.data_ptr(),
+                                             lo.numel()))
+
+    def set_nodes(self, lo, hi, cnt, raw, n_total, my_off, histo, n_inst, n_bases, used_mc):
+        hh = np.ascontiguousarray(histo, dtype=np.uint64)
+        self._nodes_keep = (lo, hi, cnt, raw)
+        check(self.lib.shk_shard_set_nodes(self.h._h, lo.data_ptr(), hi.data_ptr(), cnt.data_ptr(), raw.data_ptr(),
+                                           int(n_total), int(my_off), hh.ctypes.data, int(n_inst), int(n_bases),
+                                           int(used_mc)))
+
+    def build_graph(self):
+        self.h.build_graph()
+
+
+def _staged(group):
+    """gloo moves host memory only: device tensors are staged through the host
+    (the 2-process single-GPU test); NCCL takes them as they are."""
+    return dist.get_backend(group) == "gloo"
+
+
+def _a2a(out, inp, out_splits=None, in_splits=None, group=None):
+    if _staged(group) and out.is_cuda:
+        o = torch.empty(out.shape, dtype=out.dtype)
+        dist.all_to_all_single(o, inp.cpu(), out_splits, in_splits, group=group)
+        out.copy_(o)
+    else:
+        dist.all_to_all_single(out, inp, out_splits, in_splits, group=group)
+
+
+def _all_reduce(t, group=None):
+    if _staged(group) and t.is_cuda:
+        c = t.cpu()
+        dist.all_reduce(c, group=group)
+        t.copy_(c)
+    else:
+        dist.all_reduce(t, group=group)
+
+
+def _all_gather(parts, t, group=None):
+    if _staged(group) and t.is_cuda:
+        cp = [torch.empty(p.shape, dtype=p.dtype) for p in parts]
+        dist.all_gather(cp, t.cpu(), group=group)
+        for p, c in zip(parts, cp):
+            p.copy_(c)
+    else:
+        dist.all_gather(parts, t, group=group)
+
+
+def sharded_run(eng, group=None, timings=None):
+    """One sharded pass over the reads resident on every rank's engine.
+
+    Returns a dict of global facts (identical on every rank).  After it returns,
+    every rank's engine holds the complete node set and the complete unitig
+    graph, so the reference-facing getters answer identically on all ranks.
+    """
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    dev = eng.device
+    i64 = dict(dtype=torch.int64, device=dev)
+
+    # ---- global bucket count: the same cut on every rank ----
+    tot = torch.tensor([eng.n_positions()], **i64)
+    _all_reduce(tot, group)
+    g_pos = int(tot[0])
+    P = max(eng.buckets(g_pos), 1 << max(4, (world - 1).bit_length()))
+    lo_b, hi_b = shard_range(P, world, rank)
+    n_own = hi_b - lo_b
+
+    # ---- K1a + pack ----
+    send_records = eng.partition(P, world, rank)
+    rw = eng.rec_words
+    send_buf = torch.empty(sum(send_records) * rw, **i64)
+    send_fill = torch.empty(P, **i64)
+    eng.pack(send_buf, send_fill)
+
+    # ---- exchange: fills first (they size the receive buffer), then the records ----
+    fill_in = [shard_range(P, world, r)[1] - shard_range(P, world, r)[0] for r in range(world)]
+    recv_fill = torch.empty(world * n_own, **i64)
+    _a2a(recv_fill, send_fill, [n_own] * world, fill_in, group)
+    rf_host = recv_fill.cpu().numpy().view(np.uint64).reshape(world, n_own)
+    recv_records = [int((rf_host[s] & np.uint64(0xFFFFFFFF)).sum()) for s in range(world)]
+    recv_buf = torch.empty(sum(recv_records) * rw, **i64)
+    _a2a(recv_buf, send_buf, [n * rw for n in recv_records], [n * rw for n in send_records], group)
+    inst_local = int((rf_host >> np.uint64(32)).sum())
+
+    # ---- owner-side count, spectrum, filter ----
+    used_mc = eng.min_count
+    if eng.do_fit:
+        eng.count(recv_buf, rf_host, True, 0)
+        hist = torch.from_numpy(eng.histogram().astype(np.int64)).to(dev)
+        _all_reduce(hist, group)
+        used_mc = eng.fit(hist.cpu().numpy().astype(np.uint64), eng.min_count)
+    eng.count(recv_buf, rf_host, False, used_mc)
+    n_local, _ = eng.local_counts()
+
+    # ---- all-reduce spectrum + totals; all-gather the surviving nodes ----
+    hist = torch.from_numpy(eng.histogram().astype(np.int64)).to(dev)
+    red = torch.cat([hist, torch.tensor([inst_local, eng.n_bases()], **i64)])
+    _all_reduce(red, group)
+    g_hist = red[:500].cpu().numpy().astype(np.uint64)
+    g_inst, g_bases = int(red[500]), int(red[501])
+    counts = [torch.zeros(1, **i64) for _ in range(world)]
+    _all_gather(counts, torch.tensor([n_local], **i64), group)
+    counts = [int(c) for c in counts]
+    n_max, n_total = max(counts + [1]), sum(counts)
+    lo = torch.zeros(n_max, **i64); hi = torch.zeros(n_max, **i64)
+    cnt = torch.zeros(n_max, dtype=torch.int16, device=dev); raw = torch.zeros(n_max, dtype=torch.uint8, device=dev)
+    eng.local_nodes(lo, hi, cnt, raw)
+    gathered = []
+    for t in (lo, hi, cnt, raw):
+        b = t.view(torch.uint8)                     # collectives have no 16-bit integer type
+        w = t.element_size()
+        parts = [torch.empty_like(b) for _ in range(world)]
+        _all_gather(parts, b, group)
+        g = torch.cat([p[:c * w] for p, c in zip(parts, counts)]) if n_total else b[:0]
+        gathered.append(g.view(t.dtype))
+    my_off = sum(counts[:rank])
+    eng.set_nodes(*gathered, n_total, my_off, g_hist, g_inst, g_bases, used_mc)
+
+    # ---- graph stage over the gathered node set ----
+    eng.build_graph()
+    return {"world": world, "n_buckets": P, "n_bases": g_bases, "n_positions": g_pos, "n_instances": g_inst,
+            "n_nodes": n_total, "nodes_per_rank": counts, "used_min_count": used_mc, "histo": g_hist,
+            "send_records": send_records, "recv_records": recv_records,
+            "a2a_bytes_out": int(sum(send_records[r] for r in range(world) if r != rank)) * rw * 8}

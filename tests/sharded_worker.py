@@ -1,0 +1,169 @@
+"""Worker of the sharded-path tests: launched by tests/test_sharded.py as
+`python -m torch.distributed.run --nproc-per-node W tests/sharded_worker.py <mode> ...`.
+
+mode cpu : gloo, CPU tensors, the device stages replaced by a numpy stand-in built
+           on the oracle (CpuEngine) — covers ownership, split sizes, segment
+           layout, spectrum reduction and node gathering of sparrowhawk_b200.dist.
+mode gpu : gloo, the real C ABI engine; all ranks share cuda:0 and run their
+           kernels one after the other (host-level collectives only), every rank
+           then checks the complete result against the oracle.
+Exit code 0 = every assertion on this rank passed.
+"""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+from oracle import Oracle  # noqa: E402
+from sparrowhawk_b200 import synth  # noqa: E402
+from sparrowhawk_b200.dist import shard_range, sharded_run, split_pairs  # noqa: E402
+
+
+def _mix(lo, hi):
+    x = lo ^ (hi * np.uint64(0x9E3779B97F4A7C15))
+    x ^= x >> np.uint64(29)
+    x *= np.uint64(0xBF58476D1CE4E5B9)
+    x ^= x >> np.uint64(32)
+    return x
+
+
+class CpuEngine:
+    """Stand-in for the device stages.  A 'record' is one locally pre-aggregated
+    k-mer: 4 words (key lo, key hi, count, edge bits); the bucket is a hash of the
+    canonical key, so — like the minimizer buckets of K1a — it is the same on
+    every rank."""
+    rec_words = 4
+
+    def __init__(self, seq, qual, k, min_count, min_qual, do_fit=False):
+        self.k, self.min_count, self.min_qual, self.do_fit = k, min_count, min_qual, do_fit
+        self.device = torch.device("cpu")
+        self.seq, self.qual = seq, qual
+        o = Oracle(k, 0, min_qual, 1)
+        o.add_reads(seq, qual); o.finish_count()
+        self.local = o.export_table()
+        st = o.stats()
+        self._nb, self.n_inst = st["n_bases"], st["n_instances"]
+
+    def n_bases(self):
+        return self._nb
+
+    def n_positions(self):
+        return int(self.seq.nbytes)
+
+    def buckets(self, global_positions):
+        return 64
+
+    def partition(self, P, world, rank):
+        lo, hi, c, e = self.local
+        b = (_mix(lo, hi) & np.uint64(P - 1)).astype(np.int64)
+        order = np.argsort(b, kind="stable")
+        self.recs = np.stack([lo[order], hi[order], c[order].astype(np.uint64), e[order].astype(np.uint64)], 1)
+        bs = b[order]
+        self.fill = np.zeros(P, np.uint64)
+        np.add.at(self.fill, bs, np.uint64(1))
+        km = np.zeros(P, np.uint64)
+        np.add.at(km, bs, c[order].astype(np.uint64))
+        self.fill |= km << np.uint64(32)
+        cnt = (self.fill & np.uint64(0xFFFFFFFF)).astype(np.int64)
+        return [int(cnt[slice(*shard_range(P, world, r))].sum()) for r in range(world)]
+
+    def pack(self, send_buf, send_fill):
+        send_buf.copy_(torch.from_numpy(self.recs.reshape(-1).view(np.int64)))
+        send_fill.copy_(torch.from_numpy(self.fill.view(np.int64)))
+
+    def count(self, recv_buf, recv_fill_host, histogram_only, min_count):
+        r = recv_buf.numpy().view(np.uint64).reshape(-1, 4)
+        assert r.shape[0] == int((recv_fill_host & np.uint64(0xFFFFFFFF)).sum())
+        acc = {}
+        for lo, hi, c, e in r.tolist():
+            a = acc.setdefault((hi, lo), [0, 0])
+            a[0] += c; a[1] |= e
+        keys = sorted(acc)
+        self.hist = np.zeros(500, np.uint64)
+        for kk in keys:
+            self.hist[min(acc[kk][0], 500) - 1] += np.uint64(1)
+        surv = [kk for kk in keys if acc[kk][0] > min_count] if not histogram_only else []
+        self.nodes = (np.array([kk[1] for kk in surv], np.uint64), np.array([kk[0] for kk in surv], np.uint64),
+                      np.array([min(acc[kk][0], 65535) for kk in surv], np.uint16),
+                      np.array([acc[kk][1] for kk in surv], np.uint8))
+
+    def local_counts(self):
+        return len(self.nodes[0]), 0
+
+    def histogram(self):
+        return self.hist
+
+    def fit(self, histo, fallback):
+        return fallback
+
+    def local_nodes(self, lo, hi, cnt, raw):
+        n = len(self.nodes[0])
+        lo[:n] = torch.from_numpy(self.nodes[0].view(np.int64)); hi[:n] = torch.from_numpy(self.nodes[1].view(np.int64))
+        cnt[:n] = torch.from_numpy(self.nodes[2].view(np.int16)); raw[:n] = torch.from_numpy(self.nodes[3])
+
+    def set_nodes(self, lo, hi, cnt, raw, n_total, my_off, histo, n_inst, n_bases, used_mc):
+        self.all_nodes = (lo.numpy().view(np.uint64), hi.numpy().view(np.uint64), cnt.numpy().view(np.uint16), raw.numpy())
+        self.g = dict(n_total=n_total, my_off=my_off, histo=histo, n_inst=n_inst, n_bases=n_bases, used_mc=used_mc)
+
+    def build_graph(self):
+        pass
+
+
+def main():
+    mode, k, min_count, G, cov = sys.argv[1], int(sys.argv[2]), int(sys.argv[3]), int(sys.argv[4]), float(sys.argv[5])
+    dist.init_process_group("gloo")
+    rank, world = dist.get_rank(), dist.get_world_size()
+    min_qual, err, L = 20, 0.01, 150
+    npairs = synth.num_pairs(G, cov, L)
+    lo_p, hi_p = split_pairs(npairs, world, rank)
+    seq, qual = synth.reads(7, G, cov, err, L, pair_range=(lo_p, hi_p))
+    all_seq, all_qual = synth.reads(7, G, cov, err, L)
+    o = Oracle(k, min_count, min_qual, 2)
+    o.add_reads(all_seq, all_qual); o.finish_count(); o.build_graph()
+    so = o.stats()
+    if mode == "cpu":
+        eng = CpuEngine(seq, qual, k, min_count, min_qual)
+        info = sharded_run(eng)
+        assert info["n_bases"] == so["n_bases"] and info["n_instances"] == so["n_instances"], (info, so)
+        assert np.array_equal(info["histo"], o.histogram()), "reduced spectrum differs"
+        assert info["n_nodes"] == so["n_nodes"] and sum(info["nodes_per_rank"]) == so["n_nodes"]
+        glo, ghi, gc, graw = eng.all_nodes
+        order = np.lexsort((glo, ghi))
+        olo, ohi, oc, oraw, _ = o.export_kmers()
+        assert np.array_equal(glo[order], olo) and np.array_equal(ghi[order], ohi), "gathered node set differs"
+        assert np.array_equal(gc[order], oc) and np.array_equal(graw[order], oraw), "gathered counts / edge bits differ"
+        # ownership: this rank's slice of the gathered array holds exactly the nodes of its buckets
+        P = info["n_buckets"]
+        b = (_mix(glo, ghi) & np.uint64(P - 1)).astype(np.int64)
+        a, z = eng.g["my_off"], eng.g["my_off"] + info["nodes_per_rank"][rank]
+        blo, bhi = shard_range(P, world, rank)
+        assert ((b[a:z] >= blo) & (b[a:z] < bhi)).all() and not ((b[:a] >= blo) & (b[:a] < bhi)).any()
+        assert info["recv_records"][rank] == info["send_records"][rank]
+    else:
+        from parity import assert_parity
+        from sparrowhawk_b200 import AssemblyHelper
+        from sparrowhawk_b200.dist import GpuEngine
+        torch.cuda.set_device(0)
+        h = AssemblyHelper.new(k, False, min_count, min_qual, 0, False, False, False, False, device=0)
+        h.load_reads(seq, qual)
+        eng = GpuEngine(h, torch.device("cuda", 0))
+        for _ in range(2):                 # twice: buffers and estimates are reused on the second pass
+            info = sharded_run(eng)
+            assert info["n_nodes"] == so["n_nodes"], (info["n_nodes"], so["n_nodes"])
+            assert_parity(h, o, check_table=False)
+        if world > 1:
+            assert min(info["nodes_per_rank"]) > 0
+        h.close()
+    dist.barrier()
+    dist.destroy_process_group()
+    print(f"rank {rank}/{world} ok: {so['n_nodes']} nodes, {so['n_unitigs']} unitigs")
+
+
+if __name__ == "__main__":
+    main()
