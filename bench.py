@@ -9,13 +9,19 @@ K3..K6 graph + unitigs) over one synthetic read set of the named shape.
   e2e   : the reference-facing C-ABI calls with HOST (pinned) seq/qual buffers:
           shk_asm_preprocess_reads (H2D + K0 pack + K1 + K2 + info JSON) and
           shk_asm_assemble (K3..K6 + D2H of the unitig graph + text writers).
-  roofline    : K1 extract_count alone (shk_stats.ms_extract), algorithmic bytes
-                ALG(k, L) per input base over MEASURED_PEAKS hbm_gbs.
+  roofline    : the dominant kernel, K1b k_count_buckets (its own CUDA-event duration,
+                shk_stats.ms_count_kernel), against the table-traffic share of the
+                SURVEY §8(d) model, f_k * 2 * S_slot bytes per input base; the
+                whole-step fraction uses the full ALG(k, L).  Peak = MEASURED_PEAKS hbm_gbs.
   cpu_baseline: the CPU oracle (a port; the reference crate is absent) on a
                 bounded sample of the same reads, all host threads.
 
-N > 1: one process per GPU, each rank assembles its own genome of the same shape
-(BASELINE config 4 style batch: independent replicas, no collective) — weak scaling.
+N > 1: one process per GPU (torchrun), ONE read set sharded over the ranks
+(sparrowhawk_b200/dist.py): rank r holds the read pairs of genome r of an N-genome
+community of the named shape (even split by pair index), super-k-mer records go to
+their owner rank by minimizer-bucket range through an NCCL all-to-all, survivors
+are all-gathered and the graph stage runs on the gathered node set.  Per-GPU input
+is fixed as N grows — weak scaling; value = all ranks' bases / max-over-ranks time.
 """
 import argparse
 import json
@@ -36,6 +42,9 @@ WORKLOADS = {
 }
 L = 150
 MIN_QUAL = 20
+# dram__bytes_read.sum + dram__bytes_write.sum of ONE launch, from the committed `ncu --set full`
+# capture of the same workload (profiles/r01_ncu_k1_summary.md); None where no capture exists.
+NCU_TRAFFIC = {("B", "k_count_buckets"): 624.3e6 + 13.0e6, ("B", "k_minimizer_partition"): 221.7e6 + 594.1e6}
 
 
 def alg_bytes_per_base(k):
@@ -136,7 +145,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="B", choices=sorted(WORKLOADS))
-    ap.add_argument("--cpu-sample-frac", type=float, default=0.05)
+    ap.add_argument("--cpu-sample-frac", type=float, default=None)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--table-slots", type=int, default=0)
@@ -147,22 +156,28 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     w = dict(WORKLOADS[args.workload])
-    w["seed"] = 2 + rank          # every rank assembles its own genome (replicas)
+    w["seed"] = 2 + rank          # rank r holds the reads of genome r of the community
 
     if args.impl == "reference":
+        if args.cpu_sample_frac is None:
+            args.cpu_sample_frac = 0.2
         reference_arm(args, w, rank, world)
         return
+    if args.cpu_sample_frac is None:
+        args.cpu_sample_frac = 0.4
 
     import numpy as np
     import torch
     import torch.distributed as dist
     from sparrowhawk_b200 import AssemblyHelper, synth
+    from sparrowhawk_b200.dist import GpuEngine, sharded_run
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the product path has no CPU fallback")
     torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
     if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        dist.init_process_group("nccl", device_id=dev)
 
     # ---- synthetic reads into pinned host memory --------------------------
     npairs = synth.num_pairs(w["G"], w["cov"], L)
@@ -178,6 +193,7 @@ def main():
     h = AssemblyHelper.new(w["k"], False, w["min_count"], MIN_QUAL, 0, False, False, False, False, device=local,
                            table_slots=args.table_slots)
     h.set_stream(stream.cuda_stream or 1)   # 0 is the legacy default stream = cudaStreamLegacy (1)
+    eng = GpuEngine(h, dev) if world > 1 else None
 
     def barrier():
         torch.cuda.synchronize()
@@ -185,24 +201,43 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    stage_names = ("partition", "pack", "all_to_all", "count", "gather_nodes", "graph")
+    stage_acc = {n: [] for n in stage_names}
+
+    def step():
+        """one pass of the hot path over the resident packed reads"""
+        if world == 1:
+            h.run()
+            return
+        marks = []
+        sharded_run(eng, timings=marks)
+        step.marks = marks
+
+    def harvest():
+        m = getattr(step, "marks", None)
+        if m:
+            for (_, a), (n, b) in zip(m[:-1], m[1:]):
+                stage_acc[n].append(a.elapsed_time(b))
+
     # ---- device-resident arm ------------------------------------------------
     h.load_reads_ptr(pin_seq.data_ptr(), pin_qual.data_ptr(), nbytes)     # resident packed reads (untimed)
     torch.cuda.synchronize()
     for _ in range(args.warmup):
-        h.run()
+        step()
     launches0 = h.stats()["gpu_launches"]
     sampler = ClockSampler(local)
     barrier()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    ms_extract = []
+    ms_k1a, ms_k1b = [], []
     ms_parts = {"count": [], "filter": [], "graph": []}
     ev0.record(stream)
     for _ in range(args.steps):
-        h.run()
+        step()
         st = h.stats()
-        ms_extract.append(st["ms_extract"])
+        ms_k1a.append(st["ms_extract"]); ms_k1b.append(st["ms_count_kernel"])
         for kname in ms_parts:
             ms_parts[kname].append(st["ms_" + kname])
+        harvest()
     ev1.record(stream)
     barrier()
     clocks = sampler.stop()
@@ -218,17 +253,23 @@ def main():
     # ---- end-to-end arm: host buffers through the reference-facing calls ----
     e2e = None
     if not args.no_e2e:
-        for _ in range(1):
-            h.preprocess_reads(seq, qual); h.assemble()
+        def e2e_step():
+            if world == 1:
+                h.preprocess_reads(seq, qual)
+                info = h.get_preprocessing_info()
+            else:                       # sharded form of preprocess(): H2D + K0 of this rank's reads, then the exchange
+                h.load_reads_ptr(pin_seq.data_ptr(), pin_qual.data_ptr(), nbytes)
+                sharded_run(eng)
+                info = h.get_preprocessing_info()
+            h.assemble()
+            return info, h.get_assembly()
+        e2e_step()
         barrier()
         t0 = time.perf_counter()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream)
         for _ in range(args.steps):
-            h.preprocess_reads(seq, qual)
-            info = h.get_preprocessing_info()
-            h.assemble()
-            res = h.get_assembly()
+            info, res = e2e_step()
         e1.record(stream)
         barrier()
         wall = (time.perf_counter() - t0) * 1e3
@@ -238,21 +279,31 @@ def main():
         ms_e2e = float(t.item()) / args.steps
         s2 = h.stats()
         d2h = int(s2["unitig_bases"] + s2["n_unitigs"] * 25 + s2["n_links"] * 8 + 3 * 4200 + 128)
-        e2e = {"value": bases * world / (ms_e2e * 1e-3), "unit": "bases/s", "h2d_bytes_per_step": int(2 * nbytes),
-               "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e,
-               "calls": "shk_asm_preprocess_reads + shk_asm_preprocessing_info + shk_asm_assemble + shk_asm_get_assembly",
+        calls = ("shk_asm_preprocess_reads + shk_asm_preprocessing_info + shk_asm_assemble + shk_asm_get_assembly" if world == 1 else
+                 "shk_load_reads + sharded_run (shk_shard_* + NCCL) + shk_asm_preprocessing_info + shk_asm_assemble + shk_asm_get_assembly")
+        e2e = {"value": bases * world / (ms_e2e * 1e-3), "unit": "bases/s", "h2d_bytes_per_step": int(2 * nbytes) * world,
+               "d2h_bytes_per_step": d2h * world, "ms_per_step": ms_e2e, "calls": calls,
                "ncontigs": json.loads(res)["ncontigs"], "nkmers": json.loads(info)["nkmers"]}
 
-    # ---- roofline of the dominant kernel (K1 extract_count) -----------------
+    # ---- roofline of the dominant kernel (K1b k_count_buckets) ----------------
     peak, peak_src = peaks()
-    ms_k1 = sum(ms_extract) / len(ms_extract)
-    alg = alg_bytes_per_base(w["k"]) * bases
-    achieved = alg / (ms_k1 * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": "k_extract_count", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-                "alg_bytes_per_base": alg_bytes_per_base(w["k"]), "kernel_ms": ms_k1,
-                "whole_step_frac": (alg / (ms_step * 1e-3) / 1e9) / peak,
-                "stage_ms": {kname: sum(v) / len(v) for kname, v in ms_parts.items()}}
+    k1b = sum(ms_k1b) / len(ms_k1b)
+    k1a = sum(ms_k1a) / len(ms_k1a)
+    slot = 16 if w["k"] <= 31 else 32
+    alg_table = (L - w["k"] + 1) / L * 2 * slot          # table read-modify-write share of ALG(k, L)
+    # K1b of this rank counts the k-mers it OWNS: 1/world of all ranks' instances = one rank's worth
+    achieved = alg_table * bases / (k1b * 1e-3) / 1e9
+    alg = alg_bytes_per_base(w["k"])
+    roofline = {"bound": "hbm", "kernel": "k_count_buckets", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": NCU_TRAFFIC.get((args.workload, "k_count_buckets")),
+                "peak_source": peak_src, "alg_bytes_per_base_kernel": alg_table, "alg_bytes_per_base": alg,
+                "kernel_ms": k1b, "k_minimizer_partition_ms": k1a,
+                "whole_step_achieved": alg * bases / (ms_step * 1e-3) / 1e9,
+                "whole_step_frac": (alg * bases / (ms_step * 1e-3) / 1e9) / peak,
+                "stage_ms": ({n: sum(v) / len(v) for n, v in stage_acc.items() if v} if world > 1 else
+                             {kname: sum(v) / len(v) for kname, v in ms_parts.items()}),
+                "note": "traffic = dram bytes of one launch from the committed ncu capture (profiles/); the design "
+                        "keeps the table in shared memory, so measured traffic is far below the model's bytes"}
 
     # ---- CPU baseline (rank 0, N = 1 only) -----------------------------------
     cpu = None
@@ -270,18 +321,21 @@ def main():
                          f"{dt:.1f} s; sparrowhawk-asm native CPU: unavailable on this box"}
 
     if rank == 0:
+        multi = ("single GPU" if world == 1 else
+                 f"one read set of {world} genomes sharded by read pair over {world} ranks; records routed to the owner "
+                 "rank by minimizer-bucket range through an NCCL all-to-all; nodes all-gathered; graph stage on the gathered set")
         print(json.dumps({
             "metric": "input bases/s, k-mer count + DBG build", "value": value, "unit": "bases/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "u64" if w["k"] <= 31 else "u128", "data": "synthetic",
-            "config": {"workload": f"{args.workload}: {w['desc']}", "min_qual": MIN_QUAL, "min_count": w["min_count"],
-                       "bases_per_step_per_gpu": bases, "read_pairs": npairs,
-                       "multi_gpu": "independent genome per rank (replicas, no collective)" if world > 1 else "single GPU",
-                       "l2": "inputs larger than L2: packed reads %.0f MB + table %.0f MB vs 126 MB L2"
-                             % (st["n_positions"] * 0.375 / 1e6, st["table_slots"] * (16 if w["k"] <= 31 else 32) / 1e6),
+            "config": {"workload": f"{args.workload}: {w['desc']}" + (f" x {world} genomes" if world > 1 else ""),
+                       "min_qual": MIN_QUAL, "min_count": w["min_count"],
+                       "bases_per_step_per_gpu": bases, "read_pairs_per_gpu": npairs, "multi_gpu": multi,
+                       "l2": "inputs larger than L2: packed reads %.0f MB + super-k-mer records %.0f MB vs 126 MB L2"
+                             % (st["n_positions"] * 0.375 / 1e6, st["n_records"] * (16 if w["k"] <= 31 else 32) / 1e6),
                        "n_distinct": st["n_distinct"], "n_nodes": st["n_nodes"], "n_unitigs": st["n_unitigs"],
-                       "table_slots": st["table_slots"], "gen_seconds": round(t_gen, 2)},
+                       "fine_buckets": st["table_slots"], "gen_seconds": round(t_gen, 2)},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
             "clocks": clocks,
         }))

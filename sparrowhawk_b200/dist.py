@@ -147,6 +147,14 @@ def sharded_run(eng, group=None, timings=None):
     dev = eng.device
     i64 = dict(dtype=torch.int64, device=dev)
 
+    def mark(name):
+        """stage boundary: a CUDA event on the current stream (bench.py reads the gaps)"""
+        if timings is not None and dev.type == "cuda":
+            ev = torch.cuda.Event(enable_timing=True)
+            ev.record(torch.cuda.current_stream(dev))
+            timings.append((name, ev))
+
+    mark("start")
     # ---- global bucket count: the same cut on every rank ----
     tot = torch.tensor([eng.n_positions()], **i64)
     _all_reduce(tot, group)
@@ -157,10 +165,12 @@ def sharded_run(eng, group=None, timings=None):
 
     # ---- K1a + pack ----
     send_records = eng.partition(P, world, rank)
+    mark("partition")
     rw = eng.rec_words
     send_buf = torch.empty(sum(send_records) * rw, **i64)
     send_fill = torch.empty(P, **i64)
     eng.pack(send_buf, send_fill)
+    mark("pack")
 
     # ---- exchange: fills first (they size the receive buffer), then the records ----
     fill_in = [shard_range(P, world, r)[1] - shard_range(P, world, r)[0] for r in range(world)]
@@ -171,6 +181,7 @@ def sharded_run(eng, group=None, timings=None):
     recv_buf = torch.empty(sum(recv_records) * rw, **i64)
     _a2a(recv_buf, send_buf, [n * rw for n in recv_records], [n * rw for n in send_records], group)
     inst_local = int((rf_host >> np.uint64(32)).sum())
+    mark("all_to_all")
 
     # ---- owner-side count, spectrum, filter ----
     used_mc = eng.min_count
@@ -181,6 +192,7 @@ def sharded_run(eng, group=None, timings=None):
         used_mc = eng.fit(hist.cpu().numpy().astype(np.uint64), eng.min_count)
     eng.count(recv_buf, rf_host, False, used_mc)
     n_local, _ = eng.local_counts()
+    mark("count")
 
     # ---- all-reduce spectrum + totals; all-gather the surviving nodes ----
     hist = torch.from_numpy(eng.histogram().astype(np.int64)).to(dev)
@@ -205,9 +217,11 @@ def sharded_run(eng, group=None, timings=None):
         gathered.append(g.view(t.dtype))
     my_off = sum(counts[:rank])
     eng.set_nodes(*gathered, n_total, my_off, g_hist, g_inst, g_bases, used_mc)
+    mark("gather_nodes")
 
     # ---- graph stage over the gathered node set ----
     eng.build_graph()
+    mark("graph")
     return {"world": world, "n_buckets": P, "n_bases": g_bases, "n_positions": g_pos, "n_instances": g_inst,
             "n_nodes": n_total, "nodes_per_rank": counts, "used_min_count": used_mc, "histo": g_hist,
             "send_records": send_records, "recv_records": recv_records,
