@@ -26,27 +26,43 @@ template <int KW> __host__ __device__ constexpr size_t cb_smem_bytes() {
 }
 
 // ---- shared-table insert ---------------------------------------------------
+// Slot hash inside a CTA's table: every key of a group shares a handful of
+// minimizers, so the hash must avalanche the non-minimizer bases; two
+// multiply-xorshift rounds on the folded key are enough (placement only, S15).
+__device__ __forceinline__ u32 slot_hash(u64 key) {
+  u32 h = (u32)key * 0x9E3779B1u ^ (u32)(key >> 32) * 0x85EBCA77u;
+  h ^= h >> 15; h *= 0x2C1B3C6Du; h ^= h >> 13; h *= 0x297A2D39u; h ^= h >> 16;
+  return h;
+}
+__device__ __forceinline__ u32 slot_hash(u128 key) {
+  const u64 lo = (u64)key, hi = (u64)(key >> 64);
+  u32 h = (u32)lo * 0x9E3779B1u ^ (u32)(lo >> 32) * 0x85EBCA77u ^ (u32)hi * 0xC2B2AE3Du ^ (u32)(hi >> 32) * 0x27D4EB2Fu;
+  h ^= h >> 15; h *= 0x2C1B3C6Du; h ^= h >> 13; h *= 0x297A2D39u; h ^= h >> 16;
+  return h;
+}
+// count (low 24 bits, S7: saturation far above 65535) and edge byte (top 8 bits) of a claimed slot:
+// one ATOMS.ADD that also returns the edge bits already present, an ATOMS.OR only when new bits arrive
+__device__ __forceinline__ void slot_hit(u32 *val, u32 e) {
+  const u32 old = atomicAdd(val, 1u);
+  if (((old >> 24) & e) != e) atomicOr(val, e << 24);
+  if ((old & 0xFFFFFFu) >= 0x800000u) atomicSub(val, 1u);
+}
 // returns false when the key found no room inside the probe window (caller spills)
 __device__ __forceinline__ bool smem_insert(u64 *keys, u32 *vals, int NS, u64 key, u32 e) {
-  u32 s = (u32)(((hash_key(key) >> 32) * (u64)NS) >> 32);
+  u32 s = __umulhi(slot_hash(key), (u32)NS);
   for (int probe = 0; probe < SHK_CB_MAXPROBE; ++probe) {
     u64 cur = keys[s];
     if (cur == SHK_EMPTY64) {
       cur = atomicCAS(&keys[s], SHK_EMPTY64, key);
       if (cur == SHK_EMPTY64) cur = key;
     }
-    if (cur == key) {
-      u32 v = vals[s];
-      if ((v & 0xFFFFFFu) < 0x800000u) atomicAdd(&vals[s], 1u);      // S7: saturates far above 65535
-      if ((((v >> 24) & e)) != e) atomicOr(&vals[s], e << 24);
-      return true;
-    }
+    if (cur == key) { slot_hit(vals + s, e); return true; }
     s = (s + 1 == (u32)NS) ? 0u : s + 1;
   }
   return false;
 }
 __device__ __forceinline__ bool smem_insert(U128Pair *keys, u32 *vals, int NS, u128 key, u32 e) {
-  u32 s = (u32)(((hash_key(key) >> 32) * (u64)NS) >> 32);
+  u32 s = __umulhi(slot_hash(key), (u32)NS);
   const u64 klo = (u64)key, khi = (u64)(key >> 64);
   for (int probe = 0; probe < SHK_CB_MAXPROBE; ++probe) {
     uint4 c4 = *reinterpret_cast<const uint4 *>(keys + s);
@@ -57,43 +73,36 @@ __device__ __forceinline__ bool smem_insert(U128Pair *keys, u32 *vals, int NS, u
       lo = old.lo; hi = old.hi;
       if (hi == SHK_EMPTY64) { lo = klo; hi = khi; }
     }
-    if (lo == klo && hi == khi) {
-      u32 v = vals[s];
-      if ((v & 0xFFFFFFu) < 0x800000u) atomicAdd(&vals[s], 1u);
-      if ((((v >> 24) & e)) != e) atomicOr(&vals[s], e << 24);
-      return true;
-    }
+    if (lo == klo && hi == khi) { slot_hit(vals + s, e); return true; }
     s = (s + 1 == (u32)NS) ? 0u : s + 1;
   }
   return false;
 }
 
-// ---- record decode: canonical k-mer i of a record + its edge byte ------------
-__device__ __forceinline__ void rec_kmer(const uint4 *st /* staged record */, int i, int k, u32 n, u32 hasl, u32 hasr,
-                                         u64 &key, u32 &e, u64) {
-  uint4 r = st[0];
-  u128 R = ((u128)(((u64)r.w << 32) | r.z) << 64) | (((u64)r.y << 32) | r.x);
-  u64 fwd = (u64)((R << (2 * (1 + i))) >> (128 - 2 * k));
-  u32 a = (u32)(R >> (126 - 2 * i)) & 3u, b = (u32)(R >> (124 - 2 * i - 2 * k)) & 3u;
-  u64 rc = revcomp_key(fwd, k);
-  bool hl = i > 0 || hasl, hr = (u32)i + 1 < n || hasr;
-  if (fwd < rc) { key = fwd; e = (hr ? (1u << b) : 0u) | (hl ? (16u << a) : 0u); }
-  else { key = rc; e = (hl ? (1u << (a ^ 2u)) : 0u) | (hr ? (16u << (b ^ 2u)) : 0u); }
+// ---- record decode ------------------------------------------------------------
+// Round t of a warp hands lane l k-mer number 32 t + l of the warp's 32 staged
+// records, so the lanes are perfectly balanced whatever the record lengths.
+// The k-mer is cut out of the staged record with 32-bit funnel shifts: word j of
+// a record (j = 0 holds the first bases) sits at u32 index j ^ 3 of its uint4s.
+// Returns fwd = k-mer i, a = the base in front of it, b = the base behind it.
+__device__ __forceinline__ void kmer_at(const u32 *rw, int i, int k, u64 &fwd, u32 &a, u32 &b) {
+  const int o = 2 * i + 2, wi = o >> 5, sh = o & 31;            // bit offset of the k-mer; wi <= 1
+  const u32 w0 = rw[wi ^ 3], w1 = rw[(wi + 1) ^ 3], w2 = rw[(wi + 2) ^ 3];
+  const u64 F = ((u64)__funnelshift_l(w1, w0, sh) << 32) | __funnelshift_l(w2, w1, sh);
+  a = (rw[((o - 2) >> 5) ^ 3] >> (30 - ((o - 2) & 31))) & 3u;
+  fwd = F >> (64 - 2 * k);
+  b = (u32)(F >> (62 - 2 * k)) & 3u;                             // k <= 31
 }
-__device__ __forceinline__ void rec_kmer(const uint4 *st, int i, int k, u32 n, u32 hasl, u32 hasr, u128 &key, u32 &e,
-                                         u128) {
-  uint4 ra = st[0], rb = st[1];
-  u128 A = ((u128)(((u64)ra.w << 32) | ra.z) << 64) | (((u64)ra.y << 32) | ra.x);
-  u128 B = ((u128)(((u64)rb.w << 32) | rb.z) << 64) | (((u64)rb.y << 32) | rb.x);
-  int s = 2 * (1 + i);                                  // <= 120
-  u128 top = (A << s) | (B >> (128 - s));
-  u128 fwd = top >> (128 - 2 * k);
-  auto base_at = [&](int j) -> u32 { return j < 64 ? (u32)(A >> (126 - 2 * j)) & 3u : (u32)(B >> (126 - 2 * (j - 64))) & 3u; };
-  u32 a = base_at(i), b = base_at(1 + i + k);
-  u128 rc = revcomp_key(fwd, k);
-  bool hl = i > 0 || hasl, hr = (u32)i + 1 < n || hasr;
-  if (fwd < rc) { key = fwd; e = (hr ? (1u << b) : 0u) | (hl ? (16u << a) : 0u); }
-  else { key = rc; e = (hl ? (1u << (a ^ 2u)) : 0u) | (hr ? (16u << (b ^ 2u)) : 0u); }
+__device__ __forceinline__ void kmer_at(const u32 *rw, int i, int k, u128 &fwd, u32 &a, u32 &b) {
+  const int o = 2 * i + 2, wi = o >> 5, sh = o & 31;            // wi <= 3, words wi .. wi+4 <= 7
+  const u32 w0 = rw[wi ^ 3], w1 = rw[(wi + 1) ^ 3], w2 = rw[(wi + 2) ^ 3], w3 = rw[(wi + 3) ^ 3], w4 = rw[(wi + 4) ^ 3];
+  const u64 Fh = ((u64)__funnelshift_l(w1, w0, sh) << 32) | __funnelshift_l(w2, w1, sh);
+  const u64 Fl = ((u64)__funnelshift_l(w3, w2, sh) << 32) | __funnelshift_l(w4, w3, sh);
+  a = (rw[((o - 2) >> 5) ^ 3] >> (30 - ((o - 2) & 31))) & 3u;
+  const int s = 128 - 2 * k;                                     // 2 .. 62 (33 <= k <= 63)
+  const u64 lo = (Fl >> s) | (Fh << (64 - s)), hi = Fh >> s;
+  fwd = ((u128)hi << 64) | lo;
+  b = (u32)(Fl >> (s - 2)) & 3u;
 }
 
 struct CountOut {
@@ -128,7 +137,7 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
 
   for (;;) {
     __syncthreads();
-    if (tid == 0) misc[0] = g_begin + atomicAdd(next_group, 1u);
+    if (tid == 0) { misc[0] = g_begin + atomicAdd(next_group, 1u); misc[1] = 0; }
     __syncthreads();
     const u32 g = misc[0];
     if (g >= g_end) break;
@@ -153,12 +162,16 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
     }
     __syncthreads();
     const u32 total = gpre[nb];
-    // ---- decode + insert: each warp takes 32 records at a time ----
-    for (u32 cbase = warp * 32; cbase < total; cbase += SHK_CB_THREADS) {
+    // ---- decode + insert: a warp grabs 32 records at a time (dynamic, so no warp idles at the tail) ----
+    for (;;) {
+      u32 cbase = 0;
+      if (lane == 0) cbase = atomicAdd(&misc[1], 32u);
+      cbase = __shfl_sync(0xffffffffu, cbase, 0);
+      if (cbase >= total) break;
       const u32 f = cbase + lane;
       u32 n = 0, hasl = 0, hasr = 0;
       if (f < total) {
-        u32 lo = 0, hi = nb;                              // bucket bi with gpre[bi] <= f < gpre[bi+1]
+        u32 lo = 0, hi = nb;                              // segment with gpre[lo] <= f < gpre[lo+1]
         while (hi - lo > 1) { u32 mid = (lo + hi) >> 1; if (gpre[mid] <= f) lo = mid; else hi = mid; }
         const u64 sbase = seg_off ? seg_off[b0 + lo] : (u64)(b0 + lo) * rcap;
         const uint4 *src = reinterpret_cast<const uint4 *>(recs + (sbase + (f - gpre[lo])));
@@ -170,10 +183,10 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
           n = rb.x & 63u; hasl = (rb.x >> 6) & 1u; hasr = (rb.x >> 7) & 1u;
         }
       }
-      // exclusive prefix of n over the warp; bitmap of run starts
+      // exclusive prefix of the k-mer counts over the warp; bitmap of the first k-mer of every record
       u32 incl = n;
       for (int o = 1; o < 32; o <<= 1) { u32 v = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += v; }
-      const u32 excl = incl - n, T = __shfl_sync(0xffffffffu, incl, 31);
+      const u32 excl = incl - n, T = __shfl_sync(0xffffffffu, incl, 31);       // T <= 32 * 60
       const u32 meta = n | (hasl << 8) | (hasr << 9) | (excl << 16);
       wbm[lane] = 0; wbm[lane + 32] = 0;
       __syncwarp();
@@ -183,16 +196,19 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
       for (u32 it = 0; it * 32 < T; ++it) {
         const u32 word = wbm[it];
         const u32 t = it * 32 + lane;
-        u32 r = running + __popc(word & (0xFFFFFFFFu >> (31 - lane)));   // records started at or before t
+        u32 r = running + __popc(word & (0xFFFFFFFFu >> (31 - lane)));   // records started at or before k-mer t
         r = r ? r - 1 : 0;
-        // records with n == 0 never start a run; r indexes the r-th *non-empty* record: map through
-        // a second prefix only if empties exist (they only occur in the last partial chunk, at the end)
         const u32 mr = __shfl_sync(0xffffffffu, meta, r & 31);
         running += __popc(word);
         if (t < T) {
-          const u32 rn = mr & 0xFFu, rl = (mr >> 8) & 1u, rr = (mr >> 9) & 1u, rex = mr >> 16;
+          const u32 rn = mr & 0xFFu, rl = (mr >> 8) & 1u, rr = (mr >> 9) & 1u, i = t - (mr >> 16);
+          K fwd; u32 a, b;
+          kmer_at(reinterpret_cast<const u32 *>(wst + (size_t)(r & 31) * RECW), (int)i, k, fwd, a, b);
+          const K rc = revcomp_key(fwd, k);
+          const bool hl = i > 0 || rl, hr = i + 1 < rn || rr;
           K key; u32 e;
-          rec_kmer(wst + (size_t)(r & 31) * RECW, (int)(t - rex), k, rn, rl, rr, key, e, (K)0);
+          if (fwd < rc) { key = fwd; e = (hr ? (1u << b) : 0u) | (hl ? (16u << a) : 0u); }
+          else { key = rc; e = (hl ? (1u << (a ^ 2u)) : 0u) | (hr ? (16u << (b ^ 2u)) : 0u); }
           ++ndec;
           if (!smem_insert(keys, vals, NS, key, e)) { table_insert(ovf, key, e, 1u, ovf_flag); ++nspill; }
         }
