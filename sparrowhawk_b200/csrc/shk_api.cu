@@ -5,6 +5,7 @@
 // with SHK_ERR_NO_DEVICE.
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <cmath>
 #include <algorithm>
@@ -186,7 +187,8 @@ static shk_status count_impl(shk_asm *h, int /*reset*/, uint32_t P_override = 0)
   {
     const uint64_t *hf = (const uint64_t *)h->hfill.p;
     h->seg_kmers.resize(P);
-    for (uint32_t i = 0; i < P; ++i) h->seg_kmers[i] = (uint32_t)(hf[i] >> 32);
+    h->seg_recs.resize(P);
+    for (uint32_t i = 0; i < P; ++i) { h->seg_kmers[i] = (uint32_t)(hf[i] >> 32); h->seg_recs[i] = (uint32_t)hf[i]; }
     h->seg_per_bucket = 1; h->src_instances = h->st.n_instances; h->shard_src = false;
   }
   h->counted = true; h->filtered = h->graphed = false; h->histo_valid = false;
@@ -214,15 +216,27 @@ static shk_status count_groups(shk_asm *h, const std::vector<uint32_t> &gs, uint
                                int min_count, uint32_t node_cap) {
   SHK_CUDA(cudaMemsetAsync(d_flags(h) + 2, 0, 4, h->stream));       // next_group
   const bool sh = h->shard_src;
+  // de-dup scratch: one list per CTA, sized for the largest group of this launch
+  uint32_t uq_cap = 0;
+  if (h->kw == 1 && !h->no_dedup) {
+    for (uint32_t g = g_begin; g < g_end; ++g) {
+      uint64_t r = 0;
+      for (uint32_t sgi = gs[g]; sgi < gs[g + 1]; ++sgi) r += h->seg_recs[sgi];
+      uq_cap = (uint32_t)std::max<uint64_t>(uq_cap, r);
+    }
+    uq_cap = (uq_cap + 63u) & ~63u;
+    const size_t ctas = (size_t)sm_count();
+    SHK_TRY(h->uq_rec.ensure(ctas * uq_cap * 16 + 16)); SHK_TRY(h->uq_cnt.ensure(ctas * uq_cap * 4 + 16));
+  }
   h->st.gpu_launches += launch_count_buckets(h->kw, sh ? h->recv_recs : h->skrecs.p, h->bfill.as<uint64_t>(), h->rcap,
                                              sh ? h->seg_off.as<uint64_t>() : nullptr, sh ? h->seg_cnt.as<uint32_t>() : nullptr,
+                                             uq_cap ? h->uq_rec.p : nullptr, h->uq_cnt.as<uint32_t>(), uq_cap,
                                              h->groups.as<uint32_t>(), g_begin, g_end,
                                              d_flags(h) + 2, h->p.k, min_count, h->ovf.p, h->ovf_cap, d_flags(h),
                                              d_histo(h), h->node_lo.as<uint64_t>(), h->node_hi.as<uint64_t>(),
                                              h->node_count.as<uint16_t>(), h->node_raw.as<uint8_t>(), node_cap,
                                              d_flags(h) + 1, d_counters(h), h->stream);
   SHK_CUDA(cudaGetLastError());
-  (void)gs;
   return SHK_OK;
 }
 
@@ -473,6 +487,7 @@ shk_status shk_asm_new(const shk_params *params, shk_asm **out) {
   if (!h) { set_error("out of host memory"); return SHK_ERR_OOM; }
   h->p = *params;
   h->kw = params->k <= 31 ? 1 : 2;
+  { const char *nd = getenv("SHK_NO_DEDUP"); h->no_dedup = nd && nd[0] == '1'; }
   memset(&h->st, 0, sizeof h->st);
   memset(h->histo, 0, sizeof h->histo);
   h->st.used_min_count = params->min_count;
@@ -517,7 +532,7 @@ void shk_asm_free(shk_asm *h) {
     DevBuf *bufs[] = {&h->bases, &h->mask, &h->ascii_seq, &h->ascii_qual, &h->slots, &h->dscal, &h->node_lo, &h->node_hi,
                       &h->node_count, &h->node_raw, &h->node_edges, &h->uniq, &h->succ, &h->tail_of, &h->len_of,
                       &h->unitig_of_head, &h->elem_unitig, &h->pd, &h->cq, &h->circ, &h->recs, &h->ucirc, &h->cov_sum,
-                      &h->useq, &h->link_from, &h->link_to, &h->gscal, &h->splitters, &h->sum_of, &h->rank_work, &h->skrecs, &h->bfill, &h->groups, &h->ovf};
+                      &h->useq, &h->link_from, &h->link_to, &h->gscal, &h->splitters, &h->sum_of, &h->rank_work, &h->skrecs, &h->bfill, &h->groups, &h->ovf, &h->uq_rec, &h->uq_cnt, &h->seg_off, &h->seg_cnt, &h->pack_off};
     for (auto b : bufs) b->release();
     if (h->h_pinned) cudaFreeHost(h->h_pinned);
     h->hfill.release();
@@ -825,12 +840,12 @@ shk_status shk_shard_count(shk_asm *h, const void *d_recv, const uint64_t *recv_
   const uint32_t W = h->shard_world, lo = shard_lo(h->P, W, h->shard_rank), hi = shard_lo(h->P, W, h->shard_rank + 1), nb = hi - lo;
   // segment (owned bucket j, source s) at index j * W + s
   std::vector<uint64_t> off((size_t)nb * W); std::vector<uint32_t> cnt((size_t)nb * W);
-  h->seg_kmers.assign((size_t)nb * W, 0);
+  h->seg_kmers.assign((size_t)nb * W, 0); h->seg_recs.assign((size_t)nb * W, 0);
   uint64_t run = 0, inst = 0;
   for (uint32_t s = 0; s < W; ++s)
     for (uint32_t j = 0; j < nb; ++j) {
       const uint64_t f = recv_fill[(size_t)s * nb + j];
-      off[(size_t)j * W + s] = run; cnt[(size_t)j * W + s] = (uint32_t)f; h->seg_kmers[(size_t)j * W + s] = (uint32_t)(f >> 32);
+      off[(size_t)j * W + s] = run; cnt[(size_t)j * W + s] = (uint32_t)f; h->seg_kmers[(size_t)j * W + s] = (uint32_t)(f >> 32); h->seg_recs[(size_t)j * W + s] = (uint32_t)f;
       run += (uint32_t)f; inst += f >> 32;
     }
   if (run && !d_recv) { set_error("null receive buffer"); return SHK_ERR_BAD_ARG; }

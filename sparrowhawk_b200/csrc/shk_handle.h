@@ -70,6 +70,10 @@ struct shk_asm {
   double ratio_est = 0;         // distinct / instances, measured by a pilot or the previous run
   // ---- K1b input description: record segments (one per local bucket, or one per (owned bucket, source rank)) ----
   std::vector<uint32_t> seg_kmers;     // k-mer instances per segment (host)
+  std::vector<uint32_t> seg_recs;      // records per segment (host)
+  shk::DevBuf uq_rec, uq_cnt;          // K1b de-dup: per-CTA lists of distinct records + multiplicities
+  uint32_t uq_cap = 0;
+  bool no_dedup = false;               // SHK_NO_DEDUP=1 in the environment: count every record (A/B measurement)
   uint32_t seg_per_bucket = 1;         // segments that must share a group (all sources of one bucket)
   uint64_t src_instances = 0;          // k-mer instances K1b will see
   // ---- sharded path (include/shk.h "sharded path API") ----

@@ -59,7 +59,8 @@ int launch_partition(int kw, const uint64_t *bases, const uint32_t *mask, uint64
                      uint32_t rcap, void *recs, uint64_t *bstat /* [P]: records | k-mers << 32 */, uint64_t *counters, cudaStream_t st);
 // seg_off / seg_cnt (nullable): explicit record segments (sharded path); null = segment i is local bucket region i
 int launch_count_buckets(int kw, const void *recs, const uint64_t *bstat, uint32_t rcap, const uint64_t *seg_off,
-                         const uint32_t *seg_cnt, const uint32_t *group_start,
+                         const uint32_t *seg_cnt, void *uq_rec /* nullable: per-CTA distinct-record lists (de-dup) */,
+                         uint32_t *uq_cnt, uint32_t uq_cap, const uint32_t *group_start,
                          uint32_t g_begin, uint32_t g_end, uint32_t *next_group, int k, int min_count, void *ovf_slots,
                          uint64_t ovf_cap, uint32_t *ovf_flag, uint64_t *histo, uint64_t *node_lo, uint64_t *node_hi,
                          uint16_t *node_count, uint8_t *node_raw, uint32_t node_cap, uint32_t *n_nodes,
