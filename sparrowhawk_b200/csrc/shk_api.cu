@@ -225,7 +225,7 @@ static shk_status count_groups(shk_asm *h, const std::vector<uint32_t> &gs, uint
       uq_cap = (uint32_t)std::max<uint64_t>(uq_cap, r);
     }
     uq_cap = (uq_cap + 63u) & ~63u;
-    const size_t ctas = (size_t)sm_count();
+    const size_t ctas = (size_t)count_ctas();
     SHK_TRY(h->uq_rec.ensure(ctas * uq_cap * 16 + 16)); SHK_TRY(h->uq_cnt.ensure(ctas * uq_cap * 4 + 16));
   }
   h->st.gpu_launches += launch_count_buckets(h->kw, sh ? h->recv_recs : h->skrecs.p, h->bfill.as<uint64_t>(), h->rcap,

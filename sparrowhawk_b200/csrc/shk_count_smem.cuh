@@ -9,14 +9,17 @@
 
 namespace shk {
 
-#define SHK_CB_THREADS 1024
+#ifndef SHK_CB_THREADS
+#define SHK_CB_THREADS 1024           // 512 = two half-size CTAs per SM: measured no faster on B200 (r01), kept as a build knob
+#endif
+#define SHK_CB_PER_SM (1024 / SHK_CB_THREADS)
 #define SHK_CB_WARPS (SHK_CB_THREADS / 32)
 #define SHK_CB_MAXC 256           // record segments per group (planner splits larger groups)
 #define SHK_CB_MAXPROBE 96
 
 template <int KW> struct CbCfg;
-template <> struct CbCfg<1> { static const int NS = 16384; static const int KEYB = 8;  static const int RECW = 1; };
-template <> struct CbCfg<2> { static const int NS = 9216;  static const int KEYB = 16; static const int RECW = 2; };
+template <> struct CbCfg<1> { static const int NS = 16384 / SHK_CB_PER_SM; static const int KEYB = 8;  static const int RECW = 1; };
+template <> struct CbCfg<2> { static const int NS = 9216 / SHK_CB_PER_SM - (SHK_CB_PER_SM > 1 ? 64 : 0); static const int KEYB = 16; static const int RECW = 2; };
 
 template <int KW> __host__ __device__ constexpr size_t cb_smem_bytes() {
   return (size_t)CbCfg<KW>::NS * (CbCfg<KW>::KEYB + 4)            // keys + vals
@@ -115,7 +118,7 @@ __device__ __forceinline__ void kmer_at(const u32 *rw, int i, int k, u128 &fwd, 
 // instances vanish this way (31 % at 30x still 63 %); the result is identical
 // because a record's content fully determines its (canonical k-mer, edge) pairs and
 // those are strand-symmetric.
-#define SHK_RT_SLOTS 8192            // record-table slots (16 B key + 4 B count, time-shares the k-mer table's memory)
+#define SHK_RT_SLOTS (8192 / SHK_CB_PER_SM)            // record-table slots (16 B key + 4 B count, time-shares the k-mer table's memory)
 #define SHK_RT_MAXPROBE 32
 
 __device__ __forceinline__ uint4 canon_record(uint4 r, int k) {
@@ -164,7 +167,7 @@ struct CountOut {
 };
 
 template <int KW, bool DEDUP>
-__global__ void __launch_bounds__(SHK_CB_THREADS, 1)
+__global__ void __launch_bounds__(SHK_CB_THREADS, SHK_CB_PER_SM)
 k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__restrict__ bstat, u32 rcap,
                 const u64 *__restrict__ seg_off, const u32 *__restrict__ seg_cnt,
                 uint4 *__restrict__ uq_rec, u32 *__restrict__ uq_cnt, u32 uq_cap /* distinct-record list, per CTA */,

@@ -689,6 +689,7 @@ size_t record_bytes(int kw) { return kw == 1 ? 16 : 32; }
 int records_max_run(int kw, int k) { return rec_max_run(kw, k); }
 int count_table_slots(int kw) { return kw == 1 ? CbCfg<1>::NS : CbCfg<2>::NS; }
 int count_max_group() { return SHK_CB_MAXC; }
+int count_ctas() { return sm_count() * SHK_CB_PER_SM; }
 
 int launch_partition(int kw, const uint64_t *bases, const uint32_t *mask, uint64_t nwords, int k, uint32_t P,
                      uint32_t rcap, void *recs, uint64_t *bstat, uint64_t *counters, cudaStream_t st) {
@@ -715,7 +716,7 @@ int launch_count_buckets(int kw, const void *recs, const uint64_t *bstat, uint32
     cudaFuncSetAttribute(k_count_buckets<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cb_smem_bytes<2>());
     attr_set = true;
   }
-  unsigned grid = (unsigned)sm_count();
+  unsigned grid = (unsigned)sm_count() * SHK_CB_PER_SM;
   if (grid > g_end - g_begin) grid = g_end - g_begin;
   u32 mp = (u32)(ovf_cap < 4096 ? ovf_cap : 4096);
   CountOut out{(u64 *)histo, (u64 *)node_lo, (u64 *)node_hi, node_count, node_raw, node_cap, n_nodes, (u64 *)counters};
