@@ -122,7 +122,7 @@ __device__ __forceinline__ void window_min_pow2(const u32 *row, u32 (&R)[32]) {
 }
 
 template <int KW>
-__global__ void __launch_bounds__(SHK_PT_THREADS, 2)
+__global__ void __launch_bounds__(SHK_PT_THREADS, 3)
 k_minimizer_partition(const u64 *__restrict__ bases, const u32 *__restrict__ mask, u64 nwords, int k, u32 P,
                       u32 rcap, typename RecOf<KW>::type *__restrict__ recs, u64 *__restrict__ bstat /* [P] records | kmers << 32 */,
                       u64 *__restrict__ counters /* [1] n_instances */) {

@@ -44,16 +44,21 @@ __device__ __forceinline__ bool rank_is_head(const u32 *succ, const uint8_t *cir
 __global__ void __launch_bounds__(256)
 k_rank_mark(const u32 *__restrict__ succ, const uint8_t *__restrict__ circ, u32 n_elems, u32 *__restrict__ splitters,
             u32 *__restrict__ n_splitters) {
+  __shared__ u32 wcnt[8], cta_base;
   const u32 e = blockIdx.x * blockDim.x + threadIdx.x;
-  const int lane = threadIdx.x & 31;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   bool sp = false;
   if (e < n_elems) sp = rank_hash_splitter(e) || rank_is_head(succ, circ, e);
   const u32 ball = __ballot_sync(0xffffffffu, sp);
-  if (!ball) return;
-  u32 base = 0;
-  if (lane == 0) base = atomicAdd(n_splitters, (u32)__popc(ball));
-  base = __shfl_sync(0xffffffffu, base, 0);
-  if (sp) splitters[base + __popc(ball & ((1u << lane) - 1))] = e;
+  if (lane == 0) wcnt[warp] = __popc(ball);
+  __syncthreads();
+  if (threadIdx.x == 0) {                       // one global atomic per CTA, not per warp
+    u32 t = 0;
+    for (int i = 0; i < 8; ++i) { const u32 c = wcnt[i]; wcnt[i] = t; t += c; }
+    cta_base = t ? atomicAdd(n_splitters, t) : 0;
+  }
+  __syncthreads();
+  if (sp) splitters[cta_base + wcnt[warp] + __popc(ball & ((1u << lane) - 1))] = e;
 }
 
 // per splitter: walk to the next splitter.  loc[e] = splitter index << 32 | local rank.
