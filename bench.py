@@ -253,16 +253,25 @@ def main():
     # ---- end-to-end arm: host buffers through the reference-facing calls ----
     e2e = None
     if not args.no_e2e:
+        call_ms = {"preprocess": [], "preprocessing_info": [], "assemble": [], "get_assembly": []}
+
         def e2e_step():
+            t = [time.perf_counter()]
             if world == 1:
                 h.preprocess_reads(seq, qual)
-                info = h.get_preprocessing_info()
             else:                       # sharded form of preprocess(): H2D + K0 of this rank's reads, then the exchange
                 h.load_reads_ptr(pin_seq.data_ptr(), pin_qual.data_ptr(), nbytes)
                 sharded_run(eng)
-                info = h.get_preprocessing_info()
+            t.append(time.perf_counter())
+            info = h.get_preprocessing_info()
+            t.append(time.perf_counter())
             h.assemble()
-            return info, h.get_assembly()
+            t.append(time.perf_counter())
+            res = h.get_assembly()
+            t.append(time.perf_counter())
+            for name, a, b in zip(call_ms, t[:-1], t[1:]):
+                call_ms[name].append((b - a) * 1e3)
+            return info, res
         e2e_step()
         barrier()
         t0 = time.perf_counter()
@@ -283,6 +292,7 @@ def main():
                  "shk_load_reads + sharded_run (shk_shard_* + NCCL) + shk_asm_preprocessing_info + shk_asm_assemble + shk_asm_get_assembly")
         e2e = {"value": bases * world / (ms_e2e * 1e-3), "unit": "bases/s", "h2d_bytes_per_step": int(2 * nbytes) * world,
                "d2h_bytes_per_step": d2h * world, "ms_per_step": ms_e2e, "calls": calls,
+               "call_ms": {n: round(sum(v[1:]) / max(1, len(v) - 1), 3) for n, v in call_ms.items()},
                "ncontigs": json.loads(res)["ncontigs"], "nkmers": json.loads(info)["nkmers"]}
 
     # ---- roofline of the dominant kernel (K1b k_count_buckets) ----------------

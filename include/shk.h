@@ -197,6 +197,42 @@ shk_status shk_export_links(shk_asm *h, uint32_t *from, uint32_t *to, size_t cap
                             size_t *n);
 
 /* ------------------------------------------------------------------ */
+/* Host graph cleaning: what runs between          */
+/* "assembly:correct_graph" and "assembly:collapse_graph"              */
+/* (AssemblyPage.vue:598-603) — dead-end removal and simple bubble     */
+/* collapse on the unitig graph, then re-compaction into contigs.      */
+/* Pure host code (no device needed): a host that keeps its own        */
+/* cleaning simply does not call it.  Flags as in AssemblyHelper.new   */
+/* (Assembler.ts:25-27, docs/src/assembly.md:19-20).  Rules: see       */
+/* csrc/shk_clean.cpp.                                                 */
+/* ------------------------------------------------------------------ */
+typedef struct shk_contigs shk_contigs; /* opaque: contigs + links */
+
+/* Input = the arrays of shk_export_unitigs / shk_export_links, with the sum of
+ * k-mer counts per unitig instead of the mean (shk_export_unitig_counts). */
+shk_status shk_clean_graph(int k, const char *seq, const uint64_t *offsets,
+                           const uint64_t *kmer_count_sum, const uint8_t *circular,
+                           size_t n_unitigs, const uint32_t *link_from,
+                           const uint32_t *link_to, size_t n_links,
+                           int no_dead_end_removal, int no_bubble_collapse,
+                           shk_contigs **out);
+shk_status shk_contigs_sizes(const shk_contigs *c, size_t *n_contigs, size_t *n_bases,
+                             size_t *n_links, size_t *n_tips_removed,
+                             size_t *n_bubbles_removed);
+/* Any pointer may be NULL.  offsets has n_contigs+1 entries; links as in
+ * shk_export_links (contig id * 2 + orientation). */
+shk_status shk_contigs_export(const shk_contigs *c, char *seq, uint64_t *offsets,
+                              uint64_t *kmer_count_sum, uint8_t *circular,
+                              uint32_t *link_from, uint32_t *link_to);
+void shk_contigs_free(shk_contigs *c);
+/* Sum of k-mer counts per unitig (exact; mean_cov of shk_export_unitigs is this
+ * divided by the number of k-mers). */
+shk_status shk_export_unitig_counts(shk_asm *h, uint64_t *kmer_count_sum, size_t unitig_cap);
+/* The cleaned graph of the last shk_asm_assemble (owned by the handle; valid
+ * until the next assemble / free). */
+shk_status shk_asm_contigs(shk_asm *h, const shk_contigs **out);
+
+/* ------------------------------------------------------------------ */
 /* Sharded path API (one 8xB200 box; SURVEY §8e, north_star: "reads   */
 /* shard evenly across GPUs and k-mers route to an owner GPU by hash   */
 /* range through an NCCL all-to-all").  One handle per rank / GPU.     */

@@ -154,3 +154,235 @@ def unitigs(nodes, edges, k):
         sq = path[0] + "".join(p[-1] for p in path[1:])
         out.append(min(sq, rc_str(sq)))
     return sorted(out)
+
+
+# ---------------------------------------------------------------------------
+# Unitig links and host graph cleaning, restated on strings.
+# Independent of csrc/shk_clean.cpp: oriented strings, dicts and sets, no end ids.
+# ---------------------------------------------------------------------------
+def unitig_links(units, edges, k):
+    """units: list of unitig strings (any orientation); edges: set of validated
+    (k+1)-mers (either strand).  -> set of (a, oa, b, ob): reading unitig a in
+    orientation oa (1 = reverse complement) runs into unitig b in orientation ob."""
+    Efull = set(edges) | {rc_str(e) for e in edges}
+    first = {}
+    for i, u in enumerate(units):
+        for o, s in ((0, u), (1, rc_str(u))):
+            first.setdefault(s[:k], []).append((i, o))
+    out = set()
+    for i, u in enumerate(units):
+        for o, s in ((0, u), (1, rc_str(u))):
+            last = s[-k:]
+            for b in "ACGT":
+                if last + b in Efull:
+                    for (j, oj) in first.get(last[1:] + b, []):
+                        # the edge inside a unitig is not a link; the closing edge of a cycle is
+                        out.add((i, o, j, oj))
+    return out
+
+
+def _key(seq, kc, k):
+    from fractions import Fraction
+    nk = len(seq) - k + 1
+    return (Fraction(kc, nk), nk, min(seq, rc_str(seq)))
+
+
+def _rot_min(s, k):
+    """linear form of a circular contig, started at its minimum canonical k-mer (S14)."""
+    n = len(s) - k + 1
+    circle = s[:n]
+    best = None
+    for strand, c in ((0, circle), (1, rc_str(circle))):
+        ext = (c * (k // n + 2))
+        for i in range(n):
+            km = ext[i:i + k]
+            v = enc(km)
+            if best is None or v < best[0]:
+                best = (v, strand, i)
+    _, strand, i = best
+    c = circle if strand == 0 else rc_str(circle)
+    ext = c * ((n + k) // n + 2)
+    return ext[i:i + n + k - 1]
+
+
+def clean_graph(units, kcs, circs, links, k, tips=True, bubbles=True):
+    """units/kcs/circs: unitig strings, k-mer count sums, circular flags;
+    links: iterable of (a, oa, b, ob).  Returns (contigs, links) with contigs a
+    list of (canonical seq, kc, circ) and links a set of (canon_a, oa, canon_b, ob)
+    relative to the canonical strings — the comparison form of the tests."""
+    # a node is an oriented string pair; identity = integer id, state in dicts
+    seq = {i: s for i, s in enumerate(units)}
+    kc = {i: int(c) for i, c in enumerate(kcs)}
+    circ = {i: bool(c) for i, c in enumerate(circs)}
+    nxt = [len(units)]
+    # succ[(a, oa)] = set of (b, ob); kept symmetric: (b, 1-ob) -> (a, 1-oa)
+    succ = {}
+
+    def add(a, oa, b, ob):
+        succ.setdefault((a, oa), set()).add((b, ob))
+        succ.setdefault((b, 1 - ob), set()).add((a, 1 - oa))
+
+    for (a, oa, b, ob) in links:
+        add(int(a), int(oa), int(b), int(ob))
+
+    def out(a, oa):
+        return succ.get((a, oa), set())
+
+    def ori(a, oa):
+        return seq[a] if oa == 0 else rc_str(seq[a])
+
+    def drop(dead):
+        for d in dead:
+            del seq[d], kc[d], circ[d]
+        for key in list(succ):
+            if key[0] in dead:
+                del succ[key]
+            else:
+                succ[key] = {t for t in succ[key] if t[0] not in dead}
+
+    def compact():
+        def unique_next(a, oa):
+            o = out(a, oa)
+            if len(o) != 1:
+                return None
+            (b, ob), = o
+            if b == a or len(out(b, 1 - ob)) != 1:
+                return None
+            return (b, ob)
+
+        done, new = set(), []
+        for a in sorted(seq):
+            if a in done:
+                continue
+            # walk back
+            cur, ring = (a, 1), False
+            while True:
+                n = unique_next(*cur)
+                if n is None:
+                    break
+                cur = n
+                if cur[0] == a:
+                    ring = True
+                    break
+            start = (a, 0) if ring else (cur[0], 1 - cur[1])
+            chain, cur = [start], start
+            while True:
+                n = unique_next(*cur)
+                if n is None or n[0] == start[0]:
+                    break
+                chain.append(n)
+                cur = n
+            for c in chain:
+                done.add(c[0])
+            if len(chain) > 1:
+                new.append((chain, ring))
+        if not new:
+            return
+        for chain, ring in new:
+            s = ori(*chain[0])
+            for c in chain[1:]:
+                s += ori(*c)[k - 1:]
+            if ring:
+                s = _rot_min(s, k)
+            nid = nxt[0]
+            nxt[0] += 1
+            tot = sum(kc[c[0]] for c in chain)
+            first, last = chain[0], chain[-1]
+            outs = set() if ring else set(out(*last))
+            ins = set() if ring else set(out(first[0], 1 - first[1]))
+            members = {c[0] for c in chain}
+            drop(members)
+            seq[nid], kc[nid], circ[nid] = s, tot, ring
+            if ring:
+                add(nid, 0, nid, 0)
+            else:
+                for (b, ob) in outs:
+                    if b in members:            # cannot happen for a maximal chain
+                        continue
+                    add(nid, 0, b, ob)
+                for (b, ob) in ins:
+                    if b in members:
+                        continue
+                    add(nid, 1, b, ob)
+
+    def is_tip(a):
+        if circ[a] or len(seq[a]) >= 2 * k:
+            return False
+        return (len(out(a, 0)) == 0) != (len(out(a, 1)) == 0)
+
+    def tip_round():
+        tipset = {a for a in seq if is_tip(a)}
+        dead = set()
+        for a in tipset:
+            oa = 0 if out(a, 0) else 1          # orientation that leaves through the attached end
+            ka = _key(seq[a], kc[a], k)
+            hit = False
+            for (b, ob) in out(a, oa):
+                # other branches arriving at the same end of b: everything b reaches going back
+                for (c, oc) in out(b, 1 - ob):
+                    if c == a:
+                        continue
+                    if c not in tipset or _key(seq[c], kc[c], k) > ka:
+                        hit = True
+            if hit:
+                dead.add(a)
+        drop(dead)
+        return len(dead)
+
+    def bubble_round():
+        dead = set()
+        for a in sorted(seq):
+            if circ[a] or len(seq[a]) - k + 1 > 2 * k:
+                continue
+            if len(out(a, 0)) != 1 or len(out(a, 1)) != 1:
+                continue
+            (t, ot), = out(a, 0)                # a runs into t
+            (s_, os_), = out(a, 1)              # reverse of a runs into s_
+            if t == a or s_ == a or (t, ot) == (s_, os_):
+                continue
+            into_t = out(t, 1 - ot)             # who else arrives at that end of t
+            into_s = out(s_, 1 - os_)
+            if len(into_t) != 2 or len(into_s) != 2:
+                continue
+            (b, ob1), = {x for x in into_t if x != (a, 1)}      # b reversed-arrival form
+            if b == a or b in (t, s_) or circ[b] or len(seq[b]) - k + 1 > 2 * k:
+                continue
+            if len(out(b, 0)) != 1 or len(out(b, 1)) != 1:
+                continue
+            # b leaves towards t in orientation 1-ob1 and towards s_ in orientation ob1
+            if out(b, 1 - ob1) != {(t, ot)} or out(b, ob1) != {(s_, os_)}:
+                continue
+            lo = a if _key(seq[a], kc[a], k) < _key(seq[b], kc[b], k) else b
+            dead.add(lo)
+        drop(dead)
+        return len(dead)
+
+    compact()
+    while True:
+        removed = 0
+        if tips:
+            r = tip_round()
+            removed += r
+            if r:
+                compact()
+        if bubbles:
+            r = bubble_round()
+            removed += r
+            if r:
+                compact()
+        if not removed:
+            break
+
+    def canon_o(a, oa):
+        s = seq[a]
+        r = rc_str(s)
+        return (s, oa) if s <= r else (r, 1 - oa)
+
+    contigs = sorted((min(seq[a], rc_str(seq[a])), kc[a], circ[a]) for a in seq)
+    lk = set()
+    for (a, oa), tgt in succ.items():
+        for (b, ob) in tgt:
+            ca, coa = canon_o(a, oa)
+            cb, cob = canon_o(b, ob)
+            lk.add((ca, coa, cb, cob))
+    return contigs, lk

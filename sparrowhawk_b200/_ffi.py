@@ -70,6 +70,14 @@ SYMBOLS = {
                                    C.POINTER(C.c_size_t)]),
     "shk_export_unitigs": (C.c_int, [_H, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]),
     "shk_export_links": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]),
+    # host graph cleaning
+    "shk_clean_graph": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p,
+                                  C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.POINTER(_H)]),
+    "shk_contigs_sizes": (C.c_int, [_H] + [C.POINTER(C.c_size_t)] * 5),
+    "shk_contigs_export": (C.c_int, [_H] + [C.c_void_p] * 6),
+    "shk_contigs_free": (None, [_H]),
+    "shk_export_unitig_counts": (C.c_int, [_H, C.c_void_p, C.c_size_t]),
+    "shk_asm_contigs": (C.c_int, [_H, C.POINTER(_H)]),
     # sharded path
     "shk_shard_buckets": (C.c_uint32, [C.c_uint64, C.c_int]),
     "shk_record_bytes": (C.c_size_t, [C.c_int]),

@@ -29,6 +29,39 @@ def _buf(a):
     raise TypeError(f"unsupported buffer type {type(a)}")
 
 
+def _read_contigs(lib, c):
+    n, nb, nl, nt, nbub = (C.c_size_t() for _ in range(5))
+    check(lib.shk_contigs_sizes(c, C.byref(n), C.byref(nb), C.byref(nl), C.byref(nt), C.byref(nbub)))
+    seq = np.zeros(max(nb.value, 1), np.uint8); off = np.zeros(n.value + 1, np.uint64)
+    kc = np.zeros(max(n.value, 1), np.uint64); circ = np.zeros(max(n.value, 1), np.uint8)
+    lf = np.zeros(max(nl.value, 1), np.uint32); lt = np.zeros(max(nl.value, 1), np.uint32)
+    check(lib.shk_contigs_export(c, seq.ctypes.data, off.ctypes.data, kc.ctypes.data, circ.ctypes.data,
+                                 lf.ctypes.data, lt.ctypes.data))
+    s = seq[:nb.value].tobytes().decode()
+    seqs = [s[int(off[i]):int(off[i + 1])] for i in range(n.value)]
+    return {"seq": seqs, "kc": [int(x) for x in kc[:n.value]], "circ": [int(x) for x in circ[:n.value]],
+            "link_from": lf[:nl.value].copy(), "link_to": lt[:nl.value].copy(),
+            "tips_removed": nt.value, "bubbles_removed": nbub.value}
+
+
+def clean_graph(k, seqs, kc, circ, link_from, link_to, no_dead_end_removal=False, no_bubble_collapse=False):
+    """Host graph cleaning of include/shk.h (shk_clean_graph) on plain arrays; needs no device."""
+    lib = _ffi.lib()
+    blob = "".join(seqs).encode()
+    off = np.zeros(len(seqs) + 1, np.uint64)
+    off[1:] = np.cumsum([len(s) for s in seqs], dtype=np.uint64)
+    kc = np.ascontiguousarray(kc, np.uint64); circ = np.ascontiguousarray(circ, np.uint8)
+    lf = np.ascontiguousarray(link_from, np.uint32); lt = np.ascontiguousarray(link_to, np.uint32)
+    c = C.c_void_p()
+    check(lib.shk_clean_graph(int(k), blob, off.ctypes.data, kc.ctypes.data, circ.ctypes.data, len(seqs),
+                              lf.ctypes.data, lt.ctypes.data, len(lf), int(no_dead_end_removal),
+                              int(no_bubble_collapse), C.byref(c)))
+    try:
+        return _read_contigs(lib, c)
+    finally:
+        lib.shk_contigs_free(c)
+
+
 class AssemblyHelper:
     def __init__(self, k=31, verbose=False, min_count=5, min_qual=20, chunk_size=0, do_bloom=False,
                  do_fit=False, no_bubble_collapse=False, no_dead_end_removal=False, *, device=-1,
@@ -173,6 +206,18 @@ class AssemblyHelper:
         got = C.c_size_t()
         check(self._lib.shk_export_links(self._h, a.ctypes.data, b.ctypes.data, n, C.byref(got)))
         return a[:n], b[:n]
+
+    def export_unitig_counts(self):
+        nu = self.stats()["n_unitigs"]
+        kc = np.zeros(max(nu, 1), np.uint64)
+        check(self._lib.shk_export_unitig_counts(self._h, kc.ctypes.data, nu))
+        return kc[:nu]
+
+    def contigs(self):
+        """cleaned graph of the last assemble(): (seqs, kmer_count_sums, circular, link_from, link_to)"""
+        c = C.c_void_p()
+        check(self._lib.shk_asm_contigs(self._h, C.byref(c)))
+        return _read_contigs(self._lib, c)
 
     # convenience: parsed results like Assembler.ts:109-118 / 127-137
     def preprocessing_result(self) -> dict:

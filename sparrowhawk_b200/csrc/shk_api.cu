@@ -526,6 +526,7 @@ shk_status shk_asm_new(const shk_params *params, shk_asm **out) {
 
 void shk_asm_free(shk_asm *h) {
   if (!h) return;
+  if (h->contigs) { shk_contigs_free(h->contigs); h->contigs = nullptr; }
   if (h->dev >= 0) {
     cudaSetDevice(h->dev);
     if (h->stream) cudaStreamSynchronize(h->stream);
@@ -622,7 +623,7 @@ shk_status fetch_unitigs(shk_asm *h) {
   HostUnitigs &u = h->hu;
   size_t nu = h->st.n_unitigs, k = (size_t)h->p.k;
   u.seq.assign(h->st.unitig_bases, 0); u.off.assign(nu + 1, 0); u.cov.assign(nu, 0.f); u.circ.assign(nu, 0);
-  u.link_from.assign(h->st.n_links, 0); u.link_to.assign(h->st.n_links, 0);
+  u.link_from.assign(h->st.n_links, 0); u.link_to.assign(h->st.n_links, 0); u.kc.assign(nu, 0);
   if (nu) {
     struct Rec { uint32_t head, len; uint64_t off; };
     std::vector<Rec> recs(nu); std::vector<uint64_t> cs(nu); std::vector<char> raw(h->st.unitig_bases);
@@ -641,6 +642,7 @@ shk_status fetch_unitigs(shk_asm *h) {
       u.off[i] = p;
       memcpy(u.seq.data() + p, raw.data() + recs[i].off, len);
       u.cov[i] = (float)((double)cs[i] / (double)recs[i].len);
+      u.kc[i] = cs[i];
       p += len;
     }
     u.off[nu] = p;
@@ -661,6 +663,21 @@ shk_status shk_export_unitigs(shk_asm *h, char *seq, size_t seq_cap, uint64_t *o
   if (offsets) memcpy(offsets, u.off.data(), (nu + 1) * 8);
   if (mean_cov && nu) memcpy(mean_cov, u.cov.data(), nu * 4);
   if (circular && nu) memcpy(circular, u.circ.data(), nu);
+  return SHK_OK;
+}
+
+shk_status shk_export_unitig_counts(shk_asm *h, uint64_t *kmer_count_sum, size_t unitig_cap) {
+  SHK_TRY(fetch_unitigs(h));
+  const size_t nu = h->hu.kc.size();
+  if (unitig_cap < nu || (nu && !kmer_count_sum)) { set_error("export buffer too small"); return SHK_ERR_BAD_ARG; }
+  if (nu) memcpy(kmer_count_sum, h->hu.kc.data(), nu * 8);
+  return SHK_OK;
+}
+
+shk_status shk_asm_contigs(shk_asm *h, const shk_contigs **out) {
+  if (!h || !out) { set_error("null argument"); return SHK_ERR_BAD_ARG; }
+  if (!h->contigs) { set_error("contigs before assemble"); return SHK_ERR_STATE; }
+  *out = h->contigs;
   return SHK_OK;
 }
 

@@ -45,10 +45,28 @@ struct HostUnitigs {
   std::vector<float> cov;
   std::vector<uint8_t> circ;
   std::vector<uint32_t> link_from, link_to;
+  std::vector<uint64_t> kc;           // sum of the k-mer counts of each unitig
   bool valid = false;
 };
 
+// Result of the host graph cleaning (shk_clean.cpp): contigs + their links.
+struct CleanGraph {
+  std::vector<std::string> seq;
+  std::vector<uint64_t> kc;           // sum of k-mer counts (mean coverage = kc / (len - k + 1))
+  std::vector<uint8_t> circ;
+  std::vector<uint32_t> link_from, link_to;   // contig id * 2 + orientation, both directions present
+  size_t n_tips = 0, n_bubbles = 0, rounds = 0;
+};
+void clean_unitig_graph(int k, const char *seq, const uint64_t *off, const uint64_t *kc, const uint8_t *circ, size_t n,
+                        const uint32_t *lf, const uint32_t *lt, size_t nl, bool tips, bool bubbles, CleanGraph &out);
+std::string revcomp_string(const std::string &s);
+bool revcomp_is_smaller(const char *s, size_t n);
+
 }  // namespace shk
+
+struct shk_contigs {
+  shk::CleanGraph g;
+};
 
 struct shk_asm {
   shk_params p;
@@ -100,6 +118,7 @@ struct shk_asm {
   uint64_t histo[SHK_HISTO_BINS];
   bool counted = false, filtered = false, graphed = false, histo_valid = false;
   shk::HostUnitigs hu;
+  shk_contigs *contigs = nullptr;     // cleaned graph of the last assemble()
   std::string json_pre, json_asm;
 
   // ---- FASTQ streaming parser (shk_asm_preprocess_push) ----

@@ -143,118 +143,124 @@ int fit_min_count(const uint64_t *histo, int fallback) {
 }
 
 // ---------------------------------------------------------------------------
-// Writers.  Contigs are reported in a canonical, schedule-independent form:
-// each sequence flipped to min(seq, revcomp), sorted by (length desc, seq).
+// Cleaning + writers.  assemble() runs the host cleaning (shk_clean.cpp) on the
+// GPU-built unitig graph, then reports the contigs in a canonical,
+// schedule-independent form: each sequence flipped to min(seq, revcomp), sorted by
+// (length desc, seq); contig_<i> of the FASTA is contig id i-1 of shk_asm_contigs.
 // Text layouts are [DECISION]s (the reference writers are in the absent crate;
 // SURVEY §8b "exact textual layout … unpinned"); the JSON keys are the
-// reference's (Assembler.ts:7-13).
+// reference's (Assembler.ts:7-13).  The four texts are written straight into the
+// JSON string in escaped form (sequences are plain ACGT and need no escaping).
 // ---------------------------------------------------------------------------
-static std::string revcomp_str(const char *s, size_t n) {
-  std::string r(n, 'N');
-  for (size_t i = 0; i < n; ++i) {
-    char c = s[n - 1 - i];
-    r[i] = c == 'A' ? 'T' : c == 'C' ? 'G' : c == 'G' ? 'C' : c == 'T' ? 'A' : 'N';
-  }
-  return r;
-}
-
-static void json_escape_into(std::string &out, const std::string &s) {
-  out.reserve(out.size() + s.size() + s.size() / 32 + 2);
-  for (char c : s) {
-    switch (c) {
+static void json_escape_into(std::string &out, const char *s) {
+  for (; *s; ++s) {
+    switch (*s) {
       case '"': out += "\\\""; break;
       case '\\': out += "\\\\"; break;
       case '\n': out += "\\n"; break;
       case '\t': out += "\\t"; break;
       case '\r': out += "\\r"; break;
-      default: out += c;
+      default: out += *s;
     }
   }
 }
 
-struct Contig { std::string seq; float cov; bool circ; uint32_t src; bool flipped; };
+// canonical orientation + canonical order, applied to the cleaned graph in place
+static void canonicalise(CleanGraph &g) {
+  const size_t n = g.seq.size();
+  std::vector<uint8_t> flipped(n, 0);
+  for (size_t i = 0; i < n; ++i)
+    if (revcomp_is_smaller(g.seq[i].data(), g.seq[i].size())) { g.seq[i] = revcomp_string(g.seq[i]); flipped[i] = 1; }
+  std::vector<uint32_t> order(n);
+  std::iota(order.begin(), order.end(), 0u);
+  std::sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) {
+    if (g.seq[a].size() != g.seq[b].size()) return g.seq[a].size() > g.seq[b].size();
+    return g.seq[a] < g.seq[b];
+  });
+  std::vector<uint32_t> newid(n);
+  for (size_t i = 0; i < n; ++i) newid[order[i]] = (uint32_t)i;
+  std::vector<std::string> seq(n); std::vector<uint64_t> kc(n); std::vector<uint8_t> circ(n);
+  for (size_t i = 0; i < n; ++i) { seq[i] = std::move(g.seq[order[i]]); kc[i] = g.kc[order[i]]; circ[i] = g.circ[order[i]]; }
+  g.seq.swap(seq); g.kc.swap(kc); g.circ.swap(circ);
+  // links in the new naming, sorted, unique (u+ -> v+ and v- -> u- are both kept: shk_export_links form)
+  std::vector<std::pair<uint32_t, uint32_t>> lk(g.link_from.size());
+  for (size_t i = 0; i < lk.size(); ++i) {
+    const uint32_t f = g.link_from[i], t = g.link_to[i];
+    lk[i] = {2 * newid[f >> 1] + ((f & 1u) ^ flipped[f >> 1]), 2 * newid[t >> 1] + ((t & 1u) ^ flipped[t >> 1])};
+  }
+  std::sort(lk.begin(), lk.end());
+  lk.erase(std::unique(lk.begin(), lk.end()), lk.end());
+  g.link_from.resize(lk.size()); g.link_to.resize(lk.size());
+  for (size_t i = 0; i < lk.size(); ++i) { g.link_from[i] = lk[i].first; g.link_to[i] = lk[i].second; }
+}
 
 shk_status build_assembly_json(shk_asm *h) {
   const HostUnitigs &u = h->hu;
-  const size_t nu = u.cov.size();
   const int k = h->p.k;
   progress(h, "assembly:correct_graph");
-  // Host graph cleaning (dead ends, bubbles) consumes the unitig graph; see
-  // shk_clean.cpp once present.  Flags: no_dead_end_removal, no_bubble_collapse.
+  if (!h->contigs) {
+    h->contigs = new (std::nothrow) shk_contigs();
+    if (!h->contigs) { set_error("out of host memory"); return SHK_ERR_OOM; }
+  }
+  CleanGraph &g = h->contigs->g;
+  clean_unitig_graph(k, u.seq.data(), u.off.data(), u.kc.data(), u.circ.data(), u.kc.size(), u.link_from.data(),
+                     u.link_to.data(), u.link_from.size(), !h->p.no_dead_end_removal, !h->p.no_bubble_collapse, g);
   progress(h, "assembly:collapse_graph");
-  std::vector<Contig> cs(nu);
-  for (size_t i = 0; i < nu; ++i) {
-    const char *s = u.seq.data() + u.off[i];
-    size_t len = (size_t)(u.off[i + 1] - u.off[i]);
-    std::string f(s, len), r = revcomp_str(s, len);
-    bool flip = r < f;
-    cs[i] = Contig{flip ? r : f, u.cov[i], u.circ[i] != 0, (uint32_t)i, flip};
-  }
-  std::vector<uint32_t> order(nu);
-  std::iota(order.begin(), order.end(), 0u);
-  std::sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) {
-    if (cs[a].seq.size() != cs[b].seq.size()) return cs[a].seq.size() > cs[b].seq.size();
-    return cs[a].seq < cs[b].seq;
-  });
-  std::vector<uint32_t> newid(nu);
-  for (size_t i = 0; i < nu; ++i) newid[order[i]] = (uint32_t)i;
-  // links in the new naming, de-duplicated (u+ -> v+ is also reported as v- -> u-)
-  struct Lk { uint32_t a; int ao; uint32_t b; int bo; };
-  std::vector<Lk> links;
-  for (size_t i = 0; i < u.link_from.size(); ++i) {
-    uint32_t fu = u.link_from[i] >> 1, tu = u.link_to[i] >> 1;
-    int fo = (int)(u.link_from[i] & 1) ^ (cs[fu].flipped ? 1 : 0), to = (int)(u.link_to[i] & 1) ^ (cs[tu].flipped ? 1 : 0);
-    Lk a{newid[fu], fo, newid[tu], to}, b{newid[tu], to ^ 1, newid[fu], fo ^ 1};
-    auto key = [](const Lk &l) { return std::make_tuple(l.a, l.ao, l.b, l.bo); };
-    links.push_back(key(b) < key(a) ? b : a);
-  }
-  std::sort(links.begin(), links.end(), [](const Lk &x, const Lk &y) {
-    return std::make_tuple(x.a, x.ao, x.b, x.bo) < std::make_tuple(y.a, y.ao, y.b, y.bo);
-  });
-  links.erase(std::unique(links.begin(), links.end(), [](const Lk &x, const Lk &y) {
-    return x.a == y.a && x.ao == y.ao && x.b == y.b && x.bo == y.bo; }), links.end());
+  canonicalise(g);
+  const size_t nc = g.seq.size();
 
   progress(h, "assembly:saving");
-  std::string fasta, gfa, gfa2, dot;
+  size_t total = 0;
+  for (auto &s : g.seq) total += s.size();
+  std::string fasta, gfa, gfa2, dot;          // escaped JSON string bodies
+  fasta.reserve(total + nc * 64 + 64); gfa.reserve(total + nc * 96 + g.link_from.size() * 40 + 64);
+  gfa2.reserve(total + nc * 96 + g.link_from.size() * 72 + 64); dot.reserve(nc * 80 + g.link_from.size() * 40 + 64);
   char line[256];
-  gfa += "H\tVN:Z:1.0\n";
-  gfa2 += "H\tVN:Z:2.0\n";
-  dot += "digraph sparrowhawk {\n";
-  for (size_t i = 0; i < nu; ++i) {
-    const Contig &c = cs[order[i]];
-    size_t nk = c.seq.size() - (size_t)k + 1;                  // k-mers in the contig
-    snprintf(line, sizeof line, ">contig_%zu len=%zu cov=%.2f%s\n", i + 1, c.seq.size(), c.cov, c.circ ? " circular=true" : "");
-    fasta += line; fasta += c.seq; fasta += '\n';
-    snprintf(line, sizeof line, "S\t%zu\t", i + 1); gfa += line; gfa += c.seq;
-    snprintf(line, sizeof line, "\tLN:i:%zu\tKC:i:%llu\tdp:f:%.2f\n", c.seq.size(), (unsigned long long)(c.cov * (double)nk + 0.5), c.cov);
-    gfa += line;
-    snprintf(line, sizeof line, "S\t%zu\t%zu\t", i + 1, c.seq.size()); gfa2 += line; gfa2 += c.seq;
-    snprintf(line, sizeof line, "\tKC:i:%llu\n", (unsigned long long)(c.cov * (double)nk + 0.5)); gfa2 += line;
-    snprintf(line, sizeof line, "  %zu [label=\"contig_%zu len=%zu cov=%.2f\"];\n", i + 1, i + 1, c.seq.size(), c.cov);
-    dot += line;
+  json_escape_into(gfa, "H\tVN:Z:1.0\n");
+  json_escape_into(gfa2, "H\tVN:Z:2.0\n");
+  json_escape_into(dot, "digraph sparrowhawk {\n");
+  for (size_t i = 0; i < nc; ++i) {
+    const std::string &sq = g.seq[i];
+    const size_t nk = sq.size() - (size_t)k + 1;                 // k-mers in the contig
+    const double cov = (double)g.kc[i] / (double)nk;
+    snprintf(line, sizeof line, ">contig_%zu len=%zu cov=%.2f%s\n", i + 1, sq.size(), cov, g.circ[i] ? " circular=true" : "");
+    json_escape_into(fasta, line); fasta += sq; fasta += "\\n";
+    snprintf(line, sizeof line, "S\t%zu\t", i + 1); json_escape_into(gfa, line); gfa += sq;
+    snprintf(line, sizeof line, "\tLN:i:%zu\tKC:i:%llu\tdp:f:%.2f\n", sq.size(), (unsigned long long)g.kc[i], cov);
+    json_escape_into(gfa, line);
+    snprintf(line, sizeof line, "S\t%zu\t%zu\t", i + 1, sq.size()); json_escape_into(gfa2, line); gfa2 += sq;
+    snprintf(line, sizeof line, "\tKC:i:%llu\n", (unsigned long long)g.kc[i]); json_escape_into(gfa2, line);
+    snprintf(line, sizeof line, "  %zu [label=\"contig_%zu len=%zu cov=%.2f\"];\n", i + 1, i + 1, sq.size(), cov);
+    json_escape_into(dot, line);
   }
-  for (const Lk &l : links) {
-    snprintf(line, sizeof line, "L\t%u\t%c\t%u\t%c\t%dM\n", l.a + 1, l.ao ? '-' : '+', l.b + 1, l.bo ? '-' : '+', k - 1);
-    gfa += line;
+  for (size_t i = 0; i < g.link_from.size(); ++i) {
+    // each undirected join is stored in both directions; report the smaller of the two spellings once
+    const uint32_t f = g.link_from[i], t = g.link_to[i];
+    const uint32_t mf = t ^ 1u, mt = f ^ 1u;                      // the mirrored spelling
+    if (std::make_pair(mf, mt) < std::make_pair(f, t)) continue;
+    const uint32_t a = f >> 1, ao = f & 1u, b = t >> 1, bo = t & 1u;
+    snprintf(line, sizeof line, "L\t%u\t%c\t%u\t%c\t%dM\n", a + 1, ao ? '-' : '+', b + 1, bo ? '-' : '+', k - 1);
+    json_escape_into(gfa, line);
     // GFA2 edge: overlap of k-1 bases at the matching ends
-    size_t la = cs[order[l.a]].seq.size(), lb = cs[order[l.b]].seq.size();
-    size_t ab = l.ao ? 0 : la - (size_t)(k - 1), ae = l.ao ? (size_t)(k - 1) : la;
-    size_t bb = l.bo ? lb - (size_t)(k - 1) : 0, be = l.bo ? lb : (size_t)(k - 1);
-    snprintf(line, sizeof line, "E\t*\t%u%c\t%u%c\t%zu%s\t%zu%s\t%zu%s\t%zu%s\t%dM\n", l.a + 1, l.ao ? '-' : '+', l.b + 1,
-             l.bo ? '-' : '+', ab, ab == la ? "$" : "", ae, ae == la ? "$" : "", bb, bb == lb ? "$" : "", be,
+    const size_t la = g.seq[a].size(), lb = g.seq[b].size();
+    const size_t ab = ao ? 0 : la - (size_t)(k - 1), ae = ao ? (size_t)(k - 1) : la;
+    const size_t bb = bo ? lb - (size_t)(k - 1) : 0, be = bo ? lb : (size_t)(k - 1);
+    snprintf(line, sizeof line, "E\t*\t%u%c\t%u%c\t%zu%s\t%zu%s\t%zu%s\t%zu%s\t%dM\n", a + 1, ao ? '-' : '+', b + 1,
+             bo ? '-' : '+', ab, ab == la ? "$" : "", ae, ae == la ? "$" : "", bb, bb == lb ? "$" : "", be,
              be == lb ? "$" : "", k - 1);
-    gfa2 += line;
-    snprintf(line, sizeof line, "  %u -> %u [label=\"%c%c\"];\n", l.a + 1, l.b + 1, l.ao ? '-' : '+', l.bo ? '-' : '+');
-    dot += line;
+    json_escape_into(gfa2, line);
+    snprintf(line, sizeof line, "  %u -> %u [label=\"%c%c\"];\n", a + 1, b + 1, ao ? '-' : '+', bo ? '-' : '+');
+    json_escape_into(dot, line);
   }
-  dot += "}\n";
+  json_escape_into(dot, "}\n");
   std::string &j = h->json_asm;
   j.clear();
-  j += "{\"outfasta\":\""; json_escape_into(j, fasta);
-  j += "\",\"ncontigs\":" + std::to_string(nu);
-  j += ",\"outdot\":\""; json_escape_into(j, dot);
-  j += "\",\"outgfa\":\""; json_escape_into(j, gfa);
-  j += "\",\"outgfav2\":\""; json_escape_into(j, gfa2);
+  j.reserve(fasta.size() + gfa.size() + gfa2.size() + dot.size() + 128);
+  j += "{\"outfasta\":\""; j += fasta;
+  j += "\",\"ncontigs\":" + std::to_string(nc);
+  j += ",\"outdot\":\""; j += dot;
+  j += "\",\"outgfa\":\""; j += gfa;
+  j += "\",\"outgfav2\":\""; j += gfa2;
   j += "\"}";
   return SHK_OK;
 }

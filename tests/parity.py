@@ -82,3 +82,59 @@ def make_stream(reads, quals=None):
     else:
         qual = b"".join(q.encode() + b"\n" for q in quals)
     return np.frombuffer(seq, np.uint8).copy(), np.frombuffer(qual, np.uint8).copy()
+
+
+# ---- unitig graph in the oracle's terms (links + exact k-mer count sums) -------------
+_CODE2ASCII = "ACTG"
+
+
+def _dec(lo, hi, k):
+    v = (int(hi) << 64) | int(lo)
+    return "".join(_CODE2ASCII[(v >> (2 * (k - 1 - i))) & 3] for i in range(k))
+
+
+def oracle_graph(oracle, k):
+    """(units, kcs, circs, links) of the oracle's unitig graph.  Links and count
+    sums are derived here from the oracle's validated node edge bits with
+    pyref.unitig_links (string based), not taken from any product code."""
+    from oracle import pyref
+    units, _cov, circ = oracle.export_unitigs()
+    lo, hi, cnt, _raw, val = oracle.export_kmers()
+    count_of, edges = {}, set()
+    for i in range(len(lo)):
+        s = _dec(lo[i], hi[i], k)
+        count_of[s] = int(cnt[i])
+        e = int(val[i])
+        for b in range(4):
+            if e >> b & 1:
+                edges.add(s + _CODE2ASCII[b])
+            if e >> (4 + b) & 1:
+                edges.add(_CODE2ASCII[b] + s)
+    kcs = []
+    for u in units:
+        t = 0
+        for i in range(len(u) - k + 1):
+            km = u[i:i + k]
+            r = km.translate(_COMP)[::-1]
+            t += count_of[km] if km in count_of else count_of[r]
+        kcs.append(t)
+    links = pyref.unitig_links(units, edges, k)
+    return units, kcs, [int(c) for c in circ], links
+
+
+def canon_links(units, link_from, link_to):
+    """product link arrays (id*2+orient) -> set of (canon_a, oa, canon_b, ob) on canonical strings"""
+    out = set()
+    flip = [canon_unitig(u) != u for u in units]
+    can = [canon_unitig(u) for u in units]
+    for f, t in zip(link_from, link_to):
+        a, oa, b, ob = int(f) >> 1, int(f) & 1, int(t) >> 1, int(t) & 1
+        out.add((can[a], oa ^ flip[a], can[b], ob ^ flip[b]))
+    return out
+
+
+def canon_link_tuples(units, links):
+    """pyref link tuples (a, oa, b, ob) -> the same comparison form"""
+    flip = [canon_unitig(u) != u for u in units]
+    can = [canon_unitig(u) for u in units]
+    return {(can[a], oa ^ flip[a], can[b], ob ^ flip[b]) for (a, oa, b, ob) in links}

@@ -12,7 +12,8 @@ import pytest
 from oracle import Oracle
 from sparrowhawk_b200 import AssemblyHelper, ShkError, synth
 
-from parity import assert_parity, canon_unitig, gpu_pipeline, make_stream, run_oracle
+from parity import (assert_parity, canon_link_tuples, canon_links, canon_unitig, gpu_pipeline, make_stream, oracle_graph,
+                    run_oracle)
 from test_oracle import GOLD, _rand_case, parse_fastq, stream
 
 pytestmark = pytest.mark.gpu
@@ -144,7 +145,8 @@ def test_chunked_equals_bulk(tmp_path):
     states = {}
     for chunk in (0, 777):
         st = []
-        h = AssemblyHelper.new(31, True, 2, 20, chunk, False, False, False, False, progress=st.append)
+        # cleaning switched off (no_bubble_collapse, no_dead_end_removal): contigs == unitigs
+        h = AssemblyHelper.new(31, True, 2, 20, chunk, False, False, True, True, progress=st.append)
         h.preprocess(p1, p2)
         info = h.preprocessing_result()
         assert info["nkmers"] == o.stats()["n_nodes"] and info["used_min_count"] == 2
@@ -172,6 +174,50 @@ def test_chunked_equals_bulk(tmp_path):
         h.preprocess_push(data[i:i + n]); i += n
     h.preprocess_finish(); h.assemble()
     assert_parity(h, o, check_table=False)
+
+
+def test_unitig_links_match_oracle():
+    """K6 unitig-level links against links derived from the oracle's node edge bits (pyref.unitig_links)."""
+    for k, mc, err in ((21, 1, 0.01), (31, 0, 0.01), (47, 1, 0.02)):
+        seq, qual = synth.reads(21, 15_000, 20.0, err)
+        h = gpu_pipeline(seq, qual, k, mc, 20, keep_table=False)
+        o = run_oracle(seq, qual, k, mc, 20)
+        units, kcs, circs, links = oracle_graph(o, k)
+        gu, _, _ = h.export_unitigs()
+        lf, lt = h.export_links()
+        assert len(links) > 20
+        assert canon_links(gu, lf, lt) == canon_link_tuples(units, links)
+        # exact k-mer count sums per unitig
+        assert sorted(zip((canon_unitig(u) for u in gu), (int(x) for x in h.export_unitig_counts()))) == sorted(zip(units, kcs))
+
+
+@pytest.mark.parametrize("flags", [(False, False), (True, False), (False, True)])
+def test_assemble_contigs_match_cleaned_oracle_graph(flags):
+    """assemble() = GPU graph + host cleaning; contigs and their links against
+    pyref.clean_graph on the oracle's own unitig graph."""
+    from oracle import pyref
+    no_bubble, no_tips = flags
+    k, mc = 25, 1
+    seq, qual = synth.reads(33, 30_000, 25.0, 0.01)
+    h = AssemblyHelper.new(k, False, mc, 20, 0, False, False, no_bubble, no_tips)
+    h.preprocess_reads(seq, qual)
+    h.assemble()
+    o = run_oracle(seq, qual, k, mc, 20)
+    units, kcs, circs, links = oracle_graph(o, k)
+    pc, pl = pyref.clean_graph(units, kcs, circs, links, k, tips=not no_tips, bubbles=not no_bubble)
+    c = h.contigs()
+    got = sorted(zip(c["seq"], c["kc"], (bool(x) for x in c["circ"])))
+    assert all(s == canon_unitig(s) for s in c["seq"]), "contigs are reported in canonical orientation"
+    assert got == pc
+    assert canon_links(c["seq"], c["link_from"], c["link_to"]) == pl
+    res = h.assembly_result()
+    assert res["ncontigs"] == len(pc) < len(units)
+    fa = [l for l in res["outfasta"].splitlines() if not l.startswith(">")]
+    assert sorted(fa) == [p[0] for p in pc]
+    assert res["outgfa"].count("\nS\t") == len(pc) and res["outgfav2"].startswith("H\tVN:Z:2.0")
+    # FASTA order: length descending, contig_<i> = contig id i-1
+    assert fa == c["seq"] and [len(x) for x in fa] == sorted((len(x) for x in fa), reverse=True)
+    h.close()
 
 
 def test_errors():
