@@ -188,19 +188,23 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
   uint4 *wst = stage + (size_t)warp * 32 * RECW;
   u32 *wbm = bitmaps + warp * 64;
   for (int i = tid; i < SHK_NBINS; i += SHK_CB_THREADS) hist[i] = 0;
-  u64 ndist = 0, nspill = 0, ndec = 0;
+  // the table starts empty; every later phase hands it back empty (the sweep and the record
+  // compaction clear the slots they visit), so no group pays for a separate clearing pass
+  for (int i = tid; i < NS * (KW == 1 ? 1 : 2); i += SHK_CB_THREADS) reinterpret_cast<u64 *>(keys)[i] = SHK_EMPTY64;
+  for (int i = tid; i < NS; i += SHK_CB_THREADS) vals[i] = 0;
+  unsigned short *surv = reinterpret_cast<unsigned short *>(stage);                     // survivor slots of the sweep (staging is idle then)
+  constexpr u32 SURV_CAP = (u32)SHK_CB_WARPS * 32 * 16 * RECW / 2;
+  u64 nspill = 0, ndec = 0;
+  u32 ndist = 0, nb0 = 0, nb1 = 0;                                  // per-thread: distinct k-mers, spectrum bins 0 and 1
 
   for (;;) {
     __syncthreads();
-    if (tid == 0) { misc[0] = g_begin + atomicAdd(next_group, 1u); misc[1] = 0; misc[2] = 0; }
+    if (tid == 0) { misc[0] = g_begin + atomicAdd(next_group, 1u); misc[1] = 0; misc[2] = 0; misc[3] = 0; }
     __syncthreads();
     const u32 g = misc[0];
     if (g >= g_end) break;
     const u32 b0 = group_start[g], nb = group_start[g + 1] - b0;
-    // ---- clear the table (the record table first when de-duplicating: it time-shares the same memory),
-    //      prefix of the group's record counts ----
-    for (int i = tid; i < NS * (KW == 1 ? 1 : 2); i += SHK_CB_THREADS) reinterpret_cast<u64 *>(keys)[i] = SHK_EMPTY64;
-    for (int i = tid; i < NS; i += SHK_CB_THREADS) vals[i] = 0;
+    // ---- prefix of the group's record counts (the table is empty here) ----
     if (warp == 0) {
       u32 run = 0;
       for (u32 base = 0; base < nb; base += 32) {
@@ -250,12 +254,14 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
           if (lane == 0) basei = atomicAdd(&misc[2], (u32)__popc(om));
           basei = __shfl_sync(0xffffffffu, basei, 0);
           const u32 idx = basei + __popc(om & ((1u << lane) - 1));
-          if (occ && idx < uq_cap) { myrec[idx] = c4; mycnt[idx] = rcnt[s]; }
+          if (occ) {
+            if (idx < uq_cap) { myrec[idx] = c4; mycnt[idx] = rcnt[s]; }
+            rkeys[s] = U128Pair{SHK_EMPTY64, SHK_EMPTY64}; rcnt[s] = 0;      // hand the memory back empty
+          }
         }
       }
       __syncthreads();
       total = min(misc[2], uq_cap);
-      for (int i = tid; i < NS; i += SHK_CB_THREADS) { reinterpret_cast<u64 *>(keys)[i] = SHK_EMPTY64; vals[i] = 0; }
       if (tid == 0) misc[1] = 0;
       __syncthreads();
     }
@@ -319,44 +325,74 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
       __syncwarp();
     }
     __syncthreads();
-    // ---- sweep: spectrum, filter, compaction (NS is a multiple of the CTA size) ----
+    // ---- sweep: spectrum, filter, compaction; every visited slot is left empty ----
+    // Bins 0 and 1 (sequencing errors: most distinct k-mers) and the distinct count live in registers;
+    // survivors are collected as slot numbers in shared memory so the group pays ONE global atomic
+    // and writes its nodes densely.
     for (int s = tid; s < NS; s += SHK_CB_THREADS) {
-      K key; bool occ;
-      if (KW == 1) { u64 kk = reinterpret_cast<u64 *>(keys)[s]; occ = kk != SHK_EMPTY64; key = (K)kk; }
-      else { U128Pair kk = reinterpret_cast<U128Pair *>(keys)[s]; occ = kk.hi != SHK_EMPTY64; key = (K)(((u128)kk.hi << 64) | kk.lo); }
-      u32 v = vals[s], c = v & 0xFFFFFFu, e = v >> 24;
+      bool occ;
+      if (KW == 1) occ = reinterpret_cast<u64 *>(keys)[s] != SHK_EMPTY64;
+      else occ = reinterpret_cast<U128Pair *>(keys)[s].hi != SHK_EMPTY64;
+      if (!occ) continue;
+      const u32 v = vals[s];
+      u32 c = v & 0xFFFFFFu;
       if (c > SHK_COUNT_MAX) c = SHK_COUNT_MAX;
-      const u32 bin = occ ? shk_histo_bin(c ? c : 1u) : 0xFFFFu;
-      const u32 occm = __ballot_sync(0xffffffffu, occ);
-      if (occm) {
-        // the first bins hold most k-mers (sequencing errors): count them by ballot
-        const u32 m0 = __ballot_sync(0xffffffffu, bin == 0), m1 = __ballot_sync(0xffffffffu, bin == 1);
-        if (lane == 0) { if (m0) atomicAdd(&hist[0], (u32)__popc(m0)); if (m1) atomicAdd(&hist[1], (u32)__popc(m1)); ndist += __popc(occm); }
-        if (occ && bin > 1) atomicAdd(&hist[bin], 1u);
-        const bool surv = occ && shk_passes(c, min_count);
-        const u32 sm = __ballot_sync(0xffffffffu, surv);
-        if (sm) {
-          u32 basei = 0;
-          if (lane == 0) basei = atomicAdd(out.n_nodes, (u32)__popc(sm));
-          basei = __shfl_sync(0xffffffffu, basei, 0);
-          if (surv) {
-            u32 id = basei + __popc(sm & ((1u << lane) - 1));
-            if (id < out.node_cap) {
-              out.node_lo[id] = (u64)key;
-              if (KW == 2) out.node_hi[id] = (u64)((u128)key >> 64);
-              out.node_count[id] = (uint16_t)c;
-              out.node_raw[id] = (uint8_t)e;
-            }
-          }
+      const u32 bin = shk_histo_bin(c ? c : 1u);
+      ++ndist;
+      if (bin == 0) ++nb0; else if (bin == 1) ++nb1; else atomicAdd(&hist[bin], 1u);
+      if (shk_passes(c, min_count)) {
+        const u32 idx = atomicAdd(&misc[3], 1u);
+        if (idx < SURV_CAP) { surv[idx] = (unsigned short)s; continue; }         // written (and cleared) below
+        // more survivors than the list holds (tiny min_count): straight to the node arrays
+        const u32 id = atomicAdd(out.n_nodes, 1u);
+        if (id < out.node_cap) {
+          if (KW == 1) out.node_lo[id] = reinterpret_cast<u64 *>(keys)[s];
+          else { const U128Pair kk = reinterpret_cast<U128Pair *>(keys)[s]; out.node_lo[id] = kk.lo; out.node_hi[id] = kk.hi; }
+          out.node_count[id] = (uint16_t)c;
+          out.node_raw[id] = (uint8_t)(v >> 24);
         }
+      }
+      if (KW == 1) reinterpret_cast<u64 *>(keys)[s] = SHK_EMPTY64;
+      else reinterpret_cast<U128Pair *>(keys)[s] = U128Pair{SHK_EMPTY64, SHK_EMPTY64};
+      vals[s] = 0;
+    }
+    __syncthreads();
+    const u32 nsurv = min(misc[3], SURV_CAP);
+    if (nsurv) {
+      if (tid == 0) misc[4] = atomicAdd(out.n_nodes, nsurv);
+      __syncthreads();
+      const u32 nbase = misc[4];
+      for (u32 i = tid; i < nsurv; i += SHK_CB_THREADS) {
+        const u32 s = surv[i], id = nbase + i;
+        const u32 v = vals[s];
+        u32 c = v & 0xFFFFFFu;
+        if (c > SHK_COUNT_MAX) c = SHK_COUNT_MAX;
+        if (KW == 1) {
+          const u64 kk = reinterpret_cast<u64 *>(keys)[s];
+          if (id < out.node_cap) out.node_lo[id] = kk;
+          reinterpret_cast<u64 *>(keys)[s] = SHK_EMPTY64;
+        } else {
+          const U128Pair kk = reinterpret_cast<U128Pair *>(keys)[s];
+          if (id < out.node_cap) { out.node_lo[id] = kk.lo; out.node_hi[id] = kk.hi; }
+          reinterpret_cast<U128Pair *>(keys)[s] = U128Pair{SHK_EMPTY64, SHK_EMPTY64};
+        }
+        if (id < out.node_cap) { out.node_count[id] = (uint16_t)c; out.node_raw[id] = (uint8_t)(v >> 24); }
+        vals[s] = 0;
       }
     }
   }
+  // per-thread spectrum registers -> the CTA's shared spectrum
+  for (int o = 16; o; o >>= 1) { nb0 += __shfl_xor_sync(0xffffffffu, nb0, o); nb1 += __shfl_xor_sync(0xffffffffu, nb1, o); }
+  if (lane == 0) { if (nb0) atomicAdd(&hist[0], nb0); if (nb1) atomicAdd(&hist[1], nb1); }
   __syncthreads();
   for (int i = tid; i < SHK_NBINS; i += SHK_CB_THREADS) if (hist[i]) atomicAdd(&out.histo[i], (u64)hist[i]);
-  for (int o = 16; o; o >>= 1) { nspill += __shfl_xor_sync(0xffffffffu, nspill, o); ndec += __shfl_xor_sync(0xffffffffu, ndec, o); }
+  u64 ndist64 = ndist;
+  for (int o = 16; o; o >>= 1) {
+    nspill += __shfl_xor_sync(0xffffffffu, nspill, o); ndec += __shfl_xor_sync(0xffffffffu, ndec, o);
+    ndist64 += __shfl_xor_sync(0xffffffffu, ndist64, o);
+  }
   if (lane == 0) {
-    if (ndist) atomicAdd(&out.counters[2], ndist);
+    if (ndist64) atomicAdd(&out.counters[2], ndist64);
     if (nspill) atomicAdd(&out.counters[4], nspill);
     if (ndec) atomicAdd(&out.counters[5], ndec);
   }
