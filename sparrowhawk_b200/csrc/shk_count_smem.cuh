@@ -25,7 +25,8 @@ template <int KW> __host__ __device__ constexpr size_t cb_smem_bytes() {
   return (size_t)CbCfg<KW>::NS * (CbCfg<KW>::KEYB + 4)            // keys + vals
          + (size_t)SHK_CB_WARPS * 32 * 16 * CbCfg<KW>::RECW        // record staging
          + (size_t)SHK_CB_WARPS * 64 * 4                           // run-start bitmaps
-         + SHK_NBINS * 4 + (SHK_CB_MAXC + 1) * 4 + 64;
+         + SHK_NBINS * 4 + (SHK_CB_MAXC + 1) * 4 + 64
+         + 64 * 4;                                                  // record-length bins + cursors
 }
 
 // ---- shared-table insert ---------------------------------------------------
@@ -137,26 +138,28 @@ __device__ __forceinline__ uint4 canon_record(uint4 r, int k) {
   return make_uint4((u32)ol, (u32)(ol >> 32), (u32)oh, (u32)(oh >> 32));
 }
 
-// Insert a canonical record; returns false when no slot was found inside the probe
-// window (the caller then keeps the record as its own list entry — still exact).
-__device__ __forceinline__ bool rtable_insert(U128Pair *rkeys, u32 *rcnt, uint4 c) {
+// Insert a canonical record.  Returns 0 when no slot was found inside the probe window (the caller
+// then keeps the record as its own list entry — still exact), 1 when the record was already there,
+// 2 when this call claimed slot `s` for it.
+__device__ __forceinline__ int rtable_insert(U128Pair *rkeys, u32 *rcnt, uint4 c, u32 &s) {
   const u64 lo = ((u64)c.y << 32) | c.x, hi = ((u64)c.w << 32) | c.z;
   u32 h = c.x * 0x9E3779B1u ^ c.y * 0x85EBCA77u ^ c.z * 0xC2B2AE3Du ^ c.w * 0x27D4EB2Fu;
   h ^= h >> 15; h *= 0x2C1B3C6Du; h ^= h >> 13; h *= 0x297A2D39u; h ^= h >> 16;
-  u32 s = __umulhi(h, (u32)SHK_RT_SLOTS);
+  s = __umulhi(h, (u32)SHK_RT_SLOTS);
   for (int probe = 0; probe < SHK_RT_MAXPROBE; ++probe) {
     const uint4 c4 = *reinterpret_cast<const uint4 *>(rkeys + s);
     u64 clo = ((u64)c4.y << 32) | c4.x, chi = ((u64)c4.w << 32) | c4.z;
+    int won = 1;
     if ((clo & chi) == SHK_EMPTY64) {                           // empty: n = 31 never occurs in a record
       U128Pair expect{SHK_EMPTY64, SHK_EMPTY64}, want{lo, hi};
       const U128Pair old = atomicCAS(rkeys + s, expect, want);  // ATOMS.CAS.128
       clo = old.lo; chi = old.hi;
-      if ((clo & chi) == SHK_EMPTY64) { clo = lo; chi = hi; }
+      if ((clo & chi) == SHK_EMPTY64) { clo = lo; chi = hi; won = 2; }
     }
-    if (clo == lo && chi == hi) { atomicAdd(rcnt + s, 1u); return true; }
+    if (clo == lo && chi == hi) { atomicAdd(rcnt + s, 1u); return won; }
     s = (s + 1 == (u32)SHK_RT_SLOTS) ? 0u : s + 1;
   }
-  return false;
+  return 0;
 }
 
 struct CountOut {
@@ -183,11 +186,15 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
   u32 *bitmaps = reinterpret_cast<u32 *>(stage + (size_t)SHK_CB_WARPS * 32 * RECW);
   u32 *hist = bitmaps + SHK_CB_WARPS * 64;
   u32 *gpre = hist + SHK_NBINS;                         // [MAXC+1] prefix of record counts in the group
-  u32 *misc = gpre + SHK_CB_MAXC + 1;                   // [0] current group
+  u32 *misc = gpre + SHK_CB_MAXC + 1;                   // [0] current group [1] grab cursor [2] direct records [3] survivors
+                                                        // [4] node base [5] claimed record slots [6] distinct records
+  u32 *rbins = misc + 16;                               // [32] distinct records per run length n, [32] write cursors
+  unsigned short *rlist = reinterpret_cast<unsigned short *>(stage);   // record-table slots in claim order (phase 1 only)
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   uint4 *wst = stage + (size_t)warp * 32 * RECW;
   u32 *wbm = bitmaps + warp * 64;
   for (int i = tid; i < SHK_NBINS; i += SHK_CB_THREADS) hist[i] = 0;
+  if (tid < 64) rbins[tid] = 0;
   // the table starts empty; every later phase hands it back empty (the sweep and the record
   // compaction clear the slots they visit), so no group pays for a separate clearing pass
   for (int i = tid; i < NS * (KW == 1 ? 1 : 2); i += SHK_CB_THREADS) reinterpret_cast<u64 *>(keys)[i] = SHK_EMPTY64;
@@ -199,7 +206,7 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
 
   for (;;) {
     __syncthreads();
-    if (tid == 0) { misc[0] = g_begin + atomicAdd(next_group, 1u); misc[1] = 0; misc[2] = 0; misc[3] = 0; }
+    if (tid == 0) { misc[0] = g_begin + atomicAdd(next_group, 1u); misc[1] = 0; misc[2] = 0; misc[3] = 0; misc[5] = 0; }
     __syncthreads();
     const u32 g = misc[0];
     if (g >= g_end) break;
@@ -238,34 +245,85 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
           while (hi - lo > 1) { u32 mid = (lo + hi) >> 1; if (gpre[mid] <= f) lo = mid; else hi = mid; }
           const u64 sbase = seg_off ? seg_off[b0 + lo] : (u64)(b0 + lo) * rcap;
           const uint4 c = canon_record(__ldcs(reinterpret_cast<const uint4 *>(recs + (sbase + (f - gpre[lo])))), k);
-          if (!rtable_insert(rkeys, rcnt, c)) {
+          u32 slot;
+          const int got = rtable_insert(rkeys, rcnt, c, slot);
+          if (got == 2) {                                           // first sight of this record: remember its slot and length
+            rlist[atomicAdd(&misc[5], 1u)] = (unsigned short)slot;
+            atomicAdd(&rbins[c.x & 31u], 1u);
+          } else if (got == 0) {
             const u32 idx = atomicAdd(&misc[2], 1u);
             if (idx < uq_cap) { myrec[idx] = c; mycnt[idx] = 1u; }
           }
         }
       }
       __syncthreads();
-      for (int s = tid; s < SHK_RT_SLOTS; s += SHK_CB_THREADS) {
-        const uint4 c4 = *reinterpret_cast<const uint4 *>(rkeys + s);
-        const bool occ = (c4.x & c4.y & c4.z & c4.w) != 0xFFFFFFFFu;
-        const u32 om = __ballot_sync(0xffffffffu, occ);
-        if (om) {
-          u32 basei = 0;
-          if (lane == 0) basei = atomicAdd(&misc[2], (u32)__popc(om));
-          basei = __shfl_sync(0xffffffffu, basei, 0);
-          const u32 idx = basei + __popc(om & ((1u << lane) - 1));
-          if (occ) {
-            if (idx < uq_cap) { myrec[idx] = c4; mycnt[idx] = rcnt[s]; }
-            rkeys[s] = U128Pair{SHK_EMPTY64, SHK_EMPTY64}; rcnt[s] = 0;      // hand the memory back empty
-          }
-        }
+      // distinct records leave the table sorted by run length, longest first: the decode below gives every
+      // lane one record, so equal lengths keep the lanes of a warp in step, and handing out the long
+      // records first keeps the warps of the CTA finishing together
+      if (warp == 0) {
+        const u32 cn = rbins[lane];
+        u32 suf = cn;
+        for (int o = 1; o < 32; o <<= 1) { const u32 v = __shfl_down_sync(0xffffffffu, suf, o); if (lane + o < 32) suf += v; }
+        rbins[32 + lane] = misc[2] + suf - cn;                     // records with a longer run come first
+        rbins[lane] = 0;
+        if (lane == 0) misc[6] = misc[2] + suf;
       }
       __syncthreads();
-      total = min(misc[2], uq_cap);
+      const u32 nl = misc[5];
+      for (u32 i = tid; i < nl; i += SHK_CB_THREADS) {
+        const u32 sl = rlist[i];
+        const uint4 c4 = *reinterpret_cast<const uint4 *>(rkeys + sl);
+        const u32 pos = atomicAdd(&rbins[32 + (c4.x & 31u)], 1u);
+        if (pos < uq_cap) { myrec[pos] = c4; mycnt[pos] = rcnt[sl]; }
+        rkeys[sl] = U128Pair{SHK_EMPTY64, SHK_EMPTY64}; rcnt[sl] = 0;   // hand the memory back empty
+      }
+      __syncthreads();
+      total = min(misc[6], uq_cap);
       if (tid == 0) misc[1] = 0;
       __syncthreads();
     }
     // ---- decode + insert: a warp grabs 32 records at a time (dynamic, so no warp idles at the tail) ----
+    if (DEDUP && KW == 1) {
+      // one distinct record per lane, k-mers rolled out of registers (no re-extraction, no staging)
+      const u64 km = kmask_of(k, (u64)0);
+      for (;;) {
+        u32 cbase = 0;
+        if (lane == 0) cbase = atomicAdd(&misc[1], 32u);
+        cbase = __shfl_sync(0xffffffffu, cbase, 0);
+        if (cbase >= total) break;
+        const u32 f = cbase + lane;
+        u32 n = 0, wgt = 0, hasl = 0, hasr = 0, a = 0;
+        u64 fwd = 0, rc = 0, S = 0;
+        if (f < total) {
+          const uint4 r = myrec[f]; wgt = mycnt[f];
+          n = r.x & 31u; hasl = (r.x >> 5) & 1u; hasr = (r.x >> 6) & 1u;
+          const u64 hi = ((u64)r.w << 32) | r.z, lo = ((u64)r.y << 32) | r.x;
+          a = (u32)(hi >> 62);                                        // base 0: the left flank
+          fwd = ((hi << 2) | (lo >> 62)) >> (64 - 2 * k);             // bases 1 .. k
+          rc = revcomp_key(fwd, k);
+          const int sh = 2 * (k + 1);                                 // bases k+1 .. : what follows the first k-mer
+          S = sh >= 64 ? lo : ((hi << sh) | (lo >> (64 - sh)));
+        }
+        const u32 nmax = __reduce_max_sync(0xffffffffu, n);
+        for (u32 i = 0; i < nmax; ++i) {
+          if (i < n) {
+            const u32 b = (u32)(S >> 62);
+            const bool hl = i > 0 || hasl, hr = i + 1 < n || hasr;
+            u64 key; u32 e;
+            if (fwd < rc) { key = fwd; e = (hr ? (1u << b) : 0u) | (hl ? (16u << a) : 0u); }
+            else { key = rc; e = (hl ? (1u << (a ^ 2u)) : 0u) | (hr ? (16u << (b ^ 2u)) : 0u); }
+            ndec += wgt;
+            if (!smem_insert(reinterpret_cast<u64 *>(keys), vals, NS, key, e, wgt)) {
+              table_insert(ovf, (K)key, e, wgt, ovf_flag); nspill += wgt;
+            }
+            a = (u32)(fwd >> (2 * k - 2)) & 3u;
+            fwd = ((fwd << 2) | b) & km;
+            rc = (rc >> 2) | ((u64)(b ^ 2u) << (2 * k - 2));
+            S <<= 2;
+          }
+        }
+      }
+    } else
     for (;;) {
       u32 cbase = 0;
       if (lane == 0) cbase = atomicAdd(&misc[1], 32u);
