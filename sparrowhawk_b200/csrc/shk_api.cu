@@ -220,9 +220,10 @@ static shk_status count_groups(shk_asm *h, const std::vector<uint32_t> &gs, uint
   uint32_t uq_cap = 0;
   if (h->kw == 1 && !h->no_dedup) {
     for (uint32_t g = g_begin; g < g_end; ++g) {
+      // items of the distinct-record list: a record of n k-mers is cut into ceil(n / 8) items
       uint64_t r = 0;
-      for (uint32_t sgi = gs[g]; sgi < gs[g + 1]; ++sgi) r += h->seg_recs[sgi];
-      uq_cap = (uint32_t)std::max<uint64_t>(uq_cap, r);
+      for (uint32_t sgi = gs[g]; sgi < gs[g + 1]; ++sgi) r += (uint64_t)h->seg_recs[sgi] + h->seg_kmers[sgi] / 8;
+      uq_cap = (uint32_t)std::min<uint64_t>(std::max<uint64_t>(uq_cap, r), 0x7FFFFFC0ull);
     }
     uq_cap = (uq_cap + 63u) & ~63u;
     const size_t ctas = (size_t)count_ctas();

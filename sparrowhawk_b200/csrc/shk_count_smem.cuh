@@ -162,6 +162,18 @@ __device__ __forceinline__ int rtable_insert(U128Pair *rkeys, u32 *rcnt, uint4 c
   return 0;
 }
 
+// An item = up to SHK_CB_SEG consecutive k-mers of a distinct record: the record with its header byte
+// rewritten to  bits 0-3 k-mers in the item, 4-5 item number j (the item starts at k-mer j * SHK_CB_SEG),
+// 6 "the first k-mer has a k-mer or flank in front", 7 "the last k-mer has one behind".
+#define SHK_CB_SEG 8
+__device__ __forceinline__ uint4 record_item(uint4 c, u32 j) {
+  const u32 n = c.x & 31u, hasl = (c.x >> 5) & 1u, hasr = (c.x >> 6) & 1u, off = j * SHK_CB_SEG;
+  const u32 ne = min((u32)SHK_CB_SEG, n - off);
+  const u32 hl = (off > 0 || hasl) ? 1u : 0u, hr = (off + ne < n || hasr) ? 1u : 0u;
+  c.x = (c.x & ~0xFFu) | ne | (j << 4) | (hl << 6) | (hr << 7);
+  return c;
+}
+
 struct CountOut {
   u64 *histo;                 // [500] global spectrum
   u64 *node_lo, *node_hi; uint16_t *node_count; uint8_t *node_raw;
@@ -247,19 +259,23 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
           const uint4 c = canon_record(__ldcs(reinterpret_cast<const uint4 *>(recs + (sbase + (f - gpre[lo])))), k);
           u32 slot;
           const int got = rtable_insert(rkeys, rcnt, c, slot);
-          if (got == 2) {                                           // first sight of this record: remember its slot and length
+          const u32 rn = c.x & 31u, full = rn / SHK_CB_SEG, rem = rn % SHK_CB_SEG;
+          if (got == 2) {                                           // first sight of this record: remember its slot, count its items
             rlist[atomicAdd(&misc[5], 1u)] = (unsigned short)slot;
-            atomicAdd(&rbins[c.x & 31u], 1u);
+            if (full) atomicAdd(&rbins[SHK_CB_SEG], full);
+            if (rem) atomicAdd(&rbins[rem], 1u);
           } else if (got == 0) {
-            const u32 idx = atomicAdd(&misc[2], 1u);
-            if (idx < uq_cap) { myrec[idx] = c; mycnt[idx] = 1u; }
+            const u32 nit = full + (rem ? 1u : 0u), idx = atomicAdd(&misc[2], nit);
+            for (u32 j = 0; j < nit; ++j)
+              if (idx + j < uq_cap) { myrec[idx + j] = record_item(c, j); mycnt[idx + j] = 1u; }
           }
         }
       }
       __syncthreads();
-      // distinct records leave the table sorted by run length, longest first: the decode below gives every
-      // lane one record, so equal lengths keep the lanes of a warp in step, and handing out the long
-      // records first keeps the warps of the CTA finishing together
+      // distinct records leave the table cut into items of at most SHK_CB_SEG k-mers, sorted by item length,
+      // longest first: the decode below gives every lane one item, so equal lengths keep the lanes of a warp
+      // in step, short items bound the size of a warp's job, and handing out the long ones first keeps the
+      // warps of the CTA finishing together
       if (warp == 0) {
         const u32 cn = rbins[lane];
         u32 suf = cn;
@@ -273,8 +289,15 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
       for (u32 i = tid; i < nl; i += SHK_CB_THREADS) {
         const u32 sl = rlist[i];
         const uint4 c4 = *reinterpret_cast<const uint4 *>(rkeys + sl);
-        const u32 pos = atomicAdd(&rbins[32 + (c4.x & 31u)], 1u);
-        if (pos < uq_cap) { myrec[pos] = c4; mycnt[pos] = rcnt[sl]; }
+        const u32 rn = c4.x & 31u, full = rn / SHK_CB_SEG, rem = rn % SHK_CB_SEG, mult = rcnt[sl];
+        for (u32 j = 0; j < full; ++j) {
+          const u32 pos = atomicAdd(&rbins[32 + SHK_CB_SEG], 1u);
+          if (pos < uq_cap) { myrec[pos] = record_item(c4, j); mycnt[pos] = mult; }
+        }
+        if (rem) {
+          const u32 pos = atomicAdd(&rbins[32 + rem], 1u);
+          if (pos < uq_cap) { myrec[pos] = record_item(c4, full); mycnt[pos] = mult; }
+        }
         rkeys[sl] = U128Pair{SHK_EMPTY64, SHK_EMPTY64}; rcnt[sl] = 0;   // hand the memory back empty
       }
       __syncthreads();
@@ -296,8 +319,10 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
         u64 fwd = 0, rc = 0, S = 0;
         if (f < total) {
           const uint4 r = myrec[f]; wgt = mycnt[f];
-          n = r.x & 31u; hasl = (r.x >> 5) & 1u; hasr = (r.x >> 6) & 1u;
-          const u64 hi = ((u64)r.w << 32) | r.z, lo = ((u64)r.y << 32) | r.x;
+          n = r.x & 15u; hasl = (r.x >> 6) & 1u; hasr = (r.x >> 7) & 1u;      // item header (record_item)
+          const int ish = 2 * SHK_CB_SEG * (int)((r.x >> 4) & 3u);            // the item starts this many bits into the record
+          u64 hi = ((u64)r.w << 32) | r.z, lo = ((u64)r.y << 32) | r.x;
+          if (ish) { hi = (hi << ish) | (lo >> (64 - ish)); lo <<= ish; }
           a = (u32)(hi >> 62);                                        // base 0: the left flank
           fwd = ((hi << 2) | (lo >> 62)) >> (64 - 2 * k);             // bases 1 .. k
           rc = revcomp_key(fwd, k);
