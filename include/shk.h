@@ -141,6 +141,8 @@ typedef struct shk_stats {
   float ms_count_kernel;   /* K1b count_buckets main launch alone */
   uint64_t n_spilled;      /* k-mer instances that went through the global overflow table */
   uint64_t n_records;      /* super-k-mer records written by K1a */
+  uint32_t device_planned; /* 1: the last count ran the steady-state path (K1b groups planned on the device) */
+  uint32_t reserved;
 } shk_stats;
 
 /* Use `stream` (a cudaStream_t passed as void*) for all work of this handle;

@@ -191,7 +191,7 @@ static shk_status count_impl(shk_asm *h, int /*reset*/, uint32_t P_override = 0)
     for (uint32_t i = 0; i < P; ++i) { h->seg_kmers[i] = (uint32_t)(hf[i] >> 32); h->seg_recs[i] = (uint32_t)hf[i]; }
     h->seg_per_bucket = 1; h->src_instances = h->st.n_instances; h->shard_src = false;
   }
-  h->counted = true; h->filtered = h->graphed = false; h->histo_valid = false;
+  h->counted = true; h->counted_fast = false; h->st.device_planned = 0; h->filtered = h->graphed = false; h->histo_valid = false;
   return SHK_OK;
 }
 
@@ -228,12 +228,13 @@ static shk_status count_groups(shk_asm *h, const std::vector<uint32_t> &gs, uint
     uq_cap = (uq_cap + 63u) & ~63u;
     const size_t ctas = (size_t)count_ctas();
     SHK_TRY(h->uq_rec.ensure(ctas * uq_cap * 16 + 16)); SHK_TRY(h->uq_cnt.ensure(ctas * uq_cap * 4 + 16));
+    h->uq_cap = std::max(h->uq_cap, uq_cap);
   }
   h->st.gpu_launches += launch_count_buckets(h->kw, sh ? h->recv_recs : h->skrecs.p, h->bfill.as<uint64_t>(), h->rcap,
                                              sh ? h->seg_off.as<uint64_t>() : nullptr, sh ? h->seg_cnt.as<uint32_t>() : nullptr,
                                              uq_cap ? h->uq_rec.p : nullptr, h->uq_cnt.as<uint32_t>(), uq_cap,
-                                             h->groups.as<uint32_t>(), g_begin, g_end,
-                                             d_flags(h) + 2, h->p.k, min_count, h->ovf.p, h->ovf_cap, d_flags(h),
+                                             h->groups.as<uint32_t>(), g_begin, g_end, nullptr,
+                                             d_flags(h) + 2, h->p.k, min_count, h->ovf.p, h->ovf_cap, d_flags(h), d_flags(h) + 6,
                                              d_histo(h), h->node_lo.as<uint64_t>(), h->node_hi.as<uint64_t>(),
                                              h->node_count.as<uint16_t>(), h->node_raw.as<uint8_t>(), node_cap,
                                              d_flags(h) + 1, d_counters(h), h->stream);
@@ -241,10 +242,118 @@ static shk_status count_groups(shk_asm *h, const std::vector<uint32_t> &gs, uint
   return SHK_OK;
 }
 
+// tail shared by the planned-on-host and planned-on-device paths: sweep the overflow table when
+// something spilled, read the spectrum and the node count back, build the node index
+static shk_status sweep_overflow(shk_asm *h, int mc_eff, uint32_t node_cap) {
+  h->st.gpu_launches += launch_histogram_filter(h->kw, h->ovf.p, h->ovf_cap, mc_eff, d_histo(h),
+                                                h->node_lo.as<uint64_t>(), h->node_hi.as<uint64_t>(),
+                                                h->node_count.as<uint16_t>(), h->node_raw.as<uint8_t>(), node_cap,
+                                                d_flags(h) + 1, h->stream);
+  SHK_CUDA(cudaGetLastError());
+  return read_scalars(h);
+}
+
 static shk_status index_impl(shk_asm *h);
+// ---- steady-state K1a + K1b: nothing on the host between the two kernels ----------------
+// Preconditions (fast_ready): this handle has run the host-planned path on a read set of this
+// size, so the bucket count, the region size, the distinct/instances ratio and the de-dup list
+// size are known.  The groups are planned by k_plan_groups on the stream; everything the host
+// would have checked before K1b is checked after it, and any violation falls back to the
+// host-planned path (same results, one wasted pass).
+static bool fast_ready(shk_asm *h) {
+  static const bool off = [] { const char *e = getenv("SHK_NO_FAST"); return e && e[0] == '1'; }();
+  return !off && h->ratio_est > 0 && h->P && h->rcap && h->fast_positions == h->n_positions && h->n_positions > 0 &&
+         !h->shard_world && (h->kw == 2 || h->no_dedup || h->uq_cap > 0) && h->ovf_cap > 0;
+}
+
+static shk_status count_filter_fast(shk_asm *h, int min_count, bool &fell_back) {
+  fell_back = false;
+  SHK_TRY(require_device(h));
+  const uint64_t *b = h->bases.as<uint64_t>() + 1;
+  const uint32_t *m = h->mask.as<uint32_t>() + 1;
+  const uint32_t P = h->P, rcap = h->rcap;
+  const bool dedup = h->kw == 1 && !h->no_dedup;
+  uint64_t bound = h->n_positions / ((uint64_t)std::max(min_count, 0) + 1) + 1;     // instances <= positions
+  if (bound > 0xFFFFFFF0ull) { fell_back = true; return SHK_OK; }
+  const uint32_t node_cap = (uint32_t)bound;
+  SHK_TRY(h->node_lo.ensure((size_t)node_cap * 8));
+  if (h->kw == 2) SHK_TRY(h->node_hi.ensure((size_t)node_cap * 8));
+  SHK_TRY(h->node_count.ensure((size_t)node_cap * 2));
+  SHK_TRY(h->node_raw.ensure((size_t)node_cap));
+  SHK_TRY(h->groups.ensure((size_t)(P + 2) * 4));
+  SHK_TRY(h->plan_scratch.ensure((size_t)(P + 2) * 8));
+  // de-dup lists: the device planner cuts groups differently from the host planner (up to one bucket more per
+  // group), so size them with headroom over the host-planned need, or for what the last device plan asked
+  uint32_t uq_fast = 0;
+  if (dedup) {
+    uq_fast = (uint32_t)std::min<uint64_t>(std::max<uint64_t>((uint64_t)h->uq_cap * 2 + 1024, (uint64_t)h->uq_need_hint + h->uq_need_hint / 8), 0x7FFFFFC0ull);
+    uq_fast = (uq_fast + 63u) & ~63u;
+    const size_t ctas = (size_t)count_ctas();
+    SHK_TRY(h->uq_rec.ensure(ctas * uq_fast * 16 + 16)); SHK_TRY(h->uq_cnt.ensure(ctas * uq_fast * 4 + 16));
+  }
+  h->node_cap = node_cap;
+  SHK_CUDA(cudaEventRecord(h->ev[2], h->stream));
+  SHK_CUDA(cudaMemsetAsync(h->bfill.p, 0, (size_t)P * 8, h->stream));
+  SHK_CUDA(cudaMemsetAsync(d_counters(h) + 1, 0, 8, h->stream));                     // n_instances
+  SHK_CUDA(cudaMemsetAsync(d_counters(h) + 2, 0, 8, h->stream));                     // n_distinct ([3] = bases of the resident reads stays)
+  SHK_CUDA(cudaMemsetAsync(d_counters(h) + 4, 0, 4 * 8 + SHK_HISTO_BINS * 8 + 8 * 4, h->stream));   // spilled, decoded, records, spectrum, flags
+  SHK_CUDA(cudaEventRecord(h->ev[8], h->stream));
+  h->st.gpu_launches += launch_partition(h->kw, b, m, h->nwords, h->p.k, P, rcap, h->skrecs.p, h->bfill.as<uint64_t>(), d_counters(h), h->stream);
+  SHK_CUDA(cudaEventRecord(h->ev[9], h->stream));
+  SHK_CUDA(cudaEventRecord(h->ev[3], h->stream));
+  SHK_CUDA(cudaEventRecord(h->ev[4], h->stream));
+  h->st.gpu_launches += launch_table_fill(h->ovf.p, h->ovf_cap, h->kw, h->stream);
+  h->st.gpu_launches += launch_plan_groups(h->bfill.as<uint64_t>(), P, rcap, h->ratio_est, count_table_slots(h->kw) * 0.55,
+                                           (uint32_t)count_max_group(), h->groups.as<uint32_t>(), h->plan_scratch.as<uint64_t>(),
+                                           d_flags(h) + 3, d_counters(h) + 6, h->stream);
+  SHK_CUDA(cudaEventRecord(h->ev[10], h->stream));
+  h->st.gpu_launches += launch_count_buckets(h->kw, h->skrecs.p, h->bfill.as<uint64_t>(), rcap, nullptr, nullptr,
+                                             dedup ? h->uq_rec.p : nullptr, h->uq_cnt.as<uint32_t>(), uq_fast,
+                                             h->groups.as<uint32_t>(), 0, 0, d_flags(h) + 3, d_flags(h) + 2, h->p.k, min_count,
+                                             h->ovf.p, h->ovf_cap, d_flags(h), d_flags(h) + 6, d_histo(h),
+                                             h->node_lo.as<uint64_t>(), h->node_hi.as<uint64_t>(), h->node_count.as<uint16_t>(),
+                                             h->node_raw.as<uint8_t>(), node_cap, d_flags(h) + 1, d_counters(h), h->stream);
+  SHK_CUDA(cudaGetLastError());
+  SHK_CUDA(cudaEventRecord(h->ev[11], h->stream));
+  SHK_TRY(read_scalars(h));
+  const uint32_t *fl = (const uint32_t *)(h->h_pinned + 8 + SHK_HISTO_BINS);
+  if (fl[0] || fl[6] || fl[4] > rcap || (dedup && fl[5] > uq_fast)) {
+    if (h->p.verbose > 1 || getenv("SHK_DEBUG"))
+      fprintf(stderr, "[shk] steady-state path fell back: overflow table %u, list flag %u, largest fill %u / %u, list need %u / %u\n",
+              fl[0], fl[6], fl[4], rcap, fl[5], uq_fast);
+    if (dedup) h->uq_need_hint = std::max(h->uq_need_hint, fl[5]);
+    h->uq_retry = !fl[0] && fl[4] <= rcap;
+    fell_back = true;
+    return SHK_OK;
+  }
+  if (dedup) h->uq_need_hint = fl[5];
+  h->n_records = h->h_pinned[6];
+  h->n_bases = h->h_pinned[3];
+  h->counted_positions = h->n_positions;
+  h->st.n_bases = h->n_bases; h->st.n_positions = h->n_positions; h->st.n_instances = h->h_pinned[1];
+  h->st.table_slots = P; h->st.table_retries = 0; h->st.n_records = h->n_records;
+  h->src_instances = h->st.n_instances; h->shard_src = false; h->seg_per_bucket = 1;
+  h->seg_kmers.clear(); h->seg_recs.clear();               // the host-side bucket description is not fetched on this path
+  h->counted = true; h->counted_fast = true; h->st.device_planned = 1;
+  h->st.n_spilled = h->h_pinned[4];
+  if (h->st.n_spilled) SHK_TRY(sweep_overflow(h, min_count, node_cap));
+  memcpy(h->histo, h->h_pinned + 8, sizeof h->histo);
+  h->histo_valid = true;
+  uint64_t nd = 0;
+  for (int i = 0; i < SHK_HISTO_BINS; ++i) nd += h->histo[i];
+  h->st.n_distinct = nd;
+  if (h->st.n_instances) h->ratio_est = std::min(1.0, 1.10 * (double)nd / (double)h->st.n_instances + 0.005);
+  const uint32_t nn = ((const uint32_t *)(h->h_pinned + 8 + SHK_HISTO_BINS))[1];
+  if (nn > node_cap) { set_error("node buffer overflow (%u > %u)", nn, node_cap); return SHK_ERR_STATE; }
+  h->st.n_nodes = nn;
+  h->st.used_min_count = min_count;
+  return index_impl(h);
+}
+
 static shk_status filter_impl(shk_asm *h, int min_count, bool histogram_only = false, bool build_index = true) {
   SHK_TRY(require_device(h));
   if (!h->counted) { set_error("filter before count"); return SHK_ERR_STATE; }
+  if (h->counted_fast) SHK_TRY(count_impl(h, 1));          // the bucket description was never fetched: cut again, host-planned
   SHK_CUDA(cudaEventRecord(h->ev[4], h->stream));
   const uint64_t ninst = h->src_instances;
   // survivors have count > min_count  =>  n_nodes <= instances / (min_count + 1)
@@ -303,12 +412,7 @@ static shk_status filter_impl(shk_asm *h, int min_count, bool histogram_only = f
     }
     if (spilled) {
       // sweep the overflow table into the same spectrum / node arrays
-      h->st.gpu_launches += launch_histogram_filter(h->kw, h->ovf.p, h->ovf_cap, mc_eff, d_histo(h),
-                                                    h->node_lo.as<uint64_t>(), h->node_hi.as<uint64_t>(),
-                                                    h->node_count.as<uint16_t>(), h->node_raw.as<uint8_t>(), node_cap,
-                                                    d_flags(h) + 1, h->stream);
-      SHK_CUDA(cudaGetLastError());
-      SHK_TRY(read_scalars(h));
+      SHK_TRY(sweep_overflow(h, mc_eff, node_cap));
     }
     break;
   }
@@ -323,6 +427,7 @@ static shk_status filter_impl(shk_asm *h, int min_count, bool histogram_only = f
   if (histogram_only) { SHK_CUDA(cudaEventRecord(h->ev[5], h->stream)); return SHK_OK; }
   h->st.n_nodes = nn;
   h->st.used_min_count = min_count;
+  if (!h->shard_src) h->fast_positions = h->counted_positions;      // calibrated for a read set of this size
   if (!build_index) {          // sharded path: the index is built over the gathered node set (shk_shard_set_nodes)
     SHK_CUDA(cudaEventRecord(h->ev[5], h->stream));
     h->filtered = false; h->graphed = false; h->hu.valid = false;
@@ -534,7 +639,7 @@ void shk_asm_free(shk_asm *h) {
     DevBuf *bufs[] = {&h->bases, &h->mask, &h->ascii_seq, &h->ascii_qual, &h->slots, &h->dscal, &h->node_lo, &h->node_hi,
                       &h->node_count, &h->node_raw, &h->node_edges, &h->uniq, &h->succ, &h->tail_of, &h->len_of,
                       &h->unitig_of_head, &h->elem_unitig, &h->pd, &h->cq, &h->circ, &h->recs, &h->ucirc, &h->cov_sum,
-                      &h->useq, &h->link_from, &h->link_to, &h->gscal, &h->splitters, &h->sum_of, &h->rank_work, &h->skrecs, &h->bfill, &h->groups, &h->ovf, &h->uq_rec, &h->uq_cnt, &h->seg_off, &h->seg_cnt, &h->pack_off};
+                      &h->useq, &h->link_from, &h->link_to, &h->gscal, &h->splitters, &h->sum_of, &h->rank_work, &h->skrecs, &h->bfill, &h->groups, &h->ovf, &h->uq_rec, &h->uq_cnt, &h->seg_off, &h->seg_cnt, &h->pack_off, &h->plan_scratch};
     for (auto b : bufs) b->release();
     if (h->h_pinned) cudaFreeHost(h->h_pinned);
     h->hfill.release();
@@ -571,9 +676,24 @@ shk_status shk_load_reads_device(shk_asm *h, const void *d_seq, const void *d_qu
 shk_status shk_count(shk_asm *h, int reset) { return count_impl(h, reset); }
 shk_status shk_filter(shk_asm *h) { if (!h) { set_error("null handle"); return SHK_ERR_BAD_ARG; } return filter_impl(h, h->p.min_count); }
 shk_status shk_build_graph(shk_asm *h) { return graph_impl(h); }
-shk_status shk_run(shk_asm *h) {
+static shk_status count_filter(shk_asm *h, int min_count) {
+  if (h && h->dev >= 0 && fast_ready(h)) {
+    bool fell_back = false;
+    SHK_TRY(count_filter_fast(h, min_count, fell_back));
+    if (!fell_back) return SHK_OK;
+    if (h->uq_retry) {                  // only the de-dup lists were too small: their need is known now
+      h->uq_retry = false;
+      SHK_TRY(count_filter_fast(h, min_count, fell_back));
+      if (!fell_back) return SHK_OK;
+    }
+    // re-calibrate on the host-planned path (which sets fast_positions again when it succeeds)
+  }
   SHK_TRY(count_impl(h, 1));
-  SHK_TRY(filter_impl(h, h->p.min_count));
+  return filter_impl(h, min_count);
+}
+shk_status shk_run(shk_asm *h) {
+  if (!h) { set_error("null handle"); return SHK_ERR_BAD_ARG; }
+  SHK_TRY(count_filter(h, h->p.min_count));
   return graph_impl(h);
 }
 shk_status shk_get_stats(shk_asm *h, shk_stats *out) {
@@ -701,21 +821,27 @@ static void build_pre_json(shk_asm *h) {
   j += "],\"used_min_count\":" + std::to_string(h->st.used_min_count) + "}";
 }
 
-shk_status shk_internal_finish_preprocess(shk_asm *h, const char *mode) {
+static shk_status count_filter(shk_asm *h, int min_count);
+// need_count: the resident reads have not been cut into records yet (count and filter run back to back,
+// on the steady-state path when the handle is calibrated)
+static shk_status finish_preprocess(shk_asm *h, const char *mode, bool need_count) {
   char st[96];
   int mc = h->p.min_count;
+  if (need_count && h->p.do_fit) { SHK_TRY(count_impl(h, 1)); need_count = false; }
   if (h->p.do_fit) {
     snprintf(st, sizeof st, "preprocess:%s:fitting", mode); progress(h, st);
     SHK_TRY(histogram_impl(h));
     mc = shk::fit_min_count(h->histo, h->p.min_count);
   }
   snprintf(st, sizeof st, "preprocess:%s:filtering", mode); progress(h, st);
-  SHK_TRY(filter_impl(h, mc));
+  if (need_count) SHK_TRY(count_filter(h, mc));
+  else SHK_TRY(filter_impl(h, mc));
   progress(h, "preprocess:saving");
   build_pre_json(h);
   progress(h, "preprocess:end");
   return SHK_OK;
 }
+shk_status shk_internal_finish_preprocess(shk_asm *h, const char *mode) { return finish_preprocess(h, mode, false); }
 
 shk_status shk_asm_preprocess_reads(shk_asm *h, const uint8_t *seq, const uint8_t *qual, size_t n) {
   SHK_TRY(require_device(h));
@@ -725,8 +851,7 @@ shk_status shk_asm_preprocess_reads(shk_asm *h, const uint8_t *seq, const uint8_
   SHK_TRY(load_reads_host(h, seq, qual, n, 0));
   progress(h, "preprocess:bulk:loop:end");
   progress(h, "preprocess:bulk:sorting");   // the counting step (reference bulk mode sorts; we hash)
-  SHK_TRY(count_impl(h, 1));
-  return shk_internal_finish_preprocess(h, "bulk");
+  return finish_preprocess(h, "bulk", true);
 }
 
 shk_status shk_asm_preprocessing_info(shk_asm *h, const char **json, size_t *len) {

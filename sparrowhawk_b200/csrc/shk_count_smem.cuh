@@ -186,8 +186,9 @@ __global__ void __launch_bounds__(SHK_CB_THREADS, SHK_CB_PER_SM)
 k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__restrict__ bstat, u32 rcap,
                 const u64 *__restrict__ seg_off, const u32 *__restrict__ seg_cnt,
                 uint4 *__restrict__ uq_rec, u32 *__restrict__ uq_cnt, u32 uq_cap /* distinct-record list, per CTA */,
-                const u32 *__restrict__ group_start, u32 g_begin, u32 g_end, u32 *__restrict__ next_group, int k,
-                int min_count, Table<KW> ovf, u32 *__restrict__ ovf_flag, CountOut out) {
+                const u32 *__restrict__ group_start, u32 g_begin, u32 g_end, const u32 *__restrict__ g_end_dev /* nullable: planned on the device */,
+                u32 *__restrict__ next_group, int k, int min_count, Table<KW> ovf, u32 *__restrict__ ovf_flag,
+                u32 *__restrict__ uq_flag /* set when a de-dup list is too small */, CountOut out) {
   typedef typename KeyOf<KW>::type K;
   typedef typename std::conditional<KW == 1, u64, U128Pair>::type SK;
   constexpr int NS = CbCfg<KW>::NS, RECW = CbCfg<KW>::RECW;
@@ -203,6 +204,7 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
   u32 *rbins = misc + 16;                               // [32] distinct records per run length n, [32] write cursors
   unsigned short *rlist = reinterpret_cast<unsigned short *>(stage);   // record-table slots in claim order (phase 1 only)
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (g_end_dev) g_end = g_begin + *g_end_dev;
   uint4 *wst = stage + (size_t)warp * 32 * RECW;
   u32 *wbm = bitmaps + warp * 64;
   for (int i = tid; i < SHK_NBINS; i += SHK_CB_THREADS) hist[i] = 0;
@@ -282,7 +284,7 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
         for (int o = 1; o < 32; o <<= 1) { const u32 v = __shfl_down_sync(0xffffffffu, suf, o); if (lane + o < 32) suf += v; }
         rbins[32 + lane] = misc[2] + suf - cn;                     // records with a longer run come first
         rbins[lane] = 0;
-        if (lane == 0) misc[6] = misc[2] + suf;
+        if (lane == 0) { misc[6] = misc[2] + suf; if (misc[2] + suf > uq_cap) atomicExch(uq_flag, 1u); }
       }
       __syncthreads();
       const u32 nl = misc[5];
@@ -478,6 +480,90 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
     if (ndist64) atomicAdd(&out.counters[2], ndist64);
     if (nspill) atomicAdd(&out.counters[4], nspill);
     if (ndec) atomicAdd(&out.counters[5], ndec);
+  }
+}
+
+// ---- device-side group planning -------------------------------------------------
+// Steady-state runs (shk_run on a handle that has already measured distinct/instances
+// for a read set of this size) plan the bucket groups of K1b on the device, right
+// behind K1a on the stream, so the host never waits for the bucket fills.
+// Bucket i opens a new group when floor(E(i) / budget) + floor(i / maxc) changes, E =
+// exclusive prefix of the estimated distinct k-mers (instances * ratio): a group holds
+// at most `budget` + one bucket of them and at most maxc buckets.  Also returns what
+// the host must verify after the run: the largest bucket fill (region overflow), the
+// record total and the largest item count of a group (size of the de-dup lists).
+#define SHK_PLAN_THREADS 1024
+__device__ __forceinline__ u64 plan_block_scan(u64 v, u64 *sm, u64 &total) {       // exclusive prefix over the CTA
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  u64 inc = v;
+  for (int o = 1; o < 32; o <<= 1) { const u64 t = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += t; }
+  __syncthreads();
+  if (lane == 31) sm[warp] = inc;
+  __syncthreads();
+  u64 base = 0, tot = 0;
+  for (int i = 0; i < SHK_PLAN_THREADS / 32; ++i) { const u64 t = sm[i]; if (i < warp) base += t; tot += t; }
+  total = tot;
+  return base + inc - v;
+}
+__global__ void __launch_bounds__(SHK_PLAN_THREADS)
+k_plan_groups(const u64 *__restrict__ bstat, u32 P, u32 rcap, u32 ratio_q16, u64 budget_q16, u32 maxc,
+              u32 *__restrict__ groups /* [P + 1] */, u64 *__restrict__ gitems /* scratch [P + 1] */,
+              u32 *__restrict__ scal /* [0] groups [1] largest fill [2] most items in a group */, u64 *__restrict__ nrec_out) {
+  __shared__ u64 sm[SHK_PLAN_THREADS / 32];
+  __shared__ u32 smx[SHK_PLAN_THREADS / 32];
+  const u32 t = threadIdx.x, chunk = (P + SHK_PLAN_THREADS - 1) / SHK_PLAN_THREADS;
+  const u32 lo = min(P, t * chunk), hi = min(P, lo + chunk);
+  u64 est = 0, items = 0, nrec = 0; u32 mx = 0;
+  for (u32 i = lo; i < hi; ++i) {
+    const u64 v = bstat[i];
+    const u32 fill = (u32)v, km = (u32)(v >> 32), r = min(fill, rcap);
+    mx = max(mx, fill); nrec += r; est += (u64)km * ratio_q16; items += (u64)r + km / SHK_CB_SEG;
+  }
+  u64 tot_est, tot_items, tot_rec;
+  const u64 base_est = plan_block_scan(est, sm, tot_est);
+  const u64 base_items = plan_block_scan(items, sm, tot_items);
+  plan_block_scan(nrec, sm, tot_rec);
+  // boundaries inside the chunk
+  u64 E = base_est;
+  u64 prev_key = 0;
+  if (lo > 0 && lo < P) {
+    const u64 pe = base_est - (u64)(u32)(bstat[lo - 1] >> 32) * ratio_q16;
+    prev_key = pe / budget_q16 + (lo - 1) / maxc;
+  }
+  u32 nfl = 0;
+  for (u32 i = lo; i < hi; ++i) {
+    const u64 key = E / budget_q16 + i / maxc;
+    if (i > 0 && key != prev_key) ++nfl;
+    prev_key = key;
+    E += (u64)(u32)(bstat[i] >> 32) * ratio_q16;
+  }
+  u64 tot_fl;
+  u32 g = 1 + (u32)plan_block_scan((u64)nfl, sm, tot_fl);
+  const u32 G = 1 + (u32)tot_fl;
+  // write the group starts and the item prefix at every start
+  E = base_est; u64 I = base_items;
+  if (lo > 0 && lo < P) {
+    const u64 pe = base_est - (u64)(u32)(bstat[lo - 1] >> 32) * ratio_q16;
+    prev_key = pe / budget_q16 + (lo - 1) / maxc;
+  }
+  for (u32 i = lo; i < hi; ++i) {
+    const u64 v = bstat[i];
+    const u32 fill = (u32)v, km = (u32)(v >> 32);
+    const u64 key = E / budget_q16 + i / maxc;
+    if (i > 0 && key != prev_key) { groups[g] = i; gitems[g] = I; ++g; }
+    prev_key = key;
+    E += (u64)km * ratio_q16; I += (u64)min(fill, rcap) + km / SHK_CB_SEG;
+  }
+  if (t == 0) { groups[0] = 0; gitems[0] = 0; groups[G] = P; gitems[G] = tot_items; }
+  __syncthreads();
+  u32 most = 0;
+  for (u32 j = t; j < G; j += SHK_PLAN_THREADS) most = max(most, (u32)min(gitems[j + 1] - gitems[j], (u64)0xFFFFFFFFu));
+  for (int o = 16; o; o >>= 1) { most = max(most, __shfl_xor_sync(0xffffffffu, most, o)); mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o)); }
+  if ((t & 31) == 0) { smx[t >> 5] = most; sm[t >> 5] = mx; }
+  __syncthreads();
+  if (t == 0) {
+    for (int i = 1; i < SHK_PLAN_THREADS / 32; ++i) { most = max(most, smx[i]); mx = max(mx, (u32)sm[i]); }
+    scal[0] = P ? G : 0; scal[1] = mx; scal[2] = most; *nrec_out = tot_rec;
   }
 }
 

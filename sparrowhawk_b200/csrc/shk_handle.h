@@ -90,7 +90,12 @@ struct shk_asm {
   std::vector<uint32_t> seg_kmers;     // k-mer instances per segment (host)
   std::vector<uint32_t> seg_recs;      // records per segment (host)
   shk::DevBuf uq_rec, uq_cnt;          // K1b de-dup: per-CTA lists of distinct records + multiplicities
-  uint32_t uq_cap = 0;
+  uint32_t uq_cap = 0;                 // items per CTA list the buffers above hold
+  bool uq_retry = false;               // the last fallback was caused by the list size alone
+  uint32_t uq_need_hint = 0;           // items the last device plan needed
+  shk::DevBuf plan_scratch;            // k_plan_groups: item prefix per group start
+  uint64_t fast_positions = 0;         // n_positions the steady-state path is calibrated for (0 = not yet)
+  bool counted_fast = false;           // last count came from the device-planned path (no host-side bucket description)
   bool no_dedup = false;               // SHK_NO_DEDUP=1 in the environment: count every record (A/B measurement)
   uint32_t seg_per_bucket = 1;         // segments that must share a group (all sources of one bucket)
   uint64_t src_instances = 0;          // k-mer instances K1b will see

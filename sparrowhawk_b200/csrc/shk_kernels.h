@@ -62,10 +62,15 @@ int launch_partition(int kw, const uint64_t *bases, const uint32_t *mask, uint64
 int launch_count_buckets(int kw, const void *recs, const uint64_t *bstat, uint32_t rcap, const uint64_t *seg_off,
                          const uint32_t *seg_cnt, void *uq_rec /* nullable: per-CTA distinct-record lists (de-dup) */,
                          uint32_t *uq_cnt, uint32_t uq_cap, const uint32_t *group_start,
-                         uint32_t g_begin, uint32_t g_end, uint32_t *next_group, int k, int min_count, void *ovf_slots,
-                         uint64_t ovf_cap, uint32_t *ovf_flag, uint64_t *histo, uint64_t *node_lo, uint64_t *node_hi,
+                         uint32_t g_begin, uint32_t g_end, const uint32_t *g_end_dev /* nullable: group count planned on the device */,
+                         uint32_t *next_group, int k, int min_count, void *ovf_slots,
+                         uint64_t ovf_cap, uint32_t *ovf_flag, uint32_t *uq_flag, uint64_t *histo, uint64_t *node_lo, uint64_t *node_hi,
                          uint16_t *node_count, uint8_t *node_raw, uint32_t node_cap, uint32_t *n_nodes,
                          uint64_t *counters, cudaStream_t st);
+// device-side planning of the K1b bucket groups (steady-state runs): scal[0] groups, [1] largest bucket fill,
+// [2] most de-dup items in one group; *nrec_out = records; gitems = scratch of P + 1 u64
+int launch_plan_groups(const uint64_t *bstat, uint32_t P, uint32_t rcap, double ratio, double budget, uint32_t maxc,
+                       uint32_t *groups, uint64_t *gitems, uint32_t *scal, uint64_t *nrec_out, cudaStream_t st);
 int launch_pack_records(int kw, const void *recs, const uint64_t *bstat, uint32_t rcap, const uint64_t *dst_off, uint32_t P,
                         void *out, cudaStream_t st);
 int launch_index_nodes(int kw, void *slots, uint64_t cap, const uint64_t *node_lo, const uint64_t *node_hi, uint32_t n_nodes,

@@ -220,6 +220,46 @@ def test_assemble_contigs_match_cleaned_oracle_graph(flags):
     h.close()
 
 
+@pytest.mark.parametrize("k", [31, 63])
+def test_steady_state_path(k):
+    """Second and later runs on a handle plan the K1b groups on the device (no host round trip between
+    K1a and K1b).  Same results; stale calibration (another read set of the same size) must still be exact."""
+    seq, qual = synth.reads(41, 80_000, 30.0, 0.01)
+    h = AssemblyHelper.new(k, False, 2, 20, 0, False, False, False, False)
+    h.load_reads(seq, qual)
+    h.run()
+    assert h.stats()["device_planned"] == 0
+    o = run_oracle(seq, qual, k, 2, 20)
+    assert_parity(h, o, check_table=False)
+    h.run()
+    assert h.stats()["device_planned"] == 1
+    assert_parity(h, o, check_table=False)
+    # the reference-facing call on a calibrated handle
+    h.preprocess_reads(seq, qual)
+    assert h.stats()["device_planned"] == 1
+    h.assemble()
+    assert_parity(h, o, check_table=False)
+    assert h.preprocessing_result()["nkmers"] == o.stats()["n_nodes"]
+    # same size, other content: four times the error rate (many more distinct k-mers than calibrated for)
+    seq2, qual2 = synth.reads(42, 80_000, 30.0, 0.04)
+    assert seq2.nbytes == seq.nbytes
+    h.load_reads(seq2, qual2)
+    h.run()
+    assert_parity(h, run_oracle(seq2, qual2, k, 2, 20), check_table=False)
+    # and back, with the estimates of the noisy set
+    h.load_reads(seq, qual)
+    h.run()
+    assert_parity(h, o, check_table=False)
+    # low-complexity reads of the same size: one huge bucket, region overflow -> falls back, still exact
+    seq3 = seq.copy()
+    body = seq3.reshape(-1, 151)[:, :150]
+    body[:] = np.frombuffer(b"ACGTTGCAACGTA" * 12, np.uint8)[:150]
+    h.load_reads(seq3, qual)
+    h.run()
+    assert_parity(h, run_oracle(seq3, qual, k, 2, 20), check_table=False)
+    h.close()
+
+
 def test_errors():
     h = AssemblyHelper.new(31, False, 2, 20, 0, False, False, False, False)
     with pytest.raises(ShkError):
