@@ -7,7 +7,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libshk_b200.so")
+# SHK_LIB: another build of the same library (A/B measurements of build-time knobs)
+LIB_PATH = os.environ.get("SHK_LIB") or os.path.join(_HERE, "libshk_b200.so")
 GEN_PATH = os.path.join(_HERE, "libshk_gen.so")
 
 HISTO_BINS = 500

@@ -135,6 +135,11 @@ static uint32_t next_pow2(uint64_t x) { uint32_t p = 1; while (p < x && p < (1u 
 
 // instances a fine bucket should hold on average: all of them distinct must still
 // fit the shared-memory table of K1b at ~70 % load.
+// fill of a shared-memory table the planners aim for (SHK_LOAD overrides it for measurements)
+static double table_load() {
+  static const double v = [] { const char *e = getenv("SHK_LOAD"); double x = e ? atof(e) : 0.0; return x > 0.05 && x < 0.95 ? x : 0.55; }();
+  return v;
+}
 static uint32_t target_bucket_instances(int kw) { return (uint32_t)(count_table_slots(kw) * 0.70); }
 
 static shk_status count_impl(shk_asm *h, int /*reset*/, uint32_t P_override = 0) {
@@ -199,7 +204,7 @@ static shk_status count_impl(shk_asm *h, int /*reset*/, uint32_t P_override = 0)
 // Groups of consecutive fine buckets whose estimated distinct k-mers fit the
 // shared table at ~55 % load.  `ratio` = distinct / instances estimate.
 static void plan_groups(shk_asm *h, uint32_t first_seg, double ratio, std::vector<uint32_t> &gs) {
-  const double budget = count_table_slots(h->kw) * 0.55;
+  const double budget = count_table_slots(h->kw) * table_load();
   const uint32_t maxc = (uint32_t)count_max_group(), spb = h->seg_per_bucket;
   const uint32_t nseg = (uint32_t)h->seg_kmers.size();
   double acc = 0; uint32_t cnt = 0;
@@ -303,7 +308,7 @@ static shk_status count_filter_fast(shk_asm *h, int min_count, bool &fell_back) 
   SHK_CUDA(cudaEventRecord(h->ev[3], h->stream));
   SHK_CUDA(cudaEventRecord(h->ev[4], h->stream));
   h->st.gpu_launches += launch_table_fill(h->ovf.p, h->ovf_cap, h->kw, h->stream);
-  h->st.gpu_launches += launch_plan_groups(h->bfill.as<uint64_t>(), P, rcap, h->ratio_est, count_table_slots(h->kw) * 0.55,
+  h->st.gpu_launches += launch_plan_groups(h->bfill.as<uint64_t>(), P, rcap, h->ratio_est, count_table_slots(h->kw) * table_load(),
                                            (uint32_t)count_max_group(), h->groups.as<uint32_t>(), h->plan_scratch.as<uint64_t>(),
                                            d_flags(h) + 3, d_counters(h) + 6, h->stream);
   SHK_CUDA(cudaEventRecord(h->ev[10], h->stream));
@@ -369,7 +374,7 @@ static shk_status filter_impl(shk_asm *h, int min_count, bool histogram_only = f
   double ratio = h->ratio_est;
   for (int attempt = 0;; ++attempt) {
     // overflow table: only keys that found no room in a shared table land here
-    uint64_t ovf_cap = std::max<uint64_t>(1u << 16, ninst / (attempt ? 4 : 32));
+    uint64_t ovf_cap = std::max<uint64_t>(1u << 16, ninst / (attempt ? 4 : 512));   // spills are rare: keep the table (and its clearing) small
     SHK_TRY(h->ovf.ensure(ovf_cap * slot_bytes(h->kw)));
     h->ovf_cap = ovf_cap;
     h->st.gpu_launches += launch_table_fill(h->ovf.p, ovf_cap, h->kw, h->stream);

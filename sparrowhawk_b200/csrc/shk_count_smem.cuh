@@ -514,8 +514,9 @@ k_plan_groups(const u64 *__restrict__ bstat, u32 P, u32 rcap, u32 ratio_q16, u64
   const u32 t = threadIdx.x, chunk = (P + SHK_PLAN_THREADS - 1) / SHK_PLAN_THREADS;
   const u32 lo = min(P, t * chunk), hi = min(P, lo + chunk);
   u64 est = 0, items = 0, nrec = 0; u32 mx = 0;
+#pragma unroll 8
   for (u32 i = lo; i < hi; ++i) {
-    const u64 v = bstat[i];
+    const u64 v = __ldg(bstat + i);
     const u32 fill = (u32)v, km = (u32)(v >> 32), r = min(fill, rcap);
     mx = max(mx, fill); nrec += r; est += (u64)km * ratio_q16; items += (u64)r + km / SHK_CB_SEG;
   }
@@ -523,36 +524,47 @@ k_plan_groups(const u64 *__restrict__ bstat, u32 P, u32 rcap, u32 ratio_q16, u64
   const u64 base_est = plan_block_scan(est, sm, tot_est);
   const u64 base_items = plan_block_scan(items, sm, tot_items);
   plan_block_scan(nrec, sm, tot_rec);
-  // boundaries inside the chunk
-  u64 E = base_est;
-  u64 prev_key = 0;
-  if (lo > 0 && lo < P) {
-    const u64 pe = base_est - (u64)(u32)(bstat[lo - 1] >> 32) * ratio_q16;
-    prev_key = pe / budget_q16 + (lo - 1) / maxc;
+  // boundaries inside the chunk.  key(i) = E(i) / budget + i / maxc, both quotients kept incrementally
+  // (one 64-bit division per thread, not per bucket)
+  u64 q0 = 0, qb0 = 0; u32 c0 = 0, cn0 = maxc; u64 prev0 = 0;
+  if (lo < P) {
+    q0 = base_est / budget_q16; qb0 = q0 * budget_q16;
+    c0 = lo / maxc; cn0 = (c0 + 1) * maxc;
+    if (lo > 0) {
+      const u64 pe = base_est - (u64)(u32)(__ldg(bstat + lo - 1) >> 32) * ratio_q16;
+      prev0 = pe / budget_q16 + (lo - 1) / maxc;
+    }
   }
   u32 nfl = 0;
-  for (u32 i = lo; i < hi; ++i) {
-    const u64 key = E / budget_q16 + i / maxc;
-    if (i > 0 && key != prev_key) ++nfl;
-    prev_key = key;
-    E += (u64)(u32)(bstat[i] >> 32) * ratio_q16;
+  {
+    u64 E = base_est, q = q0, qb = qb0, prev_key = prev0; u32 c = c0, cn = cn0;
+#pragma unroll 8
+    for (u32 i = lo; i < hi; ++i) {
+      if (i == cn) { ++c; cn += maxc; }
+      const u64 key = q + c;
+      if (i > 0 && key != prev_key) ++nfl;
+      prev_key = key;
+      E += (u64)(u32)(__ldg(bstat + i) >> 32) * ratio_q16;
+      while (E >= qb + budget_q16) { ++q; qb += budget_q16; }
+    }
   }
   u64 tot_fl;
   u32 g = 1 + (u32)plan_block_scan((u64)nfl, sm, tot_fl);
   const u32 G = 1 + (u32)tot_fl;
   // write the group starts and the item prefix at every start
-  E = base_est; u64 I = base_items;
-  if (lo > 0 && lo < P) {
-    const u64 pe = base_est - (u64)(u32)(bstat[lo - 1] >> 32) * ratio_q16;
-    prev_key = pe / budget_q16 + (lo - 1) / maxc;
-  }
-  for (u32 i = lo; i < hi; ++i) {
-    const u64 v = bstat[i];
-    const u32 fill = (u32)v, km = (u32)(v >> 32);
-    const u64 key = E / budget_q16 + i / maxc;
-    if (i > 0 && key != prev_key) { groups[g] = i; gitems[g] = I; ++g; }
-    prev_key = key;
-    E += (u64)km * ratio_q16; I += (u64)min(fill, rcap) + km / SHK_CB_SEG;
+  {
+    u64 E = base_est, I = base_items, q = q0, qb = qb0, prev_key = prev0; u32 c = c0, cn = cn0;
+#pragma unroll 8
+    for (u32 i = lo; i < hi; ++i) {
+      const u64 v = __ldg(bstat + i);
+      const u32 fill = (u32)v, km = (u32)(v >> 32);
+      if (i == cn) { ++c; cn += maxc; }
+      const u64 key = q + c;
+      if (i > 0 && key != prev_key) { groups[g] = i; gitems[g] = I; ++g; }
+      prev_key = key;
+      E += (u64)km * ratio_q16; I += (u64)min(fill, rcap) + km / SHK_CB_SEG;
+      while (E >= qb + budget_q16) { ++q; qb += budget_q16; }
+    }
   }
   if (t == 0) { groups[0] = 0; gitems[0] = 0; groups[G] = P; gitems[G] = tot_items; }
   __syncthreads();

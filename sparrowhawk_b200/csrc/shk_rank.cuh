@@ -26,7 +26,9 @@
 
 namespace shk {
 
+#ifndef SHK_SPLIT_MASK
 #define SHK_SPLIT_MASK 31u
+#endif
 
 struct __align__(16) WyState { u32 ptr; u32 dist; u64 sum; };
 
