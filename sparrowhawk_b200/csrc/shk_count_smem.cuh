@@ -65,6 +65,19 @@ __device__ __forceinline__ bool smem_insert(u64 *keys, u32 *vals, int NS, u64 ke
   }
   return false;
 }
+// same, with the slot and the first probe supplied by the caller (software-pipelined decode)
+__device__ __forceinline__ bool smem_insert_at(u64 *keys, u32 *vals, int NS, u64 key, u32 e, u32 add, u32 s, u64 cur) {
+  for (int probe = 0; probe < SHK_CB_MAXPROBE; ++probe) {
+    if (cur == SHK_EMPTY64) {
+      cur = atomicCAS(&keys[s], SHK_EMPTY64, key);
+      if (cur == SHK_EMPTY64) cur = key;
+    }
+    if (cur == key) { slot_hit(vals + s, e, add); return true; }
+    s = (s + 1 == (u32)NS) ? 0u : s + 1;
+    cur = keys[s];
+  }
+  return false;
+}
 __device__ __forceinline__ bool smem_insert(U128Pair *keys, u32 *vals, int NS, u128 key, u32 e, u32 add) {
   u32 s = __umulhi(slot_hash(key), (u32)NS);
   const u64 klo = (u64)key, khi = (u64)(key >> 64);
@@ -218,14 +231,16 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
   u64 nspill = 0, ndec = 0;
   u32 ndist = 0, nb0 = 0, nb1 = 0;                                  // per-thread: distinct k-mers, spectrum bins 0 and 1
 
+  if (tid == 0) { misc[7] = g_begin + atomicAdd(next_group, 1u); misc[3] = 0; }
+  __syncthreads();
   for (;;) {
-    __syncthreads();
-    if (tid == 0) { misc[0] = g_begin + atomicAdd(next_group, 1u); misc[1] = 0; misc[2] = 0; misc[3] = 0; misc[5] = 0; }
-    __syncthreads();
-    const u32 g = misc[0];
+    // misc[7] = this CTA's next group, fetched one group ahead (thread 0, below) so that no barrier
+    // is spent on handing it out
+    const u32 g = misc[7];
     if (g >= g_end) break;
     const u32 b0 = group_start[g], nb = group_start[g + 1] - b0;
     // ---- prefix of the group's record counts (the table is empty here) ----
+    if (tid == 0) { misc[1] = 0; misc[2] = 0; misc[5] = 0; }       // nobody touches these before the next barrier
     if (warp == 0) {
       u32 run = 0;
       for (u32 base = 0; base < nb; base += 32) {
@@ -241,6 +256,7 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
       if (lane == 0) gpre[0] = 0;
     }
     __syncthreads();
+    if (tid == 0) { misc[3] = 0; misc[7] = g_begin + atomicAdd(next_group, 1u); }   // every thread has read both by now
     u32 total = gpre[nb];
     uint4 *myrec = nullptr; u32 *mycnt = nullptr;
     if (DEDUP) {
@@ -284,7 +300,7 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
         for (int o = 1; o < 32; o <<= 1) { const u32 v = __shfl_down_sync(0xffffffffu, suf, o); if (lane + o < 32) suf += v; }
         rbins[32 + lane] = misc[2] + suf - cn;                     // records with a longer run come first
         rbins[lane] = 0;
-        if (lane == 0) { misc[6] = misc[2] + suf; if (misc[2] + suf > uq_cap) atomicExch(uq_flag, 1u); }
+        if (lane == 0) { misc[6] = misc[2] + suf; misc[1] = 0; if (misc[2] + suf > uq_cap) atomicExch(uq_flag, 1u); }
       }
       __syncthreads();
       const u32 nl = misc[5];
@@ -304,8 +320,6 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
       }
       __syncthreads();
       total = min(misc[6], uq_cap);
-      if (tid == 0) misc[1] = 0;
-      __syncthreads();
     }
     // ---- decode + insert: a warp grabs 32 records at a time (dynamic, so no warp idles at the tail) ----
     if (DEDUP && KW == 1) {
@@ -332,22 +346,30 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
           S = sh >= 64 ? lo : ((hi << sh) | (lo >> (64 - sh)));
         }
         const u32 nmax = __reduce_max_sync(0xffffffffu, n);
+        u64 *tk = reinterpret_cast<u64 *>(keys);
+        // k-mer i of the item -> canonical key + edge bits, then roll to k-mer i + 1
+        auto next_kmer = [&](u32 i, u64 &key, u32 &e) {
+          const u32 b = (u32)(S >> 62);
+          const bool hl = i > 0 || hasl, hr = i + 1 < n || hasr;
+          if (fwd < rc) { key = fwd; e = (hr ? (1u << b) : 0u) | (hl ? (16u << a) : 0u); }
+          else { key = rc; e = (hl ? (1u << (a ^ 2u)) : 0u) | (hr ? (16u << (b ^ 2u)) : 0u); }
+          a = (u32)(fwd >> (2 * k - 2)) & 3u;
+          fwd = ((fwd << 2) | b) & km;
+          rc = (rc >> 2) | ((u64)(b ^ 2u) << (2 * k - 2));
+          S <<= 2;
+        };
+        // software pipeline: the slot of k-mer i + 1 is hashed and its first probe is in flight while
+        // k-mer i goes through its compare / CAS / add (a stale EMPTY is caught by the CAS, keys never change)
+        u64 key = 0, cur = 0; u32 e = 0, sl = 0;
+        if (n) { next_kmer(0, key, e); sl = __umulhi(slot_hash(key), (u32)NS); cur = tk[sl]; }
         for (u32 i = 0; i < nmax; ++i) {
+          u64 nkey = 0, ncur = 0; u32 ne = 0, nsl = 0;
+          if (i + 1 < n) { next_kmer(i + 1, nkey, ne); nsl = __umulhi(slot_hash(nkey), (u32)NS); ncur = tk[nsl]; }
           if (i < n) {
-            const u32 b = (u32)(S >> 62);
-            const bool hl = i > 0 || hasl, hr = i + 1 < n || hasr;
-            u64 key; u32 e;
-            if (fwd < rc) { key = fwd; e = (hr ? (1u << b) : 0u) | (hl ? (16u << a) : 0u); }
-            else { key = rc; e = (hl ? (1u << (a ^ 2u)) : 0u) | (hr ? (16u << (b ^ 2u)) : 0u); }
             ndec += wgt;
-            if (!smem_insert(reinterpret_cast<u64 *>(keys), vals, NS, key, e, wgt)) {
-              table_insert(ovf, (K)key, e, wgt, ovf_flag); nspill += wgt;
-            }
-            a = (u32)(fwd >> (2 * k - 2)) & 3u;
-            fwd = ((fwd << 2) | b) & km;
-            rc = (rc >> 2) | ((u64)(b ^ 2u) << (2 * k - 2));
-            S <<= 2;
+            if (!smem_insert_at(tk, vals, NS, key, e, wgt, sl, cur)) { table_insert(ovf, (K)key, e, wgt, ovf_flag); nspill += wgt; }
           }
+          key = nkey; e = ne; sl = nsl; cur = ncur;
         }
       }
     } else
