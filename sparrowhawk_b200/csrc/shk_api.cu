@@ -268,6 +268,7 @@ static shk_status index_impl(shk_asm *h);
 static bool fast_ready(shk_asm *h) {
   static const bool off = [] { const char *e = getenv("SHK_NO_FAST"); return e && e[0] == '1'; }();
   return !off && h->ratio_est > 0 && h->P && h->rcap && h->fast_positions == h->n_positions && h->n_positions > 0 &&
+         h->fast_banned_positions != h->n_positions &&
          !h->shard_world && (h->kw == 2 || h->no_dedup || h->uq_cap > 0) && h->ovf_cap > 0;
 }
 
@@ -328,6 +329,9 @@ static shk_status count_filter_fast(shk_asm *h, int min_count, bool &fell_back) 
               fl[0], fl[6], fl[4], rcap, fl[5], uq_fast);
     if (dedup) h->uq_need_hint = std::max(h->uq_need_hint, fl[5]);
     h->uq_retry = !fl[0] && fl[4] <= rcap;
+    // a full overflow table means the device planner's groups (which may exceed the budget by one bucket) do not
+    // suit this input — few, uneven buckets per group: stay on the host-planned path for read sets of this size
+    if (fl[0]) h->fast_banned_positions = h->n_positions;
     fell_back = true;
     return SHK_OK;
   }
@@ -341,6 +345,7 @@ static shk_status count_filter_fast(shk_asm *h, int min_count, bool &fell_back) 
   h->seg_kmers.clear(); h->seg_recs.clear();               // the host-side bucket description is not fetched on this path
   h->counted = true; h->counted_fast = true; h->st.device_planned = 1;
   h->st.n_spilled = h->h_pinned[4];
+  h->spill_hint = h->st.n_spilled;
   if (h->st.n_spilled) SHK_TRY(sweep_overflow(h, min_count, node_cap));
   memcpy(h->histo, h->h_pinned + 8, sizeof h->histo);
   h->histo_valid = true;
@@ -374,7 +379,10 @@ static shk_status filter_impl(shk_asm *h, int min_count, bool histogram_only = f
   double ratio = h->ratio_est;
   for (int attempt = 0;; ++attempt) {
     // overflow table: only keys that found no room in a shared table land here
-    uint64_t ovf_cap = std::max<uint64_t>(1u << 16, ninst / (attempt ? 4 : 512));   // spills are rare: keep the table (and its clearing) small
+    // Spills are rare, so the table (and its clearing) starts small: 1/512 of the instances, or four slots per
+    // instance that spilled on this handle's last run; a full table is retried at 1/32, then 1/4.
+    uint64_t ovf_cap = std::max<uint64_t>(1u << 16, ninst / (attempt == 0 ? 512 : attempt == 1 ? 32 : 4));
+    if (attempt == 0) ovf_cap = std::max<uint64_t>(ovf_cap, std::min<uint64_t>(4 * h->spill_hint, ninst / 4 + 1));
     SHK_TRY(h->ovf.ensure(ovf_cap * slot_bytes(h->kw)));
     h->ovf_cap = ovf_cap;
     h->st.gpu_launches += launch_table_fill(h->ovf.p, ovf_cap, h->kw, h->stream);
@@ -410,9 +418,11 @@ static shk_status filter_impl(shk_asm *h, int min_count, bool histogram_only = f
     uint32_t *fl = (uint32_t *)(h->h_pinned + 8 + SHK_HISTO_BINS);
     const uint64_t spilled = h->h_pinned[4];
     h->st.n_spilled = spilled; h->st.n_records = h->n_records;
-    if (fl[0]) {                                      // overflow table itself overflowed: replan denser
+    if (!fl[0]) h->spill_hint = spilled;
+    if (fl[0]) {                                      // overflow table itself overflowed: larger table, then also replan denser
       if (attempt >= 3) { set_error("k-mer overflow table full after retries"); return SHK_ERR_TABLE_FULL; }
-      ratio = std::min(1.0, ratio * 2.0); ++h->st.table_retries;
+      if (attempt >= 1) ratio = std::min(1.0, ratio * 2.0);
+      ++h->st.table_retries;
       continue;
     }
     if (spilled) {

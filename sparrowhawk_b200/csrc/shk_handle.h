@@ -84,7 +84,7 @@ struct shk_asm {
   shk::DevBuf skrecs, bfill /* u32 fill[P] | u32 kcount[P] */, groups, ovf;
   shk::PinBuf hfill;
   uint32_t P = 0, rcap = 0;
-  uint64_t n_records = 0, ovf_cap = 0;
+  uint64_t n_records = 0, ovf_cap = 0, spill_hint = 0 /* instances that spilled on the last run */;
   double ratio_est = 0;         // distinct / instances, measured by a pilot or the previous run
   // ---- K1b input description: record segments (one per local bucket, or one per (owned bucket, source rank)) ----
   std::vector<uint32_t> seg_kmers;     // k-mer instances per segment (host)
@@ -94,6 +94,7 @@ struct shk_asm {
   bool uq_retry = false;               // the last fallback was caused by the list size alone
   uint32_t uq_need_hint = 0;           // items the last device plan needed
   shk::DevBuf plan_scratch;            // k_plan_groups: item prefix per group start
+  uint64_t fast_banned_positions = 0;  // read-set size for which the device planner overflowed (host planning only)
   uint64_t fast_positions = 0;         // n_positions the steady-state path is calibrated for (0 = not yet)
   bool counted_fast = false;           // last count came from the device-planned path (no host-side bucket description)
   bool no_dedup = false;               // SHK_NO_DEDUP=1 in the environment: count every record (A/B measurement)
