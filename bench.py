@@ -44,7 +44,7 @@ L = 150
 MIN_QUAL = 20
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch, from the committed `ncu --set full`
 # capture of the same workload (profiles/r01_ncu_k1_summary.md); None where no capture exists.
-NCU_TRAFFIC = {("B", "k_count_buckets"): 624.3e6 + 13.0e6, ("B", "k_minimizer_partition"): 221.7e6 + 594.1e6}
+NCU_TRAFFIC = {("B", "k_count_buckets"): 624.2e6 + 17.0e6, ("B", "k_minimizer_partition"): 222.5e6 + 594.1e6}
 
 
 def alg_bytes_per_base(k):
@@ -60,43 +60,62 @@ def peaks():
 
 
 class ClockSampler:
+    """SM clock + throttle reasons sampled DURING the timed region (B200_PROFILING.md clocks line).
+    NVML is polled from a thread every 2 ms (the timed region is tens of ms: `nvidia-smi -lms` is too
+    coarse to land a sample in it); falls back to one nvidia-smi query if NVML is unavailable."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
-        self.p = None
+        import threading
+        self.index, self.samples, self.reasons, self.power = index, [], set(), []
+        self.stop_flag, self.thread, self.max_mhz = False, None, None
         try:
-            self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                       "-lms", "100", "-i", str(index)], stdout=subprocess.PIPE,
-                                      stderr=subprocess.DEVNULL, text=True)
+            import pynvml as N
+            N.nvmlInit()
+            self.N = N
+            self.dev = N.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = float(N.nvmlDeviceGetMaxClockInfo(self.dev, N.NVML_CLOCK_SM))
+            self.thread = threading.Thread(target=self._poll, daemon=True)
+            self.thread.start()
         except Exception:
-            self.p = None
+            self.N = None
+
+    def _poll(self):
+        N = self.N
+        names = {"hw_slowdown": getattr(N, "nvmlClocksThrottleReasonHwSlowdown", 0x8),
+                 "hw_thermal_slowdown": getattr(N, "nvmlClocksThrottleReasonHwThermalSlowdown", 0x40),
+                 "sw_thermal_slowdown": getattr(N, "nvmlClocksThrottleReasonSwThermalSlowdown", 0x20),
+                 "sw_power_cap": getattr(N, "nvmlClocksThrottleReasonSwPowerCap", 0x4)}
+        while not self.stop_flag:
+            try:
+                self.samples.append(float(N.nvmlDeviceGetClockInfo(self.dev, N.NVML_CLOCK_SM)))
+                r = N.nvmlDeviceGetCurrentClocksThrottleReasons(self.dev)
+                for n, bit in names.items():
+                    if r & bit:
+                        self.reasons.add(n)
+                self.power.append(N.nvmlDeviceGetPowerUsage(self.dev) / 1e3)
+            except Exception:
+                pass
+            time.sleep(0.002)
 
     def stop(self):
-        if not self.p:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.p.terminate()
+        if self.thread is not None:
+            self.stop_flag = True
+            self.thread.join(timeout=2)
+            sm = sorted(self.samples)
+            return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                    "samples": len(sm), "power_w_max": round(max(self.power), 1) if self.power else None, "source": "nvml, 2 ms"}
         try:
-            out, _ = self.p.communicate(timeout=5)
+            out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.index)],
+                                 capture_output=True, text=True, timeout=10).stdout
+            f = [x.strip() for x in out.splitlines()[0].split(",")]
+            names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+            return {"sm_mhz": float(f[0]), "sm_max_mhz": float(f[1]),
+                    "reasons": [n for n, v in zip(names, f[2:6]) if v.lower().startswith("active")], "samples": 1,
+                    "source": "nvidia-smi, one query after the timed region"}
         except Exception:
-            self.p.kill()
-            out = ""
-        sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for line in out.splitlines():
-            f = [x.strip() for x in line.split(",")]
-            if len(f) < 6:
-                continue
-            try:
-                sm.append(float(f[0])); mx.append(float(f[1]))
-            except ValueError:
-                continue
-            for n, v in zip(names, f[2:6]):
-                if v.lower().startswith("active"):
-                    reasons.add(n)
-        sm.sort()
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"], "samples": 0}
 
 
 def reference_arm(args, w, rank, world):

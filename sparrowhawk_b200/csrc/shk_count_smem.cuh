@@ -536,11 +536,18 @@ k_plan_groups(const u64 *__restrict__ bstat, u32 P, u32 rcap, u32 ratio_q16, u64
   const u32 t = threadIdx.x, chunk = (P + SHK_PLAN_THREADS - 1) / SHK_PLAN_THREADS;
   const u32 lo = min(P, t * chunk), hi = min(P, lo + chunk);
   u64 est = 0, items = 0, nrec = 0; u32 mx = 0;
-#pragma unroll 8
-  for (u32 i = lo; i < hi; ++i) {
-    const u64 v = __ldg(bstat + i);
-    const u32 fill = (u32)v, km = (u32)(v >> 32), r = min(fill, rcap);
-    mx = max(mx, fill); nrec += r; est += (u64)km * ratio_q16; items += (u64)r + km / SHK_CB_SEG;
+  // every pass reads the thread's buckets in batches of SHK_PLAN_BATCH independent loads
+#define SHK_PLAN_BATCH 16
+#define SHK_PLAN_LOAD(v, i0)                                                                    \
+  u64 v[SHK_PLAN_BATCH];                                                                        \
+  _Pragma("unroll") for (int j = 0; j < SHK_PLAN_BATCH; ++j) v[j] = (i0) + j < hi ? __ldg(bstat + (i0) + j) : 0ull;
+  for (u32 i0 = lo; i0 < hi; i0 += SHK_PLAN_BATCH) {
+    SHK_PLAN_LOAD(v, i0)
+#pragma unroll
+    for (int j = 0; j < SHK_PLAN_BATCH; ++j) {
+      const u32 fill = (u32)v[j], km = (u32)(v[j] >> 32), r = min(fill, rcap);     // buckets past hi read as 0
+      mx = max(mx, fill); nrec += r; est += (u64)km * ratio_q16; items += (u64)r + km / SHK_CB_SEG;
+    }
   }
   u64 tot_est, tot_items, tot_rec;
   const u64 base_est = plan_block_scan(est, sm, tot_est);
@@ -560,14 +567,20 @@ k_plan_groups(const u64 *__restrict__ bstat, u32 P, u32 rcap, u32 ratio_q16, u64
   u32 nfl = 0;
   {
     u64 E = base_est, q = q0, qb = qb0, prev_key = prev0; u32 c = c0, cn = cn0;
-#pragma unroll 8
-    for (u32 i = lo; i < hi; ++i) {
-      if (i == cn) { ++c; cn += maxc; }
-      const u64 key = q + c;
-      if (i > 0 && key != prev_key) ++nfl;
-      prev_key = key;
-      E += (u64)(u32)(__ldg(bstat + i) >> 32) * ratio_q16;
-      while (E >= qb + budget_q16) { ++q; qb += budget_q16; }
+    for (u32 i0 = lo; i0 < hi; i0 += SHK_PLAN_BATCH) {
+      SHK_PLAN_LOAD(v, i0)
+#pragma unroll
+      for (int j = 0; j < SHK_PLAN_BATCH; ++j) {
+        const u32 i = i0 + j;
+        if (i < hi) {
+          if (i == cn) { ++c; cn += maxc; }
+          const u64 key = q + c;
+          if (i > 0 && key != prev_key) ++nfl;
+          prev_key = key;
+          E += (u64)(u32)(v[j] >> 32) * ratio_q16;
+          while (E >= qb + budget_q16) { ++q; qb += budget_q16; }
+        }
+      }
     }
   }
   u64 tot_fl;
@@ -576,18 +589,24 @@ k_plan_groups(const u64 *__restrict__ bstat, u32 P, u32 rcap, u32 ratio_q16, u64
   // write the group starts and the item prefix at every start
   {
     u64 E = base_est, I = base_items, q = q0, qb = qb0, prev_key = prev0; u32 c = c0, cn = cn0;
-#pragma unroll 8
-    for (u32 i = lo; i < hi; ++i) {
-      const u64 v = __ldg(bstat + i);
-      const u32 fill = (u32)v, km = (u32)(v >> 32);
-      if (i == cn) { ++c; cn += maxc; }
-      const u64 key = q + c;
-      if (i > 0 && key != prev_key) { groups[g] = i; gitems[g] = I; ++g; }
-      prev_key = key;
-      E += (u64)km * ratio_q16; I += (u64)min(fill, rcap) + km / SHK_CB_SEG;
-      while (E >= qb + budget_q16) { ++q; qb += budget_q16; }
+    for (u32 i0 = lo; i0 < hi; i0 += SHK_PLAN_BATCH) {
+      SHK_PLAN_LOAD(v, i0)
+#pragma unroll
+      for (int j = 0; j < SHK_PLAN_BATCH; ++j) {
+        const u32 i = i0 + j;
+        if (i < hi) {
+          const u32 fill = (u32)v[j], km = (u32)(v[j] >> 32);
+          if (i == cn) { ++c; cn += maxc; }
+          const u64 key = q + c;
+          if (i > 0 && key != prev_key) { groups[g] = i; gitems[g] = I; ++g; }
+          prev_key = key;
+          E += (u64)km * ratio_q16; I += (u64)min(fill, rcap) + km / SHK_CB_SEG;
+          while (E >= qb + budget_q16) { ++q; qb += budget_q16; }
+        }
+      }
     }
   }
+#undef SHK_PLAN_LOAD
   if (t == 0) { groups[0] = 0; gitems[0] = 0; groups[G] = P; gitems[G] = tot_items; }
   __syncthreads();
   u32 most = 0;
