@@ -262,7 +262,7 @@ static shk_status index_impl(shk_asm *h);
 // ---- steady-state K1a + K1b: nothing on the host between the two kernels ----------------
 // Preconditions (fast_ready): this handle has run the host-planned path on a read set of this
 // size, so the bucket count, the region size, the distinct/instances ratio and the de-dup list
-// size are known.  The groups are planned by k_plan_groups on the stream; everything the host
+// size are known.  K1b's CTAs cut the bucket groups themselves (SelfPlan, shk_count_smem.cuh); everything the host
 // would have checked before K1b is checked after it, and any violation falls back to the
 // host-planned path (same results, one wasted pass).
 static bool fast_ready(shk_asm *h) {
@@ -286,10 +286,8 @@ static shk_status count_filter_fast(shk_asm *h, int min_count, bool &fell_back) 
   if (h->kw == 2) SHK_TRY(h->node_hi.ensure((size_t)node_cap * 8));
   SHK_TRY(h->node_count.ensure((size_t)node_cap * 2));
   SHK_TRY(h->node_raw.ensure((size_t)node_cap));
-  SHK_TRY(h->groups.ensure((size_t)(P + 2) * 4));
-  SHK_TRY(h->plan_scratch.ensure((size_t)(P + 2) * 8));
-  // de-dup lists: the device planner cuts groups differently from the host planner (up to one bucket more per
-  // group), so size them with headroom over the host-planned need, or for what the last device plan asked
+  // de-dup lists: the groups the CTAs cut for themselves differ from the host planner's (chunk ends, another
+  // ratio estimate), so size them with headroom over the host-planned need, or for what the last such run needed
   uint32_t uq_fast = 0;
   if (dedup) {
     uq_fast = (uint32_t)std::min<uint64_t>(std::max<uint64_t>((uint64_t)h->uq_cap * 2 + 1024, (uint64_t)h->uq_need_hint + h->uq_need_hint / 8), 0x7FFFFFC0ull);
@@ -309,13 +307,11 @@ static shk_status count_filter_fast(shk_asm *h, int min_count, bool &fell_back) 
   SHK_CUDA(cudaEventRecord(h->ev[3], h->stream));
   SHK_CUDA(cudaEventRecord(h->ev[4], h->stream));
   h->st.gpu_launches += launch_table_fill(h->ovf.p, h->ovf_cap, h->kw, h->stream);
-  h->st.gpu_launches += launch_plan_groups(h->bfill.as<uint64_t>(), P, rcap, h->ratio_est, count_table_slots(h->kw) * table_load(),
-                                           (uint32_t)count_max_group(), h->groups.as<uint32_t>(), h->plan_scratch.as<uint64_t>(),
-                                           d_flags(h) + 3, d_counters(h) + 6, h->stream);
+  SelfPlanArgs spa{P, h->ratio_est, count_table_slots(h->kw) * table_load(), d_flags(h) + 4, d_counters(h) + 6};
   SHK_CUDA(cudaEventRecord(h->ev[10], h->stream));
   h->st.gpu_launches += launch_count_buckets(h->kw, h->skrecs.p, h->bfill.as<uint64_t>(), rcap, nullptr, nullptr,
                                              dedup ? h->uq_rec.p : nullptr, h->uq_cnt.as<uint32_t>(), uq_fast,
-                                             h->groups.as<uint32_t>(), 0, 0, d_flags(h) + 3, d_flags(h) + 2, h->p.k, min_count,
+                                             nullptr, 0, 0, &spa, d_flags(h) + 2, h->p.k, min_count,
                                              h->ovf.p, h->ovf_cap, d_flags(h), d_flags(h) + 6, d_histo(h),
                                              h->node_lo.as<uint64_t>(), h->node_hi.as<uint64_t>(), h->node_count.as<uint16_t>(),
                                              h->node_raw.as<uint8_t>(), node_cap, d_flags(h) + 1, d_counters(h), h->stream);
@@ -654,7 +650,7 @@ void shk_asm_free(shk_asm *h) {
     DevBuf *bufs[] = {&h->bases, &h->mask, &h->ascii_seq, &h->ascii_qual, &h->slots, &h->dscal, &h->node_lo, &h->node_hi,
                       &h->node_count, &h->node_raw, &h->node_edges, &h->uniq, &h->succ, &h->tail_of, &h->len_of,
                       &h->unitig_of_head, &h->elem_unitig, &h->pd, &h->cq, &h->circ, &h->recs, &h->ucirc, &h->cov_sum,
-                      &h->useq, &h->link_from, &h->link_to, &h->gscal, &h->splitters, &h->sum_of, &h->rank_work, &h->skrecs, &h->bfill, &h->groups, &h->ovf, &h->uq_rec, &h->uq_cnt, &h->seg_off, &h->seg_cnt, &h->pack_off, &h->plan_scratch};
+                      &h->useq, &h->link_from, &h->link_to, &h->gscal, &h->splitters, &h->sum_of, &h->rank_work, &h->skrecs, &h->bfill, &h->groups, &h->ovf, &h->uq_rec, &h->uq_cnt, &h->seg_off, &h->seg_cnt, &h->pack_off};
     for (auto b : bufs) b->release();
     if (h->h_pinned) cudaFreeHost(h->h_pinned);
     h->hfill.release();

@@ -187,6 +187,18 @@ __device__ __forceinline__ uint4 record_item(uint4 c, u32 j) {
   return c;
 }
 
+// Self-planning mode (steady-state runs, group_start == null): CTAs take chunks of consecutive buckets (sized
+// by the launcher: about eight chunks per CTA, so the tail stays short while few groups are cut short by a chunk
+// end) from a global counter and cut them into groups themselves, greedily, exactly like the host planner
+// (buckets are added while the estimated distinct k-mers, instances * ratio, stay within the budget) — so
+// nothing stands between K1a and K1b on the stream.  What the host would have checked before the launch it
+// reads afterwards: stats[0] = largest bucket fill (region overflow), stats[1] = most distinct items in a
+// group (size of the de-dup lists), *nrec = records.
+struct SelfPlan {
+  u32 P; u32 chunk /* buckets per chunk, <= SHK_CB_MAXC */; u32 ratio_q16; u64 budget_q16;
+  u32 *stats; u64 *nrec;
+};
+
 struct CountOut {
   u64 *histo;                 // [500] global spectrum
   u64 *node_lo, *node_hi; uint16_t *node_count; uint8_t *node_raw;
@@ -199,8 +211,8 @@ __global__ void __launch_bounds__(SHK_CB_THREADS, SHK_CB_PER_SM)
 k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__restrict__ bstat, u32 rcap,
                 const u64 *__restrict__ seg_off, const u32 *__restrict__ seg_cnt,
                 uint4 *__restrict__ uq_rec, u32 *__restrict__ uq_cnt, u32 uq_cap /* distinct-record list, per CTA */,
-                const u32 *__restrict__ group_start, u32 g_begin, u32 g_end, const u32 *__restrict__ g_end_dev /* nullable: planned on the device */,
-                u32 *__restrict__ next_group, int k, int min_count, Table<KW> ovf, u32 *__restrict__ ovf_flag,
+                const u32 *__restrict__ group_start /* null: the CTAs cut their own groups (SelfPlan) */, u32 g_begin, u32 g_end,
+                SelfPlan sp, u32 *__restrict__ next_group, int k, int min_count, Table<KW> ovf, u32 *__restrict__ ovf_flag,
                 u32 *__restrict__ uq_flag /* set when a de-dup list is too small */, CountOut out) {
   typedef typename KeyOf<KW>::type K;
   typedef typename std::conditional<KW == 1, u64, U128Pair>::type SK;
@@ -217,7 +229,6 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
   u32 *rbins = misc + 16;                               // [32] distinct records per run length n, [32] write cursors
   unsigned short *rlist = reinterpret_cast<unsigned short *>(stage);   // record-table slots in claim order (phase 1 only)
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  if (g_end_dev) g_end = g_begin + *g_end_dev;
   uint4 *wst = stage + (size_t)warp * 32 * RECW;
   u32 *wbm = bitmaps + warp * 64;
   for (int i = tid; i < SHK_NBINS; i += SHK_CB_THREADS) hist[i] = 0;
@@ -231,17 +242,30 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
   u64 nspill = 0, ndec = 0;
   u32 ndist = 0, nb0 = 0, nb1 = 0;                                  // per-thread: distinct k-mers, spectrum bins 0 and 1
 
-  if (tid == 0) { misc[7] = g_begin + atomicAdd(next_group, 1u); misc[3] = 0; }
+  const bool self_plan = group_start == nullptr;
+  u32 sp_mxfill = 0, sp_need = 0; u64 sp_nrec = 0;                 // warp 0: what the host verifies after a self-planned run
+  if (tid == 0) { misc[7] = g_begin + atomicAdd(next_group, 1u); misc[3] = 0; misc[8] = 0; misc[9] = 0; }
   __syncthreads();
   for (;;) {
-    // misc[7] = this CTA's next group, fetched one group ahead (thread 0, below) so that no barrier
-    // is spent on handing it out
-    const u32 g = misc[7];
-    if (g >= g_end) break;
-    const u32 b0 = group_start[g], nb = group_start[g + 1] - b0;
+    // misc[7] = this CTA's next group (or next bucket chunk), fetched one ahead (thread 0, below) so that no
+    // barrier is spent on handing it out; misc[8], misc[9] = first unprocessed bucket and end of the current chunk
+    u32 b0, nb = 0, ce = 0;
+    bool took_chunk = false;
+    if (!self_plan) {
+      const u32 g = misc[7];
+      if (g >= g_end) break;
+      b0 = group_start[g]; nb = group_start[g + 1] - b0;
+    } else {
+      b0 = misc[8]; ce = misc[9];
+      if (b0 >= ce) {
+        const u64 cb = (u64)misc[7] * sp.chunk;
+        if (cb >= sp.P) break;
+        b0 = (u32)cb; ce = min(sp.P, b0 + sp.chunk); took_chunk = true;
+      }
+    }
     // ---- prefix of the group's record counts (the table is empty here) ----
     if (tid == 0) { misc[1] = 0; misc[2] = 0; misc[5] = 0; }       // nobody touches these before the next barrier
-    if (warp == 0) {
+    if (warp == 0 && !self_plan) {
       u32 run = 0;
       for (u32 base = 0; base < nb; base += 32) {
         // a segment = one dense run of records: fine bucket i of the local regions (seg_off == null), or the
@@ -254,9 +278,37 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
         run += __shfl_sync(0xffffffffu, inc, 31);
       }
       if (lane == 0) gpre[0] = 0;
+    } else if (warp == 0) {
+      // greedy cut: buckets b0, b0+1, ... while the estimated distinct k-mers stay within the budget (at least one)
+      u32 run = 0, cnt = 0; u64 acc = 0;
+      for (u32 base = 0; b0 + base < ce; base += 32) {
+        const u32 i = base + lane;
+        const bool valid = b0 + i < ce;
+        const u64 v = valid ? bstat[b0 + i] : 0ull;
+        const u32 fill = (u32)v, f = min(fill, rcap);
+        sp_mxfill = max(sp_mxfill, fill);
+        u64 est = (u64)(u32)(v >> 32) * sp.ratio_q16; u32 inc = f;
+        for (int o = 1; o < 32; o <<= 1) {
+          const u64 t = __shfl_up_sync(0xffffffffu, est, o); const u32 u = __shfl_up_sync(0xffffffffu, inc, o);
+          if (lane >= o) { est += t; inc += u; }
+        }
+        const bool fits = valid && (acc + est <= sp.budget_q16 || (cnt == 0 && lane == 0));
+        const u32 m = __ballot_sync(0xffffffffu, fits);               // a prefix of the lanes: est only grows
+        const u32 take = m == 0xFFFFFFFFu ? 32u : (u32)__ffs(~m) - 1u;
+        if ((u32)lane < take) { gpre[i + 1] = run + inc; sp_nrec += f; }
+        if (take) { run += __shfl_sync(0xffffffffu, inc, take - 1); acc += __shfl_sync(0xffffffffu, est, take - 1); }
+        cnt += take;
+        if (take < 32) break;
+      }
+      if (lane == 0) { gpre[0] = 0; misc[10] = cnt; }
     }
     __syncthreads();
-    if (tid == 0) { misc[3] = 0; misc[7] = g_begin + atomicAdd(next_group, 1u); }   // every thread has read both by now
+    if (self_plan) nb = misc[10];
+    if (tid == 0) {                                                   // every thread has read misc[3], [7], [8], [9] by now
+      misc[3] = 0;
+      if (!self_plan) misc[7] = g_begin + atomicAdd(next_group, 1u);
+      else { misc[8] = b0 + nb; misc[9] = ce; if (took_chunk) misc[7] = g_begin + atomicAdd(next_group, 1u); }
+    }
     u32 total = gpre[nb];
     uint4 *myrec = nullptr; u32 *mycnt = nullptr;
     if (DEDUP) {
@@ -300,7 +352,11 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
         for (int o = 1; o < 32; o <<= 1) { const u32 v = __shfl_down_sync(0xffffffffu, suf, o); if (lane + o < 32) suf += v; }
         rbins[32 + lane] = misc[2] + suf - cn;                     // records with a longer run come first
         rbins[lane] = 0;
-        if (lane == 0) { misc[6] = misc[2] + suf; misc[1] = 0; if (misc[2] + suf > uq_cap) atomicExch(uq_flag, 1u); }
+        if (lane == 0) {
+          misc[6] = misc[2] + suf; misc[1] = 0;
+          sp_need = max(sp_need, misc[2] + suf);
+          if (misc[2] + suf > uq_cap) atomicExch(uq_flag, 1u);
+        }
       }
       __syncthreads();
       const u32 nl = misc[5];
@@ -493,6 +549,10 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
   if (lane == 0) { if (nb0) atomicAdd(&hist[0], nb0); if (nb1) atomicAdd(&hist[1], nb1); }
   __syncthreads();
   for (int i = tid; i < SHK_NBINS; i += SHK_CB_THREADS) if (hist[i]) atomicAdd(&out.histo[i], (u64)hist[i]);
+  if (self_plan && warp == 0) {
+    for (int o = 16; o; o >>= 1) { sp_mxfill = max(sp_mxfill, __shfl_xor_sync(0xffffffffu, sp_mxfill, o)); sp_nrec += __shfl_xor_sync(0xffffffffu, sp_nrec, o); }
+    if (lane == 0) { atomicMax(sp.stats, sp_mxfill); atomicMax(sp.stats + 1, sp_need); if (sp_nrec) atomicAdd(sp.nrec, sp_nrec); }
+  }
   u64 ndist64 = ndist;
   for (int o = 16; o; o >>= 1) {
     nspill += __shfl_xor_sync(0xffffffffu, nspill, o); ndec += __shfl_xor_sync(0xffffffffu, ndec, o);
@@ -502,121 +562,6 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
     if (ndist64) atomicAdd(&out.counters[2], ndist64);
     if (nspill) atomicAdd(&out.counters[4], nspill);
     if (ndec) atomicAdd(&out.counters[5], ndec);
-  }
-}
-
-// ---- device-side group planning -------------------------------------------------
-// Steady-state runs (shk_run on a handle that has already measured distinct/instances
-// for a read set of this size) plan the bucket groups of K1b on the device, right
-// behind K1a on the stream, so the host never waits for the bucket fills.
-// Bucket i opens a new group when floor(E(i) / budget) + floor(i / maxc) changes, E =
-// exclusive prefix of the estimated distinct k-mers (instances * ratio): a group holds
-// at most `budget` + one bucket of them and at most maxc buckets.  Also returns what
-// the host must verify after the run: the largest bucket fill (region overflow), the
-// record total and the largest item count of a group (size of the de-dup lists).
-#define SHK_PLAN_THREADS 1024
-__device__ __forceinline__ u64 plan_block_scan(u64 v, u64 *sm, u64 &total) {       // exclusive prefix over the CTA
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  u64 inc = v;
-  for (int o = 1; o < 32; o <<= 1) { const u64 t = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += t; }
-  __syncthreads();
-  if (lane == 31) sm[warp] = inc;
-  __syncthreads();
-  u64 base = 0, tot = 0;
-  for (int i = 0; i < SHK_PLAN_THREADS / 32; ++i) { const u64 t = sm[i]; if (i < warp) base += t; tot += t; }
-  total = tot;
-  return base + inc - v;
-}
-__global__ void __launch_bounds__(SHK_PLAN_THREADS)
-k_plan_groups(const u64 *__restrict__ bstat, u32 P, u32 rcap, u32 ratio_q16, u64 budget_q16, u32 maxc,
-              u32 *__restrict__ groups /* [P + 1] */, u64 *__restrict__ gitems /* scratch [P + 1] */,
-              u32 *__restrict__ scal /* [0] groups [1] largest fill [2] most items in a group */, u64 *__restrict__ nrec_out) {
-  __shared__ u64 sm[SHK_PLAN_THREADS / 32];
-  __shared__ u32 smx[SHK_PLAN_THREADS / 32];
-  const u32 t = threadIdx.x, chunk = (P + SHK_PLAN_THREADS - 1) / SHK_PLAN_THREADS;
-  const u32 lo = min(P, t * chunk), hi = min(P, lo + chunk);
-  u64 est = 0, items = 0, nrec = 0; u32 mx = 0;
-  // every pass reads the thread's buckets in batches of SHK_PLAN_BATCH independent loads
-#define SHK_PLAN_BATCH 16
-#define SHK_PLAN_LOAD(v, i0)                                                                    \
-  u64 v[SHK_PLAN_BATCH];                                                                        \
-  _Pragma("unroll") for (int j = 0; j < SHK_PLAN_BATCH; ++j) v[j] = (i0) + j < hi ? __ldg(bstat + (i0) + j) : 0ull;
-  for (u32 i0 = lo; i0 < hi; i0 += SHK_PLAN_BATCH) {
-    SHK_PLAN_LOAD(v, i0)
-#pragma unroll
-    for (int j = 0; j < SHK_PLAN_BATCH; ++j) {
-      const u32 fill = (u32)v[j], km = (u32)(v[j] >> 32), r = min(fill, rcap);     // buckets past hi read as 0
-      mx = max(mx, fill); nrec += r; est += (u64)km * ratio_q16; items += (u64)r + km / SHK_CB_SEG;
-    }
-  }
-  u64 tot_est, tot_items, tot_rec;
-  const u64 base_est = plan_block_scan(est, sm, tot_est);
-  const u64 base_items = plan_block_scan(items, sm, tot_items);
-  plan_block_scan(nrec, sm, tot_rec);
-  // boundaries inside the chunk.  key(i) = E(i) / budget + i / maxc, both quotients kept incrementally
-  // (one 64-bit division per thread, not per bucket)
-  u64 q0 = 0, qb0 = 0; u32 c0 = 0, cn0 = maxc; u64 prev0 = 0;
-  if (lo < P) {
-    q0 = base_est / budget_q16; qb0 = q0 * budget_q16;
-    c0 = lo / maxc; cn0 = (c0 + 1) * maxc;
-    if (lo > 0) {
-      const u64 pe = base_est - (u64)(u32)(__ldg(bstat + lo - 1) >> 32) * ratio_q16;
-      prev0 = pe / budget_q16 + (lo - 1) / maxc;
-    }
-  }
-  u32 nfl = 0;
-  {
-    u64 E = base_est, q = q0, qb = qb0, prev_key = prev0; u32 c = c0, cn = cn0;
-    for (u32 i0 = lo; i0 < hi; i0 += SHK_PLAN_BATCH) {
-      SHK_PLAN_LOAD(v, i0)
-#pragma unroll
-      for (int j = 0; j < SHK_PLAN_BATCH; ++j) {
-        const u32 i = i0 + j;
-        if (i < hi) {
-          if (i == cn) { ++c; cn += maxc; }
-          const u64 key = q + c;
-          if (i > 0 && key != prev_key) ++nfl;
-          prev_key = key;
-          E += (u64)(u32)(v[j] >> 32) * ratio_q16;
-          while (E >= qb + budget_q16) { ++q; qb += budget_q16; }
-        }
-      }
-    }
-  }
-  u64 tot_fl;
-  u32 g = 1 + (u32)plan_block_scan((u64)nfl, sm, tot_fl);
-  const u32 G = 1 + (u32)tot_fl;
-  // write the group starts and the item prefix at every start
-  {
-    u64 E = base_est, I = base_items, q = q0, qb = qb0, prev_key = prev0; u32 c = c0, cn = cn0;
-    for (u32 i0 = lo; i0 < hi; i0 += SHK_PLAN_BATCH) {
-      SHK_PLAN_LOAD(v, i0)
-#pragma unroll
-      for (int j = 0; j < SHK_PLAN_BATCH; ++j) {
-        const u32 i = i0 + j;
-        if (i < hi) {
-          const u32 fill = (u32)v[j], km = (u32)(v[j] >> 32);
-          if (i == cn) { ++c; cn += maxc; }
-          const u64 key = q + c;
-          if (i > 0 && key != prev_key) { groups[g] = i; gitems[g] = I; ++g; }
-          prev_key = key;
-          E += (u64)km * ratio_q16; I += (u64)min(fill, rcap) + km / SHK_CB_SEG;
-          while (E >= qb + budget_q16) { ++q; qb += budget_q16; }
-        }
-      }
-    }
-  }
-#undef SHK_PLAN_LOAD
-  if (t == 0) { groups[0] = 0; gitems[0] = 0; groups[G] = P; gitems[G] = tot_items; }
-  __syncthreads();
-  u32 most = 0;
-  for (u32 j = t; j < G; j += SHK_PLAN_THREADS) most = max(most, (u32)min(gitems[j + 1] - gitems[j], (u64)0xFFFFFFFFu));
-  for (int o = 16; o; o >>= 1) { most = max(most, __shfl_xor_sync(0xffffffffu, most, o)); mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o)); }
-  if ((t & 31) == 0) { smx[t >> 5] = most; sm[t >> 5] = mx; }
-  __syncthreads();
-  if (t == 0) {
-    for (int i = 1; i < SHK_PLAN_THREADS / 32; ++i) { most = max(most, smx[i]); mx = max(mx, (u32)sm[i]); }
-    scal[0] = P ? G : 0; scal[1] = mx; scal[2] = most; *nrec_out = tot_rec;
   }
 }
 

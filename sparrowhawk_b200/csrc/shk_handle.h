@@ -93,7 +93,6 @@ struct shk_asm {
   uint32_t uq_cap = 0;                 // items per CTA list the buffers above hold
   bool uq_retry = false;               // the last fallback was caused by the list size alone
   uint32_t uq_need_hint = 0;           // items the last device plan needed
-  shk::DevBuf plan_scratch;            // k_plan_groups: item prefix per group start
   uint64_t fast_banned_positions = 0;  // read-set size for which the device planner overflowed (host planning only)
   uint64_t fast_positions = 0;         // n_positions the steady-state path is calibrated for (0 = not yet)
   bool counted_fast = false;           // last count came from the device-planned path (no host-side bucket description)

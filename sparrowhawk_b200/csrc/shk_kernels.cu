@@ -704,11 +704,20 @@ int launch_partition(int kw, const uint64_t *bases, const uint32_t *mask, uint64
 
 int launch_count_buckets(int kw, const void *recs, const uint64_t *bstat, uint32_t rcap, const uint64_t *seg_off,
                          const uint32_t *seg_cnt, void *uq_rec, uint32_t *uq_cnt, uint32_t uq_cap, const uint32_t *group_start,
-                         uint32_t g_begin, uint32_t g_end, const uint32_t *g_end_dev, uint32_t *next_group, int k, int min_count, void *ovf_slots,
+                         uint32_t g_begin, uint32_t g_end, const SelfPlanArgs *self_plan, uint32_t *next_group, int k, int min_count, void *ovf_slots,
                          uint64_t ovf_cap, uint32_t *ovf_flag, uint32_t *uq_flag, uint64_t *histo, uint64_t *node_lo, uint64_t *node_hi,
                          uint16_t *node_count, uint8_t *node_raw, uint32_t node_cap, uint32_t *n_nodes,
                          uint64_t *counters, cudaStream_t st) {
-  if (!g_end_dev && g_end <= g_begin) return 0;
+  if (group_start && g_end <= g_begin) return 0;
+  SelfPlan sp{0, 1, 0, 1, nullptr, nullptr};
+  if (!group_start) {
+    if (!self_plan || !self_plan->n_buckets) return 0;
+    u32 rq = (u32)(self_plan->ratio * 65536.0 + 0.5);
+    u64 bq = (u64)(self_plan->budget * 65536.0);
+    u32 chunk = 16;                                       // ~8 chunks per CTA, a power of two in [16, SHK_CB_MAXC]
+    while (chunk < SHK_CB_MAXC && (u64)chunk * 2 * 8 * (u64)count_ctas() <= self_plan->n_buckets) chunk *= 2;
+    sp = SelfPlan{self_plan->n_buckets, chunk, rq < 1 ? 1u : rq, bq < 1 ? 1ull : bq, self_plan->stats, (u64 *)self_plan->nrec};
+  }
   static bool attr_set = false;
   if (!attr_set) {
     cudaFuncSetAttribute(k_count_buckets<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cb_smem_bytes<1>());
@@ -717,29 +726,19 @@ int launch_count_buckets(int kw, const void *recs, const uint64_t *bstat, uint32
     attr_set = true;
   }
   unsigned grid = (unsigned)sm_count() * SHK_CB_PER_SM;
-  if (!g_end_dev && grid > g_end - g_begin) grid = g_end - g_begin;
+  if (group_start && grid > g_end - g_begin) grid = g_end - g_begin;
   u32 mp = (u32)(ovf_cap < 4096 ? ovf_cap : 4096);
   CountOut out{(u64 *)histo, (u64 *)node_lo, (u64 *)node_hi, node_count, node_raw, node_cap, n_nodes, (u64 *)counters};
   // record-level de-duplication needs the per-CTA list of distinct records (k <= 31 only for now)
   if (kw == 1 && uq_rec && uq_cap)
     k_count_buckets<1, true><<<grid, SHK_CB_THREADS, cb_smem_bytes<1>(), st>>>((const uint4 *)recs, (const u64 *)bstat, rcap, (const u64 *)seg_off, seg_cnt,
-        (uint4 *)uq_rec, uq_cnt, uq_cap, group_start, g_begin, g_end, g_end_dev, next_group, k, min_count, Table<1>{(Slot1 *)ovf_slots, ovf_cap, mp}, ovf_flag, uq_flag, out);
+        (uint4 *)uq_rec, uq_cnt, uq_cap, group_start, g_begin, g_end, sp, next_group, k, min_count, Table<1>{(Slot1 *)ovf_slots, ovf_cap, mp}, ovf_flag, uq_flag, out);
   else if (kw == 1)
     k_count_buckets<1, false><<<grid, SHK_CB_THREADS, cb_smem_bytes<1>(), st>>>((const uint4 *)recs, (const u64 *)bstat, rcap, (const u64 *)seg_off, seg_cnt,
-        nullptr, nullptr, 0, group_start, g_begin, g_end, g_end_dev, next_group, k, min_count, Table<1>{(Slot1 *)ovf_slots, ovf_cap, mp}, ovf_flag, uq_flag, out);
+        nullptr, nullptr, 0, group_start, g_begin, g_end, sp, next_group, k, min_count, Table<1>{(Slot1 *)ovf_slots, ovf_cap, mp}, ovf_flag, uq_flag, out);
   else
     k_count_buckets<2, false><<<grid, SHK_CB_THREADS, cb_smem_bytes<2>(), st>>>((const Rec32 *)recs, (const u64 *)bstat, rcap, (const u64 *)seg_off, seg_cnt,
-        nullptr, nullptr, 0, group_start, g_begin, g_end, g_end_dev, next_group, k, min_count, Table<2>{(Slot2 *)ovf_slots, ovf_cap, mp}, ovf_flag, uq_flag, out);
-  return 1;
-}
-
-int launch_plan_groups(const uint64_t *bstat, uint32_t P, uint32_t rcap, double ratio, double budget, uint32_t maxc,
-                       uint32_t *groups, uint64_t *gitems, uint32_t *scal, uint64_t *nrec_out, cudaStream_t st) {
-  u32 rq = (u32)(ratio * 65536.0 + 0.5);
-  if (rq < 1) rq = 1;
-  u64 bq = (u64)(budget * 65536.0);
-  if (bq < 1) bq = 1;
-  k_plan_groups<<<1, SHK_PLAN_THREADS, 0, st>>>((const u64 *)bstat, P, rcap, rq, bq, maxc ? maxc : 1u, groups, (u64 *)gitems, scal, (u64 *)nrec_out);
+        nullptr, nullptr, 0, group_start, g_begin, g_end, sp, next_group, k, min_count, Table<2>{(Slot2 *)ovf_slots, ovf_cap, mp}, ovf_flag, uq_flag, out);
   return 1;
 }
 

@@ -58,19 +58,18 @@ int count_max_group();
 int count_ctas();          // CTAs of one K1b launch (sizes the per-CTA de-dup lists)
 int launch_partition(int kw, const uint64_t *bases, const uint32_t *mask, uint64_t nwords, int k, uint32_t P,
                      uint32_t rcap, void *recs, uint64_t *bstat /* [P]: records | k-mers << 32 */, uint64_t *counters, cudaStream_t st);
+// group_start == null: the CTAs cut their own groups (steady-state runs).  stats (device, zeroed by the caller):
+// [0] largest bucket fill, [1] most distinct items in a group; *nrec (device, zeroed): records counted.
+struct SelfPlanArgs { uint32_t n_buckets; double ratio; double budget; uint32_t *stats; uint64_t *nrec; };
 // seg_off / seg_cnt (nullable): explicit record segments (sharded path); null = segment i is local bucket region i
 int launch_count_buckets(int kw, const void *recs, const uint64_t *bstat, uint32_t rcap, const uint64_t *seg_off,
                          const uint32_t *seg_cnt, void *uq_rec /* nullable: per-CTA distinct-record lists (de-dup) */,
                          uint32_t *uq_cnt, uint32_t uq_cap, const uint32_t *group_start,
-                         uint32_t g_begin, uint32_t g_end, const uint32_t *g_end_dev /* nullable: group count planned on the device */,
+                         uint32_t g_begin, uint32_t g_end, const SelfPlanArgs *self_plan /* used when group_start is null */,
                          uint32_t *next_group, int k, int min_count, void *ovf_slots,
                          uint64_t ovf_cap, uint32_t *ovf_flag, uint32_t *uq_flag, uint64_t *histo, uint64_t *node_lo, uint64_t *node_hi,
                          uint16_t *node_count, uint8_t *node_raw, uint32_t node_cap, uint32_t *n_nodes,
                          uint64_t *counters, cudaStream_t st);
-// device-side planning of the K1b bucket groups (steady-state runs): scal[0] groups, [1] largest bucket fill,
-// [2] most de-dup items in one group; *nrec_out = records; gitems = scratch of P + 1 u64
-int launch_plan_groups(const uint64_t *bstat, uint32_t P, uint32_t rcap, double ratio, double budget, uint32_t maxc,
-                       uint32_t *groups, uint64_t *gitems, uint32_t *scal, uint64_t *nrec_out, cudaStream_t st);
 int launch_pack_records(int kw, const void *recs, const uint64_t *bstat, uint32_t rcap, const uint64_t *dst_off, uint32_t P,
                         void *out, cudaStream_t st);
 int launch_index_nodes(int kw, void *slots, uint64_t cap, const uint64_t *node_lo, const uint64_t *node_hi, uint32_t n_nodes,
