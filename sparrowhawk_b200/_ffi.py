@@ -53,9 +53,9 @@ SYMBOLS = {
     "shk_asm_preprocess_push": (C.c_int, [_H, _U8P, C.c_size_t]),
     "shk_asm_preprocess_finish": (C.c_int, [_H]),
     "shk_asm_preprocess_reads": (C.c_int, [_H, _U8P, _U8P, C.c_size_t]),
-    "shk_asm_preprocessing_info": (C.c_int, [_H, C.POINTER(C.c_char_p), C.POINTER(C.c_size_t)]),
+    "shk_asm_preprocessing_info": (C.c_int, [_H, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]),
     "shk_asm_assemble": (C.c_int, [_H]),
-    "shk_asm_get_assembly": (C.c_int, [_H, C.POINTER(C.c_char_p), C.POINTER(C.c_size_t)]),
+    "shk_asm_get_assembly": (C.c_int, [_H, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]),
     "shk_last_error": (C.c_char_p, []),
     "shk_abi_version": (C.c_int, []),
     "shk_set_stream": (C.c_int, [_H, C.c_void_p]),

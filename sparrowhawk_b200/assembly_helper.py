@@ -29,6 +29,16 @@ def _buf(a):
     raise TypeError(f"unsupported buffer type {type(a)}")
 
 
+_decode_latin1 = C.pythonapi.PyUnicode_DecodeLatin1
+_decode_latin1.restype = C.py_object
+_decode_latin1.argtypes = [C.c_void_p, C.c_ssize_t, C.c_char_p]
+
+
+def _ascii_str(ptr, n):
+    """The library's JSON is plain ASCII: one copy straight into a str (no bytes object in between)."""
+    return _decode_latin1(ptr, n, None) if n else ""
+
+
 def _read_contigs(lib, c):
     n, nb, nl, nt, nbub = (C.c_size_t() for _ in range(5))
     check(lib.shk_contigs_sizes(c, C.byref(n), C.byref(nb), C.byref(nl), C.byref(nt), C.byref(nbub)))
@@ -117,17 +127,17 @@ class AssemblyHelper:
         check(self._lib.shk_asm_preprocess_files(self._h, str(file1).encode(), p2))
 
     def get_preprocessing_info(self) -> str:
-        s, n = C.c_char_p(), C.c_size_t()
+        s, n = C.c_void_p(), C.c_size_t()
         check(self._lib.shk_asm_preprocessing_info(self._h, C.byref(s), C.byref(n)))
-        return C.string_at(s, n.value).decode()
+        return _ascii_str(s, n.value)
 
     def assemble(self):
         check(self._lib.shk_asm_assemble(self._h))
 
     def get_assembly(self) -> str:
-        s, n = C.c_char_p(), C.c_size_t()
+        s, n = C.c_void_p(), C.c_size_t()
         check(self._lib.shk_asm_get_assembly(self._h, C.byref(s), C.byref(n)))
-        return C.string_at(s, n.value).decode()
+        return _ascii_str(s, n.value)
 
     # ---- other preprocess forms of the C ABI ----------------------------
     def preprocess_reads(self, seq, qual=None):

@@ -653,7 +653,7 @@ void shk_asm_free(shk_asm *h) {
                       &h->useq, &h->link_from, &h->link_to, &h->gscal, &h->splitters, &h->sum_of, &h->rank_work, &h->skrecs, &h->bfill, &h->groups, &h->ovf, &h->uq_rec, &h->uq_cnt, &h->seg_off, &h->seg_cnt, &h->pack_off};
     for (auto b : bufs) b->release();
     if (h->h_pinned) cudaFreeHost(h->h_pinned);
-    h->hfill.release();
+    h->hfill.release(); h->pin_stage.release();
     for (auto &e : h->ev) if (e) cudaEventDestroy(e);
     if (h->own_stream) cudaStreamDestroy(h->own_stream);
   }
@@ -758,11 +758,13 @@ shk_status fetch_unitigs(shk_asm *h) {
   u.link_from.assign(h->st.n_links, 0); u.link_to.assign(h->st.n_links, 0); u.kc.assign(nu, 0);
   if (nu) {
     struct Rec { uint32_t head, len; uint64_t off; };
-    std::vector<Rec> recs(nu); std::vector<uint64_t> cs(nu); std::vector<char> raw(h->st.unitig_bases);
+    std::vector<Rec> recs(nu); std::vector<uint64_t> cs(nu);
+    SHK_TRY(h->pin_stage.ensure_host(h->st.unitig_bases + 64));      // pinned: the sequence copy runs at link rate
+    const char *raw = (const char *)h->pin_stage.p;
     SHK_CUDA(cudaMemcpyAsync(recs.data(), h->recs.p, nu * sizeof(Rec), cudaMemcpyDeviceToHost, h->stream));
     SHK_CUDA(cudaMemcpyAsync(cs.data(), h->cov_sum.p, nu * 8, cudaMemcpyDeviceToHost, h->stream));
     SHK_CUDA(cudaMemcpyAsync(u.circ.data(), h->ucirc.p, nu, cudaMemcpyDeviceToHost, h->stream));
-    SHK_CUDA(cudaMemcpyAsync(raw.data(), h->useq.p, raw.size(), cudaMemcpyDeviceToHost, h->stream));
+    SHK_CUDA(cudaMemcpyAsync(h->pin_stage.p, h->useq.p, h->st.unitig_bases, cudaMemcpyDeviceToHost, h->stream));
     if (h->st.n_links) {
       SHK_CUDA(cudaMemcpyAsync(u.link_from.data(), h->link_from.p, h->st.n_links * 4, cudaMemcpyDeviceToHost, h->stream));
       SHK_CUDA(cudaMemcpyAsync(u.link_to.data(), h->link_to.p, h->st.n_links * 4, cudaMemcpyDeviceToHost, h->stream));
@@ -772,7 +774,7 @@ shk_status fetch_unitigs(shk_asm *h) {
     for (size_t i = 0; i < nu; ++i) {
       size_t len = recs[i].len + k - 1;
       u.off[i] = p;
-      memcpy(u.seq.data() + p, raw.data() + recs[i].off, len);
+      memcpy(u.seq.data() + p, raw + recs[i].off, len);
       u.cov[i] = (float)((double)cs[i] / (double)recs[i].len);
       u.kc[i] = cs[i];
       p += len;

@@ -212,35 +212,59 @@ shk_status build_assembly_json(shk_asm *h) {
   progress(h, "assembly:saving");
   size_t total = 0;
   for (auto &s : g.seq) total += s.size();
-  std::string fasta, gfa, gfa2, dot;          // escaped JSON string bodies
-  fasta.reserve(total + nc * 64 + 64); gfa.reserve(total + nc * 96 + g.link_from.size() * 40 + 64);
-  gfa2.reserve(total + nc * 96 + g.link_from.size() * 72 + 64); dot.reserve(nc * 80 + g.link_from.size() * 40 + 64);
+  const size_t nl = g.link_from.size();
+  // the four texts are written one after the other straight into the JSON string (escaped form)
+  std::string &j = h->json_asm;
+  j.clear();
+  j.reserve(3 * total + nc * 360 + nl * 160 + 256);
   char line[256];
-  json_escape_into(gfa, "H\tVN:Z:1.0\n");
-  json_escape_into(gfa2, "H\tVN:Z:2.0\n");
-  json_escape_into(dot, "digraph sparrowhawk {\n");
-  for (size_t i = 0; i < nc; ++i) {
-    const std::string &sq = g.seq[i];
-    const size_t nk = sq.size() - (size_t)k + 1;                 // k-mers in the contig
-    const double cov = (double)g.kc[i] / (double)nk;
-    snprintf(line, sizeof line, ">contig_%zu len=%zu cov=%.2f%s\n", i + 1, sq.size(), cov, g.circ[i] ? " circular=true" : "");
-    json_escape_into(fasta, line); fasta += sq; fasta += "\\n";
-    snprintf(line, sizeof line, "S\t%zu\t", i + 1); json_escape_into(gfa, line); gfa += sq;
-    snprintf(line, sizeof line, "\tLN:i:%zu\tKC:i:%llu\tdp:f:%.2f\n", sq.size(), (unsigned long long)g.kc[i], cov);
-    json_escape_into(gfa, line);
-    snprintf(line, sizeof line, "S\t%zu\t%zu\t", i + 1, sq.size()); json_escape_into(gfa2, line); gfa2 += sq;
-    snprintf(line, sizeof line, "\tKC:i:%llu\n", (unsigned long long)g.kc[i]); json_escape_into(gfa2, line);
-    snprintf(line, sizeof line, "  %zu [label=\"contig_%zu len=%zu cov=%.2f\"];\n", i + 1, i + 1, sq.size(), cov);
-    json_escape_into(dot, line);
-  }
-  for (size_t i = 0; i < g.link_from.size(); ++i) {
-    // each undirected join is stored in both directions; report the smaller of the two spellings once
+  auto cov_of = [&](size_t i) { return (double)g.kc[i] / (double)(g.seq[i].size() - (size_t)k + 1); };
+  // a link is stored in both directions; each join is reported once, in its smaller spelling
+  auto reported = [&](size_t i) {
     const uint32_t f = g.link_from[i], t = g.link_to[i];
-    const uint32_t mf = t ^ 1u, mt = f ^ 1u;                      // the mirrored spelling
-    if (std::make_pair(mf, mt) < std::make_pair(f, t)) continue;
+    return !(std::make_pair(t ^ 1u, f ^ 1u) < std::make_pair(f, t));
+  };
+  j += "{\"outfasta\":\"";
+  for (size_t i = 0; i < nc; ++i) {
+    snprintf(line, sizeof line, ">contig_%zu len=%zu cov=%.2f%s\n", i + 1, g.seq[i].size(), cov_of(i), g.circ[i] ? " circular=true" : "");
+    json_escape_into(j, line); j += g.seq[i]; j += "\\n";
+  }
+  j += "\",\"ncontigs\":" + std::to_string(nc) + ",\"outdot\":\"";
+  json_escape_into(j, "digraph sparrowhawk {\n");
+  for (size_t i = 0; i < nc; ++i) {
+    snprintf(line, sizeof line, "  %zu [label=\"contig_%zu len=%zu cov=%.2f\"];\n", i + 1, i + 1, g.seq[i].size(), cov_of(i));
+    json_escape_into(j, line);
+  }
+  for (size_t i = 0; i < nl; ++i) {
+    if (!reported(i)) continue;
+    const uint32_t f = g.link_from[i], t = g.link_to[i];
+    snprintf(line, sizeof line, "  %u -> %u [label=\"%c%c\"];\n", (f >> 1) + 1, (t >> 1) + 1, (f & 1u) ? '-' : '+', (t & 1u) ? '-' : '+');
+    json_escape_into(j, line);
+  }
+  json_escape_into(j, "}\n");
+  j += "\",\"outgfa\":\"";
+  json_escape_into(j, "H\tVN:Z:1.0\n");
+  for (size_t i = 0; i < nc; ++i) {
+    snprintf(line, sizeof line, "S\t%zu\t", i + 1); json_escape_into(j, line); j += g.seq[i];
+    snprintf(line, sizeof line, "\tLN:i:%zu\tKC:i:%llu\tdp:f:%.2f\n", g.seq[i].size(), (unsigned long long)g.kc[i], cov_of(i));
+    json_escape_into(j, line);
+  }
+  for (size_t i = 0; i < nl; ++i) {
+    if (!reported(i)) continue;
+    const uint32_t f = g.link_from[i], t = g.link_to[i];
+    snprintf(line, sizeof line, "L\t%u\t%c\t%u\t%c\t%dM\n", (f >> 1) + 1, (f & 1u) ? '-' : '+', (t >> 1) + 1, (t & 1u) ? '-' : '+', k - 1);
+    json_escape_into(j, line);
+  }
+  j += "\",\"outgfav2\":\"";
+  json_escape_into(j, "H\tVN:Z:2.0\n");
+  for (size_t i = 0; i < nc; ++i) {
+    snprintf(line, sizeof line, "S\t%zu\t%zu\t", i + 1, g.seq[i].size()); json_escape_into(j, line); j += g.seq[i];
+    snprintf(line, sizeof line, "\tKC:i:%llu\n", (unsigned long long)g.kc[i]); json_escape_into(j, line);
+  }
+  for (size_t i = 0; i < nl; ++i) {
+    if (!reported(i)) continue;
+    const uint32_t f = g.link_from[i], t = g.link_to[i];
     const uint32_t a = f >> 1, ao = f & 1u, b = t >> 1, bo = t & 1u;
-    snprintf(line, sizeof line, "L\t%u\t%c\t%u\t%c\t%dM\n", a + 1, ao ? '-' : '+', b + 1, bo ? '-' : '+', k - 1);
-    json_escape_into(gfa, line);
     // GFA2 edge: overlap of k-1 bases at the matching ends
     const size_t la = g.seq[a].size(), lb = g.seq[b].size();
     const size_t ab = ao ? 0 : la - (size_t)(k - 1), ae = ao ? (size_t)(k - 1) : la;
@@ -248,19 +272,8 @@ shk_status build_assembly_json(shk_asm *h) {
     snprintf(line, sizeof line, "E\t*\t%u%c\t%u%c\t%zu%s\t%zu%s\t%zu%s\t%zu%s\t%dM\n", a + 1, ao ? '-' : '+', b + 1,
              bo ? '-' : '+', ab, ab == la ? "$" : "", ae, ae == la ? "$" : "", bb, bb == lb ? "$" : "", be,
              be == lb ? "$" : "", k - 1);
-    json_escape_into(gfa2, line);
-    snprintf(line, sizeof line, "  %u -> %u [label=\"%c%c\"];\n", a + 1, b + 1, ao ? '-' : '+', bo ? '-' : '+');
-    json_escape_into(dot, line);
+    json_escape_into(j, line);
   }
-  json_escape_into(dot, "}\n");
-  std::string &j = h->json_asm;
-  j.clear();
-  j.reserve(fasta.size() + gfa.size() + gfa2.size() + dot.size() + 128);
-  j += "{\"outfasta\":\""; j += fasta;
-  j += "\",\"ncontigs\":" + std::to_string(nc);
-  j += ",\"outdot\":\""; j += dot;
-  j += "\",\"outgfa\":\""; j += gfa;
-  j += "\",\"outgfav2\":\""; j += gfa2;
   j += "\"}";
   return SHK_OK;
 }

@@ -62,7 +62,7 @@ def test_no_device_means_no_compute():
         assert L.shk_asm_preprocess_reads(h, seq, None, len(seq)) == 2
         assert L.shk_asm_assemble(h) == 2
         assert b"no CPU path" in L.shk_last_error()
-        s, n = C.c_char_p(), C.c_size_t()
+        s, n = C.c_void_p(), C.c_size_t()
         assert L.shk_asm_preprocessing_info(h, C.byref(s), C.byref(n)) == 8   # SHK_ERR_STATE
     finally:
         L.shk_asm_free(h)
