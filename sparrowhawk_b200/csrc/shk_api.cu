@@ -109,12 +109,74 @@ static shk_status pack_from_device(shk_asm *h, const uint8_t *d_seq, const uint8
   h->nwords = total;
   h->n_positions += n;
   h->counted = h->filtered = h->graphed = false;
+  h->partition_done = false;
+  return SHK_OK;
+}
+
+static bool fast_ready_for(shk_asm *h, uint64_t n_positions);
+static shk_status fast_prologue(shk_asm *h);
+// Steady-state form of the load (a calibrated handle, see count_filter_fast): the host->device copy runs in
+// slices on a second stream, and K0 of slice i and K1a of slice i-1 (its halo reaches into slice i) run on the
+// main stream underneath the copy of slice i+1.  Leaves the reads packed AND cut into records.
+static shk_status load_reads_overlapped(shk_asm *h, const uint8_t *seq, const uint8_t *qual, size_t n) {
+  const int S = 8;
+  const uint64_t tile_pos = (uint64_t)partition_tile_words() * 32;
+  const uint64_t slice = ((n + S - 1) / S + tile_pos - 1) / tile_pos * tile_pos;       // positions per slice, whole K1a tiles
+  if (!h->copy_stream) {
+    SHK_CUDA(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+    for (auto &e : h->copy_ev) SHK_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  }
+  SHK_CUDA(cudaEventRecord(h->ev[0], h->stream));
+  SHK_TRY(h->ascii_seq.ensure(n + 64)); SHK_TRY(h->ascii_qual.ensure(n + 64));
+  const uint64_t total = (n + 31) / 32;
+  SHK_TRY(h->bases.ensure((total + 5) * 8)); SHK_TRY(h->mask.ensure((total + 5) * 4));
+  uint64_t *b = h->bases.as<uint64_t>() + 1;
+  uint32_t *m = h->mask.as<uint32_t>() + 1;
+  SHK_CUDA(cudaMemsetAsync(h->bases.p, 0, 8, h->stream));
+  SHK_CUDA(cudaMemsetAsync(h->mask.p, 0, 4, h->stream));
+  SHK_CUDA(cudaMemsetAsync(d_counters(h) + 3, 0, 8, h->stream));
+  SHK_CUDA(cudaMemsetAsync(b + total, 0, 4 * 8, h->stream));
+  SHK_CUDA(cudaMemsetAsync(m + total, 0, 4 * 4, h->stream));
+  h->nwords = total; h->n_positions = n;
+  SHK_TRY(fast_prologue(h));
+  // the copy stream starts after everything queued so far (the ASCII buffers may still feed an earlier K0)
+  SHK_CUDA(cudaEventRecord(h->copy_ev[S], h->stream));
+  SHK_CUDA(cudaStreamWaitEvent(h->copy_stream, h->copy_ev[S], 0));
+  uint8_t *dseq = h->ascii_seq.as<uint8_t>(), *dqual = h->ascii_qual.as<uint8_t>();
+  bool first_k1a = true;
+  auto k1a = [&](int i) {
+    const uint64_t wb = (uint64_t)i * slice / 32, we = std::min<uint64_t>(total, (uint64_t)(i + 1) * slice / 32);
+    if (wb >= we) return;
+    if (first_k1a) { cudaEventRecord(h->ev[8], h->stream); first_k1a = false; }
+    h->st.gpu_launches += launch_partition(h->kw, b, m, total, h->p.k, h->P, h->rcap, h->skrecs.p, h->bfill.as<uint64_t>(),
+                                           d_counters(h), h->stream, wb, we);
+  };
+  for (int i = 0; i < S; ++i) {
+    const uint64_t off = (uint64_t)i * slice;
+    if (off >= n) break;
+    const uint64_t len = std::min<uint64_t>(slice, n - off);
+    SHK_CUDA(cudaMemcpyAsync(dseq + off, seq + off, len, cudaMemcpyHostToDevice, h->copy_stream));
+    SHK_CUDA(cudaMemcpyAsync(dqual + off, qual + off, len, cudaMemcpyHostToDevice, h->copy_stream));
+    SHK_CUDA(cudaEventRecord(h->copy_ev[i], h->copy_stream));
+    SHK_CUDA(cudaStreamWaitEvent(h->stream, h->copy_ev[i], 0));
+    h->st.gpu_launches += launch_pack_reads(dseq + off, dqual + off, len, (len + 31) / 32, h->p.min_qual, b + off / 32, m + off / 32,
+                                            d_counters(h) + 3, h->stream);
+    if (i == 0) SHK_CUDA(cudaEventRecord(h->ev[1], h->stream));
+    if (i > 0) k1a(i - 1);
+  }
+  for (int i = 0; i < S; ++i) if ((uint64_t)(i + 1) * slice >= n) { k1a(i); break; }
+  SHK_CUDA(cudaGetLastError());
+  SHK_CUDA(cudaEventRecord(h->ev[9], h->stream));
+  h->counted = h->filtered = h->graphed = false;
+  h->partition_done = true;
   return SHK_OK;
 }
 
 static shk_status load_reads_host(shk_asm *h, const uint8_t *seq, const uint8_t *qual, size_t n, int append) {
   SHK_TRY(require_device(h));
   if (!seq && n) { set_error("seq is null"); return SHK_ERR_BAD_ARG; }
+  h->partition_done = false;
+  if (!append && qual && n >= h->overlap_min && fast_ready_for(h, n)) return load_reads_overlapped(h, seq, qual, n);
   SHK_CUDA(cudaEventRecord(h->ev[0], h->stream));
   SHK_TRY(h->ascii_seq.ensure(n + 64));
   if (qual) SHK_TRY(h->ascii_qual.ensure(n + 64));
@@ -196,6 +258,7 @@ static shk_status count_impl(shk_asm *h, int /*reset*/, uint32_t P_override = 0)
     for (uint32_t i = 0; i < P; ++i) { h->seg_kmers[i] = (uint32_t)(hf[i] >> 32); h->seg_recs[i] = (uint32_t)hf[i]; }
     h->seg_per_bucket = 1; h->src_instances = h->st.n_instances; h->shard_src = false;
   }
+  h->partition_done = false;
   h->counted = true; h->counted_fast = false; h->st.device_planned = 0; h->filtered = h->graphed = false; h->histo_valid = false;
   return SHK_OK;
 }
@@ -265,11 +328,22 @@ static shk_status index_impl(shk_asm *h);
 // size are known.  K1b's CTAs cut the bucket groups themselves (SelfPlan, shk_count_smem.cuh); everything the host
 // would have checked before K1b is checked after it, and any violation falls back to the
 // host-planned path (same results, one wasted pass).
-static bool fast_ready(shk_asm *h) {
+static bool fast_ready_for(shk_asm *h, uint64_t n_positions) {
   static const bool off = [] { const char *e = getenv("SHK_NO_FAST"); return e && e[0] == '1'; }();
-  return !off && h->ratio_est > 0 && h->P && h->rcap && h->fast_positions == h->n_positions && h->n_positions > 0 &&
-         h->fast_banned_positions != h->n_positions &&
+  return !off && h->ratio_est > 0 && h->P && h->rcap && h->fast_positions == n_positions && n_positions > 0 &&
+         h->fast_banned_positions != n_positions &&
          !h->shard_world && (h->kw == 2 || h->no_dedup || h->uq_cap > 0) && h->ovf_cap > 0;
+}
+static bool fast_ready(shk_asm *h) { return fast_ready_for(h, h->n_positions); }
+
+// everything the steady-state path queues in front of K1a
+static shk_status fast_prologue(shk_asm *h) {
+  SHK_CUDA(cudaEventRecord(h->ev[2], h->stream));
+  SHK_CUDA(cudaMemsetAsync(h->bfill.p, 0, (size_t)h->P * 8, h->stream));
+  SHK_CUDA(cudaMemsetAsync(d_counters(h) + 1, 0, 8, h->stream));                     // n_instances
+  SHK_CUDA(cudaMemsetAsync(d_counters(h) + 2, 0, 8, h->stream));                     // n_distinct ([3] = bases of the resident reads stays)
+  SHK_CUDA(cudaMemsetAsync(d_counters(h) + 4, 0, 4 * 8 + SHK_HISTO_BINS * 8 + 8 * 4, h->stream));   // spilled, decoded, records, spectrum, flags
+  return SHK_OK;
 }
 
 static shk_status count_filter_fast(shk_asm *h, int min_count, bool &fell_back) {
@@ -296,14 +370,13 @@ static shk_status count_filter_fast(shk_asm *h, int min_count, bool &fell_back) 
     SHK_TRY(h->uq_rec.ensure(ctas * uq_fast * 16 + 16)); SHK_TRY(h->uq_cnt.ensure(ctas * uq_fast * 4 + 16));
   }
   h->node_cap = node_cap;
-  SHK_CUDA(cudaEventRecord(h->ev[2], h->stream));
-  SHK_CUDA(cudaMemsetAsync(h->bfill.p, 0, (size_t)P * 8, h->stream));
-  SHK_CUDA(cudaMemsetAsync(d_counters(h) + 1, 0, 8, h->stream));                     // n_instances
-  SHK_CUDA(cudaMemsetAsync(d_counters(h) + 2, 0, 8, h->stream));                     // n_distinct ([3] = bases of the resident reads stays)
-  SHK_CUDA(cudaMemsetAsync(d_counters(h) + 4, 0, 4 * 8 + SHK_HISTO_BINS * 8 + 8 * 4, h->stream));   // spilled, decoded, records, spectrum, flags
-  SHK_CUDA(cudaEventRecord(h->ev[8], h->stream));
-  h->st.gpu_launches += launch_partition(h->kw, b, m, h->nwords, h->p.k, P, rcap, h->skrecs.p, h->bfill.as<uint64_t>(), d_counters(h), h->stream);
-  SHK_CUDA(cudaEventRecord(h->ev[9], h->stream));
+  if (!h->partition_done) {                           // (the overlapped load has already cut the reads into records)
+    SHK_TRY(fast_prologue(h));
+    SHK_CUDA(cudaEventRecord(h->ev[8], h->stream));
+    h->st.gpu_launches += launch_partition(h->kw, b, m, h->nwords, h->p.k, P, rcap, h->skrecs.p, h->bfill.as<uint64_t>(), d_counters(h), h->stream);
+    SHK_CUDA(cudaEventRecord(h->ev[9], h->stream));
+  }
+  h->partition_done = false;                          // K1b consumes it; a fallback starts over
   SHK_CUDA(cudaEventRecord(h->ev[3], h->stream));
   SHK_CUDA(cudaEventRecord(h->ev[4], h->stream));
   h->st.gpu_launches += launch_table_fill(h->ovf.p, h->ovf_cap, h->kw, h->stream);
@@ -605,6 +678,7 @@ shk_status shk_asm_new(const shk_params *params, shk_asm **out) {
   h->p = *params;
   h->kw = params->k <= 31 ? 1 : 2;
   { const char *nd = getenv("SHK_NO_DEDUP"); h->no_dedup = nd && nd[0] == '1'; }
+  { const char *om = getenv("SHK_OVERLAP_MIN"); if (om && atoll(om) > 0) h->overlap_min = (uint64_t)atoll(om); }
   memset(&h->st, 0, sizeof h->st);
   memset(h->histo, 0, sizeof h->histo);
   h->st.used_min_count = params->min_count;
@@ -656,6 +730,7 @@ void shk_asm_free(shk_asm *h) {
     h->hfill.release(); h->pin_stage.release();
     for (auto &e : h->ev) if (e) cudaEventDestroy(e);
     if (h->own_stream) cudaStreamDestroy(h->own_stream);
+    if (h->copy_stream) { cudaStreamDestroy(h->copy_stream); for (auto &e : h->copy_ev) if (e) cudaEventDestroy(e); }
   }
   delete h;
 }

@@ -73,6 +73,10 @@ struct shk_asm {
   int kw = 1, dev = 0;
   cudaStream_t own_stream = nullptr, stream = nullptr;
   cudaEvent_t ev[12] = {};
+  cudaStream_t copy_stream = nullptr;  // host->device slices of the overlapped load
+  cudaEvent_t copy_ev[9] = {};
+  uint64_t overlap_min = 32u << 20;    // smallest load (bytes per stream) worth slicing (SHK_OVERLAP_MIN overrides)
+  bool partition_done = false;         // the resident reads are already cut into records (overlapped load)
   shk_progress_fn cb = nullptr;
   void *cb_user = nullptr;
 

@@ -692,15 +692,18 @@ int count_max_group() { return SHK_CB_MAXC; }
 int count_ctas() { return sm_count() * SHK_CB_PER_SM; }
 
 int launch_partition(int kw, const uint64_t *bases, const uint32_t *mask, uint64_t nwords, int k, uint32_t P,
-                     uint32_t rcap, void *recs, uint64_t *bstat, uint64_t *counters, cudaStream_t st) {
-  if (!nwords) return 0;
-  unsigned g = blocks_for(nwords, SHK_PT_WORDS);
+                     uint32_t rcap, void *recs, uint64_t *bstat, uint64_t *counters, cudaStream_t st,
+                     uint64_t word_begin, uint64_t word_end) {
+  if (word_end > nwords) word_end = nwords;
+  if (word_begin >= word_end) return 0;
+  unsigned g = blocks_for(word_end - word_begin, SHK_PT_WORDS);
   if (kw == 1)
-    k_minimizer_partition<1><<<g, SHK_PT_THREADS, 0, st>>>((const u64 *)bases, mask, nwords, k, P, rcap, (uint4 *)recs, (u64 *)bstat, (u64 *)counters);
+    k_minimizer_partition<1><<<g, SHK_PT_THREADS, 0, st>>>((const u64 *)bases, mask, nwords, word_begin, k, P, rcap, (uint4 *)recs, (u64 *)bstat, (u64 *)counters);
   else
-    k_minimizer_partition<2><<<g, SHK_PT_THREADS, 0, st>>>((const u64 *)bases, mask, nwords, k, P, rcap, (Rec32 *)recs, (u64 *)bstat, (u64 *)counters);
+    k_minimizer_partition<2><<<g, SHK_PT_THREADS, 0, st>>>((const u64 *)bases, mask, nwords, word_begin, k, P, rcap, (Rec32 *)recs, (u64 *)bstat, (u64 *)counters);
   return 1;
 }
+int partition_tile_words() { return SHK_PT_WORDS; }
 
 int launch_count_buckets(int kw, const void *recs, const uint64_t *bstat, uint32_t rcap, const uint64_t *seg_off,
                          const uint32_t *seg_cnt, void *uq_rec, uint32_t *uq_cnt, uint32_t uq_cap, const uint32_t *group_start,

@@ -57,7 +57,10 @@ int count_table_slots(int kw);
 int count_max_group();
 int count_ctas();          // CTAs of one K1b launch (sizes the per-CTA de-dup lists)
 int launch_partition(int kw, const uint64_t *bases, const uint32_t *mask, uint64_t nwords, int k, uint32_t P,
-                     uint32_t rcap, void *recs, uint64_t *bstat /* [P]: records | k-mers << 32 */, uint64_t *counters, cudaStream_t st);
+                     uint32_t rcap, void *recs, uint64_t *bstat /* [P]: records | k-mers << 32 */, uint64_t *counters, cudaStream_t st,
+                     uint64_t word_begin = 0, uint64_t word_end = ~0ull /* a slice of the stream: begin must be a multiple of
+                     partition_tile_words(), and the words behind word_end (the halo) must already be packed */);
+int partition_tile_words();
 // group_start == null: the CTAs cut their own groups (steady-state runs).  stats (device, zeroed by the caller):
 // [0] largest bucket fill, [1] most distinct items in a group; *nrec (device, zeroed): records counted.
 struct SelfPlanArgs { uint32_t n_buckets; double ratio; double budget; uint32_t *stats; uint64_t *nrec; };

@@ -123,7 +123,8 @@ __device__ __forceinline__ void window_min_pow2(const u32 *row, u32 (&R)[32]) {
 
 template <int KW>
 __global__ void __launch_bounds__(SHK_PT_THREADS, 3)
-k_minimizer_partition(const u64 *__restrict__ bases, const u32 *__restrict__ mask, u64 nwords, int k, u32 P,
+k_minimizer_partition(const u64 *__restrict__ bases, const u32 *__restrict__ mask, u64 nwords /* of the whole stream */,
+                      u64 word_begin /* first word of this launch (a multiple of SHK_PT_WORDS) */, int k, u32 P,
                       u32 rcap, typename RecOf<KW>::type *__restrict__ recs, u64 *__restrict__ bstat /* [P] records | kmers << 32 */,
                       u64 *__restrict__ counters /* [1] n_instances */) {
   __shared__ u64 sb[SHK_PT_TILE];
@@ -134,7 +135,7 @@ k_minimizer_partition(const u64 *__restrict__ bases, const u32 *__restrict__ mas
   __shared__ u32 desc[SHK_PT_DESC];
   __shared__ u32 wsum[SHK_PT_THREADS / 32 + 1];
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
-  const u64 w0 = (u64)blockIdx.x * SHK_PT_WORDS;
+  const u64 w0 = word_begin + (u64)blockIdx.x * SHK_PT_WORDS;
   // tile index i holds stream word w0 - 1 + i
   for (int i = t; i < SHK_PT_TILE; i += SHK_PT_THREADS) {
     u64 gw = w0 + (u64)i;                       // = word index + 1

@@ -221,6 +221,28 @@ def test_assemble_contigs_match_cleaned_oracle_graph(flags):
 
 
 @pytest.mark.parametrize("k", [31, 63])
+def test_overlapped_load(k, monkeypatch):
+    """A calibrated handle copies the reads in slices and packs / cuts slice i-1 under the copy of slice i
+    (k-mers that span a slice boundary must not be lost)."""
+    monkeypatch.setenv("SHK_OVERLAP_MIN", "1")
+    seq, qual = synth.reads(51, 120_000, 30.0, 0.01)
+    h = AssemblyHelper.new(k, False, 2, 20, 0, False, False, False, False)
+    o = run_oracle(seq, qual, k, 2, 20)
+    for it in range(3):
+        h.preprocess_reads(seq, qual)
+        assert h.stats()["device_planned"] == (1 if it else 0)
+        h.assemble()
+        assert_parity(h, o, check_table=False)
+    # load only, then the low-level calls: the records cut by the overlapped load are simply cut again
+    h.load_reads(seq, qual); h.count(True); h.filter(); h.build_graph()
+    assert_parity(h, o, check_table=False)
+    h.load_reads(seq, qual); h.run()
+    assert h.stats()["device_planned"] == 1
+    assert_parity(h, o, check_table=False)
+    h.close()
+
+
+@pytest.mark.parametrize("k", [31, 63])
 def test_steady_state_path(k):
     """Second and later runs on a handle plan the K1b groups on the device (no host round trip between
     K1a and K1b).  Same results; stale calibration (another read set of the same size) must still be exact."""
