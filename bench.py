@@ -222,6 +222,7 @@ def main():
 
     stage_names = ("partition", "pack", "all_to_all", "count", "gather_nodes", "graph")
     stage_acc = {n: [] for n in stage_names}
+    host_acc = {}
 
     def step():
         """one pass of the hot path over the resident packed reads"""
@@ -235,8 +236,9 @@ def main():
     def harvest():
         m = getattr(step, "marks", None)
         if m:
-            for (_, a), (n, b) in zip(m[:-1], m[1:]):
+            for (_, a, _h0), (n, b, hs) in zip(m[:-1], m[1:]):
                 stage_acc[n].append(a.elapsed_time(b))
+                host_acc.setdefault(n, []).append(hs * 1e3)
 
     # ---- device-resident arm ------------------------------------------------
     h.load_reads_ptr(pin_seq.data_ptr(), pin_qual.data_ptr(), nbytes)     # resident packed reads (untimed)
@@ -331,6 +333,7 @@ def main():
                 "whole_step_frac": (alg * bases / (ms_step * 1e-3) / 1e9) / peak,
                 "stage_ms": ({n: sum(v) / len(v) for n, v in stage_acc.items() if v} if world > 1 else
                              {kname: sum(v) / len(v) for kname, v in ms_parts.items()}),
+                "stage_host_ms": {n: round(sum(v) / len(v), 3) for n, v in host_acc.items() if v} if world > 1 else None,
                 "note": "traffic = dram bytes of one launch from the committed ncu capture (profiles/); the design "
                         "keeps the table in shared memory, so measured traffic is far below the model's bytes"}
 

@@ -219,6 +219,9 @@ static shk_status count_impl(shk_asm *h, int /*reset*/, uint32_t P_override = 0)
   const int mlen = k < 11 ? k : 11, w = k - mlen + 1;
   double avg_run = std::min<double>(records_max_run(h->kw, k), std::max(1.0, (w + 1) / 2.0 * 0.6));
   uint64_t rcap64 = (uint64_t)(3.0 * (double)positions / avg_run / (double)P) + 64;
+  // a read set of the same size cut into the same buckets on this handle before: start from the region size
+  // that was needed then (skewed buckets make the estimate fall short, and a retry costs a whole K1a pass)
+  if (h->P == P && h->counted_positions == h->n_positions && h->rcap > rcap64) rcap64 = h->rcap;
   h->st.table_retries = 0;
   for (;;) {
     if (rcap64 > 0x7FFFFFFFull) { set_error("record region too large"); return SHK_ERR_OOM; }

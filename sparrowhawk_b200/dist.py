@@ -147,12 +147,18 @@ def sharded_run(eng, group=None, timings=None):
     dev = eng.device
     i64 = dict(dtype=torch.int64, device=dev)
 
+    import time as _time
+    host_t = [_time.perf_counter()]
+
     def mark(name):
-        """stage boundary: a CUDA event on the current stream (bench.py reads the gaps)"""
+        """stage boundary: a CUDA event on the current stream (bench.py reads the gaps); the host-side time
+        since the previous boundary rides along (timings entries: name, event, host seconds)"""
         if timings is not None and dev.type == "cuda":
             ev = torch.cuda.Event(enable_timing=True)
             ev.record(torch.cuda.current_stream(dev))
-            timings.append((name, ev))
+            now = _time.perf_counter()
+            timings.append((name, ev, now - host_t[0]))
+            host_t[0] = now
 
     mark("start")
     # ---- global bucket count: the same cut on every rank ----
@@ -194,26 +200,40 @@ def sharded_run(eng, group=None, timings=None):
     n_local, _ = eng.local_counts()
     mark("count")
 
-    # ---- all-reduce spectrum + totals; all-gather the surviving nodes ----
-    hist = torch.from_numpy(eng.histogram().astype(np.int64)).to(dev)
-    red = torch.cat([hist, torch.tensor([inst_local, eng.n_bases()], **i64)])
+    # ---- one all-reduce: spectrum, totals and every rank's node count (slot 502 + r) ----
+    red = torch.zeros(502 + world, **i64)
+    red[:500] = torch.from_numpy(eng.histogram().astype(np.int64))
+    red[500:502] = torch.tensor([inst_local, eng.n_bases()], dtype=torch.int64)
+    red[502 + rank] = n_local
     _all_reduce(red, group)
-    g_hist = red[:500].cpu().numpy().astype(np.uint64)
-    g_inst, g_bases = int(red[500]), int(red[501])
-    counts = [torch.zeros(1, **i64) for _ in range(world)]
-    _all_gather(counts, torch.tensor([n_local], **i64), group)
-    counts = [int(c) for c in counts]
+    red_h = red.cpu().numpy()
+    g_hist = red_h[:500].astype(np.uint64)
+    g_inst, g_bases = int(red_h[500]), int(red_h[501])
+    counts = [int(c) for c in red_h[502:]]
     n_max, n_total = max(counts + [1]), sum(counts)
-    lo = torch.zeros(n_max, **i64); hi = torch.zeros(n_max, **i64)
-    cnt = torch.zeros(n_max, dtype=torch.int16, device=dev); raw = torch.zeros(n_max, dtype=torch.uint8, device=dev)
+    # ---- all-gather the surviving nodes: key (high half only when k > 31), count, raw edge bits ----
+    wide = eng.k > 31
+    lo = torch.empty(n_max, **i64); hi = torch.empty(n_max if wide else 0, **i64)
+    cnt = torch.empty(n_max, dtype=torch.int16, device=dev); raw = torch.empty(n_max, dtype=torch.uint8, device=dev)
     eng.local_nodes(lo, hi, cnt, raw)
     gathered = []
     for t in (lo, hi, cnt, raw):
         b = t.view(torch.uint8)                     # collectives have no 16-bit integer type
         w = t.element_size()
-        parts = [torch.empty_like(b) for _ in range(world)]
-        _all_gather(parts, b, group)
-        g = torch.cat([p[:c * w] for p, c in zip(parts, counts)]) if n_total else b[:0]
+        if t.numel() == 0:
+            gathered.append(t)
+            continue
+        if _staged(group) or not b.is_cuda:
+            parts = [torch.empty_like(b) for _ in range(world)]
+            _all_gather(parts, b, group)
+        else:                                        # one NCCL all-gather into one buffer, rank r at r * n_max
+            flat = torch.empty(world * b.numel(), dtype=torch.uint8, device=dev)
+            dist.all_gather_into_tensor(flat, b, group=group)
+            parts = list(flat.split(b.numel()))
+        if all(c == n_max for c in counts) and not (_staged(group) or not b.is_cuda):
+            g = flat                                # nothing to squeeze out
+        else:
+            g = torch.cat([p[:c * w] for p, c in zip(parts, counts)]) if n_total else b[:0]
         gathered.append(g.view(t.dtype))
     my_off = sum(counts[:rank])
     eng.set_nodes(*gathered, n_total, my_off, g_hist, g_inst, g_bases, used_mc)

@@ -104,11 +104,14 @@ class CpuEngine:
 
     def local_nodes(self, lo, hi, cnt, raw):
         n = len(self.nodes[0])
-        lo[:n] = torch.from_numpy(self.nodes[0].view(np.int64)); hi[:n] = torch.from_numpy(self.nodes[1].view(np.int64))
+        lo[:n] = torch.from_numpy(self.nodes[0].view(np.int64))
+        if hi.numel():                               # the high key half travels only when k > 31
+            hi[:n] = torch.from_numpy(self.nodes[1].view(np.int64))
         cnt[:n] = torch.from_numpy(self.nodes[2].view(np.int16)); raw[:n] = torch.from_numpy(self.nodes[3])
 
     def set_nodes(self, lo, hi, cnt, raw, n_total, my_off, histo, n_inst, n_bases, used_mc):
-        self.all_nodes = (lo.numpy().view(np.uint64), hi.numpy().view(np.uint64), cnt.numpy().view(np.uint16), raw.numpy())
+        ghi = hi.numpy().view(np.uint64) if hi.numel() else np.zeros(lo.numel(), np.uint64)
+        self.all_nodes = (lo.numpy().view(np.uint64), ghi, cnt.numpy().view(np.uint16), raw.numpy())
         self.g = dict(n_total=n_total, my_off=my_off, histo=histo, n_inst=n_inst, n_bases=n_bases, used_mc=used_mc)
 
     def build_graph(self):
