@@ -316,30 +316,37 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
       U128Pair *rkeys = reinterpret_cast<U128Pair *>(smraw);      // SHK_RT_SLOTS x 16 B = the k-mer key area
       u32 *rcnt = vals;                                           // cleared above
       myrec = uq_rec + (size_t)blockIdx.x * uq_cap; mycnt = uq_cnt + (size_t)blockIdx.x * uq_cap;
-      for (;;) {
-        u32 cbase = 0;
-        if (lane == 0) cbase = atomicAdd(&misc[1], 32u);
-        cbase = __shfl_sync(0xffffffffu, cbase, 0);
-        if (cbase >= total) break;
-        const u32 f = cbase + lane;
-        if (f < total) {
-          u32 lo = 0, hi = nb;
-          while (hi - lo > 1) { u32 mid = (lo + hi) >> 1; if (gpre[mid] <= f) lo = mid; else hi = mid; }
-          const u64 sbase = seg_off ? seg_off[b0 + lo] : (u64)(b0 + lo) * rcap;
-          const uint4 c = canon_record(__ldcs(reinterpret_cast<const uint4 *>(recs + (sbase + (f - gpre[lo])))), k);
-          u32 slot;
-          const int got = rtable_insert(rkeys, rcnt, c, slot);
-          const u32 rn = c.x & 31u, full = rn / SHK_CB_SEG, rem = rn % SHK_CB_SEG;
-          if (got == 2) {                                           // first sight of this record: remember its slot, count its items
-            rlist[atomicAdd(&misc[5], 1u)] = (unsigned short)slot;
-            if (full) atomicAdd(&rbins[SHK_CB_SEG], full);
-            if (rem) atomicAdd(&rbins[rem], 1u);
-          } else if (got == 0) {
-            const u32 nit = full + (rem ? 1u : 0u), idx = atomicAdd(&misc[2], nit);
-            for (u32 j = 0; j < nit; ++j)
-              if (idx + j < uq_cap) { myrec[idx + j] = record_item(c, j); mycnt[idx + j] = 1u; }
-          }
+      // address of record f of the group: segment by binary search over the prefix
+      auto rec_ptr = [&](u32 f) {
+        u32 lo = 0, hi = nb;
+        while (hi - lo > 1) { u32 mid = (lo + hi) >> 1; if (gpre[mid] <= f) lo = mid; else hi = mid; }
+        const u64 sbase = seg_off ? seg_off[b0 + lo] : (u64)(b0 + lo) * rcap;
+        return reinterpret_cast<const uint4 *>(recs + (sbase + (f - gpre[lo])));
+      };
+      auto insert_record = [&](uint4 c) {
+        u32 slot;
+        const int got = rtable_insert(rkeys, rcnt, c, slot);
+        const u32 rn = c.x & 31u, full = rn / SHK_CB_SEG, rem = rn % SHK_CB_SEG;
+        if (got == 2) {                                             // first sight of this record: remember its slot, count its items
+          rlist[atomicAdd(&misc[5], 1u)] = (unsigned short)slot;
+          if (full) atomicAdd(&rbins[SHK_CB_SEG], full);
+          if (rem) atomicAdd(&rbins[rem], 1u);
+        } else if (got == 0) {
+          const u32 nit = full + (rem ? 1u : 0u), idx = atomicAdd(&misc[2], nit);
+          for (u32 j = 0; j < nit; ++j)
+            if (idx + j < uq_cap) { myrec[idx + j] = record_item(c, j); mycnt[idx + j] = 1u; }
         }
+      };
+      // two records per thread and round: both loads are in flight together and the two canonicalisations
+      // (long dependent chains) interleave
+      for (u32 f = tid; f < total; f += 2 * SHK_CB_THREADS) {
+        const u32 f2 = f + SHK_CB_THREADS;
+        const bool two = f2 < total;
+        const uint4 r1 = __ldcs(rec_ptr(f));
+        const uint4 r2 = two ? __ldcs(rec_ptr(f2)) : r1;
+        const uint4 c1 = canon_record(r1, k), c2 = canon_record(r2, k);
+        insert_record(c1);
+        if (two) insert_record(c2);
       }
       __syncthreads();
       // distinct records leave the table cut into items of at most SHK_CB_SEG k-mers, sorted by item length,
