@@ -282,6 +282,29 @@ def test_steady_state_path(k):
     h.close()
 
 
+@pytest.mark.timeout(600)
+@pytest.mark.parametrize("name", ["A", "B", "C"])
+def test_baseline_configs_full_size(name):
+    """BASELINE.json configs at their full size (A: 60 Mbase, B and C: 500 Mbase, C at k = 63): the CUDA path against the C++
+    oracle on all host cores — spectrum, filtered k-mers with counts and edge bits, unitig multiset — plus
+    the size-independent invariants, on the first (host-planned) and the steady-state run."""
+    cfg = synth.CONFIGS[name]
+    seq, qual = synth.reads(cfg["seed"], cfg["G"], cfg["cov"], cfg["err"])
+    k, mc = cfg["k"], cfg["min_count"]
+    o = run_oracle(seq, qual, k, mc, 20, nthreads=os.cpu_count() or 4)
+    h = AssemblyHelper.new(k, False, mc, 20, 0, False, False, False, False)
+    h.load_reads(seq, qual)
+    for it in range(2):
+        h.run()
+        st = h.stats()
+        assert st["device_planned"] == it
+        assert st["n_bases"] == seq.nbytes - seq.nbytes // 151
+        assert int(h.histogram().sum()) == st["n_distinct"]
+        assert st["unitig_bases"] == st["n_nodes"] + st["n_unitigs"] * (k - 1)
+        assert_parity(h, o, check_table=False)
+    h.close()
+
+
 def test_errors():
     h = AssemblyHelper.new(31, False, 2, 20, 0, False, False, False, False)
     with pytest.raises(ShkError):
