@@ -68,6 +68,14 @@ pub struct shk_stats {
     pub ms_count_kernel: f32,
     pub n_spilled: u64,
     pub n_records: u64,
+    pub device_planned: u32,
+    pub reserved: u32,
+}
+
+/// opaque: contigs + links produced by the host graph cleaning
+#[repr(C)]
+pub struct shk_contigs {
+    _private: [u8; 0],
 }
 
 #[repr(C)]
@@ -109,4 +117,17 @@ extern "C" {
     pub fn shk_export_unitigs(h: *mut shk_asm, seq: *mut c_char, seq_cap: usize, offsets: *mut u64,
                               mean_cov: *mut f32, circular: *mut u8, unitig_cap: usize) -> shk_status;
     pub fn shk_export_links(h: *mut shk_asm, from: *mut u32, to: *mut u32, cap: usize, n: *mut usize) -> shk_status;
+    pub fn shk_export_unitig_counts(h: *mut shk_asm, kmer_count_sum: *mut u64, unitig_cap: usize) -> shk_status;
+
+    // host graph cleaning (dead-end removal, simple bubble collapse, re-compaction) on plain arrays
+    pub fn shk_clean_graph(k: c_int, seq: *const c_char, offsets: *const u64, kmer_count_sum: *const u64,
+                           circular: *const u8, n_unitigs: usize, link_from: *const u32, link_to: *const u32,
+                           n_links: usize, no_dead_end_removal: c_int, no_bubble_collapse: c_int,
+                           out: *mut *mut shk_contigs) -> shk_status;
+    pub fn shk_contigs_sizes(c: *const shk_contigs, n_contigs: *mut usize, n_bases: *mut usize, n_links: *mut usize,
+                             n_tips_removed: *mut usize, n_bubbles_removed: *mut usize) -> shk_status;
+    pub fn shk_contigs_export(c: *const shk_contigs, seq: *mut c_char, offsets: *mut u64, kmer_count_sum: *mut u64,
+                              circular: *mut u8, link_from: *mut u32, link_to: *mut u32) -> shk_status;
+    pub fn shk_contigs_free(c: *mut shk_contigs);
+    pub fn shk_asm_contigs(h: *mut shk_asm, out: *mut *const shk_contigs) -> shk_status;
 }
