@@ -305,6 +305,31 @@ def test_baseline_configs_full_size(name):
     h.close()
 
 
+@pytest.mark.parametrize("k", [31, 63])
+def test_repeatability_under_load(k):
+    """The same reads 40 times on one handle (host-planned once, then steady-state): the shared-memory
+    phases of K1b hand their tables on without clearing passes, so any race between phases would show up
+    as a run that differs.  Every run must reproduce the first one exactly."""
+    seq, qual = synth.reads(71, 700_000, 30.0, 0.01)
+    h = AssemblyHelper.new(k, False, 2, 20, 0, False, False, False, False)
+    h.load_reads(seq, qual)
+    ref = None
+    for it in range(40):
+        h.run()
+        st = h.stats()
+        lo, hi, cnt, raw, val = h.export_kmers()
+        order = np.lexsort((lo, hi))
+        cur = (st["n_instances"], st["n_distinct"], st["n_nodes"], st["n_unitigs"], st["unitig_bases"], st["n_links"],
+               h.histogram().tobytes(), lo[order].tobytes(), hi[order].tobytes(), cnt[order].tobytes(),
+               raw[order].tobytes(), val[order].tobytes())
+        if ref is None:
+            ref = cur
+            assert_parity(h, run_oracle(seq, qual, k, 2, 20), check_table=False)
+        else:
+            assert cur == ref, f"run {it} differs from run 0"
+    h.close()
+
+
 def test_errors():
     h = AssemblyHelper.new(31, False, 2, 20, 0, False, False, False, False)
     with pytest.raises(ShkError):
