@@ -97,12 +97,14 @@ __device__ __forceinline__ u64 stream_bits64(const u64 *sb, int i) {
 }
 __device__ __forceinline__ u32 mask_bit(const u32 *sm, int i) { int j = i + 32; return (sm[j >> 5] >> (j & 31)) & 1u; }
 
-// bijective 32-bit mixer of the canonical m-mer: its order defines the minimizer
+// bijective 32-bit mixer of the canonical m-mer: its order defines the minimizer, its low bits the bucket.
+// multiply - xorshift - multiply: the xorshift folds the high product bits into the low ones before the second
+// multiply, so the low bits depend on the whole m-mer.  (A closing xorshift changed nothing in the bucket
+// balance — K1b time identical — and K1a is bound by the ALU pipe: 1.363 -> 1.329 ms without it.)
 __device__ __forceinline__ u32 mmer_hash(u32 c) {
   u32 h = c * 0x9E3779B1u;
   h ^= h >> 15;
   h *= 0x85EBCA77u;
-  h ^= h >> 13;
   return h;
 }
 
