@@ -253,16 +253,18 @@ static shk_status count_impl(shk_asm *h, int /*reset*/, uint32_t P_override = 0)
   h->st.n_instances = h->h_pinned[1];
   h->st.n_distinct = 0;
   h->st.table_slots = (uint64_t)P;
-  // K1b input: one segment per local bucket region
-  {
+  // K1b input: one segment per local bucket region (the sharded path counts received records instead)
+  if (!P_override) {
     const uint64_t *hf = (const uint64_t *)h->hfill.p;
     h->seg_kmers.resize(P);
     h->seg_recs.resize(P);
     for (uint32_t i = 0; i < P; ++i) { h->seg_kmers[i] = (uint32_t)(hf[i] >> 32); h->seg_recs[i] = (uint32_t)hf[i]; }
     h->seg_per_bucket = 1; h->src_instances = h->st.n_instances; h->shard_src = false;
+  } else {
+    h->seg_kmers.clear(); h->seg_recs.clear(); h->shard_src = false;
   }
   h->partition_done = false;
-  h->counted = true; h->counted_fast = false; h->st.device_planned = 0; h->filtered = h->graphed = false; h->histo_valid = false;
+  h->counted = true; h->counted_fast = P_override != 0 /* no host-side bucket description either */; h->st.device_planned = 0; h->filtered = h->graphed = false; h->histo_valid = false;
   return SHK_OK;
 }
 
@@ -730,7 +732,7 @@ void shk_asm_free(shk_asm *h) {
                       &h->useq, &h->link_from, &h->link_to, &h->gscal, &h->splitters, &h->sum_of, &h->rank_work, &h->skrecs, &h->bfill, &h->groups, &h->ovf, &h->uq_rec, &h->uq_cnt, &h->seg_off, &h->seg_cnt, &h->pack_off};
     for (auto b : bufs) b->release();
     if (h->h_pinned) cudaFreeHost(h->h_pinned);
-    h->hfill.release(); h->pin_stage.release();
+    h->hfill.release(); h->pin_stage.release(); h->hoff.release(); h->hseg.release();
     for (auto &e : h->ev) if (e) cudaEventDestroy(e);
     if (h->own_stream) cudaStreamDestroy(h->own_stream);
     if (h->copy_stream) { cudaStreamDestroy(h->copy_stream); for (auto &e : h->copy_ev) if (e) cudaEventDestroy(e); }
@@ -1041,7 +1043,8 @@ shk_status shk_shard_partition(shk_asm *h, uint32_t n_buckets, uint32_t world, u
   h->shard_world = world; h->shard_rank = rank;
   // dense offsets of every bucket in the send buffer (bucket order = owner order)
   const uint64_t *hf = (const uint64_t *)h->hfill.p;
-  std::vector<uint64_t> off(n_buckets);
+  SHK_TRY(h->hoff.ensure_host((size_t)n_buckets * 8));          // pinned and owned by the handle: the copy needs no wait
+  uint64_t *off = (uint64_t *)h->hoff.p;
   uint64_t run = 0;
   for (uint32_t r = 0, b = 0; r < world; ++r) {
     const uint32_t hi = shard_lo(n_buckets, world, r + 1);
@@ -1050,8 +1053,7 @@ shk_status shk_shard_partition(shk_asm *h, uint32_t n_buckets, uint32_t world, u
     send_records[r] = run - start;
   }
   SHK_TRY(h->pack_off.ensure((size_t)n_buckets * 8));
-  SHK_CUDA(cudaMemcpyAsync(h->pack_off.p, off.data(), (size_t)n_buckets * 8, cudaMemcpyHostToDevice, h->stream));
-  SHK_CUDA(cudaStreamSynchronize(h->stream));       // `off` is pageable and dies here
+  SHK_CUDA(cudaMemcpyAsync(h->pack_off.p, off, (size_t)n_buckets * 8, cudaMemcpyHostToDevice, h->stream));
   return SHK_OK;
 }
 
@@ -1072,23 +1074,33 @@ shk_status shk_shard_count(shk_asm *h, const void *d_recv, const uint64_t *recv_
   if (!h->counted || !h->shard_world) { set_error("shard_count before shard_partition"); return SHK_ERR_STATE; }
   if (!recv_fill) { set_error("null recv_fill"); return SHK_ERR_BAD_ARG; }
   const uint32_t W = h->shard_world, lo = shard_lo(h->P, W, h->shard_rank), hi = shard_lo(h->P, W, h->shard_rank + 1), nb = hi - lo;
-  // segment (owned bucket j, source s) at index j * W + s
-  std::vector<uint64_t> off((size_t)nb * W); std::vector<uint32_t> cnt((size_t)nb * W);
-  h->seg_kmers.assign((size_t)nb * W, 0); h->seg_recs.assign((size_t)nb * W, 0);
+  // segment (owned bucket j, source s) at index j * W + s; the received records lie source by source
+  const size_t nseg = (size_t)nb * W;
+  SHK_TRY(h->hseg.ensure_host(nseg * 12 + 16));                    // pinned, owned by the handle: async copy, no wait
+  uint64_t *off = (uint64_t *)h->hseg.p;
+  uint32_t *cnt = (uint32_t *)(off + nseg);
+  h->seg_kmers.resize(nseg); h->seg_recs.resize(nseg);
+  std::vector<uint64_t> run_s(W, 0);
   uint64_t run = 0, inst = 0;
-  for (uint32_t s = 0; s < W; ++s)
-    for (uint32_t j = 0; j < nb; ++j) {
-      const uint64_t f = recv_fill[(size_t)s * nb + j];
-      off[(size_t)j * W + s] = run; cnt[(size_t)j * W + s] = (uint32_t)f; h->seg_kmers[(size_t)j * W + s] = (uint32_t)(f >> 32); h->seg_recs[(size_t)j * W + s] = (uint32_t)f;
-      run += (uint32_t)f; inst += f >> 32;
+  for (uint32_t sidx = 0; sidx < W; ++sidx) {                      // where each source's records start
+    run_s[sidx] = run;
+    const uint64_t *f = recv_fill + (size_t)sidx * nb;
+    for (uint32_t j = 0; j < nb; ++j) { run += (uint32_t)f[j]; inst += f[j] >> 32; }
+  }
+  for (uint32_t j = 0; j < nb; ++j)                                // W sequential read streams, one sequential write stream
+    for (uint32_t sidx = 0; sidx < W; ++sidx) {
+      const uint64_t f = recv_fill[(size_t)sidx * nb + j];
+      const size_t q = (size_t)j * W + sidx;
+      off[q] = run_s[sidx]; cnt[q] = (uint32_t)f; h->seg_kmers[q] = (uint32_t)(f >> 32); h->seg_recs[q] = (uint32_t)f;
+      run_s[sidx] += (uint32_t)f;
     }
   if (run && !d_recv) { set_error("null receive buffer"); return SHK_ERR_BAD_ARG; }
-  SHK_TRY(h->seg_off.ensure(off.size() * 8 + 8)); SHK_TRY(h->seg_cnt.ensure(cnt.size() * 4 + 4));
-  if (!off.empty()) {
-    SHK_CUDA(cudaMemcpyAsync(h->seg_off.p, off.data(), off.size() * 8, cudaMemcpyHostToDevice, h->stream));
-    SHK_CUDA(cudaMemcpyAsync(h->seg_cnt.p, cnt.data(), cnt.size() * 4, cudaMemcpyHostToDevice, h->stream));
-    SHK_CUDA(cudaStreamSynchronize(h->stream));
+  SHK_TRY(h->seg_off.ensure(nseg * 8 + 8)); SHK_TRY(h->seg_cnt.ensure(nseg * 4 + 4));
+  if (nseg) {
+    SHK_CUDA(cudaMemcpyAsync(h->seg_off.p, off, nseg * 8, cudaMemcpyHostToDevice, h->stream));
+    SHK_CUDA(cudaMemcpyAsync(h->seg_cnt.p, cnt, nseg * 4, cudaMemcpyHostToDevice, h->stream));
   }
+  h->counted_fast = false;                                         // the segments below are the bucket description
   h->seg_per_bucket = W; h->src_instances = inst; h->shard_src = true; h->recv_recs = d_recv;
   h->histo_valid = false;
   shk_status st = filter_impl(h, min_count < 0 ? h->p.min_count : min_count, histogram_only != 0, false);

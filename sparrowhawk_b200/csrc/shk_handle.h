@@ -86,6 +86,7 @@ struct shk_asm {
   uint64_t n_positions = 0, n_bases = 0, counted_positions = 0;
   // ---- K1a output: super-k-mer records in P fine-bucket regions of rcap records ----
   shk::DevBuf skrecs, bfill /* u32 fill[P] | u32 kcount[P] */, groups, ovf;
+  shk::PinBuf hoff /* shard_partition: dense send offsets */, hseg /* shard_count: segment offsets + counts */;
   shk::PinBuf hfill, pin_stage /* D2H staging of the unitig sequences */;
   uint32_t P = 0, rcap = 0;
   uint64_t n_records = 0, ovf_cap = 0, spill_hint = 0 /* instances that spilled on the last run */;
