@@ -247,7 +247,7 @@ shk_status shk_asm_contigs(shk_asm *h, const shk_contigs **out);
 /*   2 shk_shard_partition      K1a with the GLOBAL bucket count        */
 /*   3 shk_shard_pack           dense send buffer ordered by owner      */
 /*   4 host: all-to-all of per-bucket fills, then of the records        */
-/*   5 shk_shard_count          K1b/K2 over the received records        */
+/*   5 shk_shard_count[_device] K1b/K2 over the received records        */
 /*   6 host: all-reduce spectrum, all-gather surviving nodes            */
 /*   7 shk_shard_set_nodes      global node set + index on every rank   */
 /*   8 shk_build_graph          K3..K6                                  */
@@ -271,6 +271,16 @@ shk_status shk_shard_pack(shk_asm *h, void *d_send, uint64_t *d_send_fill);
  * histogram_only != 0: spectrum only (for do_fit); min_count < 0: the handle's. */
 shk_status shk_shard_count(shk_asm *h, const void *d_recv, const uint64_t *recv_fill,
                            int histogram_only, int min_count);
+/* The same with the fills left on the DEVICE (d_recv_fill, u64[world][n_own], as the
+ * all-to-all delivered them): the segment table is built by a kernel and K1b's CTAs cut
+ * the bucket groups themselves, so no host loop runs over buckets x ranks.  recv_records
+ * (HOST, u64[world]) = records received from each source; n_instances = k-mer instances
+ * in them (the high halves of the fills, summed).  A handle that has not yet been through
+ * one shk_shard_count of the same shape, or whose device-side plan fails verification,
+ * takes shk_shard_count with the fills fetched to the host — same results. */
+shk_status shk_shard_count_device(shk_asm *h, const void *d_recv, const uint64_t *d_recv_fill,
+                                  const uint64_t *recv_records, uint64_t n_instances,
+                                  int histogram_only, int min_count);
 /* D2D copy of this rank's surviving nodes (shk_stats.n_nodes of them) into
  * caller-owned device arrays: u64 lo, u64 hi, u16 count, u8 raw edge bits. */
 shk_status shk_shard_local_nodes(shk_asm *h, void *d_lo, void *d_hi, void *d_count,

@@ -204,7 +204,12 @@ static double table_load() {
 }
 static uint32_t target_bucket_instances(int kw) { return (uint32_t)(count_table_slots(kw) * 0.70); }
 
-static shk_status count_impl(shk_asm *h, int /*reset*/, uint32_t P_override = 0) {
+static inline uint32_t shard_lo(uint32_t P, uint32_t world, uint32_t r) { return (uint32_t)((uint64_t)r * P / world); }
+
+// P_override / world: the sharded cut (every rank uses the same buckets).  With world <= 64 the per-owner send
+// totals, the rank-local send offsets (pack_off) and the largest fill come from a kernel and only world + 1 numbers
+// cross to the host (h->hsend); otherwise the fills are fetched and walked on the host as in the single-GPU form.
+static shk_status count_impl(shk_asm *h, int /*reset*/, uint32_t P_override = 0, uint32_t world = 0) {
   SHK_TRY(require_device(h));
   SHK_CUDA(cudaEventRecord(h->ev[2], h->stream));
   const uint64_t *b = h->bases.as<uint64_t>() + 1;
@@ -235,12 +240,30 @@ static shk_status count_impl(shk_asm *h, int /*reset*/, uint32_t P_override = 0)
     h->st.gpu_launches += launch_partition(h->kw, b, m, h->nwords, k, P, rcap, h->skrecs.p, h->bfill.as<uint64_t>(), d_counters(h), h->stream);
     SHK_CUDA(cudaGetLastError());
     SHK_CUDA(cudaEventRecord(h->ev[9], h->stream));
-    SHK_CUDA(cudaMemcpyAsync(h->hfill.p, h->bfill.p, (size_t)P * 8, cudaMemcpyDeviceToHost, h->stream));
-    SHK_CUDA(cudaEventRecord(h->ev[3], h->stream));
-    SHK_TRY(read_scalars(h));
-    const uint64_t *hf = (const uint64_t *)h->hfill.p;   // records | k-mers << 32 per bucket
+    const bool dev_plan = P_override && world && world <= 64 && (int)world <= shard_max_world();
     uint32_t mx = 0; uint64_t nrec = 0;
-    for (uint32_t i = 0; i < P; ++i) { mx = std::max(mx, (uint32_t)hf[i]); nrec += (uint32_t)hf[i]; }
+    if (dev_plan) {
+      uint32_t starts[65];
+      for (uint32_t r = 0; r <= world; ++r) starts[r] = shard_lo(P, world, r);
+      SHK_TRY(h->pack_off.ensure((size_t)P * 8)); SHK_TRY(h->send_tot.ensure((size_t)(world + 1) * 8));
+      SHK_TRY(h->hsend.ensure_host((size_t)(world + 1) * 8));
+      SHK_CUDA(cudaMemsetAsync(h->send_tot.p, 0, (size_t)(world + 1) * 8, h->stream));
+      h->st.gpu_launches += launch_shard_send_plan(h->bfill.as<uint64_t>(), rcap, world, starts, h->pack_off.as<uint64_t>(),
+                                                   h->send_tot.as<uint64_t>(), h->stream);
+      SHK_CUDA(cudaMemcpyAsync(h->hsend.p, h->send_tot.p, (size_t)(world + 1) * 8, cudaMemcpyDeviceToHost, h->stream));
+      SHK_CUDA(cudaEventRecord(h->ev[3], h->stream));
+      SHK_TRY(read_scalars(h));
+      const uint64_t *hs = (const uint64_t *)h->hsend.p;
+      for (uint32_t r = 0; r < world; ++r) nrec += hs[r];
+      mx = (uint32_t)hs[world];
+    } else {
+      SHK_CUDA(cudaMemcpyAsync(h->hfill.p, h->bfill.p, (size_t)P * 8, cudaMemcpyDeviceToHost, h->stream));
+      SHK_CUDA(cudaEventRecord(h->ev[3], h->stream));
+      SHK_TRY(read_scalars(h));
+      const uint64_t *hf = (const uint64_t *)h->hfill.p;   // records | k-mers << 32 per bucket
+      for (uint32_t i = 0; i < P; ++i) { mx = std::max(mx, (uint32_t)hf[i]); nrec += (uint32_t)hf[i]; }
+    }
+    h->send_planned = dev_plan;
     h->P = P; h->rcap = rcap; h->n_records = nrec;
     if (mx <= rcap) break;
     if (++h->st.table_retries > 3) { set_error("record regions overflow after retries"); return SHK_ERR_TABLE_FULL; }
@@ -732,7 +755,7 @@ void shk_asm_free(shk_asm *h) {
                       &h->useq, &h->link_from, &h->link_to, &h->gscal, &h->splitters, &h->sum_of, &h->rank_work, &h->skrecs, &h->bfill, &h->groups, &h->ovf, &h->uq_rec, &h->uq_cnt, &h->seg_off, &h->seg_cnt, &h->pack_off};
     for (auto b : bufs) b->release();
     if (h->h_pinned) cudaFreeHost(h->h_pinned);
-    h->hfill.release(); h->pin_stage.release(); h->hoff.release(); h->hseg.release();
+    h->hfill.release(); h->pin_stage.release(); h->hoff.release(); h->hseg.release(); h->hfill2.release(); h->hsend.release();
     for (auto &e : h->ev) if (e) cudaEventDestroy(e);
     if (h->own_stream) cudaStreamDestroy(h->own_stream);
     if (h->copy_stream) { cudaStreamDestroy(h->copy_stream); for (auto &e : h->copy_ev) if (e) cudaEventDestroy(e); }
@@ -1032,15 +1055,19 @@ uint32_t shk_shard_buckets(uint64_t global_positions, int k) {
 }
 size_t shk_record_bytes(int k) { return record_bytes(k <= 31 ? 1 : 2); }
 
-static inline uint32_t shard_lo(uint32_t P, uint32_t world, uint32_t r) { return (uint32_t)((uint64_t)r * P / world); }
-
 shk_status shk_shard_partition(shk_asm *h, uint32_t n_buckets, uint32_t world, uint32_t rank, uint64_t *send_records) {
   SHK_TRY(require_device(h));
   if (!world || rank >= world || !send_records || n_buckets < world || (n_buckets & (n_buckets - 1))) {
     set_error("shard_partition: need a power-of-two bucket count >= world and rank < world"); return SHK_ERR_BAD_ARG;
   }
-  SHK_TRY(count_impl(h, 1, n_buckets));
+  SHK_TRY(count_impl(h, 1, n_buckets, world));
   h->shard_world = world; h->shard_rank = rank;
+  if (h->send_planned) {                       // offsets (local to the owner) and totals were cut on the device
+    const uint64_t *hs = (const uint64_t *)h->hsend.p;
+    uint64_t run = 0;
+    for (uint32_t r = 0; r < world; ++r) { send_records[r] = hs[r]; h->send_base[r] = run; run += hs[r]; }
+    return SHK_OK;
+  }
   // dense offsets of every bucket in the send buffer (bucket order = owner order)
   const uint64_t *hf = (const uint64_t *)h->hfill.p;
   SHK_TRY(h->hoff.ensure_host((size_t)n_buckets * 8));          // pinned and owned by the handle: the copy needs no wait
@@ -1063,7 +1090,7 @@ shk_status shk_shard_pack(shk_asm *h, void *d_send, uint64_t *d_send_fill) {
   if (h->n_records && !d_send) { set_error("null send buffer"); return SHK_ERR_BAD_ARG; }
   if (h->n_records)
     h->st.gpu_launches += launch_pack_records(h->kw, h->skrecs.p, h->bfill.as<uint64_t>(), h->rcap, h->pack_off.as<uint64_t>(),
-                                              h->P, d_send, h->stream);
+                                              h->P, d_send, h->stream, h->send_planned ? h->shard_world : 0, h->send_base);
   SHK_CUDA(cudaGetLastError());
   if (d_send_fill) SHK_CUDA(cudaMemcpyAsync(d_send_fill, h->bfill.p, (size_t)h->P * 8, cudaMemcpyDeviceToDevice, h->stream));
   return SHK_OK;
@@ -1105,6 +1132,104 @@ shk_status shk_shard_count(shk_asm *h, const void *d_recv, const uint64_t *recv_
   h->histo_valid = false;
   shk_status st = filter_impl(h, min_count < 0 ? h->p.min_count : min_count, histogram_only != 0, false);
   h->shard_nodes_local = st == SHK_OK && !histogram_only ? h->st.n_nodes : 0;
+  return st;
+}
+
+// Steady-state form of shk_shard_count: the fills stay on the device.  The segment table is built by a kernel
+// (launch_shard_segments) and K1b's CTAs cut the bucket groups themselves from the per-bucket totals, so the host
+// walks nothing of size buckets x ranks.  Needs a handle calibrated by one host-planned sharded run (ratio,
+// de-dup list size, overflow table); everything the host planner would have guaranteed is verified after the
+// kernel, and any violation — or an uncalibrated handle — takes shk_shard_count with the fills copied to the host.
+shk_status shk_shard_count_device(shk_asm *h, const void *d_recv, const uint64_t *d_recv_fill, const uint64_t *recv_records,
+                                  uint64_t n_instances, int histogram_only, int min_count) {
+  SHK_TRY(require_device(h));
+  if (!h->counted || !h->shard_world) { set_error("shard_count before shard_partition"); return SHK_ERR_STATE; }
+  if (!d_recv_fill || !recv_records) { set_error("null recv_fill / recv_records"); return SHK_ERR_BAD_ARG; }
+  const uint32_t W = h->shard_world, lo = shard_lo(h->P, W, h->shard_rank), hi = shard_lo(h->P, W, h->shard_rank + 1), nb = hi - lo;
+  const size_t nseg = (size_t)nb * W;
+  const int mc = min_count < 0 ? h->p.min_count : min_count;
+  const bool dedup = h->kw == 1 && !h->no_dedup;
+  static const bool off = [] { const char *e = getenv("SHK_NO_FAST"); return e && e[0] == '1'; }();
+  uint64_t run = 0;
+  uint64_t base[64];
+  for (uint32_t s = 0; s < W && s < 64; ++s) { base[s] = run; run += recv_records[s]; }
+  uint64_t bound = n_instances / ((uint64_t)std::max(mc, 0) + 1) + 1;
+  bool fast = !off && !histogram_only && (int)W <= std::min(64, shard_max_world()) && nb > 0 && h->ratio_est > 0 && h->ovf_cap > 0 &&
+              (!dedup || h->uq_cap > 0) && h->shard_cal_nb == nb && h->shard_cal_world == W && !h->shard_fast_banned &&
+              run <= 0xFFFFFFFFull && bound <= 0xFFFFFFF0ull && (W == 1 || (uint32_t)count_max_group() / W >= 1);
+  if (run && !d_recv) { set_error("null receive buffer"); return SHK_ERR_BAD_ARG; }
+  if (fast) {
+    const uint32_t node_cap = (uint32_t)bound;
+    SHK_CUDA(cudaEventRecord(h->ev[4], h->stream));
+    SHK_TRY(h->seg_off.ensure(nseg * 8 + 8)); SHK_TRY(h->seg_cnt.ensure(nseg * 4 + 4)); SHK_TRY(h->shard_btot.ensure((size_t)nb * 8 + 8));
+    SHK_TRY(h->node_lo.ensure((size_t)node_cap * 8));
+    if (h->kw == 2) SHK_TRY(h->node_hi.ensure((size_t)node_cap * 8));
+    SHK_TRY(h->node_count.ensure((size_t)node_cap * 2));
+    SHK_TRY(h->node_raw.ensure((size_t)node_cap));
+    h->node_cap = node_cap;
+    uint32_t uq_fast = 0;
+    if (dedup) {
+      uq_fast = (uint32_t)std::min<uint64_t>(std::max<uint64_t>((uint64_t)h->uq_cap * 2 + 1024, (uint64_t)h->uq_need_hint + h->uq_need_hint / 8), 0x7FFFFFC0ull);
+      uq_fast = (uq_fast + 63u) & ~63u;
+      const size_t ctas = (size_t)count_ctas();
+      SHK_TRY(h->uq_rec.ensure(ctas * uq_fast * 16 + 16)); SHK_TRY(h->uq_cnt.ensure(ctas * uq_fast * 4 + 16));
+    }
+    h->st.gpu_launches += launch_shard_segments(d_recv_fill, nb, W, base, h->seg_off.as<uint64_t>(), h->seg_cnt.as<uint32_t>(),
+                                                h->shard_btot.as<uint64_t>(), h->stream);
+    SHK_CUDA(cudaMemsetAsync(d_counters(h) + 2, 0, 8, h->stream));                     // n_distinct ([1], [3]: K1a's totals stay)
+    SHK_CUDA(cudaMemsetAsync(d_counters(h) + 4, 0, 4 * 8 + SHK_HISTO_BINS * 8 + 8 * 4, h->stream));   // spilled, decoded, records, spectrum, flags
+    h->st.gpu_launches += launch_table_fill(h->ovf.p, h->ovf_cap, h->kw, h->stream);
+    SelfPlanArgs spa{nb, h->ratio_est, count_table_slots(h->kw) * table_load(), d_flags(h) + 4, d_counters(h) + 6, W};
+    SHK_CUDA(cudaEventRecord(h->ev[10], h->stream));
+    h->st.gpu_launches += launch_count_buckets(h->kw, d_recv, h->shard_btot.as<uint64_t>(), 0xFFFFFFFFu, h->seg_off.as<uint64_t>(),
+                                               h->seg_cnt.as<uint32_t>(), dedup ? h->uq_rec.p : nullptr, h->uq_cnt.as<uint32_t>(), uq_fast,
+                                               nullptr, 0, 0, &spa, d_flags(h) + 2, h->p.k, mc,
+                                               h->ovf.p, h->ovf_cap, d_flags(h), d_flags(h) + 6, d_histo(h),
+                                               h->node_lo.as<uint64_t>(), h->node_hi.as<uint64_t>(), h->node_count.as<uint16_t>(),
+                                               h->node_raw.as<uint8_t>(), node_cap, d_flags(h) + 1, d_counters(h), h->stream);
+    SHK_CUDA(cudaGetLastError());
+    SHK_CUDA(cudaEventRecord(h->ev[11], h->stream));
+    SHK_TRY(read_scalars(h));
+    const uint32_t *fl = (const uint32_t *)(h->h_pinned + 8 + SHK_HISTO_BINS);
+    const uint32_t nn = fl[1];
+    if (fl[0] || fl[6] || (dedup && fl[5] > uq_fast) || nn > node_cap || h->h_pinned[6] != run) {
+      if (h->p.verbose > 1 || getenv("SHK_DEBUG"))
+        fprintf(stderr, "[shk] sharded steady-state count fell back: overflow table %u, list flag %u, list need %u / %u, records %llu / %llu\n",
+                fl[0], fl[6], fl[5], uq_fast, (unsigned long long)h->h_pinned[6], (unsigned long long)run);
+      if (dedup) h->uq_need_hint = std::max(h->uq_need_hint, fl[5]);
+      if (fl[0] || h->shard_fast_retried) h->shard_fast_banned = true;   // one more try with the larger lists, then stay host-planned
+      h->shard_fast_retried = true;
+      fast = false;
+    } else {
+      if (dedup) h->uq_need_hint = fl[5];
+      h->shard_fast_retried = false;
+      h->seg_per_bucket = W; h->src_instances = n_instances; h->shard_src = true; h->recv_recs = d_recv;
+      h->seg_kmers.clear(); h->seg_recs.clear();
+      h->counted_fast = false; h->st.device_planned = 1;
+      h->st.n_spilled = h->h_pinned[4]; h->spill_hint = h->st.n_spilled; h->st.n_records = run;
+      if (h->st.n_spilled) SHK_TRY(sweep_overflow(h, mc, node_cap));
+      memcpy(h->histo, h->h_pinned + 8, sizeof h->histo);
+      h->histo_valid = true;
+      uint64_t nd = 0;
+      for (int i = 0; i < SHK_HISTO_BINS; ++i) nd += h->histo[i];
+      h->st.n_distinct = nd;
+      if (n_instances) h->ratio_est = std::min(1.0, 1.10 * (double)nd / (double)n_instances + 0.005);
+      const uint32_t nn2 = ((const uint32_t *)(h->h_pinned + 8 + SHK_HISTO_BINS))[1];
+      if (nn2 > node_cap) { set_error("node buffer overflow (%u > %u)", nn2, node_cap); return SHK_ERR_STATE; }
+      h->st.n_nodes = nn2; h->st.used_min_count = mc;
+      SHK_CUDA(cudaEventRecord(h->ev[5], h->stream));
+      h->filtered = false; h->graphed = false; h->hu.valid = false;
+      h->shard_nodes_local = nn2;
+      return SHK_OK;
+    }
+  }
+  // host-planned: fetch the fills
+  SHK_TRY(h->hfill2.ensure_host(nseg * 8 + 8));
+  if (nseg) SHK_CUDA(cudaMemcpyAsync(h->hfill2.p, d_recv_fill, nseg * 8, cudaMemcpyDeviceToHost, h->stream));
+  SHK_CUDA(cudaStreamSynchronize(h->stream));
+  h->st.device_planned = 0;
+  shk_status st = shk_shard_count(h, d_recv, (const uint64_t *)h->hfill2.p, histogram_only, min_count);
+  if (st == SHK_OK && !histogram_only) { h->shard_cal_nb = nb; h->shard_cal_world = W; }
   return st;
 }
 

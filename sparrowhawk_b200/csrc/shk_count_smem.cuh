@@ -197,6 +197,8 @@ __device__ __forceinline__ uint4 record_item(uint4 c, u32 j) {
 struct SelfPlan {
   u32 P; u32 chunk /* buckets per chunk, <= SHK_CB_MAXC */; u32 ratio_q16; u64 budget_q16;
   u32 *stats; u64 *nrec;
+  u32 spb;   // segments per bucket: 1 = the local regions; W on the sharded path (bucket j = segments j*W .. j*W+W-1,
+             // one per source rank), where bstat holds the per-bucket totals over the sources
 };
 
 struct CountOut {
@@ -281,11 +283,12 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
     } else if (warp == 0) {
       // greedy cut: buckets b0, b0+1, ... while the estimated distinct k-mers stay within the budget (at least one)
       u32 run = 0, cnt = 0; u64 acc = 0;
+      const u32 maxb = (u32)SHK_CB_MAXC / sp.spb;
       for (u32 base = 0; b0 + base < ce; base += 32) {
         const u32 i = base + lane;
         const bool valid = b0 + i < ce;
         const u64 v = valid ? bstat[b0 + i] : 0ull;
-        const u32 fill = (u32)v, f = min(fill, rcap);
+        const u32 fill = (u32)v, f = seg_off ? fill : min(fill, rcap);
         sp_mxfill = max(sp_mxfill, fill);
         u64 est = (u64)(u32)(v >> 32) * sp.ratio_q16; u32 inc = f;
         for (int o = 1; o < 32; o <<= 1) {
@@ -294,11 +297,25 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
         }
         const bool fits = valid && (acc + est <= sp.budget_q16 || (cnt == 0 && lane == 0));
         const u32 m = __ballot_sync(0xffffffffu, fits);               // a prefix of the lanes: est only grows
-        const u32 take = m == 0xFFFFFFFFu ? 32u : (u32)__ffs(~m) - 1u;
+        u32 take = m == 0xFFFFFFFFu ? 32u : (u32)__ffs(~m) - 1u;
+        const bool capped = cnt + take > maxb;                          // a group holds at most SHK_CB_MAXC segments
+        if (capped) take = maxb - cnt;
         if ((u32)lane < take) { gpre[i + 1] = run + inc; sp_nrec += f; }
         if (take) { run += __shfl_sync(0xffffffffu, inc, take - 1); acc += __shfl_sync(0xffffffffu, est, take - 1); }
         cnt += take;
-        if (take < 32) break;
+        if (take < 32 || capped) break;
+      }
+      if (sp.spb > 1) {
+        // the buckets are chosen; the record prefix runs over their segments (one per source rank)
+        const u32 ns = cnt * sp.spb, s0 = b0 * sp.spb;
+        run = 0;
+        for (u32 base = 0; base < ns; base += 32) {
+          const u32 i = base + lane;
+          u32 inc = i < ns ? seg_cnt[s0 + i] : 0u;
+          for (int o = 1; o < 32; o <<= 1) { u32 v = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += v; }
+          if (i < ns) gpre[i + 1] = run + inc;
+          run += __shfl_sync(0xffffffffu, inc, 31);
+        }
       }
       if (lane == 0) { gpre[0] = 0; misc[10] = cnt; }
     }
@@ -309,7 +326,9 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
       if (!self_plan) misc[7] = g_begin + atomicAdd(next_group, 1u);
       else { misc[8] = b0 + nb; misc[9] = ce; if (took_chunk) misc[7] = g_begin + atomicAdd(next_group, 1u); }
     }
-    u32 total = gpre[nb];
+    // the group in segment units (group_start counts segments; the self-planner counts buckets)
+    const u32 sb0 = self_plan ? b0 * sp.spb : b0, snb = self_plan ? nb * sp.spb : nb;
+    u32 total = gpre[snb];
     uint4 *myrec = nullptr; u32 *mycnt = nullptr;
     if (DEDUP) {
       // ---- phase 1: distinct canonical records of the group, with multiplicities ----
@@ -318,9 +337,9 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
       myrec = uq_rec + (size_t)blockIdx.x * uq_cap; mycnt = uq_cnt + (size_t)blockIdx.x * uq_cap;
       // address of record f of the group: segment by binary search over the prefix
       auto rec_ptr = [&](u32 f) {
-        u32 lo = 0, hi = nb;
+        u32 lo = 0, hi = snb;
         while (hi - lo > 1) { u32 mid = (lo + hi) >> 1; if (gpre[mid] <= f) lo = mid; else hi = mid; }
-        const u64 sbase = seg_off ? seg_off[b0 + lo] : (u64)(b0 + lo) * rcap;
+        const u64 sbase = seg_off ? seg_off[sb0 + lo] : (u64)(sb0 + lo) * rcap;
         return reinterpret_cast<const uint4 *>(recs + (sbase + (f - gpre[lo])));
       };
       auto insert_record = [&](uint4 c) {
@@ -449,9 +468,9 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
           n = r.x & 31u; hasl = (r.x >> 5) & 1u; hasr = (r.x >> 6) & 1u;
         }
       } else if (f < total) {
-        u32 lo = 0, hi = nb;                              // segment with gpre[lo] <= f < gpre[lo+1]
+        u32 lo = 0, hi = snb;                             // segment with gpre[lo] <= f < gpre[lo+1]
         while (hi - lo > 1) { u32 mid = (lo + hi) >> 1; if (gpre[mid] <= f) lo = mid; else hi = mid; }
-        const u64 sbase = seg_off ? seg_off[b0 + lo] : (u64)(b0 + lo) * rcap;
+        const u64 sbase = seg_off ? seg_off[sb0 + lo] : (u64)(sb0 + lo) * rcap;
         const uint4 *src = reinterpret_cast<const uint4 *>(recs + (sbase + (f - gpre[lo])));
         if (KW == 1) {
           uint4 r = __ldcs(src); wst[lane] = r;

@@ -87,6 +87,10 @@ struct shk_asm {
   // ---- K1a output: super-k-mer records in P fine-bucket regions of rcap records ----
   shk::DevBuf skrecs, bfill /* u32 fill[P] | u32 kcount[P] */, groups, ovf;
   shk::PinBuf hoff /* shard_partition: dense send offsets */, hseg /* shard_count: segment offsets + counts */;
+  shk::PinBuf hfill2 /* shard_count_device falling back: the received fills on the host */;
+  shk::PinBuf hsend /* shard_partition: records per owner rank + largest fill, from the device-side send plan */;
+  uint64_t send_base[64] = {0};                // first record of each owner rank in the send buffer
+  bool send_planned = false;                   // pack_off holds rank-local offsets (device-side send plan)
   shk::PinBuf hfill, pin_stage /* D2H staging of the unitig sequences */;
   uint32_t P = 0, rcap = 0;
   uint64_t n_records = 0, ovf_cap = 0, spill_hint = 0 /* instances that spilled on the last run */;
@@ -108,8 +112,11 @@ struct shk_asm {
   uint32_t shard_world = 0, shard_rank = 0;      // 0 = not in a sharded run
   bool shard_src = false;                        // K1b reads the received records instead of the local regions
   const void *recv_recs = nullptr;               // caller-owned device buffer (records received from all ranks)
-  shk::DevBuf seg_off, seg_cnt, pack_off;
+  shk::DevBuf seg_off, seg_cnt, pack_off, send_tot, shard_btot /* per owned bucket: records | k-mers << 32 over all sources */;
   uint64_t shard_node_offset = 0, shard_nodes_local = 0;
+  // sharded steady-state count (shk_shard_count_device): calibrated by a host-planned run over this many owned buckets / ranks
+  uint32_t shard_cal_nb = 0, shard_cal_world = 0;
+  bool shard_fast_banned = false, shard_fast_retried = false;
   // ---- node index (key -> node id) for the graph stage ----
   shk::DevBuf slots;
   uint64_t cap = 0;

@@ -689,6 +689,7 @@ size_t record_bytes(int kw) { return kw == 1 ? 16 : 32; }
 int records_max_run(int kw, int k) { return rec_max_run(kw, k); }
 int count_table_slots(int kw) { return kw == 1 ? CbCfg<1>::NS : CbCfg<2>::NS; }
 int count_max_group() { return SHK_CB_MAXC; }
+#define SHK_MAX_WORLD 64          // ranks of the sharded path whose segment tables are built on the device
 int count_ctas() { return sm_count() * SHK_CB_PER_SM; }
 
 int launch_partition(int kw, const uint64_t *bases, const uint32_t *mask, uint64_t nwords, int k, uint32_t P,
@@ -712,14 +713,16 @@ int launch_count_buckets(int kw, const void *recs, const uint64_t *bstat, uint32
                          uint16_t *node_count, uint8_t *node_raw, uint32_t node_cap, uint32_t *n_nodes,
                          uint64_t *counters, cudaStream_t st) {
   if (group_start && g_end <= g_begin) return 0;
-  SelfPlan sp{0, 1, 0, 1, nullptr, nullptr};
+  SelfPlan sp{0, 1, 0, 1, nullptr, nullptr, 1};
   if (!group_start) {
     if (!self_plan || !self_plan->n_buckets) return 0;
     u32 rq = (u32)(self_plan->ratio * 65536.0 + 0.5);
     u64 bq = (u64)(self_plan->budget * 65536.0);
     u32 chunk = 16;                                       // ~8 chunks per CTA, a power of two in [16, SHK_CB_MAXC]
     while (chunk < SHK_CB_MAXC && (u64)chunk * 2 * 8 * (u64)count_ctas() <= self_plan->n_buckets) chunk *= 2;
-    sp = SelfPlan{self_plan->n_buckets, chunk, rq < 1 ? 1u : rq, bq < 1 ? 1ull : bq, self_plan->stats, (u64 *)self_plan->nrec};
+    const u32 spb = self_plan->seg_per_bucket ? self_plan->seg_per_bucket : 1u;
+    if (spb > SHK_CB_MAXC) return 0;
+    sp = SelfPlan{self_plan->n_buckets, chunk, rq < 1 ? 1u : rq, bq < 1 ? 1ull : bq, self_plan->stats, (u64 *)self_plan->nrec, spb};
   }
   static bool attr_set = false;
   if (!attr_set) {
@@ -745,27 +748,137 @@ int launch_count_buckets(int kw, const void *recs, const uint64_t *bstat, uint32
   return 1;
 }
 
+struct PackBases { u32 n; u64 base[64]; };           // n = 0: dst_off is absolute
 // Sharded path: compact the fixed-stride bucket regions into one dense buffer ordered
 // by bucket (= ordered by owner rank), the send buffer of the record all-to-all.
 // One warp per bucket, 128-bit copies.
 __global__ void __launch_bounds__(256)
 k_pack_records(const uint4 *__restrict__ recs, const u64 *__restrict__ bstat, u32 rcap, const u64 *__restrict__ dst_off,
-               u32 P, int rw /* uint4s per record */, uint4 *__restrict__ out) {
+               u32 P, int rw /* uint4s per record */, uint4 *__restrict__ out, PackBases pb) {
   const u32 lane = threadIdx.x & 31;
   const u32 warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
   for (u32 b = warp; b < P; b += nwarps) {
     const u64 n = (u64)min((u32)bstat[b], rcap) * (u64)rw;
     const uint4 *src = recs + (u64)b * rcap * (u64)rw;
-    uint4 *dst = out + dst_off[b] * (u64)rw;
+    u64 first = dst_off[b];
+    if (pb.n) {                                        // offsets are local to the owner rank: add where that rank's records start
+      u32 r = (u32)(((u64)b * pb.n) / P);
+      while (r + 1 < pb.n && (u32)(((u64)(r + 1) * P) / pb.n) <= b) ++r;
+      first += pb.base[r];
+    }
+    uint4 *dst = out + first * (u64)rw;
     for (u64 i = lane; i < n; i += 32) dst[i] = __ldcs(src + i);
   }
 }
 int launch_pack_records(int kw, const void *recs, const uint64_t *bstat, uint32_t rcap, const uint64_t *dst_off, uint32_t P,
-                        void *out, cudaStream_t st) {
+                        void *out, cudaStream_t st, uint32_t world, const uint64_t *rank_base) {
   if (!P) return 0;
+  PackBases pb; pb.n = 0;
+  if (world && rank_base && world <= 64) { pb.n = world; for (u32 i = 0; i < world; ++i) pb.base[i] = rank_base[i]; }
   unsigned g = grid_persistent((uint64_t)P * 32, 256, 8);
-  k_pack_records<<<g, 256, 0, st>>>((const uint4 *)recs, (const u64 *)bstat, rcap, (const u64 *)dst_off, P, kw == 1 ? 1 : 2, (uint4 *)out);
+  k_pack_records<<<g, 256, 0, st>>>((const uint4 *)recs, (const u64 *)bstat, rcap, (const u64 *)dst_off, P, kw == 1 ? 1 : 2, (uint4 *)out, pb);
   return 1;
+}
+
+// Sharded path, owner side: the received fills (records | k-mers << 32, source-major: entry (s, j) at s * nb + j)
+// become the segment table K1b reads — segment (bucket j, source s) at j * W + s, its first record and its
+// record count — and the per-bucket totals the self-planner cuts groups from.  One CTA per source scans that
+// source's nb fills (its records lie densely, in bucket order, from src_base[s] on).
+struct ShardSources { u32 n; u64 base[SHK_MAX_WORLD]; };
+
+__global__ void __launch_bounds__(1024)
+k_shard_segments(const u64 *__restrict__ fill, u32 nb, ShardSources src, u64 *__restrict__ seg_off, u32 *__restrict__ seg_cnt) {
+  __shared__ u32 wsum[32];
+  __shared__ u64 carry;
+  const u32 s = blockIdx.x, W = src.n, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (threadIdx.x == 0) carry = src.base[s];
+  __syncthreads();
+  for (u32 j0 = 0; j0 < nb; j0 += 1024) {
+    const u32 j = j0 + threadIdx.x;
+    const u32 f = j < nb ? (u32)fill[(size_t)s * nb + j] : 0u;
+    u32 inc = f;
+    for (int o = 1; o < 32; o <<= 1) { u32 v = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += v; }
+    if (lane == 31) wsum[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+      u32 w = wsum[lane];
+      for (int o = 1; o < 32; o <<= 1) { u32 v = __shfl_up_sync(0xffffffffu, w, o); if (lane >= o) w += v; }
+      wsum[lane] = w;                                                // inclusive over the warps
+    }
+    __syncthreads();
+    const u64 before = carry + (warp ? wsum[warp - 1] : 0u) + (inc - f);
+    if (j < nb) { seg_off[(size_t)j * W + s] = before; seg_cnt[(size_t)j * W + s] = f; }
+    __syncthreads();
+    if (threadIdx.x == 0) carry += wsum[31];
+    __syncthreads();
+  }
+}
+
+__global__ void __launch_bounds__(256)
+k_shard_bucket_totals(const u64 *__restrict__ fill, u32 nb, u32 W, u64 *__restrict__ tot) {
+  const u32 j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= nb) return;
+  u64 t = 0;
+  for (u32 s = 0; s < W; ++s) t += fill[(size_t)s * nb + j];         // both halves add without a carry (checked by the host)
+  tot[j] = t;
+}
+
+// Sharded path, sender side: rank-local dense offsets of the buckets in the send buffer (one CTA per owner rank
+// scans the clamped fills of that rank's bucket range), the records held for each owner, the largest fill.
+struct ShardRanges { u32 n; u32 start[SHK_MAX_WORLD + 1]; };
+
+__global__ void __launch_bounds__(1024)
+k_shard_send_plan(const u64 *__restrict__ fill, u32 rcap, ShardRanges rg, u64 *__restrict__ off, u64 *__restrict__ totals /* [n] + max fill */) {
+  __shared__ u32 wsum[32];
+  __shared__ u64 carry;
+  const u32 s = blockIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const u32 b0 = rg.start[s], b1 = rg.start[s + 1];
+  if (threadIdx.x == 0) carry = 0;
+  u32 mx = 0;
+  __syncthreads();
+  for (u32 j0 = b0; j0 < b1; j0 += 1024) {
+    const u32 j = j0 + threadIdx.x;
+    const u32 raw = j < b1 ? (u32)fill[j] : 0u, f = min(raw, rcap);
+    mx = max(mx, raw);
+    u32 inc = f;
+    for (int o = 1; o < 32; o <<= 1) { u32 v = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += v; }
+    if (lane == 31) wsum[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+      u32 w = wsum[lane];
+      for (int o = 1; o < 32; o <<= 1) { u32 v = __shfl_up_sync(0xffffffffu, w, o); if (lane >= o) w += v; }
+      wsum[lane] = w;
+    }
+    __syncthreads();
+    if (j < b1) off[j] = carry + (warp ? wsum[warp - 1] : 0u) + (inc - f);
+    __syncthreads();
+    if (threadIdx.x == 0) carry += wsum[31];
+    __syncthreads();
+  }
+  for (int o = 16; o; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  if (lane == 0 && mx) atomicMax(reinterpret_cast<u32 *>(totals + rg.n), mx);
+  if (threadIdx.x == 0) totals[s] = carry;
+}
+
+int launch_shard_send_plan(const uint64_t *d_fill, uint32_t rcap, uint32_t world, const uint32_t *starts, uint64_t *off,
+                           uint64_t *totals, cudaStream_t st) {
+  if (!world || world > SHK_MAX_WORLD) return 0;
+  ShardRanges rg; rg.n = world;
+  for (u32 i = 0; i <= world; ++i) rg.start[i] = starts[i];
+  k_shard_send_plan<<<world, 1024, 0, st>>>((const u64 *)d_fill, rcap, rg, (u64 *)off, (u64 *)totals);
+  return 1;
+}
+
+int shard_max_world() { return SHK_MAX_WORLD; }
+
+int launch_shard_segments(const uint64_t *d_fill, uint32_t nb, uint32_t world, const uint64_t *src_base, uint64_t *seg_off,
+                          uint32_t *seg_cnt, uint64_t *bucket_tot, cudaStream_t st) {
+  if (!nb || !world || world > SHK_MAX_WORLD) return 0;
+  ShardSources src; src.n = world;
+  for (u32 i = 0; i < world; ++i) src.base[i] = src_base[i];
+  k_shard_segments<<<world, 1024, 0, st>>>((const u64 *)d_fill, nb, src, (u64 *)seg_off, seg_cnt);
+  k_shard_bucket_totals<<<blocks_for(nb, 256), 256, 0, st>>>((const u64 *)d_fill, nb, world, (u64 *)bucket_tot);
+  return 2;
 }
 
 int launch_index_nodes(int kw, void *slots, uint64_t cap, const uint64_t *node_lo, const uint64_t *node_hi, uint32_t n_nodes,

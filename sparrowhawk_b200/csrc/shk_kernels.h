@@ -63,7 +63,8 @@ int launch_partition(int kw, const uint64_t *bases, const uint32_t *mask, uint64
 int partition_tile_words();
 // group_start == null: the CTAs cut their own groups (steady-state runs).  stats (device, zeroed by the caller):
 // [0] largest bucket fill, [1] most distinct items in a group; *nrec (device, zeroed): records counted.
-struct SelfPlanArgs { uint32_t n_buckets; double ratio; double budget; uint32_t *stats; uint64_t *nrec; };
+// seg_per_bucket: 0/1 = one segment per bucket; W = the sharded path (bucket j = segments j*W .. j*W+W-1, bstat = totals)
+struct SelfPlanArgs { uint32_t n_buckets; double ratio; double budget; uint32_t *stats; uint64_t *nrec; uint32_t seg_per_bucket; };
 // seg_off / seg_cnt (nullable): explicit record segments (sharded path); null = segment i is local bucket region i
 int launch_count_buckets(int kw, const void *recs, const uint64_t *bstat, uint32_t rcap, const uint64_t *seg_off,
                          const uint32_t *seg_cnt, void *uq_rec /* nullable: per-CTA distinct-record lists (de-dup) */,
@@ -73,8 +74,17 @@ int launch_count_buckets(int kw, const void *recs, const uint64_t *bstat, uint32
                          uint64_t ovf_cap, uint32_t *ovf_flag, uint32_t *uq_flag, uint64_t *histo, uint64_t *node_lo, uint64_t *node_hi,
                          uint16_t *node_count, uint8_t *node_raw, uint32_t node_cap, uint32_t *n_nodes,
                          uint64_t *counters, cudaStream_t st);
+// world / rank_base (host, nullable): dst_off is local to the owner rank and rank r's records start at rank_base[r]
 int launch_pack_records(int kw, const void *recs, const uint64_t *bstat, uint32_t rcap, const uint64_t *dst_off, uint32_t P,
-                        void *out, cudaStream_t st);
+                        void *out, cudaStream_t st, uint32_t world = 0, const uint64_t *rank_base = nullptr);
+// sharded path, sender side: rank-local send offsets per bucket, records per owner (totals[0..world)), largest fill
+// (low word of totals[world], zeroed by the caller); starts = world + 1 bucket range boundaries (host)
+int launch_shard_send_plan(const uint64_t *d_fill, uint32_t rcap, uint32_t world, const uint32_t *starts, uint64_t *off,
+                           uint64_t *totals, cudaStream_t st);
+// sharded path, owner side: segment table + per-bucket totals from the received fills, on the device (world <= shard_max_world())
+int shard_max_world();
+int launch_shard_segments(const uint64_t *d_fill, uint32_t nb, uint32_t world, const uint64_t *src_base /* host, [world] */,
+                          uint64_t *seg_off, uint32_t *seg_cnt, uint64_t *bucket_tot, cudaStream_t st);
 int launch_index_nodes(int kw, void *slots, uint64_t cap, const uint64_t *node_lo, const uint64_t *node_hi, uint32_t n_nodes,
                        uint32_t *overflow, cudaStream_t st);
 

@@ -72,6 +72,13 @@ class GpuEngine:
         check(self.lib.shk_shard_count(self.h._h, recv_buf.data_ptr() if recv_buf.numel() else None, rf.ctypes.data,
                                        int(histogram_only), int(min_count)))
 
+    def count_device(self, recv_buf, recv_fill, recv_records, n_instances, min_count):
+        """fills stay on the device (steady-state form; falls back to the host-planned count inside the library)"""
+        rr = np.asarray(recv_records, dtype=np.uint64)
+        self._keep = (recv_buf, recv_fill)
+        check(self.lib.shk_shard_count_device(self.h._h, recv_buf.data_ptr() if recv_buf.numel() else None,
+                                              recv_fill.data_ptr(), rr.ctypes.data, int(n_instances), 0, int(min_count)))
+
     def local_counts(self):
         st = self.h.stats()
         return st["n_nodes"], int(self._instances_seen())
@@ -182,11 +189,20 @@ def sharded_run(eng, group=None, timings=None):
     fill_in = [shard_range(P, world, r)[1] - shard_range(P, world, r)[0] for r in range(world)]
     recv_fill = torch.empty(world * n_own, **i64)
     _a2a(recv_fill, send_fill, [n_own] * world, fill_in, group)
-    rf_host = recv_fill.cpu().numpy().view(np.uint64).reshape(world, n_own)
-    recv_records = [int((rf_host[s] & np.uint64(0xFFFFFFFF)).sum()) for s in range(world)]
+    on_device = hasattr(eng, "count_device") and recv_fill.is_cuda and not eng.do_fit
+    if on_device:
+        # only the per-source sums cross to the host: records (sizes of the second all-to-all), k-mer instances
+        rf2 = recv_fill.view(world, n_own)
+        sums = torch.stack([(rf2 & 0xFFFFFFFF).sum(1), (rf2 >> 32).sum(1)]).cpu().numpy()
+        recv_records = [int(x) for x in sums[0]]
+        inst_local = int(sums[1].sum())
+        rf_host = None
+    else:
+        rf_host = recv_fill.cpu().numpy().view(np.uint64).reshape(world, n_own)
+        recv_records = [int((rf_host[s] & np.uint64(0xFFFFFFFF)).sum()) for s in range(world)]
+        inst_local = int((rf_host >> np.uint64(32)).sum())
     recv_buf = torch.empty(sum(recv_records) * rw, **i64)
     _a2a(recv_buf, send_buf, [n * rw for n in recv_records], [n * rw for n in send_records], group)
-    inst_local = int((rf_host >> np.uint64(32)).sum())
     mark("all_to_all")
 
     # ---- owner-side count, spectrum, filter ----
@@ -196,7 +212,10 @@ def sharded_run(eng, group=None, timings=None):
         hist = torch.from_numpy(eng.histogram().astype(np.int64)).to(dev)
         _all_reduce(hist, group)
         used_mc = eng.fit(hist.cpu().numpy().astype(np.uint64), eng.min_count)
-    eng.count(recv_buf, rf_host, False, used_mc)
+    if on_device:
+        eng.count_device(recv_buf, recv_fill, recv_records, inst_local, used_mc)
+    else:
+        eng.count(recv_buf, rf_host, False, used_mc)
     n_local, _ = eng.local_counts()
     mark("count")
 

@@ -156,10 +156,14 @@ def main():
         h = AssemblyHelper.new(k, False, min_count, min_qual, 0, False, False, False, False, device=0)
         h.load_reads(seq, qual)
         eng = GpuEngine(h, torch.device("cuda", 0))
-        for _ in range(2):                 # twice: buffers and estimates are reused on the second pass
-            info = sharded_run(eng)
+        planned = []
+        for _ in range(3):                 # the first pass calibrates (host-planned count); later ones reuse buffers and
+            info = sharded_run(eng)        # estimates and count with the fills left on the device (shk_shard_count_device)
+            planned.append(h.stats()["device_planned"])
             assert info["n_nodes"] == so["n_nodes"], (info["n_nodes"], so["n_nodes"])
             assert_parity(h, o, check_table=False)
+        print(f"rank {rank}: device-planned count per pass {planned}")
+        assert planned[0] == 0 and planned[-1] == 1, planned
         if world > 1:
             assert min(info["nodes_per_rank"]) > 0
         h.close()
