@@ -144,7 +144,7 @@ def reference_arm(args, w, rank, world):
     ms = 1e3 * sum(times) / len(times)
     v = bases / (ms * 1e-3)
     sample = f"first {sp} of {npairs} read pairs ({bases/1e6:.1f} Mbase) of workload {args.workload}"
-    print(json.dumps({
+    print(file=_OUT, flush=True, *[json.dumps({
         "impl": "reference", "metric": "input bases/s, k-mer count + DBG build", "value": v, "unit": "bases/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64" if w["k"] <= 31 else "u128",
@@ -154,7 +154,10 @@ def reference_arm(args, w, rank, world):
         "e2e": {"value": v, "unit": "bases/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
         "note": "CPU oracle (restatement of the path); sparrowhawk-asm native CPU: unavailable on this box",
-    }))
+    })])
+
+
+_OUT = sys.stdout
 
 
 def main():
@@ -173,6 +176,11 @@ def main():
         args.warmup = 1
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
+    # stdout carries the one JSON line and nothing else: whatever libraries print (NCCL's version banner) goes to stderr
+    sys.stdout.flush()
+    global _OUT
+    _OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     local = int(os.environ.get("LOCAL_RANK", "0"))
     w = dict(WORKLOADS[args.workload])
     w["seed"] = 2 + rank          # rank r holds the reads of genome r of the community
@@ -196,7 +204,6 @@ def main():
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")     # stdout carries the one JSON line only
         dist.init_process_group("nccl", device_id=dev)
 
     # ---- synthetic reads into pinned host memory --------------------------
@@ -287,9 +294,12 @@ def main():
             t.append(time.perf_counter())
             info = h.get_preprocessing_info()
             t.append(time.perf_counter())
-            h.assemble()
+            # every rank holds the complete unitig graph after sharded_run; the host-side tail (cleaning, contigs, the
+            # four texts) is one job's worth of work, done once — on rank 0 — while the others wait at the barrier
+            if rank == 0:
+                h.assemble()
             t.append(time.perf_counter())
-            res = h.get_assembly()
+            res = h.get_assembly_view() if rank == 0 else None      # the C ABI's pointer + length: no copy into a str
             t.append(time.perf_counter())
             for name, a, b in zip(call_ms, t[:-1], t[1:]):
                 call_ms[name].append((b - a) * 1e3)
@@ -310,12 +320,12 @@ def main():
         ms_e2e = float(t.item()) / args.steps
         s2 = h.stats()
         d2h = int(s2["unitig_bases"] + s2["n_unitigs"] * 25 + s2["n_links"] * 8 + 3 * 4200 + 128)
-        calls = ("shk_asm_preprocess_reads + shk_asm_preprocessing_info + shk_asm_assemble + shk_asm_get_assembly" if world == 1 else
-                 "shk_load_reads + sharded_run (shk_shard_* + NCCL) + shk_asm_preprocessing_info + shk_asm_assemble + shk_asm_get_assembly")
+        calls = ("shk_asm_preprocess_reads + shk_asm_preprocessing_info + shk_asm_assemble + shk_asm_get_assembly (pointer + length)" if world == 1 else
+                 "per rank: shk_load_reads + sharded_run (shk_shard_* + NCCL) + shk_asm_preprocessing_info; rank 0: shk_asm_assemble + shk_asm_get_assembly")
         e2e = {"value": bases * world / (ms_e2e * 1e-3), "unit": "bases/s", "h2d_bytes_per_step": int(2 * nbytes) * world,
                "d2h_bytes_per_step": d2h * world, "ms_per_step": ms_e2e, "calls": calls,
                "call_ms": {n: round(sum(v[1:]) / max(1, len(v) - 1), 3) for n, v in call_ms.items()},
-               "ncontigs": json.loads(res)["ncontigs"], "nkmers": json.loads(info)["nkmers"]}
+               "ncontigs": json.loads(bytes(res))["ncontigs"] if res is not None else None, "nkmers": json.loads(info)["nkmers"]}
 
     # ---- roofline of the dominant kernel (K1b k_count_buckets) ----------------
     peak, peak_src = peaks()
@@ -357,7 +367,7 @@ def main():
         multi = ("single GPU" if world == 1 else
                  f"one read set of {world} genomes sharded by read pair over {world} ranks; records routed to the owner "
                  "rank by minimizer-bucket range through an NCCL all-to-all; nodes all-gathered; graph stage on the gathered set")
-        print(json.dumps({
+        print(file=_OUT, flush=True, *[json.dumps({
             "metric": "input bases/s, k-mer count + DBG build", "value": value, "unit": "bases/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -371,7 +381,7 @@ def main():
                        "fine_buckets": st["table_slots"], "gen_seconds": round(t_gen, 2)},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
             "clocks": clocks,
-        }))
+        })])
     h.close()
     if world > 1:
         dist.destroy_process_group()

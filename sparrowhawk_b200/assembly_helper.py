@@ -139,6 +139,14 @@ class AssemblyHelper:
         check(self._lib.shk_asm_get_assembly(self._h, C.byref(s), C.byref(n)))
         return _ascii_str(s, n.value)
 
+    def get_assembly_view(self) -> memoryview:
+        """The same JSON as get_assembly(), as a read-only view of the library's own buffer — what a C or Rust
+        caller of shk_asm_get_assembly holds (pointer + length, no copy).  Valid until the next assemble() or
+        close(); `bytes(view)` / `str(view, "ascii")` make the copy get_assembly() makes."""
+        s, n = C.c_void_p(), C.c_size_t()
+        check(self._lib.shk_asm_get_assembly(self._h, C.byref(s), C.byref(n)))
+        return memoryview((C.c_char * n.value).from_address(s.value)).toreadonly()
+
     # ---- other preprocess forms of the C ABI ----------------------------
     def preprocess_reads(self, seq, qual=None):
         sp, n, k1 = _buf(seq)

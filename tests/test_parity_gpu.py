@@ -211,6 +211,7 @@ def test_assemble_contigs_match_cleaned_oracle_graph(flags):
     assert got == pc
     assert canon_links(c["seq"], c["link_from"], c["link_to"]) == pl
     res = h.assembly_result()
+    assert bytes(h.get_assembly_view()) == h.get_assembly().encode("ascii")       # the no-copy form of the same answer
     assert res["ncontigs"] == len(pc) < len(units)
     fa = [l for l in res["outfasta"].splitlines() if not l.startswith(">")]
     assert sorted(fa) == [p[0] for p in pc]
