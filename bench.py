@@ -39,6 +39,9 @@ WORKLOADS = {
     "B": dict(G=5_000_000, cov=100.0, err=0.005, k=31, min_count=5, desc="5 Mb genome, 100x 150bp PE, 0.5% error, k=31"),
     "C": dict(G=5_000_000, cov=100.0, err=0.01, k=63, min_count=5, desc="5 Mb genome, 100x 150bp PE, 1% error, k=63"),
     "S": dict(G=200_000, cov=30.0, err=0.005, k=31, min_count=3, desc="smoke: 200 kb genome, 30x"),
+    # replicas only: independent genomes, no collective; rank r assembles genomes r*96/N .. (r+1)*96/N
+    "D": dict(G=3_000_000, cov=50.0, err=0.005, k=31, min_count=3, n_genomes=96,
+              desc="batch of 96 x 3 Mb genomes, 50x 150bp PE, 0.5% error, k=31 (replicas, no collective)"),
 }
 L = 150
 MIN_QUAL = 20
@@ -160,6 +163,132 @@ def reference_arm(args, w, rank, world):
 _OUT = sys.stdout
 
 
+def replicas_arm(args, w, rank, world, local):
+    """Config D: a batch of independent genomes, `n_genomes / world` per rank, no data-path collective.
+    Each rank keeps WORKERS handles (own stream each) busy from a shared queue of its genomes, one host
+    thread per handle, so one genome's host round trips hide under another's kernels.  The genomes of a rank
+    cycle through DISTINCT synthetic read sets of the same shape (every genome is still loaded, cut, counted
+    and compacted in full inside the timed region)."""
+    import queue
+    import threading
+    import torch
+    import torch.distributed as dist
+    from sparrowhawk_b200 import AssemblyHelper, synth
+    WORKERS, DISTINCT = 3, 4
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    n_g = w["n_genomes"]
+    mine = list(range(rank * n_g // world, (rank + 1) * n_g // world))
+    npairs = synth.num_pairs(w["G"], w["cov"], L)
+    nbytes = npairs * 2 * (L + 1)
+    bases = npairs * 2 * L
+    host, devb = [], []
+    t0 = time.perf_counter()
+    for d in range(min(DISTINCT, len(mine))):
+        ps = torch.empty(nbytes, dtype=torch.uint8, pin_memory=True)
+        pq = torch.empty(nbytes, dtype=torch.uint8, pin_memory=True)
+        synth.reads(1000 + 17 * rank + d, w["G"], w["cov"], w["err"], L, out=(ps.numpy(), pq.numpy()))
+        host.append((ps, pq)); devb.append((ps.cuda(), pq.cuda()))
+    t_gen = time.perf_counter() - t0
+    hs = [AssemblyHelper.new(w["k"], False, w["min_count"], MIN_QUAL, 0, False, False, False, False, device=local)
+          for _ in range(WORKERS)]                      # each handle runs on its own stream
+
+    def run_batch(e2e):
+        q = queue.Queue()
+        for i, g in enumerate(mine):
+            q.put(i)
+        err = []
+
+        def worker(h):
+            try:
+                while True:
+                    try:
+                        i = q.get_nowait()
+                    except queue.Empty:
+                        return
+                    if e2e:       # host buffers through the reference-facing calls
+                        ps, pq = host[i % len(host)]
+                        h.preprocess_reads(ps.numpy(), pq.numpy()); h.get_preprocessing_info(); h.assemble(); h.get_assembly_view()
+                    else:         # device-resident reads: K0 from the resident ASCII, then the path
+                        ds, dq = devb[i % len(devb)]
+                        h.load_reads_ptr(ds.data_ptr(), dq.data_ptr(), nbytes, device=True); h.run()
+            except Exception as ex:        # noqa: BLE001
+                err.append(ex)
+        th = [threading.Thread(target=worker, args=(h,)) for h in hs]
+        for t in th:
+            t.start()
+        for t in th:
+            t.join()
+        if err:
+            raise err[0]
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(e2e, steps, warmup):
+        for _ in range(warmup):
+            run_batch(e2e)
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); t0 = time.perf_counter()
+        for _ in range(steps):
+            run_batch(e2e)
+        torch.cuda.synchronize()                      # all the handles' streams
+        e1.record(); e1.synchronize()
+        ms = max((time.perf_counter() - t0) * 1e3, e0.elapsed_time(e1))
+        barrier()
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item()) / steps
+
+    l0 = sum(h.stats()["gpu_launches"] for h in hs)
+    sampler = ClockSampler(local)
+    ms_step = timed(False, args.steps, args.warmup)
+    clocks = sampler.stop()
+    launches = (sum(h.stats()["gpu_launches"] for h in hs) - l0) // (args.steps + args.warmup) * args.steps
+    k1b = sum(h.stats()["ms_count_kernel"] for h in hs) / len(hs)
+    k1a = sum(h.stats()["ms_extract"] for h in hs) / len(hs)
+    st = hs[0].stats()
+    e2e = None
+    if not args.no_e2e:
+        ms_e2e = timed(True, max(1, args.steps // 2), 1)
+        e2e = {"value": bases * n_g / (ms_e2e * 1e-3), "unit": "bases/s", "h2d_bytes_per_step": int(2 * nbytes) * n_g,
+               "d2h_bytes_per_step": int(st["unitig_bases"] + st["n_unitigs"] * 25 + 4400) * n_g, "ms_per_step": ms_e2e,
+               "calls": "per genome: shk_asm_preprocess_reads + shk_asm_preprocessing_info + shk_asm_assemble + shk_asm_get_assembly (pointer + length)"}
+    peak, peak_src = peaks()
+    slot = 16
+    alg_table = (L - w["k"] + 1) / L * 2 * slot
+    alg_all = alg_bytes_per_base(w["k"])
+    total_bases = bases * n_g
+    if rank == 0:
+        print(file=_OUT, flush=True, *[json.dumps({
+            "metric": "input bases/s, k-mer count + DBG build", "value": total_bases / (ms_step * 1e-3), "unit": "bases/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+            "config": {"workload": f"D: {w['desc']}", "min_qual": MIN_QUAL, "min_count": w["min_count"],
+                       "genomes_per_step": n_g, "genomes_per_gpu": len(mine), "bases_per_genome": bases,
+                       "multi_gpu": "replicas only: independent handles, no collective",
+                       "handles_per_gpu": WORKERS, "distinct_read_sets_per_gpu": len(host),
+                       "l2": "inputs larger than L2: each genome's ASCII reads %.0f MB + records" % (2 * nbytes / 1e6),
+                       "n_nodes": st["n_nodes"], "n_unitigs": st["n_unitigs"], "gen_seconds": round(t_gen, 2)},
+            "roofline": {"bound": "hbm", "kernel": "k_count_buckets", "achieved": alg_table * bases / (k1b * 1e-3) / 1e9,
+                         "peak": peak, "unit": "GB/s", "frac": alg_table * bases / (k1b * 1e-3) / 1e9 / peak, "traffic": None,
+                         "peak_source": peak_src, "kernel_ms": k1b, "k_minimizer_partition_ms": k1a,
+                         "whole_step_achieved": alg_all * total_bases / world / (ms_step * 1e-3) / 1e9,
+                         "whole_step_frac": alg_all * total_bases / world / (ms_step * 1e-3) / 1e9 / peak},
+            "cpu_baseline": None, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
+        })])
+    for h in hs:
+        h.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -192,6 +321,12 @@ def main():
         return
     if args.cpu_sample_frac is None:
         args.cpu_sample_frac = 0.4
+    if "n_genomes" in w:
+        import torch
+        if not torch.cuda.is_available():
+            raise SystemExit("bench.py needs a CUDA device: the product path has no CPU fallback")
+        replicas_arm(args, w, rank, world, local)
+        return
 
     import numpy as np
     import torch

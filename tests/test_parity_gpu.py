@@ -331,6 +331,32 @@ def test_repeatability_under_load(k):
     h.close()
 
 
+def test_replica_handles_run_concurrently():
+    """Config D's form (replicas only): independent handles on their own streams, driven from one
+    host thread each at the same time, every one bit-exact against the oracle on its own genome."""
+    import threading
+    sets = [synth.reads(90 + i, 120_000 + 10_000 * i, 25.0, 0.01) for i in range(3)]
+    hs = [AssemblyHelper.new(31, False, 2, 20, 0, False, False, False, False) for _ in sets]
+    errs = []
+
+    def work(h, seq, qual):
+        try:
+            for _ in range(3):             # host-planned once, then the steady-state path
+                h.load_reads(seq, qual)
+                h.run()
+        except Exception as ex:            # noqa: BLE001
+            errs.append(ex)
+    th = [threading.Thread(target=work, args=(h, s, q)) for h, (s, q) in zip(hs, sets)]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    assert not errs, errs
+    for h, (s, q) in zip(hs, sets):
+        assert_parity(h, run_oracle(s, q, 31, 2, 20), check_table=False)
+        h.close()
+
+
 def test_errors():
     h = AssemblyHelper.new(31, False, 2, 20, 0, False, False, False, False)
     with pytest.raises(ShkError):
