@@ -600,8 +600,8 @@ k_index_nodes(Table<KW> t, const u64 *__restrict__ node_lo, const u64 *__restric
   typedef typename KeyOf<KW>::type K;
   u32 n = blockIdx.x * blockDim.x + threadIdx.x;
   if (n >= n_nodes) return;
-  K key = (K)node_lo[n];
-  if (KW == 2) key |= (K)((u128)node_hi[n] << 64);
+  K key = (K)__ldcs(node_lo + n);                     // streamed once: leave the L2 to the table
+  if (KW == 2) key |= (K)((u128)__ldcs(node_hi + n) << 64);
   u64 i = slot_of(hash_key(key), t.cap);
   for (u32 probe = 0; probe < t.max_probe; ++probe) {
     typename SlotOf<KW>::type *sp = t.slots + i;

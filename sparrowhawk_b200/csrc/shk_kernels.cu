@@ -289,9 +289,10 @@ k_build_edges(Table<KW> tbl, int k, const u64 *__restrict__ node_lo, const u64 *
   typedef typename KeyOf<KW>::type K;
   u32 n = blockIdx.x * blockDim.x + threadIdx.x;
   if (n >= n_nodes) return;
-  K X = (K)node_lo[n];
-  if (KW == 2) X |= (K)((u128)node_hi[n] << 64);
-  u32 raw = node_raw[n], valid = 0;
+  // the node arrays stream through once; the index (the random-access side) should keep the L2
+  K X = (K)__ldcs(node_lo + n);
+  if (KW == 2) X |= (K)((u128)__ldcs(node_hi + n) << 64);
+  u32 raw = __ldcs(node_raw + n), valid = 0;
   u32 un[2] = {SHK_NONE, SHK_NONE};
   for (int bit = 0; bit < 8; ++bit) {
     if (!((raw >> bit) & 1u)) continue;
@@ -300,8 +301,8 @@ k_build_edges(Table<KW> tbl, int k, const u64 *__restrict__ node_lo, const u64 *
     if (id != SHK_NONE) { valid |= 1u << bit; un[bit >> 2] = (id << 1) | (u32)s_in; }
   }
   node_edges[n] = (uint8_t)valid;
-  uniq[2 * n + 0] = __popc(valid & 15u) == 1 ? un[0] : SHK_NONE;
-  uniq[2 * n + 1] = __popc(valid >> 4) == 1 ? un[1] : SHK_NONE;
+  __stcs(reinterpret_cast<uint2 *>(uniq) + n, make_uint2(__popc(valid & 15u) == 1 ? un[0] : SHK_NONE,
+                                                         __popc(valid >> 4) == 1 ? un[1] : SHK_NONE));
 }
 
 // =====================================================================
