@@ -151,7 +151,8 @@ def reference_arm(args, w, rank, world):
         "impl": "reference", "metric": "input bases/s, k-mer count + DBG build", "value": v, "unit": "bases/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64" if w["k"] <= 31 else "u128",
-        "data": "synthetic", "config": {"workload": f"{args.workload}: {w['desc']}", "min_qual": MIN_QUAL,
+        "data": "synthetic", "config": {"workload": f"{args.workload}: {w['desc']}" + (f" x {world} genomes" if world > 1 and "n_genomes" not in w else ""),
+                                        "min_qual": MIN_QUAL,
                                         "min_count": w["min_count"], "bases_per_step": bases},
         "cpu_baseline": {"value": v, "unit": "bases/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": "bases/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -257,7 +258,9 @@ def replicas_arm(args, w, rank, world, local):
     e2e = None
     if not args.no_e2e:
         ms_e2e = timed(True, max(1, args.steps // 2), 1)
-        e2e = {"value": bases * n_g / (ms_e2e * 1e-3), "unit": "bases/s", "h2d_bytes_per_step": int(2 * nbytes) * n_g,
+        hq = hs[0].stats()["host_qual_bits"]
+        e2e = {"value": bases * n_g / (ms_e2e * 1e-3), "unit": "bases/s",
+               "h2d_bytes_per_step": int(nbytes + (4 * ((nbytes + 31) // 32) if hq else nbytes)) * n_g, "host_quality_bits": bool(hq),
                "d2h_bytes_per_step": int(st["unitig_bases"] + st["n_unitigs"] * 25 + 4400) * n_g, "ms_per_step": ms_e2e,
                "calls": "per genome: shk_asm_preprocess_reads + shk_asm_preprocessing_info + shk_asm_assemble + shk_asm_get_assembly (pointer + length)"}
     peak, peak_src = peaks()
@@ -457,7 +460,11 @@ def main():
         d2h = int(s2["unitig_bases"] + s2["n_unitigs"] * 25 + s2["n_links"] * 8 + 3 * 4200 + 128)
         calls = ("shk_asm_preprocess_reads + shk_asm_preprocessing_info + shk_asm_assemble + shk_asm_get_assembly (pointer + length)" if world == 1 else
                  "per rank: shk_load_reads + sharded_run (shk_shard_* + NCCL) + shk_asm_preprocessing_info; rank 0: shk_asm_assemble + shk_asm_get_assembly")
-        e2e = {"value": bases * world / (ms_e2e * 1e-3), "unit": "bases/s", "h2d_bytes_per_step": int(2 * nbytes) * world,
+        # bytes that cross the link per step: the sequence characters, and the quality characters or — when the
+        # steady-state load took the quality test on the host cores — one bit per position
+        h2d = int(nbytes + (4 * ((nbytes + 31) // 32) if s2["host_qual_bits"] else nbytes))
+        e2e = {"value": bases * world / (ms_e2e * 1e-3), "unit": "bases/s", "h2d_bytes_per_step": h2d * world,
+               "host_quality_bits": bool(s2["host_qual_bits"]), "host_quality_wait_ms": max(0, s2["host_qual_bits"] - 1) / 1e3,
                "d2h_bytes_per_step": d2h * world, "ms_per_step": ms_e2e, "calls": calls,
                "call_ms": {n: round(sum(v[1:]) / max(1, len(v) - 1), 3) for n, v in call_ms.items()},
                "ncontigs": json.loads(bytes(res))["ncontigs"] if res is not None else None, "nkmers": json.loads(info)["nkmers"]}

@@ -69,7 +69,7 @@ pub struct shk_stats {
     pub n_spilled: u64,
     pub n_records: u64,
     pub device_planned: u32,
-    pub reserved: u32,
+    pub host_qual_bits: u32,
 }
 
 /// opaque: contigs + links produced by the host graph cleaning

@@ -9,9 +9,18 @@
 #include <cstring>
 #include <cmath>
 #include <algorithm>
+#include <atomic>
+#include <chrono>
+#include <memory>
+#include <thread>
 #include <vector>
 
+#if defined(__SSE2__)
+#include <emmintrin.h>
+#endif
+
 #include "shk_handle.h"
+#include "../../include/shk_spec.h"
 
 namespace shk {
 
@@ -115,6 +124,48 @@ static shk_status pack_from_device(shk_asm *h, const uint8_t *d_seq, const uint8
 
 static bool fast_ready_for(shk_asm *h, uint64_t n_positions);
 static shk_status fast_prologue(shk_asm *h);
+static double now_ms() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+
+// ---- quality test on the host (steady-state load) ---------------------------------
+// The path needs one bit of every quality byte — (q - 33) >= min_qual (S3).  Taking that bit on the host cores
+// while the bases are on the wire cuts the host->device bytes of a read set from 2 to 1.125 per position; the
+// link is what bounds the end-to-end call.  32 quality bytes -> one u32 (bit j = byte j passes), SWAR on 8 bytes:
+// adding 128 - T to the low seven bits carries into bit 7 exactly when the byte is >= T (bytes >= 128 pass as is).
+static inline uint32_t qual_bits32(const uint8_t *q, uint64_t add) {
+  uint32_t out = 0;
+  for (int j = 0; j < 4; ++j) {
+    uint64_t x; memcpy(&x, q + 8 * j, 8);
+    const uint64_t y = (((x & 0x7F7F7F7F7F7F7F7Full) + add) | x) & 0x8080808080808080ull;
+    out |= (uint32_t)(((y >> 7) * 0x0102040810204080ull) >> 56) << (8 * j);
+  }
+  return out;
+}
+static void qual_bits_range(const uint8_t *qual, uint64_t pos0, uint64_t pos1, uint64_t n, int min_qual, uint32_t *out /* word pos0/32 at out[0] */) {
+  const int T = min_qual + 33;
+  const uint64_t add = (uint64_t)(128 - T) * 0x0101010101010101ull;
+  uint64_t p = pos0;
+#if defined(__SSE2__)
+  // x86-64: compare + movemask, 16 bytes at a time (memory-bound: about 8 GB/s per core)
+  const __m128i t = _mm_set1_epi8((char)(T - 1));
+  for (; p + 32 <= pos1 && p + 32 <= n; p += 32) {
+    const __m128i a = _mm_loadu_si128((const __m128i *)(qual + p)), b = _mm_loadu_si128((const __m128i *)(qual + p + 16));
+    out[(p - pos0) >> 5] = (uint32_t)_mm_movemask_epi8(_mm_or_si128(_mm_cmpgt_epi8(a, t), a)) |
+                           ((uint32_t)_mm_movemask_epi8(_mm_or_si128(_mm_cmpgt_epi8(b, t), b)) << 16);
+  }
+#endif
+  for (; p + 32 <= pos1 && p + 32 <= n; p += 32) out[(p - pos0) >> 5] = qual_bits32(qual + p, add);
+  for (; p < pos1; p += 32) {                                        // ragged end of the stream
+    uint32_t w = 0;
+    for (int j = 0; j < 32 && p + j < n; ++j) w |= (uint32_t)shk_qual_ok(qual[p + j], min_qual) << j;
+    out[(p - pos0) >> 5] = w;
+  }
+}
+static bool qpack_usable(const shk_asm *h) {
+  static const int mode = [] { const char *e = getenv("SHK_QPACK"); return e ? atoi(e) : -1; }();     // 0 = never, 1 = always
+  const int T = h->p.min_qual + 33;
+  if (T < 1 || T > 127 || mode == 0) return false;
+  return mode == 1 || h->qpack_ok;
+}
 // Steady-state form of the load (a calibrated handle, see count_filter_fast): the host->device copy runs in
 // slices on a second stream, and K0 of slice i and K1a of slice i-1 (its halo reaches into slice i) run on the
 // main stream underneath the copy of slice i+1.  Leaves the reads packed AND cut into records.
@@ -151,18 +202,68 @@ static shk_status load_reads_overlapped(shk_asm *h, const uint8_t *seq, const ui
     h->st.gpu_launches += launch_partition(h->kw, b, m, total, h->p.k, h->P, h->rcap, h->skrecs.p, h->bfill.as<uint64_t>(),
                                            d_counters(h), h->stream, wb, we);
   };
+  // quality bits taken on the host by a few threads, slice by slice, in chunks handed out from a counter; the
+  // calling thread queues slice i's copies as soon as that slice's chunks are done
+  const bool qpack = qpack_usable(h);
+  const uint64_t CH = 1ull << 18;                                      // positions per chunk (a multiple of 32)
+  std::vector<std::thread> workers;
+  std::vector<uint64_t> ch_off, ch_end; std::vector<int> ch_slice;
+  std::unique_ptr<std::atomic<int>[]> remaining(new std::atomic<int>[S]);
+  std::atomic<size_t> next_chunk{0};
+  uint32_t *hq = nullptr, *dq = nullptr;
+  if (qpack) {
+    SHK_TRY(h->qbits_pin.ensure_host((total + 8) * 4)); SHK_TRY(h->qbits_dev.ensure((total + 8) * 4));
+    hq = (uint32_t *)h->qbits_pin.p; dq = h->qbits_dev.as<uint32_t>();
+    for (int i = 0; i < S; ++i) {
+      const uint64_t off = (uint64_t)i * slice, end = std::min<uint64_t>(n, off + slice);
+      int c = 0;
+      for (uint64_t p = off; p < end; p += CH) { ch_off.push_back(p); ch_end.push_back(std::min(end, p + CH)); ch_slice.push_back(i); ++c; }
+      remaining[i].store(c, std::memory_order_relaxed);
+    }
+    const unsigned hw = std::thread::hardware_concurrency();
+    unsigned T = std::min<unsigned>(std::max(1u, hw > 4 ? hw - 2 : hw), 12u);
+    if (const char *e = getenv("SHK_QPACK_THREADS")) T = (unsigned)std::max(1, atoi(e));
+    const int mq = h->p.min_qual;
+    for (unsigned t = 0; t < T; ++t)
+      workers.emplace_back([&, mq] {
+        for (;;) {
+          const size_t c = next_chunk.fetch_add(1, std::memory_order_relaxed);
+          if (c >= ch_off.size()) return;
+          qual_bits_range(qual, ch_off[c], ch_end[c], n, mq, hq + ch_off[c] / 32);
+          remaining[ch_slice[c]].fetch_sub(1, std::memory_order_release);
+        }
+      });
+  }
+  struct Joiner { std::vector<std::thread> &w; ~Joiner() { for (auto &t : w) if (t.joinable()) t.join(); } } joiner{workers};
+  double pack_wait_ms = 0;
   for (int i = 0; i < S; ++i) {
     const uint64_t off = (uint64_t)i * slice;
     if (off >= n) break;
     const uint64_t len = std::min<uint64_t>(slice, n - off);
     SHK_CUDA(cudaMemcpyAsync(dseq + off, seq + off, len, cudaMemcpyHostToDevice, h->copy_stream));
-    SHK_CUDA(cudaMemcpyAsync(dqual + off, qual + off, len, cudaMemcpyHostToDevice, h->copy_stream));
+    if (qpack) {
+      const double tw = now_ms();
+      while (remaining[i].load(std::memory_order_acquire) > 0) std::this_thread::yield();
+      pack_wait_ms += now_ms() - tw;
+      SHK_CUDA(cudaMemcpyAsync(dq + off / 32, hq + off / 32, (len + 31) / 32 * 4, cudaMemcpyHostToDevice, h->copy_stream));
+    } else {
+      SHK_CUDA(cudaMemcpyAsync(dqual + off, qual + off, len, cudaMemcpyHostToDevice, h->copy_stream));
+    }
     SHK_CUDA(cudaEventRecord(h->copy_ev[i], h->copy_stream));
     SHK_CUDA(cudaStreamWaitEvent(h->stream, h->copy_ev[i], 0));
-    h->st.gpu_launches += launch_pack_reads(dseq + off, dqual + off, len, (len + 31) / 32, h->p.min_qual, b + off / 32, m + off / 32,
-                                            d_counters(h) + 3, h->stream);
+    h->st.gpu_launches += launch_pack_reads(dseq + off, qpack ? nullptr : dqual + off, len, (len + 31) / 32, h->p.min_qual, b + off / 32, m + off / 32,
+                                            d_counters(h) + 3, h->stream, qpack ? dq + off / 32 : nullptr);
     if (i == 0) SHK_CUDA(cudaEventRecord(h->ev[1], h->stream));
     if (i > 0) k1a(i - 1);
+  }
+  if (qpack) {
+    for (auto &t : workers) t.join();
+    workers.clear();
+    // the host cores must keep ahead of the link (about 55 GB/s of quality bytes saved): if the calling thread spent
+    // more time waiting for bits than sending the raw bytes would have cost, go back to sending them
+    const double raw_ms = (double)n / 50e6;
+    if (pack_wait_ms > raw_ms && !getenv("SHK_QPACK")) { h->qpack_ok = false; }
+    h->st.host_qual_bits = 1u + (uint32_t)(pack_wait_ms * 1000.0);
   }
   for (int i = 0; i < S; ++i) if ((uint64_t)(i + 1) * slice >= n) { k1a(i); break; }
   SHK_CUDA(cudaGetLastError());
@@ -176,6 +277,7 @@ static shk_status load_reads_host(shk_asm *h, const uint8_t *seq, const uint8_t 
   SHK_TRY(require_device(h));
   if (!seq && n) { set_error("seq is null"); return SHK_ERR_BAD_ARG; }
   h->partition_done = false;
+  h->st.host_qual_bits = 0;
   if (!append && qual && n >= h->overlap_min && fast_ready_for(h, n)) return load_reads_overlapped(h, seq, qual, n);
   SHK_CUDA(cudaEventRecord(h->ev[0], h->stream));
   SHK_TRY(h->ascii_seq.ensure(n + 64));
@@ -755,7 +857,7 @@ void shk_asm_free(shk_asm *h) {
                       &h->useq, &h->link_from, &h->link_to, &h->gscal, &h->splitters, &h->sum_of, &h->rank_work, &h->skrecs, &h->bfill, &h->groups, &h->ovf, &h->uq_rec, &h->uq_cnt, &h->seg_off, &h->seg_cnt, &h->pack_off};
     for (auto b : bufs) b->release();
     if (h->h_pinned) cudaFreeHost(h->h_pinned);
-    h->hfill.release(); h->pin_stage.release(); h->hoff.release(); h->hseg.release(); h->hfill2.release(); h->hsend.release();
+    h->hfill.release(); h->pin_stage.release(); h->hoff.release(); h->hseg.release(); h->hfill2.release(); h->hsend.release(); h->qbits_pin.release();
     for (auto &e : h->ev) if (e) cudaEventDestroy(e);
     if (h->own_stream) cudaStreamDestroy(h->own_stream);
     if (h->copy_stream) { cudaStreamDestroy(h->copy_stream); for (auto &e : h->copy_ev) if (e) cudaEventDestroy(e); }

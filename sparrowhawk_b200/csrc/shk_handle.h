@@ -87,6 +87,8 @@ struct shk_asm {
   // ---- K1a output: super-k-mer records in P fine-bucket regions of rcap records ----
   shk::DevBuf skrecs, bfill /* u32 fill[P] | u32 kcount[P] */, groups, ovf;
   shk::PinBuf hoff /* shard_partition: dense send offsets */, hseg /* shard_count: segment offsets + counts */;
+  shk::PinBuf qbits_pin /* overlapped load: quality bits taken on the host */;
+  bool qpack_ok = true;                        // host cores keep ahead of the link (checked on every overlapped load)
   shk::PinBuf hfill2 /* shard_count_device falling back: the received fills on the host */;
   shk::PinBuf hsend /* shard_partition: records per owner rank + largest fill, from the device-side send plan */;
   uint64_t send_base[64] = {0};                // first record of each owner rank in the send buffer
@@ -112,7 +114,7 @@ struct shk_asm {
   uint32_t shard_world = 0, shard_rank = 0;      // 0 = not in a sharded run
   bool shard_src = false;                        // K1b reads the received records instead of the local regions
   const void *recv_recs = nullptr;               // caller-owned device buffer (records received from all ranks)
-  shk::DevBuf seg_off, seg_cnt, pack_off, send_tot, shard_btot /* per owned bucket: records | k-mers << 32 over all sources */;
+  shk::DevBuf seg_off, seg_cnt, pack_off, send_tot, qbits_dev, shard_btot /* per owned bucket: records | k-mers << 32 over all sources */;
   uint64_t shard_node_offset = 0, shard_nodes_local = 0;
   // sharded steady-state count (shk_shard_count_device): calibrated by a host-planned run over this many owned buckets / ranks
   uint32_t shard_cal_nb = 0, shard_cal_world = 0;

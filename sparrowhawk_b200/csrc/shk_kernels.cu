@@ -21,7 +21,8 @@ namespace shk {
 __global__ void __launch_bounds__(256)
 k_pack_reads(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual, u64 n,
              u64 nwords, int min_qual, u64 *__restrict__ bases, u32 *__restrict__ mask,
-             u64 *__restrict__ counters /* [0]=n_bases */) {
+             u64 *__restrict__ counters /* [0]=n_bases */,
+             const u32 *__restrict__ qbits /* nullable: the quality test already taken on the host, 1 bit per position */) {
   u64 w = (u64)blockIdx.x * blockDim.x + threadIdx.x;
   u64 nb = 0;
   if (w < nwords) {
@@ -44,11 +45,12 @@ k_pack_reads(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual, 
     }
     const uint8_t *sb = reinterpret_cast<const uint8_t *>(s);
     const uint8_t *qb = reinterpret_cast<const uint8_t *>(q);
+    const u32 qm = qbits ? __ldg(qbits + w) : 0xFFFFFFFFu;
     u64 bw = 0; u32 mw = 0;
 #pragma unroll
     for (int j = 0; j < 32; ++j) {
       uint8_t c = sb[j];
-      bool ok = shk_valid_base(c) && (!qual || shk_qual_ok(qb[j], min_qual));
+      bool ok = shk_valid_base(c) && ((qm >> j) & 1u) && (!qual || shk_qual_ok(qb[j], min_qual));
       bw = (bw << 2) | (u64)shk_encode_base(c);
       mw |= (ok ? 1u : 0u) << j;
       nb += (c != '\n') ? 1 : 0;   // unit of the metric: every sequence character
@@ -507,10 +509,10 @@ static inline unsigned grid_persistent(uint64_t work_items, unsigned threads, un
 }
 
 int launch_pack_reads(const uint8_t *seq, const uint8_t *qual, uint64_t n, uint64_t nwords, int min_qual,
-                      uint64_t *bases, uint32_t *mask, uint64_t *counters, cudaStream_t st) {
+                      uint64_t *bases, uint32_t *mask, uint64_t *counters, cudaStream_t st, const uint32_t *qbits) {
   if (!nwords) return 0;
   k_pack_reads<<<blocks_for(nwords, 256), 256, 0, st>>>(seq, qual, n, nwords, min_qual, (u64 *)bases, mask,
-                                                        (u64 *)counters);
+                                                        (u64 *)counters, qbits);
   return 1;
 }
 

@@ -25,8 +25,9 @@ struct GraphBuffers {
 size_t slot_bytes(int kw);
 int sm_count();
 
+// qbits (nullable, device): the quality test taken on the host, bit j of word w = position 32 w + j passes; qual is null then
 int launch_pack_reads(const uint8_t *seq, const uint8_t *qual, uint64_t n, uint64_t nwords, int min_qual,
-                      uint64_t *bases, uint32_t *mask, uint64_t *counters, cudaStream_t st);
+                      uint64_t *bases, uint32_t *mask, uint64_t *counters, cudaStream_t st, const uint32_t *qbits = nullptr);
 int launch_table_fill(void *slots, uint64_t cap, int kw, cudaStream_t st);
 int launch_extract_count(int kw, const uint64_t *bases, const uint32_t *mask, uint64_t nwords, int k,
                          void *slots, uint64_t cap, uint64_t *counters, uint32_t *overflow, cudaStream_t st);

@@ -243,6 +243,33 @@ def test_overlapped_load(k, monkeypatch):
     h.close()
 
 
+@pytest.mark.parametrize("min_qual", [2, 20, 37])
+def test_overlapped_load_quality_bits_from_host(min_qual, monkeypatch):
+    """The steady-state load takes the quality test on the host cores (one bit per position crosses the link
+    instead of the quality byte): qualities on both sides of the threshold, bytes >= 128 (pass, S3),
+    a stream length that is not a multiple of 32."""
+    monkeypatch.setenv("SHK_OVERLAP_MIN", "1")
+    seq, qual = synth.reads(61, 90_000, 30.0, 0.01)
+    rng = np.random.default_rng(5)
+    qual = qual.copy()
+    body = qual != ord("\n")
+    low = body & (rng.random(qual.size) < 0.03)              # 3 % of the positions get a quality around the threshold
+    qual[low] = rng.integers(33, 33 + 45, size=int(low.sum()), dtype=np.uint8)
+    qual[body & (rng.random(qual.size) < 0.001)] = 200
+    cut = seq.size - 1 - int(np.argmax(seq[::-1][1:] == ord("\n")))      # drop the last read: ragged stream end
+    seq, qual = seq[:cut].copy(), qual[:cut].copy()
+    assert seq.size % 32 != 0 and seq[-1] == ord("\n")
+    h = AssemblyHelper.new(31, False, 2, min_qual, 0, False, False, False, False)
+    o = run_oracle(seq, qual, 31, 2, min_qual)
+    for it in range(3):
+        h.preprocess_reads(seq, qual)
+        st = h.stats()
+        assert st["device_planned"] == (1 if it else 0) and bool(st["host_qual_bits"]) == bool(it)
+        h.assemble()
+        assert_parity(h, o, check_table=False)
+    h.close()
+
+
 @pytest.mark.parametrize("k", [31, 63])
 def test_steady_state_path(k):
     """Second and later runs on a handle plan the K1b groups on the device (no host round trip between
