@@ -956,10 +956,11 @@ namespace shk {
 shk_status fetch_unitigs(shk_asm *h) {
   if (h->hu.valid) return SHK_OK;
   SHK_TRY(require_device(h));
+  const double t_fetch0 = now_ms();
   if (!h->graphed) { set_error("unitigs need build_graph"); return SHK_ERR_STATE; }
   HostUnitigs &u = h->hu;
   size_t nu = h->st.n_unitigs, k = (size_t)h->p.k;
-  u.seq.assign(h->st.unitig_bases, 0); u.off.assign(nu + 1, 0); u.cov.assign(nu, 0.f); u.circ.assign(nu, 0);
+  u.seq.resize(h->st.unitig_bases) /* every byte is written below */; u.off.assign(nu + 1, 0); u.cov.assign(nu, 0.f); u.circ.assign(nu, 0);
   u.link_from.assign(h->st.n_links, 0); u.link_to.assign(h->st.n_links, 0); u.kc.assign(nu, 0);
   if (nu) {
     struct Rec { uint32_t head, len; uint64_t off; };
@@ -987,6 +988,7 @@ shk_status fetch_unitigs(shk_asm *h) {
     u.off[nu] = p;
   }
   u.valid = true;
+  if (getenv("SHK_DEBUG")) fprintf(stderr, "[shk] unitigs to the host: %.2f ms (%llu bases)\n", now_ms() - t_fetch0, (unsigned long long)h->st.unitig_bases);
   return SHK_OK;
 }
 }  // namespace shk

@@ -267,6 +267,24 @@ void clean_unitig_graph(int k, const char *seq, const uint64_t *off, const uint6
   Work w; w.k = k;
   w.seq.resize(n); w.kc.assign(kc, kc + n); w.circ.assign(n, 0); w.alive.assign(n, 1);
   w.adj.assign(2 * n, {}); w.canon_cache.assign(n, std::string()); w.canon_have.assign(n, 0);
+  // Long sequences take over the buffers of the result `out` held before (a handle that assembles read set after
+  // read set): a multi-megabyte std::string is an mmap + page faults + munmap per call otherwise.
+  {
+    const size_t BIG = 1u << 16;
+    std::vector<std::string> pool;
+    for (auto &t : out.seq) if (t.capacity() >= BIG) pool.push_back(std::move(t));
+    if (!pool.empty()) {
+      std::sort(pool.begin(), pool.end(), [](const std::string &a, const std::string &b) { return a.capacity() > b.capacity(); });
+      std::vector<uint32_t> big;
+      for (size_t i = 0; i < n; ++i) if (off[i + 1] - off[i] >= BIG) big.push_back((uint32_t)i);
+      std::sort(big.begin(), big.end(), [&](uint32_t a, uint32_t b) { return off[a + 1] - off[a] > off[b + 1] - off[b]; });
+      size_t pi = 0;
+      for (uint32_t i : big) {
+        if (pi >= pool.size() || pool[pi].capacity() < off[i + 1] - off[i]) break;     // largest remaining buffer is too small
+        w.seq[i] = std::move(pool[pi++]);
+      }
+    }
+  }
   for (size_t i = 0; i < n; ++i) { w.seq[i].assign(seq + off[i], seq + off[i + 1]); w.circ[i] = circ ? circ[i] : 0; }
   for (size_t i = 0; i < nl; ++i) {
     const uint32_t x = lf[i], y = lt[i] ^ 1u;
