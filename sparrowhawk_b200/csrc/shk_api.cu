@@ -169,7 +169,9 @@ static bool qpack_usable(const shk_asm *h) {
 // Steady-state form of the load (a calibrated handle, see count_filter_fast): the host->device copy runs in
 // slices on a second stream, and K0 of slice i and K1a of slice i-1 (its halo reaches into slice i) run on the
 // main stream underneath the copy of slice i+1.  Leaves the reads packed AND cut into records.
-static shk_status load_reads_overlapped(shk_asm *h, const uint8_t *seq, const uint8_t *qual, size_t n) {
+// cut == false (a handle that is not calibrated yet, or the sharded path, whose K1a uses the global bucket count): the
+// same sliced copy with the quality bits from the host and K0 per slice, without K1a.
+static shk_status load_reads_overlapped(shk_asm *h, const uint8_t *seq, const uint8_t *qual, size_t n, bool cut) {
   const int S = 8;
   const uint64_t tile_pos = (uint64_t)partition_tile_words() * 32;
   const uint64_t slice = ((n + S - 1) / S + tile_pos - 1) / tile_pos * tile_pos;       // positions per slice, whole K1a tiles
@@ -189,7 +191,7 @@ static shk_status load_reads_overlapped(shk_asm *h, const uint8_t *seq, const ui
   SHK_CUDA(cudaMemsetAsync(b + total, 0, 4 * 8, h->stream));
   SHK_CUDA(cudaMemsetAsync(m + total, 0, 4 * 4, h->stream));
   h->nwords = total; h->n_positions = n;
-  SHK_TRY(fast_prologue(h));
+  if (cut) SHK_TRY(fast_prologue(h));
   // the copy stream starts after everything queued so far (the ASCII buffers may still feed an earlier K0)
   SHK_CUDA(cudaEventRecord(h->copy_ev[S], h->stream));
   SHK_CUDA(cudaStreamWaitEvent(h->copy_stream, h->copy_ev[S], 0));
@@ -197,7 +199,7 @@ static shk_status load_reads_overlapped(shk_asm *h, const uint8_t *seq, const ui
   bool first_k1a = true;
   auto k1a = [&](int i) {
     const uint64_t wb = (uint64_t)i * slice / 32, we = std::min<uint64_t>(total, (uint64_t)(i + 1) * slice / 32);
-    if (wb >= we) return;
+    if (wb >= we || !cut) return;
     if (first_k1a) { cudaEventRecord(h->ev[8], h->stream); first_k1a = false; }
     h->st.gpu_launches += launch_partition(h->kw, b, m, total, h->p.k, h->P, h->rcap, h->skrecs.p, h->bfill.as<uint64_t>(),
                                            d_counters(h), h->stream, wb, we);
@@ -267,9 +269,9 @@ static shk_status load_reads_overlapped(shk_asm *h, const uint8_t *seq, const ui
   }
   for (int i = 0; i < S; ++i) if ((uint64_t)(i + 1) * slice >= n) { k1a(i); break; }
   SHK_CUDA(cudaGetLastError());
-  SHK_CUDA(cudaEventRecord(h->ev[9], h->stream));
+  if (cut) SHK_CUDA(cudaEventRecord(h->ev[9], h->stream));
   h->counted = h->filtered = h->graphed = false;
-  h->partition_done = true;
+  h->partition_done = cut;
   return SHK_OK;
 }
 
@@ -278,7 +280,10 @@ static shk_status load_reads_host(shk_asm *h, const uint8_t *seq, const uint8_t 
   if (!seq && n) { set_error("seq is null"); return SHK_ERR_BAD_ARG; }
   h->partition_done = false;
   h->st.host_qual_bits = 0;
-  if (!append && qual && n >= h->overlap_min && fast_ready_for(h, n)) return load_reads_overlapped(h, seq, qual, n);
+  if (!append && qual && n >= h->overlap_min) {
+    const bool cut = fast_ready_for(h, n);
+    if (cut || qpack_usable(h)) return load_reads_overlapped(h, seq, qual, n, cut);
+  }
   SHK_CUDA(cudaEventRecord(h->ev[0], h->stream));
   SHK_TRY(h->ascii_seq.ensure(n + 64));
   if (qual) SHK_TRY(h->ascii_qual.ensure(n + 64));

@@ -264,7 +264,7 @@ def test_overlapped_load_quality_bits_from_host(min_qual, monkeypatch):
     for it in range(3):
         h.preprocess_reads(seq, qual)
         st = h.stats()
-        assert st["device_planned"] == (1 if it else 0) and bool(st["host_qual_bits"]) == bool(it)
+        assert st["device_planned"] == (1 if it else 0) and st["host_qual_bits"] > 0
         h.assemble()
         assert_parity(h, o, check_table=False)
     h.close()
