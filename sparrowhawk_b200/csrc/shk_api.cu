@@ -161,7 +161,8 @@ static void qual_bits_range(const uint8_t *qual, uint64_t pos0, uint64_t pos1, u
   }
 }
 static bool qpack_usable(const shk_asm *h) {
-  static const int mode = [] { const char *e = getenv("SHK_QPACK"); return e ? atoi(e) : -1; }();     // 0 = never, 1 = always
+  const char *e = getenv("SHK_QPACK");                     // 0 = never, 1 = always (read per call: tests flip it)
+  const int mode = e ? atoi(e) : -1;
   const int T = h->p.min_qual + 33;
   if (T < 1 || T > 127 || mode == 0) return false;
   return mode == 1 || h->qpack_ok;
@@ -264,7 +265,7 @@ static shk_status load_reads_overlapped(shk_asm *h, const uint8_t *seq, const ui
     // the host cores must keep ahead of the link (about 55 GB/s of quality bytes saved): if the calling thread spent
     // more time waiting for bits than sending the raw bytes would have cost, go back to sending them
     const double raw_ms = (double)n / 50e6;
-    if (pack_wait_ms > raw_ms && !getenv("SHK_QPACK")) { h->qpack_ok = false; }
+    if (raw_ms > 1.0 && pack_wait_ms > raw_ms && !getenv("SHK_QPACK")) h->qpack_ok = false;      // (small loads say nothing)
     h->st.host_qual_bits = 1u + (uint32_t)(pack_wait_ms * 1000.0);
   }
   for (int i = 0; i < S; ++i) if ((uint64_t)(i + 1) * slice >= n) { k1a(i); break; }

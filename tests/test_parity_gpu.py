@@ -243,12 +243,13 @@ def test_overlapped_load(k, monkeypatch):
     h.close()
 
 
-@pytest.mark.parametrize("min_qual", [2, 20, 37])
-def test_overlapped_load_quality_bits_from_host(min_qual, monkeypatch):
+@pytest.mark.parametrize("min_qual,qpack", [(2, 1), (20, 1), (37, 1), (20, 0)])
+def test_overlapped_load_quality_bits_from_host(min_qual, qpack, monkeypatch):
     """The steady-state load takes the quality test on the host cores (one bit per position crosses the link
     instead of the quality byte): qualities on both sides of the threshold, bytes >= 128 (pass, S3),
     a stream length that is not a multiple of 32."""
     monkeypatch.setenv("SHK_OVERLAP_MIN", "1")
+    monkeypatch.setenv("SHK_QPACK", str(qpack))              # forced on / off (the library's own choice is timing-based)
     seq, qual = synth.reads(61, 90_000, 30.0, 0.01)
     rng = np.random.default_rng(5)
     qual = qual.copy()
@@ -264,7 +265,7 @@ def test_overlapped_load_quality_bits_from_host(min_qual, monkeypatch):
     for it in range(3):
         h.preprocess_reads(seq, qual)
         st = h.stats()
-        assert st["device_planned"] == (1 if it else 0) and st["host_qual_bits"] > 0
+        assert st["device_planned"] == (1 if it else 0) and (st["host_qual_bits"] > 0) == bool(qpack)
         h.assemble()
         assert_parity(h, o, check_table=False)
     h.close()
