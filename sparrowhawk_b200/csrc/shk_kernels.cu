@@ -296,11 +296,38 @@ k_build_edges(Table<KW> tbl, int k, const u64 *__restrict__ node_lo, const u64 *
   if (KW == 2) X |= (K)((u128)__ldcs(node_hi + n) << 64);
   u32 raw = __ldcs(node_raw + n), valid = 0;
   u32 un[2] = {SHK_NONE, SHK_NONE};
-  for (int bit = 0; bit < 8; ++bit) {
-    if (!((raw >> bit) & 1u)) continue;
-    int s_in; K Y = neighbour_key(X, k, bit >> 2, (u32)(bit & 3), s_in);
-    u32 id = table_find<KW>(tbl, Y);
+  // The lookups of a node are independent random accesses into the index: take the set bits two at a time so that
+  // both first probes are in flight together (a typical unitig-interior node has exactly two, one per side).
+  auto resolve = [&](int bit, K Y, int s_in, u64 i, bool nonempty, K cur, u32 cnt) {
+    u32 id = SHK_NONE;
+    if (nonempty) {
+      if (cur == Y) id = cnt;
+      else {                                                          // collision: walk on from the next slot
+        for (u32 probe = 1; probe < tbl.max_probe; ++probe) {
+          if (++i == tbl.cap) i = 0;
+          K c2; u32 n2, e2;
+          if (!slot_load<KW>(tbl.slots + i, c2, n2, e2)) break;
+          if (c2 == Y) { id = n2; break; }
+        }
+      }
+    }
     if (id != SHK_NONE) { valid |= 1u << bit; un[bit >> 2] = (id << 1) | (u32)s_in; }
+  };
+  u32 rem = raw;
+  while (rem) {
+    const int b0 = __ffs(rem) - 1; rem &= rem - 1;
+    const int b1 = rem ? __ffs(rem) - 1 : -1; if (b1 >= 0) rem &= rem - 1;
+    int s0, s1 = 0;
+    const K Y0 = neighbour_key(X, k, b0 >> 2, (u32)(b0 & 3), s0);
+    const u64 i0 = slot_of(hash_key(Y0), tbl.cap);
+    K Y1 = 0; u64 i1 = 0;
+    if (b1 >= 0) { Y1 = neighbour_key(X, k, b1 >> 2, (u32)(b1 & 3), s1); i1 = slot_of(hash_key(Y1), tbl.cap); }
+    K c0, c1 = 0; u32 n0, n1 = 0, e0, e1;
+    const bool f0 = slot_load<KW>(tbl.slots + i0, c0, n0, e0);
+    bool f1 = false;
+    if (b1 >= 0) f1 = slot_load<KW>(tbl.slots + i1, c1, n1, e1);
+    resolve(b0, Y0, s0, i0, f0, c0, n0);
+    if (b1 >= 0) resolve(b1, Y1, s1, i1, f1, c1, n1);
   }
   node_edges[n] = (uint8_t)valid;
   __stcs(reinterpret_cast<uint2 *>(uniq) + n, make_uint2(__popc(valid & 15u) == 1 ? un[0] : SHK_NONE,
