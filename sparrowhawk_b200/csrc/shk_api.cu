@@ -225,6 +225,10 @@ static shk_status load_reads_overlapped(shk_asm *h, const uint8_t *seq, const ui
     }
     const unsigned hw = std::thread::hardware_concurrency();
     unsigned T = std::min<unsigned>(std::max(1u, hw > 4 ? hw - 2 : hw), 12u);
+    if (const char *e = getenv("LOCAL_WORLD_SIZE")) {                 // several ranks share this host's cores (torchrun)
+      const int lws = atoi(e);
+      if (lws > 1) T = std::max(2u, std::min(T, (hw > 4 ? hw - 2 : hw) / (unsigned)lws));
+    }
     if (const char *e = getenv("SHK_QPACK_THREADS")) T = (unsigned)std::max(1, atoi(e));
     const int mq = h->p.min_qual;
     for (unsigned t = 0; t < T; ++t)
@@ -262,10 +266,11 @@ static shk_status load_reads_overlapped(shk_asm *h, const uint8_t *seq, const ui
   if (qpack) {
     for (auto &t : workers) t.join();
     workers.clear();
-    // the host cores must keep ahead of the link (about 55 GB/s of quality bytes saved): if the calling thread spent
-    // more time waiting for bits than sending the raw bytes would have cost, go back to sending them
+    // the host cores must keep ahead of the link: the load takes max(link time of 1.125 n bytes, time to take the bits)
+    // against the link time of 2 n bytes — once waiting for bits costs clearly more than the n quality bytes would
+    // have cost on the wire, go back to sending them
     const double raw_ms = (double)n / 50e6;
-    if (raw_ms > 1.0 && pack_wait_ms > raw_ms && !getenv("SHK_QPACK")) h->qpack_ok = false;      // (small loads say nothing)
+    if (raw_ms > 1.0 && pack_wait_ms > 1.6 * raw_ms && !getenv("SHK_QPACK")) h->qpack_ok = false;   // (small loads say nothing)
     h->st.host_qual_bits = 1u + (uint32_t)(pack_wait_ms * 1000.0);
   }
   for (int i = 0; i < S; ++i) if ((uint64_t)(i + 1) * slice >= n) { k1a(i); break; }
