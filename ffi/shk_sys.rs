@@ -118,6 +118,8 @@ extern "C" {
                               mean_cov: *mut f32, circular: *mut u8, unitig_cap: usize) -> shk_status;
     pub fn shk_export_links(h: *mut shk_asm, from: *mut u32, to: *mut u32, cap: usize, n: *mut usize) -> shk_status;
     pub fn shk_export_unitig_counts(h: *mut shk_asm, kmer_count_sum: *mut u64, unitig_cap: usize) -> shk_status;
+    /// host-side quality test of the steady-state load (needs no device)
+    pub fn shk_qual_bits(qual: *const u8, n: usize, min_qual: c_int, out: *mut u32) -> shk_status;
 
     // host graph cleaning (dead-end removal, simple bubble collapse, re-compaction) on plain arrays
     pub fn shk_clean_graph(k: c_int, seq: *const c_char, offsets: *const u64, kmer_count_sum: *const u64,

@@ -282,6 +282,11 @@ shk_status shk_shard_count(shk_asm *h, const void *d_recv, const uint64_t *recv_
 shk_status shk_shard_count_device(shk_asm *h, const void *d_recv, const uint64_t *d_recv_fill,
                                   const uint64_t *recv_records, uint64_t n_instances,
                                   int histogram_only, int min_count);
+/* Host-side quality test (S3), as the steady-state load takes it before the copy: bit j of
+ * out[w] = ((int)qual[32 w + j] - 33 >= min_qual), positions past n read as 0.  out holds
+ * ceil(n / 32) words.  Needs no device.  -32 <= min_qual <= 94. */
+shk_status shk_qual_bits(const uint8_t *qual, size_t n, int min_qual, uint32_t *out);
+
 /* D2D copy of this rank's surviving nodes (shk_stats.n_nodes of them) into
  * caller-owned device arrays: u64 lo, u64 hi, u16 count, u8 raw edge bits. */
 shk_status shk_shard_local_nodes(shk_asm *h, void *d_lo, void *d_hi, void *d_count,

@@ -86,6 +86,7 @@ SYMBOLS = {
     "shk_shard_partition": (C.c_int, [_H, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p]),
     "shk_shard_pack": (C.c_int, [_H, C.c_void_p, C.c_void_p]),
     "shk_shard_count": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
+    "shk_qual_bits": (C.c_int, [C.c_void_p, C.c_size_t, C.c_int, C.c_void_p]),
     "shk_shard_count_device": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_int]),
     "shk_shard_local_nodes": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]),
     "shk_shard_set_nodes": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t,

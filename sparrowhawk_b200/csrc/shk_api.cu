@@ -1392,6 +1392,15 @@ shk_status shk_shard_set_nodes(shk_asm *h, const void *d_lo, const void *d_hi, c
   return SHK_OK;
 }
 
+// the host-side quality test of the steady-state load, on its own (needs no device)
+shk_status shk_qual_bits(const uint8_t *qual, size_t n, int min_qual, uint32_t *out) {
+  if ((!qual || !out) && n) { set_error("null argument"); return SHK_ERR_BAD_ARG; }
+  const int T = min_qual + 33;
+  if (T < 1 || T > 127) { set_error("min_qual out of the range the packed test covers (%d)", min_qual); return SHK_ERR_BAD_ARG; }
+  qual_bits_range(qual, 0, (n + 31) / 32 * 32, n, min_qual, out);
+  return SHK_OK;
+}
+
 int shk_fit_min_count(const uint64_t *histo, int fallback) { return histo ? shk::fit_min_count(histo, fallback) : fallback; }
 
 }  // extern "C"

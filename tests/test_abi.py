@@ -77,3 +77,25 @@ def test_product_does_not_touch_oracle():
                 txt = open(os.path.join(dirpath, f), errors="replace").read()
                 for pat in (r"import\s+oracle", r"from\s+oracle", r"oracle/", r"liboracle", r"\borc_[a-z]"):
                     assert not re.search(pat, txt), f"{f} references the oracle ({pat})"
+
+
+def test_host_quality_bits_match_the_spec():
+    """shk_qual_bits (the quality test the steady-state load takes on the host cores, SSE2 / SWAR) against
+    the one-line rule of S3 on random bytes: every threshold, bytes >= 128, ragged lengths."""
+    import ctypes as C
+    import numpy as np
+    from sparrowhawk_b200 import _ffi
+    lib = _ffi.lib()
+    rng = np.random.default_rng(3)
+    for n in (0, 1, 31, 32, 33, 64, 1000, 4099, 65536 + 7):
+        q = rng.integers(0, 256, size=n, dtype=np.uint8)
+        for mq in (-32, 0, 2, 20, 41, 60, 93, 94):
+            out = np.full((n + 31) // 32 + 1, 0xDEADBEEF, np.uint32)
+            assert lib.shk_qual_bits(q.ctypes.data if n else None, n, mq, out.ctypes.data) == 0
+            ok = (q.astype(np.int32) - 33 >= mq)
+            want = np.zeros(((n + 31) // 32) * 32, bool); want[:n] = ok
+            got = ((out[:-1, None] >> np.arange(32, dtype=np.uint32)) & 1).astype(bool).ravel()
+            assert np.array_equal(got, want), (n, mq)
+            assert out[-1] == 0xDEADBEEF
+    q = np.zeros(32, np.uint8); out = np.zeros(1, np.uint32)
+    assert lib.shk_qual_bits(q.ctypes.data, 32, 95, out.ctypes.data) != 0      # threshold beyond a 7-bit byte
