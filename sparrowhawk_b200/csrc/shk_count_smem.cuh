@@ -9,22 +9,33 @@
 
 namespace shk {
 
-#ifndef SHK_CB_THREADS
-#define SHK_CB_THREADS 1024           // 512 = two half-size CTAs per SM: measured no faster on B200 (r01), kept as a build knob
+// CTA shape per key width.  k <= 31: two 512-thread CTAs per SM, each with half the shared memory (the barriers of
+// one hide under the other's work: 2.28 -> 2.21 ms on config B once the groups were cut inside the kernel).
+// k <= 63: one 1024-thread CTA with the whole table (halving the 9216-slot table costs more groups and spills
+// than the overlap wins back: 9.1 -> 11.4 ms on config C).  Build knobs for measurements.
+#ifndef SHK_CB_THREADS1
+#define SHK_CB_THREADS1 512
 #endif
-#define SHK_CB_PER_SM (1024 / SHK_CB_THREADS)
-#define SHK_CB_WARPS (SHK_CB_THREADS / 32)
+#ifndef SHK_CB_THREADS2
+#define SHK_CB_THREADS2 1024
+#endif
 #define SHK_CB_MAXC 256           // record segments per group (planner splits larger groups)
 #define SHK_CB_MAXPROBE 96
 
 template <int KW> struct CbCfg;
-template <> struct CbCfg<1> { static const int NS = 16384 / SHK_CB_PER_SM; static const int KEYB = 8;  static const int RECW = 1; };
-template <> struct CbCfg<2> { static const int NS = 9216 / SHK_CB_PER_SM - (SHK_CB_PER_SM > 1 ? 64 : 0); static const int KEYB = 16; static const int RECW = 2; };
+template <> struct CbCfg<1> {
+  static const int THREADS = SHK_CB_THREADS1, PER_SM = 1024 / THREADS, WARPS = THREADS / 32;
+  static const int NS = 16384 / PER_SM; static const int KEYB = 8;  static const int RECW = 1;
+};
+template <> struct CbCfg<2> {
+  static const int THREADS = SHK_CB_THREADS2, PER_SM = 1024 / THREADS, WARPS = THREADS / 32;
+  static const int NS = 9216 / PER_SM - (PER_SM > 1 ? 64 : 0); static const int KEYB = 16; static const int RECW = 2;
+};
 
 template <int KW> __host__ __device__ constexpr size_t cb_smem_bytes() {
   return (size_t)CbCfg<KW>::NS * (CbCfg<KW>::KEYB + 4)            // keys + vals
-         + (size_t)SHK_CB_WARPS * 32 * 16 * CbCfg<KW>::RECW        // record staging
-         + (size_t)SHK_CB_WARPS * 64 * 4                           // run-start bitmaps
+         + (size_t)CbCfg<KW>::WARPS * 32 * 16 * CbCfg<KW>::RECW    // record staging
+         + (size_t)CbCfg<KW>::WARPS * 64 * 4                       // run-start bitmaps
          + SHK_NBINS * 4 + (SHK_CB_MAXC + 1) * 4 + 64
          + 64 * 4;                                                  // record-length bins + cursors
 }
@@ -132,7 +143,7 @@ __device__ __forceinline__ void kmer_at(const u32 *rw, int i, int k, u128 &fwd, 
 // instances vanish this way (31 % at 30x still 63 %); the result is identical
 // because a record's content fully determines its (canonical k-mer, edge) pairs and
 // those are strand-symmetric.
-#define SHK_RT_SLOTS (8192 / SHK_CB_PER_SM)            // record-table slots (16 B key + 4 B count, time-shares the k-mer table's memory)
+#define SHK_RT_SLOTS (8192 / (1024 / SHK_CB_THREADS1))            // record-table slots (16 B key + 4 B count, time-shares the k-mer table's memory)
 #define SHK_RT_MAXPROBE 32
 
 __device__ __forceinline__ uint4 canon_record(uint4 r, int k) {
@@ -209,7 +220,7 @@ struct CountOut {
 };
 
 template <int KW, bool DEDUP>
-__global__ void __launch_bounds__(SHK_CB_THREADS, SHK_CB_PER_SM)
+__global__ void __launch_bounds__(CbCfg<KW>::THREADS, CbCfg<KW>::PER_SM)
 k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__restrict__ bstat, u32 rcap,
                 const u64 *__restrict__ seg_off, const u32 *__restrict__ seg_cnt,
                 uint4 *__restrict__ uq_rec, u32 *__restrict__ uq_cnt, u32 uq_cap /* distinct-record list, per CTA */,
@@ -218,13 +229,13 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
                 u32 *__restrict__ uq_flag /* set when a de-dup list is too small */, CountOut out) {
   typedef typename KeyOf<KW>::type K;
   typedef typename std::conditional<KW == 1, u64, U128Pair>::type SK;
-  constexpr int NS = CbCfg<KW>::NS, RECW = CbCfg<KW>::RECW;
+  constexpr int NS = CbCfg<KW>::NS, RECW = CbCfg<KW>::RECW, THREADS = CbCfg<KW>::THREADS, WARPS = CbCfg<KW>::WARPS;
   extern __shared__ __align__(16) unsigned char smraw[];
   SK *keys = reinterpret_cast<SK *>(smraw);
   u32 *vals = reinterpret_cast<u32 *>(smraw + (size_t)NS * CbCfg<KW>::KEYB);
   uint4 *stage = reinterpret_cast<uint4 *>(smraw + (size_t)NS * (CbCfg<KW>::KEYB + 4));
-  u32 *bitmaps = reinterpret_cast<u32 *>(stage + (size_t)SHK_CB_WARPS * 32 * RECW);
-  u32 *hist = bitmaps + SHK_CB_WARPS * 64;
+  u32 *bitmaps = reinterpret_cast<u32 *>(stage + (size_t)WARPS * 32 * RECW);
+  u32 *hist = bitmaps + WARPS * 64;
   u32 *gpre = hist + SHK_NBINS;                         // [MAXC+1] prefix of record counts in the group
   u32 *misc = gpre + SHK_CB_MAXC + 1;                   // [0] current group [1] grab cursor [2] direct records [3] survivors
                                                         // [4] node base [5] claimed record slots [6] distinct records
@@ -233,14 +244,14 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   uint4 *wst = stage + (size_t)warp * 32 * RECW;
   u32 *wbm = bitmaps + warp * 64;
-  for (int i = tid; i < SHK_NBINS; i += SHK_CB_THREADS) hist[i] = 0;
+  for (int i = tid; i < SHK_NBINS; i += THREADS) hist[i] = 0;
   if (tid < 64) rbins[tid] = 0;
   // the table starts empty; every later phase hands it back empty (the sweep and the record
   // compaction clear the slots they visit), so no group pays for a separate clearing pass
-  for (int i = tid; i < NS * (KW == 1 ? 1 : 2); i += SHK_CB_THREADS) reinterpret_cast<u64 *>(keys)[i] = SHK_EMPTY64;
-  for (int i = tid; i < NS; i += SHK_CB_THREADS) vals[i] = 0;
+  for (int i = tid; i < NS * (KW == 1 ? 1 : 2); i += THREADS) reinterpret_cast<u64 *>(keys)[i] = SHK_EMPTY64;
+  for (int i = tid; i < NS; i += THREADS) vals[i] = 0;
   unsigned short *surv = reinterpret_cast<unsigned short *>(stage);                     // survivor slots of the sweep (staging is idle then)
-  constexpr u32 SURV_CAP = (u32)SHK_CB_WARPS * 32 * 16 * RECW / 2;
+  constexpr u32 SURV_CAP = (u32)WARPS * 32 * 16 * RECW / 2;
   u64 nspill = 0, ndec = 0;
   u32 ndist = 0, nb0 = 0, nb1 = 0;                                  // per-thread: distinct k-mers, spectrum bins 0 and 1
 
@@ -358,8 +369,8 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
       };
       // two records per thread and round: both loads are in flight together and the two canonicalisations
       // (long dependent chains) interleave
-      for (u32 f = tid; f < total; f += 2 * SHK_CB_THREADS) {
-        const u32 f2 = f + SHK_CB_THREADS;
+      for (u32 f = tid; f < total; f += 2 * THREADS) {
+        const u32 f2 = f + THREADS;
         const bool two = f2 < total;
         const uint4 r1 = __ldcs(rec_ptr(f));
         const uint4 r2 = two ? __ldcs(rec_ptr(f2)) : r1;
@@ -386,7 +397,7 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
       }
       __syncthreads();
       const u32 nl = misc[5];
-      for (u32 i = tid; i < nl; i += SHK_CB_THREADS) {
+      for (u32 i = tid; i < nl; i += THREADS) {
         const u32 sl = rlist[i];
         const uint4 c4 = *reinterpret_cast<const uint4 *>(rkeys + sl);
         const u32 rn = c4.x & 31u, full = rn / SHK_CB_SEG, rem = rn % SHK_CB_SEG, mult = rcnt[sl];
@@ -518,7 +529,7 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
     // Bins 0 and 1 (sequencing errors: most distinct k-mers) and the distinct count live in registers;
     // survivors are collected as slot numbers in shared memory so the group pays ONE global atomic
     // and writes its nodes densely.
-    for (int s = tid; s < NS; s += SHK_CB_THREADS) {
+    for (int s = tid; s < NS; s += THREADS) {
       bool occ;
       if (KW == 1) occ = reinterpret_cast<u64 *>(keys)[s] != SHK_EMPTY64;
       else occ = reinterpret_cast<U128Pair *>(keys)[s].hi != SHK_EMPTY64;
@@ -551,7 +562,7 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
       if (tid == 0) misc[4] = atomicAdd(out.n_nodes, nsurv);
       __syncthreads();
       const u32 nbase = misc[4];
-      for (u32 i = tid; i < nsurv; i += SHK_CB_THREADS) {
+      for (u32 i = tid; i < nsurv; i += THREADS) {
         const u32 s = surv[i], id = nbase + i;
         const u32 v = vals[s];
         u32 c = v & 0xFFFFFFu;
@@ -574,7 +585,7 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
   for (int o = 16; o; o >>= 1) { nb0 += __shfl_xor_sync(0xffffffffu, nb0, o); nb1 += __shfl_xor_sync(0xffffffffu, nb1, o); }
   if (lane == 0) { if (nb0) atomicAdd(&hist[0], nb0); if (nb1) atomicAdd(&hist[1], nb1); }
   __syncthreads();
-  for (int i = tid; i < SHK_NBINS; i += SHK_CB_THREADS) if (hist[i]) atomicAdd(&out.histo[i], (u64)hist[i]);
+  for (int i = tid; i < SHK_NBINS; i += THREADS) if (hist[i]) atomicAdd(&out.histo[i], (u64)hist[i]);
   if (self_plan && warp == 0) {
     for (int o = 16; o; o >>= 1) { sp_mxfill = max(sp_mxfill, __shfl_xor_sync(0xffffffffu, sp_mxfill, o)); sp_nrec += __shfl_xor_sync(0xffffffffu, sp_nrec, o); }
     if (lane == 0) { atomicMax(sp.stats, sp_mxfill); atomicMax(sp.stats + 1, sp_need); if (sp_nrec) atomicAdd(sp.nrec, sp_nrec); }

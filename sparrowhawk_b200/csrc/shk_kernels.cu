@@ -720,7 +720,7 @@ int records_max_run(int kw, int k) { return rec_max_run(kw, k); }
 int count_table_slots(int kw) { return kw == 1 ? CbCfg<1>::NS : CbCfg<2>::NS; }
 int count_max_group() { return SHK_CB_MAXC; }
 #define SHK_MAX_WORLD 64          // ranks of the sharded path whose segment tables are built on the device
-int count_ctas() { return sm_count() * SHK_CB_PER_SM; }
+int count_ctas(int kw) { return sm_count() * (kw == 2 ? CbCfg<2>::PER_SM : CbCfg<1>::PER_SM); }
 
 int launch_partition(int kw, const uint64_t *bases, const uint32_t *mask, uint64_t nwords, int k, uint32_t P,
                      uint32_t rcap, void *recs, uint64_t *bstat, uint64_t *counters, cudaStream_t st,
@@ -749,7 +749,7 @@ int launch_count_buckets(int kw, const void *recs, const uint64_t *bstat, uint32
     u32 rq = (u32)(self_plan->ratio * 65536.0 + 0.5);
     u64 bq = (u64)(self_plan->budget * 65536.0);
     u32 chunk = 16;                                       // ~8 chunks per CTA, a power of two in [16, SHK_CB_MAXC]
-    while (chunk < SHK_CB_MAXC && (u64)chunk * 2 * 8 * (u64)count_ctas() <= self_plan->n_buckets) chunk *= 2;
+    while (chunk < SHK_CB_MAXC && (u64)chunk * 2 * 8 * (u64)count_ctas(kw) <= self_plan->n_buckets) chunk *= 2;
     const u32 spb = self_plan->seg_per_bucket ? self_plan->seg_per_bucket : 1u;
     if (spb > SHK_CB_MAXC) return 0;
     sp = SelfPlan{self_plan->n_buckets, chunk, rq < 1 ? 1u : rq, bq < 1 ? 1ull : bq, self_plan->stats, (u64 *)self_plan->nrec, spb};
@@ -761,19 +761,19 @@ int launch_count_buckets(int kw, const void *recs, const uint64_t *bstat, uint32
     cudaFuncSetAttribute(k_count_buckets<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cb_smem_bytes<2>());
     attr_set = true;
   }
-  unsigned grid = (unsigned)sm_count() * SHK_CB_PER_SM;
+  unsigned grid = (unsigned)count_ctas(kw);
   if (group_start && grid > g_end - g_begin) grid = g_end - g_begin;
   u32 mp = (u32)(ovf_cap < 4096 ? ovf_cap : 4096);
   CountOut out{(u64 *)histo, (u64 *)node_lo, (u64 *)node_hi, node_count, node_raw, node_cap, n_nodes, (u64 *)counters};
   // record-level de-duplication needs the per-CTA list of distinct records (k <= 31 only for now)
   if (kw == 1 && uq_rec && uq_cap)
-    k_count_buckets<1, true><<<grid, SHK_CB_THREADS, cb_smem_bytes<1>(), st>>>((const uint4 *)recs, (const u64 *)bstat, rcap, (const u64 *)seg_off, seg_cnt,
+    k_count_buckets<1, true><<<grid, CbCfg<1>::THREADS, cb_smem_bytes<1>(), st>>>((const uint4 *)recs, (const u64 *)bstat, rcap, (const u64 *)seg_off, seg_cnt,
         (uint4 *)uq_rec, uq_cnt, uq_cap, group_start, g_begin, g_end, sp, next_group, k, min_count, Table<1>{(Slot1 *)ovf_slots, ovf_cap, mp}, ovf_flag, uq_flag, out);
   else if (kw == 1)
-    k_count_buckets<1, false><<<grid, SHK_CB_THREADS, cb_smem_bytes<1>(), st>>>((const uint4 *)recs, (const u64 *)bstat, rcap, (const u64 *)seg_off, seg_cnt,
+    k_count_buckets<1, false><<<grid, CbCfg<1>::THREADS, cb_smem_bytes<1>(), st>>>((const uint4 *)recs, (const u64 *)bstat, rcap, (const u64 *)seg_off, seg_cnt,
         nullptr, nullptr, 0, group_start, g_begin, g_end, sp, next_group, k, min_count, Table<1>{(Slot1 *)ovf_slots, ovf_cap, mp}, ovf_flag, uq_flag, out);
   else
-    k_count_buckets<2, false><<<grid, SHK_CB_THREADS, cb_smem_bytes<2>(), st>>>((const Rec32 *)recs, (const u64 *)bstat, rcap, (const u64 *)seg_off, seg_cnt,
+    k_count_buckets<2, false><<<grid, CbCfg<2>::THREADS, cb_smem_bytes<2>(), st>>>((const Rec32 *)recs, (const u64 *)bstat, rcap, (const u64 *)seg_off, seg_cnt,
         nullptr, nullptr, 0, group_start, g_begin, g_end, sp, next_group, k, min_count, Table<2>{(Slot2 *)ovf_slots, ovf_cap, mp}, ovf_flag, uq_flag, out);
   return 1;
 }

@@ -56,7 +56,7 @@ size_t record_bytes(int kw);
 int records_max_run(int kw, int k);
 int count_table_slots(int kw);
 int count_max_group();
-int count_ctas();          // CTAs of one K1b launch (sizes the per-CTA de-dup lists)
+int count_ctas(int kw = 1);   // CTAs of one K1b launch (k <= 31: also sizes the per-CTA de-dup lists)
 int launch_partition(int kw, const uint64_t *bases, const uint32_t *mask, uint64_t nwords, int k, uint32_t P,
                      uint32_t rcap, void *recs, uint64_t *bstat /* [P]: records | k-mers << 32 */, uint64_t *counters, cudaStream_t st,
                      uint64_t word_begin = 0, uint64_t word_end = ~0ull /* a slice of the stream: begin must be a multiple of
