@@ -47,7 +47,7 @@ L = 150
 MIN_QUAL = 20
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch, from the committed `ncu --set full`
 # capture of the same workload (profiles/r01_ncu_k1_summary.md); None where no capture exists.
-NCU_TRAFFIC = {("B", "k_count_buckets"): 624.4e6 + 15.1e6, ("B", "k_minimizer_partition"): 222.6e6 + 594.0e6}
+NCU_TRAFFIC = {("B", "k_count_buckets"): 624.9e6 + 15.3e6, ("B", "k_minimizer_partition"): 263.8e6 + 635.1e6}
 
 
 def alg_bytes_per_base(k):
