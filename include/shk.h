@@ -154,7 +154,13 @@ shk_status shk_set_stream(shk_asm *h, void *stream);
 void *shk_get_stream(shk_asm *h);
 
 /* HOST seq/qual streams (same meaning as shk_asm_preprocess_reads) → H2D →
- * K0 pack_reads.  Replaces (append=0) or extends (append=1) the resident reads. */
+ * K0 pack_reads.  Replaces (append=0) or extends (append=1) the resident reads.
+ * Buffer lifetime: the copies are queued, not waited for — when seq/qual are PINNED
+ * host memory they must stay valid and unmodified until the handle's stream has
+ * been synchronised (any of shk_count / shk_filter / shk_run / shk_export_* /
+ * shk_asm_* does, or cudaStreamSynchronize(shk_get_stream(h))); pageable memory
+ * is staged by the CUDA runtime before the call returns.  shk_asm_preprocess_reads
+ * returns only after everything it queued has completed. */
 shk_status shk_load_reads(shk_asm *h, const uint8_t *seq, const uint8_t *qual,
                           size_t n, int append);
 /* Same, but seq/qual are DEVICE pointers (already in HBM). */

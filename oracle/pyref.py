@@ -78,6 +78,25 @@ def histogram(counts):
     return h
 
 
+def fit_min_count(histo, fallback):
+    """Spectrum fit used when do_fit is set (docs/src/assembly.md:16, AssemblyPage.vue:318) -> used_min_count.
+    The reference's fit lives in the absent crate; [DECISION]: the valley rule.
+    histo[i] = distinct k-mers seen i + 1 times; the last of the 500 bins is a clamp and takes no part.
+    Smooth the other 499 with the 3-tap kernel (1, 2, 1) / 4 (ends repeated); the valley is the first bin
+    i >= 1 with s[i] <= s[i-1] and s[i] < s[i+1] that is followed by a coverage peak (a later smoothed bin
+    that is > 1.5 x s[i] and >= 8).  k-mers survive iff count > used_min_count (S10), so the first kept
+    count is the valley's own count i + 1 and used_min_count = i.  No valley: the requested min_count stands."""
+    h = list(histo)[:-1]
+    n = len(h)
+    s = [(h[max(0, i - 1)] + 2 * h[i] + h[min(n - 1, i + 1)]) / 4.0 for i in range(n)]
+    for i in range(1, n - 1):
+        if s[i] <= s[i - 1] and s[i] < s[i + 1]:
+            peak = max(s[i + 1:])
+            if peak > 1.5 * s[i] and peak >= 8:
+                return i
+    return fallback
+
+
 def filter_nodes(counts, min_count):
     return {s: min(c, 65535) for s, c in counts.items() if min(c, 65535) > min_count}
 

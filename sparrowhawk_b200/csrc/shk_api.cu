@@ -99,8 +99,7 @@ static shk_status pack_from_device(shk_asm *h, const uint8_t *d_seq, const uint8
       SHK_CUDA(cudaMemcpyAsync(nm.p, h->mask.p, (base_word + 1) * 4, cudaMemcpyDeviceToDevice, h->stream));
       SHK_CUDA(cudaStreamSynchronize(h->stream));
     }
-    h->bases.release(); h->mask.release();
-    h->bases = nb; h->mask = nm;
+    h->bases = std::move(nb); h->mask = std::move(nm);
   }
   uint64_t *b = h->bases.as<uint64_t>() + 1;
   uint32_t *m = h->mask.as<uint32_t>() + 1;
@@ -862,13 +861,9 @@ void shk_asm_free(shk_asm *h) {
   if (h->dev >= 0) {
     cudaSetDevice(h->dev);
     if (h->stream) cudaStreamSynchronize(h->stream);
-    DevBuf *bufs[] = {&h->bases, &h->mask, &h->ascii_seq, &h->ascii_qual, &h->slots, &h->dscal, &h->node_lo, &h->node_hi,
-                      &h->node_count, &h->node_raw, &h->node_edges, &h->uniq, &h->succ, &h->tail_of, &h->len_of,
-                      &h->unitig_of_head, &h->elem_unitig, &h->pd, &h->cq, &h->circ, &h->recs, &h->ucirc, &h->cov_sum,
-                      &h->useq, &h->link_from, &h->link_to, &h->gscal, &h->splitters, &h->sum_of, &h->rank_work, &h->skrecs, &h->bfill, &h->groups, &h->ovf, &h->uq_rec, &h->uq_cnt, &h->seg_off, &h->seg_cnt, &h->pack_off};
-    for (auto b : bufs) b->release();
+    if (h->copy_stream) cudaStreamSynchronize(h->copy_stream);
     if (h->h_pinned) cudaFreeHost(h->h_pinned);
-    h->hfill.release(); h->pin_stage.release(); h->hoff.release(); h->hseg.release(); h->hfill2.release(); h->hsend.release(); h->qbits_pin.release();
+    // every DevBuf / PinBuf member frees itself when the handle is deleted below
     for (auto &e : h->ev) if (e) cudaEventDestroy(e);
     if (h->own_stream) cudaStreamDestroy(h->own_stream);
     if (h->copy_stream) { cudaStreamDestroy(h->copy_stream); for (auto &e : h->copy_ev) if (e) cudaEventDestroy(e); }

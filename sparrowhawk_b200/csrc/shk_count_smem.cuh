@@ -55,12 +55,24 @@ __device__ __forceinline__ u32 slot_hash(u128 key) {
   h ^= h >> 15; h *= 0x2C1B3C6Du; h ^= h >> 13; h *= 0x297A2D39u; h ^= h >> 16;
   return h;
 }
-// count (low 24 bits, S7: saturation far above 65535) and edge byte (top 8 bits) of a claimed slot:
-// one ATOMS.ADD that also returns the edge bits already present, an ATOMS.OR only when new bits arrive
+// count (low 24 bits; S7 saturates at 65535, so anything >= 65536 only has to stay >= 65536) and edge byte (top 8
+// bits) of a claimed slot: one ATOMS.ADD that also returns the edge bits already present, an ATOMS.OR only when new
+// bits arrive.  A slot that has reached 65536 takes no more adds (the add is undone), so the 24-bit field can never
+// carry into the edge byte: adds on this path are <= 255, and at most 1024 of them are in flight per CTA.  A larger
+// multiplicity (one super-k-mer record seen more than 255 times) goes through a saturating CAS loop instead.
 __device__ __forceinline__ void slot_hit(u32 *val, u32 e, u32 add) {
+  if (add > 0xFFu) {
+    u32 old = *reinterpret_cast<volatile u32 *>(val);
+    for (;;) {
+      const u32 c = min((old & 0xFFFFFFu) + min(add, 0x10000u), 0x1FFFFu);
+      const u32 seen = atomicCAS(val, old, ((old & 0xFF000000u) | (e << 24)) | c);
+      if (seen == old) return;
+      old = seen;
+    }
+  }
   const u32 old = atomicAdd(val, add);
   if (((old >> 24) & e) != e) atomicOr(val, e << 24);
-  if ((old & 0xFFFFFFu) >= 0x800000u) atomicSub(val, add);
+  if ((old & 0xFFFFFFu) >= 0x10000u) atomicSub(val, add);
 }
 // returns false when the key found no room inside the probe window (caller spills)
 __device__ __forceinline__ bool smem_insert(u64 *keys, u32 *vals, int NS, u64 key, u32 e, u32 add) {

@@ -22,19 +22,29 @@ shk_status cuda_fail(cudaError_t e, const char *what);
     if (e__ != cudaSuccess) return shk::cuda_fail(e__, #call);  \
   } while (0)
 
-// grow-only device buffer
+// grow-only device buffer; move-only, frees itself (a handle releases everything it owns by being deleted)
 struct DevBuf {
   void *p = nullptr;
   size_t cap = 0;
+  DevBuf() = default;
+  DevBuf(const DevBuf &) = delete;
+  DevBuf &operator=(const DevBuf &) = delete;
+  DevBuf(DevBuf &&o) noexcept : p(o.p), cap(o.cap) { o.p = nullptr; o.cap = 0; }
+  DevBuf &operator=(DevBuf &&o) noexcept { if (this != &o) { release(); p = o.p; cap = o.cap; o.p = nullptr; o.cap = 0; } return *this; }
+  ~DevBuf() { release(); }
   shk_status ensure(size_t bytes);
   void release();
   template <class T> T *as() const { return (T *)p; }
 };
 
-// grow-only pinned host buffer
+// grow-only pinned host buffer; move-only, frees itself
 struct PinBuf {
   void *p = nullptr;
   size_t cap = 0;
+  PinBuf() = default;
+  PinBuf(const PinBuf &) = delete;
+  PinBuf &operator=(const PinBuf &) = delete;
+  ~PinBuf() { release(); }
   shk_status ensure_host(size_t bytes);
   void release();
 };

@@ -123,19 +123,21 @@ shk_status parse_fastq_files(shk_asm *h, const char *p1, const char *p2) {
 // Falls back to the requested min_count when the spectrum has no valley.
 // ---------------------------------------------------------------------------
 int fit_min_count(const uint64_t *histo, int fallback) {
-  int n = SHK_HISTO_BINS;
-  // light smoothing (3-tap) to ignore single-bin noise
+  // bin i holds count i+1; the last bin is the clamp (everything seen >= 500 times) and takes no part,
+  // neither as a peak nor through the smoothing
+  const int n = SHK_HISTO_BINS - 1;
+  // light smoothing (3-tap, ends repeated) to ignore single-bin noise
   std::vector<double> s(n);
   for (int i = 0; i < n; ++i) {
     double a = histo[std::max(0, i - 1)], b = histo[i], c = histo[std::min(n - 1, i + 1)];
     s[i] = (a + 2 * b + c) / 4.0;
   }
   int valley = -1;
-  for (int i = 1; i + 1 < n - 1; ++i) {          // bin i holds count i+1; last bin is the clamp
+  for (int i = 1; i + 1 < n; ++i) {
     if (s[i] <= s[i - 1] && s[i] < s[i + 1]) {
       // must be followed by a real peak (coverage), not noise
       double peak = 0;
-      for (int j = i + 1; j < n - 1; ++j) peak = std::max(peak, s[j]);
+      for (int j = i + 1; j < n; ++j) peak = std::max(peak, s[j]);
       if (peak > 1.5 * s[i] && peak >= 8) { valley = i; break; }
     }
   }

@@ -64,108 +64,6 @@ k_pack_reads(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual, 
 }
 
 // =====================================================================
-// K1 extract_count.  A warp takes 32 consecutive stream words (1024 positions);
-// lane i owns word i and gets its neighbours by warp shuffle (the halo words
-// come from the two edge lanes).  Every lane materialises the forward k-mer at
-// each of its 32 offsets by a funnel shift of (w, w+1[, w+2]) and the reverse
-// complement by the mirrored funnel shift of the revcomp'ed words, takes the
-// minimum (canonical, S6), builds the read-evidenced edge code (S13 / D.3) and
-// inserts into the open-addressing table: 128-bit slot load, CAS claim on the
-// key, RED.ADD on the count, RED.OR on the edge byte only when it adds bits.
-// =====================================================================
-template <int KW>
-__global__ void __launch_bounds__(256)
-k_extract_count(const u64 *__restrict__ bases, const u32 *__restrict__ mask, u64 nwords, int k,
-                Table<KW> tbl, u64 *__restrict__ counters /* [1]=n_instances [2]=n_distinct */,
-                u32 *__restrict__ overflow) {
-  typedef typename KeyOf<KW>::type K;
-  const int lane = threadIdx.x & 31;
-  const u64 warp0 = ((u64)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const u64 nwarps = ((u64)gridDim.x * blockDim.x) >> 5;
-  const u64 nchunks = (nwords + 31) >> 5;
-  const K km = kmask_of(k, (K)0);
-  u64 ninst = 0; u32 nclaim = 0;
-  for (u64 c = warp0; c < nchunks; c += nwarps) {
-    const u64 w = c * 32 + lane;
-    // arrays carry one zero word before index 0 and >= 4 after nwords-1
-    u64 b0 = w < nwords ? __ldg(bases + w) : 0;
-    u32 m0 = w < nwords ? __ldg(mask + w) : 0;
-    u64 b1 = __shfl_down_sync(0xffffffffu, b0, 1);
-    u32 m1 = __shfl_down_sync(0xffffffffu, m0, 1);
-    u64 bp = __shfl_up_sync(0xffffffffu, b0, 1);
-    u32 mp = __shfl_up_sync(0xffffffffu, m0, 1);
-    u64 b2 = 0; u32 m2 = 0;
-    if (KW == 2) {
-      b2 = __shfl_down_sync(0xffffffffu, b0, 2);
-      m2 = __shfl_down_sync(0xffffffffu, m0, 2);
-    }
-    if (lane == 31) {
-      b1 = w + 1 < nwords ? __ldg(bases + w + 1) : 0; m1 = w + 1 < nwords ? __ldg(mask + w + 1) : 0;
-    }
-    if (KW == 2 && lane >= 30) {
-      b2 = w + 2 < nwords ? __ldg(bases + w + 2) : 0; m2 = w + 2 < nwords ? __ldg(mask + w + 2) : 0;
-    }
-    if (lane == 0) {
-      bp = c ? __ldg(bases + w - 1) : 0; mp = c ? __ldg(mask + w - 1) : 0;
-    }
-    if (m0 == 0) continue;  // no window can start in this word
-    const u64 r0 = revcomp_word(b0), r1 = revcomp_word(b1);
-    const u64 r2 = KW == 2 ? revcomp_word(b2) : 0;
-    const u64 mm = (u64)m0 | ((u64)m1 << 32);
-#pragma unroll 4
-    for (int o = 0; o < 32; ++o) {
-      // validity of window [o, o+k): k mask bits all set
-      bool ok;
-      if (KW == 1) {
-        const u64 vm = (1ull << k) - 1;
-        ok = ((mm >> o) & vm) == vm;
-      } else {
-        u128 m128 = (u128)mm | ((u128)m2 << 64);
-        const u128 vm = (((u128)1) << k) - 1;
-        ok = ((m128 >> o) & vm) == vm;
-      }
-      if (!ok) continue;
-      ++ninst;
-      K fwd, rc; u32 bnext;
-      if (KW == 1) {
-        u64 H = o ? ((b0 << (2 * o)) | (b1 >> (64 - 2 * o))) : b0;      // stream << 2o, top word
-        u64 t = H >> (62 - 2 * k);
-        bnext = (u32)t & 3u; fwd = (K)(t >> 2);
-        u64 L = o ? ((r0 >> (2 * o)) | (r1 << (64 - 2 * o))) : r0;      // (r1:r0) >> 2o, low word
-        rc = (K)(L & (u64)km);
-      } else {
-        u128 S01 = ((u128)b0 << 64) | b1;
-        u128 H = o ? ((S01 << (2 * o)) | (u128)(b2 >> (64 - 2 * o))) : S01;
-        u128 t = H >> (126 - 2 * k);
-        bnext = (u32)t & 3u; fwd = (K)(t >> 2);
-        u128 R10 = ((u128)r1 << 64) | r0;
-        u128 L = o ? ((R10 >> (2 * o)) | ((u128)r2 << (128 - 2 * o))) : R10;
-        rc = (K)(L & (u128)km);
-      }
-      // neighbours in the read: previous / next window valid too?
-      const bool has_l = o ? ((m0 >> (o - 1)) & 1u) : ((mp >> 31) & 1u);
-      bool has_r;
-      if (KW == 1) has_r = (mm >> (o + k)) & 1ull;
-      else has_r = (o + k < 64) ? ((mm >> (o + k)) & 1ull) : ((m2 >> (o + k - 64)) & 1u);
-      const u32 a = o ? (u32)(b0 >> (64 - 2 * o)) & 3u : (u32)bp & 3u;
-      u32 e; K key;
-      if (fwd < rc) {
-        key = fwd;
-        e = (has_r ? (1u << bnext) : 0u) | (has_l ? (16u << a) : 0u);
-      } else {
-        key = rc;
-        e = (has_l ? (1u << (a ^ 2u)) : 0u) | (has_r ? (16u << (bnext ^ 2u)) : 0u);
-      }
-      nclaim += table_insert(tbl, key, e, 1u, overflow) ? 1u : 0u;
-    }
-  }
-  for (int o = 16; o; o >>= 1) ninst += __shfl_xor_sync(0xffffffffu, ninst, o);
-  if (lane == 0 && ninst) atomicAdd(&counters[1], ninst);
-  for (int o = 16; o; o >>= 1) nclaim += __shfl_xor_sync(0xffffffffu, nclaim, o);
-  if (lane == 0 && nclaim) atomicAdd(&counters[2], (u64)nclaim);
-}
-
-// =====================================================================
 // K2 histogram_filter: one sweep over the table.  500-bin spectrum in shared
 // memory (S9), survivors of count > min_count (S10) compacted into dense node
 // arrays with warp-aggregated cursor bumps; the slot's count word is replaced
@@ -224,39 +122,6 @@ k_histogram_filter(Table<KW> tbl, int min_count, u64 *__restrict__ histo /*[500]
           tbl.slots[i].count = id;
         }
       }
-    }
-  }
-  __syncthreads();
-  for (int i = threadIdx.x; i < SHK_NBINS; i += blockDim.x)
-    if (sh[i]) atomicAdd(&histo[i], (u64)sh[i]);
-}
-
-// Table growth (chunked mode only): re-insert every live slot of `old` into `neu`.
-template <int KW>
-__global__ void __launch_bounds__(256)
-k_rehash(Table<KW> old, Table<KW> neu, u32 *__restrict__ overflow) {
-  typedef typename KeyOf<KW>::type K;
-  const u64 stride = (u64)gridDim.x * blockDim.x;
-  for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < old.cap; i += stride) {
-    K key; u32 cnt, e;
-    if (slot_load<KW>(old.slots + i, key, cnt, e)) table_insert(neu, key, e, cnt, overflow);
-  }
-}
-
-// Count-only variant of the sweep (sizes the node arrays before compaction).
-template <int KW>
-__global__ void __launch_bounds__(256)
-k_histogram_only(Table<KW> tbl, u64 *__restrict__ histo) {
-  typedef typename KeyOf<KW>::type K;
-  __shared__ u32 sh[SHK_NBINS];
-  for (int i = threadIdx.x; i < SHK_NBINS; i += blockDim.x) sh[i] = 0;
-  __syncthreads();
-  const u64 stride = (u64)gridDim.x * blockDim.x;
-  for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < tbl.cap; i += stride) {
-    K key; u32 cnt, e;
-    if (slot_load<KW>(tbl.slots + i, key, cnt, e)) {
-      u32 c = cnt > SHK_COUNT_MAX ? SHK_COUNT_MAX : cnt;
-      atomicAdd(&sh[shk_histo_bin(c)], 1u);
     }
   }
   __syncthreads();
@@ -515,14 +380,22 @@ k_unitig_links_out(Table<KW> tbl, int k, const UnitigRec *__restrict__ recs, u32
 // =====================================================================
 // launch wrappers
 // =====================================================================
-static int g_sms = 0;
+// per device: a process may hold handles on several GPUs (shk_params.device)
+#define SHK_MAX_DEVICES 64
+static int g_sms[SHK_MAX_DEVICES] = {0};
+static int current_device_slot() {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) { cudaGetLastError(); dev = 0; }
+  return dev >= 0 && dev < SHK_MAX_DEVICES ? dev : 0;
+}
 int sm_count() {
-  if (!g_sms) {
-    int dev = 0; cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&g_sms, cudaDevAttrMultiProcessorCount, dev);
-    if (g_sms <= 0) g_sms = 148;
+  const int dev = current_device_slot();
+  if (!g_sms[dev]) {
+    int n = 0;
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    g_sms[dev] = n > 0 ? n : 148;
   }
-  return g_sms;
+  return g_sms[dev];
 }
 size_t slot_bytes(int kw) { return kw == 1 ? sizeof(Slot1) : sizeof(Slot2); }
 size_t unitig_rec_bytes() { return sizeof(UnitigRec); }
@@ -560,39 +433,6 @@ int launch_table_fill(void *slots, uint64_t cap, int kw, cudaStream_t st) {
   unsigned g = grid_persistent(cap * (kw == 2 ? 2 : 1), 256, 8);
   if (kw == 1) k_table_clear1<<<g, 256, 0, st>>>((Slot1 *)slots, cap);
   else k_table_clear2<<<g, 256, 0, st>>>((Slot2 *)slots, cap);
-  return 1;
-}
-
-int launch_extract_count(int kw, const uint64_t *bases, const uint32_t *mask, uint64_t nwords, int k,
-                         void *slots, uint64_t cap, uint64_t *counters, uint32_t *overflow, cudaStream_t st) {
-  if (!nwords) return 0;
-  unsigned g = grid_persistent(nwords, 256, 8);
-  u32 max_probe = (u32)(cap < 4096 ? cap : 4096);
-  if (kw == 1) {
-    Table<1> t{(Slot1 *)slots, cap, max_probe};
-    k_extract_count<1><<<g, 256, 0, st>>>((const u64 *)bases, mask, nwords, k, t, (u64 *)counters, overflow);
-  } else {
-    Table<2> t{(Slot2 *)slots, cap, max_probe};
-    k_extract_count<2><<<g, 256, 0, st>>>((const u64 *)bases, mask, nwords, k, t, (u64 *)counters, overflow);
-  }
-  return 1;
-}
-
-int launch_rehash(int kw, void *old_slots, uint64_t old_cap, void *new_slots, uint64_t new_cap, uint32_t *overflow,
-                  cudaStream_t st) {
-  unsigned g = grid_persistent(old_cap, 256, 8);
-  u32 mp = (u32)(new_cap < 4096 ? new_cap : 4096);
-  if (kw == 1)
-    k_rehash<1><<<g, 256, 0, st>>>(Table<1>{(Slot1 *)old_slots, old_cap, 0}, Table<1>{(Slot1 *)new_slots, new_cap, mp}, overflow);
-  else
-    k_rehash<2><<<g, 256, 0, st>>>(Table<2>{(Slot2 *)old_slots, old_cap, 0}, Table<2>{(Slot2 *)new_slots, new_cap, mp}, overflow);
-  return 1;
-}
-
-int launch_histogram_only(int kw, void *slots, uint64_t cap, uint64_t *histo, cudaStream_t st) {
-  unsigned g = grid_persistent(cap, 256, 8);
-  if (kw == 1) k_histogram_only<1><<<g, 256, 0, st>>>(Table<1>{(Slot1 *)slots, cap, 0}, (u64 *)histo);
-  else k_histogram_only<2><<<g, 256, 0, st>>>(Table<2>{(Slot2 *)slots, cap, 0}, (u64 *)histo);
   return 1;
 }
 
@@ -754,7 +594,8 @@ int launch_count_buckets(int kw, const void *recs, const uint64_t *bstat, uint32
     if (spb > SHK_CB_MAXC) return 0;
     sp = SelfPlan{self_plan->n_buckets, chunk, rq < 1 ? 1u : rq, bq < 1 ? 1ull : bq, self_plan->stats, (u64 *)self_plan->nrec, spb};
   }
-  static bool attr_set = false;
+  static bool attr_done[SHK_MAX_DEVICES] = {false};     // function attributes belong to the device's context
+  bool &attr_set = attr_done[current_device_slot()];
   if (!attr_set) {
     cudaFuncSetAttribute(k_count_buckets<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cb_smem_bytes<1>());
     cudaFuncSetAttribute(k_count_buckets<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cb_smem_bytes<1>());

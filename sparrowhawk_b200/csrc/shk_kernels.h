@@ -29,11 +29,6 @@ int sm_count();
 int launch_pack_reads(const uint8_t *seq, const uint8_t *qual, uint64_t n, uint64_t nwords, int min_qual,
                       uint64_t *bases, uint32_t *mask, uint64_t *counters, cudaStream_t st, const uint32_t *qbits = nullptr);
 int launch_table_fill(void *slots, uint64_t cap, int kw, cudaStream_t st);
-int launch_extract_count(int kw, const uint64_t *bases, const uint32_t *mask, uint64_t nwords, int k,
-                         void *slots, uint64_t cap, uint64_t *counters, uint32_t *overflow, cudaStream_t st);
-int launch_rehash(int kw, void *old_slots, uint64_t old_cap, void *new_slots, uint64_t new_cap,
-                  uint32_t *overflow, cudaStream_t st);
-int launch_histogram_only(int kw, void *slots, uint64_t cap, uint64_t *histo, cudaStream_t st);
 int launch_histogram_filter(int kw, void *slots, uint64_t cap, int min_count, uint64_t *histo,
                             uint64_t *node_lo, uint64_t *node_hi, uint16_t *node_count, uint8_t *node_raw,
                             uint32_t node_cap, uint32_t *n_nodes, cudaStream_t st);

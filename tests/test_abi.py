@@ -99,3 +99,31 @@ def test_host_quality_bits_match_the_spec():
             assert out[-1] == 0xDEADBEEF
     q = np.zeros(32, np.uint8); out = np.zeros(1, np.uint32)
     assert lib.shk_qual_bits(q.ctypes.data, 32, 95, out.ctypes.data) != 0      # threshold beyond a 7-bit byte
+
+
+def _build_consumer(tmp_path):
+    import subprocess
+    exe = str(tmp_path / "abi_consumer")
+    libdir = os.path.join(ROOT, "sparrowhawk_b200")
+    subprocess.check_call(["gcc", "-std=c11", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"),
+                           os.path.join(ROOT, "tests", "abi_consumer.c"), "-o", exe,
+                           "-L", libdir, "-l:libshk_b200.so", f"-Wl,-rpath,{libdir}"])
+    return exe
+
+
+def test_c_consumer_of_the_header(tmp_path):
+    """A C11 program compiled against include/shk.h itself (what bindgen / a C host sees): layout
+    _Static_asserts + the handle life cycle through the real prototypes; no device needed."""
+    import subprocess
+    import torch
+    exe = _build_consumer(tmp_path)
+    r = subprocess.run([exe] + (["device"] if torch.cuda.is_available() else []), capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0 and r.stdout.startswith("abi ok"), r.stdout + r.stderr
+
+
+@pytest.mark.gpu
+def test_c_consumer_on_the_device(tmp_path):
+    import subprocess
+    exe = _build_consumer(tmp_path)
+    r = subprocess.run([exe, "device"], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0 and r.stdout.startswith("abi ok"), r.stdout + r.stderr
