@@ -122,6 +122,9 @@ static shk_status pack_from_device(shk_asm *h, const uint8_t *d_seq, const uint8
 }
 
 static bool fast_ready_for(shk_asm *h, uint64_t n_positions);
+static shk_status fast_params(shk_asm *h, uint64_t n_positions);
+static uint32_t buckets_for(uint64_t positions, int kw);
+static uint64_t region_records_guess(uint64_t positions, uint32_t P, int kw, int k);
 static shk_status fast_prologue(shk_asm *h);
 static double now_ms() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
 
@@ -287,6 +290,7 @@ static shk_status load_reads_host(shk_asm *h, const uint8_t *seq, const uint8_t 
   h->st.host_qual_bits = 0;
   if (!append && qual && n >= h->overlap_min) {
     const bool cut = fast_ready_for(h, n);
+    if (cut) SHK_TRY(fast_params(h, n));
     if (cut || qpack_usable(h)) return load_reads_overlapped(h, seq, qual, n, cut);
   }
   SHK_CUDA(cudaEventRecord(h->ev[0], h->stream));
@@ -329,13 +333,9 @@ static shk_status count_impl(shk_asm *h, int /*reset*/, uint32_t P_override = 0,
   const uint64_t positions = h->nwords * 32;
   const int k = h->p.k;
   // fine buckets: power of two, sized from the input alone
-  uint32_t P = next_pow2(std::max<uint64_t>(16, positions / target_bucket_instances(h->kw)));
-  if (P > (1u << 20)) P = 1u << 20;
+  uint32_t P = buckets_for(positions, h->kw);
   if (P_override) P = P_override;                    // sharded path: every rank cuts into the same buckets
-  // records per bucket: a run holds ~ (w+1)/2 k-mers for a window of w = k-m+1 m-mers
-  const int mlen = k < 11 ? k : 11, w = k - mlen + 1;
-  double avg_run = std::min<double>(records_max_run(h->kw, k), std::max(1.0, (w + 1) / 2.0 * 0.6));
-  uint64_t rcap64 = (uint64_t)(3.0 * (double)positions / avg_run / (double)P) + 64;
+  uint64_t rcap64 = region_records_guess(positions, P, h->kw, k);
   // a read set of the same size cut into the same buckets on this handle before: start from the region size
   // that was needed then (skewed buckets make the estimate fall short, and a retry costs a whole K1a pass)
   if (h->P == P && h->counted_positions == h->n_positions && h->rcap > rcap64) rcap64 = h->rcap;
@@ -461,7 +461,7 @@ static shk_status sweep_overflow(shk_asm *h, int mc_eff, uint32_t node_cap) {
   return read_scalars(h);
 }
 
-static shk_status index_impl(shk_asm *h);
+static shk_status index_impl(shk_asm *h, uint64_t icap = 0);
 // ---- steady-state K1a + K1b: nothing on the host between the two kernels ----------------
 // Preconditions (fast_ready): this handle has run the host-planned path on a read set of this
 // size, so the bucket count, the region size, the distinct/instances ratio and the de-dup list
@@ -470,11 +470,43 @@ static shk_status index_impl(shk_asm *h);
 // host-planned path (same results, one wasted pass).
 static bool fast_ready_for(shk_asm *h, uint64_t n_positions) {
   static const bool off = [] { const char *e = getenv("SHK_NO_FAST"); return e && e[0] == '1'; }();
-  return !off && h->ratio_est > 0 && h->P && h->rcap && h->fast_positions == n_positions && n_positions > 0 &&
-         h->fast_banned_positions != n_positions &&
-         !h->shard_world && (h->kw == 2 || h->no_dedup || h->uq_cap > 0) && h->ovf_cap > 0;
+  return !off && n_positions > 0 && h->fast_banned_positions != n_positions && !h->shard_world;
 }
 static bool fast_ready(shk_asm *h) { return fast_ready_for(h, h->n_positions); }
+
+static uint32_t buckets_for(uint64_t positions, int kw) {
+  uint32_t P = next_pow2(std::max<uint64_t>(16, positions / target_bucket_instances(kw)));
+  return std::min<uint32_t>(P, 1u << 20);
+}
+static uint64_t region_records_guess(uint64_t positions, uint32_t P, int kw, int k) {
+  // records per bucket: a run holds ~ (w+1)/2 k-mers for a window of w = k-m+1 m-mers
+  const int mlen = k < 11 ? k : 11, w = k - mlen + 1;
+  const double avg_run = std::min<double>(records_max_run(kw, k), std::max(1.0, (w + 1) / 2.0 * 0.6));
+  return (uint64_t)(3.0 * (double)positions / avg_run / (double)P) + 64;
+}
+
+// What K1a -> K1b back to back needs to know before anything has run: bucket count and region size from the
+// input size alone (the formulas of the host-planned path), default sizes for the de-dup lists and the overflow
+// table.  A handle that has already counted a read set of this size keeps what that run measured.  The distinct /
+// instances ratio is NOT needed: K1b's CTAs measure it on their own first groups (SelfPlan.cold).
+static shk_status fast_params(shk_asm *h, uint64_t n_positions) {
+  const uint64_t positions = (n_positions + 31) / 32 * 32;
+  if (h->fast_positions != n_positions || !h->P || !h->rcap) {
+    const uint32_t P = buckets_for(positions, h->kw);
+    uint64_t rcap64 = region_records_guess(positions, P, h->kw, h->p.k);
+    if (h->P == P && h->counted_positions == n_positions && h->rcap > rcap64) rcap64 = h->rcap;
+    if (rcap64 > 0x7FFFFFFFull) { set_error("record region too large"); return SHK_ERR_OOM; }
+    h->P = P; h->rcap = (uint32_t)rcap64;
+    h->fast_positions = 0;                        // not verified for this size yet
+  }
+  SHK_TRY(h->skrecs.ensure((size_t)h->P * h->rcap * record_bytes(h->kw)));
+  SHK_TRY(h->bfill.ensure((size_t)h->P * 8));
+  if (!h->ovf_cap) {
+    h->ovf_cap = std::max<uint64_t>(1u << 16, positions / 512);
+    SHK_TRY(h->ovf.ensure(h->ovf_cap * slot_bytes(h->kw)));
+  }
+  return SHK_OK;
+}
 
 // everything the steady-state path queues in front of K1a
 static shk_status fast_prologue(shk_asm *h) {
@@ -491,6 +523,7 @@ static shk_status count_filter_fast(shk_asm *h, int min_count, bool &fell_back) 
   SHK_TRY(require_device(h));
   const uint64_t *b = h->bases.as<uint64_t>() + 1;
   const uint32_t *m = h->mask.as<uint32_t>() + 1;
+  if (!h->partition_done) SHK_TRY(fast_params(h, h->n_positions));   // (an overlapped load has set them before cutting)
   const uint32_t P = h->P, rcap = h->rcap;
   const bool dedup = h->kw == 1 && !h->no_dedup;
   uint64_t bound = h->n_positions / ((uint64_t)std::max(min_count, 0) + 1) + 1;     // instances <= positions
@@ -504,7 +537,9 @@ static shk_status count_filter_fast(shk_asm *h, int min_count, bool &fell_back) 
   // ratio estimate), so size them with headroom over the host-planned need, or for what the last such run needed
   uint32_t uq_fast = 0;
   if (dedup) {
-    uq_fast = (uint32_t)std::min<uint64_t>(std::max<uint64_t>((uint64_t)h->uq_cap * 2 + 1024, (uint64_t)h->uq_need_hint + h->uq_need_hint / 8), 0x7FFFFFC0ull);
+    // (the CTAs never plan a group past the list, so any size is safe; a short list only means smaller groups)
+    uq_fast = (uint32_t)std::min<uint64_t>(std::max<uint64_t>({(uint64_t)h->uq_cap * 2 + 1024, (uint64_t)h->uq_need_hint + h->uq_need_hint / 8,
+                                                               (uint64_t)(h->uq_cap || h->uq_need_hint ? 0 : 32768)}), 0x7FFFFFC0ull);
     uq_fast = (uq_fast + 63u) & ~63u;
     const size_t ctas = (size_t)count_ctas();
     SHK_TRY(h->uq_rec.ensure(ctas * uq_fast * 16 + 16)); SHK_TRY(h->uq_cnt.ensure(ctas * uq_fast * 4 + 16));
@@ -520,7 +555,8 @@ static shk_status count_filter_fast(shk_asm *h, int min_count, bool &fell_back) 
   SHK_CUDA(cudaEventRecord(h->ev[3], h->stream));
   SHK_CUDA(cudaEventRecord(h->ev[4], h->stream));
   h->st.gpu_launches += launch_table_fill(h->ovf.p, h->ovf_cap, h->kw, h->stream);
-  SelfPlanArgs spa{P, h->ratio_est, count_table_slots(h->kw) * table_load(), d_flags(h) + 4, d_counters(h) + 6};
+  const bool cold = !(h->ratio_est > 0);
+  SelfPlanArgs spa{P, cold ? 1.0 : h->ratio_est, count_table_slots(h->kw) * table_load(), d_flags(h) + 4, d_counters(h) + 6, 1, cold};
   SHK_CUDA(cudaEventRecord(h->ev[10], h->stream));
   h->st.gpu_launches += launch_count_buckets(h->kw, h->skrecs.p, h->bfill.as<uint64_t>(), rcap, nullptr, nullptr,
                                              dedup ? h->uq_rec.p : nullptr, h->uq_cnt.as<uint32_t>(), uq_fast,
@@ -553,6 +589,7 @@ static shk_status count_filter_fast(shk_asm *h, int min_count, bool &fell_back) 
   h->src_instances = h->st.n_instances; h->shard_src = false; h->seg_per_bucket = 1;
   h->seg_kmers.clear(); h->seg_recs.clear();               // the host-side bucket description is not fetched on this path
   h->counted = true; h->counted_fast = true; h->st.device_planned = 1;
+  h->fast_positions = h->n_positions;
   h->st.n_spilled = h->h_pinned[4];
   h->spill_hint = h->st.n_spilled;
   if (h->st.n_spilled) SHK_TRY(sweep_overflow(h, min_count, node_cap));
@@ -660,25 +697,19 @@ static shk_status filter_impl(shk_asm *h, int min_count, bool histogram_only = f
   return index_impl(h);
 }
 
-// node index for the graph stage: key -> node id, 2 slots per node
-static shk_status index_impl(shk_asm *h) {
+// node index for the graph stage (shk_index.cuh): key -> node id, one u32 per slot, 2 slots per node.  Only queued:
+// the overflow flag (d_flags[7]; 4096 probes at half load never happen) is read with the graph stage's scalars.
+static shk_status index_impl(shk_asm *h, uint64_t icap) {
   const uint32_t nn = (uint32_t)h->st.n_nodes;
-  // node index for the graph stage: key -> node id, 2 slots per node
-  uint64_t icap = std::max<uint64_t>(64, 2ull * nn);
-  for (int attempt = 0;; ++attempt) {
-    SHK_TRY(h->slots.ensure(icap * slot_bytes(h->kw)));
-    h->cap = icap;
-    h->st.gpu_launches += launch_table_fill(h->slots.p, icap, h->kw, h->stream);
-    SHK_CUDA(cudaMemsetAsync(d_flags(h), 0, 4, h->stream));
-    h->st.gpu_launches += launch_index_nodes(h->kw, h->slots.p, icap, h->node_lo.as<uint64_t>(), h->node_hi.as<uint64_t>(), nn,
-                                             d_flags(h), h->stream);
-    SHK_CUDA(cudaGetLastError());
-    SHK_CUDA(cudaEventRecord(h->ev[5], h->stream));
-    SHK_TRY(read_scalars(h));
-    if (!((uint32_t *)(h->h_pinned + 8 + SHK_HISTO_BINS))[0]) break;
-    if (attempt >= 3) { set_error("node index overflow"); return SHK_ERR_TABLE_FULL; }
-    icap *= 2;
-  }
+  if (!icap) icap = std::max<uint64_t>(64, 2ull * nn);
+  SHK_TRY(h->slots.ensure(icap * 4));
+  h->cap = icap;
+  SHK_CUDA(cudaMemsetAsync(h->slots.p, 0xFF, icap * 4, h->stream));
+  SHK_CUDA(cudaMemsetAsync(d_flags(h) + 7, 0, 4, h->stream));
+  h->st.gpu_launches += launch_index_nodes(h->kw, h->slots.as<uint32_t>(), icap, h->node_lo.as<uint64_t>(), h->node_hi.as<uint64_t>(), nn,
+                                           d_flags(h) + 7, h->stream);
+  SHK_CUDA(cudaGetLastError());
+  SHK_CUDA(cudaEventRecord(h->ev[5], h->stream));
   h->filtered = true; h->graphed = false;
   h->hu.valid = false;
   return SHK_OK;
@@ -687,6 +718,11 @@ static shk_status index_impl(shk_asm *h) {
 static shk_status histogram_impl(shk_asm *h) { return filter_impl(h, 0, true); }
 
 // ---- K3..K6: graph ---------------------------------------------------------
+// Everything is queued back to back — the sizes the kernels need from each other (splitters, unitigs) are read from
+// device memory — and the host reads ONE block of scalars at the end: node-index overflow, splitter work area too
+// small, elements left on unbranched cycles, unitigs, sequence bytes, links.  Anything unusual there (cycles: a
+// second ranking pass with the cycles cut at their minimum k-mer; a buffer that was guessed too small) re-runs
+// the part it invalidates.
 static shk_status graph_impl(shk_asm *h) {
   SHK_TRY(require_device(h));
   if (!h->filtered) { set_error("build_graph before filter"); return SHK_ERR_STATE; }
@@ -716,8 +752,8 @@ static shk_status graph_impl(shk_asm *h) {
   uint32_t link_cap = (uint32_t)std::min<uint64_t>((uint64_t)N / 2 + 4096, 0x7FFFFFFFull);
   SHK_TRY(h->link_from.ensure((size_t)link_cap * 4)); SHK_TRY(h->link_to.ensure((size_t)link_cap * 4));
   SHK_TRY(h->gscal.ensure(64));
-  SHK_CUDA(cudaMemsetAsync(h->gscal.p, 0, 64, h->stream));
-  SHK_CUDA(cudaMemsetAsync(h->tail_of.p, 0xFF, ne * 4, h->stream));
+  SHK_TRY(h->gpin.ensure_host(64 + 32));
+  uint32_t *hs = (uint32_t *)h->gpin.p, *hfl = hs + 16;
 
   GraphBuffers g{};
   g.node_lo = h->node_lo.as<uint64_t>(); g.node_hi = h->kw == 2 ? h->node_hi.as<uint64_t>() : nullptr;
@@ -733,59 +769,81 @@ static shk_status graph_impl(shk_asm *h) {
   g.splitters = h->splitters.as<uint32_t>(); g.sum_of = h->sum_of.as<uint64_t>();
 
   uint64_t &L = h->st.gpu_launches;
-  uint32_t hs[16];
-  L += launch_build_edges(h->kw, h->slots.p, h->cap, k, g, h->stream);
-  L += launch_unitig_links(g, h->stream);
-  // K5: rank every directed list; a second pass only when unbranched cycles exist
-  bool have_circ = false;
-  for (int pass = 0; pass < 2; ++pass) {
-    const uint8_t *circ = pass ? g.circ : nullptr;
+  // splitters = a pseudo-random 1/32 of the elements + every list head.  The work area is sized from a guess (an
+  // eighth of the elements, or what the last run on this handle needed) and verified on the device.
+  uint32_t ns_cap = (uint32_t)std::min<uint64_t>(ne, std::max<uint64_t>(ne / 8 + 65536, (uint64_t)h->ns_hint + h->ns_hint / 4 + 1024));
+  auto read_back = [&]() -> shk_status {
+    SHK_CUDA(cudaMemcpyAsync(hs, h->gscal.p, 64, cudaMemcpyDeviceToHost, h->stream));
+    SHK_CUDA(cudaMemcpyAsync(hfl, d_flags(h), 32, cudaMemcpyDeviceToHost, h->stream));
+    SHK_CUDA(cudaStreamSynchronize(h->stream));
+    return SHK_OK;
+  };
+  auto rank_pass = [&](const uint8_t *circ) -> shk_status {
+    SHK_TRY(h->rank_work.ensure((size_t)ns_cap * rank_splitter_bytes() + 64));
     SHK_CUDA(cudaMemsetAsync(h->pd.p, 0xFF, ne * 8, h->stream));
-    SHK_CUDA(cudaMemsetAsync(g.scal + 4, 0, 4, h->stream));
-    SHK_CUDA(cudaMemsetAsync(g.scal + 1, 0, 4, h->stream));
+    SHK_CUDA(cudaMemsetAsync(g.scal, 0, 64, h->stream));              // every counter and flag of the stage
     L += launch_rank_mark(g, circ, h->stream);
+    L += launch_rank_lists(g, circ, ns_cap, h->rank_work.p, h->stream);
+    return SHK_OK;
+  };
+  auto emit_pass = [&](bool have_circ) -> shk_status {
+    L += launch_unitig_heads(g, k, have_circ, h->stream);
+    L += launch_unitig_emit(h->kw, g, k, h->stream);
+    L += launch_unitig_links_out(h->kw, h->slots.as<uint32_t>(), h->cap, k, g, std::min(N, ns_cap), h->stream);
     SHK_CUDA(cudaGetLastError());
-    SHK_CUDA(cudaMemcpyAsync(hs, h->gscal.p, 64, cudaMemcpyDeviceToHost, h->stream));
-    SHK_CUDA(cudaStreamSynchronize(h->stream));
-    const uint32_t ns = hs[4];
-    SHK_TRY(h->rank_work.ensure((size_t)ns * rank_splitter_bytes() + 64));
-    L += launch_rank_lists(g, circ, ns, h->rank_work.p, h->stream);
-    SHK_CUDA(cudaGetLastError());
-    SHK_CUDA(cudaMemcpyAsync(hs, h->gscal.p, 64, cudaMemcpyDeviceToHost, h->stream));
-    SHK_CUDA(cudaStreamSynchronize(h->stream));
+    SHK_CUDA(cudaEventRecord(h->ev[7], h->stream));
+    return SHK_OK;
+  };
+  for (int attempt = 0;; ++attempt) {
+    if (attempt > 4) { set_error("graph stage did not settle after retries"); return SHK_ERR_STATE; }
+    SHK_CUDA(cudaMemsetAsync(h->tail_of.p, 0xFF, ne * 4, h->stream));
+    L += launch_build_edges(h->kw, h->slots.as<uint32_t>(), h->cap, k, g, h->stream);
+    L += launch_unitig_links(g, h->stream);
+    SHK_TRY(rank_pass(nullptr));
+    SHK_TRY(emit_pass(false));
+    SHK_TRY(read_back());
+    if (hfl[7]) {                                      // node index overflow: twice the slots, everything again
+      if (h->cap > (1ull << 36)) { set_error("node index overflow"); return SHK_ERR_TABLE_FULL; }
+      SHK_TRY(index_impl(h, h->cap * 2));
+      continue;
+    }
+    if (hs[5]) {                                       // more splitters than the work area holds: the count is known now
+      h->ns_hint = hs[4];
+      ns_cap = (uint32_t)std::min<uint64_t>(ne, (uint64_t)hs[4] + 1024);
+      continue;
+    }
+    h->ns_hint = hs[4];
     const uint32_t n_cyclic = hs[1];
-    if (!n_cyclic) break;
-    if (pass == 1) { set_error("list ranking left %u elements unranked", n_cyclic); return SHK_ERR_STATE; }
-    SHK_TRY(h->cq.ensure(2 * ne * 8));
-    SHK_TRY(h->circ.ensure(ne));
-    g.cq = h->cq.as<uint64_t>(); g.circ = h->circ.as<uint8_t>();
-    L += launch_cycle_cut(g, n_cyclic, h->stream);
-    have_circ = true;
+    if (n_cyclic) {
+      // unbranched cycles: cut each at its minimum k-mer (S14) and rank again with the cut elements as forced heads
+      SHK_TRY(h->cq.ensure(2 * ne * 8));
+      SHK_TRY(h->circ.ensure(ne));
+      g.cq = h->cq.as<uint64_t>(); g.circ = h->circ.as<uint8_t>();
+      L += launch_cycle_cut(g, n_cyclic, h->stream);
+      ns_cap = (uint32_t)std::min<uint64_t>(ne, (uint64_t)std::max(ns_cap, hs[4]) + n_cyclic + 64);
+      SHK_TRY(rank_pass(g.circ));
+      SHK_TRY(emit_pass(true));
+      SHK_TRY(read_back());
+      if (hs[5]) { set_error("splitter work area overflow in the cycle pass (%u > %u)", hs[4], ns_cap); return SHK_ERR_STATE; }
+      if (hs[1]) { set_error("list ranking left %u elements unranked", hs[1]); return SHK_ERR_STATE; }
+    }
+    break;
   }
-  L += launch_unitig_heads(g, k, have_circ, h->stream);
-  L += launch_unitig_emit(h->kw, g, k, h->stream);
-  SHK_CUDA(cudaGetLastError());
-  SHK_CUDA(cudaMemcpyAsync(hs, h->gscal.p, 64, cudaMemcpyDeviceToHost, h->stream));
-  SHK_CUDA(cudaStreamSynchronize(h->stream));
+  const bool have_circ = g.circ != nullptr;
   uint32_t nu = hs[2];
   uint64_t seq_len; memcpy(&seq_len, hs + 8, 8);
-  L += launch_unitig_links_out(h->kw, h->slots.p, h->cap, k, g, nu, h->stream);
-  SHK_CUDA(cudaGetLastError());
-  SHK_CUDA(cudaEventRecord(h->ev[7], h->stream));
-  SHK_CUDA(cudaMemcpyAsync(hs, h->gscal.p, 64, cudaMemcpyDeviceToHost, h->stream));
-  SHK_CUDA(cudaStreamSynchronize(h->stream));
   if (hs[3] > link_cap) {
     link_cap = hs[3];
     SHK_TRY(h->link_from.ensure((size_t)link_cap * 4)); SHK_TRY(h->link_to.ensure((size_t)link_cap * 4));
     g.link_from = h->link_from.as<uint32_t>(); g.link_to = h->link_to.as<uint32_t>(); g.link_cap = link_cap;
     SHK_CUDA(cudaMemsetAsync(g.scal + 3, 0, 4, h->stream));
-    L += launch_unitig_links_out(h->kw, h->slots.p, h->cap, k, g, nu, h->stream);
+    L += launch_unitig_links_out(h->kw, h->slots.as<uint32_t>(), h->cap, k, g, nu, h->stream);
     SHK_CUDA(cudaGetLastError());
     SHK_CUDA(cudaEventRecord(h->ev[7], h->stream));
-    SHK_CUDA(cudaMemcpyAsync(hs, h->gscal.p, 64, cudaMemcpyDeviceToHost, h->stream));
-    SHK_CUDA(cudaStreamSynchronize(h->stream));
+    SHK_TRY(read_back());
     if (hs[3] > link_cap) { set_error("unitig link buffer overflow (%u > %u)", hs[3], link_cap); return SHK_ERR_OOM; }
   }
+  (void)have_circ;
   h->st.n_unitigs = nu; h->st.unitig_bases = seq_len; h->st.n_links = hs[3];
   h->graphed = true; h->hu.valid = false;
   return SHK_OK;
@@ -1158,11 +1216,7 @@ shk_status shk_asm_preprocess_files(shk_asm *h, const char *path1, const char *p
 // One handle per rank.  The host's collective library moves the bytes between the
 // calls (NCCL all-to-all / all-gather through torch.distributed in this repo's
 // Python host, ncclSend/ncclRecv from a Rust host); nothing here communicates.
-uint32_t shk_shard_buckets(uint64_t global_positions, int k) {
-  const int kw = k <= 31 ? 1 : 2;
-  uint32_t P = next_pow2(std::max<uint64_t>(16, global_positions / target_bucket_instances(kw)));
-  return std::min<uint32_t>(P, 1u << 20);
-}
+uint32_t shk_shard_buckets(uint64_t global_positions, int k) { return buckets_for(global_positions, k <= 31 ? 1 : 2); }
 size_t shk_record_bytes(int k) { return record_bytes(k <= 31 ? 1 : 2); }
 
 shk_status shk_shard_partition(shk_asm *h, uint32_t n_buckets, uint32_t world, uint32_t rank, uint64_t *send_records) {
@@ -1289,7 +1343,7 @@ shk_status shk_shard_count_device(shk_asm *h, const void *d_recv, const uint64_t
     SHK_CUDA(cudaMemsetAsync(d_counters(h) + 2, 0, 8, h->stream));                     // n_distinct ([1], [3]: K1a's totals stay)
     SHK_CUDA(cudaMemsetAsync(d_counters(h) + 4, 0, 4 * 8 + SHK_HISTO_BINS * 8 + 8 * 4, h->stream));   // spilled, decoded, records, spectrum, flags
     h->st.gpu_launches += launch_table_fill(h->ovf.p, h->ovf_cap, h->kw, h->stream);
-    SelfPlanArgs spa{nb, h->ratio_est, count_table_slots(h->kw) * table_load(), d_flags(h) + 4, d_counters(h) + 6, W};
+    SelfPlanArgs spa{nb, h->ratio_est, count_table_slots(h->kw) * table_load(), d_flags(h) + 4, d_counters(h) + 6, W, false};
     SHK_CUDA(cudaEventRecord(h->ev[10], h->stream));
     h->st.gpu_launches += launch_count_buckets(h->kw, d_recv, h->shard_btot.as<uint64_t>(), 0xFFFFFFFFu, h->seg_off.as<uint64_t>(),
                                                h->seg_cnt.as<uint32_t>(), dedup ? h->uq_rec.p : nullptr, h->uq_cnt.as<uint32_t>(), uq_fast,

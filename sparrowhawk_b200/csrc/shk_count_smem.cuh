@@ -222,6 +222,8 @@ struct SelfPlan {
   u32 *stats; u64 *nrec;
   u32 spb;   // segments per bucket: 1 = the local regions; W on the sharded path (bucket j = segments j*W .. j*W+W-1,
              // one per source rank), where bstat holds the per-bucket totals over the sources
+  u32 cold;  // 1: ratio_q16 is a placeholder (nothing was ever counted on this handle): every CTA starts with one
+             // bucket per group and takes the distinct / instances ratio from what it has counted itself
 };
 
 struct CountOut {
@@ -269,7 +271,7 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
 
   const bool self_plan = group_start == nullptr;
   u32 sp_mxfill = 0, sp_need = 0; u64 sp_nrec = 0;                 // warp 0: what the host verifies after a self-planned run
-  if (tid == 0) { misc[7] = g_begin + atomicAdd(next_group, 1u); misc[3] = 0; misc[8] = 0; misc[9] = 0; }
+  if (tid == 0) { misc[7] = g_begin + atomicAdd(next_group, 1u); misc[3] = 0; misc[8] = 0; misc[9] = 0; misc[11] = sp.ratio_q16; misc[14] = sp.cold; }
   __syncthreads();
   for (;;) {
     // misc[7] = this CTA's next group (or next bucket chunk), fetched one ahead (thread 0, below) so that no
@@ -289,7 +291,7 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
       }
     }
     // ---- prefix of the group's record counts (the table is empty here) ----
-    if (tid == 0) { misc[1] = 0; misc[2] = 0; misc[5] = 0; }       // nobody touches these before the next barrier
+    if (tid == 0) { misc[1] = 0; misc[2] = 0; misc[5] = 0; misc[12] = 0; }       // nobody touches these before the next barrier
     if (warp == 0 && !self_plan) {
       u32 run = 0;
       for (u32 base = 0; base < nb; base += 32) {
@@ -305,26 +307,36 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
       if (lane == 0) gpre[0] = 0;
     } else if (warp == 0) {
       // greedy cut: buckets b0, b0+1, ... while the estimated distinct k-mers stay within the budget (at least one)
-      u32 run = 0, cnt = 0; u64 acc = 0;
-      const u32 maxb = (u32)SHK_CB_MAXC / sp.spb;
+      u32 run = 0, cnt = 0, kacc = 0; u64 acc = 0;
+      // the ratio this CTA plans with: the host's estimate at first, then what its own groups measured (below);
+      // a cold CTA takes one bucket for its first group (all of it distinct still fits: the buckets are sized so)
+      const u32 ratio_q16 = __shfl_sync(0xffffffffu, misc[11], 0);
+      const bool first_cold = __shfl_sync(0xffffffffu, misc[14], 0) != 0;
+      const u32 maxb = first_cold ? 1u : (u32)SHK_CB_MAXC / sp.spb;
       for (u32 base = 0; b0 + base < ce; base += 32) {
         const u32 i = base + lane;
         const bool valid = b0 + i < ce;
         const u64 v = valid ? bstat[b0 + i] : 0ull;
         const u32 fill = (u32)v, f = seg_off ? fill : min(fill, rcap);
         sp_mxfill = max(sp_mxfill, fill);
-        u64 est = (u64)(u32)(v >> 32) * sp.ratio_q16; u32 inc = f;
+        u64 est = (u64)(u32)(v >> 32) * ratio_q16; u32 inc = f, kin = (u32)(v >> 32);
         for (int o = 1; o < 32; o <<= 1) {
           const u64 t = __shfl_up_sync(0xffffffffu, est, o); const u32 u = __shfl_up_sync(0xffffffffu, inc, o);
-          if (lane >= o) { est += t; inc += u; }
+          const u32 kk = __shfl_up_sync(0xffffffffu, kin, o);
+          if (lane >= o) { est += t; inc += u; kin += kk; }
         }
-        const bool fits = valid && (acc + est <= sp.budget_q16 || (cnt == 0 && lane == 0));
+        // the de-dup list holds at most one item per record plus one per SHK_CB_SEG k-mers: never plan past it
+        const bool list_ok = !DEDUP || (u64)run + inc + (kacc + kin) / SHK_CB_SEG + 1 <= (u64)uq_cap;
+        const bool fits = valid && ((acc + est <= sp.budget_q16 && list_ok) || (cnt == 0 && lane == 0));
         const u32 m = __ballot_sync(0xffffffffu, fits);               // a prefix of the lanes: est only grows
         u32 take = m == 0xFFFFFFFFu ? 32u : (u32)__ffs(~m) - 1u;
         const bool capped = cnt + take > maxb;                          // a group holds at most SHK_CB_MAXC segments
         if (capped) take = maxb - cnt;
         if ((u32)lane < take) { gpre[i + 1] = run + inc; sp_nrec += f; }
-        if (take) { run += __shfl_sync(0xffffffffu, inc, take - 1); acc += __shfl_sync(0xffffffffu, est, take - 1); }
+        if (take) {
+          run += __shfl_sync(0xffffffffu, inc, take - 1); acc += __shfl_sync(0xffffffffu, est, take - 1);
+          kacc += __shfl_sync(0xffffffffu, kin, take - 1);
+        }
         cnt += take;
         if (take < 32 || capped) break;
       }
@@ -340,7 +352,7 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
           run += __shfl_sync(0xffffffffu, inc, 31);
         }
       }
-      if (lane == 0) { gpre[0] = 0; misc[10] = cnt; }
+      if (lane == 0) { gpre[0] = 0; misc[10] = cnt; misc[13] = kacc; }
     }
     __syncthreads();
     if (self_plan) nb = misc[10];
@@ -541,6 +553,7 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
     // Bins 0 and 1 (sequencing errors: most distinct k-mers) and the distinct count live in registers;
     // survivors are collected as slot numbers in shared memory so the group pays ONE global atomic
     // and writes its nodes densely.
+    const u32 ndist_before = ndist;
     for (int s = tid; s < NS; s += THREADS) {
       bool occ;
       if (KW == 1) occ = reinterpret_cast<u64 *>(keys)[s] != SHK_EMPTY64;
@@ -568,7 +581,19 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
       else reinterpret_cast<U128Pair *>(keys)[s] = U128Pair{SHK_EMPTY64, SHK_EMPTY64};
       vals[s] = 0;
     }
+    if (self_plan) {                                                 // distinct k-mers of this group, for the planning ratio
+      u32 dg = ndist - ndist_before;
+      for (int o = 16; o; o >>= 1) dg += __shfl_xor_sync(0xffffffffu, dg, o);
+      if (lane == 0 && dg) atomicAdd(&misc[12], dg);
+    }
     __syncthreads();
+    if (self_plan && tid == 0 && misc[13]) {
+      // measured distinct / instances of the group just counted, with the host planner's margin (x 1.10 + 0.005);
+      // blended with the running value — a cold CTA takes its first measurement as it is
+      const u32 meas = (u32)min((u64)65536, ((u64)misc[12] * 72090ull) / misc[13] + 328ull);
+      misc[11] = misc[14] ? meas : max(1u, (misc[11] + 3u * meas) >> 2);
+      misc[14] = 0;
+    }
     const u32 nsurv = min(misc[3], SURV_CAP);
     if (nsurv) {
       if (tid == 0) misc[4] = atomicAdd(out.n_nodes, nsurv);
@@ -612,34 +637,6 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
     if (nspill) atomicAdd(&out.counters[4], nspill);
     if (ndec) atomicAdd(&out.counters[5], ndec);
   }
-}
-
-// Node index for the graph stage: key -> node id in a compact global table
-// (2 slots per node), replacing the HBM-wide k-mer table of a one-pass design.
-template <int KW>
-__global__ void __launch_bounds__(256)
-k_index_nodes(Table<KW> t, const u64 *__restrict__ node_lo, const u64 *__restrict__ node_hi, u32 n_nodes,
-              u32 *__restrict__ overflow) {
-  typedef typename KeyOf<KW>::type K;
-  u32 n = blockIdx.x * blockDim.x + threadIdx.x;
-  if (n >= n_nodes) return;
-  K key = (K)__ldcs(node_lo + n);                     // streamed once: leave the L2 to the table
-  if (KW == 2) key |= (K)((u128)__ldcs(node_hi + n) << 64);
-  u64 i = slot_of(hash_key(key), t.cap);
-  for (u32 probe = 0; probe < t.max_probe; ++probe) {
-    typename SlotOf<KW>::type *sp = t.slots + i;
-    bool mine;
-    if (KW == 1) {
-      mine = atomicCAS(&reinterpret_cast<Slot1 *>(sp)->key, SHK_EMPTY64, (u64)key) == SHK_EMPTY64;
-    } else {
-      U128Pair expect{SHK_EMPTY64, SHK_EMPTY64}, want{(u64)key, (u64)((u128)key >> 64)};
-      U128Pair old = atomicCAS(reinterpret_cast<U128Pair *>(sp), expect, want);
-      mine = old.hi == SHK_EMPTY64;
-    }
-    if (mine) { sp->count = n; return; }
-    if (++i == t.cap) i = 0;
-  }
-  atomicExch(overflow, 1u);
 }
 
 }  // namespace shk

@@ -141,6 +141,8 @@ struct shk_asm {
   shk::DevBuf uniq, succ, tail_of, len_of, unitig_of_head, elem_unitig, pd, cq, circ;
   shk::DevBuf recs, ucirc, cov_sum, useq, link_from, link_to, gscal, splitters, sum_of, rank_work;
   uint32_t node_cap = 0;
+  shk::PinBuf gpin;             // graph stage: pinned mirror of its scalars
+  uint32_t ns_hint = 0;         // splitters the last graph stage on this handle needed
 
   // ---- results / state ----
   shk_stats st;

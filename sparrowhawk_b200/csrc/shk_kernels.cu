@@ -2,11 +2,13 @@
 // (SURVEY.md §2.2 K0..K6).  Integer / byte work bound by HBM and L2 atomics; no
 // tensor cores (nothing here is a dense contraction).  Launch wrappers at the
 // bottom are the only symbols other translation units use (shk_kernels.h).
+#include <algorithm>
 #include <type_traits>
 
 #include "shk_device.cuh"
 #include "shk_kernels.h"
 #include "shk_table.cuh"
+#include "shk_index.cuh"
 #include "shk_count_smem.cuh"
 #include "shk_rank.cuh"
 
@@ -135,64 +137,47 @@ k_histogram_filter(Table<KW> tbl, int min_count, u64 *__restrict__ histo /*[500]
 // the unique neighbour (node id << 1 | arrival side) when exactly one edge
 // survives.
 // =====================================================================
+// first probe already in flight: `id` = content of slot i.  Confirms against the key arrays, walks on after a collision.
 template <int KW>
-__device__ __forceinline__ u32 table_find(const Table<KW> &t, typename KeyOf<KW>::type key) {
-  typedef typename KeyOf<KW>::type K;
-  u64 i = slot_of(hash_key(key), t.cap);
-  for (u32 probe = 0; probe < t.max_probe; ++probe) {
-    K cur; u32 cnt, e;
-    if (!slot_load<KW>(t.slots + i, cur, cnt, e)) return SHK_NONE;  // empty: absent
-    if (cur == key) return cnt;                                     // node id or SHK_NONE
-    if (++i == t.cap) i = 0;
-  }
-  return SHK_NONE;
+__device__ __forceinline__ u32 index_resolve(const NodeIndex &ix, typename KeyOf<KW>::type Y, u64 i, u32 id, u64 klo, u64 khi) {
+  if (id == SHK_NONE) return SHK_NONE;
+  if (klo == (u64)Y && (KW == 1 || khi == (u64)((u128)Y >> 64))) return id;
+  if (++i == ix.cap) i = 0;
+  return index_find_from<KW>(ix, Y, i, __ldcg(ix.slots + i));
 }
 
 template <int KW>
 __global__ void __launch_bounds__(256)
-k_build_edges(Table<KW> tbl, int k, const u64 *__restrict__ node_lo, const u64 *__restrict__ node_hi,
-              const uint8_t *__restrict__ node_raw, u32 n_nodes, uint8_t *__restrict__ node_edges,
+k_build_edges(NodeIndex ix, int k, const uint8_t *__restrict__ node_raw, u32 n_nodes, uint8_t *__restrict__ node_edges,
               u32 *__restrict__ uniq /* [2*n_nodes] */) {
   typedef typename KeyOf<KW>::type K;
   u32 n = blockIdx.x * blockDim.x + threadIdx.x;
   if (n >= n_nodes) return;
-  // the node arrays stream through once; the index (the random-access side) should keep the L2
-  K X = (K)__ldcs(node_lo + n);
-  if (KW == 2) X |= (K)((u128)__ldcs(node_hi + n) << 64);
+  K X = (K)ix.lo[n];
+  if (KW == 2) X |= (K)((u128)ix.hi[n] << 64);
   u32 raw = __ldcs(node_raw + n), valid = 0;
   u32 un[2] = {SHK_NONE, SHK_NONE};
   // The lookups of a node are independent random accesses into the index: take the set bits two at a time so that
-  // both first probes are in flight together (a typical unitig-interior node has exactly two, one per side).
-  auto resolve = [&](int bit, K Y, int s_in, u64 i, bool nonempty, K cur, u32 cnt) {
-    u32 id = SHK_NONE;
-    if (nonempty) {
-      if (cur == Y) id = cnt;
-      else {                                                          // collision: walk on from the next slot
-        for (u32 probe = 1; probe < tbl.max_probe; ++probe) {
-          if (++i == tbl.cap) i = 0;
-          K c2; u32 n2, e2;
-          if (!slot_load<KW>(tbl.slots + i, c2, n2, e2)) break;
-          if (c2 == Y) { id = n2; break; }
-        }
-      }
-    }
-    if (id != SHK_NONE) { valid |= 1u << bit; un[bit >> 2] = (id << 1) | (u32)s_in; }
-  };
+  // both slot loads, then both key loads, are in flight together (a unitig-interior node has exactly two, one per side).
   u32 rem = raw;
   while (rem) {
     const int b0 = __ffs(rem) - 1; rem &= rem - 1;
     const int b1 = rem ? __ffs(rem) - 1 : -1; if (b1 >= 0) rem &= rem - 1;
     int s0, s1 = 0;
     const K Y0 = neighbour_key(X, k, b0 >> 2, (u32)(b0 & 3), s0);
-    const u64 i0 = slot_of(hash_key(Y0), tbl.cap);
+    const u64 i0 = slot_of(hash_key(Y0), ix.cap);
     K Y1 = 0; u64 i1 = 0;
-    if (b1 >= 0) { Y1 = neighbour_key(X, k, b1 >> 2, (u32)(b1 & 3), s1); i1 = slot_of(hash_key(Y1), tbl.cap); }
-    K c0, c1 = 0; u32 n0, n1 = 0, e0, e1;
-    const bool f0 = slot_load<KW>(tbl.slots + i0, c0, n0, e0);
-    bool f1 = false;
-    if (b1 >= 0) f1 = slot_load<KW>(tbl.slots + i1, c1, n1, e1);
-    resolve(b0, Y0, s0, i0, f0, c0, n0);
-    if (b1 >= 0) resolve(b1, Y1, s1, i1, f1, c1, n1);
+    if (b1 >= 0) { Y1 = neighbour_key(X, k, b1 >> 2, (u32)(b1 & 3), s1); i1 = slot_of(hash_key(Y1), ix.cap); }
+    const u32 c0 = __ldcg(ix.slots + i0), c1 = b1 >= 0 ? __ldcg(ix.slots + i1) : SHK_NONE;
+    u64 l0 = 0, l1 = 0, h0 = 0, h1 = 0;
+    if (c0 != SHK_NONE) { l0 = __ldcg(ix.lo + c0); if (KW == 2) h0 = __ldcg(ix.hi + c0); }
+    if (c1 != SHK_NONE) { l1 = __ldcg(ix.lo + c1); if (KW == 2) h1 = __ldcg(ix.hi + c1); }
+    const u32 id0 = index_resolve<KW>(ix, Y0, i0, c0, l0, h0);
+    if (id0 != SHK_NONE) { valid |= 1u << b0; un[b0 >> 2] = (id0 << 1) | (u32)s0; }
+    if (b1 >= 0) {
+      const u32 id1 = index_resolve<KW>(ix, Y1, i1, c1, l1, h1);
+      if (id1 != SHK_NONE) { valid |= 1u << b1; un[b1 >> 2] = (id1 << 1) | (u32)s1; }
+    }
   }
   node_edges[n] = (uint8_t)valid;
   __stcs(reinterpret_cast<uint2 *>(uniq) + n, make_uint2(__popc(valid & 15u) == 1 ? un[0] : SHK_NONE,
@@ -314,6 +299,7 @@ k_unitig_emit(const u64 *__restrict__ pd, const u32 *__restrict__ unitig_of_head
   u32 e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= n_elems) return;
   u64 v = pd[e];
+  if (v == ~0ull) { if (elem_unitig) elem_unitig[e] = SHK_NONE; return; }   // unranked: on a cycle that is cut in a second pass
   u32 h = (u32)(v >> 32), r = (u32)v;
   u32 uid = unitig_of_head[h];
   if (elem_unitig) elem_unitig[e] = uid;
@@ -336,7 +322,7 @@ k_unitig_emit(const u64 *__restrict__ pd, const u32 *__restrict__ unitig_of_head
 // the dropped mirror, the kept one is entered in reverse through its tail.
 template <int KW>
 __global__ void __launch_bounds__(256)
-k_unitig_links_out(Table<KW> tbl, int k, const UnitigRec *__restrict__ recs, u32 n_unitigs,
+k_unitig_links_out(NodeIndex ix, int k, const UnitigRec *__restrict__ recs, const u32 *__restrict__ n_unitigs_dev,
                    const u32 *__restrict__ tail_of, const u32 *__restrict__ unitig_of_head,
                    const u64 *__restrict__ node_lo, const u64 *__restrict__ node_hi,
                    const uint8_t *__restrict__ node_edges, const uint8_t *__restrict__ ucirc,
@@ -344,7 +330,7 @@ k_unitig_links_out(Table<KW> tbl, int k, const UnitigRec *__restrict__ recs, u32
                    u32 link_cap, u32 *__restrict__ n_links) {
   typedef typename KeyOf<KW>::type K;
   u32 i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= 2 * n_unitigs) return;
+  if (i >= 2 * *n_unitigs_dev) return;                   // counted by k_unitig_heads; the grid covers the host's bound
   u32 uid = i >> 1, orient = i & 1u;
   u32 head = recs[uid].head;
   u32 x = orient == 0 ? tail_of[head] : (head ^ 1u);     // exit element
@@ -361,7 +347,7 @@ k_unitig_links_out(Table<KW> tbl, int k, const UnitigRec *__restrict__ recs, u32
   for (u32 b = 0; b < 4; ++b) {
     if (!((bits >> b) & 1u)) continue;
     int s_in; K Y = neighbour_key(X, k, side, b, s_in);
-    u32 w = table_find<KW>(tbl, Y);
+    u32 w = index_find<KW>(ix, Y);
     if (w == SHK_NONE) continue;               // cannot happen after validation
     u32 f = 2 * w + ((u32)s_in ^ 1u);          // entered element: head of its list
     u32 target = unitig_of_head[f];
@@ -449,16 +435,12 @@ int launch_histogram_filter(int kw, void *slots, uint64_t cap, int min_count, ui
   return 1;
 }
 
-int launch_build_edges(int kw, void *slots, uint64_t cap, int k, const GraphBuffers &g, cudaStream_t st) {
+int launch_build_edges(int kw, const uint32_t *slots, uint64_t cap, int k, const GraphBuffers &g, cudaStream_t st) {
   if (!g.n_nodes) return 0;
-  u32 max_probe = (u32)(cap < 4096 ? cap : 4096);
   unsigned b = blocks_for(g.n_nodes, 256);
-  if (kw == 1)
-    k_build_edges<1><<<b, 256, 0, st>>>(Table<1>{(Slot1 *)slots, cap, max_probe}, k, (const u64 *)g.node_lo,
-                                        (const u64 *)g.node_hi, g.node_raw, g.n_nodes, g.node_edges, g.uniq);
-  else
-    k_build_edges<2><<<b, 256, 0, st>>>(Table<2>{(Slot2 *)slots, cap, max_probe}, k, (const u64 *)g.node_lo,
-                                        (const u64 *)g.node_hi, g.node_raw, g.n_nodes, g.node_edges, g.uniq);
+  NodeIndex ix{slots, (const u64 *)g.node_lo, kw == 2 ? (const u64 *)g.node_hi : nullptr, cap};
+  if (kw == 1) k_build_edges<1><<<b, 256, 0, st>>>(ix, k, g.node_raw, g.n_nodes, g.node_edges, g.uniq);
+  else k_build_edges<2><<<b, 256, 0, st>>>(ix, k, g.node_raw, g.n_nodes, g.node_edges, g.uniq);
   return 1;
 }
 
@@ -475,28 +457,28 @@ int launch_rank_mark(const GraphBuffers &g, const uint8_t *circ, cudaStream_t st
   return 1;
 }
 size_t rank_splitter_bytes() { return 4 + 8 + 4 + 4 + 2 * sizeof(WyState); }
-int launch_rank_lists(const GraphBuffers &g, const uint8_t *circ, uint32_t ns, void *work, cudaStream_t st) {
+int launch_rank_lists(const GraphBuffers &g, const uint8_t *circ, uint32_t ns_cap, void *work, cudaStream_t st) {
   u32 ne = 2 * g.n_nodes;
-  if (!ne || !ns) return 0;
+  if (!ne || !ns_cap) return 0;
   // carve the per-splitter work area (16-byte aligned pieces first)
-  WyState *sa = (WyState *)work, *sb = sa + ns;
-  u64 *sub_sum = (u64 *)(sb + ns);
-  u32 *sub_len = (u32 *)(sub_sum + ns), *last_elem = sub_len + ns, *next_elem = last_elem + ns;
-  int n = 0;
-  k_rank_walk<<<blocks_for(ns, 128), 128, 0, st>>>(g.succ, circ, g.node_count, g.splitters, ns, (u64 *)g.pd, sub_len,
-                                                   sub_sum, last_elem, next_elem); ++n;
-  k_rank_link<<<blocks_for(ns, 256), 256, 0, st>>>(g.succ, circ, g.splitters, ns, (const u64 *)g.pd, sub_len, sub_sum,
-                                                   next_elem, sa); ++n;
-  int rounds = 1;
-  for (u64 d = 1; d < (u64)ns; d *= 2) ++rounds;
-  for (int r = 0; r < rounds; ++r) {
-    k_rank_wyllie<<<blocks_for(ns, 256), 256, 0, st>>>(sa, sb, ns); ++n;
-    WyState *t = sa; sa = sb; sb = t;
+  WyState *sa = (WyState *)work, *sb = sa + ns_cap;
+  u64 *sub_sum = (u64 *)(sb + ns_cap);
+  u32 *sub_len = (u32 *)(sub_sum + ns_cap), *last_elem = sub_len + ns_cap, *next_elem = last_elem + ns_cap;
+  k_rank_walk<<<blocks_for(ns_cap, 128), 128, 0, st>>>(g.succ, circ, g.node_count, g.splitters, g.scal + 4, ns_cap, (u64 *)g.pd,
+                                                       sub_len, sub_sum, last_elem, next_elem);
+  // one resident wave of CTAs for the cooperative launch
+  static int occ_cache[SHK_MAX_DEVICES] = {0};
+  int &occ = occ_cache[current_device_slot()];
+  if (!occ) {
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_rank_solve, 256, 0) != cudaSuccess || occ < 1) { cudaGetLastError(); occ = 1; }
+    if (occ > 4) occ = 4;
   }
-  k_rank_finish<<<blocks_for(ns, 256), 256, 0, st>>>(sa, g.splitters, ns, sub_len, sub_sum, last_elem, next_elem,
-                                                     g.tail_of, g.len_of, (u64 *)g.sum_of); ++n;
-  k_rank_apply<<<blocks_for(ne, 256), 256, 0, st>>>(sa, g.splitters, ne, (u64 *)g.pd, g.scal + 1); ++n;
-  return n;
+  unsigned grid = (unsigned)std::min<uint64_t>((uint64_t)sm_count() * occ, blocks_for(ne, 256));
+  RankSolveArgs a{g.succ, circ, g.splitters, g.scal + 4, ns_cap, (u64 *)g.pd, ne, sub_len, sub_sum, last_elem, next_elem,
+                  sa, sb, g.tail_of, g.len_of, (u64 *)g.sum_of, g.scal + 1, g.scal + 10, g.scal + 5};
+  void *args[] = {&a};
+  cudaLaunchCooperativeKernel((void *)k_rank_solve, dim3(grid), dim3(256), args, 0, st);
+  return 2;
 }
 int launch_cycle_cut(const GraphBuffers &g, uint32_t n_cyclic, cudaStream_t st) {
   u32 ne = 2 * g.n_nodes;
@@ -536,21 +518,19 @@ int launch_unitig_emit(int kw, const GraphBuffers &g, int k, cudaStream_t st) {
                                                           ne, k, g.seq, g.elem_unitig);
   return 1;
 }
-int launch_unitig_links_out(int kw, void *slots, uint64_t cap, int k, const GraphBuffers &g, uint32_t n_unitigs,
+int launch_unitig_links_out(int kw, const uint32_t *slots, uint64_t cap, int k, const GraphBuffers &g, uint32_t unitig_bound,
                             cudaStream_t st) {
-  if (!n_unitigs) return 0;
-  u32 max_probe = (u32)(cap < 4096 ? cap : 4096);
-  unsigned b = blocks_for(2ull * n_unitigs, 256);
+  if (!unitig_bound) return 0;
+  unsigned b = blocks_for(2ull * unitig_bound, 256);
+  NodeIndex ix{slots, (const u64 *)g.node_lo, kw == 2 ? (const u64 *)g.node_hi : nullptr, cap};
   if (kw == 1)
-    k_unitig_links_out<1><<<b, 256, 0, st>>>(Table<1>{(Slot1 *)slots, cap, max_probe}, k, (const UnitigRec *)g.recs,
-                                             n_unitigs, g.tail_of, g.unitig_of_head, (const u64 *)g.node_lo,
-                                             (const u64 *)g.node_hi, g.node_edges, g.ucirc, g.link_from, g.link_to,
-                                             g.link_cap, g.scal + 3);
+    k_unitig_links_out<1><<<b, 256, 0, st>>>(ix, k, (const UnitigRec *)g.recs, g.scal + 2, g.tail_of, g.unitig_of_head,
+                                             (const u64 *)g.node_lo, (const u64 *)g.node_hi, g.node_edges, g.ucirc,
+                                             g.link_from, g.link_to, g.link_cap, g.scal + 3);
   else
-    k_unitig_links_out<2><<<b, 256, 0, st>>>(Table<2>{(Slot2 *)slots, cap, max_probe}, k, (const UnitigRec *)g.recs,
-                                             n_unitigs, g.tail_of, g.unitig_of_head, (const u64 *)g.node_lo,
-                                             (const u64 *)g.node_hi, g.node_edges, g.ucirc, g.link_from, g.link_to,
-                                             g.link_cap, g.scal + 3);
+    k_unitig_links_out<2><<<b, 256, 0, st>>>(ix, k, (const UnitigRec *)g.recs, g.scal + 2, g.tail_of, g.unitig_of_head,
+                                             (const u64 *)g.node_lo, (const u64 *)g.node_hi, g.node_edges, g.ucirc,
+                                             g.link_from, g.link_to, g.link_cap, g.scal + 3);
   return 1;
 }
 
@@ -583,7 +563,7 @@ int launch_count_buckets(int kw, const void *recs, const uint64_t *bstat, uint32
                          uint16_t *node_count, uint8_t *node_raw, uint32_t node_cap, uint32_t *n_nodes,
                          uint64_t *counters, cudaStream_t st) {
   if (group_start && g_end <= g_begin) return 0;
-  SelfPlan sp{0, 1, 0, 1, nullptr, nullptr, 1};
+  SelfPlan sp{0, 1, 0, 1, nullptr, nullptr, 1, 0};
   if (!group_start) {
     if (!self_plan || !self_plan->n_buckets) return 0;
     u32 rq = (u32)(self_plan->ratio * 65536.0 + 0.5);
@@ -592,7 +572,8 @@ int launch_count_buckets(int kw, const void *recs, const uint64_t *bstat, uint32
     while (chunk < SHK_CB_MAXC && (u64)chunk * 2 * 8 * (u64)count_ctas(kw) <= self_plan->n_buckets) chunk *= 2;
     const u32 spb = self_plan->seg_per_bucket ? self_plan->seg_per_bucket : 1u;
     if (spb > SHK_CB_MAXC) return 0;
-    sp = SelfPlan{self_plan->n_buckets, chunk, rq < 1 ? 1u : rq, bq < 1 ? 1ull : bq, self_plan->stats, (u64 *)self_plan->nrec, spb};
+    sp = SelfPlan{self_plan->n_buckets, chunk, rq < 1 ? 1u : (rq > 65536u ? 65536u : rq), bq < 1 ? 1ull : bq, self_plan->stats, (u64 *)self_plan->nrec, spb,
+                  self_plan->cold ? 1u : 0u};
   }
   static bool attr_done[SHK_MAX_DEVICES] = {false};     // function attributes belong to the device's context
   bool &attr_set = attr_done[current_device_slot()];
@@ -752,12 +733,11 @@ int launch_shard_segments(const uint64_t *d_fill, uint32_t nb, uint32_t world, c
   return 2;
 }
 
-int launch_index_nodes(int kw, void *slots, uint64_t cap, const uint64_t *node_lo, const uint64_t *node_hi, uint32_t n_nodes,
+int launch_index_nodes(int kw, uint32_t *slots, uint64_t cap, const uint64_t *node_lo, const uint64_t *node_hi, uint32_t n_nodes,
                        uint32_t *overflow, cudaStream_t st) {
   if (!n_nodes) return 0;
-  u32 mp = (u32)(cap < 4096 ? cap : 4096);
-  if (kw == 1) k_index_nodes<1><<<blocks_for(n_nodes, 256), 256, 0, st>>>(Table<1>{(Slot1 *)slots, cap, mp}, (const u64 *)node_lo, (const u64 *)node_hi, n_nodes, overflow);
-  else k_index_nodes<2><<<blocks_for(n_nodes, 256), 256, 0, st>>>(Table<2>{(Slot2 *)slots, cap, mp}, (const u64 *)node_lo, (const u64 *)node_hi, n_nodes, overflow);
+  if (kw == 1) k_index_nodes<1><<<blocks_for(n_nodes, 256), 256, 0, st>>>(slots, cap, (const u64 *)node_lo, (const u64 *)node_hi, n_nodes, overflow);
+  else k_index_nodes<2><<<blocks_for(n_nodes, 256), 256, 0, st>>>(slots, cap, (const u64 *)node_lo, (const u64 *)node_hi, n_nodes, overflow);
   return 1;
 }
 

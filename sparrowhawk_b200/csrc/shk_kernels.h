@@ -18,7 +18,8 @@ struct GraphBuffers {
   // unitigs
   void *recs; uint8_t *ucirc; uint64_t *cov_sum; char *seq;
   uint32_t *link_from, *link_to; uint32_t link_cap;
-  // device scalars: [1] n_cyclic, [2] n_unitigs, [3] n_links, [4] n_splitters ; [8..9] seq cursor
+  // device scalars: [1] n_cyclic, [2] n_unitigs, [3] n_links, [4] n_splitters, [5] splitter work area too small,
+  // [8..9] seq cursor (u64), [10..12] round flags of k_rank_solve
   uint32_t *scal; uint64_t *seq_cursor;
 };
 
@@ -32,18 +33,21 @@ int launch_table_fill(void *slots, uint64_t cap, int kw, cudaStream_t st);
 int launch_histogram_filter(int kw, void *slots, uint64_t cap, int min_count, uint64_t *histo,
                             uint64_t *node_lo, uint64_t *node_hi, uint16_t *node_count, uint8_t *node_raw,
                             uint32_t node_cap, uint32_t *n_nodes, cudaStream_t st);
-int launch_build_edges(int kw, void *slots, uint64_t cap, int k, const GraphBuffers &g, cudaStream_t st);
+// node index (shk_index.cuh): slots = u32[cap], pre-filled with 0xFF
+int launch_build_edges(int kw, const uint32_t *slots, uint64_t cap, int k, const GraphBuffers &g, cudaStream_t st);
 int launch_unitig_links(const GraphBuffers &g, cudaStream_t st);
-// K5 (shk_rank.cuh): mark counts the splitters into scal[4]; after reading that number the host sizes
-// `work` (rank_splitter_bytes() per splitter) and launches the rest.  circ may be null (first pass).
+// K5 (shk_rank.cuh): mark counts the splitters into scal[4] and the host never reads that number: `work` holds
+// ns_cap splitters (rank_splitter_bytes() each), the kernels read the count from scal[4] and set scal[5] when it
+// exceeds ns_cap (the host checks the flag with the other scalars at the end of the graph stage and runs again with
+// a larger work area).  circ may be null (first pass).
 int launch_rank_mark(const GraphBuffers &g, const uint8_t *circ, cudaStream_t st);
 size_t rank_splitter_bytes();
-int launch_rank_lists(const GraphBuffers &g, const uint8_t *circ, uint32_t n_splitters, void *work, cudaStream_t st);
+int launch_rank_lists(const GraphBuffers &g, const uint8_t *circ, uint32_t ns_cap, void *work, cudaStream_t st);
 int launch_cycle_cut(const GraphBuffers &g, uint32_t n_cyclic, cudaStream_t st);
 int launch_unitig_heads(const GraphBuffers &g, int k, bool have_circ, cudaStream_t st);
 int launch_unitig_emit(int kw, const GraphBuffers &g, int k, cudaStream_t st);
-int launch_unitig_links_out(int kw, void *slots, uint64_t cap, int k, const GraphBuffers &g,
-                            uint32_t n_unitigs, cudaStream_t st);
+int launch_unitig_links_out(int kw, const uint32_t *slots, uint64_t cap, int k, const GraphBuffers &g,
+                            uint32_t unitig_bound /* grid size; the count is read from scal[2] */, cudaStream_t st);
 size_t unitig_rec_bytes();
 
 // two-pass counting: K1a minimizer partition into super-k-mer records, K1b shared-memory count + sweep
@@ -60,7 +64,8 @@ int partition_tile_words();
 // group_start == null: the CTAs cut their own groups (steady-state runs).  stats (device, zeroed by the caller):
 // [0] largest bucket fill, [1] most distinct items in a group; *nrec (device, zeroed): records counted.
 // seg_per_bucket: 0/1 = one segment per bucket; W = the sharded path (bucket j = segments j*W .. j*W+W-1, bstat = totals)
-struct SelfPlanArgs { uint32_t n_buckets; double ratio; double budget; uint32_t *stats; uint64_t *nrec; uint32_t seg_per_bucket; };
+struct SelfPlanArgs { uint32_t n_buckets; double ratio; double budget; uint32_t *stats; uint64_t *nrec; uint32_t seg_per_bucket;
+                      bool cold /* no ratio known yet: the CTAs measure it on their first groups */; };
 // seg_off / seg_cnt (nullable): explicit record segments (sharded path); null = segment i is local bucket region i
 int launch_count_buckets(int kw, const void *recs, const uint64_t *bstat, uint32_t rcap, const uint64_t *seg_off,
                          const uint32_t *seg_cnt, void *uq_rec /* nullable: per-CTA distinct-record lists (de-dup) */,
@@ -81,7 +86,7 @@ int launch_shard_send_plan(const uint64_t *d_fill, uint32_t rcap, uint32_t world
 int shard_max_world();
 int launch_shard_segments(const uint64_t *d_fill, uint32_t nb, uint32_t world, const uint64_t *src_base /* host, [world] */,
                           uint64_t *seg_off, uint32_t *seg_cnt, uint64_t *bucket_tot, cudaStream_t st);
-int launch_index_nodes(int kw, void *slots, uint64_t cap, const uint64_t *node_lo, const uint64_t *node_hi, uint32_t n_nodes,
+int launch_index_nodes(int kw, uint32_t *slots, uint64_t cap, const uint64_t *node_lo, const uint64_t *node_hi, uint32_t n_nodes,
                        uint32_t *overflow, cudaStream_t st);
 
 }  // namespace shk

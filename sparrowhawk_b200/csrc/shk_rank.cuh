@@ -22,7 +22,11 @@
 // cycle kernels in shk_kernels.cu and the ranking is simply run again with the
 // cut element as a forced head (circ[e] == 2; succ itself is never modified).
 #pragma once
+#include <cooperative_groups.h>
+
 #include "shk_device.cuh"
+
+namespace cg = cooperative_groups;
 
 namespace shk {
 
@@ -67,10 +71,11 @@ k_rank_mark(const u32 *__restrict__ succ, const uint8_t *__restrict__ circ, u32 
 __global__ void __launch_bounds__(128)
 k_rank_walk(const u32 *__restrict__ succ, const uint8_t *__restrict__ circ,
             const uint16_t *__restrict__ node_count, const u32 *__restrict__ splitters,
-            u32 n_splitters, u64 *__restrict__ loc, u32 *__restrict__ sub_len, u64 *__restrict__ sub_sum,
-            u32 *__restrict__ last_elem, u32 *__restrict__ next_elem) {
+            const u32 *__restrict__ n_splitters_dev, u32 ns_cap, u64 *__restrict__ loc, u32 *__restrict__ sub_len,
+            u64 *__restrict__ sub_sum, u32 *__restrict__ last_elem, u32 *__restrict__ next_elem) {
   const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n_splitters) return;
+  const u32 n_splitters = *n_splitters_dev;               // counted by k_rank_mark; the host never reads it
+  if (n_splitters > ns_cap || i >= n_splitters) return;   // more splitters than the work area holds: k_rank_solve flags it
   u32 cur = splitters[i], r = 0, nxt;
   u64 sum = 0;
   for (;;) {
@@ -86,75 +91,98 @@ k_rank_walk(const u32 *__restrict__ succ, const uint8_t *__restrict__ circ,
   sub_len[i] = r + 1; sub_sum[i] = sum; last_elem[i] = cur; next_elem[i] = nxt;
 }
 
-// splitter-level list: state[j] = (pred splitter, elements before j inside pred's sublist, their count sum)
-__global__ void __launch_bounds__(256)
-k_rank_link(const u32 *__restrict__ succ, const uint8_t *__restrict__ circ, const u32 *__restrict__ splitters,
-            u32 n_splitters, const u64 *__restrict__ loc, const u32 *__restrict__ sub_len,
-            const u64 *__restrict__ sub_sum, const u32 *__restrict__ next_elem, WyState *__restrict__ state) {
-  const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n_splitters) return;
-  if (rank_is_head(succ, circ, splitters[i])) state[i] = WyState{i, 0u, 0ull};
-  const u32 t = next_elem[i];
-  if (t != SHK_NONE) {
-    const u32 j = (u32)(loc[t] >> 32);
-    state[j] = WyState{i, sub_len[i], sub_sum[i]};
-  }
-}
-
-__global__ void __launch_bounds__(256)
-k_rank_wyllie(const WyState *__restrict__ in, WyState *__restrict__ out, u32 n_splitters) {
-  const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n_splitters) return;
-  WyState v = in[i];
-  if (v.ptr != i) {
-    const WyState vp = in[v.ptr];
-    if (vp.ptr != v.ptr) { v.ptr = vp.ptr; v.dist += vp.dist; v.sum += vp.sum; }
-  }
-  out[i] = v;
-}
+// ---- splitter level, one cooperative launch -------------------------------------------------
+// link:   the splitter-level list, state[j] = (pred splitter, elements before j inside pred's sublist, their count sum)
+// jump:   Wyllie pointer jumping on the splitters, ping-pong between two state arrays, until a round changes
+//         nothing (at most ceil(log2 n) + 1 rounds: splitter-level cycles never settle, and do not have to)
+// finish: list tails tell their head the length, the tail element and the count sum
+// apply:  loc[e] -> pd[e] in place; elements on unbranched cycles get ~0 and are counted
+// Phases are separated by grid-wide barriers (cooperative launch, one resident wave of CTAs), so the 20-odd tiny
+// launches and the host round trip that sized them are gone: the splitter count is read from device memory.
+struct RankSolveArgs {
+  const u32 *succ; const uint8_t *circ; const u32 *splitters; const u32 *n_splitters; u32 ns_cap;
+  u64 *pd; u32 n_elems;
+  const u32 *sub_len; const u64 *sub_sum; const u32 *last_elem; const u32 *next_elem;
+  WyState *sa, *sb;
+  u32 *tail_of, *len_of; u64 *sum_of;
+  u32 *n_cyclic; u32 *changed /* [3] round flags, rotating */; u32 *overflow /* set when n_splitters > ns_cap */;
+};
 
 __device__ __forceinline__ bool wy_true_head(const WyState *st, u32 p) {
   const WyState v = st[p];
   return v.ptr == p && v.dist == 0;
 }
 
-// list tails tell their head the length, the tail element and the count sum
 __global__ void __launch_bounds__(256)
-k_rank_finish(const WyState *__restrict__ state, const u32 *__restrict__ splitters, u32 n_splitters,
-              const u32 *__restrict__ sub_len, const u64 *__restrict__ sub_sum, const u32 *__restrict__ last_elem,
-              const u32 *__restrict__ next_elem, u32 *__restrict__ tail_of, u32 *__restrict__ len_of,
-              u64 *__restrict__ sum_of) {
-  const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n_splitters || next_elem[i] != SHK_NONE) return;
-  const WyState v = state[i];
-  if (!wy_true_head(state, v.ptr)) return;
-  const u32 h = splitters[v.ptr];
-  tail_of[h] = last_elem[i];
-  len_of[h] = v.dist + sub_len[i];
-  sum_of[h] = v.sum + sub_sum[i];
-}
-
-// loc[e] -> pd[e] in place.  Elements on unbranched cycles get ~0 and are counted.
-__global__ void __launch_bounds__(256)
-k_rank_apply(const WyState *__restrict__ state, const u32 *__restrict__ splitters, u32 n_elems,
-             u64 *__restrict__ pd, u32 *__restrict__ n_cyclic) {
-  const u32 e = blockIdx.x * blockDim.x + threadIdx.x;
-  bool cyc = false;
-  if (e < n_elems) {
-    const u64 L = pd[e];
-    cyc = true;
-    if (L != ~0ull) {
-      const WyState v = state[(u32)(L >> 32)];
-      if (wy_true_head(state, v.ptr)) {
-        pd[e] = ((u64)splitters[v.ptr] << 32) | (u64)(v.dist + (u32)L);
-        cyc = false;
-      } else {
-        pd[e] = ~0ull;
-      }
+k_rank_solve(RankSolveArgs a) {
+  cg::grid_group grid = cg::this_grid();
+  const u32 tid = blockIdx.x * blockDim.x + threadIdx.x, nthr = gridDim.x * blockDim.x;
+  const u32 ns = *a.n_splitters;
+  if (ns > a.ns_cap) {                                     // uniform across the grid: nobody reaches a barrier
+    if (tid == 0) atomicExch(a.overflow, 1u);
+    return;
+  }
+  // ---- link ----
+  for (u32 i = tid; i < ns; i += nthr) {
+    if (rank_is_head(a.succ, a.circ, a.splitters[i])) a.sa[i] = WyState{i, 0u, 0ull};
+    const u32 t = a.next_elem[i];
+    if (t != SHK_NONE) {
+      const u32 j = (u32)(a.pd[t] >> 32);
+      a.sa[j] = WyState{i, a.sub_len[i], a.sub_sum[i]};
     }
   }
-  const u32 ball = __ballot_sync(0xffffffffu, cyc);
-  if (ball && (threadIdx.x & 31) == 0) atomicAdd(n_cyclic, (u32)__popc(ball));
+  if (tid == 0) { a.changed[0] = 0; a.changed[1] = 0; a.changed[2] = 0; }
+  grid.sync();
+  // ---- jump ----
+  WyState *in = a.sa, *out = a.sb;
+  u32 max_rounds = 2;
+  for (u32 d = 1; d < ns; d <<= 1) ++max_rounds;
+  for (u32 r = 0; r < max_rounds; ++r) {
+    bool ch = false;
+    for (u32 i = tid; i < ns; i += nthr) {
+      WyState v = in[i];
+      if (v.ptr != i) {
+        const WyState vp = in[v.ptr];
+        if (vp.ptr != v.ptr) { v.ptr = vp.ptr; v.dist += vp.dist; v.sum += vp.sum; ch = true; }
+      }
+      out[i] = v;
+    }
+    if (ch) a.changed[r % 3] = 1u;
+    grid.sync();
+    const bool any = *reinterpret_cast<volatile u32 *>(a.changed + r % 3) != 0;
+    if (tid == 0) a.changed[(r + 2) % 3] = 0;              // the flag of round r + 2 (last read after the previous barrier)
+    WyState *t = in; in = out; out = t;
+    if (!any) break;                                        // `in` and `out` now hold the same, final state
+  }
+  const WyState *st = in;
+  // ---- finish ----
+  for (u32 i = tid; i < ns; i += nthr) {
+    if (a.next_elem[i] != SHK_NONE) continue;
+    const WyState v = st[i];
+    if (!wy_true_head(st, v.ptr)) continue;
+    const u32 h = a.splitters[v.ptr];
+    a.tail_of[h] = a.last_elem[i];
+    a.len_of[h] = v.dist + a.sub_len[i];
+    a.sum_of[h] = v.sum + a.sub_sum[i];
+  }
+  // ---- apply ----
+  u32 ncyc = 0;
+  for (u32 e = tid; e < a.n_elems; e += nthr) {
+    const u64 L = a.pd[e];
+    bool cyc = true;
+    if (L != ~0ull) {
+      const WyState v = st[(u32)(L >> 32)];
+      if (wy_true_head(st, v.ptr)) {
+        a.pd[e] = ((u64)a.splitters[v.ptr] << 32) | (u64)(v.dist + (u32)L);
+        cyc = false;
+      } else {
+        a.pd[e] = ~0ull;
+      }
+    }
+    ncyc += cyc ? 1u : 0u;
+  }
+  for (int o = 16; o; o >>= 1) ncyc += __shfl_xor_sync(0xffffffffu, ncyc, o);
+  if ((threadIdx.x & 31) == 0 && ncyc) atomicAdd(a.n_cyclic, ncyc);
 }
 
 }  // namespace shk
