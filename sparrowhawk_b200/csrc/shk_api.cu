@@ -482,7 +482,8 @@ static uint64_t region_records_guess(uint64_t positions, uint32_t P, int kw, int
   // records per bucket: a run holds ~ (w+1)/2 k-mers for a window of w = k-m+1 m-mers
   const int mlen = k < 11 ? k : 11, w = k - mlen + 1;
   const double avg_run = std::min<double>(records_max_run(kw, k), std::max(1.0, (w + 1) / 2.0 * 0.6));
-  return (uint64_t)(3.0 * (double)positions / avg_run / (double)P) + 64;
+  // x 4.5: at high coverage a bucket holds a handful of genome loci times the coverage, so fills scatter widely
+  return (uint64_t)(4.5 * (double)positions / avg_run / (double)P) + 64;
 }
 
 // What K1a -> K1b back to back needs to know before anything has run: bucket count and region size from the
@@ -702,11 +703,12 @@ static shk_status filter_impl(shk_asm *h, int min_count, bool histogram_only = f
 static shk_status index_impl(shk_asm *h, uint64_t icap) {
   const uint32_t nn = (uint32_t)h->st.n_nodes;
   if (!icap) icap = std::max<uint64_t>(64, 2ull * nn);
-  SHK_TRY(h->slots.ensure(icap * 4));
+  SHK_TRY(h->slots.ensure(icap * 8));
   h->cap = icap;
-  SHK_CUDA(cudaMemsetAsync(h->slots.p, 0xFF, icap * 4, h->stream));
+  h->index_P = h->P ? h->P : 1;                        // the buckets the nodes were counted in (any power of two is valid)
+  SHK_CUDA(cudaMemsetAsync(h->slots.p, 0xFF, icap * 8, h->stream));
   SHK_CUDA(cudaMemsetAsync(d_flags(h) + 7, 0, 4, h->stream));
-  h->st.gpu_launches += launch_index_nodes(h->kw, h->slots.as<uint32_t>(), icap, h->node_lo.as<uint64_t>(), h->node_hi.as<uint64_t>(), nn,
+  h->st.gpu_launches += launch_index_nodes(h->kw, h->slots.as<uint64_t>(), icap, h->index_P, h->p.k, h->node_lo.as<uint64_t>(), h->node_hi.as<uint64_t>(), nn,
                                            d_flags(h) + 7, h->stream);
   SHK_CUDA(cudaGetLastError());
   SHK_CUDA(cudaEventRecord(h->ev[5], h->stream));
@@ -789,7 +791,7 @@ static shk_status graph_impl(shk_asm *h) {
   auto emit_pass = [&](bool have_circ) -> shk_status {
     L += launch_unitig_heads(g, k, have_circ, h->stream);
     L += launch_unitig_emit(h->kw, g, k, h->stream);
-    L += launch_unitig_links_out(h->kw, h->slots.as<uint32_t>(), h->cap, k, g, std::min(N, ns_cap), h->stream);
+    L += launch_unitig_links_out(h->kw, h->slots.as<uint64_t>(), h->cap, h->index_P, k, g, std::min(N, ns_cap), h->stream);
     SHK_CUDA(cudaGetLastError());
     SHK_CUDA(cudaEventRecord(h->ev[7], h->stream));
     return SHK_OK;
@@ -797,7 +799,7 @@ static shk_status graph_impl(shk_asm *h) {
   for (int attempt = 0;; ++attempt) {
     if (attempt > 4) { set_error("graph stage did not settle after retries"); return SHK_ERR_STATE; }
     SHK_CUDA(cudaMemsetAsync(h->tail_of.p, 0xFF, ne * 4, h->stream));
-    L += launch_build_edges(h->kw, h->slots.as<uint32_t>(), h->cap, k, g, h->stream);
+    L += launch_build_edges(h->kw, h->slots.as<uint64_t>(), h->cap, h->index_P, k, g, h->stream);
     L += launch_unitig_links(g, h->stream);
     SHK_TRY(rank_pass(nullptr));
     SHK_TRY(emit_pass(false));
@@ -837,7 +839,7 @@ static shk_status graph_impl(shk_asm *h) {
     SHK_TRY(h->link_from.ensure((size_t)link_cap * 4)); SHK_TRY(h->link_to.ensure((size_t)link_cap * 4));
     g.link_from = h->link_from.as<uint32_t>(); g.link_to = h->link_to.as<uint32_t>(); g.link_cap = link_cap;
     SHK_CUDA(cudaMemsetAsync(g.scal + 3, 0, 4, h->stream));
-    L += launch_unitig_links_out(h->kw, h->slots.as<uint32_t>(), h->cap, k, g, nu, h->stream);
+    L += launch_unitig_links_out(h->kw, h->slots.as<uint64_t>(), h->cap, h->index_P, k, g, nu, h->stream);
     SHK_CUDA(cudaGetLastError());
     SHK_CUDA(cudaEventRecord(h->ev[7], h->stream));
     SHK_TRY(read_back());

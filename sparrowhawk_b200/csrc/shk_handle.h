@@ -132,6 +132,7 @@ struct shk_asm {
   // ---- node index (key -> node id) for the graph stage ----
   shk::DevBuf slots;
   uint64_t cap = 0;
+  uint32_t index_P = 1;         // bucket count the index regions follow (shk_index.cuh)
   bool table_live = false;
   // ---- device scalars: counters[0]=n_bases [1]=n_instances [2]=n_distinct ; histo[500]
   shk::DevBuf dscal;            // u64 counters[8] | u64 histo[500] | u32 flags[8]

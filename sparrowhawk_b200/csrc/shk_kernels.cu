@@ -137,15 +137,6 @@ k_histogram_filter(Table<KW> tbl, int min_count, u64 *__restrict__ histo /*[500]
 // the unique neighbour (node id << 1 | arrival side) when exactly one edge
 // survives.
 // =====================================================================
-// first probe already in flight: `id` = content of slot i.  Confirms against the key arrays, walks on after a collision.
-template <int KW>
-__device__ __forceinline__ u32 index_resolve(const NodeIndex &ix, typename KeyOf<KW>::type Y, u64 i, u32 id, u64 klo, u64 khi) {
-  if (id == SHK_NONE) return SHK_NONE;
-  if (klo == (u64)Y && (KW == 1 || khi == (u64)((u128)Y >> 64))) return id;
-  if (++i == ix.cap) i = 0;
-  return index_find_from<KW>(ix, Y, i, __ldcg(ix.slots + i));
-}
-
 template <int KW>
 __global__ void __launch_bounds__(256)
 k_build_edges(NodeIndex ix, int k, const uint8_t *__restrict__ node_raw, u32 n_nodes, uint8_t *__restrict__ node_edges,
@@ -157,25 +148,23 @@ k_build_edges(NodeIndex ix, int k, const uint8_t *__restrict__ node_raw, u32 n_n
   if (KW == 2) X |= (K)((u128)ix.hi[n] << 64);
   u32 raw = __ldcs(node_raw + n), valid = 0;
   u32 un[2] = {SHK_NONE, SHK_NONE};
-  // The lookups of a node are independent random accesses into the index: take the set bits two at a time so that
-  // both slot loads, then both key loads, are in flight together (a unitig-interior node has exactly two, one per side).
+  // The lookups of a node are independent: take the set bits two at a time so that both first probes are in
+  // flight together (a unitig-interior node has exactly two, one per side).
   u32 rem = raw;
   while (rem) {
     const int b0 = __ffs(rem) - 1; rem &= rem - 1;
     const int b1 = rem ? __ffs(rem) - 1 : -1; if (b1 >= 0) rem &= rem - 1;
     int s0, s1 = 0;
+    u32 f0, f1 = 0;
     const K Y0 = neighbour_key(X, k, b0 >> 2, (u32)(b0 & 3), s0);
-    const u64 i0 = slot_of(hash_key(Y0), ix.cap);
+    const u64 i0 = index_home(ix, Y0, f0);
     K Y1 = 0; u64 i1 = 0;
-    if (b1 >= 0) { Y1 = neighbour_key(X, k, b1 >> 2, (u32)(b1 & 3), s1); i1 = slot_of(hash_key(Y1), ix.cap); }
-    const u32 c0 = __ldcg(ix.slots + i0), c1 = b1 >= 0 ? __ldcg(ix.slots + i1) : SHK_NONE;
-    u64 l0 = 0, l1 = 0, h0 = 0, h1 = 0;
-    if (c0 != SHK_NONE) { l0 = __ldcg(ix.lo + c0); if (KW == 2) h0 = __ldcg(ix.hi + c0); }
-    if (c1 != SHK_NONE) { l1 = __ldcg(ix.lo + c1); if (KW == 2) h1 = __ldcg(ix.hi + c1); }
-    const u32 id0 = index_resolve<KW>(ix, Y0, i0, c0, l0, h0);
+    if (b1 >= 0) { Y1 = neighbour_key(X, k, b1 >> 2, (u32)(b1 & 3), s1); i1 = index_home(ix, Y1, f1); }
+    const u64 v0 = __ldcg(ix.slots + i0), v1 = b1 >= 0 ? __ldcg(ix.slots + i1) : SHK_INDEX_EMPTY;
+    const u32 id0 = index_find_from<KW>(ix, Y0, f0, i0, v0);
     if (id0 != SHK_NONE) { valid |= 1u << b0; un[b0 >> 2] = (id0 << 1) | (u32)s0; }
     if (b1 >= 0) {
-      const u32 id1 = index_resolve<KW>(ix, Y1, i1, c1, l1, h1);
+      const u32 id1 = index_find_from<KW>(ix, Y1, f1, i1, v1);
       if (id1 != SHK_NONE) { valid |= 1u << b1; un[b1 >> 2] = (id1 << 1) | (u32)s1; }
     }
   }
@@ -435,10 +424,10 @@ int launch_histogram_filter(int kw, void *slots, uint64_t cap, int min_count, ui
   return 1;
 }
 
-int launch_build_edges(int kw, const uint32_t *slots, uint64_t cap, int k, const GraphBuffers &g, cudaStream_t st) {
+int launch_build_edges(int kw, const uint64_t *slots, uint64_t cap, uint32_t P, int k, const GraphBuffers &g, cudaStream_t st) {
   if (!g.n_nodes) return 0;
   unsigned b = blocks_for(g.n_nodes, 256);
-  NodeIndex ix{slots, (const u64 *)g.node_lo, kw == 2 ? (const u64 *)g.node_hi : nullptr, cap};
+  NodeIndex ix{(const u64 *)slots, (const u64 *)g.node_lo, kw == 2 ? (const u64 *)g.node_hi : nullptr, cap, P, k};
   if (kw == 1) k_build_edges<1><<<b, 256, 0, st>>>(ix, k, g.node_raw, g.n_nodes, g.node_edges, g.uniq);
   else k_build_edges<2><<<b, 256, 0, st>>>(ix, k, g.node_raw, g.n_nodes, g.node_edges, g.uniq);
   return 1;
@@ -471,14 +460,14 @@ int launch_rank_lists(const GraphBuffers &g, const uint8_t *circ, uint32_t ns_ca
   int &occ = occ_cache[current_device_slot()];
   if (!occ) {
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_rank_solve, 256, 0) != cudaSuccess || occ < 1) { cudaGetLastError(); occ = 1; }
-    if (occ > 4) occ = 4;
   }
-  unsigned grid = (unsigned)std::min<uint64_t>((uint64_t)sm_count() * occ, blocks_for(ne, 256));
+  unsigned grid = (unsigned)std::min<uint64_t>((uint64_t)sm_count() * occ, blocks_for(ns_cap, 256));
   RankSolveArgs a{g.succ, circ, g.splitters, g.scal + 4, ns_cap, (u64 *)g.pd, ne, sub_len, sub_sum, last_elem, next_elem,
-                  sa, sb, g.tail_of, g.len_of, (u64 *)g.sum_of, g.scal + 1, g.scal + 10, g.scal + 5};
+                  sa, sb, g.tail_of, g.len_of, (u64 *)g.sum_of, g.scal + 10, g.scal + 5};
   void *args[] = {&a};
   cudaLaunchCooperativeKernel((void *)k_rank_solve, dim3(grid), dim3(256), args, 0, st);
-  return 2;
+  k_rank_apply<<<blocks_for(ne, 256), 256, 0, st>>>(sa, g.splitters, g.scal + 4, ns_cap, ne, (u64 *)g.pd, g.scal + 1);
+  return 3;
 }
 int launch_cycle_cut(const GraphBuffers &g, uint32_t n_cyclic, cudaStream_t st) {
   u32 ne = 2 * g.n_nodes;
@@ -518,11 +507,11 @@ int launch_unitig_emit(int kw, const GraphBuffers &g, int k, cudaStream_t st) {
                                                           ne, k, g.seq, g.elem_unitig);
   return 1;
 }
-int launch_unitig_links_out(int kw, const uint32_t *slots, uint64_t cap, int k, const GraphBuffers &g, uint32_t unitig_bound,
+int launch_unitig_links_out(int kw, const uint64_t *slots, uint64_t cap, uint32_t P, int k, const GraphBuffers &g, uint32_t unitig_bound,
                             cudaStream_t st) {
   if (!unitig_bound) return 0;
   unsigned b = blocks_for(2ull * unitig_bound, 256);
-  NodeIndex ix{slots, (const u64 *)g.node_lo, kw == 2 ? (const u64 *)g.node_hi : nullptr, cap};
+  NodeIndex ix{(const u64 *)slots, (const u64 *)g.node_lo, kw == 2 ? (const u64 *)g.node_hi : nullptr, cap, P, k};
   if (kw == 1)
     k_unitig_links_out<1><<<b, 256, 0, st>>>(ix, k, (const UnitigRec *)g.recs, g.scal + 2, g.tail_of, g.unitig_of_head,
                                              (const u64 *)g.node_lo, (const u64 *)g.node_hi, g.node_edges, g.ucirc,
@@ -733,11 +722,11 @@ int launch_shard_segments(const uint64_t *d_fill, uint32_t nb, uint32_t world, c
   return 2;
 }
 
-int launch_index_nodes(int kw, uint32_t *slots, uint64_t cap, const uint64_t *node_lo, const uint64_t *node_hi, uint32_t n_nodes,
-                       uint32_t *overflow, cudaStream_t st) {
+int launch_index_nodes(int kw, uint64_t *slots, uint64_t cap, uint32_t P, int k, const uint64_t *node_lo, const uint64_t *node_hi,
+                       uint32_t n_nodes, uint32_t *overflow, cudaStream_t st) {
   if (!n_nodes) return 0;
-  if (kw == 1) k_index_nodes<1><<<blocks_for(n_nodes, 256), 256, 0, st>>>(slots, cap, (const u64 *)node_lo, (const u64 *)node_hi, n_nodes, overflow);
-  else k_index_nodes<2><<<blocks_for(n_nodes, 256), 256, 0, st>>>(slots, cap, (const u64 *)node_lo, (const u64 *)node_hi, n_nodes, overflow);
+  if (kw == 1) k_index_nodes<1><<<blocks_for(n_nodes, 256), 256, 0, st>>>((u64 *)slots, cap, P, k, (const u64 *)node_lo, (const u64 *)node_hi, n_nodes, overflow);
+  else k_index_nodes<2><<<blocks_for(n_nodes, 256), 256, 0, st>>>((u64 *)slots, cap, P, k, (const u64 *)node_lo, (const u64 *)node_hi, n_nodes, overflow);
   return 1;
 }
 

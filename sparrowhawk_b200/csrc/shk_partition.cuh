@@ -108,6 +108,27 @@ __device__ __forceinline__ u32 mmer_hash(u32 c) {
   return h;
 }
 
+// The minimizer hash of ONE k-mer (any strand: canonical m-mers make it strand-symmetric): the minimum of
+// mmer_hash over its k-m+1 m-mers — exactly what K1a's sliding window computes for the k-mer at a stream position,
+// so `minimizer_hash_of(key, k) & (P - 1)` is the fine bucket K1a filed the k-mer under.  The graph stage uses it to
+// place and find a node next to the other nodes of its bucket (shk_index.cuh), and the sharded path to name the
+// rank that owns a neighbour k-mer.
+template <class K>
+__device__ __forceinline__ u32 minimizer_hash_of(K key, int k) {
+  const int m = minimizer_len(k), w = k - m + 1, sh = 2 * (m - 1);
+  const u32 mmask = (m == 16) ? 0xFFFFFFFFu : ((1u << (2 * m)) - 1);
+  u32 fw = (u32)(key >> (2 * (k - m))) & mmask;                  // the first m bases
+  u32 rc = revcomp_m(fw, m);
+  u32 best = mmer_hash(min(fw, rc));
+  for (int j = 1; j < w; ++j) {
+    const u32 nb = (u32)(key >> (2 * (k - m - j))) & 3u;
+    fw = ((fw << 2) | nb) & mmask;
+    rc = (rc >> 2) | ((nb ^ 2u) << sh);
+    best = min(best, mmer_hash(min(fw, rc)));
+  }
+  return best;
+}
+
 // in-register sliding minimum of width J over X[0 .. 32+J-2] -> X[0..31]
 template <int J>
 __device__ __forceinline__ void window_min_pow2(const u32 *row, u32 (&R)[32]) {

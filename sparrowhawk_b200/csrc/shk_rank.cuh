@@ -96,7 +96,6 @@ k_rank_walk(const u32 *__restrict__ succ, const uint8_t *__restrict__ circ,
 // jump:   Wyllie pointer jumping on the splitters, ping-pong between two state arrays, until a round changes
 //         nothing (at most ceil(log2 n) + 1 rounds: splitter-level cycles never settle, and do not have to)
 // finish: list tails tell their head the length, the tail element and the count sum
-// apply:  loc[e] -> pd[e] in place; elements on unbranched cycles get ~0 and are counted
 // Phases are separated by grid-wide barriers (cooperative launch, one resident wave of CTAs), so the 20-odd tiny
 // launches and the host round trip that sized them are gone: the splitter count is read from device memory.
 struct RankSolveArgs {
@@ -105,7 +104,7 @@ struct RankSolveArgs {
   const u32 *sub_len; const u64 *sub_sum; const u32 *last_elem; const u32 *next_elem;
   WyState *sa, *sb;
   u32 *tail_of, *len_of; u64 *sum_of;
-  u32 *n_cyclic; u32 *changed /* [3] round flags, rotating */; u32 *overflow /* set when n_splitters > ns_cap */;
+  u32 *changed /* [3] round flags, rotating */; u32 *overflow /* set when n_splitters > ns_cap */;
 };
 
 __device__ __forceinline__ bool wy_true_head(const WyState *st, u32 p) {
@@ -165,24 +164,32 @@ k_rank_solve(RankSolveArgs a) {
     a.len_of[h] = v.dist + a.sub_len[i];
     a.sum_of[h] = v.sum + a.sub_sum[i];
   }
-  // ---- apply ----
-  u32 ncyc = 0;
-  for (u32 e = tid; e < a.n_elems; e += nthr) {
-    const u64 L = a.pd[e];
-    bool cyc = true;
+}
+
+// loc[e] -> pd[e] in place, one thread per element (three dependent loads each: this wants the whole machine, not the
+// one resident wave of k_rank_solve).  Elements on unbranched cycles get ~0 and are counted.  Acyclic lists have
+// settled in both state arrays, so `state` is always the first one.
+__global__ void __launch_bounds__(256)
+k_rank_apply(const WyState *__restrict__ state, const u32 *__restrict__ splitters, const u32 *__restrict__ n_splitters, u32 ns_cap,
+             u32 n_elems, u64 *__restrict__ pd, u32 *__restrict__ n_cyclic) {
+  const u32 e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (*n_splitters > ns_cap) return;                      // flagged by k_rank_solve; the host runs the stage again
+  bool cyc = false;
+  if (e < n_elems) {
+    const u64 L = pd[e];
+    cyc = true;
     if (L != ~0ull) {
-      const WyState v = st[(u32)(L >> 32)];
-      if (wy_true_head(st, v.ptr)) {
-        a.pd[e] = ((u64)a.splitters[v.ptr] << 32) | (u64)(v.dist + (u32)L);
+      const WyState v = state[(u32)(L >> 32)];
+      if (wy_true_head(state, v.ptr)) {
+        pd[e] = ((u64)splitters[v.ptr] << 32) | (u64)(v.dist + (u32)L);
         cyc = false;
       } else {
-        a.pd[e] = ~0ull;
+        pd[e] = ~0ull;
       }
     }
-    ncyc += cyc ? 1u : 0u;
   }
-  for (int o = 16; o; o >>= 1) ncyc += __shfl_xor_sync(0xffffffffu, ncyc, o);
-  if ((threadIdx.x & 31) == 0 && ncyc) atomicAdd(a.n_cyclic, ncyc);
+  const u32 ball = __ballot_sync(0xffffffffu, cyc);
+  if (ball && (threadIdx.x & 31) == 0) atomicAdd(n_cyclic, (u32)__popc(ball));
 }
 
 }  // namespace shk

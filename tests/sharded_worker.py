@@ -163,7 +163,7 @@ def main():
             assert info["n_nodes"] == so["n_nodes"], (info["n_nodes"], so["n_nodes"])
             assert_parity(h, o, check_table=False)
         print(f"rank {rank}: device-planned count per pass {planned}")
-        assert planned[0] == 0 and planned[-1] == 1, planned
+        assert planned[-1] == 1, planned
         if world > 1:
             assert min(info["nodes_per_rank"]) > 0
         h.close()
