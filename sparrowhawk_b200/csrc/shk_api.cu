@@ -461,7 +461,7 @@ static shk_status sweep_overflow(shk_asm *h, int mc_eff, uint32_t node_cap) {
   return read_scalars(h);
 }
 
-static shk_status index_impl(shk_asm *h, uint64_t icap = 0);
+static shk_status index_impl(shk_asm *h);
 // ---- steady-state K1a + K1b: nothing on the host between the two kernels ----------------
 // Preconditions (fast_ready): this handle has run the host-planned path on a read set of this
 // size, so the bucket count, the region size, the distinct/instances ratio and the de-dup list
@@ -698,18 +698,20 @@ static shk_status filter_impl(shk_asm *h, int min_count, bool histogram_only = f
   return index_impl(h);
 }
 
-// node index for the graph stage (shk_index.cuh): key -> node id, one u32 per slot, 2 slots per node.  Only queued:
-// the overflow flag (d_flags[7]; 4096 probes at half load never happen) is read with the graph stage's scalars.
-static shk_status index_impl(shk_asm *h, uint64_t icap) {
+// node index for the graph stage (shk_index.cuh): key -> node id, one region of slots per fine bucket, sized from
+// the nodes the bucket holds.  Only queued; cannot overflow.
+static shk_status index_impl(shk_asm *h) {
   const uint32_t nn = (uint32_t)h->st.n_nodes;
-  if (!icap) icap = std::max<uint64_t>(64, 2ull * nn);
-  SHK_TRY(h->slots.ensure(icap * 8));
-  h->cap = icap;
-  h->index_P = h->P ? h->P : 1;                        // the buckets the nodes were counted in (any power of two is valid)
-  SHK_CUDA(cudaMemsetAsync(h->slots.p, 0xFF, icap * 8, h->stream));
-  SHK_CUDA(cudaMemsetAsync(d_flags(h) + 7, 0, 4, h->stream));
-  h->st.gpu_launches += launch_index_nodes(h->kw, h->slots.as<uint64_t>(), icap, h->index_P, h->p.k, h->node_lo.as<uint64_t>(), h->node_hi.as<uint64_t>(), nn,
-                                           d_flags(h) + 7, h->stream);
+  const uint32_t P = h->P ? h->P : 1;                  // the buckets the nodes were counted in (any power of two is valid)
+  SHK_TRY(h->slots.ensure(((size_t)2 * nn + 2) * 8));
+  SHK_TRY(h->idx_off.ensure(((size_t)P + 2) * 4));
+  SHK_TRY(h->idx_tmp.ensure(((size_t)nn + index_tmp_entries(P) + 2) * 4));
+  h->index_P = P;
+  SHK_CUDA(cudaMemsetAsync(h->slots.p, 0xFF, ((size_t)2 * nn + 2) * 8, h->stream));
+  SHK_CUDA(cudaMemsetAsync(h->idx_off.p, 0, ((size_t)P + 2) * 4, h->stream));
+  h->st.gpu_launches += launch_index_nodes(h->kw, h->slots.as<uint64_t>(), h->idx_off.as<uint32_t>(), h->idx_tmp.as<uint32_t>(),
+                                           h->idx_tmp.as<uint32_t>() + nn, P, h->p.k, h->node_lo.as<uint64_t>(),
+                                           h->node_hi.as<uint64_t>(), nn, h->stream);
   SHK_CUDA(cudaGetLastError());
   SHK_CUDA(cudaEventRecord(h->ev[5], h->stream));
   h->filtered = true; h->graphed = false;
@@ -791,7 +793,7 @@ static shk_status graph_impl(shk_asm *h) {
   auto emit_pass = [&](bool have_circ) -> shk_status {
     L += launch_unitig_heads(g, k, have_circ, h->stream);
     L += launch_unitig_emit(h->kw, g, k, h->stream);
-    L += launch_unitig_links_out(h->kw, h->slots.as<uint64_t>(), h->cap, h->index_P, k, g, std::min(N, ns_cap), h->stream);
+    L += launch_unitig_links_out(h->kw, h->slots.as<uint64_t>(), h->idx_off.as<uint32_t>(), h->index_P, k, g, std::min(N, ns_cap), h->stream);
     SHK_CUDA(cudaGetLastError());
     SHK_CUDA(cudaEventRecord(h->ev[7], h->stream));
     return SHK_OK;
@@ -799,16 +801,11 @@ static shk_status graph_impl(shk_asm *h) {
   for (int attempt = 0;; ++attempt) {
     if (attempt > 4) { set_error("graph stage did not settle after retries"); return SHK_ERR_STATE; }
     SHK_CUDA(cudaMemsetAsync(h->tail_of.p, 0xFF, ne * 4, h->stream));
-    L += launch_build_edges(h->kw, h->slots.as<uint64_t>(), h->cap, h->index_P, k, g, h->stream);
+    L += launch_build_edges(h->kw, h->slots.as<uint64_t>(), h->idx_off.as<uint32_t>(), h->index_P, k, g, h->stream);
     L += launch_unitig_links(g, h->stream);
     SHK_TRY(rank_pass(nullptr));
     SHK_TRY(emit_pass(false));
     SHK_TRY(read_back());
-    if (hfl[7]) {                                      // node index overflow: twice the slots, everything again
-      if (h->cap > (1ull << 36)) { set_error("node index overflow"); return SHK_ERR_TABLE_FULL; }
-      SHK_TRY(index_impl(h, h->cap * 2));
-      continue;
-    }
     if (hs[5]) {                                       // more splitters than the work area holds: the count is known now
       h->ns_hint = hs[4];
       ns_cap = (uint32_t)std::min<uint64_t>(ne, (uint64_t)hs[4] + 1024);
@@ -839,7 +836,7 @@ static shk_status graph_impl(shk_asm *h) {
     SHK_TRY(h->link_from.ensure((size_t)link_cap * 4)); SHK_TRY(h->link_to.ensure((size_t)link_cap * 4));
     g.link_from = h->link_from.as<uint32_t>(); g.link_to = h->link_to.as<uint32_t>(); g.link_cap = link_cap;
     SHK_CUDA(cudaMemsetAsync(g.scal + 3, 0, 4, h->stream));
-    L += launch_unitig_links_out(h->kw, h->slots.as<uint64_t>(), h->cap, h->index_P, k, g, nu, h->stream);
+    L += launch_unitig_links_out(h->kw, h->slots.as<uint64_t>(), h->idx_off.as<uint32_t>(), h->index_P, k, g, nu, h->stream);
     SHK_CUDA(cudaGetLastError());
     SHK_CUDA(cudaEventRecord(h->ev[7], h->stream));
     SHK_TRY(read_back());

@@ -325,8 +325,10 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
           const u32 kk = __shfl_up_sync(0xffffffffu, kin, o);
           if (lane >= o) { est += t; inc += u; kin += kk; }
         }
-        // the de-dup list holds at most one item per record plus one per SHK_CB_SEG k-mers: never plan past it
-        const bool list_ok = !DEDUP || (u64)run + inc + (kacc + kin) / SHK_CB_SEG + 1 <= (u64)uq_cap;
+        // a cold launch runs with a default-sized de-dup list: never plan past what it holds for certain (one item
+        // per record plus one per SHK_CB_SEG k-mers).  Later launches size the list from the measured need, which
+        // is far below that bound (most records of a group are duplicates), and are verified afterwards instead.
+        const bool list_ok = !DEDUP || !sp.cold || (u64)run + inc + (kacc + kin) / SHK_CB_SEG + 1 <= (u64)uq_cap;
         const bool fits = valid && ((acc + est <= sp.budget_q16 && list_ok) || (cnt == 0 && lane == 0));
         const u32 m = __ballot_sync(0xffffffffu, fits);               // a prefix of the lanes: est only grows
         u32 take = m == 0xFFFFFFFFu ? 32u : (u32)__ffs(~m) - 1u;

@@ -130,7 +130,7 @@ struct shk_asm {
   uint32_t shard_cal_nb = 0, shard_cal_world = 0;
   bool shard_fast_banned = false, shard_fast_retried = false;
   // ---- node index (key -> node id) for the graph stage ----
-  shk::DevBuf slots;
+  shk::DevBuf slots, idx_off /* u32[P + 1]: slot region of every fine bucket */, idx_tmp /* bucket per node + scan scratch */;
   uint64_t cap = 0;
   uint32_t index_P = 1;         // bucket count the index regions follow (shk_index.cuh)
   bool table_live = false;

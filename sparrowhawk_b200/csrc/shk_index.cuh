@@ -1,15 +1,19 @@
 // shk_index.cuh — the node index of the graph stage: canonical k-mer -> node id.
 //
-// One u64 per slot (node id in the low half, 32 fingerprint bits of the key's hash in the high half, all ones =
-// empty), two slots per node, linear probing; a probe whose fingerprint matches is confirmed against the dense
-// key arrays (node_lo[, node_hi]), so the answer is exact.  The home slot is NOT a plain hash of the key: the slot
-// array is cut into P equal regions, one per fine minimizer bucket (the buckets of K1a), and a key starts
-// probing inside the region of ITS bucket.  Nine of ten de Bruijn neighbours share the minimizer — hence the
-// bucket — of the node that asks for them, and K1b writes the nodes of consecutive buckets next to each other,
-// so a CTA of K3 works on a few kilobytes of slots and keys that stay in L1/L2 instead of on two random
-// sectors per lookup in 80 MB.  The price is the minimizer of every key asked for (k-m+1 hashes, registers only).
-// The same struct describes a PEER rank's index on the sharded path: slots / lo / hi then point into that
-// rank's memory, mapped over NVLink.
+// Layout: one REGION of slots per fine minimizer bucket (the buckets of K1a), sized from the number of nodes
+// the bucket really holds (two slots per node), regions back to back in bucket order.  A key hashes to a slot
+// inside the region of ITS bucket and probes linearly, wrapping inside the region, so a crowded bucket never
+// spills into its neighbours and no probe sequence is longer than its own region.  A slot is a u64: node id in
+// the low half, 32 fingerprint bits of the key's hash in the high half, all ones = empty; a matching fingerprint
+// is confirmed against the dense key arrays (node_lo[, node_hi]), so the answer is exact.
+//
+// Why by bucket: nine of ten de Bruijn neighbours share the minimizer — hence the bucket — of the node that asks
+// for them, and K1b writes the nodes of consecutive buckets next to each other.  A CTA of K3 therefore works on a
+// few kilobytes of slots and keys that stay in L1/L2, where a table hashed over all of HBM costs a random DRAM
+// sector per lookup (160 MB at config B).  The price is the minimizer of every key asked for (k-m+1 hashes,
+// registers only) and a count + scan pass when the index is built.
+// The same struct describes a PEER rank's index on the sharded path (shk_shard.cuh): the pointers then lead into
+// that rank's memory, mapped over NVLink.
 #pragma once
 #include "shk_partition.cuh"
 
@@ -17,27 +21,12 @@ namespace shk {
 
 struct NodeIndex {
   const u64 *slots;
+  const u32 *off;         // [P + 1]: region of bucket b = slots[off[b] .. off[b+1])
   const u64 *lo, *hi;     // hi is null when k <= 31
-  u64 cap;
-  u32 P;                  // fine buckets (power of two) the regions follow
+  u32 P;                  // fine buckets (power of two)
   int k;
 };
-#define SHK_INDEX_MAXPROBE 4096u
-
 #define SHK_INDEX_EMPTY 0xFFFFFFFFFFFFFFFFull
-// home slot and fingerprint of a key whose bucket is known
-template <class K>
-__device__ __forceinline__ u64 index_home(u64 cap, u32 P, K key, u32 bucket, u32 &fp) {
-  const u64 h = hash_key(key);
-  const u64 region = cap / P;                            // slots per bucket region (0 on tiny inputs)
-  const u64 base = (u64)(((unsigned __int128)bucket * cap) / P);
-  fp = (u32)(h >> 32);
-  return region > 1 ? base + (u32)h % region : base;
-}
-template <class K>
-__device__ __forceinline__ u64 index_home(const NodeIndex &ix, K key, u32 &fp) {
-  return index_home(ix.cap, ix.P, key, minimizer_hash_of(key, ix.k) & (ix.P - 1), fp);
-}
 
 template <int KW>
 __device__ __forceinline__ bool index_key_is(const NodeIndex &ix, u32 id, typename KeyOf<KW>::type key) {
@@ -46,42 +35,59 @@ __device__ __forceinline__ bool index_key_is(const NodeIndex &ix, u32 id, typena
   return true;
 }
 
-// continue a lookup from slot i whose content `v` has already been loaded
+// lookup of a key whose bucket is known
 template <int KW>
-__device__ __forceinline__ u32 index_find_from(const NodeIndex &ix, typename KeyOf<KW>::type key, u32 fp, u64 i, u64 v) {
-  for (u32 probe = 0; probe < SHK_INDEX_MAXPROBE; ++probe) {
+__device__ __forceinline__ u32 index_find_in(const NodeIndex &ix, typename KeyOf<KW>::type key, u32 bucket) {
+  const u32 o = __ldcg(ix.off + bucket), sz = __ldcg(ix.off + bucket + 1) - o;
+  if (!sz) return SHK_NONE;
+  const u64 h = hash_key(key);
+  const u32 fp = (u32)(h >> 32);
+  u32 j = (u32)h % sz;
+  for (u32 probe = 0; probe < sz; ++probe) {
+    const u64 v = __ldcg(ix.slots + o + j);
     if (v == SHK_INDEX_EMPTY) return SHK_NONE;          // empty slot: absent
     if ((u32)(v >> 32) == fp && index_key_is<KW>(ix, (u32)v, key)) return (u32)v;
-    if (++i == ix.cap) i = 0;
-    v = __ldcg(ix.slots + i);
+    if (++j == sz) j = 0;
   }
   return SHK_NONE;
 }
 template <int KW>
 __device__ __forceinline__ u32 index_find(const NodeIndex &ix, typename KeyOf<KW>::type key) {
-  u32 fp;
-  const u64 i = index_home(ix, key, fp);
-  return index_find_from<KW>(ix, key, fp, i, __ldcg(ix.slots + i));
+  return index_find_in<KW>(ix, key, minimizer_hash_of(key, ix.k) & (ix.P - 1));
 }
 
-// build: node n claims the first empty slot of its probe sequence (slots pre-filled with 0xFF)
+// build, pass 1: two slots per node into the bucket counters; the bucket is kept for pass 2
 template <int KW>
 __global__ void __launch_bounds__(256)
-k_index_nodes(u64 *__restrict__ slots, u64 cap, u32 P, int k, const u64 *__restrict__ node_lo, const u64 *__restrict__ node_hi,
-              u32 n_nodes, u32 *__restrict__ overflow) {
+k_index_count(const u64 *__restrict__ node_lo, const u64 *__restrict__ node_hi, u32 n_nodes, u32 P, int k,
+              u32 *__restrict__ off /* zeroed [P + 1] */, u32 *__restrict__ bucket_of) {
   typedef typename KeyOf<KW>::type K;
   const u32 n = blockIdx.x * blockDim.x + threadIdx.x;
   if (n >= n_nodes) return;
   K key = (K)node_lo[n];
   if (KW == 2) key |= (K)((u128)node_hi[n] << 64);
-  u32 fp;
-  u64 i = index_home(cap, P, key, minimizer_hash_of(key, k) & (P - 1), fp);
-  const u64 mine = ((u64)fp << 32) | n;
-  for (u32 probe = 0; probe < SHK_INDEX_MAXPROBE; ++probe) {
-    if (atomicCAS(slots + i, SHK_INDEX_EMPTY, mine) == SHK_INDEX_EMPTY) return;
-    if (++i == cap) i = 0;
+  const u32 b = minimizer_hash_of(key, k) & (P - 1);
+  bucket_of[n] = b;
+  atomicAdd(off + b, 2u);
+}
+// pass 2 (after the exclusive scan of off): node n claims the first empty slot of its probe sequence
+template <int KW>
+__global__ void __launch_bounds__(256)
+k_index_insert(u64 *__restrict__ slots, const u32 *__restrict__ off, const u32 *__restrict__ bucket_of,
+               const u64 *__restrict__ node_lo, const u64 *__restrict__ node_hi, u32 n_nodes) {
+  typedef typename KeyOf<KW>::type K;
+  const u32 n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= n_nodes) return;
+  K key = (K)node_lo[n];
+  if (KW == 2) key |= (K)((u128)node_hi[n] << 64);
+  const u32 b = bucket_of[n], o = off[b], sz = off[b + 1] - o;      // sz >= 2: this node was counted
+  const u64 h = hash_key(key);
+  const u64 mine = (h & 0xFFFFFFFF00000000ull) | n;
+  u32 j = (u32)h % sz;
+  for (u32 probe = 0; probe < sz; ++probe) {                          // half of the region is free: always ends
+    if (atomicCAS(slots + o + j, SHK_INDEX_EMPTY, mine) == SHK_INDEX_EMPTY) return;
+    if (++j == sz) j = 0;
   }
-  atomicExch(overflow, 1u);
 }
 
 }  // namespace shk

@@ -9,6 +9,7 @@
 #include "shk_kernels.h"
 #include "shk_table.cuh"
 #include "shk_index.cuh"
+#include "shk_scan.cuh"
 #include "shk_count_smem.cuh"
 #include "shk_rank.cuh"
 
@@ -146,27 +147,14 @@ k_build_edges(NodeIndex ix, int k, const uint8_t *__restrict__ node_raw, u32 n_n
   if (n >= n_nodes) return;
   K X = (K)ix.lo[n];
   if (KW == 2) X |= (K)((u128)ix.hi[n] << 64);
-  u32 raw = __ldcs(node_raw + n), valid = 0;
+  u32 rem = __ldcs(node_raw + n), valid = 0;
   u32 un[2] = {SHK_NONE, SHK_NONE};
-  // The lookups of a node are independent: take the set bits two at a time so that both first probes are in
-  // flight together (a unitig-interior node has exactly two, one per side).
-  u32 rem = raw;
   while (rem) {
-    const int b0 = __ffs(rem) - 1; rem &= rem - 1;
-    const int b1 = rem ? __ffs(rem) - 1 : -1; if (b1 >= 0) rem &= rem - 1;
-    int s0, s1 = 0;
-    u32 f0, f1 = 0;
-    const K Y0 = neighbour_key(X, k, b0 >> 2, (u32)(b0 & 3), s0);
-    const u64 i0 = index_home(ix, Y0, f0);
-    K Y1 = 0; u64 i1 = 0;
-    if (b1 >= 0) { Y1 = neighbour_key(X, k, b1 >> 2, (u32)(b1 & 3), s1); i1 = index_home(ix, Y1, f1); }
-    const u64 v0 = __ldcg(ix.slots + i0), v1 = b1 >= 0 ? __ldcg(ix.slots + i1) : SHK_INDEX_EMPTY;
-    const u32 id0 = index_find_from<KW>(ix, Y0, f0, i0, v0);
-    if (id0 != SHK_NONE) { valid |= 1u << b0; un[b0 >> 2] = (id0 << 1) | (u32)s0; }
-    if (b1 >= 0) {
-      const u32 id1 = index_find_from<KW>(ix, Y1, f1, i1, v1);
-      if (id1 != SHK_NONE) { valid |= 1u << b1; un[b1 >> 2] = (id1 << 1) | (u32)s1; }
-    }
+    const int b = __ffs(rem) - 1; rem &= rem - 1;
+    int s_in;
+    const K Y = neighbour_key(X, k, b >> 2, (u32)(b & 3), s_in);
+    const u32 id = index_find<KW>(ix, Y);
+    if (id != SHK_NONE) { valid |= 1u << b; un[b >> 2] = (id << 1) | (u32)s_in; }
   }
   node_edges[n] = (uint8_t)valid;
   __stcs(reinterpret_cast<uint2 *>(uniq) + n, make_uint2(__popc(valid & 15u) == 1 ? un[0] : SHK_NONE,
@@ -424,10 +412,10 @@ int launch_histogram_filter(int kw, void *slots, uint64_t cap, int min_count, ui
   return 1;
 }
 
-int launch_build_edges(int kw, const uint64_t *slots, uint64_t cap, uint32_t P, int k, const GraphBuffers &g, cudaStream_t st) {
+int launch_build_edges(int kw, const uint64_t *slots, const uint32_t *off, uint32_t P, int k, const GraphBuffers &g, cudaStream_t st) {
   if (!g.n_nodes) return 0;
   unsigned b = blocks_for(g.n_nodes, 256);
-  NodeIndex ix{(const u64 *)slots, (const u64 *)g.node_lo, kw == 2 ? (const u64 *)g.node_hi : nullptr, cap, P, k};
+  NodeIndex ix{(const u64 *)slots, off, (const u64 *)g.node_lo, kw == 2 ? (const u64 *)g.node_hi : nullptr, P, k};
   if (kw == 1) k_build_edges<1><<<b, 256, 0, st>>>(ix, k, g.node_raw, g.n_nodes, g.node_edges, g.uniq);
   else k_build_edges<2><<<b, 256, 0, st>>>(ix, k, g.node_raw, g.n_nodes, g.node_edges, g.uniq);
   return 1;
@@ -460,6 +448,7 @@ int launch_rank_lists(const GraphBuffers &g, const uint8_t *circ, uint32_t ns_ca
   int &occ = occ_cache[current_device_slot()];
   if (!occ) {
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_rank_solve, 256, 0) != cudaSuccess || occ < 1) { cudaGetLastError(); occ = 1; }
+    if (occ > 2) occ = 2;            // grid-wide barriers get dearer with every CTA; the splitter level is small
   }
   unsigned grid = (unsigned)std::min<uint64_t>((uint64_t)sm_count() * occ, blocks_for(ns_cap, 256));
   RankSolveArgs a{g.succ, circ, g.splitters, g.scal + 4, ns_cap, (u64 *)g.pd, ne, sub_len, sub_sum, last_elem, next_elem,
@@ -507,11 +496,11 @@ int launch_unitig_emit(int kw, const GraphBuffers &g, int k, cudaStream_t st) {
                                                           ne, k, g.seq, g.elem_unitig);
   return 1;
 }
-int launch_unitig_links_out(int kw, const uint64_t *slots, uint64_t cap, uint32_t P, int k, const GraphBuffers &g, uint32_t unitig_bound,
+int launch_unitig_links_out(int kw, const uint64_t *slots, const uint32_t *off, uint32_t P, int k, const GraphBuffers &g, uint32_t unitig_bound,
                             cudaStream_t st) {
   if (!unitig_bound) return 0;
   unsigned b = blocks_for(2ull * unitig_bound, 256);
-  NodeIndex ix{(const u64 *)slots, (const u64 *)g.node_lo, kw == 2 ? (const u64 *)g.node_hi : nullptr, cap, P, k};
+  NodeIndex ix{(const u64 *)slots, off, (const u64 *)g.node_lo, kw == 2 ? (const u64 *)g.node_hi : nullptr, P, k};
   if (kw == 1)
     k_unitig_links_out<1><<<b, 256, 0, st>>>(ix, k, (const UnitigRec *)g.recs, g.scal + 2, g.tail_of, g.unitig_of_head,
                                              (const u64 *)g.node_lo, (const u64 *)g.node_hi, g.node_edges, g.ucirc,
@@ -722,12 +711,18 @@ int launch_shard_segments(const uint64_t *d_fill, uint32_t nb, uint32_t world, c
   return 2;
 }
 
-int launch_index_nodes(int kw, uint64_t *slots, uint64_t cap, uint32_t P, int k, const uint64_t *node_lo, const uint64_t *node_hi,
-                       uint32_t n_nodes, uint32_t *overflow, cudaStream_t st) {
+size_t index_tmp_entries(uint32_t P) { return scan_tmp_entries(P); }
+// slots: u64[2 * n_nodes] pre-filled with 0xFF; off: u32[P + 1] zeroed; bucket_of: u32[n_nodes]; tmp: u32[index_tmp_entries(P)]
+int launch_index_nodes(int kw, uint64_t *slots, uint32_t *off, uint32_t *bucket_of, uint32_t *tmp, uint32_t P, int k,
+                       const uint64_t *node_lo, const uint64_t *node_hi, uint32_t n_nodes, cudaStream_t st) {
   if (!n_nodes) return 0;
-  if (kw == 1) k_index_nodes<1><<<blocks_for(n_nodes, 256), 256, 0, st>>>((u64 *)slots, cap, P, k, (const u64 *)node_lo, (const u64 *)node_hi, n_nodes, overflow);
-  else k_index_nodes<2><<<blocks_for(n_nodes, 256), 256, 0, st>>>((u64 *)slots, cap, P, k, (const u64 *)node_lo, (const u64 *)node_hi, n_nodes, overflow);
-  return 1;
+  const unsigned b = blocks_for(n_nodes, 256);
+  if (kw == 1) k_index_count<1><<<b, 256, 0, st>>>((const u64 *)node_lo, (const u64 *)node_hi, n_nodes, P, k, off, bucket_of);
+  else k_index_count<2><<<b, 256, 0, st>>>((const u64 *)node_lo, (const u64 *)node_hi, n_nodes, P, k, off, bucket_of);
+  int n = 1 + launch_exclusive_scan<u32>(off, P, tmp, st);
+  if (kw == 1) k_index_insert<1><<<b, 256, 0, st>>>((u64 *)slots, off, bucket_of, (const u64 *)node_lo, (const u64 *)node_hi, n_nodes);
+  else k_index_insert<2><<<b, 256, 0, st>>>((u64 *)slots, off, bucket_of, (const u64 *)node_lo, (const u64 *)node_hi, n_nodes);
+  return n + 1;
 }
 
 }  // namespace shk

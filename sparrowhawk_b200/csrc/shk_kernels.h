@@ -33,9 +33,8 @@ int launch_table_fill(void *slots, uint64_t cap, int kw, cudaStream_t st);
 int launch_histogram_filter(int kw, void *slots, uint64_t cap, int min_count, uint64_t *histo,
                             uint64_t *node_lo, uint64_t *node_hi, uint16_t *node_count, uint8_t *node_raw,
                             uint32_t node_cap, uint32_t *n_nodes, cudaStream_t st);
-// node index (shk_index.cuh): slots = u64[cap], pre-filled with 0xFF
 // P = fine buckets of the count stage (power of two): the index keeps the nodes of a bucket together
-int launch_build_edges(int kw, const uint64_t *slots, uint64_t cap, uint32_t P, int k, const GraphBuffers &g, cudaStream_t st);
+int launch_build_edges(int kw, const uint64_t *slots, const uint32_t *off, uint32_t P, int k, const GraphBuffers &g, cudaStream_t st);
 int launch_unitig_links(const GraphBuffers &g, cudaStream_t st);
 // K5 (shk_rank.cuh): mark counts the splitters into scal[4] and the host never reads that number: `work` holds
 // ns_cap splitters (rank_splitter_bytes() each), the kernels read the count from scal[4] and set scal[5] when it
@@ -47,7 +46,7 @@ int launch_rank_lists(const GraphBuffers &g, const uint8_t *circ, uint32_t ns_ca
 int launch_cycle_cut(const GraphBuffers &g, uint32_t n_cyclic, cudaStream_t st);
 int launch_unitig_heads(const GraphBuffers &g, int k, bool have_circ, cudaStream_t st);
 int launch_unitig_emit(int kw, const GraphBuffers &g, int k, cudaStream_t st);
-int launch_unitig_links_out(int kw, const uint64_t *slots, uint64_t cap, uint32_t P, int k, const GraphBuffers &g,
+int launch_unitig_links_out(int kw, const uint64_t *slots, const uint32_t *off, uint32_t P, int k, const GraphBuffers &g,
                             uint32_t unitig_bound /* grid size; the count is read from scal[2] */, cudaStream_t st);
 size_t unitig_rec_bytes();
 
@@ -87,7 +86,10 @@ int launch_shard_send_plan(const uint64_t *d_fill, uint32_t rcap, uint32_t world
 int shard_max_world();
 int launch_shard_segments(const uint64_t *d_fill, uint32_t nb, uint32_t world, const uint64_t *src_base /* host, [world] */,
                           uint64_t *seg_off, uint32_t *seg_cnt, uint64_t *bucket_tot, cudaStream_t st);
-int launch_index_nodes(int kw, uint64_t *slots, uint64_t cap, uint32_t P, int k, const uint64_t *node_lo, const uint64_t *node_hi,
-                       uint32_t n_nodes, uint32_t *overflow, cudaStream_t st);
+// node index build (shk_index.cuh): slots u64[2 * n_nodes] pre-filled with 0xFF; off u32[P + 1] zeroed;
+// bucket_of u32[n_nodes]; tmp u32[index_tmp_entries(P)].  No overflow is possible: regions are sized from the counts.
+size_t index_tmp_entries(uint32_t P);
+int launch_index_nodes(int kw, uint64_t *slots, uint32_t *off, uint32_t *bucket_of, uint32_t *tmp, uint32_t P, int k,
+                       const uint64_t *node_lo, const uint64_t *node_hi, uint32_t n_nodes, cudaStream_t st);
 
 }  // namespace shk

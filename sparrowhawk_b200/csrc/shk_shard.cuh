@@ -1,0 +1,314 @@
+// shk_shard.cuh — the graph stage of the sharded path (north_star: "each GPU counts and builds its own
+// slice of the graph; cross-shard unitig joins are resolved by a final pointer-jumping pass").
+//
+// Every rank keeps the nodes of ITS minimizer buckets (dense arrays + the node index of shk_index.cuh) and
+// publishes them to the other ranks of the box as PEER MEMORY (CUDA IPC mappings over NVLink / NVSwitch): a
+// kernel that needs a fact about a node owned elsewhere — does this neighbour exist, how many validated edges
+// has its facing side, which chain does this element head — reads it straight out of the owner's HBM.  No node
+// is ever copied to another rank.
+//
+//   K3' k_build_edges_sharded   owned nodes; a neighbour key is looked up in the index of the rank that owns its
+//                               minimizer bucket (minimizer_hash_of); node ids are GLOBAL (rank offset + local id)
+//   K4' k_unitig_links_sharded  succ over the owned directed elements; links to an element of another rank are
+//                               kept apart (xsucc), so the local lists END at the rank border
+//   K5  local list ranking      the single-GPU kernels (shk_rank.cuh) over succ_local: every maximal run of a
+//                               unitig inside this rank becomes one CHAIN (head, tail, length, count sum)
+//       k_chain_enum / k_chain_records   chains get numbers (mirror pairs 2i / 2i+1), their border links are
+//                               translated to chain numbers by reading the owner's chain_of_head, and the 64-byte
+//                               chain records are all-gathered (about a tenth of the elements)
+//   K5" chain-level ranking     the same ruling-set + pointer-jumping kernels, weighted by chain length / count
+//                               sum, run redundantly on every rank over the gathered chains: the FINAL
+//                               pointer-jumping pass that joins the unitigs across the shards
+//       k_chain_heads + scan    one list of each mirror pair is kept (same rule as k_unitig_heads); unitig ids
+//                               and sequence offsets come from a prefix scan, so they are identical on all ranks
+//   K6' k_unitig_emit_sharded   every rank writes the bases of ITS elements at their global offsets; the host
+//                               merges the byte buffers (all-reduce, the other ranks wrote zeros)
+//       k_unitig_links_sharded_out  unitig-level links, by the rank that owns the exit node
+#pragma once
+#include "shk_index.cuh"
+#include "shk_scan.cuh"
+
+namespace shk {
+
+#define SHK_MAX_WORLD 64
+
+struct PeerView {             // one rank's published arrays as this rank addresses them (own entry: local pointers)
+  const u64 *slots; const u32 *off; const u64 *lo; const u64 *hi; u32 n_nodes;
+  const uint8_t *edges;       // validated edge bits per node (K3')
+  const u32 *chain_of_head;   // per directed element: local chain-element number of the chain it heads, or SHK_NONE
+};
+struct ShardTopo {            // device-resident, rewritten for every run
+  u32 world, rank, P; int k;
+  u32 node_off[SHK_MAX_WORLD + 1];    // global id of rank r's first node
+  u32 chain_off[SHK_MAX_WORLD + 1];   // global number of rank r's first (canonical) chain
+  PeerView peer[SHK_MAX_WORLD];
+};
+
+// 64 bytes per canonical chain i = chain elements 2i (as ranked: head .. tail) and 2i+1 (its mirror: rev(tail) .. rev(head))
+struct __align__(16) ChainRec {
+  u32 next_f, next_m;         // global chain element that follows 2i / 2i+1 across the rank border (SHK_NONE: none)
+  u32 len, flags;             // nodes in the chain; bit 0: an unbranched cycle inside one rank, already cut at its minimum
+  u64 sum;                    // sum of the k-mer counts
+  u32 head_g, tail_g;         // global directed elements of the chain's first and last node
+  u64 hkey_lo, hkey_hi, tkey_lo, tkey_hi;   // their canonical k-mers (mirror selection, S14)
+};
+
+__device__ __forceinline__ u32 owner_of_bucket(u32 b, u32 P, u32 world) {
+  u32 r = (u32)(((u64)b * world) / P);
+  while (r + 1 < world && (u32)(((u64)(r + 1) * P) / world) <= b) ++r;     // bucket b belongs to r iff r*P/W <= b < (r+1)*P/W
+  while (r > 0 && (u32)(((u64)r * P) / world) > b) --r;
+  return r;
+}
+__device__ __forceinline__ u32 owner_of_node(const ShardTopo *t, u32 g) {
+  u32 lo = 0, hi = t->world;                      // node_off[lo] <= g < node_off[hi]
+  while (hi - lo > 1) { const u32 mid = (lo + hi) >> 1; if (t->node_off[mid] <= g) lo = mid; else hi = mid; }
+  return lo;
+}
+
+// neighbour key -> global node id (SHK_NONE: no such node anywhere)
+template <int KW>
+__device__ __forceinline__ u32 shard_find(const ShardTopo *t, typename KeyOf<KW>::type Y) {
+  const u32 b = minimizer_hash_of(Y, t->k) & (t->P - 1);
+  const u32 r = owner_of_bucket(b, t->P, t->world);
+  const PeerView pv = t->peer[r];
+  if (!pv.n_nodes) return SHK_NONE;               // that rank holds no node at all
+  NodeIndex ix{pv.slots, pv.off, pv.lo, pv.hi, t->P, t->k};
+  const u32 id = index_find_in<KW>(ix, Y, b);
+  return id == SHK_NONE ? SHK_NONE : t->node_off[r] + id;
+}
+
+template <int KW>
+__global__ void __launch_bounds__(256)
+k_build_edges_sharded(const ShardTopo *__restrict__ t, const u64 *__restrict__ node_lo, const u64 *__restrict__ node_hi,
+                      const uint8_t *__restrict__ node_raw, u32 n_nodes, uint8_t *__restrict__ node_edges,
+                      u32 *__restrict__ uniq /* [2*n_nodes]: global node id << 1 | arrival side */) {
+  typedef typename KeyOf<KW>::type K;
+  const u32 n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= n_nodes) return;
+  K X = (K)node_lo[n];
+  if (KW == 2) X |= (K)((u128)node_hi[n] << 64);
+  const int k = t->k;
+  u32 rem = __ldcs(node_raw + n), valid = 0;
+  u32 un[2] = {SHK_NONE, SHK_NONE};
+  while (rem) {
+    const int b = __ffs(rem) - 1; rem &= rem - 1;
+    int s_in;
+    const K Y = neighbour_key(X, k, b >> 2, (u32)(b & 3), s_in);
+    const u32 g = shard_find<KW>(t, Y);
+    if (g != SHK_NONE) { valid |= 1u << b; un[b >> 2] = (g << 1) | (u32)s_in; }
+  }
+  node_edges[n] = (uint8_t)valid;
+  __stcs(reinterpret_cast<uint2 *>(uniq) + n, make_uint2(__popc(valid & 15u) == 1 ? un[0] : SHK_NONE,
+                                                         __popc(valid >> 4) == 1 ? un[1] : SHK_NONE));
+}
+
+// succ_local[e]: the local element that follows e, when it lives on this rank; xsucc[e]: the GLOBAL element that
+// follows e, when it lives on another rank.  Same rule as k_unitig_links (the edge must be the only one on the
+// facing side of both nodes and must not return to the same node).
+__global__ void __launch_bounds__(256)
+k_unitig_links_sharded(const ShardTopo *__restrict__ t, const uint8_t *__restrict__ node_edges, const u32 *__restrict__ uniq,
+                       u32 n_elems, u32 *__restrict__ succ_local, u32 *__restrict__ xsucc) {
+  const u32 e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= n_elems) return;
+  const u32 u = uniq[e];
+  u32 out_l = SHK_NONE, out_x = SHK_NONE;
+  if (u != SHK_NONE) {
+    const u32 w = u >> 1, s = u & 1u, me = t->rank;
+    if (w != t->node_off[me] + (e >> 1)) {
+      const u32 r = owner_of_node(t, w), wl = w - t->node_off[r];
+      const u32 ed = r == me ? (u32)node_edges[wl] : (u32)__ldcg(t->peer[r].edges + wl);
+      if (__popc(side_bits(ed, (int)s)) == 1) {
+        if (r == me) out_l = 2 * wl + (s ^ 1u);
+        else out_x = 2 * w + (s ^ 1u);
+      }
+    }
+  }
+  succ_local[e] = out_l;
+  xsucc[e] = out_x;
+}
+
+// Chains = the ranked local lists.  A list (head e, tail t) and its mirror (head rev(t), tail rev(e)) get the chain
+// elements 2i and 2i+1; the one whose head element is smaller allocates the number.  A cycle inside the rank has
+// been cut at its minimum k-mer by the local ranking: only the list through the minimum node in direction 0 becomes
+// a chain (flag bit 0), its mirror element 2i+1 stays unused.
+__global__ void __launch_bounds__(256)
+k_chain_enum(const u64 *__restrict__ pd, const u32 *__restrict__ tail_of, const uint8_t *__restrict__ circ, u32 n_elems,
+             u32 *__restrict__ chain_of_head /* pre-filled with SHK_NONE */, u32 *__restrict__ chain_head, u32 *__restrict__ n_chains) {
+  const u32 e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= n_elems || pd[e] != ((u64)e << 32)) return;
+  const bool cyc = circ && circ[e];
+  const u32 mh = tail_of[e] ^ 1u;
+  if (cyc ? (e & 1u) != 0 : e > mh) return;
+  const u32 i = atomicAdd(n_chains, 1u);
+  chain_head[i] = e;
+  chain_of_head[e] = 2 * i;
+  if (!cyc) chain_of_head[mh] = 2 * i + 1;
+}
+
+__device__ __forceinline__ u32 chain_of_global_elem(const ShardTopo *t, const u32 *my_chain_of_head, u32 g) {
+  if (g == SHK_NONE) return SHK_NONE;
+  const u32 r = owner_of_node(t, g >> 1), le = g - 2 * t->node_off[r];
+  const u32 c = r == t->rank ? my_chain_of_head[le] : __ldcg(t->peer[r].chain_of_head + le);
+  return c == SHK_NONE ? SHK_NONE : 2 * t->chain_off[r] + c;
+}
+
+__global__ void __launch_bounds__(256)
+k_chain_records(const ShardTopo *__restrict__ t, const u32 *__restrict__ chain_head, u32 n_chains, const u32 *__restrict__ tail_of,
+                const u32 *__restrict__ len_of, const u64 *__restrict__ sum_of, const u32 *__restrict__ xsucc,
+                const uint8_t *__restrict__ circ, const u32 *__restrict__ chain_of_head, const u64 *__restrict__ node_lo,
+                const u64 *__restrict__ node_hi, ChainRec *__restrict__ out, u32 *__restrict__ bad /* a border link without a chain */) {
+  const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_chains) return;
+  const u32 e = chain_head[i], tl = tail_of[e], base = 2 * t->node_off[t->rank];
+  const bool cyc = circ && circ[e];
+  ChainRec r;
+  const u32 xf = cyc ? SHK_NONE : xsucc[tl], xm = cyc ? SHK_NONE : xsucc[e ^ 1u];
+  r.next_f = chain_of_global_elem(t, chain_of_head, xf);
+  r.next_m = chain_of_global_elem(t, chain_of_head, xm);
+  if ((xf != SHK_NONE && r.next_f == SHK_NONE) || (xm != SHK_NONE && r.next_m == SHK_NONE)) atomicExch(bad, 1u);
+  r.len = len_of[e]; r.flags = cyc ? 1u : 0u; r.sum = sum_of[e];
+  r.head_g = base + e; r.tail_g = base + tl;
+  r.hkey_lo = node_lo[e >> 1]; r.tkey_lo = node_lo[tl >> 1];
+  r.hkey_hi = node_hi ? node_hi[e >> 1] : 0ull; r.tkey_hi = node_hi ? node_hi[tl >> 1] : 0ull;
+  out[i] = r;
+}
+
+// ---- chain level (every rank, over the gathered records) ------------------------------------------------
+__global__ void __launch_bounds__(256)
+k_chain_unpack(const ChainRec *__restrict__ recs, u32 n_chains, u32 *__restrict__ succ_c, u32 *__restrict__ w_len, u64 *__restrict__ w_sum) {
+  const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_chains) return;
+  const ChainRec r = recs[i];
+  succ_c[2 * i] = r.next_f; succ_c[2 * i + 1] = r.next_m;
+  w_len[i] = r.len; w_sum[i] = r.sum;
+}
+
+struct ChainEnd { u32 g; u64 lo, hi; };
+__device__ __forceinline__ ChainEnd chain_elem_head(const ChainRec *recs, u32 E) {
+  const ChainRec &r = recs[E >> 1];
+  return (E & 1u) ? ChainEnd{r.tail_g ^ 1u, r.tkey_lo, r.tkey_hi} : ChainEnd{r.head_g, r.hkey_lo, r.hkey_hi};
+}
+__device__ __forceinline__ ChainEnd chain_elem_tail(const ChainRec *recs, u32 E) {
+  const ChainRec &r = recs[E >> 1];
+  return (E & 1u) ? ChainEnd{r.head_g ^ 1u, r.hkey_lo, r.hkey_hi} : ChainEnd{r.tail_g, r.tkey_lo, r.tkey_hi};
+}
+
+// kept[E] = (1, bases of the unitig) for the chain-level list heads that are kept (rule of k_unitig_heads), else 0
+__global__ void __launch_bounds__(256)
+k_chain_heads(const u64 *__restrict__ pd_c, const u32 *__restrict__ tail_of_c, const u32 *__restrict__ len_of_c,
+              const ChainRec *__restrict__ recs, u32 n_celems, int k, u32 *__restrict__ kept_cnt, u64 *__restrict__ kept_len) {
+  const u32 E = blockIdx.x * blockDim.x + threadIdx.x;
+  if (E >= n_celems) return;
+  u32 c = 0; u64 l = 0;
+  if (pd_c[E] == ((u64)E << 32)) {
+    const bool cyc = recs[E >> 1].flags & 1u;
+    bool keep;
+    if (cyc) keep = (E & 1u) == 0;
+    else {
+      const ChainEnd h = chain_elem_head(recs, E), tl = chain_elem_tail(recs, tail_of_c[E]);
+      if ((h.g >> 1) == (tl.g >> 1)) keep = (h.g & 1u) == 0;
+      else keep = h.hi != tl.hi ? h.hi < tl.hi : h.lo < tl.lo;
+    }
+    if (keep) { c = 1; l = (u64)len_of_c[E] + (u64)k - 1; }
+  }
+  kept_cnt[E] = c; kept_len[E] = l;
+}
+
+struct UnitigRecS { u32 head, len; u64 off; };     // == UnitigRec of shk_kernels.cu; head = chain element here
+
+// after the exclusive scans of kept_cnt / kept_len (in place)
+__global__ void __launch_bounds__(256)
+k_chain_unitigs(const u64 *__restrict__ pd_c, const u32 *__restrict__ len_of_c, const u64 *__restrict__ sum_of_c,
+                const ChainRec *__restrict__ recs, const u32 *__restrict__ kept_cnt_x, const u64 *__restrict__ kept_len_x,
+                u32 n_celems, int k, u32 *__restrict__ unitig_of_head_c, UnitigRecS *__restrict__ urecs,
+                uint8_t *__restrict__ ucirc, u64 *__restrict__ cov_sum) {
+  const u32 E = blockIdx.x * blockDim.x + threadIdx.x;
+  if (E >= n_celems) return;
+  const bool last = E + 1 == n_celems;
+  // kept iff the exclusive prefix grows behind E (the totals sit one past the end)
+  const bool kept = kept_cnt_x[E + 1] != kept_cnt_x[E];
+  (void)last;
+  if (!kept) { unitig_of_head_c[E] = SHK_NONE; return; }
+  const u32 uid = kept_cnt_x[E];
+  unitig_of_head_c[E] = uid;
+  urecs[uid] = UnitigRecS{E, len_of_c[E], kept_len_x[E]};
+  ucirc[uid] = (uint8_t)(recs[E >> 1].flags & 1u);
+  cov_sum[uid] = sum_of_c[E];
+}
+
+template <int KW>
+__global__ void __launch_bounds__(256)
+k_unitig_emit_sharded(const ShardTopo *__restrict__ t, const u64 *__restrict__ pd, const u32 *__restrict__ chain_of_head,
+                      const u64 *__restrict__ pd_c, const u32 *__restrict__ unitig_of_head_c, const UnitigRecS *__restrict__ urecs,
+                      const u64 *__restrict__ node_lo, const u64 *__restrict__ node_hi, u32 n_elems, char *__restrict__ seq) {
+  typedef typename KeyOf<KW>::type K;
+  const u32 e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= n_elems) return;
+  const u64 v = pd[e];
+  if (v == ~0ull) return;
+  const u32 c = chain_of_head[(u32)(v >> 32)];
+  if (c == SHK_NONE) return;                                 // the dropped direction of a local cycle
+  const u64 vc = pd_c[2 * t->chain_off[t->rank] + c];
+  if (vc == ~0ull) return;
+  const u32 uid = unitig_of_head_c[(u32)(vc >> 32)];
+  if (uid == SHK_NONE) return;                               // the mirror list of a kept one
+  const u32 r = (u32)vc + (u32)v;                            // nodes in front of this one in the unitig
+  const int k = t->k;
+  const u32 n = e >> 1;
+  K X = (K)node_lo[n];
+  if (KW == 2) X |= (K)((u128)node_hi[n] << 64);
+  if (e & 1u) X = revcomp_key(X, k);
+  const u64 off = urecs[uid].off;
+  if (r == 0) {
+    for (int i = 0; i < k; ++i) seq[off + i] = SHK_CODE2ASCII_DEV((u32)(X >> (2 * (k - 1 - i))) & 3u);
+  } else {
+    seq[off + k - 1 + r] = SHK_CODE2ASCII_DEV((u32)X & 3u);
+  }
+}
+
+// Unitig-level links, written by the rank that owns the exit node (see k_unitig_links_out for the rules).
+template <int KW>
+__global__ void __launch_bounds__(256)
+k_unitig_links_sharded_out(const ShardTopo *__restrict__ t, const UnitigRecS *__restrict__ urecs, u32 n_unitigs,
+                           const u32 *__restrict__ tail_of_c, const u32 *__restrict__ unitig_of_head_c,
+                           const ChainRec *__restrict__ recs, const u32 *__restrict__ chain_of_head,
+                           const u64 *__restrict__ node_lo, const u64 *__restrict__ node_hi,
+                           const uint8_t *__restrict__ node_edges, const uint8_t *__restrict__ ucirc,
+                           u32 *__restrict__ from, u32 *__restrict__ to, u32 link_cap, u32 *__restrict__ n_links, u32 *__restrict__ bad) {
+  typedef typename KeyOf<KW>::type K;
+  const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= 2 * n_unitigs) return;
+  const u32 uid = i >> 1, orient = i & 1u, me = t->rank;
+  const u32 H = urecs[uid].head;
+  const u32 xg = orient == 0 ? chain_elem_tail(recs, tail_of_c[H]).g : (chain_elem_head(recs, H).g ^ 1u);   // exit element
+  if (owner_of_node(t, xg >> 1) != me) return;
+  const u32 n = (xg >> 1) - t->node_off[me]; const int side = (int)(xg & 1u);
+  const u32 bits = (u32)side_bits(node_edges[n], side);
+  if (!bits) return;
+  if (ucirc[uid]) {                            // unbranched cycle: closes on itself
+    const u32 slot = atomicAdd(n_links, 1u);
+    if (slot < link_cap) { from[slot] = i; to[slot] = i; }
+    return;
+  }
+  K X = (K)node_lo[n];
+  if (KW == 2) X |= (K)((u128)node_hi[n] << 64);
+  for (u32 b = 0; b < 4; ++b) {
+    if (!((bits >> b) & 1u)) continue;
+    int s_in; const K Y = neighbour_key(X, t->k, side, b, s_in);
+    const u32 w = shard_find<KW>(t, Y);
+    if (w == SHK_NONE) { atomicExch(bad, 1u); continue; }    // cannot happen after validation
+    const u32 Ef = chain_of_global_elem(t, chain_of_head, 2 * w + ((u32)s_in ^ 1u));   // entered element: head of its list
+    if (Ef == SHK_NONE) { atomicExch(bad, 1u); continue; }
+    u32 target = unitig_of_head_c[Ef], tor = 0;
+    if (target == SHK_NONE) {
+      const u32 tf = tail_of_c[Ef];
+      if (tf == SHK_NONE) { atomicExch(bad, 1u); continue; }
+      target = unitig_of_head_c[tf ^ 1u]; tor = 1;
+    }
+    if (target == SHK_NONE) { atomicExch(bad, 1u); continue; }
+    const u32 slot = atomicAdd(n_links, 1u);
+    if (slot < link_cap) { from[slot] = 2 * uid + orient; to[slot] = 2 * target + tor; }
+  }
+}
+
+}  // namespace shk
