@@ -304,6 +304,64 @@ shk_status shk_shard_set_nodes(shk_asm *h, const void *d_lo, const void *d_hi,
                                size_t my_offset, const uint64_t *histo_global,
                                uint64_t n_instances_global, uint64_t n_bases_global,
                                int used_min_count);
+/* ------------------------------------------------------------------ */
+/* Sharded graph stage: every rank builds ITS slice of the graph and   */
+/* the unitigs are joined across the shards by a final pointer-jumping */
+/* pass (north_star; SURVEY §8e "Graph phase", D.9).  No node leaves   */
+/* its owner: the ranks of one box publish their node arrays to each   */
+/* other as peer memory (CUDA IPC over NVLink / NVSwitch) and the      */
+/* kernels read a remote neighbour's facts in place.  The host still   */
+/* runs every collective between the calls:                            */
+/*   shk_shard_count[_device]        (as above)                         */
+/*   host: all-reduce spectrum + totals + per-rank node counts          */
+/*   1 shk_shard_graph_publish    index over the owned nodes; blob out  */
+/*   host: all-gather the blobs (also the barrier "indices complete")   */
+/*   2 shk_shard_graph_connect    map the peers' memory                 */
+/*   3 shk_shard_graph_edges      K3' neighbour validation              */
+/*   host: barrier ("edges complete")                                   */
+/*   4 shk_shard_graph_chains     K4' + local list ranking -> chains    */
+/*   host: all-gather the chain counts ("chain numbers complete")       */
+/*   5 shk_shard_graph_records    this rank's 64-byte chain records     */
+/*   host: all-gather the records                                       */
+/*   6 shk_shard_graph_join       chain-level ranking on every rank,    */
+/*                                unitig table, this rank's bases+links */
+/*   host: byte-wise all-reduce (max) of the sequence buffer,           */
+/*         all-gather of the links                                      */
+/*   7 shk_shard_graph_set_links  the gathered links                    */
+/* Afterwards every rank holds the complete unitig graph (sequences,    */
+/* coverage, links): the exports and shk_asm_assemble answer alike on   */
+/* all ranks; shk_export_kmers covers the rank's own nodes.             */
+/* Reference analogue: none (sparrowhawk-asm is one wasm thread; its     */
+/* stages "assembly:create_graph" / "assembly:collapse_graph",          */
+/* AssemblyPage.vue:595-603, are what this replaces).                   */
+/* ------------------------------------------------------------------ */
+#define SHK_PEER_BLOB_BYTES 256
+typedef struct shk_shard_join_info {
+  uint64_t n_unitigs;
+  uint64_t seq_bytes;             /* bytes of the sequence buffer to merge across ranks */
+  void *d_seq;                    /* device: this rank's bases at their global offsets, zero elsewhere */
+  uint64_t n_links_local;         /* unitig links found by this rank */
+  void *d_link_from, *d_link_to;  /* device: u32[n_links_local] each */
+  uint64_t n_cyclic_chain_elems;  /* != 0: an unbranched cycle crosses rank borders and nothing below was produced; take
+                                   * the replicated graph stage (shk_shard_local_nodes / shk_shard_set_nodes /
+                                   * shk_build_graph) for this read set */
+} shk_shard_join_info;
+/* node_counts (HOST, u64[world]): surviving nodes of every rank; the other arguments as in shk_shard_set_nodes.
+ * blob_out (HOST, SHK_PEER_BLOB_BYTES): what the other ranks need to map this rank's arrays. */
+shk_status shk_shard_graph_publish(shk_asm *h, const uint64_t *node_counts, const uint64_t *histo_global,
+                                   uint64_t n_instances_global, uint64_t n_bases_global, int used_min_count,
+                                   void *blob_out);
+/* blobs (HOST, world x SHK_PEER_BLOB_BYTES, rank order).  Fails with SHK_ERR_CUDA when peer memory cannot be
+ * mapped (then every rank takes the replicated graph stage). */
+shk_status shk_shard_graph_connect(shk_asm *h, const void *blobs);
+shk_status shk_shard_graph_edges(shk_asm *h);
+shk_status shk_shard_graph_chains(shk_asm *h, uint64_t *n_chains_out);
+/* chain_counts (HOST, u64[world]); d_records_out (device, 64 bytes x this rank's chains). */
+shk_status shk_shard_graph_records(shk_asm *h, const uint64_t *chain_counts, void *d_records_out);
+/* d_all_records (device): the records of all ranks in rank order. */
+shk_status shk_shard_graph_join(shk_asm *h, const void *d_all_records, shk_shard_join_info *info);
+shk_status shk_shard_graph_set_links(shk_asm *h, const void *d_from, const void *d_to, uint64_t n_links);
+
 /* The host-side spectrum fit used by do_fit (docs/src/assembly.md:16). */
 int shk_fit_min_count(const uint64_t *histo /*[SHK_HISTO_BINS]*/, int fallback);
 

@@ -40,6 +40,13 @@ class ShkStats(C.Structure):
     ]
 
 
+class ShkShardJoinInfo(C.Structure):
+    _fields_ = [("n_unitigs", C.c_uint64), ("seq_bytes", C.c_uint64), ("d_seq", C.c_void_p),
+                ("n_links_local", C.c_uint64), ("d_link_from", C.c_void_p), ("d_link_to", C.c_void_p),
+                ("n_cyclic_chain_elems", C.c_uint64)]
+
+
+PEER_BLOB_BYTES = 256
 PROGRESS_FN = C.CFUNCTYPE(None, C.c_char_p, C.c_void_p)
 
 # every symbol include/shk.h declares: name -> (restype, argtypes)
@@ -92,6 +99,14 @@ SYMBOLS = {
     "shk_shard_set_nodes": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t,
                                       C.c_void_p, C.c_uint64, C.c_uint64, C.c_int]),
     "shk_fit_min_count": (C.c_int, [C.c_void_p, C.c_int]),
+    # sharded graph stage (peer memory)
+    "shk_shard_graph_publish": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_int, C.c_void_p]),
+    "shk_shard_graph_connect": (C.c_int, [_H, C.c_void_p]),
+    "shk_shard_graph_edges": (C.c_int, [_H]),
+    "shk_shard_graph_chains": (C.c_int, [_H, C.POINTER(C.c_uint64)]),
+    "shk_shard_graph_records": (C.c_int, [_H, C.c_void_p, C.c_void_p]),
+    "shk_shard_graph_join": (C.c_int, [_H, C.c_void_p, C.c_void_p]),
+    "shk_shard_graph_set_links": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_uint64]),
 }
 
 _lib = None

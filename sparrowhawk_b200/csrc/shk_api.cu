@@ -399,6 +399,7 @@ static shk_status count_impl(shk_asm *h, int /*reset*/, uint32_t P_override = 0,
     h->seg_kmers.clear(); h->seg_recs.clear(); h->shard_src = false;
   }
   h->partition_done = false;
+  h->shard_graph = false;
   h->counted = true; h->counted_fast = P_override != 0 /* no host-side bucket description either */; h->st.device_planned = 0; h->filtered = h->graphed = false; h->histo_valid = false;
   return SHK_OK;
 }
@@ -482,8 +483,8 @@ static uint64_t region_records_guess(uint64_t positions, uint32_t P, int kw, int
   // records per bucket: a run holds ~ (w+1)/2 k-mers for a window of w = k-m+1 m-mers
   const int mlen = k < 11 ? k : 11, w = k - mlen + 1;
   const double avg_run = std::min<double>(records_max_run(kw, k), std::max(1.0, (w + 1) / 2.0 * 0.6));
-  // x 4.5: at high coverage a bucket holds a handful of genome loci times the coverage, so fills scatter widely
-  return (uint64_t)(4.5 * (double)positions / avg_run / (double)P) + 64;
+  // x 6: at high coverage a bucket holds a handful of genome loci times the coverage, so fills scatter widely
+  return (uint64_t)(6.0 * (double)positions / avg_run / (double)P) + 64;
 }
 
 // What K1a -> K1b back to back needs to know before anything has run: bucket count and region size from the
@@ -539,7 +540,9 @@ static shk_status count_filter_fast(shk_asm *h, int min_count, bool &fell_back) 
   uint32_t uq_fast = 0;
   if (dedup) {
     // (the CTAs never plan a group past the list, so any size is safe; a short list only means smaller groups)
-    uq_fast = (uint32_t)std::min<uint64_t>(std::max<uint64_t>({(uint64_t)h->uq_cap * 2 + 1024, (uint64_t)h->uq_need_hint + h->uq_need_hint / 8,
+    // (the groups a run cuts depend on the order its CTAs grab chunks in, so the need moves by 10-20 % between runs:
+    // twice the largest need seen)
+    uq_fast = (uint32_t)std::min<uint64_t>(std::max<uint64_t>({(uint64_t)h->uq_cap * 2 + 1024, (uint64_t)h->uq_need_hint * 2 + 1024,
                                                                (uint64_t)(h->uq_cap || h->uq_need_hint ? 0 : 32768)}), 0x7FFFFFC0ull);
     uq_fast = (uq_fast + 63u) & ~63u;
     const size_t ctas = (size_t)count_ctas();
@@ -581,7 +584,7 @@ static shk_status count_filter_fast(shk_asm *h, int min_count, bool &fell_back) 
     fell_back = true;
     return SHK_OK;
   }
-  if (dedup) h->uq_need_hint = fl[5];
+  if (dedup) h->uq_need_hint = std::max(h->uq_need_hint, fl[5]);
   h->n_records = h->h_pinned[6];
   h->n_bases = h->h_pinned[3];
   h->counted_positions = h->n_positions;
@@ -589,7 +592,7 @@ static shk_status count_filter_fast(shk_asm *h, int min_count, bool &fell_back) 
   h->st.table_slots = P; h->st.table_retries = 0; h->st.n_records = h->n_records;
   h->src_instances = h->st.n_instances; h->shard_src = false; h->seg_per_bucket = 1;
   h->seg_kmers.clear(); h->seg_recs.clear();               // the host-side bucket description is not fetched on this path
-  h->counted = true; h->counted_fast = true; h->st.device_planned = 1;
+  h->counted = true; h->counted_fast = true; h->st.device_planned = 1; h->shard_graph = false;
   h->fast_positions = h->n_positions;
   h->st.n_spilled = h->h_pinned[4];
   h->spill_hint = h->st.n_spilled;
@@ -920,6 +923,7 @@ void shk_asm_free(shk_asm *h) {
     if (h->stream) cudaStreamSynchronize(h->stream);
     if (h->copy_stream) cudaStreamSynchronize(h->copy_stream);
     if (h->h_pinned) cudaFreeHost(h->h_pinned);
+    for (auto &row : h->peer_maps) for (auto &m : row) if (m.open) { cudaIpcCloseMemHandle(m.p); m.open = false; }
     // every DevBuf / PinBuf member frees itself when the handle is deleted below
     for (auto &e : h->ev) if (e) cudaEventDestroy(e);
     if (h->own_stream) cudaStreamDestroy(h->own_stream);
@@ -1007,7 +1011,8 @@ shk_status shk_export_kmers(shk_asm *h, uint64_t *key_lo, uint64_t *key_hi, uint
   if (raw_edges) SHK_CUDA(cudaMemcpyAsync(raw_edges, h->node_raw.p, N, cudaMemcpyDeviceToHost, h->stream));
   if (edges) {
     if (!h->graphed) { set_error("validated edges need build_graph"); return SHK_ERR_STATE; }
-    SHK_CUDA(cudaMemcpyAsync(edges, h->node_edges.p, N, cudaMemcpyDeviceToHost, h->stream));
+    const void *src = h->shard_graph ? (const void *)((const uint8_t *)h->arena.p + h->arena_off_edges) : h->node_edges.p;   // (sharded: published in the arena)
+    SHK_CUDA(cudaMemcpyAsync(edges, src, N, cudaMemcpyDeviceToHost, h->stream));
   }
   SHK_CUDA(cudaStreamSynchronize(h->stream));
   return SHK_OK;
@@ -1099,7 +1104,7 @@ shk_status shk_export_links(shk_asm *h, uint32_t *from, uint32_t *to, size_t cap
 static void build_pre_json(shk_asm *h) {
   std::string &j = h->json_pre;
   j.clear(); j.reserve(4096);
-  j += "{\"nkmers\":" + std::to_string(h->st.n_nodes) + ",\"histo\":[";
+  j += "{\"nkmers\":" + std::to_string(h->shard_graph ? h->shard_nodes_global : h->st.n_nodes) + ",\"histo\":[";
   for (int i = 0; i < SHK_HISTO_BINS; ++i) { if (i) j += ','; j += std::to_string(h->histo[i]); }
   j += "],\"used_min_count\":" + std::to_string(h->st.used_min_count) + "}";
 }
@@ -1426,7 +1431,7 @@ shk_status shk_shard_set_nodes(shk_asm *h, const void *d_lo, const void *d_hi, c
     SHK_CUDA(cudaMemcpyAsync(h->node_count.p, d_count, n_total * 2, cudaMemcpyDeviceToDevice, h->stream));
     SHK_CUDA(cudaMemcpyAsync(h->node_raw.p, d_raw, n_total, cudaMemcpyDeviceToDevice, h->stream));
   }
-  h->node_cap = (uint32_t)n_total; h->st.n_nodes = n_total; h->shard_node_offset = my_offset;
+  h->node_cap = (uint32_t)n_total; h->st.n_nodes = n_total; h->shard_node_offset = my_offset; h->shard_graph = false;
   if (histo_global) {
     memcpy(h->histo, histo_global, sizeof h->histo);
     uint64_t nd = 0;

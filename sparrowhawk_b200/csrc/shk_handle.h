@@ -74,6 +74,13 @@ bool revcomp_is_smaller(const char *s, size_t n);
 
 }  // namespace shk
 
+// a peer rank's allocation mapped into this process (cudaIpcOpenMemHandle), kept while the handle bytes stay the same
+struct shk_peer_map {
+  unsigned char handle[64] = {0};
+  void *p = nullptr;
+  bool open = false;
+};
+
 struct shk_contigs {
   shk::CleanGraph g;
 };
@@ -126,6 +133,16 @@ struct shk_asm {
   const void *recv_recs = nullptr;               // caller-owned device buffer (records received from all ranks)
   shk::DevBuf seg_off, seg_cnt, pack_off, send_tot, qbits_dev, shard_btot /* per owned bucket: records | k-mers << 32 over all sources */;
   uint64_t shard_node_offset = 0, shard_nodes_local = 0;
+  // ---- sharded graph stage (shk_shard.cu): peer memory + chain level ----
+  bool shard_graph = false, shard_local_circ = false;
+  uint64_t shard_nodes_global = 0;
+  uint32_t shard_node_off[65] = {0};
+  uint32_t shard_chains_local = 0, shard_chains_global = 0, ns_hint_c = 0;
+  shk::DevBuf arena /* published: slots | off | edges | chain_of_head */, topo, xsucc, chain_head;
+  shk::PinBuf topo_pin;
+  size_t arena_off_slots = 0, arena_off_off = 0, arena_off_edges = 0, arena_off_coh = 0;
+  shk_peer_map peer_maps[64][3];
+  shk::DevBuf c_succ, c_wlen, c_wsum, c_pd, c_split, c_tail, c_len, c_sum, c_uoh, c_kcnt, c_klen, c_tmp;
   // sharded steady-state count (shk_shard_count_device): calibrated by a host-planned run over this many owned buckets / ranks
   uint32_t shard_cal_nb = 0, shard_cal_world = 0;
   bool shard_fast_banned = false, shard_fast_retried = false;

@@ -441,7 +441,7 @@ int launch_rank_lists(const GraphBuffers &g, const uint8_t *circ, uint32_t ns_ca
   WyState *sa = (WyState *)work, *sb = sa + ns_cap;
   u64 *sub_sum = (u64 *)(sb + ns_cap);
   u32 *sub_len = (u32 *)(sub_sum + ns_cap), *last_elem = sub_len + ns_cap, *next_elem = last_elem + ns_cap;
-  k_rank_walk<<<blocks_for(ns_cap, 128), 128, 0, st>>>(g.succ, circ, g.node_count, g.splitters, g.scal + 4, ns_cap, (u64 *)g.pd,
+  k_rank_walk<<<blocks_for(ns_cap, 128), 128, 0, st>>>(g.succ, circ, g.node_count, g.w_len, (const u64 *)g.w_sum, g.splitters, g.scal + 4, ns_cap, (u64 *)g.pd,
                                                        sub_len, sub_sum, last_elem, next_elem);
   // one resident wave of CTAs for the cooperative launch
   static int occ_cache[SHK_MAX_DEVICES] = {0};

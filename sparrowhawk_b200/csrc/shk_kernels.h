@@ -21,6 +21,9 @@ struct GraphBuffers {
   // device scalars: [1] n_cyclic, [2] n_unitigs, [3] n_links, [4] n_splitters, [5] splitter work area too small,
   // [8..9] seq cursor (u64), [10..12] round flags of k_rank_solve
   uint32_t *scal; uint64_t *seq_cursor;
+  // list ranking over WEIGHTED elements (chain level of the sharded path): element e weighs w_len[e >> 1] nodes and
+  // w_sum[e >> 1] k-mer counts; null = node level (weight 1, node_count)
+  const uint32_t *w_len; const uint64_t *w_sum;
 };
 
 size_t slot_bytes(int kw);

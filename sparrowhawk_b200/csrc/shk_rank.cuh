@@ -67,10 +67,13 @@ k_rank_mark(const u32 *__restrict__ succ, const uint8_t *__restrict__ circ, u32 
   if (sp) splitters[cta_base + wcnt[warp] + __popc(ball & ((1u << lane) - 1))] = e;
 }
 
-// per splitter: walk to the next splitter.  loc[e] = splitter index << 32 | local rank.
+// per splitter: walk to the next splitter.  loc[e] = splitter index << 32 | elements (weight) in front of e inside
+// the sublist.  Weights: at node level every element weighs 1 and carries its node's k-mer count; at chain level
+// (sharded path, shk_shard.cuh) element e of chain e >> 1 weighs w_len[e >> 1] nodes and w_sum[e >> 1] counts.
 __global__ void __launch_bounds__(128)
 k_rank_walk(const u32 *__restrict__ succ, const uint8_t *__restrict__ circ,
-            const uint16_t *__restrict__ node_count, const u32 *__restrict__ splitters,
+            const uint16_t *__restrict__ node_count, const u32 *__restrict__ w_len, const u64 *__restrict__ w_sum,
+            const u32 *__restrict__ splitters,
             const u32 *__restrict__ n_splitters_dev, u32 ns_cap, u64 *__restrict__ loc, u32 *__restrict__ sub_len,
             u64 *__restrict__ sub_sum, u32 *__restrict__ last_elem, u32 *__restrict__ next_elem) {
   const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -80,15 +83,16 @@ k_rank_walk(const u32 *__restrict__ succ, const uint8_t *__restrict__ circ,
   u64 sum = 0;
   for (;;) {
     loc[cur] = ((u64)i << 32) | r;
-    sum += node_count[cur >> 1];
+    if (w_len) { r += w_len[cur >> 1]; sum += w_sum[cur >> 1]; }
+    else { r += 1; sum += node_count[cur >> 1]; }
     nxt = __ldg(succ + cur);
     if (nxt == SHK_NONE) break;
     if (circ && circ[nxt] == 2) { nxt = SHK_NONE; break; }   // a cut cycle ends in front of its forced head
     // nxt has a predecessor (cur), so it can only be a splitter by the hash rule
     if (rank_hash_splitter(nxt)) break;
-    cur = nxt; ++r;
+    cur = nxt;
   }
-  sub_len[i] = r + 1; sub_sum[i] = sum; last_elem[i] = cur; next_elem[i] = nxt;
+  sub_len[i] = r; sub_sum[i] = sum; last_elem[i] = cur; next_elem[i] = nxt;
 }
 
 // ---- splitter level, one cooperative launch -------------------------------------------------

@@ -9,13 +9,21 @@ read-evidenced edge bits, S13) meet on one rank:
 
     partition (K1a) -> pack -> all-to-all(fills) -> all-to-all(records)
       -> count + spectrum + filter on the owner (K1b/K2)
-      -> all-reduce(spectrum, totals), all-gather(surviving nodes)
-      -> node index + graph stage (K3..K6)
+      -> all-reduce(spectrum, totals, node counts)
+      -> sharded graph stage: every rank indexes ITS nodes and publishes them as peer memory (CUDA IPC over
+         NVLink); K3'/K4' read a remote neighbour in place; local list ranking turns every stretch of a unitig
+         inside a rank into one chain; the 64-byte chain records are all-gathered and ranked on every rank (the
+         final pointer-jumping pass that joins the unitigs across the shards); every rank emits its own bases and
+         the byte buffers are merged with one all-reduce
+      (fallback, when peer memory is unavailable or an unbranched cycle crosses ranks: all-gather the surviving
+       nodes and run K3..K6 over the gathered set on every rank)
 
 The orchestration is written against a small engine interface so that the
 world_size-2 `gloo` tests on CPU drive exactly this code with a CPU stand-in
 for the device stages; on a GPU box the engine is the C ABI (GpuEngine).
 """
+import os
+
 import numpy as np
 import torch
 import torch.distributed as dist
@@ -107,6 +115,43 @@ class GpuEngine:
     def build_graph(self):
         self.h.build_graph()
 
+    # ---- sharded graph stage (include/shk.h): peer memory, chains, final join ----
+    def graph_publish(self, counts, histo, n_inst, n_bases, used_mc):
+        c = np.ascontiguousarray(counts, dtype=np.uint64)
+        hh = np.ascontiguousarray(histo, dtype=np.uint64)
+        blob = np.zeros(_ffi.PEER_BLOB_BYTES, np.uint8)
+        check(self.lib.shk_shard_graph_publish(self.h._h, c.ctypes.data, hh.ctypes.data, int(n_inst), int(n_bases), int(used_mc),
+                                               blob.ctypes.data))
+        return blob
+
+    def graph_connect(self, blobs):
+        b = np.ascontiguousarray(blobs, dtype=np.uint8)
+        return int(self.lib.shk_shard_graph_connect(self.h._h, b.ctypes.data))      # status: the caller agrees on a fallback
+
+    def graph_edges(self):
+        check(self.lib.shk_shard_graph_edges(self.h._h))
+
+    def graph_chains(self):
+        import ctypes as C
+        n = C.c_uint64()
+        check(self.lib.shk_shard_graph_chains(self.h._h, C.byref(n)))
+        return int(n.value)
+
+    def graph_records(self, chain_counts, out):
+        c = np.ascontiguousarray(chain_counts, dtype=np.uint64)
+        self._rec_keep = out
+        check(self.lib.shk_shard_graph_records(self.h._h, c.ctypes.data, out.data_ptr() if out.numel() else None))
+
+    def graph_join(self, all_recs):
+        import ctypes as C
+        info = _ffi.ShkShardJoinInfo()
+        self._allrec_keep = all_recs
+        check(self.lib.shk_shard_graph_join(self.h._h, all_recs.data_ptr() if all_recs.numel() else None, C.byref(info)))
+        return info
+
+    def graph_set_links(self, lf, lt, n):
+        check(self.lib.shk_shard_graph_set_links(self.h._h, lf.data_ptr() if n else None, lt.data_ptr() if n else None, int(n)))
+
 
 def _staged(group):
     """gloo moves host memory only: device tensors are staged through the host
@@ -140,6 +185,167 @@ def _all_gather(parts, t, group=None):
             p.copy_(c)
     else:
         dist.all_gather(parts, t, group=group)
+
+
+class _DevView:
+    """a device buffer owned by the library, as something torch.as_tensor understands"""
+
+    def __init__(self, ptr, nbytes):
+        self.__cuda_array_interface__ = {"shape": (int(nbytes),), "typestr": "|u1", "data": (int(ptr), False), "version": 2}
+
+
+def _dev_bytes(ptr, nbytes, dev):
+    return torch.as_tensor(_DevView(ptr, nbytes), device=dev)
+
+
+def _ag_flat(flat, t, group=None):
+    """all_gather_into_tensor that also works host-staged over gloo (flat: world * t.numel() elements on t's device)"""
+    if _staged(group) or not t.is_cuda:
+        if t.is_cuda:
+            torch.cuda.synchronize(t.device)
+        o = torch.empty(flat.shape, dtype=flat.dtype)
+        dist.all_gather(list(o.split(t.numel())), t.cpu().contiguous(), group=group)
+        flat.copy_(o)
+    else:
+        dist.all_gather_into_tensor(flat, t, group=group)
+
+
+def _barrier(dev, group=None):
+    """Every rank's queued kernels have completed before any rank's next kernel starts.  NCCL: a one-element
+    all-reduce on the stream (no host wait).  gloo (host-staged): wait for the device, then a host barrier."""
+    if _staged(group) or dev.type != "cuda":
+        if dev.type == "cuda":
+            torch.cuda.synchronize(dev)
+        dist.barrier(group=group)
+    else:
+        dist.all_reduce(torch.zeros(1, dtype=torch.int32, device=dev), group=group)
+
+
+def _gather_host_ints(vals, dev, group=None):
+    """all-gather a few integers per rank -> numpy int64 [world, len(vals)] on the host (stream-ordered on NCCL:
+    also a barrier for what was queued before it)"""
+    world = dist.get_world_size(group)
+    mine = torch.tensor(list(vals), dtype=torch.int64, device=dev)
+    out = torch.empty(world * mine.numel(), dtype=torch.int64, device=dev)
+    _ag_flat(out, mine, group)
+    return out.cpu().numpy().reshape(world, -1)
+
+
+def _gather_var(t, counts, unit, group=None):
+    """all-gather rank r's first counts[r] * unit elements of its 1-D tensor `t` -> one dense tensor in rank order.
+    (NCCL gathers equal sizes: pad to the largest, then squeeze the padding out with one device copy.)"""
+    world = dist.get_world_size(group)
+    n_max = max(list(counts) + [0])
+    if n_max == 0:
+        return t[:0]
+    pad = torch.zeros(n_max * unit, dtype=t.dtype, device=t.device) if t.numel() < n_max * unit else t[:n_max * unit]
+    if t.numel() < n_max * unit and t.numel():
+        pad[:t.numel()] = t
+    flat = torch.empty(world * n_max * unit, dtype=t.dtype, device=t.device)
+    _ag_flat(flat, pad, group)
+    if all(c == n_max for c in counts):
+        return flat
+    return torch.cat([flat[r * n_max * unit: r * n_max * unit + counts[r] * unit] for r in range(world)])
+
+
+def _sharded_graph(eng, group, counts, g_hist, g_inst, g_bases, used_mc, mark):
+    """The graph stage with every rank on its own nodes (include/shk.h "sharded graph stage").  Returns "sharded",
+    or None when this run has to take the replicated stage instead (peer memory unavailable, or an unbranched
+    cycle crosses rank borders) — the same answer on every rank."""
+    world, dev = dist.get_world_size(group), eng.device
+    # 1. index over the owned nodes, peer blob out; the all-gather of the blobs is the barrier "indices complete"
+    blob = eng.graph_publish(counts, g_hist, g_inst, g_bases, used_mc)
+    allb = torch.empty(world * blob.size, dtype=torch.uint8, device=dev)
+    _ag_flat(allb, torch.from_numpy(blob).to(dev), group)
+    blobs = allb.cpu().numpy()
+    # 2. map the peers; every rank must succeed
+    st = eng.graph_connect(blobs)
+    ok = _gather_host_ints([st], dev, group)
+    if int(ok.max()) != 0:
+        if st != 0 and dist.get_rank(group) == 0:
+            import sys
+            print("[shk] peer memory unavailable (%s): replicated graph stage" % _ffi.lib().shk_last_error().decode(errors="replace"),
+                  file=sys.stderr)
+        return None
+    mark("publish")
+    # 3. K3' over the owned nodes; barrier "edges complete"
+    eng.graph_edges()
+    _barrier(dev, group)
+    mark("edges")
+    # 4. K4' + local list ranking: one chain per stretch of a unitig inside this rank
+    nch = eng.graph_chains()
+    chain_counts = [int(x) for x in _gather_host_ints([nch], dev, group)[:, 0]]     # (barrier "chain numbers complete")
+    mark("chains")
+    # 5./6. chain records of all ranks, ranked on every rank: the final pointer-jumping pass
+    rec = torch.empty(nch * 8, dtype=torch.int64, device=dev)
+    eng.graph_records(chain_counts, rec)
+    all_recs = _gather_var(rec, chain_counts, 8, group)
+    info = eng.graph_join(all_recs)
+    if info.n_cyclic_chain_elems:
+        return None
+    mark("join")
+    # the sequence bytes: every rank wrote its own, zeros elsewhere
+    if info.seq_bytes:
+        seq = _dev_bytes(info.d_seq, info.seq_bytes, dev)
+        if _staged(group):
+            c = seq.cpu()
+            dist.all_reduce(c, op=dist.ReduceOp.MAX, group=group)
+            seq.copy_(c)
+        else:
+            dist.all_reduce(seq, op=dist.ReduceOp.MAX, group=group)
+    # the unitig links found by the ranks that own the exit nodes
+    link_counts = [int(x) for x in _gather_host_ints([info.n_links_local], dev, group)[:, 0]]
+    n_links = sum(link_counts)
+    if n_links:
+        nl = int(info.n_links_local)
+        lf = _dev_bytes(info.d_link_from, max(nl, 1) * 4, dev).view(torch.int32)[:nl]
+        lt = _dev_bytes(info.d_link_to, max(nl, 1) * 4, dev).view(torch.int32)[:nl]
+        glf = _gather_var(lf, link_counts, 1, group).contiguous()
+        glt = _gather_var(lt, link_counts, 1, group).contiguous()
+        eng._links_keep = (glf, glt)
+        eng.graph_set_links(glf, glt, n_links)
+    else:
+        eng.graph_set_links(None, None, 0)
+    mark("merge")
+    return "sharded"
+
+
+def _replicated_graph(eng, group, counts, g_hist, g_inst, g_bases, used_mc, mark):
+    """Fallback: all-gather the surviving nodes, node index + K3..K6 over the gathered set on every rank."""
+    world, rank, dev = dist.get_world_size(group), dist.get_rank(group), eng.device
+    i64 = dict(dtype=torch.int64, device=dev)
+    n_max, n_total = max(list(counts) + [1]), sum(counts)
+    # ---- all-gather the surviving nodes: key (high half only when k > 31), count, raw edge bits ----
+    wide = eng.k > 31
+    lo = torch.empty(n_max, **i64); hi = torch.empty(n_max if wide else 0, **i64)
+    cnt = torch.empty(n_max, dtype=torch.int16, device=dev); raw = torch.empty(n_max, dtype=torch.uint8, device=dev)
+    eng.local_nodes(lo, hi, cnt, raw)
+    gathered = []
+    for t in (lo, hi, cnt, raw):
+        b = t.view(torch.uint8)                     # collectives have no 16-bit integer type
+        w = t.element_size()
+        if t.numel() == 0:
+            gathered.append(t)
+            continue
+        if _staged(group) or not b.is_cuda:
+            parts = [torch.empty_like(b) for _ in range(world)]
+            _all_gather(parts, b, group)
+        else:                                        # one NCCL all-gather into one buffer, rank r at r * n_max
+            flat = torch.empty(world * b.numel(), dtype=torch.uint8, device=dev)
+            dist.all_gather_into_tensor(flat, b, group=group)
+            parts = list(flat.split(b.numel()))
+        if all(c == n_max for c in counts) and not (_staged(group) or not b.is_cuda):
+            g = flat                                # nothing to squeeze out
+        else:
+            g = torch.cat([p[:c * w] for p, c in zip(parts, counts)]) if n_total else b[:0]
+        gathered.append(g.view(t.dtype))
+    my_off = sum(counts[:rank])
+    eng.set_nodes(*gathered, n_total, my_off, g_hist, g_inst, g_bases, used_mc)
+    mark("gather_nodes")
+
+    # ---- graph stage over the gathered node set ----
+    eng.build_graph()
+    mark("graph")
 
 
 def sharded_run(eng, group=None, timings=None):
@@ -229,39 +435,14 @@ def sharded_run(eng, group=None, timings=None):
     g_hist = red_h[:500].astype(np.uint64)
     g_inst, g_bases = int(red_h[500]), int(red_h[501])
     counts = [int(c) for c in red_h[502:]]
-    n_max, n_total = max(counts + [1]), sum(counts)
-    # ---- all-gather the surviving nodes: key (high half only when k > 31), count, raw edge bits ----
-    wide = eng.k > 31
-    lo = torch.empty(n_max, **i64); hi = torch.empty(n_max if wide else 0, **i64)
-    cnt = torch.empty(n_max, dtype=torch.int16, device=dev); raw = torch.empty(n_max, dtype=torch.uint8, device=dev)
-    eng.local_nodes(lo, hi, cnt, raw)
-    gathered = []
-    for t in (lo, hi, cnt, raw):
-        b = t.view(torch.uint8)                     # collectives have no 16-bit integer type
-        w = t.element_size()
-        if t.numel() == 0:
-            gathered.append(t)
-            continue
-        if _staged(group) or not b.is_cuda:
-            parts = [torch.empty_like(b) for _ in range(world)]
-            _all_gather(parts, b, group)
-        else:                                        # one NCCL all-gather into one buffer, rank r at r * n_max
-            flat = torch.empty(world * b.numel(), dtype=torch.uint8, device=dev)
-            dist.all_gather_into_tensor(flat, b, group=group)
-            parts = list(flat.split(b.numel()))
-        if all(c == n_max for c in counts) and not (_staged(group) or not b.is_cuda):
-            g = flat                                # nothing to squeeze out
-        else:
-            g = torch.cat([p[:c * w] for p, c in zip(parts, counts)]) if n_total else b[:0]
-        gathered.append(g.view(t.dtype))
-    my_off = sum(counts[:rank])
-    eng.set_nodes(*gathered, n_total, my_off, g_hist, g_inst, g_bases, used_mc)
-    mark("gather_nodes")
-
-    # ---- graph stage over the gathered node set ----
-    eng.build_graph()
-    mark("graph")
+    n_total = sum(counts)
+    graph_mode = None
+    if hasattr(eng, "graph_publish") and os.environ.get("SHK_SHARD_GRAPH", "1") != "0":
+        graph_mode = _sharded_graph(eng, group, counts, g_hist, g_inst, g_bases, used_mc, mark)
+    if graph_mode is None:
+        _replicated_graph(eng, group, counts, g_hist, g_inst, g_bases, used_mc, mark)
+        graph_mode = "replicated"
     return {"world": world, "n_buckets": P, "n_bases": g_bases, "n_positions": g_pos, "n_instances": g_inst,
             "n_nodes": n_total, "nodes_per_rank": counts, "used_min_count": used_mc, "histo": g_hist,
-            "send_records": send_records, "recv_records": recv_records,
+            "send_records": send_records, "recv_records": recv_records, "graph_mode": graph_mode,
             "a2a_bytes_out": int(sum(send_records[r] for r in range(world) if r != rank)) * rw * 8}

@@ -25,11 +25,13 @@ def run_oracle(seq, qual, k, min_count, min_qual, nthreads=4):
     return o
 
 
-def assert_parity(helper, oracle, check_table=True, check_unitigs=True):
+def assert_parity(helper, oracle, check_table=True, check_unitigs=True, kmers=None):
     """helper: AssemblyHelper after run() (or count+filter+build_graph with the
-    table exported beforehand via `helper._table`)."""
+    table exported beforehand via `helper._table`).  kmers: the filtered k-mers to compare instead of the
+    helper's own export — the sharded path, where a handle exports ITS rank's nodes and the caller has
+    gathered the exports of all ranks."""
     so, sg = oracle.stats(), helper.stats()
-    for f in ("n_bases", "n_instances", "n_distinct", "n_nodes"):
+    for f in ("n_bases", "n_instances", "n_distinct") + (() if kmers is not None else ("n_nodes",)):
         assert sg[f] == so[f], (f, sg[f], so[f])
     assert np.array_equal(helper.histogram(), oracle.histogram()), "spectrum differs"
     if check_table and getattr(helper, "_table", None) is not None:
@@ -39,8 +41,9 @@ def assert_parity(helper, oracle, check_table=True, check_unitigs=True):
         assert np.array_equal(glo, olo) and np.array_equal(ghi, ohi), "distinct k-mer sets differ"
         assert np.array_equal(gc, np.minimum(oc, 65535)), "counts differ"
         assert np.array_equal(ge, oe), "read-evidenced edge bits differ"
-    glo, ghi, gc, graw, gval = sort_by_key(*helper.export_kmers())
+    glo, ghi, gc, graw, gval = sort_by_key(*(kmers if kmers is not None else helper.export_kmers()))
     olo, ohi, oc, oraw, oval = oracle.export_kmers()
+    assert len(glo) == so["n_nodes"], (len(glo), so["n_nodes"])
     assert np.array_equal(glo, olo) and np.array_equal(ghi, ohi), "filtered k-mer sets differ"
     assert np.array_equal(gc, oc), "filtered counts differ"
     assert np.array_equal(graw, oraw), "raw edge bits differ"

@@ -4,9 +4,11 @@
 mode cpu : gloo, CPU tensors, the device stages replaced by a numpy stand-in built
            on the oracle (CpuEngine) — covers ownership, split sizes, segment
            layout, spectrum reduction and node gathering of sparrowhawk_b200.dist.
-mode gpu : gloo, the real C ABI engine; all ranks share cuda:0 and run their
-           kernels one after the other (host-level collectives only), every rank
-           then checks the complete result against the oracle.
+mode gpu : gloo, the real C ABI engine; all ranks share cuda:0 (collectives staged through the
+           host, peer memory mapped between the processes on the one device), every rank then
+           checks the complete result against the oracle.
+mode nccl: the same over NCCL with one device per rank — the path bench.py times.
+options  : fit (do_fit), circular (unbranched cycles across the ranks), expect=<graph stage>.
 Exit code 0 = every assertion on this rank passed.
 """
 import os
@@ -120,15 +122,39 @@ class CpuEngine:
 
 def main():
     mode, k, min_count, G, cov = sys.argv[1], int(sys.argv[2]), int(sys.argv[3]), int(sys.argv[4]), float(sys.argv[5])
-    dist.init_process_group("gloo")
+    opts = sys.argv[6:]
+    do_fit = "fit" in opts
+    expect_mode = next((x.split("=")[1] for x in opts if x.startswith("expect=")), None)
+    circular = "circular" in opts
+    if mode == "nccl":
+        local = int(os.environ.get("LOCAL_RANK", "0"))
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    else:
+        dist.init_process_group("gloo")
     rank, world = dist.get_rank(), dist.get_world_size()
     min_qual, err, L = 20, 0.01, 150
-    npairs = synth.num_pairs(G, cov, L)
-    lo_p, hi_p = split_pairs(npairs, world, rank)
-    seq, qual = synth.reads(7, G, cov, err, L, pair_range=(lo_p, hi_p))
-    all_seq, all_qual = synth.reads(7, G, cov, err, L)
+    if circular:
+        # error-free reads tiled around two circular replicons: unbranched cycles that cross the rank borders
+        all_seq, all_qual = circular_reads(G, k)
+        n_reads = int((all_seq == 10).sum())
+        lo_r, hi_r = rank * n_reads // world, (rank + 1) * n_reads // world
+        ends = np.flatnonzero(all_seq == 10)
+        a0 = 0 if lo_r == 0 else int(ends[lo_r - 1]) + 1
+        a1 = int(ends[hi_r - 1]) + 1 if hi_r else 0
+        seq, qual = all_seq[a0:a1].copy(), all_qual[a0:a1].copy()
+    else:
+        npairs = synth.num_pairs(G, cov, L)
+        lo_p, hi_p = split_pairs(npairs, world, rank)
+        seq, qual = synth.reads(7, G, cov, err, L, pair_range=(lo_p, hi_p))
+        all_seq, all_qual = synth.reads(7, G, cov, err, L)
     o = Oracle(k, min_count, min_qual, 2)
     o.add_reads(all_seq, all_qual); o.finish_count(); o.build_graph()
+    if do_fit:                                   # the oracle at the min_count the fit of ITS spectrum gives
+        from oracle import pyref
+        fitted = pyref.fit_min_count([int(x) for x in o.histogram()], min_count)
+        o = Oracle(k, fitted, min_qual, 2)
+        o.add_reads(all_seq, all_qual); o.finish_count(); o.build_graph()
     so = o.stats()
     if mode == "cpu":
         eng = CpuEngine(seq, qual, k, min_count, min_qual)
@@ -149,27 +175,75 @@ def main():
         assert ((b[a:z] >= blo) & (b[a:z] < bhi)).all() and not ((b[:a] >= blo) & (b[:a] < bhi)).any()
         assert info["recv_records"][rank] == info["send_records"][rank]
     else:
-        from parity import assert_parity
-        from sparrowhawk_b200 import AssemblyHelper
-        from sparrowhawk_b200.dist import GpuEngine
-        torch.cuda.set_device(0)
-        h = AssemblyHelper.new(k, False, min_count, min_qual, 0, False, False, False, False, device=0)
-        h.load_reads(seq, qual)
-        eng = GpuEngine(h, torch.device("cuda", 0))
-        planned = []
-        for _ in range(3):                 # the first pass calibrates (host-planned count); later ones reuse buffers and
-            info = sharded_run(eng)        # estimates and count with the fills left on the device (shk_shard_count_device)
-            planned.append(h.stats()["device_planned"])
-            assert info["n_nodes"] == so["n_nodes"], (info["n_nodes"], so["n_nodes"])
-            assert_parity(h, o, check_table=False)
-        print(f"rank {rank}: device-planned count per pass {planned}")
-        assert planned[-1] == 1, planned
-        if world > 1:
-            assert min(info["nodes_per_rank"]) > 0
-        h.close()
+        gpu_rank_checks(mode, rank, world, k, min_count, min_qual, seq, qual, o, so, do_fit=do_fit, expect_mode=expect_mode)
     dist.barrier()
     dist.destroy_process_group()
     print(f"rank {rank}/{world} ok: {so['n_nodes']} nodes, {so['n_unitigs']} unitigs")
+
+
+def circular_reads(G, k):
+    """150-base error-free reads, one every 25 bases, around two circular sequences of G and G // 3 bases (and a
+    linear one): every k-mer of the circles is seen six times, nothing branches, so each circle is ONE circular
+    unitig (S14) whose nodes are spread over all ranks."""
+    rng = np.random.default_rng(11)
+    reads = []
+    for n, circ in ((G, True), (G // 3, True), (G // 2, False)):
+        g = rng.integers(0, 4, size=n)
+        s = np.frombuffer(b"ACGT", np.uint8)[g]
+        ext = np.concatenate([s, s[:150]]) if circ else s
+        for p in range(0, (n if circ else n - 150), 25):
+            reads.append(ext[p:p + 150].tobytes())
+    seq = b"".join(r + b"\n" for r in reads)
+    qual = b"".join(b"I" * len(r) + b"\n" for r in reads)
+    return np.frombuffer(seq, np.uint8).copy(), np.frombuffer(qual, np.uint8).copy()
+
+
+def gathered_kmers(h, info):
+    """the filtered k-mers of ALL ranks (every rank exports its own slice on the sharded graph path)"""
+    mine = h.export_kmers()
+    if info["graph_mode"] != "sharded":
+        return mine
+    parts = [None] * dist.get_world_size()
+    dist.all_gather_object(parts, mine)
+    return tuple(np.concatenate([p[i] for p in parts]) for i in range(5))
+
+
+def gpu_rank_checks(mode, rank, world, k, min_count, min_qual, seq, qual, o, so, do_fit=False, expect_mode=None):
+    """the real C ABI engine on this rank: mode "gpu" = gloo, every rank on cuda:0; mode "nccl" = one device per rank"""
+    import json
+    from parity import assert_parity, canon_link_tuples, canon_links, oracle_graph
+    from sparrowhawk_b200 import AssemblyHelper
+    from sparrowhawk_b200.dist import GpuEngine
+    devi = rank if mode == "nccl" else 0
+    torch.cuda.set_device(devi)
+    h = AssemblyHelper.new(k, False, min_count, min_qual, 0, False, do_fit, False, False, device=devi)
+    h.load_reads(seq, qual)
+    eng = GpuEngine(h, torch.device("cuda", devi))
+    planned, modes = [], []
+    for _ in range(3):                 # the first pass calibrates (host-planned count); later ones reuse buffers and
+        info = sharded_run(eng)        # estimates and count with the fills left on the device (shk_shard_count_device)
+        planned.append(h.stats()["device_planned"]); modes.append(info["graph_mode"])
+        assert info["n_nodes"] == so["n_nodes"], (info["n_nodes"], so["n_nodes"])
+        assert_parity(h, o, check_table=False, kmers=gathered_kmers(h, info))
+        assert json.loads(h.get_preprocessing_info())["nkmers"] == so["n_nodes"]
+    # unitig-level links of the complete graph (every rank holds them) against the oracle's
+    units, _, _ = h.export_unitigs()
+    lf, lt = h.export_links()
+    ou, _okc, _oc, olinks = oracle_graph(o, k)
+    assert canon_links(units, lf, lt) == canon_link_tuples(ou, olinks), "unitig links differ"
+    print(f"rank {rank}: device-planned count per pass {planned}, graph stage {modes}")
+    assert planned[-1] == 1 or do_fit, planned
+    if expect_mode:
+        assert modes == [expect_mode] * 3, modes
+    if world > 1:
+        assert min(info["nodes_per_rank"]) > 0
+    # the host tail on every rank: same contigs everywhere
+    h.assemble()
+    res = json.loads(h.get_assembly())
+    outs = [None] * world
+    dist.all_gather_object(outs, (res["ncontigs"], res["outfasta"]))
+    assert all(x == outs[0] for x in outs), "ranks disagree on the assembly"
+    h.close()
 
 
 if __name__ == "__main__":

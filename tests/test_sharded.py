@@ -54,4 +54,51 @@ def test_sharded_orchestration_gloo_cpu(world, k):
 @pytest.mark.gpu
 @pytest.mark.parametrize("world,k,G", [(2, 31, 60000), (2, 63, 40000), (3, 31, 30000), (1, 31, 30000)])
 def test_sharded_gpu_matches_oracle(world, k, G):
-    _launch(world, "gpu", k, 3, G, 30.0)
+    """gloo, every rank on cuda:0: the sharded graph stage (peer memory between the processes, chains joined by
+    the chain-level ranking) must be the one that ran, and every rank must hold the oracle's graph."""
+    _launch(world, "gpu", k, 3, G, 30.0, "expect=sharded")
+
+
+@pytest.mark.gpu
+def test_sharded_gpu_replicated_stage_still_exact(monkeypatch):
+    monkeypatch.setenv("SHK_SHARD_GRAPH", "0")
+    _launch(2, "gpu", 31, 3, 40000, 30.0, "expect=replicated")
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("world,k", [(2, 31), (3, 63)])
+def test_sharded_gpu_cycles_across_ranks(world, k):
+    """circular replicons whose single unitig is spread over all ranks (S14: cut at the minimum k-mer)"""
+    _launch(world, "gpu", k, 2, 6000, 0.0, "circular")
+
+
+@pytest.mark.gpu
+def test_sharded_gpu_do_fit():
+    """the do_fit branch of the sharded run: spectrum all-reduced, fitted on every rank, counted at the fit"""
+    _launch(2, "gpu", 31, 5, 100000, 25.0, "fit")
+
+
+def _n_devices():
+    try:
+        import torch
+        return torch.cuda.device_count()
+    except Exception:
+        return 0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("world,k,G", [(2, 31, 200000), (2, 63, 100000)])
+def test_sharded_nccl_matches_oracle(world, k, G):
+    """the path bench.py times at N > 1: NCCL, one device per rank, peer memory over NVLink — against the oracle on
+    every rank.  Needs as many devices as ranks."""
+    if _n_devices() < world:
+        pytest.skip(f"needs {world} devices")
+    _launch(world, "nccl", k, 3, G, 30.0, "expect=sharded")
+
+
+@pytest.mark.gpu
+def test_sharded_nccl_cycles_and_fit():
+    if _n_devices() < 2:
+        pytest.skip("needs 2 devices")
+    _launch(2, "nccl", 31, 2, 6000, 0.0, "circular")
+    _launch(2, "nccl", 31, 5, 100000, 25.0, "fit")
