@@ -325,6 +325,8 @@ shk_status shk_shard_set_nodes(shk_asm *h, const void *d_lo, const void *d_hi,
 /*   host: all-gather the records                                       */
 /*   6 shk_shard_graph_join       chain-level ranking on every rank,    */
 /*                                unitig table, this rank's bases+links */
+/*     (cycles across ranks: shk_shard_graph_cycle_info, all-gather,    */
+/*      join again — see shk_shard_join_info)                           */
 /*   host: byte-wise all-reduce (max) of the sequence buffer,           */
 /*         all-gather of the links                                      */
 /*   7 shk_shard_graph_set_links  the gathered links                    */
@@ -342,9 +344,9 @@ typedef struct shk_shard_join_info {
   void *d_seq;                    /* device: this rank's bases at their global offsets, zero elsewhere */
   uint64_t n_links_local;         /* unitig links found by this rank */
   void *d_link_from, *d_link_to;  /* device: u32[n_links_local] each */
-  uint64_t n_cyclic_chain_elems;  /* != 0: an unbranched cycle crosses rank borders and nothing below was produced; take
-                                   * the replicated graph stage (shk_shard_local_nodes / shk_shard_set_nodes /
-                                   * shk_build_graph) for this read set */
+  uint64_t n_cyclic_chain_elems;  /* != 0 (join called without cycle info): an unbranched cycle of the graph crosses rank
+                                   * borders and nothing above was produced — all-gather shk_shard_graph_cycle_info
+                                   * and call shk_shard_graph_join again with it */
 } shk_shard_join_info;
 /* node_counts (HOST, u64[world]): surviving nodes of every rank; the other arguments as in shk_shard_set_nodes.
  * blob_out (HOST, SHK_PEER_BLOB_BYTES): what the other ranks need to map this rank's arrays. */
@@ -358,8 +360,14 @@ shk_status shk_shard_graph_edges(shk_asm *h);
 shk_status shk_shard_graph_chains(shk_asm *h, uint64_t *n_chains_out);
 /* chain_counts (HOST, u64[world]); d_records_out (device, 64 bytes x this rank's chains). */
 shk_status shk_shard_graph_records(shk_asm *h, const uint64_t *chain_counts, void *d_records_out);
-/* d_all_records (device): the records of all ranks in rank order. */
-shk_status shk_shard_graph_join(shk_asm *h, const void *d_all_records, shk_shard_join_info *info);
+/* d_all_records (device): the records of all ranks in rank order.  d_all_cycle_info (device, nullable): the
+ * gathered output of shk_shard_graph_cycle_info, 24 bytes per chain, same order — needed only when a first call
+ * reported chains on a cycle (a circular replicon whose one unitig is spread over the ranks, S14). */
+shk_status shk_shard_graph_join(shk_asm *h, const void *d_all_records, const void *d_all_cycle_info,
+                                shk_shard_join_info *info);
+/* d_out (device, 24 bytes x this rank's chains): for every chain of this rank that lies on a cycle of chains, the
+ * minimum canonical k-mer inside it and its position (all ones for the other chains). */
+shk_status shk_shard_graph_cycle_info(shk_asm *h, void *d_out);
 shk_status shk_shard_graph_set_links(shk_asm *h, const void *d_from, const void *d_to, uint64_t n_links);
 
 /* The host-side spectrum fit used by do_fit (docs/src/assembly.md:16). */

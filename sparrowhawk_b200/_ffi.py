@@ -105,7 +105,8 @@ SYMBOLS = {
     "shk_shard_graph_edges": (C.c_int, [_H]),
     "shk_shard_graph_chains": (C.c_int, [_H, C.POINTER(C.c_uint64)]),
     "shk_shard_graph_records": (C.c_int, [_H, C.c_void_p, C.c_void_p]),
-    "shk_shard_graph_join": (C.c_int, [_H, C.c_void_p, C.c_void_p]),
+    "shk_shard_graph_join": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "shk_shard_graph_cycle_info": (C.c_int, [_H, C.c_void_p]),
     "shk_shard_graph_set_links": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_uint64]),
 }
 

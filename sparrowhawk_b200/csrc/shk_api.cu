@@ -1101,7 +1101,7 @@ shk_status shk_export_links(shk_asm *h, uint32_t *from, uint32_t *to, size_t cap
 }
 
 // ---- reference-facing entry points -------------------------------------------
-static void build_pre_json(shk_asm *h) {
+void shk_internal_build_pre_json(shk_asm *h) {
   std::string &j = h->json_pre;
   j.clear(); j.reserve(4096);
   j += "{\"nkmers\":" + std::to_string(h->shard_graph ? h->shard_nodes_global : h->st.n_nodes) + ",\"histo\":[";
@@ -1125,7 +1125,7 @@ static shk_status finish_preprocess(shk_asm *h, const char *mode, bool need_coun
   if (need_count) SHK_TRY(count_filter(h, mc));
   else SHK_TRY(filter_impl(h, mc));
   progress(h, "preprocess:saving");
-  build_pre_json(h);
+  shk_internal_build_pre_json(h);
   progress(h, "preprocess:end");
   return SHK_OK;
 }
@@ -1441,7 +1441,7 @@ shk_status shk_shard_set_nodes(shk_asm *h, const void *d_lo, const void *d_hi, c
   h->st.n_instances = n_instances_global; h->st.n_bases = n_bases_global; h->n_bases = n_bases_global;
   if (used_min_count >= 0) h->st.used_min_count = used_min_count;
   SHK_TRY(index_impl(h));
-  build_pre_json(h);
+  shk_internal_build_pre_json(h);
   return SHK_OK;
 }
 

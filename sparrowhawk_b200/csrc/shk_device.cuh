@@ -89,16 +89,15 @@ __device__ __forceinline__ u128 kmask_of(int k, u128) {
 // arrives on.
 template <class K>
 __device__ __forceinline__ K neighbour_key(K X, int k, int side, u32 base, int &s_in) {
-  K km = kmask_of(k, (K)0);
-  if (side == 0) {
-    K Y = ((X << 2) | (K)base) & km, r = revcomp_key(Y, k);
-    if (Y < r) { s_in = 1; return Y; }
-    s_in = 0; return r;
-  } else {
-    K W = (X >> 2) | ((K)base << (2 * (k - 1))), r = revcomp_key(W, k);
-    if (W < r) { s_in = 0; return W; }
-    s_in = 1; return r;
-  }
+  // branch-free: the lanes of a warp ask for different sides, and what follows (minimizer, index probes) is long
+  const K km = kmask_of(k, (K)0);
+  const K R = ((X << 2) | (K)base) & km;                         // side 0: X . b
+  const K Lf = (X >> 2) | ((K)base << (2 * (k - 1)));            // side 1: a . X
+  const K F = side == 0 ? R : Lf;
+  const K r = revcomp_key(F, k);
+  const bool fwd = F < r;
+  s_in = (fwd ? 1 : 0) ^ side;      // side 0: the edge arrives on the left (1) of a forward neighbour; side 1: mirrored
+  return fwd ? F : r;
 }
 
 __device__ __forceinline__ int side_bits(u32 e, int side) { return side == 0 ? (e & 15) : ((e >> 4) & 15); }

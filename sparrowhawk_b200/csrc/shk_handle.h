@@ -142,7 +142,7 @@ struct shk_asm {
   shk::PinBuf topo_pin;
   size_t arena_off_slots = 0, arena_off_off = 0, arena_off_edges = 0, arena_off_coh = 0;
   shk_peer_map peer_maps[64][3];
-  shk::DevBuf c_succ, c_wlen, c_wsum, c_pd, c_split, c_tail, c_len, c_sum, c_uoh, c_kcnt, c_klen, c_tmp;
+  shk::DevBuf c_succ, c_wlen, c_wsum, c_pd, c_split, c_tail, c_len, c_sum, c_uoh, c_kcnt, c_klen, c_tmp, c_rot, c_cq, c_circ, c_mlo, c_mhi;
   // sharded steady-state count (shk_shard_count_device): calibrated by a host-planned run over this many owned buckets / ranks
   uint32_t shard_cal_nb = 0, shard_cal_world = 0;
   bool shard_fast_banned = false, shard_fast_retried = false;
@@ -194,3 +194,4 @@ shk_status fetch_unitigs(shk_asm *h);
 }  // namespace shk
 extern "C" shk_status shk_internal_flush_batch(shk_asm *h, bool final_batch);
 extern "C" shk_status shk_internal_finish_preprocess(shk_asm *h, const char *mode);
+extern "C" void shk_internal_build_pre_json(shk_asm *h);

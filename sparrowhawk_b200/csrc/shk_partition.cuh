@@ -120,8 +120,11 @@ __device__ __forceinline__ u32 minimizer_hash_of(K key, int k) {
   u32 fw = (u32)(key >> (2 * (k - m))) & mmask;                  // the first m bases
   u32 rc = revcomp_m(fw, m);
   u32 best = mmer_hash(min(fw, rc));
+  // the bases behind them, top aligned, shifted out two bits at a time (no variable shift inside the loop)
+  K rest = w > 1 ? key << (8 * (int)sizeof(K) - 2 * (k - m)) : (K)0;
   for (int j = 1; j < w; ++j) {
-    const u32 nb = (u32)(key >> (2 * (k - m - j))) & 3u;
+    const u32 nb = (u32)(rest >> (8 * (int)sizeof(K) - 2));
+    rest <<= 2;
     fw = ((fw << 2) | nb) & mmask;
     rc = (rc >> 2) | ((nb ^ 2u) << sh);
     best = min(best, mmer_hash(min(fw, rc)));

@@ -114,6 +114,7 @@ shk_status shk_shard_graph_publish(shk_asm *h, const uint64_t *node_counts, cons
   memcpy(blob_out, &b, sizeof b);
   h->filtered = true; h->graphed = false; h->hu.valid = false;
   h->shard_graph = true;
+  shk_internal_build_pre_json(h);                      // nkmers = the global node count
   return SHK_OK;
 }
 
@@ -257,8 +258,28 @@ shk_status shk_shard_graph_records(shk_asm *h, const uint64_t *chain_counts, voi
   return SHK_OK;
 }
 
+// ---- 5b. cycle info: only when shk_shard_graph_join reported chains on a cycle (n_cyclic_chain_elems != 0) --------
+shk_status shk_shard_graph_cycle_info(shk_asm *h, void *d_out) {
+  SHK_TRY(require_device(h));
+  if (!h->shard_graph) { set_error("shard_graph_cycle_info before publish"); return SHK_ERR_STATE; }
+  const uint32_t nc = h->shard_chains_local, N = (uint32_t)h->shard_nodes_local;
+  if (!nc) return SHK_OK;
+  if (!d_out) { set_error("null cycle-info buffer"); return SHK_ERR_BAD_ARG; }
+  SHK_CUDA(cudaMemsetAsync(d_out, 0xFF, (size_t)nc * sizeof(ChainMin), h->stream));
+  const ShardTopo *t = (const ShardTopo *)h->topo.p;
+  const uint32_t *coh = (const uint32_t *)((uint8_t *)h->arena.p + h->arena_off_coh);
+  const unsigned eb = (unsigned)((2 * (size_t)N + 255) / 256);
+  const u64 *hi = h->kw == 2 ? h->node_hi.as<u64>() : nullptr;
+  k_chain_min<0><<<eb, 256, 0, h->stream>>>(t, h->pd.as<u64>(), coh, h->c_pd.as<u64>(), h->node_lo.as<u64>(), hi, 2 * N, (ChainMin *)d_out);
+  k_chain_min<1><<<eb, 256, 0, h->stream>>>(t, h->pd.as<u64>(), coh, h->c_pd.as<u64>(), h->node_lo.as<u64>(), hi, 2 * N, (ChainMin *)d_out);
+  k_chain_min<2><<<eb, 256, 0, h->stream>>>(t, h->pd.as<u64>(), coh, h->c_pd.as<u64>(), h->node_lo.as<u64>(), hi, 2 * N, (ChainMin *)d_out);
+  h->st.gpu_launches += 3;
+  SHK_CUDA(cudaGetLastError());
+  return SHK_OK;
+}
+
 // ---- 6. join: the gathered chains ranked on every rank, unitig table, this rank's bases and links ---------------
-shk_status shk_shard_graph_join(shk_asm *h, const void *d_all_records, shk_shard_join_info *info) {
+shk_status shk_shard_graph_join(shk_asm *h, const void *d_all_records, const void *d_all_cycle_info, shk_shard_join_info *info) {
   SHK_TRY(require_device(h));
   if (!h->shard_graph || !info) { set_error("shard_graph_join before publish / null argument"); return SHK_ERR_STATE; }
   memset(info, 0, sizeof *info);
@@ -270,6 +291,7 @@ shk_status shk_shard_graph_join(shk_asm *h, const void *d_all_records, shk_shard
   if (!C) { SHK_CUDA(cudaEventRecord(h->ev[7], h->stream)); SHK_CUDA(cudaStreamSynchronize(h->stream)); h->graphed = true; return SHK_OK; }
   if (!d_all_records) { set_error("null record buffer"); return SHK_ERR_BAD_ARG; }
   const ChainRec *recs = (const ChainRec *)d_all_records;
+  const ChainMin *cmin = (const ChainMin *)d_all_cycle_info;
   // chain-level buffers
   SHK_TRY(h->c_succ.ensure(ce * 4)); SHK_TRY(h->c_wlen.ensure((size_t)C * 4)); SHK_TRY(h->c_wsum.ensure((size_t)C * 8));
   SHK_TRY(h->c_pd.ensure(ce * 8)); SHK_TRY(h->c_split.ensure(ce * 4)); SHK_TRY(h->c_tail.ensure(ce * 4));
@@ -277,6 +299,7 @@ shk_status shk_shard_graph_join(shk_asm *h, const void *d_all_records, shk_shard
   SHK_TRY(h->c_kcnt.ensure((ce + 2) * 4)); SHK_TRY(h->c_klen.ensure((ce + 2) * 8));
   SHK_TRY(h->c_tmp.ensure((scan_tmp_entries(ce) + 2) * 8));
   SHK_TRY(h->recs.ensure((size_t)C * sizeof(UnitigRecS))); SHK_TRY(h->ucirc.ensure(C)); SHK_TRY(h->cov_sum.ensure((size_t)C * 8));
+  SHK_TRY(h->c_rot.ensure((size_t)C * 4));
   const uint64_t seq_bound = (uint64_t)h->shard_nodes_global + (uint64_t)C * (uint64_t)(k - 1);   // every unitig has >= one chain
   SHK_TRY(h->useq.ensure(seq_bound + 16));
   uint32_t link_cap = (uint32_t)std::min<uint64_t>((uint64_t)N / 2 + 4096, 0x7FFFFFFFull);
@@ -295,33 +318,50 @@ shk_status shk_shard_graph_join(shk_asm *h, const void *d_all_records, shk_shard
   k_chain_unpack<<<cb, 256, 0, h->stream>>>(recs, C, gc.succ, h->c_wlen.as<u32>(), h->c_wsum.as<u64>()); ++L;
   uint32_t ns_cap = (uint32_t)std::min<uint64_t>(ce, std::max<uint64_t>(ce / 4 + 65536, (uint64_t)h->ns_hint_c + h->ns_hint_c / 4 + 1024));
   u32 *kcnt = h->c_kcnt.as<u32>(); u64 *klen = h->c_klen.as<u64>();
-  for (int attempt = 0;; ++attempt) {
-    if (attempt > 3) { set_error("chain-level ranking did not settle after retries"); return SHK_ERR_STATE; }
+  const uint8_t *circ_c = nullptr;
+  // one pass: rank the chain-level lists, pick the kept one of each mirror pair, number the unitigs by prefix scans
+  auto pass = [&]() -> shk_status {
     SHK_TRY(h->rank_work.ensure((size_t)ns_cap * rank_splitter_bytes() + 64));
     SHK_CUDA(cudaMemsetAsync(h->c_pd.p, 0xFF, ce * 8, h->stream));
     SHK_CUDA(cudaMemsetAsync(gc.scal, 0, 64, h->stream));
     SHK_CUDA(cudaMemsetAsync(h->c_tail.p, 0xFF, ce * 4, h->stream));
-    L += launch_rank_mark(gc, nullptr, h->stream);
-    L += launch_rank_lists(gc, nullptr, ns_cap, h->rank_work.p, h->stream);
-    k_chain_heads<<<ceb, 256, 0, h->stream>>>((const u64 *)gc.pd, gc.tail_of, gc.len_of, recs, (u32)ce, k, kcnt, klen); ++L;
+    L += launch_rank_mark(gc, circ_c, h->stream);
+    L += launch_rank_lists(gc, circ_c, ns_cap, h->rank_work.p, h->stream);
+    k_chain_heads<<<ceb, 256, 0, h->stream>>>((const u64 *)gc.pd, gc.tail_of, gc.len_of, recs, circ_c, cmin, h->c_wlen.as<u32>(), (u32)ce, k, kcnt, klen); ++L;
     L += launch_exclusive_scan<u32>(kcnt, ce, (u32 *)h->c_tmp.p, h->stream);
     L += launch_exclusive_scan<u64>(klen, ce, (u64 *)h->c_tmp.p, h->stream);
-    k_chain_unitigs<<<ceb, 256, 0, h->stream>>>((const u64 *)gc.pd, gc.len_of, (const u64 *)gc.sum_of, recs, kcnt, klen, (u32)ce, k, h->c_uoh.as<u32>(),
-                                               (UnitigRecS *)h->recs.p, h->ucirc.as<uint8_t>(), h->cov_sum.as<u64>()); ++L;
+    k_chain_unitigs<<<ceb, 256, 0, h->stream>>>((const u64 *)gc.pd, gc.len_of, (const u64 *)gc.sum_of, recs, circ_c, cmin, h->c_wlen.as<u32>(), kcnt, klen,
+                                               (u32)ce, k, h->c_uoh.as<u32>(), (UnitigRecS *)h->recs.p, h->ucirc.as<uint8_t>(), h->cov_sum.as<u64>(),
+                                               h->c_rot.as<u32>()); ++L;
     // totals to the scalar block: [2] unitigs, [8..9] sequence bytes
     SHK_CUDA(cudaMemcpyAsync(gc.scal + 2, kcnt + ce, 4, cudaMemcpyDeviceToDevice, h->stream));
     SHK_CUDA(cudaMemcpyAsync(gc.scal + 8, klen + ce, 8, cudaMemcpyDeviceToDevice, h->stream));
     SHK_CUDA(cudaGetLastError());
-    SHK_TRY(read_back(h, hs));
+    return read_back(h, hs);
+  };
+  for (int attempt = 0;; ++attempt) {
+    if (attempt > 3) { set_error("chain-level ranking did not settle after retries"); return SHK_ERR_STATE; }
+    SHK_TRY(pass());
     if (hs[5]) { h->ns_hint_c = hs[4]; ns_cap = (uint32_t)std::min<uint64_t>(ce, (uint64_t)hs[4] + 1024); continue; }
     h->ns_hint_c = hs[4];
     break;
   }
-  info->n_cyclic_chain_elems = hs[1];
   if (hs[1]) {
-    // a cycle that crosses rank borders: the caller takes the replicated graph stage for this read set
-    h->graphed = false;
-    return SHK_OK;
+    // chains on a cycle: an unbranched cycle of the graph crosses rank borders
+    info->n_cyclic_chain_elems = hs[1];
+    if (!cmin) { h->graphed = false; return SHK_OK; }           // the caller gathers shk_shard_graph_cycle_info and calls again
+    const uint32_t n_cyclic = hs[1];
+    SHK_TRY(h->c_cq.ensure(2 * ce * 8)); SHK_TRY(h->c_circ.ensure(ce));
+    SHK_TRY(h->c_mlo.ensure((size_t)C * 8)); SHK_TRY(h->c_mhi.ensure((size_t)C * 8));
+    k_chain_min_unpack<<<cb, 256, 0, h->stream>>>(cmin, C, h->c_mlo.as<u64>(), h->c_mhi.as<u64>()); ++L;
+    gc.node_lo = h->c_mlo.as<uint64_t>(); gc.node_hi = h->c_mhi.as<uint64_t>();
+    gc.cq = h->c_cq.as<uint64_t>(); gc.circ = h->c_circ.as<uint8_t>();
+    L += launch_cycle_cut(gc, n_cyclic, h->stream);
+    ns_cap = (uint32_t)std::min<uint64_t>(ce, (uint64_t)std::max(ns_cap, hs[4]) + n_cyclic + 64);
+    circ_c = gc.circ;
+    SHK_TRY(pass());
+    if (hs[5] || hs[1]) { set_error("chain-level ranking left %u elements unranked", hs[1]); return SHK_ERR_STATE; }
+    info->n_cyclic_chain_elems = 0;
   }
   const uint32_t nu = hs[2];
   uint64_t seq_len; memcpy(&seq_len, hs + 8, 8);
@@ -332,10 +372,10 @@ shk_status shk_shard_graph_join(shk_asm *h, const void *d_all_records, shk_shard
     const unsigned eb = (unsigned)((2 * (size_t)N + 255) / 256);
     if (h->kw == 1)
       k_unitig_emit_sharded<1><<<eb, 256, 0, h->stream>>>(t, h->pd.as<u64>(), coh, (const u64 *)gc.pd, h->c_uoh.as<u32>(), (const UnitigRecS *)h->recs.p,
-                                                         h->node_lo.as<u64>(), nullptr, 2 * N, h->useq.as<char>());
+                                                         h->c_rot.as<u32>(), h->node_lo.as<u64>(), nullptr, 2 * N, h->useq.as<char>());
     else
       k_unitig_emit_sharded<2><<<eb, 256, 0, h->stream>>>(t, h->pd.as<u64>(), coh, (const u64 *)gc.pd, h->c_uoh.as<u32>(), (const UnitigRecS *)h->recs.p,
-                                                         h->node_lo.as<u64>(), h->node_hi.as<u64>(), 2 * N, h->useq.as<char>());
+                                                         h->c_rot.as<u32>(), h->node_lo.as<u64>(), h->node_hi.as<u64>(), 2 * N, h->useq.as<char>());
     ++L;
   }
   for (int attempt = 0; attempt < 2; ++attempt) {

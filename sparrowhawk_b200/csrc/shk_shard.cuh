@@ -193,17 +193,36 @@ __device__ __forceinline__ ChainEnd chain_elem_tail(const ChainRec *recs, u32 E)
   return (E & 1u) ? ChainEnd{r.head_g ^ 1u, r.hkey_lo, r.hkey_hi} : ChainEnd{r.tail_g, r.tkey_lo, r.tkey_hi};
 }
 
+// An unbranched cycle that crosses rank borders shows up as a cycle of CHAINS.  Its cut (S14: in front of the
+// minimum canonical k-mer, kept in the direction that traverses that node canonically) is found in two steps: every
+// rank reports, for each of its chains on such a cycle, the minimum node key inside the chain and where it sits
+// (k_chain_min_*; gathered as ChainMin), the chain-level cycle is cut in front of the chain that holds the overall
+// minimum (the k_cycle_* kernels over those keys; circ_c == 2 marks the forced head), and the unitig is then ROTATED
+// by the position of the minimum node inside that first chain.
+struct ChainMin { u64 lo, hi, rank_dir; };     // rank_dir: local rank of the minimum node in direction 2i | its direction << 32
+
+// position (in nodes) of the minimum node inside the list that starts at the forced head E, and whether that
+// list traverses it canonically
+__device__ __forceinline__ u32 cross_rot(const ChainMin *cmin, const u32 *w_len, u32 E, bool &canonical) {
+  const u64 rd = cmin[E >> 1].rank_dir;
+  const u32 rf = (u32)rd, dir = (u32)(rd >> 32) & 1u;
+  canonical = ((E & 1u) ^ dir) == 0;
+  return (E & 1u) ? w_len[E >> 1] - 1 - rf : rf;
+}
+
 // kept[E] = (1, bases of the unitig) for the chain-level list heads that are kept (rule of k_unitig_heads), else 0
 __global__ void __launch_bounds__(256)
 k_chain_heads(const u64 *__restrict__ pd_c, const u32 *__restrict__ tail_of_c, const u32 *__restrict__ len_of_c,
-              const ChainRec *__restrict__ recs, u32 n_celems, int k, u32 *__restrict__ kept_cnt, u64 *__restrict__ kept_len) {
+              const ChainRec *__restrict__ recs, const uint8_t *__restrict__ circ_c, const ChainMin *__restrict__ cmin,
+              const u32 *__restrict__ w_len, u32 n_celems, int k, u32 *__restrict__ kept_cnt, u64 *__restrict__ kept_len) {
   const u32 E = blockIdx.x * blockDim.x + threadIdx.x;
   if (E >= n_celems) return;
   u32 c = 0; u64 l = 0;
   if (pd_c[E] == ((u64)E << 32)) {
     const bool cyc = recs[E >> 1].flags & 1u;
     bool keep;
-    if (cyc) keep = (E & 1u) == 0;
+    if (circ_c && circ_c[E] == 2) (void)cross_rot(cmin, w_len, E, keep);
+    else if (cyc) keep = (E & 1u) == 0;
     else {
       const ChainEnd h = chain_elem_head(recs, E), tl = chain_elem_tail(recs, tail_of_c[E]);
       if ((h.g >> 1) == (tl.g >> 1)) keep = (h.g & 1u) == 0;
@@ -219,28 +238,57 @@ struct UnitigRecS { u32 head, len; u64 off; };     // == UnitigRec of shk_kernel
 // after the exclusive scans of kept_cnt / kept_len (in place)
 __global__ void __launch_bounds__(256)
 k_chain_unitigs(const u64 *__restrict__ pd_c, const u32 *__restrict__ len_of_c, const u64 *__restrict__ sum_of_c,
-                const ChainRec *__restrict__ recs, const u32 *__restrict__ kept_cnt_x, const u64 *__restrict__ kept_len_x,
+                const ChainRec *__restrict__ recs, const uint8_t *__restrict__ circ_c, const ChainMin *__restrict__ cmin,
+                const u32 *__restrict__ w_len, const u32 *__restrict__ kept_cnt_x, const u64 *__restrict__ kept_len_x,
                 u32 n_celems, int k, u32 *__restrict__ unitig_of_head_c, UnitigRecS *__restrict__ urecs,
-                uint8_t *__restrict__ ucirc, u64 *__restrict__ cov_sum) {
+                uint8_t *__restrict__ ucirc, u64 *__restrict__ cov_sum, u32 *__restrict__ urot) {
   const u32 E = blockIdx.x * blockDim.x + threadIdx.x;
   if (E >= n_celems) return;
-  const bool last = E + 1 == n_celems;
   // kept iff the exclusive prefix grows behind E (the totals sit one past the end)
-  const bool kept = kept_cnt_x[E + 1] != kept_cnt_x[E];
-  (void)last;
-  if (!kept) { unitig_of_head_c[E] = SHK_NONE; return; }
+  if (kept_cnt_x[E + 1] == kept_cnt_x[E]) { unitig_of_head_c[E] = SHK_NONE; return; }
   const u32 uid = kept_cnt_x[E];
+  const bool cross = circ_c && circ_c[E] == 2;
+  bool canonical;
   unitig_of_head_c[E] = uid;
   urecs[uid] = UnitigRecS{E, len_of_c[E], kept_len_x[E]};
-  ucirc[uid] = (uint8_t)(recs[E >> 1].flags & 1u);
+  ucirc[uid] = (uint8_t)((recs[E >> 1].flags & 1u) | (cross ? 1u : 0u));
   cov_sum[uid] = sum_of_c[E];
+  urot[uid] = cross ? cross_rot(cmin, w_len, E, canonical) : 0u;
+}
+
+// minimum node key of every local chain that lies on a chain-level cycle (three passes: high half, low half, position)
+template <int PASS>
+__global__ void __launch_bounds__(256)
+k_chain_min(const ShardTopo *__restrict__ t, const u64 *__restrict__ pd, const u32 *__restrict__ chain_of_head,
+            const u64 *__restrict__ pd_c, const u64 *__restrict__ node_lo, const u64 *__restrict__ node_hi, u32 n_elems,
+            ChainMin *__restrict__ out /* [local chains], pre-filled with 0xFF */) {
+  const u32 e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= n_elems) return;
+  const u64 v = pd[e];
+  if (v == ~0ull) return;
+  const u32 c = chain_of_head[(u32)(v >> 32)];
+  if (c == SHK_NONE || (c & 1u)) return;                     // every node once: in the direction of chain element 2i
+  if (pd_c[2 * t->chain_off[t->rank] + c] != ~0ull) return;  // ranked: not on a cycle of chains
+  ChainMin *m = out + (c >> 1);
+  const u64 lo = node_lo[e >> 1], hi = node_hi ? node_hi[e >> 1] : 0ull;
+  if (PASS == 0) atomicMin(&m->hi, hi);
+  else if (PASS == 1) { if (hi == m->hi) atomicMin(&m->lo, lo); }
+  else if (hi == m->hi && lo == m->lo) m->rank_dir = (u64)(u32)v | ((u64)(e & 1u) << 32);
+}
+
+__global__ void __launch_bounds__(256)
+k_chain_min_unpack(const ChainMin *__restrict__ cmin, u32 n_chains, u64 *__restrict__ lo, u64 *__restrict__ hi) {
+  const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_chains) return;
+  lo[i] = cmin[i].lo; hi[i] = cmin[i].hi;
 }
 
 template <int KW>
 __global__ void __launch_bounds__(256)
 k_unitig_emit_sharded(const ShardTopo *__restrict__ t, const u64 *__restrict__ pd, const u32 *__restrict__ chain_of_head,
                       const u64 *__restrict__ pd_c, const u32 *__restrict__ unitig_of_head_c, const UnitigRecS *__restrict__ urecs,
-                      const u64 *__restrict__ node_lo, const u64 *__restrict__ node_hi, u32 n_elems, char *__restrict__ seq) {
+                      const u32 *__restrict__ urot, const u64 *__restrict__ node_lo, const u64 *__restrict__ node_hi, u32 n_elems,
+                      char *__restrict__ seq) {
   typedef typename KeyOf<KW>::type K;
   const u32 e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= n_elems) return;
@@ -252,7 +300,9 @@ k_unitig_emit_sharded(const ShardTopo *__restrict__ t, const u64 *__restrict__ p
   if (vc == ~0ull) return;
   const u32 uid = unitig_of_head_c[(u32)(vc >> 32)];
   if (uid == SHK_NONE) return;                               // the mirror list of a kept one
-  const u32 r = (u32)vc + (u32)v;                            // nodes in front of this one in the unitig
+  u32 r = (u32)vc + (u32)v;                                  // nodes in front of this one in the unitig
+  const u32 rot = urot[uid];
+  if (rot) { const u32 T = urecs[uid].len; r = r >= rot ? r - rot : r + T - rot; }   // a cycle across ranks starts at its minimum k-mer
   const int k = t->k;
   const u32 n = e >> 1;
   K X = (K)node_lo[n];

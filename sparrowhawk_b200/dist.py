@@ -142,12 +142,18 @@ class GpuEngine:
         self._rec_keep = out
         check(self.lib.shk_shard_graph_records(self.h._h, c.ctypes.data, out.data_ptr() if out.numel() else None))
 
-    def graph_join(self, all_recs):
+    def graph_join(self, all_recs, all_cycle_info=None):
         import ctypes as C
         info = _ffi.ShkShardJoinInfo()
-        self._allrec_keep = all_recs
-        check(self.lib.shk_shard_graph_join(self.h._h, all_recs.data_ptr() if all_recs.numel() else None, C.byref(info)))
+        self._allrec_keep = (all_recs, all_cycle_info)
+        check(self.lib.shk_shard_graph_join(self.h._h, all_recs.data_ptr() if all_recs.numel() else None,
+                                            all_cycle_info.data_ptr() if all_cycle_info is not None and all_cycle_info.numel() else None,
+                                            C.byref(info)))
         return info
+
+    def graph_cycle_info(self, out):
+        self._ci_keep = out
+        check(self.lib.shk_shard_graph_cycle_info(self.h._h, out.data_ptr() if out.numel() else None))
 
     def graph_set_links(self, lf, lt, n):
         check(self.lib.shk_shard_graph_set_links(self.h._h, lf.data_ptr() if n else None, lt.data_ptr() if n else None, int(n)))
@@ -282,7 +288,14 @@ def _sharded_graph(eng, group, counts, g_hist, g_inst, g_bases, used_mc, mark):
     all_recs = _gather_var(rec, chain_counts, 8, group)
     info = eng.graph_join(all_recs)
     if info.n_cyclic_chain_elems:
-        return None
+        # an unbranched cycle crosses rank borders (every rank sees the same count): each rank reports the minimum
+        # k-mer inside its chains on such cycles, and the join runs again with the cut placed there (S14)
+        ci = torch.empty(nch * 3, dtype=torch.int64, device=dev)
+        eng.graph_cycle_info(ci)
+        all_ci = _gather_var(ci, chain_counts, 3, group)
+        info = eng.graph_join(all_recs, all_ci)
+        if info.n_cyclic_chain_elems:
+            return None
     mark("join")
     # the sequence bytes: every rank wrote its own, zeros elsewhere
     if info.seq_bytes:
