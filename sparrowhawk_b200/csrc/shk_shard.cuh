@@ -84,19 +84,28 @@ k_build_edges_sharded(const ShardTopo *__restrict__ t, const u64 *__restrict__ n
                       u32 *__restrict__ uniq /* [2*n_nodes]: global node id << 1 | arrival side */) {
   typedef typename KeyOf<KW>::type K;
   const u32 n = blockIdx.x * blockDim.x + threadIdx.x;
-  if (n >= n_nodes) return;
-  K X = (K)node_lo[n];
-  if (KW == 2) X |= (K)((u128)node_hi[n] << 64);
+  const bool live = n < n_nodes;
   const int k = t->k;
-  u32 rem = __ldcs(node_raw + n), valid = 0;
-  u32 un[2] = {SHK_NONE, SHK_NONE};
-  while (rem) {
-    const int b = __ffs(rem) - 1; rem &= rem - 1;
-    int s_in;
-    const K Y = neighbour_key(X, k, b >> 2, (u32)(b & 3), s_in);
-    const u32 g = shard_find<KW>(t, Y);
-    if (g != SHK_NONE) { valid |= 1u << b; un[b >> 2] = (g << 1) | (u32)s_in; }
+  K X = 0;
+  u32 rem = 0, valid = 0;
+  if (live) {
+    X = (K)node_lo[n];
+    if (KW == 2) X |= (K)((u128)node_hi[n] << 64);
+    rem = __ldcs(node_raw + n);
   }
+  u32 un[2] = {SHK_NONE, SHK_NONE};
+  const int rounds = __reduce_max_sync(0xffffffffu, __popc(rem));   // (re-converged every round: see k_build_edges)
+  for (int it = 0; it < rounds; ++it) {
+    if (rem) {
+      const int b = __ffs(rem) - 1; rem &= rem - 1;
+      int s_in;
+      const K Y = neighbour_key(X, k, b >> 2, (u32)(b & 3), s_in);
+      const u32 g = shard_find<KW>(t, Y);
+      if (g != SHK_NONE) { valid |= 1u << b; un[b >> 2] = (g << 1) | (u32)s_in; }
+    }
+    __syncwarp();
+  }
+  if (!live) return;
   node_edges[n] = (uint8_t)valid;
   __stcs(reinterpret_cast<uint2 *>(uniq) + n, make_uint2(__popc(valid & 15u) == 1 ? un[0] : SHK_NONE,
                                                          __popc(valid >> 4) == 1 ? un[1] : SHK_NONE));
