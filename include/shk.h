@@ -357,6 +357,8 @@ shk_status shk_shard_graph_publish(shk_asm *h, const uint64_t *node_counts, cons
  * mapped (then every rank takes the replicated graph stage). */
 shk_status shk_shard_graph_connect(shk_asm *h, const void *blobs);
 shk_status shk_shard_graph_edges(shk_asm *h);
+/* *n_chains_out == UINT64_MAX: K3' ran out of list space on this rank — when ANY rank reports it, every rank calls
+ * shk_shard_graph_edges again (the needed size is remembered), barrier, then shk_shard_graph_chains. */
 shk_status shk_shard_graph_chains(shk_asm *h, uint64_t *n_chains_out);
 /* chain_counts (HOST, u64[world]); d_records_out (device, 64 bytes x this rank's chains). */
 shk_status shk_shard_graph_records(shk_asm *h, const uint64_t *chain_counts, void *d_records_out);

@@ -744,8 +744,8 @@ static shk_status graph_impl(shk_asm *h) {
     h->graphed = true;
     return SHK_OK;
   }
-  if (N > 0x7FFFFFF0u) { set_error("too many nodes"); return SHK_ERR_BAD_ARG; }
-  SHK_TRY(h->node_edges.ensure(N));
+  if (N >= (1u << 29)) { set_error("too many nodes for one device (%u)", N); return SHK_ERR_BAD_ARG; }   // (K3 packs node << 3 | bit)
+  SHK_TRY(h->node_edges.ensure((size_t)N + 4));
   SHK_TRY(h->uniq.ensure(ne * 4)); SHK_TRY(h->succ.ensure(ne * 4));
   SHK_TRY(h->tail_of.ensure(ne * 4)); SHK_TRY(h->len_of.ensure(ne * 4));
   SHK_TRY(h->unitig_of_head.ensure(ne * 4)); SHK_TRY(h->elem_unitig.ensure(ne * 4));
@@ -779,6 +779,8 @@ static shk_status graph_impl(shk_asm *h) {
   // splitters = a pseudo-random 1/32 of the elements + every list head.  The work area is sized from a guess (an
   // eighth of the elements, or what the last run on this handle needed) and verified on the device.
   uint32_t ns_cap = (uint32_t)std::min<uint64_t>(ne, std::max<uint64_t>(ne / 8 + 65536, (uint64_t)h->ns_hint + h->ns_hint / 4 + 1024));
+  // K3's second phase: lookups that missed in the node's own bucket (about a fifth of them; at most 8 per node)
+  uint32_t work_cap = (uint32_t)std::min<uint64_t>(8ull * N, std::max<uint64_t>((uint64_t)N + 65536, (uint64_t)h->k3_hint + h->k3_hint / 4 + 1024));
   auto read_back = [&]() -> shk_status {
     SHK_CUDA(cudaMemcpyAsync(hs, h->gscal.p, 64, cudaMemcpyDeviceToHost, h->stream));
     SHK_CUDA(cudaMemcpyAsync(hfl, d_flags(h), 32, cudaMemcpyDeviceToHost, h->stream));
@@ -788,7 +790,8 @@ static shk_status graph_impl(shk_asm *h) {
   auto rank_pass = [&](const uint8_t *circ) -> shk_status {
     SHK_TRY(h->rank_work.ensure((size_t)ns_cap * rank_splitter_bytes() + 64));
     SHK_CUDA(cudaMemsetAsync(h->pd.p, 0xFF, ne * 8, h->stream));
-    SHK_CUDA(cudaMemsetAsync(g.scal, 0, 64, h->stream));              // every counter and flag of the stage
+    SHK_CUDA(cudaMemsetAsync(g.scal, 0, 24, h->stream));              // every counter and flag of the stage ...
+    SHK_CUDA(cudaMemsetAsync(g.scal + 7, 0, 36, h->stream));          // ... except [6], K3's deferred lookups
     L += launch_rank_mark(g, circ, h->stream);
     L += launch_rank_lists(g, circ, ns_cap, h->rank_work.p, h->stream);
     return SHK_OK;
@@ -804,11 +807,19 @@ static shk_status graph_impl(shk_asm *h) {
   for (int attempt = 0;; ++attempt) {
     if (attempt > 4) { set_error("graph stage did not settle after retries"); return SHK_ERR_STATE; }
     SHK_CUDA(cudaMemsetAsync(h->tail_of.p, 0xFF, ne * 4, h->stream));
-    L += launch_build_edges(h->kw, h->slots.as<uint64_t>(), h->idx_off.as<uint32_t>(), h->index_P, k, g, h->stream);
+    SHK_CUDA(cudaMemsetAsync(g.scal + 6, 0, 4, h->stream));
+    SHK_TRY(h->k3_work.ensure((size_t)work_cap * 4 + 16));
+    L += launch_build_edges(h->kw, h->slots.as<uint64_t>(), h->idx_off.as<uint32_t>(), h->idx_tmp.as<uint32_t>(), h->index_P, k, g,
+                            h->k3_work.as<uint32_t>(), work_cap, h->stream);
     L += launch_unitig_links(g, h->stream);
     SHK_TRY(rank_pass(nullptr));
     SHK_TRY(emit_pass(false));
     SHK_TRY(read_back());
+    if (hs[6] > work_cap) {                            // more deferred lookups than the list holds: the count is known now
+      work_cap = hs[6] + 1024;
+      continue;
+    }
+    h->k3_hint = hs[6];
     if (hs[5]) {                                       // more splitters than the work area holds: the count is known now
       h->ns_hint = hs[4];
       ns_cap = (uint32_t)std::min<uint64_t>(ne, (uint64_t)hs[4] + 1024);

@@ -88,18 +88,21 @@ __device__ __forceinline__ bool smem_insert(u64 *keys, u32 *vals, int NS, u64 ke
   }
   return false;
 }
-// same, with the slot and the first probe supplied by the caller (software-pipelined decode)
-__device__ __forceinline__ bool smem_insert_at(u64 *keys, u32 *vals, int NS, u64 key, u32 e, u32 add, u32 s, u64 cur) {
+// The claim half of an insert, with the slot and the first probe supplied by the caller (software-pipelined decode):
+// returns the slot that holds `key` now (claimed here or found), or SHK_NONE when the probe window is full.  The
+// caller adds the count AFTER its warp has re-converged: lanes leave this loop after different numbers of probes, and
+// the count / edge update behind it would otherwise run once per group of lanes (measured: 2.4 passes per round).
+__device__ __forceinline__ u32 smem_claim_at(u64 *keys, int NS, u64 key, u32 s, u64 cur) {
   for (int probe = 0; probe < SHK_CB_MAXPROBE; ++probe) {
     if (cur == SHK_EMPTY64) {
       cur = atomicCAS(&keys[s], SHK_EMPTY64, key);
       if (cur == SHK_EMPTY64) cur = key;
     }
-    if (cur == key) { slot_hit(vals + s, e, add); return true; }
+    if (cur == key) return s;
     s = (s + 1 == (u32)NS) ? 0u : s + 1;
     cur = keys[s];
   }
-  return false;
+  return SHK_NONE;
 }
 __device__ __forceinline__ bool smem_insert(U128Pair *keys, u32 *vals, int NS, u128 key, u32 e, u32 add) {
   u32 s = __umulhi(slot_hash(key), (u32)NS);
@@ -484,9 +487,13 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
         for (u32 i = 0; i < nmax; ++i) {
           u64 nkey = 0, ncur = 0; u32 ne = 0, nsl = 0;
           if (i + 1 < n) { next_kmer(i + 1, nkey, ne); nsl = __umulhi(slot_hash(nkey), (u32)NS); ncur = tk[nsl]; }
+          u32 at = SHK_NONE;
+          if (i < n) at = smem_claim_at(tk, NS, key, sl, cur);
+          __syncwarp();                                               // (every lane runs all nmax rounds)
           if (i < n) {
             ndec += wgt;
-            if (!smem_insert_at(tk, vals, NS, key, e, wgt, sl, cur)) { table_insert(ovf, (K)key, e, wgt, ovf_flag); nspill += wgt; }
+            if (at != SHK_NONE) slot_hit(vals + at, e, wgt);
+            else { table_insert(ovf, (K)key, e, wgt, ovf_flag); nspill += wgt; }
           }
           key = nkey; e = ne; sl = nsl; cur = ncur;
         }

@@ -161,6 +161,8 @@ struct shk_asm {
   uint32_t node_cap = 0;
   shk::PinBuf gpin;             // graph stage: pinned mirror of its scalars
   uint32_t ns_hint = 0;         // splitters the last graph stage on this handle needed
+  uint32_t k3_hint = 0, k3_cap = 0;   // K3 lookups the last graph stage deferred to its second phase; size of the list
+  shk::DevBuf k3_work;
 
   // ---- results / state ----
   shk_stats st;

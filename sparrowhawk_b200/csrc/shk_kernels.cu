@@ -9,6 +9,7 @@
 #include "shk_kernels.h"
 #include "shk_table.cuh"
 #include "shk_index.cuh"
+#include "shk_edges.cuh"
 #include "shk_scan.cuh"
 #include "shk_count_smem.cuh"
 #include "shk_rank.cuh"
@@ -138,41 +139,6 @@ k_histogram_filter(Table<KW> tbl, int min_count, u64 *__restrict__ histo /*[500]
 // the unique neighbour (node id << 1 | arrival side) when exactly one edge
 // survives.
 // =====================================================================
-template <int KW>
-__global__ void __launch_bounds__(256)
-k_build_edges(NodeIndex ix, int k, const uint8_t *__restrict__ node_raw, u32 n_nodes, uint8_t *__restrict__ node_edges,
-              u32 *__restrict__ uniq /* [2*n_nodes] */) {
-  typedef typename KeyOf<KW>::type K;
-  const u32 n = blockIdx.x * blockDim.x + threadIdx.x;
-  const bool live = n < n_nodes;
-  K X = 0;
-  u32 rem = 0, valid = 0;
-  if (live) {
-    X = (K)ix.lo[n];
-    if (KW == 2) X |= (K)((u128)ix.hi[n] << 64);
-    rem = __ldcs(node_raw + n);
-  }
-  u32 un[2] = {SHK_NONE, SHK_NONE};
-  // One set bit per lane and round, every lane for as many rounds as the busiest lane of the warp needs, and the warp
-  // re-converged after every round: the lookup is a long stretch of code (minimizer of the neighbour key, probes),
-  // and lanes that drift apart inside it would each run it alone (measured: 7.7 passes per warp at 11 active lanes).
-  const int rounds = __reduce_max_sync(0xffffffffu, __popc(rem));
-  for (int it = 0; it < rounds; ++it) {
-    if (rem) {
-      const int b = __ffs(rem) - 1; rem &= rem - 1;
-      int s_in;
-      const K Y = neighbour_key(X, k, b >> 2, (u32)(b & 3), s_in);
-      const u32 id = index_find<KW>(ix, Y);
-      if (id != SHK_NONE) { valid |= 1u << b; un[b >> 2] = (id << 1) | (u32)s_in; }
-    }
-    __syncwarp();
-  }
-  if (!live) return;
-  node_edges[n] = (uint8_t)valid;
-  __stcs(reinterpret_cast<uint2 *>(uniq) + n, make_uint2(__popc(valid & 15u) == 1 ? un[0] : SHK_NONE,
-                                                         __popc(valid >> 4) == 1 ? un[1] : SHK_NONE));
-}
-
 // =====================================================================
 // K4 unitig_links over directed elements e = 2*node + dir (dir 0 = canonical
 // orientation, leaves through the right side; dir 1 leaves through the left).
@@ -181,13 +147,13 @@ k_build_edges(NodeIndex ix, int k, const uint8_t *__restrict__ node_raw, u32 n_n
 // pd[e] = (pred, 1) or (e, 0) for heads, packed (ptr << 32 | dist).
 // =====================================================================
 __global__ void __launch_bounds__(256)
-k_unitig_links(const uint8_t *__restrict__ node_edges, const u32 *__restrict__ uniq, u32 n_elems,
+k_unitig_links(const uint8_t *__restrict__ node_edges, const u32 *__restrict__ nbr, u32 n_elems,
                u32 *__restrict__ succ) {
   u32 e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= n_elems) return;
-  u32 u = uniq[e], out = SHK_NONE;   // out side of e == dir == e & 1
-  if (u != SHK_NONE) {
-    u32 w = u >> 1, s = u & 1u;
+  u32 out = SHK_NONE;                // out side of e == dir == e & 1
+  if (__popc(side_bits(node_edges[e >> 1], (int)(e & 1u))) == 1) {          // exactly one validated edge: nbr[e] is it
+    const u32 u = nbr[e], w = u >> 1, s = u & 1u;
     if (w != (e >> 1) && __popc(side_bits(node_edges[w], (int)s)) == 1) out = 2 * w + (s ^ 1u);
   }
   succ[e] = out;
@@ -424,13 +390,20 @@ int launch_histogram_filter(int kw, void *slots, uint64_t cap, int min_count, ui
   return 1;
 }
 
-int launch_build_edges(int kw, const uint64_t *slots, const uint32_t *off, uint32_t P, int k, const GraphBuffers &g, cudaStream_t st) {
+// work: u32[work_cap] list of deferred (node, bit) pairs; scal[6] counts them (more than work_cap = run again larger)
+int launch_build_edges(int kw, const uint64_t *slots, const uint32_t *off, const uint32_t *bucket_of, uint32_t P, int k,
+                       const GraphBuffers &g, uint32_t *work, uint32_t work_cap, cudaStream_t st) {
   if (!g.n_nodes) return 0;
-  unsigned b = blocks_for(g.n_nodes, 256);
+  unsigned b = blocks_for(g.n_nodes, 256), bs = blocks_for(work_cap, 256);
   NodeIndex ix{(const u64 *)slots, off, (const u64 *)g.node_lo, kw == 2 ? (const u64 *)g.node_hi : nullptr, P, k};
-  if (kw == 1) k_build_edges<1><<<b, 256, 0, st>>>(ix, k, g.node_raw, g.n_nodes, g.node_edges, g.uniq);
-  else k_build_edges<2><<<b, 256, 0, st>>>(ix, k, g.node_raw, g.n_nodes, g.node_edges, g.uniq);
-  return 1;
+  if (kw == 1) {
+    k_build_edges_fast<1><<<b, 256, 0, st>>>(ix, k, bucket_of, g.node_raw, g.n_nodes, 0u, g.node_edges, g.uniq, work, work_cap, g.scal + 6);
+    k_build_edges_slow<1><<<bs, 256, 0, st>>>(ix, k, bucket_of, work, work_cap, g.scal + 6, g.node_edges, g.uniq);
+  } else {
+    k_build_edges_fast<2><<<b, 256, 0, st>>>(ix, k, bucket_of, g.node_raw, g.n_nodes, 0u, g.node_edges, g.uniq, work, work_cap, g.scal + 6);
+    k_build_edges_slow<2><<<bs, 256, 0, st>>>(ix, k, bucket_of, work, work_cap, g.scal + 6, g.node_edges, g.uniq);
+  }
+  return 2;
 }
 
 int launch_unitig_links(const GraphBuffers &g, cudaStream_t st) {

@@ -19,6 +19,7 @@ struct GraphBuffers {
   void *recs; uint8_t *ucirc; uint64_t *cov_sum; char *seq;
   uint32_t *link_from, *link_to; uint32_t link_cap;
   // device scalars: [1] n_cyclic, [2] n_unitigs, [3] n_links, [4] n_splitters, [5] splitter work area too small,
+  // [6] K3 lookups deferred to the second phase,
   // [8..9] seq cursor (u64), [10..12] round flags of k_rank_solve
   uint32_t *scal; uint64_t *seq_cursor;
   // list ranking over WEIGHTED elements (chain level of the sharded path): element e weighs w_len[e >> 1] nodes and
@@ -37,7 +38,10 @@ int launch_histogram_filter(int kw, void *slots, uint64_t cap, int min_count, ui
                             uint64_t *node_lo, uint64_t *node_hi, uint16_t *node_count, uint8_t *node_raw,
                             uint32_t node_cap, uint32_t *n_nodes, cudaStream_t st);
 // P = fine buckets of the count stage (power of two): the index keeps the nodes of a bucket together
-int launch_build_edges(int kw, const uint64_t *slots, const uint32_t *off, uint32_t P, int k, const GraphBuffers &g, cudaStream_t st);
+// bucket_of: the fine bucket of every node (kept by the index build); work / work_cap: list of the lookups deferred to the
+// second phase, counted in scal[6]
+int launch_build_edges(int kw, const uint64_t *slots, const uint32_t *off, const uint32_t *bucket_of, uint32_t P, int k,
+                       const GraphBuffers &g, uint32_t *work, uint32_t work_cap, cudaStream_t st);
 int launch_unitig_links(const GraphBuffers &g, cudaStream_t st);
 // K5 (shk_rank.cuh): mark counts the splitters into scal[4] and the host never reads that number: `work` holds
 // ns_cap splitters (rank_splitter_bytes() each), the kernels read the count from scal[4] and set scal[5] when it

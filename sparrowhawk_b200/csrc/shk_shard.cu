@@ -160,12 +160,32 @@ shk_status shk_shard_graph_edges(shk_asm *h) {
   SHK_TRY(h->uniq.ensure(((size_t)2 * n + 2) * 4));
   if (!n) return SHK_OK;
   const ShardTopo *t = (const ShardTopo *)h->topo.p;
-  uint8_t *edges = (uint8_t *)h->arena.p + h->arena_off_edges;
-  if (h->kw == 1)
-    k_build_edges_sharded<1><<<(n + 255) / 256, 256, 0, h->stream>>>(t, h->node_lo.as<u64>(), nullptr, h->node_raw.as<uint8_t>(), n, edges, h->uniq.as<u32>());
-  else
-    k_build_edges_sharded<2><<<(n + 255) / 256, 256, 0, h->stream>>>(t, h->node_lo.as<u64>(), h->node_hi.as<u64>(), h->node_raw.as<uint8_t>(), n, edges, h->uniq.as<u32>());
-  ++h->st.gpu_launches;
+  uint8_t *A = (uint8_t *)h->arena.p;
+  uint8_t *edges = A + h->arena_off_edges;
+  SHK_TRY(h->gscal.ensure(64));
+  // phase 1 over this rank's own index (the node's own bucket), phase 2 for the lookups that missed there
+  const uint32_t work_cap = (uint32_t)std::min<uint64_t>(8ull * n, std::max<uint64_t>((uint64_t)n + 65536, (uint64_t)h->k3_hint * 2 + 1024));
+  SHK_TRY(h->k3_work.ensure((size_t)work_cap * 4 + 16));
+  h->k3_cap = work_cap;
+  u32 *nw = h->gscal.as<u32>() + 13;                    // (the scalar block is cleared by the ranking passes: [13] is not theirs)
+  SHK_CUDA(cudaMemsetAsync(nw, 0, 4, h->stream));
+  NodeIndex ix{(const u64 *)(A + h->arena_off_slots), (const u32 *)(A + h->arena_off_off), h->node_lo.as<u64>(),
+               h->kw == 2 ? h->node_hi.as<u64>() : nullptr, h->P, h->p.k};
+  const u32 *bucket_of = h->idx_tmp.as<u32>();
+  const unsigned nb = (n + 255) / 256, wb = (work_cap + 255) / 256;
+  const u32 base = h->shard_node_off[h->shard_rank];
+  if (h->kw == 1) {
+    k_build_edges_fast<1><<<nb, 256, 0, h->stream>>>(ix, h->p.k, bucket_of, h->node_raw.as<uint8_t>(), n, base, edges, h->uniq.as<u32>(),
+                                                    h->k3_work.as<u32>(), work_cap, nw);
+    k_build_edges_sharded_slow<1><<<wb, 256, 0, h->stream>>>(t, h->node_lo.as<u64>(), nullptr, bucket_of, h->k3_work.as<u32>(), work_cap, nw,
+                                                            edges, h->uniq.as<u32>());
+  } else {
+    k_build_edges_fast<2><<<nb, 256, 0, h->stream>>>(ix, h->p.k, bucket_of, h->node_raw.as<uint8_t>(), n, base, edges, h->uniq.as<u32>(),
+                                                    h->k3_work.as<u32>(), work_cap, nw);
+    k_build_edges_sharded_slow<2><<<wb, 256, 0, h->stream>>>(t, h->node_lo.as<u64>(), h->node_hi.as<u64>(), bucket_of, h->k3_work.as<u32>(),
+                                                            work_cap, nw, edges, h->uniq.as<u32>());
+  }
+  h->st.gpu_launches += 2;
   SHK_CUDA(cudaGetLastError());
   return SHK_OK;
 }
@@ -196,7 +216,7 @@ shk_status shk_shard_graph_chains(shk_asm *h, uint64_t *n_chains_out) {
   auto pass = [&]() -> shk_status {
     SHK_TRY(h->rank_work.ensure((size_t)ns_cap * rank_splitter_bytes() + 64));
     SHK_CUDA(cudaMemsetAsync(h->pd.p, 0xFF, ne * 8, h->stream));
-    SHK_CUDA(cudaMemsetAsync(g.scal, 0, 64, h->stream));
+    SHK_CUDA(cudaMemsetAsync(g.scal, 0, 52, h->stream));             // (all but [13], K3's deferred lookups)
     SHK_CUDA(cudaMemsetAsync(h->tail_of.p, 0xFF, ne * 4, h->stream));
     L += launch_rank_mark(g, circ, h->stream);
     L += launch_rank_lists(g, circ, ns_cap, h->rank_work.p, h->stream);
@@ -210,6 +230,14 @@ shk_status shk_shard_graph_chains(shk_asm *h, uint64_t *n_chains_out) {
     if (attempt > 4) { set_error("local list ranking did not settle after retries"); return SHK_ERR_STATE; }
     circ = nullptr;
     SHK_TRY(pass());
+    if (hs[13] > h->k3_cap) {
+      // K3' deferred more lookups than its list holds: the edges are incomplete.  Every rank must run
+      // shk_shard_graph_edges again (the count is remembered) — reported through the chain count.
+      h->k3_hint = hs[13];
+      *n_chains_out = ~0ull;
+      return SHK_OK;
+    }
+    h->k3_hint = std::max(h->k3_hint / 2, hs[13]);
     if (hs[5]) { h->ns_hint = hs[4]; ns_cap = (uint32_t)std::min<uint64_t>(ne, (uint64_t)hs[4] + 1024); continue; }
     h->ns_hint = hs[4];
     if (hs[1]) {                                       // unbranched cycles inside this rank: cut at the minimum k-mer, rank again

@@ -7,8 +7,9 @@
 // has its facing side, which chain does this element head — reads it straight out of the owner's HBM.  No node
 // is ever copied to another rank.
 //
-//   K3' k_build_edges_sharded   owned nodes; a neighbour key is looked up in the index of the rank that owns its
-//                               minimizer bucket (minimizer_hash_of); node ids are GLOBAL (rank offset + local id)
+//   K3' k_build_edges_fast + k_build_edges_sharded_slow   owned nodes; a neighbour that is not in the node's own bucket
+//                               is looked up in the index of the rank that owns ITS minimizer bucket
+//                               (minimizer_hash_of); node ids are GLOBAL (rank offset + local id)
 //   K4' k_unitig_links_sharded  succ over the owned directed elements; links to an element of another rank are
 //                               kept apart (xsucc), so the local lists END at the rank border
 //   K5  local list ranking      the single-GPU kernels (shk_rank.cuh) over succ_local: every maximal run of a
@@ -26,6 +27,7 @@
 //       k_unitig_links_sharded_out  unitig-level links, by the rank that owns the exit node
 #pragma once
 #include "shk_index.cuh"
+#include "shk_edges.cuh"
 #include "shk_scan.cuh"
 
 namespace shk {
@@ -77,38 +79,33 @@ __device__ __forceinline__ u32 shard_find(const ShardTopo *t, typename KeyOf<KW>
   return id == SHK_NONE ? SHK_NONE : t->node_off[r] + id;
 }
 
+// K3' second phase (the first is k_build_edges_fast over the rank's own index, shk_edges.cuh): the lookups that missed
+// in the node's own bucket.  The neighbour's minimizer names its bucket, the bucket its owner rank; that rank's index
+// is probed in place (peer memory when it is another rank).
 template <int KW>
 __global__ void __launch_bounds__(256)
-k_build_edges_sharded(const ShardTopo *__restrict__ t, const u64 *__restrict__ node_lo, const u64 *__restrict__ node_hi,
-                      const uint8_t *__restrict__ node_raw, u32 n_nodes, uint8_t *__restrict__ node_edges,
-                      u32 *__restrict__ uniq /* [2*n_nodes]: global node id << 1 | arrival side */) {
+k_build_edges_sharded_slow(const ShardTopo *__restrict__ t, const u64 *__restrict__ node_lo, const u64 *__restrict__ node_hi,
+                           const u32 *__restrict__ bucket_of, const u32 *__restrict__ work, u32 work_cap, const u32 *__restrict__ n_work,
+                           uint8_t *__restrict__ node_edges, u32 *__restrict__ nbr) {
   typedef typename KeyOf<KW>::type K;
-  const u32 n = blockIdx.x * blockDim.x + threadIdx.x;
-  const bool live = n < n_nodes;
-  const int k = t->k;
-  K X = 0;
-  u32 rem = 0, valid = 0;
-  if (live) {
-    X = (K)node_lo[n];
-    if (KW == 2) X |= (K)((u128)node_hi[n] << 64);
-    rem = __ldcs(node_raw + n);
-  }
-  u32 un[2] = {SHK_NONE, SHK_NONE};
-  const int rounds = __reduce_max_sync(0xffffffffu, __popc(rem));   // (re-converged every round: see k_build_edges)
-  for (int it = 0; it < rounds; ++it) {
-    if (rem) {
-      const int b = __ffs(rem) - 1; rem &= rem - 1;
-      int s_in;
-      const K Y = neighbour_key(X, k, b >> 2, (u32)(b & 3), s_in);
-      const u32 g = shard_find<KW>(t, Y);
-      if (g != SHK_NONE) { valid |= 1u << b; un[b >> 2] = (g << 1) | (u32)s_in; }
-    }
-    __syncwarp();
-  }
-  if (!live) return;
-  node_edges[n] = (uint8_t)valid;
-  __stcs(reinterpret_cast<uint2 *>(uniq) + n, make_uint2(__popc(valid & 15u) == 1 ? un[0] : SHK_NONE,
-                                                         __popc(valid >> 4) == 1 ? un[1] : SHK_NONE));
+  const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+  const u32 nw = min(*n_work, work_cap);
+  if (i >= nw) return;
+  const u32 item = work[i], n = item >> 3, b = item & 7u;
+  K X = (K)node_lo[n];
+  if (KW == 2) X |= (K)((u128)node_hi[n] << 64);
+  int s_in;
+  const K Y = neighbour_key(X, t->k, (int)(b >> 2), b & 3u, s_in);
+  const u32 yb = minimizer_hash_of(Y, t->k) & (t->P - 1);
+  if (yb == bucket_of[n]) return;                         // looked up there already: no such node
+  const u32 r = owner_of_bucket(yb, t->P, t->world);
+  const PeerView pv = t->peer[r];
+  if (!pv.n_nodes) return;
+  NodeIndex ix{pv.slots, pv.off, pv.lo, pv.hi, t->P, t->k};
+  const u32 id = index_find_in<KW>(ix, Y, yb);
+  if (id == SHK_NONE) return;
+  atomicOr(reinterpret_cast<u32 *>(node_edges + (n & ~3u)), (1u << b) << (8u * (n & 3u)));
+  nbr[2 * n + (b >> 2)] = ((t->node_off[r] + id) << 1) | (u32)s_in;
 }
 
 // succ_local[e]: the local element that follows e, when it lives on this rank; xsucc[e]: the GLOBAL element that
@@ -119,10 +116,9 @@ k_unitig_links_sharded(const ShardTopo *__restrict__ t, const uint8_t *__restric
                        u32 n_elems, u32 *__restrict__ succ_local, u32 *__restrict__ xsucc) {
   const u32 e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= n_elems) return;
-  const u32 u = uniq[e];
   u32 out_l = SHK_NONE, out_x = SHK_NONE;
-  if (u != SHK_NONE) {
-    const u32 w = u >> 1, s = u & 1u, me = t->rank;
+  if (__popc(side_bits(node_edges[e >> 1], (int)(e & 1u))) == 1) {       // exactly one validated edge: uniq[e] is it
+    const u32 u = uniq[e], w = u >> 1, s = u & 1u, me = t->rank;
     if (w != t->node_off[me] + (e >> 1)) {
       const u32 r = owner_of_node(t, w), wl = w - t->node_off[r];
       const u32 ed = r == me ? (u32)node_edges[wl] : (u32)__ldcg(t->peer[r].edges + wl);

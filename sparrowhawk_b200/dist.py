@@ -135,7 +135,7 @@ class GpuEngine:
         import ctypes as C
         n = C.c_uint64()
         check(self.lib.shk_shard_graph_chains(self.h._h, C.byref(n)))
-        return int(n.value)
+        return -1 if n.value == 0xFFFFFFFFFFFFFFFF else int(n.value)
 
     def graph_records(self, chain_counts, out):
         c = np.ascontiguousarray(chain_counts, dtype=np.uint64)
@@ -274,13 +274,19 @@ def _sharded_graph(eng, group, counts, g_hist, g_inst, g_bases, used_mc, mark):
                   file=sys.stderr)
         return None
     mark("publish")
-    # 3. K3' over the owned nodes; barrier "edges complete"
-    eng.graph_edges()
-    _barrier(dev, group)
-    mark("edges")
-    # 4. K4' + local list ranking: one chain per stretch of a unitig inside this rank
-    nch = eng.graph_chains()
-    chain_counts = [int(x) for x in _gather_host_ints([nch], dev, group)[:, 0]]     # (barrier "chain numbers complete")
+    for attempt in range(3):
+        # 3. K3' over the owned nodes; barrier "edges complete"
+        eng.graph_edges()
+        _barrier(dev, group)
+        if attempt == 0:
+            mark("edges")
+        # 4. K4' + local list ranking: one chain per stretch of a unitig inside this rank
+        nch = eng.graph_chains()
+        chain_counts = [int(x) for x in _gather_host_ints([nch], dev, group)[:, 0]]     # (barrier "chain numbers complete")
+        if min(chain_counts) >= 0:
+            break                                    # (-1: a rank's K3' list was too small; sized now, once more)
+    else:
+        return None
     mark("chains")
     # 5./6. chain records of all ranks, ranked on every rank: the final pointer-jumping pass
     rec = torch.empty(nch * 8, dtype=torch.int64, device=dev)
