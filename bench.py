@@ -566,10 +566,12 @@ def sharded_arm(args, name, w, ctx, steps, warmup, with_e2e=True, with_cold=Fals
                "call_ms": {n: round(sum(v[1:]) / max(1, len(v) - 1), 3) for n, v in call_ms.items()},
                "ncontigs": json.loads(bytes(res))["ncontigs"] if res is not None else None, "nkmers": json.loads(info)["nkmers"]}
 
+    n_nodes_global = json.loads(h.get_preprocessing_info())["nkmers"] if world > 1 else st["n_nodes"]   # (sharded: the ranks' sum)
     # ---- cold path: a FRESH handle, as the reference workflow uses one (new -> preprocess -> assemble,
-    # Assembler.ts:92-100): allocations, first-run planning and everything else a first call pays ----
+    # Assembler.ts:92-100, with `helper = null` in between: the previous handle is gone) ----
     cold = None
     if with_cold and world == 1 and not args.no_cold:
+        h.close()
         hc = AssemblyHelper.new(w["k"], False, w["min_count"], MIN_QUAL, 0, False, False, False, False, device=local)
         hc.set_stream(stream.cuda_stream or 1)
         hc.load_reads_ptr(pin_seq.data_ptr(), pin_qual.data_ptr(), nbytes)
@@ -588,8 +590,9 @@ def sharded_arm(args, name, w, ctx, steps, warmup, with_e2e=True, with_cold=Fals
         hc.close()
         cold = {"ms_first_run": first_run, "e2e_first_call_ms": first_call, "vs_warm_step": first_run / ms_step,
                 "device_planned": int(sc["device_planned"]), "table_retries": int(sc["table_retries"]),
-                "note": "fresh handle in a warm process (CUDA context and module already loaded): every allocation, "
-                        "the planning of the first run and any fallback it takes are inside"}
+                "note": "fresh handle in a warm process (CUDA context and module loaded; the previous handle freed, so its "
+                        "memory is back in the library's device pool): every allocation, the planning of the first run and "
+                        "any fallback it takes are inside"}
 
     # ---- roofline of the dominant kernel (K1b k_count_buckets) ----------------
     peak, peak_src = peaks()
@@ -637,7 +640,7 @@ def sharded_arm(args, name, w, ctx, steps, warmup, with_e2e=True, with_cold=Fals
     cfg.update({"bases_per_step_this_gpu": bases, "multi_gpu": multi, "graph_mode": modes[-1] if modes else "single",
                 "l2": "inputs larger than L2: packed reads %.0f MB + super-k-mer records %.0f MB vs 126 MB L2"
                       % (st["n_positions"] * 0.375 / 1e6, st["n_records"] * (16 if w["k"] <= 31 else 32) / 1e6),
-                "n_distinct": st["n_distinct"], "n_nodes": json.loads(h.get_preprocessing_info())["nkmers"], "n_unitigs": st["n_unitigs"],
+                "n_distinct": st["n_distinct"], "n_nodes": n_nodes_global, "n_unitigs": st["n_unitigs"],
                 "fine_buckets": st["table_slots"], "gen_seconds": round(t_gen, 2)})
     out = {"metric": "input bases/s, k-mer count + DBG build", "value": value, "unit": "bases/s",
            "n_gpus": world, "steps": steps, "warmup": warmup, "ms_per_step": ms_step,

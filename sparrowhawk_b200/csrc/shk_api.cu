@@ -12,6 +12,7 @@
 #include <atomic>
 #include <chrono>
 #include <memory>
+#include <mutex>
 #include <thread>
 #include <vector>
 
@@ -37,29 +38,88 @@ shk_status cuda_fail(cudaError_t e, const char *what) {
   return e == cudaErrorMemoryAllocation ? SHK_ERR_OOM : SHK_ERR_CUDA;
 }
 
+// ---- memory: a process-wide pool behind the handles -----------------------------------------------------------
+// The reference workflow makes a new AssemblyHelper per job (Assembler.ts:92-100, `helper = null` in between), so a
+// handle's allocations are on the user's clock.  Device buffers therefore come from the device's stream-ordered
+// memory pool (cudaMallocAsync, release threshold = never): what one handle gives back the next one gets in
+// microseconds, and growing a buffer no longer synchronises the device (the free is ordered on the handle's stream).
+// Pinned host buffers are recycled through a free list.  Buffers that are published to other processes (the peer-memory
+// arena of the sharded graph stage) stay plain cudaMalloc: pool memory has no cudaIpc handle.
+// SHK_NO_POOL=1 turns both off (plain cudaMalloc / cudaMallocHost).
+static thread_local cudaStream_t tls_stream = nullptr;   // stream of the handle whose call runs on this thread
+static thread_local bool tls_stream_ok = false;
+static bool pool_enabled() {
+  static const bool on = [] { const char *e = getenv("SHK_NO_POOL"); return !(e && e[0] == '1'); }();
+  return on;
+}
+static void pool_setup_once(int dev) {
+  static std::atomic<uint64_t> done{0};
+  if (dev < 0 || dev >= 64 || (done.load() >> dev) & 1) return;
+  cudaMemPool_t pool;
+  if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
+    uint64_t keep = ~0ull;
+    cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+  } else {
+    cudaGetLastError();
+  }
+  done.fetch_or(1ull << dev);
+}
+
 shk_status DevBuf::ensure(size_t bytes) {
   if (bytes <= cap) return SHK_OK;
   release();
   size_t want = bytes + bytes / 8 + 256;
-  cudaError_t e = cudaMalloc(&p, want);
+  cudaError_t e;
+  if (!plain && pool_enabled() && tls_stream_ok) {
+    e = cudaMallocAsync(&p, want, tls_stream);
+    pooled = e == cudaSuccess;
+    if (e != cudaSuccess) { cudaGetLastError(); e = cudaMalloc(&p, want); }
+  } else {
+    e = cudaMalloc(&p, want);
+    pooled = false;
+  }
   if (e != cudaSuccess) { p = nullptr; return cuda_fail(e, "cudaMalloc"); }
   cap = want;
   return SHK_OK;
 }
 void DevBuf::release() {
-  if (p) cudaFree(p);
-  p = nullptr; cap = 0;
+  if (p) {
+    if (pooled && tls_stream_ok) cudaFreeAsync(p, tls_stream);      // ordered behind the work queued on the handle's stream
+    else cudaFree(p);                                               // (synchronises; also valid for pool memory)
+  }
+  p = nullptr; cap = 0; pooled = false;
 }
+
+namespace {
+struct PinBlock { void *p; size_t cap; };
+std::mutex g_pin_mu;
+std::vector<PinBlock> g_pin_free;
+}  // namespace
 shk_status PinBuf::ensure_host(size_t bytes) {
   if (bytes <= cap) return SHK_OK;
   release();
-  cudaError_t e = cudaMallocHost(&p, bytes + bytes / 4 + 256);
+  const size_t want = bytes + bytes / 4 + 256;
+  if (pool_enabled()) {
+    std::lock_guard<std::mutex> lk(g_pin_mu);
+    size_t best = g_pin_free.size();
+    for (size_t i = 0; i < g_pin_free.size(); ++i)                   // smallest block that fits, but not a wildly larger one
+      if (g_pin_free[i].cap >= bytes && g_pin_free[i].cap <= 4 * want + (1u << 20) && (best == g_pin_free.size() || g_pin_free[i].cap < g_pin_free[best].cap)) best = i;
+    if (best != g_pin_free.size()) {
+      p = g_pin_free[best].p; cap = g_pin_free[best].cap;
+      g_pin_free.erase(g_pin_free.begin() + (long)best);
+      return SHK_OK;
+    }
+  }
+  cudaError_t e = cudaMallocHost(&p, want);
   if (e != cudaSuccess) { p = nullptr; return cuda_fail(e, "cudaMallocHost"); }
-  cap = bytes + bytes / 4 + 256;
+  cap = want;
   return SHK_OK;
 }
 void PinBuf::release() {
-  if (p) cudaFreeHost(p);
+  if (p) {
+    if (pool_enabled()) { std::lock_guard<std::mutex> lk(g_pin_mu); g_pin_free.push_back(PinBlock{p, cap}); }
+    else cudaFreeHost(p);
+  }
   p = nullptr; cap = 0;
 }
 
@@ -72,6 +132,7 @@ shk_status require_device(shk_asm *h) {
   if (!h) { set_error("null handle"); return SHK_ERR_BAD_ARG; }
   if (h->dev < 0) { set_error("no CUDA device: this library has no CPU path"); return SHK_ERR_NO_DEVICE; }
   SHK_CUDA(cudaSetDevice(h->dev));
+  tls_stream = h->stream; tls_stream_ok = h->stream != nullptr;     // allocations of this call are ordered on the handle's stream
   return SHK_OK;
 }
 
@@ -915,6 +976,8 @@ shk_status shk_asm_new(const shk_params *params, shk_asm **out) {
   }
   if (cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking) != cudaSuccess) { delete h; return cuda_fail(cudaGetLastError(), "cudaStreamCreate"); }
   h->stream = h->own_stream;
+  pool_setup_once(dev);
+  tls_stream = h->stream; tls_stream_ok = true;
   for (auto &e : h->ev) cudaEventCreate(&e);
   if (h->dscal.ensure(DSCAL_BYTES) != SHK_OK || cudaMallocHost((void **)&h->h_pinned, DSCAL_BYTES) != cudaSuccess) {
     shk_asm_free(h); set_error("scalar buffer allocation failed"); return SHK_ERR_OOM;
@@ -934,6 +997,7 @@ void shk_asm_free(shk_asm *h) {
     if (h->stream) cudaStreamSynchronize(h->stream);
     if (h->copy_stream) cudaStreamSynchronize(h->copy_stream);
     if (h->h_pinned) cudaFreeHost(h->h_pinned);
+    tls_stream = nullptr; tls_stream_ok = false;                      // the members below free themselves synchronously (back into the pool)
     for (auto &row : h->peer_maps) for (auto &m : row) if (m.open) { cudaIpcCloseMemHandle(m.p); m.open = false; }
     // every DevBuf / PinBuf member frees itself when the handle is deleted below
     for (auto &e : h->ev) if (e) cudaEventDestroy(e);
@@ -953,6 +1017,7 @@ shk_status shk_set_stream(shk_asm *h, void *stream) {
   if (!h) { set_error("null handle"); return SHK_ERR_BAD_ARG; }
   if (h->dev >= 0 && h->stream) { cudaSetDevice(h->dev); cudaStreamSynchronize(h->stream); }   // work queued so far is ordered before the switch
   h->stream = stream ? (cudaStream_t)stream : h->own_stream;
+  tls_stream = h->stream; tls_stream_ok = h->dev >= 0;
   return SHK_OK;
 }
 void *shk_get_stream(shk_asm *h) { return h ? (void *)h->stream : nullptr; }

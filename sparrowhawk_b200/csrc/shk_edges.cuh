@@ -20,9 +20,13 @@ k_build_edges_fast(NodeIndex ix, int k, const u32 *__restrict__ bucket_of, const
                    uint8_t *__restrict__ node_edges, u32 *__restrict__ nbr /* [2*n_nodes] */,
                    u32 *__restrict__ work, u32 work_cap, u32 *__restrict__ n_work) {
   typedef typename KeyOf<KW>::type K;
+  __shared__ u32 s_items[256 * 8];                     // this CTA's deferred lookups (at most 8 per node)
+  __shared__ u32 s_count, s_base;
   const u32 n = blockIdx.x * blockDim.x + threadIdx.x;
   const bool live = n < n_nodes;
   const int lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) s_count = 0;
+  __syncthreads();
   K X = 0;
   u32 rem = 0, valid = 0, myb = 0;
   if (live) {
@@ -45,17 +49,25 @@ k_build_edges_fast(NodeIndex ix, int k, const u32 *__restrict__ bucket_of, const
     }
     __syncwarp();
     const u32 ball = __ballot_sync(0xffffffffu, defer);
-    if (ball) {
+    if (ball) {                                        // one shared atomic per warp and round, one global atomic per CTA (below)
       u32 base = 0;
-      if (lane == 0) base = atomicAdd(n_work, (u32)__popc(ball));
+      if (lane == 0) base = atomicAdd(&s_count, (u32)__popc(ball));
       base = __shfl_sync(0xffffffffu, base, 0);
-      const u32 pos = base + __popc(ball & ((1u << lane) - 1));
-      if (defer && pos < work_cap) work[pos] = item;               // (an overflow is seen in the count: the host re-runs)
+      if (defer) s_items[base + __popc(ball & ((1u << lane) - 1))] = item;
     }
   }
-  if (!live) return;
-  node_edges[n] = (uint8_t)valid;
-  __stcs(reinterpret_cast<uint2 *>(nbr) + n, make_uint2(un[0], un[1]));
+  if (live) {
+    node_edges[n] = (uint8_t)valid;
+    __stcs(reinterpret_cast<uint2 *>(nbr) + n, make_uint2(un[0], un[1]));
+  }
+  __syncthreads();
+  const u32 cnt = s_count;
+  if (!cnt) return;
+  if (threadIdx.x == 0) s_base = atomicAdd(n_work, cnt);
+  __syncthreads();
+  const u32 gb = s_base;
+  for (u32 j = threadIdx.x; j < cnt; j += blockDim.x)
+    if (gb + j < work_cap) work[gb + j] = s_items[j];  // (an overflow is seen in the count: the host runs the stage again)
 }
 
 template <int KW>

@@ -26,11 +26,16 @@ shk_status cuda_fail(cudaError_t e, const char *what);
 struct DevBuf {
   void *p = nullptr;
   size_t cap = 0;
+  bool pooled = false;   // from the device's stream-ordered pool (shk_api.cu "memory")
+  bool plain = false;    // always plain cudaMalloc: the buffer is published to other processes (cudaIpc)
   DevBuf() = default;
   DevBuf(const DevBuf &) = delete;
   DevBuf &operator=(const DevBuf &) = delete;
-  DevBuf(DevBuf &&o) noexcept : p(o.p), cap(o.cap) { o.p = nullptr; o.cap = 0; }
-  DevBuf &operator=(DevBuf &&o) noexcept { if (this != &o) { release(); p = o.p; cap = o.cap; o.p = nullptr; o.cap = 0; } return *this; }
+  DevBuf(DevBuf &&o) noexcept : p(o.p), cap(o.cap), pooled(o.pooled), plain(o.plain) { o.p = nullptr; o.cap = 0; o.pooled = false; }
+  DevBuf &operator=(DevBuf &&o) noexcept {
+    if (this != &o) { release(); p = o.p; cap = o.cap; pooled = o.pooled; plain = o.plain; o.p = nullptr; o.cap = 0; o.pooled = false; }
+    return *this;
+  }
   ~DevBuf() { release(); }
   shk_status ensure(size_t bytes);
   void release();
@@ -140,8 +145,10 @@ struct shk_asm {
   uint32_t shard_chains_local = 0, shard_chains_global = 0, ns_hint_c = 0;
   shk::DevBuf arena /* published: slots | off | edges | chain_of_head */, topo, xsucc, chain_head;
   shk::PinBuf topo_pin;
-  size_t arena_off_slots = 0, arena_off_off = 0, arena_off_edges = 0, arena_off_coh = 0;
-  shk_peer_map peer_maps[64][3];
+  size_t arena_off_slots = 0, arena_off_off = 0, arena_off_edges = 0, arena_off_coh = 0, arena_off_lo = 0, arena_off_hi = 0;
+  unsigned char arena_ipc[64] = {0};   // cudaIpcMemHandle_t of the arena allocation `arena_exported`
+  void *arena_exported = nullptr; size_t arena_exported_cap = 0;
+  shk_peer_map peer_maps[64][1];
   shk::DevBuf c_succ, c_wlen, c_wsum, c_pd, c_split, c_tail, c_len, c_sum, c_uoh, c_kcnt, c_klen, c_tmp, c_rot, c_cq, c_circ, c_mlo, c_mhi;
   // sharded steady-state count (shk_shard_count_device): calibrated by a host-planned run over this many owned buckets / ranks
   uint32_t shard_cal_nb = 0, shard_cal_world = 0;

@@ -19,8 +19,8 @@ namespace {
 
 // what a rank publishes (all-gathered by the host, SHK_PEER_BLOB_BYTES each)
 struct PeerBlob {
-  cudaIpcMemHandle_t arena, lo, hi;
-  uint64_t off_slots, off_off, off_edges, off_coh;      // byte offsets inside the arena
+  cudaIpcMemHandle_t arena;                                        // ONE allocation per rank holds everything the others read
+  uint64_t off_slots, off_off, off_edges, off_coh, off_lo, off_hi; // byte offsets inside the arena
   uint32_t n_nodes, has_hi, device, magic;
 };
 static_assert(sizeof(PeerBlob) <= SHK_PEER_BLOB_BYTES, "peer blob grew past its ABI size");
@@ -86,17 +86,25 @@ shk_status shk_shard_graph_publish(shk_asm *h, const uint64_t *node_counts, cons
   h->st.n_instances = n_instances_global; h->st.n_bases = n_bases_global; h->n_bases = n_bases_global;
   if (used_min_count >= 0) h->st.used_min_count = used_min_count;
   h->st.n_nodes = n;                                   // the exports of this handle cover ITS nodes
-  // arena: [slots u64 x (2n+2)] [off u32 x (P+2)] [edges u8 x n] [chain_of_head u32 x 2n]
+  // arena (plain cudaMalloc: it is exported): [slots u64 x (2n+2)] [off u32 x (P+2)] [edges u8 x n] [chain_of_head u32 x 2n]
+  // [key lo u64 x n] [key hi u64 x n] — the keys are a copy of this rank's node arrays, so that one handle covers all
+  if (n >= (1u << 29)) { set_error("too many nodes on one rank (%u)", n); return SHK_ERR_BAD_ARG; }   // (K3' packs node << 3 | bit)
   const uint32_t P = h->P;
   size_t o = 0;
   h->arena_off_slots = o; o = align_up(o + ((size_t)2 * n + 2) * 8, 256);
   h->arena_off_off = o;   o = align_up(o + ((size_t)P + 2) * 4, 256);
   h->arena_off_edges = o; o = align_up(o + (size_t)n + 16, 256);
   h->arena_off_coh = o;   o = align_up(o + ((size_t)2 * n + 2) * 4, 256);
+  h->arena_off_lo = o;    o = align_up(o + ((size_t)n + 1) * 8, 256);
+  h->arena_off_hi = o;    o = align_up(o + (h->kw == 2 ? ((size_t)n + 1) * 8 : 8), 256);
+  h->arena.plain = true;
   SHK_TRY(h->arena.ensure(o));
-  SHK_TRY(h->node_lo.ensure(8)); if (h->kw == 2) SHK_TRY(h->node_hi.ensure(8));      // a rank without nodes still publishes
   SHK_TRY(h->idx_tmp.ensure(((size_t)n + index_tmp_entries(P) + 2) * 4));
   uint8_t *A = (uint8_t *)h->arena.p;
+  if (n) {
+    SHK_CUDA(cudaMemcpyAsync(A + h->arena_off_lo, h->node_lo.p, (size_t)n * 8, cudaMemcpyDeviceToDevice, h->stream));
+    if (h->kw == 2) SHK_CUDA(cudaMemcpyAsync(A + h->arena_off_hi, h->node_hi.p, (size_t)n * 8, cudaMemcpyDeviceToDevice, h->stream));
+  }
   SHK_CUDA(cudaMemsetAsync(A + h->arena_off_slots, 0xFF, ((size_t)2 * n + 2) * 8, h->stream));
   SHK_CUDA(cudaMemsetAsync(A + h->arena_off_off, 0, ((size_t)P + 2) * 4, h->stream));
   h->index_P = P;
@@ -105,10 +113,13 @@ shk_status shk_shard_graph_publish(shk_asm *h, const uint64_t *node_counts, cons
                                            h->node_lo.as<uint64_t>(), h->node_hi.as<uint64_t>(), n, h->stream);
   SHK_CUDA(cudaGetLastError());
   PeerBlob b; memset(&b, 0, sizeof b);
-  SHK_CUDA(cudaIpcGetMemHandle(&b.arena, h->arena.p));
-  SHK_CUDA(cudaIpcGetMemHandle(&b.lo, h->node_lo.p));
-  if (h->kw == 2) SHK_CUDA(cudaIpcGetMemHandle(&b.hi, h->node_hi.p));
+  if (h->arena.p != h->arena_exported || h->arena.cap != h->arena_exported_cap) {   // once per allocation (a grown arena is a new one,
+    SHK_CUDA(cudaIpcGetMemHandle((cudaIpcMemHandle_t *)h->arena_ipc, h->arena.p));     // even at the old address)
+    h->arena_exported = h->arena.p; h->arena_exported_cap = h->arena.cap;
+  }
+  memcpy(&b.arena, h->arena_ipc, sizeof b.arena);
   b.off_slots = h->arena_off_slots; b.off_off = h->arena_off_off; b.off_edges = h->arena_off_edges; b.off_coh = h->arena_off_coh;
+  b.off_lo = h->arena_off_lo; b.off_hi = h->arena_off_hi;
   b.n_nodes = n; b.has_hi = h->kw == 2; b.device = (uint32_t)h->dev; b.magic = BLOB_MAGIC;
   memset(blob_out, 0, SHK_PEER_BLOB_BYTES);
   memcpy(blob_out, &b, sizeof b);
@@ -133,15 +144,10 @@ shk_status shk_shard_graph_connect(shk_asm *h, const void *blobs) {
     PeerBlob b; memcpy(&b, (const uint8_t *)blobs + (size_t)r * SHK_PEER_BLOB_BYTES, sizeof b);
     if (b.magic != BLOB_MAGIC) { set_error("peer blob of rank %u is not one of ours", r); return SHK_ERR_BAD_ARG; }
     if (b.n_nodes != t->node_off[r + 1] - t->node_off[r]) { set_error("peer blob of rank %u disagrees with the node counts", r); return SHK_ERR_BAD_ARG; }
-    uint8_t *A; const uint64_t *lo, *hi = nullptr;
-    if (r == me) {
-      A = (uint8_t *)h->arena.p; lo = h->node_lo.as<uint64_t>(); if (h->kw == 2) hi = h->node_hi.as<uint64_t>();
-    } else {
-      void *p;
-      SHK_TRY(open_peer(h, r, 0, b.arena, &p)); A = (uint8_t *)p;
-      SHK_TRY(open_peer(h, r, 1, b.lo, &p)); lo = (const uint64_t *)p;
-      if (b.has_hi) { SHK_TRY(open_peer(h, r, 2, b.hi, &p)); hi = (const uint64_t *)p; }
-    }
+    uint8_t *A;
+    if (r == me) A = (uint8_t *)h->arena.p;
+    else { void *p; SHK_TRY(open_peer(h, r, 0, b.arena, &p)); A = (uint8_t *)p; }
+    const uint64_t *lo = (const uint64_t *)(A + b.off_lo), *hi = b.has_hi ? (const uint64_t *)(A + b.off_hi) : nullptr;
     PeerView &pv = t->peer[r];
     pv.slots = (const u64 *)(A + b.off_slots); pv.off = (const u32 *)(A + b.off_off);
     pv.lo = (const u64 *)lo; pv.hi = (const u64 *)hi; pv.n_nodes = b.n_nodes;
