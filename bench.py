@@ -566,6 +566,41 @@ def sharded_arm(args, name, w, ctx, steps, warmup, with_e2e=True, with_cold=Fals
                "call_ms": {n: round(sum(v[1:]) / max(1, len(v) - 1), 3) for n, v in call_ms.items()},
                "ncontigs": json.loads(bytes(res))["ncontigs"] if res is not None else None, "nkmers": json.loads(info)["nkmers"]}
 
+    # ---- the same end to end from PACKED host buffers (a host that packs while it parses: 0.375 B per position
+    # cross the link, no K0): shk_asm_preprocess_packed + the same three calls.  The packing itself is timed apart. ----
+    e2e_packed = None
+    if with_e2e and not args.no_e2e and world == 1:
+        from sparrowhawk_b200.assembly_helper import pack_reads
+        nw = (nbytes + 31) // 32
+        pb = torch.empty(nw, dtype=torch.int64, pin_memory=True); pm = torch.empty(nw, dtype=torch.int32, pin_memory=True)
+        bview, mview = pb.numpy().view("uint64"), pm.numpy().view("uint32")
+        t0 = time.perf_counter()
+        _, _, nb_packed = pack_reads(seq, qual, MIN_QUAL, out=(bview, mview))
+        t_pack_all = (time.perf_counter() - t0) * 1e3
+        t0 = time.perf_counter()
+        pack_reads(seq[:nbytes // 16], qual[:nbytes // 16], MIN_QUAL, n_threads=1)
+        t_pack_1 = (time.perf_counter() - t0) * 1e3
+
+        def packed_step():
+            h.load_packed_ptr(pb.data_ptr(), pm.data_ptr(), nbytes, nb_packed, preprocess=True)
+            h.get_preprocessing_info(); h.assemble()
+            return h.get_assembly_view()
+        packed_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            resp = packed_step()
+        torch.cuda.synchronize()
+        ms_p = (time.perf_counter() - t0) * 1e3 / steps
+        sp_ = h.stats()
+        e2e_packed = {"value": total_bases / (ms_p * 1e-3), "unit": "bases/s", "ms_per_step": ms_p,
+                      "h2d_bytes_per_step": int(nw * 12), "d2h_bytes_per_step": int(sp_["unitig_bases"] + sp_["n_unitigs"] * 25 + sp_["n_links"] * 8 + 3 * 4200 + 128),
+                      "calls": "shk_asm_preprocess_packed + shk_asm_preprocessing_info + shk_asm_assemble + shk_asm_get_assembly (pointer + length)",
+                      "ncontigs": json.loads(bytes(resp))["ncontigs"], "nkmers": sp_["n_nodes"],
+                      "host_pack_ms_all_threads": round(t_pack_all, 2), "host_pack_GBps_one_thread": round(2 * (nbytes // 16) / (t_pack_1 * 1e-3) / 1e9, 2),
+                      "note": "input = the reads already packed by the host (shk_pack_reads_host layout); packing is host work a "
+                              "parser does while it reads and is timed apart (host_pack_*), as parsing is for `e2e`"}
+        del pb, pm
     n_nodes_global = json.loads(h.get_preprocessing_info())["nkmers"] if world > 1 else st["n_nodes"]   # (sharded: the ranks' sum)
     # ---- cold path: a FRESH handle, as the reference workflow uses one (new -> preprocess -> assemble,
     # Assembler.ts:92-100, with `helper = null` in between: the previous handle is gone) ----
@@ -574,8 +609,10 @@ def sharded_arm(args, name, w, ctx, steps, warmup, with_e2e=True, with_cold=Fals
         h.close()
         hc = AssemblyHelper.new(w["k"], False, w["min_count"], MIN_QUAL, 0, False, False, False, False, device=local)
         hc.set_stream(stream.cuda_stream or 1)
-        hc.load_reads_ptr(pin_seq.data_ptr(), pin_qual.data_ptr(), nbytes)
+        dsq, dql = pin_seq.cuda(), pin_qual.cuda()     # (from device memory: the load packs only, so the timed run cuts the reads too)
+        hc.load_reads_ptr(dsq.data_ptr(), dql.data_ptr(), nbytes, device=True)
         torch.cuda.synchronize()
+        del dsq, dql
         c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         c0.record(stream); hc.run(); c1.record(stream); torch.cuda.synchronize()
         first_run = c0.elapsed_time(c1)
@@ -646,7 +683,8 @@ def sharded_arm(args, name, w, ctx, steps, warmup, with_e2e=True, with_cold=Fals
            "n_gpus": world, "steps": steps, "warmup": warmup, "ms_per_step": ms_step,
            "higher_is_better": True, "scaling": "strong" if community else "weak", "vs_baseline": None,
            "dtype": "u64" if w["k"] <= 31 else "u128", "data": "synthetic", "config": cfg,
-           "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "cold": cold, "gpu_launches": int(launches), "clocks": clocks}
+           "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "e2e_packed": e2e_packed, "cold": cold, "gpu_launches": int(launches),
+           "clocks": clocks}
     h.close()
     del pins, pin_seq, pin_qual
     return out
@@ -663,6 +701,7 @@ def brief(name, r):
             "stage_ms": rf.get("stage_ms"),
             "e2e": ({k: r["e2e"][k] for k in ("value", "unit", "ms_per_step", "h2d_bytes_per_step", "d2h_bytes_per_step") if k in r["e2e"]}
                     if r.get("e2e") else None),
+            "e2e_packed": ({k: r["e2e_packed"][k] for k in ("value", "ms_per_step", "h2d_bytes_per_step")} if r.get("e2e_packed") else None),
             "cold": r.get("cold"), "gpu_launches": r["gpu_launches"], "clocks": r["clocks"],
             "config": {k: v for k, v in r["config"].items() if k in keep}}
 

@@ -100,6 +100,16 @@ shk_status shk_asm_preprocess_finish(shk_asm *h);
 shk_status shk_asm_preprocess_reads(shk_asm *h, const uint8_t *seq,
                                     const uint8_t *qual, size_t n);
 
+/* preprocess for hosts that PACK while they parse (what sketchlib's own reader does on the host,
+ * nthash_iterator.rs:206-252): the reads in the device layout — one u64 per 32 stream positions holding their 2-bit
+ * codes, first position most significant (A=0 C=1 T/U=2 G=3), and one u32 per 32 positions holding
+ * their validity bits, bit j = position j (valid = ACGTUacgtu with a passing quality; read separators, N and padding
+ * are 0).  0.375 bytes per position cross the link instead of 2, and K0 does not run.  n_positions
+ * counts every stream position (separators included), n_bases the sequence characters (the unit of the metric).
+ * shk_pack_reads_host builds the two arrays from the ASCII streams of shk_asm_preprocess_reads. */
+shk_status shk_asm_preprocess_packed(shk_asm *h, const uint64_t *bases, const uint32_t *mask, uint64_t n_positions,
+                                     uint64_t n_bases);
+
 /* AssemblyHelper.get_preprocessing_info() -> JSON {nkmers, histo[500],
  * used_min_count} — Assembler.ts:1-5,110.  Pointer valid until the next call
  * on the handle. */
@@ -166,6 +176,13 @@ shk_status shk_load_reads(shk_asm *h, const uint8_t *seq, const uint8_t *qual,
 /* Same, but seq/qual are DEVICE pointers (already in HBM). */
 shk_status shk_load_reads_device(shk_asm *h, const void *d_seq, const void *d_qual,
                                  size_t n, int append);
+
+/* The same from PACKED host arrays (layout: shk_asm_preprocess_packed): H2D only, no K0.  Replaces the resident reads. */
+shk_status shk_load_packed(shk_asm *h, const uint64_t *bases, const uint32_t *mask, uint64_t n_positions, uint64_t n_bases);
+/* Host-side packer (no device needed): ASCII seq / qual streams (qual may be NULL) -> bases[ceil(n/32)], mask[ceil(n/32)],
+ * *n_bases.  n_threads <= 0: all host threads.  Bit-identical to what K0 writes for the same input. */
+shk_status shk_pack_reads_host(const uint8_t *seq, const uint8_t *qual, size_t n, int min_qual, uint64_t *bases, uint32_t *mask,
+                               uint64_t *n_bases, int n_threads);
 
 /* K1a minimizer_partition over ALL resident packed reads: cuts the stream into
  * super-k-mer records grouped by minimizer bucket.  `reset` is kept for ABI
@@ -313,10 +330,10 @@ shk_status shk_shard_set_nodes(shk_asm *h, const void *d_lo, const void *d_hi,
 /* kernels read a remote neighbour's facts in place.  The host still   */
 /* runs every collective between the calls:                            */
 /*   shk_shard_count[_device]        (as above)                         */
-/*   host: all-reduce spectrum + totals + per-rank node counts          */
 /*   1 shk_shard_graph_publish    index over the owned nodes; blob out  */
-/*   host: all-gather the blobs (also the barrier "indices complete")   */
-/*   2 shk_shard_graph_connect    map the peers' memory                 */
+/*   host: ONE reduction carries spectrum + totals + per-rank node      */
+/*         counts + the blobs (also the barrier "indices complete")     */
+/*   2 shk_shard_graph_connect    global facts in, peers' memory mapped */
 /*   3 shk_shard_graph_edges      K3' neighbour validation              */
 /*   host: barrier ("edges complete")                                   */
 /*   4 shk_shard_graph_chains     K4' + local list ranking -> chains    */
@@ -348,14 +365,14 @@ typedef struct shk_shard_join_info {
                                    * borders and nothing above was produced — all-gather shk_shard_graph_cycle_info
                                    * and call shk_shard_graph_join again with it */
 } shk_shard_join_info;
-/* node_counts (HOST, u64[world]): surviving nodes of every rank; the other arguments as in shk_shard_set_nodes.
- * blob_out (HOST, SHK_PEER_BLOB_BYTES): what the other ranks need to map this rank's arrays. */
-shk_status shk_shard_graph_publish(shk_asm *h, const uint64_t *node_counts, const uint64_t *histo_global,
-                                   uint64_t n_instances_global, uint64_t n_bases_global, int used_min_count,
-                                   void *blob_out);
-/* blobs (HOST, world x SHK_PEER_BLOB_BYTES, rank order).  Fails with SHK_ERR_CUDA when peer memory cannot be
- * mapped (then every rank takes the replicated graph stage). */
-shk_status shk_shard_graph_connect(shk_asm *h, const void *blobs);
+/* blob_out (HOST, SHK_PEER_BLOB_BYTES): what the other ranks need to map this rank's arrays.  Needs only this rank's
+ * own count result, so the host can send the blob along with the spectrum / node-count reduction. */
+shk_status shk_shard_graph_publish(shk_asm *h, void *blob_out);
+/* blobs (HOST, world x SHK_PEER_BLOB_BYTES, rank order); node_counts (HOST, u64[world]): surviving nodes of every
+ * rank; the other arguments as in shk_shard_set_nodes.  Fails with SHK_ERR_CUDA when peer memory cannot be mapped
+ * (then every rank takes the replicated graph stage). */
+shk_status shk_shard_graph_connect(shk_asm *h, const void *blobs, const uint64_t *node_counts, const uint64_t *histo_global,
+                                   uint64_t n_instances_global, uint64_t n_bases_global, int used_min_count);
 shk_status shk_shard_graph_edges(shk_asm *h);
 /* *n_chains_out == UINT64_MAX: K3' ran out of list space on this rank — when ANY rank reports it, every rank calls
  * shk_shard_graph_edges again (the needed size is remembered), barrier, then shk_shard_graph_chains. */

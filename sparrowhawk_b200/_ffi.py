@@ -69,6 +69,9 @@ SYMBOLS = {
     "shk_get_stream": (C.c_void_p, [_H]),
     "shk_load_reads": (C.c_int, [_H, _U8P, _U8P, C.c_size_t, C.c_int]),
     "shk_load_reads_device": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_size_t, C.c_int]),
+    "shk_load_packed": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64]),
+    "shk_pack_reads_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_void_p, C.POINTER(C.c_uint64), C.c_int]),
+    "shk_asm_preprocess_packed": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64]),
     "shk_count": (C.c_int, [_H, C.c_int]),
     "shk_filter": (C.c_int, [_H]),
     "shk_build_graph": (C.c_int, [_H]),
@@ -100,8 +103,8 @@ SYMBOLS = {
                                       C.c_void_p, C.c_uint64, C.c_uint64, C.c_int]),
     "shk_fit_min_count": (C.c_int, [C.c_void_p, C.c_int]),
     # sharded graph stage (peer memory)
-    "shk_shard_graph_publish": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_int, C.c_void_p]),
-    "shk_shard_graph_connect": (C.c_int, [_H, C.c_void_p]),
+    "shk_shard_graph_publish": (C.c_int, [_H, C.c_void_p]),
+    "shk_shard_graph_connect": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_int]),
     "shk_shard_graph_edges": (C.c_int, [_H]),
     "shk_shard_graph_chains": (C.c_int, [_H, C.POINTER(C.c_uint64)]),
     "shk_shard_graph_records": (C.c_int, [_H, C.c_void_p, C.c_void_p]),

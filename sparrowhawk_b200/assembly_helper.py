@@ -54,6 +54,21 @@ def _read_contigs(lib, c):
             "tips_removed": nt.value, "bubbles_removed": nbub.value}
 
 
+def pack_reads(seq, qual, min_qual, n_threads=0, out=None):
+    """Host-side packer of include/shk.h (shk_pack_reads_host; needs no device): ASCII streams ->
+    (bases u64[ceil(n/32)], mask u32[ceil(n/32)], n_bases)."""
+    sp, n, k1 = _buf(seq)
+    qp, nq, k2 = _buf(qual)
+    nw = (n + 31) // 32
+    if out is None:
+        bases = np.empty(nw, np.uint64); mask = np.empty(nw, np.uint32)
+    else:
+        bases, mask = out
+    nb = C.c_uint64()
+    check(_ffi.lib().shk_pack_reads_host(sp, qp, n, int(min_qual), bases.ctypes.data, mask.ctypes.data, C.byref(nb), int(n_threads)))
+    return bases[:nw], mask[:nw], int(nb.value)
+
+
 def clean_graph(k, seqs, kc, circ, link_from, link_to, no_dead_end_removal=False, no_bubble_collapse=False):
     """Host graph cleaning of include/shk.h (shk_clean_graph) on plain arrays; needs no device."""
     lib = _ffi.lib()
@@ -154,6 +169,21 @@ class AssemblyHelper:
         if qual is not None and nq != n:
             raise ValueError("seq and qual streams differ in length")
         check(self._lib.shk_asm_preprocess_reads(self._h, sp, qp, n))
+
+    def preprocess_packed(self, bases, mask, n_positions, n_bases):
+        """reads already in the device layout (u64 2-bit words + u32 validity words; pack_reads() makes them)"""
+        b = np.ascontiguousarray(bases, dtype=np.uint64); m = np.ascontiguousarray(mask, dtype=np.uint32)
+        self._packed_keep = (b, m)
+        check(self._lib.shk_asm_preprocess_packed(self._h, b.ctypes.data, m.ctypes.data, int(n_positions), int(n_bases)))
+
+    def load_packed(self, bases, mask, n_positions, n_bases):
+        b = np.ascontiguousarray(bases, dtype=np.uint64); m = np.ascontiguousarray(mask, dtype=np.uint32)
+        self._packed_keep = (b, m)
+        check(self._lib.shk_load_packed(self._h, b.ctypes.data, m.ctypes.data, int(n_positions), int(n_bases)))
+
+    def load_packed_ptr(self, bases_ptr, mask_ptr, n_positions, n_bases, preprocess=False):
+        fn = self._lib.shk_asm_preprocess_packed if preprocess else self._lib.shk_load_packed
+        check(fn(self._h, C.c_void_p(bases_ptr), C.c_void_p(mask_ptr), int(n_positions), int(n_bases)))
 
     def preprocess_push(self, data):
         p, n, keep = _buf(data)

@@ -369,6 +369,138 @@ static shk_status load_reads_host(shk_asm *h, const uint8_t *seq, const uint8_t 
   return SHK_OK;
 }
 
+// ---- packed reads from the host (what a host that packs while it parses hands over) ---------------
+// 32 positions -> one u64 of 2-bit codes (first base most significant, S4) + one u32 of validity bits (S2/S3): the
+// layout of shk_device.cuh, 0.375 bytes per position instead of the 2 bytes of the ASCII streams.
+static inline void pack_word_scalar(const uint8_t *seq, const uint8_t *qual, uint64_t p0, uint64_t n, int min_qual,
+                                    uint64_t &bw, uint32_t &mw, uint64_t &nb) {
+  bw = 0; mw = 0;
+  for (int j = 0; j < 32; ++j) {
+    const uint64_t p = p0 + j;
+    const uint8_t c = p < n ? seq[p] : (uint8_t)'\n';
+    const bool ok = p < n && shk_valid_base(c) && (!qual || shk_qual_ok(qual[p], min_qual));
+    bw = (bw << 2) | (uint64_t)shk_encode_base(c);
+    mw |= (ok ? 1u : 0u) << j;
+    nb += (c != '\n') ? 1 : 0;
+  }
+}
+#if defined(__x86_64__)
+#include <immintrin.h>
+// 32 positions at once: validity by byte compares + movemask (as the quality bits), codes by PEXT of bits 1-2 of
+// every byte (bytes swapped first: PEXT packs from the low end and the first base is the most significant)
+__attribute__((target("bmi2,sse4.2,popcnt")))
+static void pack_range_bmi2(const uint8_t *seq, const uint8_t *qual, uint64_t w0, uint64_t w1, uint64_t n, int min_qual,
+                            uint64_t *bases, uint32_t *mask, uint64_t *n_bases) {
+  const int T = min_qual + 33;
+  const __m128i tq = _mm_set1_epi8((char)(T - 1)), lower = _mm_set1_epi8(0x20), nl = _mm_set1_epi8('\n');
+  const __m128i ca = _mm_set1_epi8('a'), cc = _mm_set1_epi8('c'), cg = _mm_set1_epi8('g'), ct = _mm_set1_epi8('t'), cu = _mm_set1_epi8('u');
+  const bool fastq = qual && T >= 1 && T <= 127;
+  uint64_t nb = 0;
+  for (uint64_t w = w0; w < w1; ++w) {
+    const uint64_t p0 = w * 32;
+    if (p0 + 32 > n || (qual && !fastq)) { uint64_t bw; uint32_t mw; pack_word_scalar(seq, qual, p0, n, min_qual, bw, mw, nb); bases[w] = bw; mask[w] = mw; continue; }
+    uint32_t mw = 0, nlm = 0;
+    for (int half = 0; half < 2; ++half) {
+      const __m128i x = _mm_loadu_si128((const __m128i *)(seq + p0 + 16 * half));
+      const __m128i xl = _mm_or_si128(x, lower);
+      __m128i v = _mm_or_si128(_mm_or_si128(_mm_cmpeq_epi8(xl, ca), _mm_cmpeq_epi8(xl, cc)),
+                               _mm_or_si128(_mm_or_si128(_mm_cmpeq_epi8(xl, cg), _mm_cmpeq_epi8(xl, ct)), _mm_cmpeq_epi8(xl, cu)));
+      if (fastq) {
+        const __m128i q = _mm_loadu_si128((const __m128i *)(qual + p0 + 16 * half));
+        v = _mm_and_si128(v, _mm_or_si128(_mm_cmpgt_epi8(q, tq), q));          // (bytes >= 128 pass: their sign bit is set)
+      }
+      mw |= (uint32_t)_mm_movemask_epi8(v) << (16 * half);
+      nlm |= (uint32_t)_mm_movemask_epi8(_mm_cmpeq_epi8(x, nl)) << (16 * half);
+    }
+    uint64_t bw = 0;
+    for (int j = 0; j < 4; ++j) {
+      uint64_t x; memcpy(&x, seq + p0 + 8 * j, 8);
+      bw = (bw << 16) | _pext_u64(__builtin_bswap64(x), 0x0606060606060606ull);
+    }
+    bases[w] = bw; mask[w] = mw;
+    nb += 32 - (uint64_t)_mm_popcnt_u32(nlm);
+  }
+  *n_bases = nb;
+}
+#endif
+static void pack_range(const uint8_t *seq, const uint8_t *qual, uint64_t w0, uint64_t w1, uint64_t n, int min_qual,
+                       uint64_t *bases, uint32_t *mask, uint64_t *n_bases) {
+#if defined(__x86_64__)
+  static const bool bmi2 = __builtin_cpu_supports("bmi2") && __builtin_cpu_supports("sse4.2") && __builtin_cpu_supports("popcnt");
+  if (bmi2) { pack_range_bmi2(seq, qual, w0, w1, n, min_qual, bases, mask, n_bases); return; }
+#endif
+  uint64_t nb = 0;
+  for (uint64_t w = w0; w < w1; ++w) { uint64_t bw; uint32_t mw; pack_word_scalar(seq, qual, w * 32, n, min_qual, bw, mw, nb); bases[w] = bw; mask[w] = mw; }
+  *n_bases = nb;
+}
+
+// Sliced host->device copy of packed reads on the copy stream; on a handle that takes the K1a -> K1b path (cut), K1a
+// of slice i-1 runs underneath the copy of slice i+1 — the packed twin of load_reads_overlapped (no K0: nothing to pack).
+static shk_status load_packed_impl(shk_asm *h, const uint64_t *bases, const uint32_t *mask, uint64_t n_positions, uint64_t n_bases) {
+  SHK_TRY(require_device(h));
+  if ((!bases || !mask) && n_positions) { set_error("null packed arrays"); return SHK_ERR_BAD_ARG; }
+  const uint64_t total = (n_positions + 31) / 32;
+  h->st.host_qual_bits = 0;
+  SHK_CUDA(cudaEventRecord(h->ev[0], h->stream));
+  SHK_TRY(h->bases.ensure((total + 5) * 8)); SHK_TRY(h->mask.ensure((total + 5) * 4));
+  uint64_t *b = h->bases.as<uint64_t>() + 1;
+  uint32_t *m = h->mask.as<uint32_t>() + 1;
+  SHK_CUDA(cudaMemsetAsync(h->bases.p, 0, 8, h->stream));
+  SHK_CUDA(cudaMemsetAsync(h->mask.p, 0, 4, h->stream));
+  SHK_CUDA(cudaMemsetAsync(b + total, 0, 4 * 8, h->stream));
+  SHK_CUDA(cudaMemsetAsync(m + total, 0, 4 * 4, h->stream));
+  h->h_pinned[7] = n_bases;                                            // ([7] of the mirror is not a counter the kernels report)
+  SHK_CUDA(cudaMemcpyAsync(d_counters(h) + 3, h->h_pinned + 7, 8, cudaMemcpyHostToDevice, h->stream));
+  h->nwords = total; h->n_positions = n_positions;
+  h->counted = h->filtered = h->graphed = false; h->partition_done = false;
+  const bool cut = n_positions * 3 / 8 >= h->overlap_min / 4 && fast_ready_for(h, n_positions);
+  if (!cut || !total) {
+    if (total) {
+      SHK_CUDA(cudaMemcpyAsync(b, bases, total * 8, cudaMemcpyHostToDevice, h->stream));
+      SHK_CUDA(cudaMemcpyAsync(m, mask, total * 4, cudaMemcpyHostToDevice, h->stream));
+    }
+    SHK_CUDA(cudaEventRecord(h->ev[1], h->stream));
+    return SHK_OK;
+  }
+  SHK_TRY(fast_params(h, n_positions));
+  const int S = 8;
+  const uint64_t tile = (uint64_t)partition_tile_words();
+  const uint64_t slice = ((total + S - 1) / S + tile - 1) / tile * tile;     // words per slice, whole K1a tiles
+  if (!h->copy_stream) {
+    SHK_CUDA(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+    for (auto &e : h->copy_ev) SHK_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  }
+  SHK_TRY(fast_prologue(h));
+  SHK_CUDA(cudaEventRecord(h->copy_ev[S], h->stream));
+  SHK_CUDA(cudaStreamWaitEvent(h->copy_stream, h->copy_ev[S], 0));
+  bool first = true;
+  auto k1a = [&](int i) {
+    const uint64_t wb = (uint64_t)i * slice, we = std::min<uint64_t>(total, (uint64_t)(i + 1) * slice);
+    if (wb >= we) return;
+    if (first) { cudaEventRecord(h->ev[8], h->stream); first = false; }
+    h->st.gpu_launches += launch_partition(h->kw, b, m, total, h->p.k, h->P, h->rcap, h->skrecs.p, h->bfill.as<uint64_t>(),
+                                           d_counters(h), h->stream, wb, we);
+  };
+  int last = -1;
+  for (int i = 0; i < S; ++i) {
+    const uint64_t off = (uint64_t)i * slice;
+    if (off >= total) break;
+    const uint64_t len = std::min<uint64_t>(slice, total - off);
+    SHK_CUDA(cudaMemcpyAsync(b + off, bases + off, len * 8, cudaMemcpyHostToDevice, h->copy_stream));
+    SHK_CUDA(cudaMemcpyAsync(m + off, mask + off, len * 4, cudaMemcpyHostToDevice, h->copy_stream));
+    SHK_CUDA(cudaEventRecord(h->copy_ev[i], h->copy_stream));
+    SHK_CUDA(cudaStreamWaitEvent(h->stream, h->copy_ev[i], 0));
+    if (i == 0) SHK_CUDA(cudaEventRecord(h->ev[1], h->stream));
+    if (i > 0) k1a(i - 1);                                               // (its halo reaches into slice i: arrived)
+    last = i;
+  }
+  if (last >= 0) k1a(last);
+  SHK_CUDA(cudaGetLastError());
+  SHK_CUDA(cudaEventRecord(h->ev[9], h->stream));
+  h->partition_done = true;
+  return SHK_OK;
+}
+
 // ---- K1a: minimizer partition into super-k-mer records ---------------------
 static uint32_t next_pow2(uint64_t x) { uint32_t p = 1; while (p < x && p < (1u << 30)) p <<= 1; return p; }
 
@@ -1032,6 +1164,26 @@ shk_status shk_load_reads_device(shk_asm *h, const void *d_seq, const void *d_qu
   SHK_CUDA(cudaEventRecord(h->ev[1], h->stream));
   return SHK_OK;
 }
+shk_status shk_pack_reads_host(const uint8_t *seq, const uint8_t *qual, size_t n, int min_qual, uint64_t *bases, uint32_t *mask,
+                               uint64_t *n_bases, int n_threads) {
+  if ((!seq || !bases || !mask) && n) { set_error("null argument"); return SHK_ERR_BAD_ARG; }
+  const uint64_t total = ((uint64_t)n + 31) / 32;
+  unsigned T = n_threads > 0 ? (unsigned)n_threads : std::max(1u, std::thread::hardware_concurrency());
+  T = (unsigned)std::min<uint64_t>(T, std::max<uint64_t>(1, total / 4096));
+  std::vector<uint64_t> nb(T, 0);
+  std::vector<std::thread> th;
+  for (unsigned t = 1; t < T; ++t)
+    th.emplace_back([&, t] { pack_range(seq, qual, total * t / T, total * (t + 1) / T, n, min_qual, bases, mask, &nb[t]); });
+  pack_range(seq, qual, 0, total / T, n, min_qual, bases, mask, &nb[0]);
+  for (auto &x : th) x.join();
+  uint64_t s = 0;
+  for (uint64_t v : nb) s += v;
+  if (n_bases) *n_bases = s;
+  return SHK_OK;
+}
+shk_status shk_load_packed(shk_asm *h, const uint64_t *bases, const uint32_t *mask, uint64_t n_positions, uint64_t n_bases) {
+  return load_packed_impl(h, bases, mask, n_positions, n_bases);
+}
 shk_status shk_count(shk_asm *h, int reset) { return count_impl(h, reset); }
 shk_status shk_filter(shk_asm *h) { if (!h) { set_error("null handle"); return SHK_ERR_BAD_ARG; } return filter_impl(h, h->p.min_count); }
 shk_status shk_build_graph(shk_asm *h) { return graph_impl(h); }
@@ -1215,6 +1367,17 @@ shk_status shk_asm_preprocess_reads(shk_asm *h, const uint8_t *seq, const uint8_
   SHK_TRY(load_reads_host(h, seq, qual, n, 0));
   progress(h, "preprocess:bulk:loop:end");
   progress(h, "preprocess:bulk:sorting");   // the counting step (reference bulk mode sorts; we hash)
+  return finish_preprocess(h, "bulk", true);
+}
+
+shk_status shk_asm_preprocess_packed(shk_asm *h, const uint64_t *bases, const uint32_t *mask, uint64_t n_positions, uint64_t n_bases) {
+  SHK_TRY(require_device(h));
+  progress(h, "preprocess:start");
+  progress(h, "preprocess:bulk:start");
+  progress(h, "preprocess:bulk:loop:start");
+  SHK_TRY(load_packed_impl(h, bases, mask, n_positions, n_bases));
+  progress(h, "preprocess:bulk:loop:end");
+  progress(h, "preprocess:bulk:sorting");
   return finish_preprocess(h, "bulk", true);
 }
 

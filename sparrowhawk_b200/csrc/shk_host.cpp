@@ -11,7 +11,11 @@
 #include <map>
 #include <numeric>
 #include <chrono>
+#include <condition_variable>
+#include <deque>
+#include <mutex>
 #include <string>
+#include <thread>
 #include <tuple>
 #include <vector>
 
@@ -83,6 +87,102 @@ shk_status fastq_feed(shk_asm *h, const uint8_t *bytes, size_t n) {
   return SHK_OK;
 }
 
+// ---------------------------------------------------------------------------
+// File form of preprocess(): one decoder thread per file (the two mates of a paired run inflate and split in
+// parallel; the reference decodes them one after the other through one MultiGzDecoder,
+// sketchlib.rust/src/fastx_wasm.rs:52-69), each cutting its reads into batches that the CALLING thread
+// loads while the decoders are already on the next batch — so gunzip, line splitting and H2D + K0 overlap.
+// Mates are independent reads (S2) and the result does not depend on the batching (S8), so the batches
+// are loaded in the order they arrive.  Progress strings come from the calling thread only.
+// ---------------------------------------------------------------------------
+namespace {
+struct ReadBatch { std::vector<uint8_t> seq, qual; uint64_t reads = 0; };
+struct BatchQueue {
+  std::mutex mu; std::condition_variable cv_put, cv_get;
+  std::deque<ReadBatch> q; int producers = 0; bool abort = false;
+  shk_status err = SHK_OK; std::string err_msg;
+  bool put(ReadBatch &&b) {                      // false: the consumer gave up
+    std::unique_lock<std::mutex> lk(mu);
+    cv_put.wait(lk, [&] { return q.size() < 4 || abort; });
+    if (abort) return false;
+    q.push_back(std::move(b)); cv_get.notify_one();
+    return true;
+  }
+  void fail(shk_status s, const std::string &m) {
+    std::lock_guard<std::mutex> lk(mu);
+    if (err == SHK_OK) { err = s; err_msg = m; }
+    abort = true; cv_get.notify_all(); cv_put.notify_all();
+  }
+  void done() { std::lock_guard<std::mutex> lk(mu); --producers; cv_get.notify_all(); }
+};
+
+// one file -> batches.  limit_reads > 0: a batch per that many reads (chunked mode); else by size.
+void decode_file(const char *path, uint64_t limit_reads, BatchQueue *bq) {
+  auto fail = [&](shk_status s, const char *fmt, auto... a) { char m[400]; snprintf(m, sizeof m, fmt, a...); bq->fail(s, m); bq->done(); };
+  gzFile gz = gzopen(path, "rb");                // transparent for plain files, multi-member aware
+  if (!gz) return fail(SHK_ERR_IO, "cannot open %s", path);
+  struct Closer { gzFile &g; ~Closer() { if (g) gzclose(g); } } closer{gz};
+  gzbuffer(gz, 1 << 20);
+  std::vector<uint8_t> buf(1 << 22), pend;
+  ReadBatch cur;
+  const size_t limit_bytes = 32u << 20;
+  int line_in_rec = 0; uint64_t nrec = 0;
+  auto line = [&](const uint8_t *l, size_t n) -> bool {
+    while (n && l[n - 1] == '\r') --n;
+    switch (line_in_rec) {
+      case 0:
+        if (n == 0) return true;
+        if (l[0] == '>') { fail(SHK_ERR_FORMAT, "FASTA input in %s: the assembler needs FASTQ reads", path); return false; }
+        if (l[0] != '@') { fail(SHK_ERR_FORMAT, "%s: FASTQ record %llu does not start with '@'", path, (unsigned long long)nrec); return false; }
+        line_in_rec = 1; return true;
+      case 1:
+        cur.seq.insert(cur.seq.end(), l, l + n); cur.seq.push_back('\n');
+        line_in_rec = 2; return true;
+      case 2:
+        if (n == 0 || l[0] != '+') { fail(SHK_ERR_FORMAT, "%s: FASTQ record %llu: missing '+' line", path, (unsigned long long)nrec); return false; }
+        line_in_rec = 3; return true;
+      default: {
+        const size_t want = cur.seq.size() - cur.qual.size() - 1;
+        if (n != want) { fail(SHK_ERR_FORMAT, "%s: FASTQ record %llu: %zu quality values for %zu bases", path, (unsigned long long)nrec, n, want); return false; }
+        cur.qual.insert(cur.qual.end(), l, l + n); cur.qual.push_back('\n');
+        line_in_rec = 0; ++nrec; ++cur.reads;
+        if (limit_reads ? cur.reads >= limit_reads : cur.seq.size() >= limit_bytes) {
+          ReadBatch out; out.seq.reserve(cur.seq.capacity()); out.qual.reserve(cur.qual.capacity());
+          std::swap(out, cur);
+          if (!bq->put(std::move(out))) { bq->done(); return false; }
+        }
+        return true;
+      }
+    }
+  };
+  auto feed = [&](const uint8_t *bytes, size_t n) -> bool {
+    size_t i = 0;
+    while (i < n) {
+      const uint8_t *nl = (const uint8_t *)memchr(bytes + i, '\n', n - i);
+      if (!nl) { pend.insert(pend.end(), bytes + i, bytes + n); break; }
+      const size_t len = (size_t)(nl - (bytes + i));
+      if (!pend.empty()) {
+        pend.insert(pend.end(), bytes + i, bytes + i + len);
+        std::vector<uint8_t> l; l.swap(pend);
+        if (!line(l.data(), l.size())) return false;
+      } else if (!line(bytes + i, len)) return false;
+      i += len + 1;
+    }
+    return true;
+  };
+  for (;;) {
+    const int r = gzread(gz, buf.data(), (unsigned)buf.size());
+    if (r < 0) { int e; const char *m = gzerror(gz, &e); return fail(SHK_ERR_FORMAT, "gzip error in %s: %s", path, m); }
+    if (r == 0) break;
+    if (!feed(buf.data(), (size_t)r)) return;    // (failed or aborted: fail() / done() already called)
+  }
+  if (!feed((const uint8_t *)"\n", 1)) return;   // a file may end without a trailing newline; records never span files
+  if (line_in_rec != 0 || !pend.empty()) return fail(SHK_ERR_FORMAT, "truncated FASTQ record at end of %s", path);
+  if (cur.reads && !bq->put(std::move(cur))) { bq->done(); return; }
+  bq->done();
+}
+}  // namespace
+
 shk_status parse_fastq_files(shk_asm *h, const char *p1, const char *p2) {
   const char *paths[2] = {p1, p2};
   h->any_batch_counted = false; h->total_reads = 0; h->batch_reads = 0; h->line_in_rec = 0;
@@ -91,24 +191,33 @@ shk_status parse_fastq_files(shk_asm *h, const char *p1, const char *p2) {
   progress(h, "preprocess:start");
   progress(h, chunked ? "preprocess:chunked:start" : "preprocess:bulk:start");
   if (!chunked) progress(h, "preprocess:bulk:loop:start");
-  std::vector<uint8_t> buf(1 << 22);
-  for (int f = 0; f < 2; ++f) {
-    if (!paths[f]) continue;
-    gzFile gz = gzopen(paths[f], "rb");      // transparent for plain files, multi-member aware
-    if (!gz) { set_error("cannot open %s", paths[f]); return SHK_ERR_IO; }
-    gzbuffer(gz, 1 << 20);
-    for (;;) {
-      int r = gzread(gz, buf.data(), (unsigned)buf.size());
-      if (r < 0) { int e; set_error("gzip error in %s: %s", paths[f], gzerror(gz, &e)); gzclose(gz); return SHK_ERR_FORMAT; }
-      if (r == 0) break;
-      shk_status s = fastq_feed(h, buf.data(), (size_t)r);
-      if (s != SHK_OK) { gzclose(gz); return s; }
+  BatchQueue bq;
+  std::vector<std::thread> th;
+  for (int f = 0; f < 2; ++f) if (paths[f]) ++bq.producers;
+  for (int f = 0; f < 2; ++f)
+    if (paths[f]) th.emplace_back(decode_file, paths[f], chunked ? (uint64_t)h->p.chunk_size : 0ull, &bq);
+  shk_status st = SHK_OK;
+  uint64_t next_tick = 500000;
+  for (;;) {
+    ReadBatch b;
+    {
+      std::unique_lock<std::mutex> lk(bq.mu);
+      bq.cv_get.wait(lk, [&] { return !bq.q.empty() || bq.producers == 0 || bq.abort; });
+      if (bq.abort && bq.err != SHK_OK) break;
+      if (bq.q.empty()) { if (bq.producers == 0) break; continue; }
+      b = std::move(bq.q.front()); bq.q.pop_front();
+      bq.cv_put.notify_one();
     }
-    gzclose(gz);
-    // a file may end without a trailing newline; records never span files
-    SHK_TRY(fastq_feed(h, (const uint8_t *)"\n", 1));
-    if (h->line_in_rec != 0) { set_error("truncated FASTQ record at end of %s", paths[f]); return SHK_ERR_FORMAT; }
+    h->hseq.swap(b.seq); h->hqual.swap(b.qual);
+    h->total_reads += b.reads; h->batch_reads = b.reads;
+    char s[96];
+    if (chunked) { snprintf(s, sizeof s, "preprocess:chunked:loop:%llu", (unsigned long long)h->total_reads); progress(h, s); }
+    else while (h->total_reads >= next_tick) { snprintf(s, sizeof s, "preprocess:bulk:loop:%llu", (unsigned long long)next_tick); progress(h, s); next_tick += 500000; }
+    st = shk_internal_flush_batch(h, false);       // H2D + K0 of this batch, appended to the resident reads
+    if (st != SHK_OK) { bq.fail(st, shk_last_error()); break; }
   }
+  for (auto &t : th) t.join();
+  if (bq.err != SHK_OK) { set_error("%s", bq.err_msg.c_str()); return bq.err; }
   if (!chunked) { progress(h, "preprocess:bulk:loop:end"); progress(h, "preprocess:bulk:sorting"); }
   SHK_TRY(shk_internal_flush_batch(h, true));
   // shared tail (fit / filter / saving / end) lives in the API file

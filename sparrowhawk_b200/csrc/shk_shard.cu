@@ -62,29 +62,12 @@ shk_status read_back(shk_asm *h, uint32_t *hs) {
 
 extern "C" {
 
-// ---- 1. publish: global facts in, this rank's index built over ITS nodes, the peer blob out -------------------
-shk_status shk_shard_graph_publish(shk_asm *h, const uint64_t *node_counts, const uint64_t *histo_global,
-                                   uint64_t n_instances_global, uint64_t n_bases_global, int used_min_count, void *blob_out) {
+// ---- 1. publish: this rank's index built over ITS nodes, the peer blob out -------------------------------------
+shk_status shk_shard_graph_publish(shk_asm *h, void *blob_out) {
   SHK_TRY(require_device(h));
-  if (!h->shard_world || !node_counts || !blob_out) { set_error("shard_graph_publish: not in a sharded run / null argument"); return SHK_ERR_BAD_ARG; }
-  const uint32_t W = h->shard_world, me = h->shard_rank;
-  if (W > SHK_MAX_WORLD) { set_error("world %u > %d", W, SHK_MAX_WORLD); return SHK_ERR_BAD_ARG; }
-  uint64_t tot = 0;
-  for (uint32_t r = 0; r < W; ++r) { h->shard_node_off[r] = (uint32_t)tot; tot += node_counts[r]; }
-  if (tot > 0x7FFFFFF0ull) { set_error("too many nodes for 32-bit element ids (%llu)", (unsigned long long)tot); return SHK_ERR_BAD_ARG; }
-  h->shard_node_off[W] = (uint32_t)tot;
+  if (!h->shard_world || !blob_out) { set_error("shard_graph_publish: not in a sharded run / null argument"); return SHK_ERR_BAD_ARG; }
+  if (h->shard_world > SHK_MAX_WORLD) { set_error("world %u > %d", h->shard_world, SHK_MAX_WORLD); return SHK_ERR_BAD_ARG; }
   const uint32_t n = (uint32_t)h->shard_nodes_local;
-  if (node_counts[me] != n) { set_error("node_counts[rank] = %llu, this rank holds %u", (unsigned long long)node_counts[me], n); return SHK_ERR_BAD_ARG; }
-  h->shard_nodes_global = tot;
-  // global facts for the reference-facing getters (identical on every rank)
-  if (histo_global) {
-    memcpy(h->histo, histo_global, sizeof h->histo);
-    uint64_t nd = 0;
-    for (int i = 0; i < SHK_HISTO_BINS; ++i) nd += h->histo[i];
-    h->st.n_distinct = nd; h->histo_valid = true;
-  }
-  h->st.n_instances = n_instances_global; h->st.n_bases = n_bases_global; h->n_bases = n_bases_global;
-  if (used_min_count >= 0) h->st.used_min_count = used_min_count;
   h->st.n_nodes = n;                                   // the exports of this handle cover ITS nodes
   // arena (plain cudaMalloc: it is exported): [slots u64 x (2n+2)] [off u32 x (P+2)] [edges u8 x n] [chain_of_head u32 x 2n]
   // [key lo u64 x n] [key hi u64 x n] — the keys are a copy of this rank's node arrays, so that one handle covers all
@@ -125,15 +108,34 @@ shk_status shk_shard_graph_publish(shk_asm *h, const uint64_t *node_counts, cons
   memcpy(blob_out, &b, sizeof b);
   h->filtered = true; h->graphed = false; h->hu.valid = false;
   h->shard_graph = true;
-  shk_internal_build_pre_json(h);                      // nkmers = the global node count
   return SHK_OK;
 }
 
-// ---- 2. connect: map every other rank's arrays, write the topology for the kernels ---------------------------
-shk_status shk_shard_graph_connect(shk_asm *h, const void *blobs) {
+// ---- 2. connect: the global facts in, every other rank's arrays mapped, the topology written for the kernels -------
+shk_status shk_shard_graph_connect(shk_asm *h, const void *blobs, const uint64_t *node_counts, const uint64_t *histo_global,
+                                   uint64_t n_instances_global, uint64_t n_bases_global, int used_min_count) {
   SHK_TRY(require_device(h));
-  if (!h->shard_graph || !blobs) { set_error("shard_graph_connect before publish / null blobs"); return SHK_ERR_STATE; }
+  if (!h->shard_graph || !blobs || !node_counts) { set_error("shard_graph_connect before publish / null argument"); return SHK_ERR_STATE; }
   const uint32_t W = h->shard_world, me = h->shard_rank;
+  uint64_t tot = 0;
+  for (uint32_t r = 0; r < W; ++r) { h->shard_node_off[r] = (uint32_t)tot; tot += node_counts[r]; }
+  if (tot > 0x7FFFFFF0ull) { set_error("too many nodes for 32-bit element ids (%llu)", (unsigned long long)tot); return SHK_ERR_BAD_ARG; }
+  h->shard_node_off[W] = (uint32_t)tot;
+  if (node_counts[me] != h->shard_nodes_local) {
+    set_error("node_counts[rank] = %llu, this rank holds %llu", (unsigned long long)node_counts[me], (unsigned long long)h->shard_nodes_local);
+    return SHK_ERR_BAD_ARG;
+  }
+  h->shard_nodes_global = tot;
+  // global facts for the reference-facing getters (identical on every rank)
+  if (histo_global) {
+    memcpy(h->histo, histo_global, sizeof h->histo);
+    uint64_t nd = 0;
+    for (int i = 0; i < SHK_HISTO_BINS; ++i) nd += h->histo[i];
+    h->st.n_distinct = nd; h->histo_valid = true;
+  }
+  h->st.n_instances = n_instances_global; h->st.n_bases = n_bases_global; h->n_bases = n_bases_global;
+  if (used_min_count >= 0) h->st.used_min_count = used_min_count;
+  shk_internal_build_pre_json(h);                      // nkmers = the global node count
   SHK_TRY(h->topo_pin.ensure_host(sizeof(ShardTopo)));
   SHK_TRY(h->topo.ensure(sizeof(ShardTopo)));
   ShardTopo *t = (ShardTopo *)h->topo_pin.p;

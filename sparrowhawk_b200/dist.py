@@ -116,17 +116,18 @@ class GpuEngine:
         self.h.build_graph()
 
     # ---- sharded graph stage (include/shk.h): peer memory, chains, final join ----
-    def graph_publish(self, counts, histo, n_inst, n_bases, used_mc):
-        c = np.ascontiguousarray(counts, dtype=np.uint64)
-        hh = np.ascontiguousarray(histo, dtype=np.uint64)
+    def graph_publish(self):
         blob = np.zeros(_ffi.PEER_BLOB_BYTES, np.uint8)
-        check(self.lib.shk_shard_graph_publish(self.h._h, c.ctypes.data, hh.ctypes.data, int(n_inst), int(n_bases), int(used_mc),
-                                               blob.ctypes.data))
+        check(self.lib.shk_shard_graph_publish(self.h._h, blob.ctypes.data))
         return blob
 
-    def graph_connect(self, blobs):
+    def graph_connect(self, blobs, counts, histo, n_inst, n_bases, used_mc):
         b = np.ascontiguousarray(blobs, dtype=np.uint8)
-        return int(self.lib.shk_shard_graph_connect(self.h._h, b.ctypes.data))      # status: the caller agrees on a fallback
+        c = np.ascontiguousarray(counts, dtype=np.uint64)
+        hh = np.ascontiguousarray(histo, dtype=np.uint64)
+        # status, not an exception: every rank has to agree on a fallback
+        return int(self.lib.shk_shard_graph_connect(self.h._h, b.ctypes.data, c.ctypes.data, hh.ctypes.data, int(n_inst), int(n_bases),
+                                                    int(used_mc)))
 
     def graph_edges(self):
         check(self.lib.shk_shard_graph_edges(self.h._h))
@@ -254,35 +255,31 @@ def _gather_var(t, counts, unit, group=None):
     return torch.cat([flat[r * n_max * unit: r * n_max * unit + counts[r] * unit] for r in range(world)])
 
 
-def _sharded_graph(eng, group, counts, g_hist, g_inst, g_bases, used_mc, mark):
+def _sharded_graph(eng, group, blobs, counts, g_hist, g_inst, g_bases, used_mc, mark):
     """The graph stage with every rank on its own nodes (include/shk.h "sharded graph stage").  Returns "sharded",
-    or None when this run has to take the replicated stage instead (peer memory unavailable, or an unbranched
-    cycle crosses rank borders) — the same answer on every rank."""
+    or None when this run has to take the replicated stage instead (peer memory unavailable) — the same answer on
+    every rank.  The index over the owned nodes has been built and every rank's blob has arrived with the reduction."""
     world, dev = dist.get_world_size(group), eng.device
-    # 1. index over the owned nodes, peer blob out; the all-gather of the blobs is the barrier "indices complete"
-    blob = eng.graph_publish(counts, g_hist, g_inst, g_bases, used_mc)
-    allb = torch.empty(world * blob.size, dtype=torch.uint8, device=dev)
-    _ag_flat(allb, torch.from_numpy(blob).to(dev), group)
-    blobs = allb.cpu().numpy()
-    # 2. map the peers; every rank must succeed
-    st = eng.graph_connect(blobs)
-    ok = _gather_host_ints([st], dev, group)
-    if int(ok.max()) != 0:
-        if st != 0 and dist.get_rank(group) == 0:
-            import sys
-            print("[shk] peer memory unavailable (%s): replicated graph stage" % _ffi.lib().shk_last_error().decode(errors="replace"),
-                  file=sys.stderr)
-        return None
+    # 2. map the peers (cached while their allocations stay the same).  A rank that cannot sits the kernels out and
+    #    says so with its chain count; everybody then falls back together.
+    st = eng.graph_connect(blobs, counts, g_hist, g_inst, g_bases, used_mc)
+    if st != 0 and dist.get_rank(group) == 0:
+        import sys
+        print("[shk] peer memory unavailable (%s): replicated graph stage" % _ffi.lib().shk_last_error().decode(errors="replace"),
+              file=sys.stderr)
     mark("publish")
     for attempt in range(3):
         # 3. K3' over the owned nodes; barrier "edges complete"
-        eng.graph_edges()
+        if st == 0:
+            eng.graph_edges()
         _barrier(dev, group)
         if attempt == 0:
             mark("edges")
         # 4. K4' + local list ranking: one chain per stretch of a unitig inside this rank
-        nch = eng.graph_chains()
+        nch = eng.graph_chains() if st == 0 else -2
         chain_counts = [int(x) for x in _gather_host_ints([nch], dev, group)[:, 0]]     # (barrier "chain numbers complete")
+        if min(chain_counts) == -2:
+            return None                              # some rank has no peer memory
         if min(chain_counts) >= 0:
             break                                    # (-1: a rank's K3' list was too small; sized now, once more)
     else:
@@ -444,20 +441,28 @@ def sharded_run(eng, group=None, timings=None):
     n_local, _ = eng.local_counts()
     mark("count")
 
-    # ---- one all-reduce: spectrum, totals and every rank's node count (slot 502 + r) ----
-    red = torch.zeros(502 + world, **i64)
-    red[:500] = torch.from_numpy(eng.histogram().astype(np.int64))
-    red[500:502] = torch.tensor([inst_local, eng.n_bases()], dtype=torch.int64)
-    red[502 + rank] = n_local
+    # ---- one all-reduce: spectrum, totals, every rank's node count (slot 502 + r) and — for the sharded graph stage —
+    # every rank's peer blob (32 words at 502 + world + 32 r; the index over the owned nodes is queued before it, so the
+    # reduction is also the barrier "indices complete") ----
+    peer_graph = hasattr(eng, "graph_publish") and os.environ.get("SHK_SHARD_GRAPH", "1") != "0"
+    bw = _ffi.PEER_BLOB_BYTES // 8
+    red_np = np.zeros(502 + world + (world * bw if peer_graph else 0), np.int64)
+    red_np[:500] = eng.histogram().astype(np.int64)
+    red_np[500], red_np[501] = inst_local, eng.n_bases()
+    red_np[502 + rank] = n_local
+    if peer_graph:
+        red_np[502 + world + rank * bw: 502 + world + (rank + 1) * bw] = eng.graph_publish().view(np.int64)
+    red = torch.from_numpy(red_np).to(dev)
     _all_reduce(red, group)
     red_h = red.cpu().numpy()
     g_hist = red_h[:500].astype(np.uint64)
     g_inst, g_bases = int(red_h[500]), int(red_h[501])
-    counts = [int(c) for c in red_h[502:]]
+    counts = [int(c) for c in red_h[502:502 + world]]
     n_total = sum(counts)
     graph_mode = None
-    if hasattr(eng, "graph_publish") and os.environ.get("SHK_SHARD_GRAPH", "1") != "0":
-        graph_mode = _sharded_graph(eng, group, counts, g_hist, g_inst, g_bases, used_mc, mark)
+    if peer_graph:
+        blobs = np.ascontiguousarray(red_h[502 + world:]).view(np.uint8)
+        graph_mode = _sharded_graph(eng, group, blobs, counts, g_hist, g_inst, g_bases, used_mc, mark)
     if graph_mode is None:
         _replicated_graph(eng, group, counts, g_hist, g_inst, g_bases, used_mc, mark)
         graph_mode = "replicated"
