@@ -1411,14 +1411,14 @@ shk_status shk_asm_get_assembly(shk_asm *h, const char **json, size_t *len) {
 
 // Batch boundary of the streaming / file forms: counts the reads parsed so far.
 shk_status shk_internal_flush_batch(shk_asm *h, bool final_batch) {
-  if (h->hseq.empty() && !(final_batch && !h->any_batch_counted)) return SHK_OK;
-  // chunked mode: batches are packed and appended to the resident stream (0.375
-  // B/base of HBM); counting runs once over all of it at the end — the result is
-  // identical to bulk (S8) and no batch is ever re-read from the host.
-  SHK_TRY(load_reads_host(h, h->hseq.data(), h->hqual.data(), h->hseq.size(), h->any_batch_counted ? 1 : 0));
-  h->any_batch_counted = true;
+  // batches are packed and appended to the resident stream (0.375 B/base of HBM); counting runs once over all of it
+  // at the end — the result is identical to bulk (S8) and no batch is ever re-read from the host.
+  if (!h->hseq.empty() || (final_batch && !h->any_batch_counted)) {
+    SHK_TRY(load_reads_host(h, h->hseq.data(), h->hqual.data(), h->hseq.size(), h->any_batch_counted ? 1 : 0));
+    h->any_batch_counted = true;
+    h->hseq.clear(); h->hqual.clear(); h->batch_reads = 0;
+  }
   if (final_batch) SHK_TRY(count_impl(h, 1));
-  h->hseq.clear(); h->hqual.clear(); h->batch_reads = 0;
   return SHK_OK;
 }
 

@@ -90,19 +90,19 @@ k_build_edges_sharded_slow(const ShardTopo *__restrict__ t, const u64 *__restric
   typedef typename KeyOf<KW>::type K;
   const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
   const u32 nw = min(*n_work, work_cap);
-  if (i >= nw) return;
-  const u32 item = work[i], n = item >> 3, b = item & 7u;
-  K X = (K)node_lo[n];
-  if (KW == 2) X |= (K)((u128)node_hi[n] << 64);
+  if ((i & ~31u) >= nw) return;                           // whole warps leave together (the probes below run in lockstep)
+  const bool live = i < nw;
+  const u32 item = live ? work[i] : 0u, n = item >> 3, b = item & 7u;
+  K X = 0;
+  if (live) { X = (K)node_lo[n]; if (KW == 2) X |= (K)((u128)node_hi[n] << 64); }
   int s_in;
   const K Y = neighbour_key(X, t->k, (int)(b >> 2), b & 3u, s_in);
   const u32 yb = minimizer_hash_of(Y, t->k) & (t->P - 1);
-  if (yb == bucket_of[n]) return;                         // looked up there already: no such node
   const u32 r = owner_of_bucket(yb, t->P, t->world);
   const PeerView pv = t->peer[r];
-  if (!pv.n_nodes) return;
+  const bool look = live && yb != bucket_of[n] && pv.n_nodes != 0;   // (its own bucket was looked up already: no such node)
   NodeIndex ix{pv.slots, pv.off, pv.lo, pv.hi, t->P, t->k};
-  const u32 id = index_find_in<KW>(ix, Y, yb);
+  const u32 id = index_find_in_warp<KW>(ix, Y, yb, look);
   if (id == SHK_NONE) return;
   atomicOr(reinterpret_cast<u32 *>(node_edges + (n & ~3u)), (1u << b) << (8u * (n & 3u)));
   nbr[2 * n + (b >> 2)] = ((t->node_off[r] + id) << 1) | (u32)s_in;
