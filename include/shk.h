@@ -154,6 +154,7 @@ typedef struct shk_stats {
   uint32_t device_planned; /* 1: the last count ran the steady-state path (K1b groups planned on the device) */
   uint32_t host_qual_bits;     /* last load: 0 = the quality bytes crossed the link; else 1 + microseconds the calling
                                 * thread waited for the quality bits taken on the host (1 bit per position crossed) */
+  uint64_t n_spilled_records;  /* super-k-mer records that found their bucket's region full and went through the spill area */
 } shk_stats;
 
 /* Use `stream` (a cudaStream_t passed as void*) for all work of this handle;

@@ -36,7 +36,7 @@ class ShkStats(C.Structure):
         ("gpu_launches", C.c_uint64), ("used_min_count", C.c_int32), ("table_retries", C.c_int32),
         ("ms_pack", C.c_float), ("ms_count", C.c_float), ("ms_filter", C.c_float), ("ms_graph", C.c_float),
         ("ms_extract", C.c_float), ("ms_count_kernel", C.c_float), ("n_spilled", C.c_uint64), ("n_records", C.c_uint64),
-        ("device_planned", C.c_uint32), ("host_qual_bits", C.c_uint32),
+        ("device_planned", C.c_uint32), ("host_qual_bits", C.c_uint32), ("n_spilled_records", C.c_uint64),
     ]
 
 

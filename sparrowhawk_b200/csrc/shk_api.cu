@@ -186,6 +186,9 @@ static bool fast_ready_for(shk_asm *h, uint64_t n_positions);
 static shk_status fast_params(shk_asm *h, uint64_t n_positions);
 static uint32_t buckets_for(uint64_t positions, int kw);
 static uint64_t region_records_guess(uint64_t positions, uint32_t P, int kw, int k);
+static SpillArgs spill_args(shk_asm *h);
+static uint32_t spill_guess(uint64_t positions, int kw, int k);
+static shk_status ensure_regions(shk_asm *h, uint32_t P, uint32_t rcap);
 static shk_status fast_prologue(shk_asm *h);
 static double now_ms() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
 
@@ -265,8 +268,9 @@ static shk_status load_reads_overlapped(shk_asm *h, const uint8_t *seq, const ui
     const uint64_t wb = (uint64_t)i * slice / 32, we = std::min<uint64_t>(total, (uint64_t)(i + 1) * slice / 32);
     if (wb >= we || !cut) return;
     if (first_k1a) { cudaEventRecord(h->ev[8], h->stream); first_k1a = false; }
+    const SpillArgs sa = spill_args(h);
     h->st.gpu_launches += launch_partition(h->kw, b, m, total, h->p.k, h->P, h->rcap, h->skrecs.p, h->bfill.as<uint64_t>(),
-                                           d_counters(h), h->stream, wb, we);
+                                           d_counters(h), h->stream, wb, we, &sa);
   };
   // quality bits taken on the host by a few threads, slice by slice, in chunks handed out from a counter; the
   // calling thread queues slice i's copies as soon as that slice's chunks are done
@@ -478,8 +482,9 @@ static shk_status load_packed_impl(shk_asm *h, const uint64_t *bases, const uint
     const uint64_t wb = (uint64_t)i * slice, we = std::min<uint64_t>(total, (uint64_t)(i + 1) * slice);
     if (wb >= we) return;
     if (first) { cudaEventRecord(h->ev[8], h->stream); first = false; }
+    const SpillArgs sa = spill_args(h);
     h->st.gpu_launches += launch_partition(h->kw, b, m, total, h->p.k, h->P, h->rcap, h->skrecs.p, h->bfill.as<uint64_t>(),
-                                           d_counters(h), h->stream, wb, we);
+                                           d_counters(h), h->stream, wb, we, &sa);
   };
   int last = -1;
   for (int i = 0; i < S; ++i) {
@@ -536,13 +541,18 @@ static shk_status count_impl(shk_asm *h, int /*reset*/, uint32_t P_override = 0,
   for (;;) {
     if (rcap64 > 0x7FFFFFFFull) { set_error("record region too large"); return SHK_ERR_OOM; }
     uint32_t rcap = (uint32_t)rcap64;
-    SHK_TRY(h->skrecs.ensure((size_t)P * rcap * record_bytes(h->kw)));
-    SHK_TRY(h->bfill.ensure((size_t)P * 8));
+    // the spill area absorbs crowded buckets on the single-GPU cut; the sharded cut packs regions only and re-cuts instead
+    if (P_override) h->spill_cap = 0;
+    else h->spill_cap = std::max(h->spill_cap, spill_guess(positions, h->kw, k));
+    SHK_TRY(ensure_regions(h, P, rcap));
     SHK_TRY(h->hfill.ensure_host((size_t)P * 8));
     SHK_CUDA(cudaMemsetAsync(h->bfill.p, 0, (size_t)P * 8, h->stream));
     SHK_CUDA(cudaMemsetAsync(d_counters(h) + 1, 0, 8, h->stream));    // n_instances
+    SHK_CUDA(cudaMemsetAsync(d_flags(h) + 3, 0, 4, h->stream));       // spill cursor
     SHK_CUDA(cudaEventRecord(h->ev[8], h->stream));
-    h->st.gpu_launches += launch_partition(h->kw, b, m, h->nwords, k, P, rcap, h->skrecs.p, h->bfill.as<uint64_t>(), d_counters(h), h->stream);
+    const SpillArgs sa = spill_args(h);
+    h->st.gpu_launches += launch_partition(h->kw, b, m, h->nwords, k, P, rcap, h->skrecs.p, h->bfill.as<uint64_t>(), d_counters(h), h->stream,
+                                           0, ~0ull, &sa);
     SHK_CUDA(cudaGetLastError());
     SHK_CUDA(cudaEventRecord(h->ev[9], h->stream));
     const bool dev_plan = P_override && world && world <= 64 && (int)world <= shard_max_world();
@@ -570,9 +580,19 @@ static shk_status count_impl(shk_asm *h, int /*reset*/, uint32_t P_override = 0,
     }
     h->send_planned = dev_plan;
     h->P = P; h->rcap = rcap; h->n_records = nrec;
+    const uint32_t spilled = ((const uint32_t *)(h->h_pinned + 8 + SHK_HISTO_BINS))[3];
+    h->st.n_spilled_records = spilled;
+    h->spill_mode = false;
     if (mx <= rcap) break;
+    if (h->spill_cap && spilled <= h->spill_cap) {    // the overflow sits in the spill area, complete: sort it by bucket
+      h->st.gpu_launches += launch_spill_sort(h->kw, h->skrecs.p, h->bfill.as<uint64_t>(), P, rcap, sa, h->spill_cur.as<uint32_t>(),
+                                              h->seg_off.as<uint64_t>(), h->seg_cnt.as<uint32_t>(), h->stream);
+      h->spill_mode = true;
+      break;
+    }
     if (++h->st.table_retries > 3) { set_error("record regions overflow after retries"); return SHK_ERR_TABLE_FULL; }
-    rcap64 = (uint64_t)mx + mx / 4 + 64;              // exact need is known now
+    if (h->spill_cap) h->spill_cap = spilled + spilled / 4 + 1024;     // a larger spill area, the same regions
+    else rcap64 = (uint64_t)mx + mx / 4 + 64;                          // (sharded cut) exact need is known now
   }
   h->n_bases = h->h_pinned[3];
   h->counted_positions = h->n_positions;
@@ -584,10 +604,21 @@ static shk_status count_impl(shk_asm *h, int /*reset*/, uint32_t P_override = 0,
   // K1b input: one segment per local bucket region (the sharded path counts received records instead)
   if (!P_override) {
     const uint64_t *hf = (const uint64_t *)h->hfill.p;
-    h->seg_kmers.resize(P);
-    h->seg_recs.resize(P);
-    for (uint32_t i = 0; i < P; ++i) { h->seg_kmers[i] = (uint32_t)(hf[i] >> 32); h->seg_recs[i] = (uint32_t)hf[i]; }
-    h->seg_per_bucket = 1; h->src_instances = h->st.n_instances; h->shard_src = false;
+    if (h->spill_mode) {                               // bucket b = segments 2b (its region) and 2b + 1 (its sorted spill)
+      h->seg_kmers.assign((size_t)2 * P, 0); h->seg_recs.assign((size_t)2 * P, 0);
+      for (uint32_t i = 0; i < P; ++i) {
+        const uint32_t f = (uint32_t)hf[i];
+        h->seg_kmers[2 * i] = (uint32_t)(hf[i] >> 32);
+        h->seg_recs[2 * i] = std::min(f, h->rcap); h->seg_recs[2 * i + 1] = f > h->rcap ? f - h->rcap : 0;
+      }
+      h->seg_per_bucket = 2;
+    } else {
+      h->seg_kmers.resize(P);
+      h->seg_recs.resize(P);
+      for (uint32_t i = 0; i < P; ++i) { h->seg_kmers[i] = (uint32_t)(hf[i] >> 32); h->seg_recs[i] = (uint32_t)hf[i]; }
+      h->seg_per_bucket = 1;
+    }
+    h->src_instances = h->st.n_instances; h->shard_src = false;
   } else {
     h->seg_kmers.clear(); h->seg_recs.clear(); h->shard_src = false;
   }
@@ -617,7 +648,7 @@ static void plan_groups(shk_asm *h, uint32_t first_seg, double ratio, std::vecto
 static shk_status count_groups(shk_asm *h, const std::vector<uint32_t> &gs, uint32_t g_begin, uint32_t g_end,
                                int min_count, uint32_t node_cap) {
   SHK_CUDA(cudaMemsetAsync(d_flags(h) + 2, 0, 4, h->stream));       // next_group
-  const bool sh = h->shard_src;
+  const bool sh = h->shard_src, segs = h->shard_src || h->spill_mode;
   // de-dup scratch: one list per CTA, sized for the largest group of this launch
   uint32_t uq_cap = 0;
   if (h->kw == 1 && !h->no_dedup) {
@@ -633,7 +664,7 @@ static shk_status count_groups(shk_asm *h, const std::vector<uint32_t> &gs, uint
     h->uq_cap = std::max(h->uq_cap, uq_cap);
   }
   h->st.gpu_launches += launch_count_buckets(h->kw, sh ? h->recv_recs : h->skrecs.p, h->bfill.as<uint64_t>(), h->rcap,
-                                             sh ? h->seg_off.as<uint64_t>() : nullptr, sh ? h->seg_cnt.as<uint32_t>() : nullptr,
+                                             segs ? h->seg_off.as<uint64_t>() : nullptr, segs ? h->seg_cnt.as<uint32_t>() : nullptr,
                                              uq_cap ? h->uq_rec.p : nullptr, h->uq_cnt.as<uint32_t>(), uq_cap,
                                              h->groups.as<uint32_t>(), g_begin, g_end, nullptr,
                                              d_flags(h) + 2, h->p.k, min_count, h->ovf.p, h->ovf_cap, d_flags(h), d_flags(h) + 6,
@@ -672,11 +703,28 @@ static uint32_t buckets_for(uint64_t positions, int kw) {
   uint32_t P = next_pow2(std::max<uint64_t>(16, positions / target_bucket_instances(kw)));
   return std::min<uint32_t>(P, 1u << 20);
 }
+// spill area behind the regions (records that found their bucket's region full): an eighth of the records expected
+static uint32_t spill_guess(uint64_t positions, int kw, int k) {
+  const int mlen = k < 11 ? k : 11, w = k - mlen + 1;
+  const double avg_run = std::min<double>(records_max_run(kw, k), std::max(1.0, (w + 1) / 2.0 * 0.6));
+  return (uint32_t)std::min<double>(1u << 30, std::max(65536.0, (double)positions / avg_run / 8.0));
+}
+static SpillArgs spill_args(shk_asm *h) { return SpillArgs{h->spill_cap, d_flags(h) + 3, h->spill_bkt.as<uint32_t>()}; }
+static shk_status ensure_regions(shk_asm *h, uint32_t P, uint32_t rcap) {
+  SHK_TRY(h->skrecs.ensure(((size_t)P * rcap + 2 * (size_t)h->spill_cap) * record_bytes(h->kw)));
+  SHK_TRY(h->bfill.ensure((size_t)P * 8));
+  if (h->spill_cap) {
+    SHK_TRY(h->spill_bkt.ensure((size_t)h->spill_cap * 4)); SHK_TRY(h->spill_cur.ensure((size_t)P * 4));
+    SHK_TRY(h->seg_off.ensure((size_t)2 * P * 8 + 8)); SHK_TRY(h->seg_cnt.ensure((size_t)2 * P * 4 + 4));
+  }
+  return SHK_OK;
+}
 static uint64_t region_records_guess(uint64_t positions, uint32_t P, int kw, int k) {
   // records per bucket: a run holds ~ (w+1)/2 k-mers for a window of w = k-m+1 m-mers
   const int mlen = k < 11 ? k : 11, w = k - mlen + 1;
   const double avg_run = std::min<double>(records_max_run(kw, k), std::max(1.0, (w + 1) / 2.0 * 0.6));
-  // x 6: at high coverage a bucket holds a handful of genome loci times the coverage, so fills scatter widely
+  // x 6: at high coverage a bucket holds a handful of genome loci times the coverage, so fills scatter widely (what
+  // still does not fit goes to the spill area)
   return (uint64_t)(6.0 * (double)positions / avg_run / (double)P) + 64;
 }
 
@@ -694,8 +742,8 @@ static shk_status fast_params(shk_asm *h, uint64_t n_positions) {
     h->P = P; h->rcap = (uint32_t)rcap64;
     h->fast_positions = 0;                        // not verified for this size yet
   }
-  SHK_TRY(h->skrecs.ensure((size_t)h->P * h->rcap * record_bytes(h->kw)));
-  SHK_TRY(h->bfill.ensure((size_t)h->P * 8));
+  h->spill_cap = std::max(h->spill_cap, spill_guess(positions, h->kw, h->p.k));
+  SHK_TRY(ensure_regions(h, h->P, h->rcap));
   if (!h->ovf_cap) {
     h->ovf_cap = std::max<uint64_t>(1u << 16, positions / 512);
     SHK_TRY(h->ovf.ensure(h->ovf_cap * slot_bytes(h->kw)));
@@ -745,32 +793,55 @@ static shk_status count_filter_fast(shk_asm *h, int min_count, bool &fell_back) 
   if (!h->partition_done) {                           // (the overlapped load has already cut the reads into records)
     SHK_TRY(fast_prologue(h));
     SHK_CUDA(cudaEventRecord(h->ev[8], h->stream));
-    h->st.gpu_launches += launch_partition(h->kw, b, m, h->nwords, h->p.k, P, rcap, h->skrecs.p, h->bfill.as<uint64_t>(), d_counters(h), h->stream);
+    const SpillArgs sa = spill_args(h);
+    h->st.gpu_launches += launch_partition(h->kw, b, m, h->nwords, h->p.k, P, rcap, h->skrecs.p, h->bfill.as<uint64_t>(), d_counters(h), h->stream,
+                                           0, ~0ull, &sa);
     SHK_CUDA(cudaEventRecord(h->ev[9], h->stream));
   }
   h->partition_done = false;                          // K1b consumes it; a fallback starts over
+  // records that found their region full sit in the spill area: sort them by bucket (no-ops when nothing spilled)
+  const SpillArgs sa = spill_args(h);
+  h->st.gpu_launches += launch_spill_sort(h->kw, h->skrecs.p, h->bfill.as<uint64_t>(), P, rcap, sa, h->spill_cur.as<uint32_t>(),
+                                          h->seg_off.as<uint64_t>(), h->seg_cnt.as<uint32_t>(), h->stream);
   SHK_CUDA(cudaEventRecord(h->ev[3], h->stream));
   SHK_CUDA(cudaEventRecord(h->ev[4], h->stream));
   h->st.gpu_launches += launch_table_fill(h->ovf.p, h->ovf_cap, h->kw, h->stream);
   const bool cold = !(h->ratio_est > 0);
   SelfPlanArgs spa{P, cold ? 1.0 : h->ratio_est, count_table_slots(h->kw) * table_load(), d_flags(h) + 4, d_counters(h) + 6, 1, cold};
   SHK_CUDA(cudaEventRecord(h->ev[10], h->stream));
+  // Two launches back to back, exactly one of which does the work — the device knows whether K1a spilled, the host
+  // does not (and does not wait to find out): the plain one reads a bucket from its region; the other one reads it as
+  // two segments, region part + sorted spill part.
   h->st.gpu_launches += launch_count_buckets(h->kw, h->skrecs.p, h->bfill.as<uint64_t>(), rcap, nullptr, nullptr,
                                              dedup ? h->uq_rec.p : nullptr, h->uq_cnt.as<uint32_t>(), uq_fast,
                                              nullptr, 0, 0, &spa, d_flags(h) + 2, h->p.k, min_count,
                                              h->ovf.p, h->ovf_cap, d_flags(h), d_flags(h) + 6, d_histo(h),
                                              h->node_lo.as<uint64_t>(), h->node_hi.as<uint64_t>(), h->node_count.as<uint16_t>(),
-                                             h->node_raw.as<uint8_t>(), node_cap, d_flags(h) + 1, d_counters(h), h->stream);
+                                             h->node_raw.as<uint8_t>(), node_cap, d_flags(h) + 1, d_counters(h), h->stream,
+                                             h->spill_cap ? d_flags(h) + 3 : nullptr, 0);
+  if (h->spill_cap) {
+    SelfPlanArgs spa2 = spa; spa2.seg_per_bucket = 2;
+    h->st.gpu_launches += launch_count_buckets(h->kw, h->skrecs.p, h->bfill.as<uint64_t>(), rcap, h->seg_off.as<uint64_t>(), h->seg_cnt.as<uint32_t>(),
+                                               dedup ? h->uq_rec.p : nullptr, h->uq_cnt.as<uint32_t>(), uq_fast,
+                                               nullptr, 0, 0, &spa2, d_flags(h) + 2, h->p.k, min_count,
+                                               h->ovf.p, h->ovf_cap, d_flags(h), d_flags(h) + 6, d_histo(h),
+                                               h->node_lo.as<uint64_t>(), h->node_hi.as<uint64_t>(), h->node_count.as<uint16_t>(),
+                                               h->node_raw.as<uint8_t>(), node_cap, d_flags(h) + 1, d_counters(h), h->stream,
+                                               d_flags(h) + 3, 1);
+  }
   SHK_CUDA(cudaGetLastError());
   SHK_CUDA(cudaEventRecord(h->ev[11], h->stream));
   SHK_TRY(read_scalars(h));
   const uint32_t *fl = (const uint32_t *)(h->h_pinned + 8 + SHK_HISTO_BINS);
-  if (fl[0] || fl[6] || fl[4] > rcap || (dedup && fl[5] > uq_fast)) {
+  const bool region_lost = fl[4] > rcap && (!h->spill_cap || fl[3] > h->spill_cap);   // records dropped: nowhere to spill them
+  if (fl[3] > h->spill_cap) h->spill_cap = fl[3] + fl[3] / 4 + 1024;                   // (what the next cut needs)
+  h->st.n_spilled_records = fl[3];
+  if (fl[0] || fl[6] || region_lost || (dedup && fl[5] > uq_fast)) {
     if (h->p.verbose > 1 || getenv("SHK_DEBUG"))
       fprintf(stderr, "[shk] steady-state path fell back: overflow table %u, list flag %u, largest fill %u / %u, list need %u / %u\n",
               fl[0], fl[6], fl[4], rcap, fl[5], uq_fast);
     if (dedup) h->uq_need_hint = std::max(h->uq_need_hint, fl[5]);
-    h->uq_retry = !fl[0] && fl[4] <= rcap;
+    h->uq_retry = !fl[0] && !region_lost;
     // a full overflow table means the device planner's groups (which may exceed the budget by one bucket) do not
     // suit this input — few, uneven buckets per group: stay on the host-planned path for read sets of this size
     if (fl[0]) h->fast_banned_positions = h->n_positions;
@@ -785,7 +856,7 @@ static shk_status count_filter_fast(shk_asm *h, int min_count, bool &fell_back) 
   h->st.table_slots = P; h->st.table_retries = 0; h->st.n_records = h->n_records;
   h->src_instances = h->st.n_instances; h->shard_src = false; h->seg_per_bucket = 1;
   h->seg_kmers.clear(); h->seg_recs.clear();               // the host-side bucket description is not fetched on this path
-  h->counted = true; h->counted_fast = true; h->st.device_planned = 1; h->shard_graph = false;
+  h->counted = true; h->counted_fast = true; h->st.device_planned = 1; h->shard_graph = false; h->spill_mode = false;
   h->fast_positions = h->n_positions;
   h->st.n_spilled = h->h_pinned[4];
   h->spill_hint = h->st.n_spilled;
@@ -899,11 +970,11 @@ static shk_status filter_impl(shk_asm *h, int min_count, bool histogram_only = f
 static shk_status index_impl(shk_asm *h) {
   const uint32_t nn = (uint32_t)h->st.n_nodes;
   const uint32_t P = h->P ? h->P : 1;                  // the buckets the nodes were counted in (any power of two is valid)
-  SHK_TRY(h->slots.ensure(((size_t)2 * nn + 2) * 8));
+  SHK_TRY(h->slots.ensure(index_slots(nn) * 8));
   SHK_TRY(h->idx_off.ensure(((size_t)P + 2) * 4));
   SHK_TRY(h->idx_tmp.ensure(((size_t)nn + index_tmp_entries(P) + 2) * 4));
   h->index_P = P;
-  SHK_CUDA(cudaMemsetAsync(h->slots.p, 0xFF, ((size_t)2 * nn + 2) * 8, h->stream));
+  SHK_CUDA(cudaMemsetAsync(h->slots.p, 0xFF, index_slots(nn) * 8, h->stream));
   SHK_CUDA(cudaMemsetAsync(h->idx_off.p, 0, ((size_t)P + 2) * 4, h->stream));
   h->st.gpu_launches += launch_index_nodes(h->kw, h->slots.as<uint64_t>(), h->idx_off.as<uint32_t>(), h->idx_tmp.as<uint32_t>(),
                                            h->idx_tmp.as<uint32_t>() + nn, P, h->p.k, h->node_lo.as<uint64_t>(),

@@ -243,7 +243,10 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
                 uint4 *__restrict__ uq_rec, u32 *__restrict__ uq_cnt, u32 uq_cap /* distinct-record list, per CTA */,
                 const u32 *__restrict__ group_start /* null: the CTAs cut their own groups (SelfPlan) */, u32 g_begin, u32 g_end,
                 SelfPlan sp, u32 *__restrict__ next_group, int k, int min_count, Table<KW> ovf, u32 *__restrict__ ovf_flag,
-                u32 *__restrict__ uq_flag /* set when a de-dup list is too small */, CountOut out) {
+                u32 *__restrict__ uq_flag /* set when a de-dup list is too small */, CountOut out,
+                const u32 *__restrict__ gate, u32 gate_want /* gate != null: run only if (*gate != 0) == gate_want — the plain and
+                the spill-aware launch are queued back to back and the device picks the one that fits what K1a did */) {
+  if (gate && ((*gate != 0u) ? 1u : 0u) != gate_want) return;
   typedef typename KeyOf<KW>::type K;
   typedef typename std::conditional<KW == 1, u64, U128Pair>::type SK;
   constexpr int NS = CbCfg<KW>::NS, RECW = CbCfg<KW>::RECW, THREADS = CbCfg<KW>::THREADS, WARPS = CbCfg<KW>::WARPS;

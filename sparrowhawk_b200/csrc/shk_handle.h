@@ -117,6 +117,9 @@ struct shk_asm {
   bool send_planned = false;                   // pack_off holds rank-local offsets (device-side send plan)
   shk::PinBuf hfill, pin_stage /* D2H staging of the unitig sequences */;
   uint32_t P = 0, rcap = 0;
+  uint32_t spill_cap = 0;              // records the spill area behind the regions holds (0: none)
+  bool spill_mode = false;             // host-planned count: buckets are two segments (region, sorted spill)
+  shk::DevBuf spill_bkt, spill_cur;
   uint64_t n_records = 0, ovf_cap = 0, spill_hint = 0 /* instances that spilled on the last run */;
   double ratio_est = 0;         // distinct / instances, measured by a pilot or the previous run
   // ---- K1b input description: record segments (one per local bucket, or one per (owned bucket, source rank)) ----

@@ -1,7 +1,7 @@
 // shk_index.cuh — the node index of the graph stage: canonical k-mer -> node id.
 //
 // Layout: one REGION of slots per fine minimizer bucket (the buckets of K1a), sized from the number of nodes
-// the bucket really holds (two slots per node), regions back to back in bucket order.  A key hashes to a slot
+// the bucket really holds (four slots per node), regions back to back in bucket order.  A key hashes to a slot
 // inside the region of ITS bucket and probes linearly, wrapping inside the region, so a crowded bucket never
 // spills into its neighbours and no probe sequence is longer than its own region.  A slot is a u64: node id in
 // the low half, 32 fingerprint bits of the key's hash in the high half, all ones = empty; a matching fingerprint
@@ -27,6 +27,10 @@ struct NodeIndex {
   int k;
 };
 #define SHK_INDEX_EMPTY 0xFFFFFFFFFFFFFFFFull
+// slots per node: a quarter-full region keeps linear probing short — what costs in K3 is not the average probe count but
+// its tail (a warp waits for its slowest lane; measured at two slots per node: 5 probe rounds per lookup round, 3-5 lanes
+// active in them), and every lookup of an ABSENT neighbour (an error k-mer below the filter) runs to the first empty slot
+#define SHK_INDEX_SLOTS_PER_NODE 4u
 
 template <int KW>
 __device__ __forceinline__ bool index_key_is(const NodeIndex &ix, u32 id, typename KeyOf<KW>::type key) {
@@ -82,7 +86,7 @@ __device__ __forceinline__ u32 index_find_in_warp(const NodeIndex &ix, typename 
   return id;
 }
 
-// build, pass 1: two slots per node into the bucket counters; the bucket is kept for pass 2
+// build, pass 1: SHK_INDEX_SLOTS_PER_NODE slots per node into the bucket counters; the bucket is kept for pass 2
 template <int KW>
 __global__ void __launch_bounds__(256)
 k_index_count(const u64 *__restrict__ node_lo, const u64 *__restrict__ node_hi, u32 n_nodes, u32 P, int k,
@@ -94,7 +98,7 @@ k_index_count(const u64 *__restrict__ node_lo, const u64 *__restrict__ node_hi, 
   if (KW == 2) key |= (K)((u128)node_hi[n] << 64);
   const u32 b = minimizer_hash_of(key, k) & (P - 1);
   bucket_of[n] = b;
-  atomicAdd(off + b, 2u);
+  atomicAdd(off + b, SHK_INDEX_SLOTS_PER_NODE);
 }
 // pass 2 (after the exclusive scan of off): node n claims the first empty slot of its probe sequence
 template <int KW>
@@ -106,11 +110,11 @@ k_index_insert(u64 *__restrict__ slots, const u32 *__restrict__ off, const u32 *
   if (n >= n_nodes) return;
   K key = (K)node_lo[n];
   if (KW == 2) key |= (K)((u128)node_hi[n] << 64);
-  const u32 b = bucket_of[n], o = off[b], sz = off[b + 1] - o;      // sz >= 2: this node was counted
+  const u32 b = bucket_of[n], o = off[b], sz = off[b + 1] - o;      // sz >= 4: this node was counted
   const u64 h = hash_key(key);
   const u64 mine = (h & 0xFFFFFFFF00000000ull) | n;
   u32 j = (u32)h % sz;
-  for (u32 probe = 0; probe < sz; ++probe) {                          // half of the region is free: always ends
+  for (u32 probe = 0; probe < sz; ++probe) {                          // most of the region is free: always ends
     if (atomicCAS(slots + o + j, SHK_INDEX_EMPTY, mine) == SHK_INDEX_EMPTY) return;
     if (++j == sz) j = 0;
   }

@@ -507,15 +507,72 @@ int count_ctas(int kw) { return sm_count() * (kw == 2 ? CbCfg<2>::PER_SM : CbCfg
 
 int launch_partition(int kw, const uint64_t *bases, const uint32_t *mask, uint64_t nwords, int k, uint32_t P,
                      uint32_t rcap, void *recs, uint64_t *bstat, uint64_t *counters, cudaStream_t st,
-                     uint64_t word_begin, uint64_t word_end) {
+                     uint64_t word_begin, uint64_t word_end, const SpillArgs *sp) {
   if (word_end > nwords) word_end = nwords;
   if (word_begin >= word_end) return 0;
   unsigned g = blocks_for(word_end - word_begin, SHK_PT_WORDS);
+  const u32 scap = sp ? sp->cap : 0u; u32 *scur = sp ? sp->cursor : nullptr, *sbkt = sp ? sp->bucket : nullptr;
   if (kw == 1)
-    k_minimizer_partition<1><<<g, SHK_PT_THREADS, 0, st>>>((const u64 *)bases, mask, nwords, word_begin, k, P, rcap, (uint4 *)recs, (u64 *)bstat, (u64 *)counters);
+    k_minimizer_partition<1><<<g, SHK_PT_THREADS, 0, st>>>((const u64 *)bases, mask, nwords, word_begin, k, P, rcap, (uint4 *)recs, (u64 *)bstat, (u64 *)counters, scap, scur, sbkt);
   else
-    k_minimizer_partition<2><<<g, SHK_PT_THREADS, 0, st>>>((const u64 *)bases, mask, nwords, word_begin, k, P, rcap, (Rec32 *)recs, (u64 *)bstat, (u64 *)counters);
+    k_minimizer_partition<2><<<g, SHK_PT_THREADS, 0, st>>>((const u64 *)bases, mask, nwords, word_begin, k, P, rcap, (Rec32 *)recs, (u64 *)bstat, (u64 *)counters, scap, scur, sbkt);
   return 1;
+}
+
+// ---- spill area -> per-bucket spill segments (only when K1a spilled: both kernels leave at once otherwise) ----------
+// plan: one CTA walks the P fills; bucket b's excess over its region gets the range [off, off + excess) of the SORTED
+// spill area, and the two record segments K1b reads for it are written: (region, min(fill, rcap)) and (sorted spill,
+// excess).  scatter: every spilled record moves to its bucket's range.
+__global__ void __launch_bounds__(1024)
+k_spill_plan(const u64 *__restrict__ fill, u32 P, u32 rcap, u32 spill_cap, const u32 *__restrict__ cursor,
+             u32 *__restrict__ cur /* [P] running write position per bucket */, u64 *__restrict__ seg_off, u32 *__restrict__ seg_cnt) {
+  if (*cursor == 0) return;
+  __shared__ u32 wsum[32];
+  __shared__ u32 carry;
+  const u32 lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (threadIdx.x == 0) carry = 0;
+  __syncthreads();
+  const u64 sorted_base = (u64)P * rcap + spill_cap;
+  for (u32 j0 = 0; j0 < P; j0 += 1024) {
+    const u32 j = j0 + threadIdx.x;
+    const u32 f = j < P ? (u32)fill[j] : 0u, ex = f > rcap ? f - rcap : 0u;
+    u32 inc = ex;
+    for (int o = 1; o < 32; o <<= 1) { u32 v = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= (u32)o) inc += v; }
+    if (lane == 31) wsum[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+      u32 w = wsum[lane];
+      for (int o = 1; o < 32; o <<= 1) { u32 v = __shfl_up_sync(0xffffffffu, w, o); if (lane >= (u32)o) w += v; }
+      wsum[lane] = w;
+    }
+    __syncthreads();
+    const u32 before = carry + (warp ? wsum[warp - 1] : 0u) + (inc - ex);
+    if (j < P) {
+      cur[j] = before;
+      seg_off[2 * j] = (u64)j * rcap; seg_cnt[2 * j] = min(f, rcap);
+      seg_off[2 * j + 1] = sorted_base + before; seg_cnt[2 * j + 1] = ex;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) carry += wsum[31];
+    __syncthreads();
+  }
+}
+__global__ void __launch_bounds__(256)
+k_spill_scatter(uint4 *__restrict__ recs, int rw, u32 P, u32 rcap, u32 spill_cap, const u32 *__restrict__ cursor,
+                const u32 *__restrict__ bkt, u32 *__restrict__ cur) {
+  const u32 n = min(*cursor, spill_cap);
+  const u64 base = (u64)P * rcap, sorted_base = base + spill_cap;
+  for (u32 i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const u32 pos = atomicAdd(cur + bkt[i], 1u);
+    for (int j = 0; j < rw; ++j) recs[(sorted_base + pos) * rw + j] = recs[(base + i) * rw + j];
+  }
+}
+int launch_spill_sort(int kw, void *recs, const uint64_t *bstat, uint32_t P, uint32_t rcap, const SpillArgs &sp, uint32_t *cur,
+                      uint64_t *seg_off, uint32_t *seg_cnt, cudaStream_t st) {
+  if (!sp.cap) return 0;
+  k_spill_plan<<<1, 1024, 0, st>>>((const u64 *)bstat, P, rcap, sp.cap, sp.cursor, cur, (u64 *)seg_off, seg_cnt);
+  k_spill_scatter<<<grid_persistent(sp.cap, 256, 4), 256, 0, st>>>((uint4 *)recs, kw == 1 ? 1 : 2, P, rcap, sp.cap, sp.cursor, sp.bucket, cur);
+  return 2;
 }
 int partition_tile_words() { return SHK_PT_WORDS; }
 
@@ -524,7 +581,7 @@ int launch_count_buckets(int kw, const void *recs, const uint64_t *bstat, uint32
                          uint32_t g_begin, uint32_t g_end, const SelfPlanArgs *self_plan, uint32_t *next_group, int k, int min_count, void *ovf_slots,
                          uint64_t ovf_cap, uint32_t *ovf_flag, uint32_t *uq_flag, uint64_t *histo, uint64_t *node_lo, uint64_t *node_hi,
                          uint16_t *node_count, uint8_t *node_raw, uint32_t node_cap, uint32_t *n_nodes,
-                         uint64_t *counters, cudaStream_t st) {
+                         uint64_t *counters, cudaStream_t st, const uint32_t *gate, uint32_t gate_want) {
   if (group_start && g_end <= g_begin) return 0;
   SelfPlan sp{0, 1, 0, 1, nullptr, nullptr, 1, 0};
   if (!group_start) {
@@ -553,13 +610,13 @@ int launch_count_buckets(int kw, const void *recs, const uint64_t *bstat, uint32
   // record-level de-duplication needs the per-CTA list of distinct records (k <= 31 only for now)
   if (kw == 1 && uq_rec && uq_cap)
     k_count_buckets<1, true><<<grid, CbCfg<1>::THREADS, cb_smem_bytes<1>(), st>>>((const uint4 *)recs, (const u64 *)bstat, rcap, (const u64 *)seg_off, seg_cnt,
-        (uint4 *)uq_rec, uq_cnt, uq_cap, group_start, g_begin, g_end, sp, next_group, k, min_count, Table<1>{(Slot1 *)ovf_slots, ovf_cap, mp}, ovf_flag, uq_flag, out);
+        (uint4 *)uq_rec, uq_cnt, uq_cap, group_start, g_begin, g_end, sp, next_group, k, min_count, Table<1>{(Slot1 *)ovf_slots, ovf_cap, mp}, ovf_flag, uq_flag, out, gate, gate_want);
   else if (kw == 1)
     k_count_buckets<1, false><<<grid, CbCfg<1>::THREADS, cb_smem_bytes<1>(), st>>>((const uint4 *)recs, (const u64 *)bstat, rcap, (const u64 *)seg_off, seg_cnt,
-        nullptr, nullptr, 0, group_start, g_begin, g_end, sp, next_group, k, min_count, Table<1>{(Slot1 *)ovf_slots, ovf_cap, mp}, ovf_flag, uq_flag, out);
+        nullptr, nullptr, 0, group_start, g_begin, g_end, sp, next_group, k, min_count, Table<1>{(Slot1 *)ovf_slots, ovf_cap, mp}, ovf_flag, uq_flag, out, gate, gate_want);
   else
     k_count_buckets<2, false><<<grid, CbCfg<2>::THREADS, cb_smem_bytes<2>(), st>>>((const Rec32 *)recs, (const u64 *)bstat, rcap, (const u64 *)seg_off, seg_cnt,
-        nullptr, nullptr, 0, group_start, g_begin, g_end, sp, next_group, k, min_count, Table<2>{(Slot2 *)ovf_slots, ovf_cap, mp}, ovf_flag, uq_flag, out);
+        nullptr, nullptr, 0, group_start, g_begin, g_end, sp, next_group, k, min_count, Table<2>{(Slot2 *)ovf_slots, ovf_cap, mp}, ovf_flag, uq_flag, out, gate, gate_want);
   return 1;
 }
 
@@ -697,7 +754,8 @@ int launch_shard_segments(const uint64_t *d_fill, uint32_t nb, uint32_t world, c
 }
 
 size_t index_tmp_entries(uint32_t P) { return scan_tmp_entries(P); }
-// slots: u64[2 * n_nodes] pre-filled with 0xFF; off: u32[P + 1] zeroed; bucket_of: u32[n_nodes]; tmp: u32[index_tmp_entries(P)]
+size_t index_slots(uint32_t n_nodes) { return (size_t)SHK_INDEX_SLOTS_PER_NODE * n_nodes + 2; }
+// slots: u64[index_slots(n_nodes)] pre-filled with 0xFF; off: u32[P + 1] zeroed; bucket_of: u32[n_nodes]; tmp: u32[index_tmp_entries(P)]
 int launch_index_nodes(int kw, uint64_t *slots, uint32_t *off, uint32_t *bucket_of, uint32_t *tmp, uint32_t P, int k,
                        const uint64_t *node_lo, const uint64_t *node_hi, uint32_t n_nodes, cudaStream_t st) {
   if (!n_nodes) return 0;

@@ -63,10 +63,20 @@ int records_max_run(int kw, int k);
 int count_table_slots(int kw);
 int count_max_group();
 int count_ctas(int kw = 1);   // CTAs of one K1b launch (k <= 31: also sizes the per-CTA de-dup lists)
+// Spill area of the record regions: `recs` holds P * rcap region records, then cap spill records as K1a wrote them
+// (bucket[i] = their bucket, *cursor = how many — more than cap means some were dropped), then cap more for the same
+// records sorted by bucket (launch_spill_sort).  cap == 0 / null: records beyond a full region are dropped and counted.
+struct SpillArgs { uint32_t cap; uint32_t *cursor; uint32_t *bucket; };
 int launch_partition(int kw, const uint64_t *bases, const uint32_t *mask, uint64_t nwords, int k, uint32_t P,
                      uint32_t rcap, void *recs, uint64_t *bstat /* [P]: records | k-mers << 32 */, uint64_t *counters, cudaStream_t st,
                      uint64_t word_begin = 0, uint64_t word_end = ~0ull /* a slice of the stream: begin must be a multiple of
-                     partition_tile_words(), and the words behind word_end (the halo) must already be packed */);
+                     partition_tile_words(), and the words behind word_end (the halo) must already be packed */,
+                     const SpillArgs *spill = nullptr);
+// after K1a, when something spilled (no-ops otherwise): spill records sorted by bucket, and the two record segments of
+// every bucket (region part, spill part) written to seg_off / seg_cnt [2 P] for a K1b launch with seg_per_bucket = 2.
+// cur: u32[P] scratch.
+int launch_spill_sort(int kw, void *recs, const uint64_t *bstat, uint32_t P, uint32_t rcap, const SpillArgs &sp, uint32_t *cur,
+                      uint64_t *seg_off, uint32_t *seg_cnt, cudaStream_t st);
 int partition_tile_words();
 // group_start == null: the CTAs cut their own groups (steady-state runs).  stats (device, zeroed by the caller):
 // [0] largest bucket fill, [1] most distinct items in a group; *nrec (device, zeroed): records counted.
@@ -81,7 +91,8 @@ int launch_count_buckets(int kw, const void *recs, const uint64_t *bstat, uint32
                          uint32_t *next_group, int k, int min_count, void *ovf_slots,
                          uint64_t ovf_cap, uint32_t *ovf_flag, uint32_t *uq_flag, uint64_t *histo, uint64_t *node_lo, uint64_t *node_hi,
                          uint16_t *node_count, uint8_t *node_raw, uint32_t node_cap, uint32_t *n_nodes,
-                         uint64_t *counters, cudaStream_t st);
+                         uint64_t *counters, cudaStream_t st,
+                         const uint32_t *gate = nullptr, uint32_t gate_want = 0 /* run only if (*gate != 0) == gate_want */);
 // world / rank_base (host, nullable): dst_off is local to the owner rank and rank r's records start at rank_base[r]
 int launch_pack_records(int kw, const void *recs, const uint64_t *bstat, uint32_t rcap, const uint64_t *dst_off, uint32_t P,
                         void *out, cudaStream_t st, uint32_t world = 0, const uint64_t *rank_base = nullptr);
@@ -93,9 +104,10 @@ int launch_shard_send_plan(const uint64_t *d_fill, uint32_t rcap, uint32_t world
 int shard_max_world();
 int launch_shard_segments(const uint64_t *d_fill, uint32_t nb, uint32_t world, const uint64_t *src_base /* host, [world] */,
                           uint64_t *seg_off, uint32_t *seg_cnt, uint64_t *bucket_tot, cudaStream_t st);
-// node index build (shk_index.cuh): slots u64[2 * n_nodes] pre-filled with 0xFF; off u32[P + 1] zeroed;
+// node index build (shk_index.cuh): slots u64[index_slots(n_nodes)] pre-filled with 0xFF; off u32[P + 1] zeroed;
 // bucket_of u32[n_nodes]; tmp u32[index_tmp_entries(P)].  No overflow is possible: regions are sized from the counts.
 size_t index_tmp_entries(uint32_t P);
+size_t index_slots(uint32_t n_nodes);
 int launch_index_nodes(int kw, uint64_t *slots, uint32_t *off, uint32_t *bucket_of, uint32_t *tmp, uint32_t P, int k,
                        const uint64_t *node_lo, const uint64_t *node_hi, uint32_t n_nodes, cudaStream_t st);
 

@@ -152,7 +152,8 @@ __global__ void __launch_bounds__(SHK_PT_THREADS, 3)
 k_minimizer_partition(const u64 *__restrict__ bases, const u32 *__restrict__ mask, u64 nwords /* of the whole stream */,
                       u64 word_begin /* first word of this launch (a multiple of SHK_PT_WORDS) */, int k, u32 P,
                       u32 rcap, typename RecOf<KW>::type *__restrict__ recs, u64 *__restrict__ bstat /* [P] records | kmers << 32 */,
-                      u64 *__restrict__ counters /* [1] n_instances */) {
+                      u64 *__restrict__ counters /* [1] n_instances */,
+                      u32 spill_cap, u32 *__restrict__ spill_cursor, u32 *__restrict__ spill_bkt /* spill area: see below */) {
   __shared__ u64 sb[SHK_PT_TILE];
   __shared__ u32 sm[SHK_PT_TILE];
   __shared__ u32 hs[SHK_PT_HROWS * SHK_PT_ROW];
@@ -315,9 +316,19 @@ k_minimizer_partition(const u64 *__restrict__ bases, const u32 *__restrict__ mas
       for (u32 c = 0; c < len; c += (u32)nmax, ++idx) {
         const int s = s0 + (int)c;
         const int n = (int)min((u32)nmax, len - c);
-        if (idx >= rcap) continue;                      // region overflow: the host re-runs with the exact size
+        u64 at = (u64)b * rcap + idx;
+        if (idx >= rcap) {
+          // The bucket's region is full (a hot minimizer: duplicated reads, low complexity; or simply a crowded
+          // bucket at high coverage).  The record goes to the SPILL AREA behind the regions, tagged with its bucket;
+          // k_spill_plan / k_spill_scatter sort that area by bucket and K1b reads a bucket as region + spill
+          // segment.  So a skewed input costs a bounded amount of memory instead of P times its largest bucket.
+          const u32 si = spill_cap ? atomicAdd(spill_cursor, 1u) : 0u;
+          if (si >= spill_cap) continue;                // (no room: the count tells the host, which runs again larger)
+          spill_bkt[si] = b;
+          at = (u64)P * rcap + si;
+        }
         const u32 hasl = mask_bit(sm, s - 1), hasr = mask_bit(sm, s + n - 1 + k);
-        uint4 *dst = reinterpret_cast<uint4 *>(recs + ((u64)b * rcap + idx));
+        uint4 *dst = reinterpret_cast<uint4 *>(recs + at);
         if (KW == 1) {
           u64 hi = stream_bits64(sb, s - 1), lo = stream_bits64(sb, s - 1 + 32);
           lo = (lo & ~0x7Full) | (u64)n | ((u64)hasl << 5) | ((u64)hasr << 6);

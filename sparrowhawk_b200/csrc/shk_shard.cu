@@ -69,12 +69,12 @@ shk_status shk_shard_graph_publish(shk_asm *h, void *blob_out) {
   if (h->shard_world > SHK_MAX_WORLD) { set_error("world %u > %d", h->shard_world, SHK_MAX_WORLD); return SHK_ERR_BAD_ARG; }
   const uint32_t n = (uint32_t)h->shard_nodes_local;
   h->st.n_nodes = n;                                   // the exports of this handle cover ITS nodes
-  // arena (plain cudaMalloc: it is exported): [slots u64 x (2n+2)] [off u32 x (P+2)] [edges u8 x n] [chain_of_head u32 x 2n]
+  // arena (plain cudaMalloc: it is exported): [slots u64 x index_slots(n)] [off u32 x (P+2)] [edges u8 x n] [chain_of_head u32 x 2n]
   // [key lo u64 x n] [key hi u64 x n] — the keys are a copy of this rank's node arrays, so that one handle covers all
   if (n >= (1u << 29)) { set_error("too many nodes on one rank (%u)", n); return SHK_ERR_BAD_ARG; }   // (K3' packs node << 3 | bit)
   const uint32_t P = h->P;
   size_t o = 0;
-  h->arena_off_slots = o; o = align_up(o + ((size_t)2 * n + 2) * 8, 256);
+  h->arena_off_slots = o; o = align_up(o + index_slots(n) * 8, 256);
   h->arena_off_off = o;   o = align_up(o + ((size_t)P + 2) * 4, 256);
   h->arena_off_edges = o; o = align_up(o + (size_t)n + 16, 256);
   h->arena_off_coh = o;   o = align_up(o + ((size_t)2 * n + 2) * 4, 256);
@@ -88,7 +88,7 @@ shk_status shk_shard_graph_publish(shk_asm *h, void *blob_out) {
     SHK_CUDA(cudaMemcpyAsync(A + h->arena_off_lo, h->node_lo.p, (size_t)n * 8, cudaMemcpyDeviceToDevice, h->stream));
     if (h->kw == 2) SHK_CUDA(cudaMemcpyAsync(A + h->arena_off_hi, h->node_hi.p, (size_t)n * 8, cudaMemcpyDeviceToDevice, h->stream));
   }
-  SHK_CUDA(cudaMemsetAsync(A + h->arena_off_slots, 0xFF, ((size_t)2 * n + 2) * 8, h->stream));
+  SHK_CUDA(cudaMemsetAsync(A + h->arena_off_slots, 0xFF, index_slots(n) * 8, h->stream));
   SHK_CUDA(cudaMemsetAsync(A + h->arena_off_off, 0, ((size_t)P + 2) * 4, h->stream));
   h->index_P = P;
   h->st.gpu_launches += launch_index_nodes(h->kw, (uint64_t *)(A + h->arena_off_slots), (uint32_t *)(A + h->arena_off_off),
