@@ -70,7 +70,21 @@ pub struct shk_stats {
     pub n_records: u64,
     pub device_planned: u32,
     pub host_qual_bits: u32,
+    pub n_spilled_records: u64,
 }
+
+/// what shk_shard_graph_join reports (include/shk.h)
+#[repr(C)]
+pub struct shk_shard_join_info {
+    pub n_unitigs: u64,
+    pub seq_bytes: u64,
+    pub d_seq: *mut c_void,
+    pub n_links_local: u64,
+    pub d_link_from: *mut c_void,
+    pub d_link_to: *mut c_void,
+    pub n_cyclic_chain_elems: u64,
+}
+pub const SHK_PEER_BLOB_BYTES: usize = 256;
 
 /// opaque: contigs + links produced by the host graph cleaning
 #[repr(C)]
@@ -95,6 +109,8 @@ extern "C" {
     pub fn shk_asm_preprocess_push(h: *mut shk_asm, bytes: *const u8, n: usize) -> shk_status;
     pub fn shk_asm_preprocess_finish(h: *mut shk_asm) -> shk_status;
     pub fn shk_asm_preprocess_reads(h: *mut shk_asm, seq: *const u8, qual: *const u8, n: usize) -> shk_status;
+    /// reads already packed by the host: 2-bit words + validity words (0.375 bytes per position cross the link)
+    pub fn shk_asm_preprocess_packed(h: *mut shk_asm, bases: *const u64, mask: *const u32, n_positions: u64, n_bases: u64) -> shk_status;
     pub fn shk_asm_preprocessing_info(h: *mut shk_asm, json: *mut *const c_char, len: *mut usize) -> shk_status;
     pub fn shk_asm_assemble(h: *mut shk_asm) -> shk_status;
     pub fn shk_asm_get_assembly(h: *mut shk_asm, json: *mut *const c_char, len: *mut usize) -> shk_status;
@@ -106,6 +122,10 @@ extern "C" {
     pub fn shk_get_stream(h: *mut shk_asm) -> *mut c_void;
     pub fn shk_load_reads(h: *mut shk_asm, seq: *const u8, qual: *const u8, n: usize, append: c_int) -> shk_status;
     pub fn shk_load_reads_device(h: *mut shk_asm, d_seq: *const c_void, d_qual: *const c_void, n: usize, append: c_int) -> shk_status;
+    pub fn shk_load_packed(h: *mut shk_asm, bases: *const u64, mask: *const u32, n_positions: u64, n_bases: u64) -> shk_status;
+    /// host-side packer (needs no device): ASCII streams -> the device layout
+    pub fn shk_pack_reads_host(seq: *const u8, qual: *const u8, n: usize, min_qual: c_int, bases: *mut u64, mask: *mut u32,
+                               n_bases: *mut u64, n_threads: c_int) -> shk_status;
     pub fn shk_count(h: *mut shk_asm, reset: c_int) -> shk_status;
     pub fn shk_filter(h: *mut shk_asm) -> shk_status;
     pub fn shk_build_graph(h: *mut shk_asm) -> shk_status;
@@ -132,4 +152,30 @@ extern "C" {
                               circular: *mut u8, link_from: *mut u32, link_to: *mut u32) -> shk_status;
     pub fn shk_contigs_free(c: *mut shk_contigs);
     pub fn shk_asm_contigs(h: *mut shk_asm, out: *mut *const shk_contigs) -> shk_status;
+
+    // ---- sharded path (one handle per rank / GPU; the host runs the collectives between the calls) ----
+    pub fn shk_shard_buckets(global_positions: u64, k: c_int) -> u32;
+    pub fn shk_record_bytes(k: c_int) -> usize;
+    pub fn shk_shard_partition(h: *mut shk_asm, n_buckets: u32, world: u32, rank: u32, send_records: *mut u64) -> shk_status;
+    pub fn shk_shard_pack(h: *mut shk_asm, d_send: *mut c_void, d_send_fill: *mut u64) -> shk_status;
+    pub fn shk_shard_count(h: *mut shk_asm, d_recv: *const c_void, recv_fill: *const u64, histogram_only: c_int, min_count: c_int) -> shk_status;
+    pub fn shk_shard_count_device(h: *mut shk_asm, d_recv: *const c_void, d_recv_fill: *const u64, recv_records: *const u64,
+                                  n_instances: u64, histogram_only: c_int, min_count: c_int) -> shk_status;
+    // graph stage with every rank on its own nodes (peer memory over NVLink), unitigs joined by the chain-level ranking
+    pub fn shk_shard_graph_publish(h: *mut shk_asm, blob_out: *mut c_void) -> shk_status;
+    pub fn shk_shard_graph_connect(h: *mut shk_asm, blobs: *const c_void, node_counts: *const u64, histo_global: *const u64,
+                                   n_instances_global: u64, n_bases_global: u64, used_min_count: c_int) -> shk_status;
+    pub fn shk_shard_graph_edges(h: *mut shk_asm) -> shk_status;
+    pub fn shk_shard_graph_chains(h: *mut shk_asm, n_chains_out: *mut u64) -> shk_status;
+    pub fn shk_shard_graph_records(h: *mut shk_asm, chain_counts: *const u64, d_records_out: *mut c_void) -> shk_status;
+    pub fn shk_shard_graph_cycle_info(h: *mut shk_asm, d_out: *mut c_void) -> shk_status;
+    pub fn shk_shard_graph_join(h: *mut shk_asm, d_all_records: *const c_void, d_all_cycle_info: *const c_void,
+                                info: *mut shk_shard_join_info) -> shk_status;
+    pub fn shk_shard_graph_set_links(h: *mut shk_asm, d_from: *const c_void, d_to: *const c_void, n_links: u64) -> shk_status;
+    // replicated graph stage (fallback: no peer memory)
+    pub fn shk_shard_local_nodes(h: *mut shk_asm, d_lo: *mut c_void, d_hi: *mut c_void, d_count: *mut c_void, d_raw: *mut c_void, cap: usize) -> shk_status;
+    pub fn shk_shard_set_nodes(h: *mut shk_asm, d_lo: *const c_void, d_hi: *const c_void, d_count: *const c_void, d_raw: *const c_void,
+                               n_total: usize, my_offset: usize, histo_global: *const u64, n_instances_global: u64,
+                               n_bases_global: u64, used_min_count: c_int) -> shk_status;
+    pub fn shk_fit_min_count(histo: *const u64, fallback: c_int) -> c_int;
 }

@@ -417,16 +417,16 @@ def test_handles_on_two_devices_in_one_process():
 
 @pytest.mark.parametrize("k", [31, 63])
 def test_spill_area_absorbs_hot_buckets(k):
-    """Skewed input: 5 % copies of one read, 2 % homopolymer / dinucleotide reads — a few minimizer buckets get
-    hundreds of times the mean.  Their overflow must go through the spill area behind the record regions (bounded
+    """Skewed input: 20 % copies of one read, 10 % homopolymer / dinucleotide reads — a few minimizer buckets
+    get many times the size of their region.  Their overflow must go through the spill area behind the record regions (bounded
     memory, no second K1a pass), on the K1a -> K1b path and on the host-planned one, and count exactly."""
     seq, qual = synth.reads(81, 400_000, 20.0, 0.01)
     rows = seq.reshape(-1, 151)
     rng = np.random.default_rng(3)
     n = rows.shape[0]
-    dup = rng.choice(n, n // 20, replace=False)
+    dup = rng.choice(n, n // 5, replace=False)
     rows[dup] = rows[dup[0]]
-    low = rng.choice(n, n // 50, replace=False)
+    low = rng.choice(n, n // 10, replace=False)
     rows[low[::2], :150] = ord("A")
     rows[low[1::2], :150] = np.frombuffer(b"AC" * 75, np.uint8)
     o = run_oracle(seq, qual, k, 2, 20)
