@@ -706,6 +706,9 @@ def brief(name, r):
             "config": {k: v for k, v in r["config"].items() if k in keep}}
 
 
+T0 = time.perf_counter()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -719,7 +722,7 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cold", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="headline workload only (no extra_configs, no parity digest)")
-    ap.add_argument("--extras-budget-s", type=float, default=300.0, help="wall-clock limit of everything after the headline")
+    ap.add_argument("--extras-budget-s", type=float, default=240.0, help="wall-clock limit of everything after the headline")
     ap.add_argument("--e-scale", type=float, default=None, help="genome length scale of workload E (1 = the full 500 Mb community)")
     args = ap.parse_args()
     if args.warmup < 1:
@@ -732,6 +735,9 @@ def main():
     _OUT = os.fdopen(os.dup(1), "w")
     os.dup2(2, 1)
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    if os.environ.get("SHK_BENCH_TRACE"):                # where is every thread after that many seconds (a hang in a multi-rank run)
+        import faulthandler
+        faulthandler.dump_traceback_later(float(os.environ["SHK_BENCH_TRACE"]), repeat=True, file=sys.stderr)
     name = args.workload
     if args.e_scale is not None:
         WORKLOADS["E"]["scale"] = args.e_scale
@@ -758,6 +764,7 @@ def main():
     else:
         res = sharded_arm(args, name, w, ctx, args.steps, args.warmup, with_e2e=True, with_cold=True, with_cpu=True)
 
+    print(f"[bench] rank {rank}: headline done at +{time.perf_counter() - T0:.1f} s", file=sys.stderr, flush=True)
     # ---- the other configs, in the same process, after the headline --------------------------------------------------
     extras, digest = [], None
     # the headline is measured; whatever happens below (a hung collective in an extra config included) it gets printed:
@@ -784,11 +791,14 @@ def main():
     watchdog.start()
     if not args.no_extras and name == "B":
         xs, xw = max(2, min(args.steps, 5)), 3
-        plan = [("A", xs, xw), ("C", xs, xw)] if world == 1 else []
-        plan += [("D", 2, 1)]
-        if world > 1:
-            plan += [("E", 3, 2)]
+        if world > 1:                                # first the cheap and important one: parity of the NCCL path
+            try:
+                digest = parity_digest(ctx)
+            except Exception as ex:        # noqa: BLE001
+                digest = {"ok": False, "error": f"{type(ex).__name__}: {ex}"[:300]}
+        plan = [("A", xs, xw), ("C", xs, xw), ("D", 2, 1)] if world == 1 else [("E", 3, 2), ("D", 2, 1)]
         for xn, s_, w_ in plan:
+            print(f"[bench] rank {rank}: extra config {xn} starts at +{time.perf_counter() - T0:.1f} s", file=sys.stderr, flush=True)
             try:
                 xwl = dict(WORKLOADS[xn])
                 if "n_genomes" in xwl:
@@ -799,11 +809,6 @@ def main():
             except Exception as ex:        # noqa: BLE001  (an extra config must not take the headline down with it)
                 extras.append({"name": xn, "error": f"{type(ex).__name__}: {ex}"[:300]})
                 torch.cuda.synchronize()
-        if world > 1:
-            try:
-                digest = parity_digest(ctx)
-            except Exception as ex:        # noqa: BLE001
-                digest = {"ok": False, "error": f"{type(ex).__name__}: {ex}"[:300]}
     watchdog.cancel()
     emit()
     if world > 1:

@@ -294,7 +294,7 @@ static shk_status load_reads_overlapped(shk_asm *h, const uint8_t *seq, const ui
     unsigned T = std::min<unsigned>(std::max(1u, hw > 4 ? hw - 2 : hw), 12u);
     if (const char *e = getenv("LOCAL_WORLD_SIZE")) {                 // several ranks share this host's cores (torchrun)
       const int lws = atoi(e);
-      if (lws > 1) T = std::max(2u, std::min(T, (hw > 4 ? hw - 2 : hw) / (unsigned)lws));
+      if (lws > 1) T = std::max(1u, std::min(T, (hw > 4 ? hw - 2 : hw) / (unsigned)lws));
     }
     if (const char *e = getenv("SHK_QPACK_THREADS")) T = (unsigned)std::max(1, atoi(e));
     const int mq = h->p.min_qual;
@@ -317,7 +317,12 @@ static shk_status load_reads_overlapped(shk_asm *h, const uint8_t *seq, const ui
     SHK_CUDA(cudaMemcpyAsync(dseq + off, seq + off, len, cudaMemcpyHostToDevice, h->copy_stream));
     if (qpack) {
       const double tw = now_ms();
-      while (remaining[i].load(std::memory_order_acquire) > 0) std::this_thread::yield();
+      // (brief spinning, then sleeping: with several ranks and handles per host the cores are oversubscribed, and a
+      // spinning waiter takes the time the packers need)
+      for (int spins = 0; remaining[i].load(std::memory_order_acquire) > 0; ++spins) {
+        if (spins < 200) std::this_thread::yield();
+        else std::this_thread::sleep_for(std::chrono::microseconds(50));
+      }
       pack_wait_ms += now_ms() - tw;
       SHK_CUDA(cudaMemcpyAsync(dq + off / 32, hq + off / 32, (len + 31) / 32 * 4, cudaMemcpyHostToDevice, h->copy_stream));
     } else {
@@ -1042,7 +1047,7 @@ static shk_status graph_impl(shk_asm *h) {
   uint64_t &L = h->st.gpu_launches;
   // splitters = a pseudo-random 1/32 of the elements + every list head.  The work area is sized from a guess (an
   // eighth of the elements, or what the last run on this handle needed) and verified on the device.
-  uint32_t ns_cap = (uint32_t)std::min<uint64_t>(ne, std::max<uint64_t>(ne / 8 + 65536, (uint64_t)h->ns_hint + h->ns_hint / 4 + 1024));
+  uint32_t ns_cap = (uint32_t)std::min<uint64_t>(ne, std::max<uint64_t>(rank_splitter_guess(ne), (uint64_t)h->ns_hint + h->ns_hint / 4 + 1024));
   // K3's second phase: lookups that missed in the node's own bucket (about a fifth of them; at most 8 per node)
   uint32_t work_cap = (uint32_t)std::min<uint64_t>(8ull * N, std::max<uint64_t>((uint64_t)N + 65536, (uint64_t)h->k3_hint + h->k3_hint / 4 + 1024));
   auto read_back = [&]() -> shk_status {

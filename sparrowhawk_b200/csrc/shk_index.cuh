@@ -30,7 +30,9 @@ struct NodeIndex {
 // slots per node: a quarter-full region keeps linear probing short — what costs in K3 is not the average probe count but
 // its tail (a warp waits for its slowest lane; measured at two slots per node: 5 probe rounds per lookup round, 3-5 lanes
 // active in them), and every lookup of an ABSENT neighbour (an error k-mer below the filter) runs to the first empty slot
+#ifndef SHK_INDEX_SLOTS_PER_NODE
 #define SHK_INDEX_SLOTS_PER_NODE 4u
+#endif
 
 template <int KW>
 __device__ __forceinline__ bool index_key_is(const NodeIndex &ix, u32 id, typename KeyOf<KW>::type key) {

@@ -412,36 +412,63 @@ int launch_unitig_links(const GraphBuffers &g, cudaStream_t st) {
   k_unitig_links<<<blocks_for(ne, 256), 256, 0, st>>>(g.node_edges, g.uniq, ne, g.succ);
   return 1;
 }
+// one or two levels (SHK_RANK_LEVELS=1 in the environment: the one-level ranking, for A/B measurements)
+static bool rank_two_levels() {
+  static const bool two = [] { const char *e = getenv("SHK_RANK_LEVELS"); return !(e && e[0] == '1'); }();
+  return two;
+}
 int launch_rank_mark(const GraphBuffers &g, const uint8_t *circ, cudaStream_t st) {
   u32 ne = 2 * g.n_nodes;
   if (!ne) return 0;
-  k_rank_mark<<<blocks_for(ne, 256), 256, 0, st>>>(g.succ, circ, ne, g.splitters, g.scal + 4);
+  k_rank_mark<<<blocks_for(ne, 256), 256, 0, st>>>(g.succ, circ, ne, rank_two_levels() ? SHK_SPLIT_MASK2 : SHK_SPLIT_MASK, g.splitters, g.scal + 4);
   return 1;
 }
-size_t rank_splitter_bytes() { return 4 + 8 + 4 + 4 + 2 * sizeof(WyState); }
+// per splitter of the work area: first level 64 B (sub_len, sub_sum, last, next, state, next1, loc1, psum1) + second level
+// 56 B (two states, len, sum, next, index) for as many entries (every splitter could be a list head)
+size_t rank_splitter_bytes() { return 4 + 8 + 4 + 4 + 2 * sizeof(WyState) + 4 + 8 + 8 + (2 * sizeof(WyState) + 4 + 8 + 4 + 4); }
+uint32_t rank_splitter_guess(uint64_t n_elems) { return (uint32_t)std::min<uint64_t>(n_elems, rank_two_levels() ? n_elems / 8 + n_elems / 16 + 65536 : n_elems / 8 + 65536); }
 int launch_rank_lists(const GraphBuffers &g, const uint8_t *circ, uint32_t ns_cap, void *work, cudaStream_t st) {
   u32 ne = 2 * g.n_nodes;
   if (!ne || !ns_cap) return 0;
+  const bool two = rank_two_levels();
+  const u32 smask = two ? SHK_SPLIT_MASK2 : SHK_SPLIT_MASK;
   // carve the per-splitter work area (16-byte aligned pieces first)
-  WyState *sa = (WyState *)work, *sb = sa + ns_cap;
-  u64 *sub_sum = (u64 *)(sb + ns_cap);
-  u32 *sub_len = (u32 *)(sub_sum + ns_cap), *last_elem = sub_len + ns_cap, *next_elem = last_elem + ns_cap;
-  k_rank_walk<<<blocks_for(ns_cap, 128), 128, 0, st>>>(g.succ, circ, g.node_count, g.w_len, (const u64 *)g.w_sum, g.splitters, g.scal + 4, ns_cap, (u64 *)g.pd,
-                                                       sub_len, sub_sum, last_elem, next_elem);
+  WyState *sa = (WyState *)work, *sb = sa + ns_cap, *sa1 = sb + ns_cap, *sb1 = sa1 + ns_cap;
+  u64 *sub_sum = (u64 *)(sb1 + ns_cap), *loc1 = sub_sum + ns_cap, *psum1 = loc1 + ns_cap, *sum1 = psum1 + ns_cap;
+  u32 *sub_len = (u32 *)(sum1 + ns_cap), *last_elem = sub_len + ns_cap, *next_elem = last_elem + ns_cap, *next1 = next_elem + ns_cap;
+  u32 *spl1 = next1 + ns_cap, *len1 = spl1 + ns_cap, *nexts1 = len1 + ns_cap;
+  k_rank_walk<<<blocks_for(ns_cap, 128), 128, 0, st>>>(g.succ, circ, g.node_count, g.w_len, (const u64 *)g.w_sum, g.splitters, smask, g.scal + 4,
+                                                       ns_cap, (u64 *)g.pd, sub_len, sub_sum, last_elem, next_elem);
   // one resident wave of CTAs for the cooperative launch
-  static int occ_cache[SHK_MAX_DEVICES] = {0};
-  int &occ = occ_cache[current_device_slot()];
+  static int occ_cache[SHK_MAX_DEVICES][2] = {{0}};
+  int &occ = occ_cache[current_device_slot()][two ? 1 : 0];
   if (!occ) {
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_rank_solve, 256, 0) != cudaSuccess || occ < 1) { cudaGetLastError(); occ = 1; }
+    cudaError_t e = two ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_rank_solve2, 256, 0)
+                        : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_rank_solve, 256, 0);
+    if (e != cudaSuccess || occ < 1) { cudaGetLastError(); occ = 1; }
     if (occ > 2) occ = 2;            // grid-wide barriers get dearer with every CTA; the splitter level is small
   }
   unsigned grid = (unsigned)std::min<uint64_t>((uint64_t)sm_count() * occ, blocks_for(ns_cap, 256));
-  RankSolveArgs a{g.succ, circ, g.splitters, g.scal + 4, ns_cap, (u64 *)g.pd, ne, sub_len, sub_sum, last_elem, next_elem,
-                  sa, sb, g.tail_of, g.len_of, (u64 *)g.sum_of, g.scal + 10, g.scal + 5};
-  void *args[] = {&a};
-  cudaLaunchCooperativeKernel((void *)k_rank_solve, dim3(grid), dim3(256), args, 0, st);
+  int n = 1;
+  if (two) {
+    cudaMemsetAsync(loc1, 0xFF, (size_t)ns_cap * 8, st);             // splitters no stretch reaches (cycles) stay ~0
+    k_rank_link1<<<blocks_for(ns_cap, 256), 256, 0, st>>>(g.succ, circ, g.splitters, g.scal + 4, ns_cap, SHK_SPLIT_MASK2, (const u64 *)g.pd, next_elem,
+                                                         next1, spl1, g.scal + 14);
+    k_rank_walk1<<<blocks_for(ns_cap, 128), 128, 0, st>>>(next1, sub_len, sub_sum, spl1, g.scal + 14, ns_cap, SHK_SPLIT_MASK2, loc1, psum1, len1, sum1, nexts1);
+    RankSolve2Args a{g.splitters, g.scal + 4, ns_cap, sub_len, sub_sum, last_elem, next_elem, next1, loc1, psum1, spl1, g.scal + 14, ns_cap,
+                     len1, sum1, nexts1, sa1, sb1, sa, g.tail_of, g.len_of, (u64 *)g.sum_of, g.scal + 10, g.scal + 5};
+    void *args[] = {&a};
+    cudaLaunchCooperativeKernel((void *)k_rank_solve2, dim3(grid), dim3(256), args, 0, st);
+    n += 3;
+  } else {
+    RankSolveArgs a{g.succ, circ, g.splitters, g.scal + 4, ns_cap, (u64 *)g.pd, ne, sub_len, sub_sum, last_elem, next_elem,
+                    sa, sb, g.tail_of, g.len_of, (u64 *)g.sum_of, g.scal + 10, g.scal + 5};
+    void *args[] = {&a};
+    cudaLaunchCooperativeKernel((void *)k_rank_solve, dim3(grid), dim3(256), args, 0, st);
+    n += 1;
+  }
   k_rank_apply<<<blocks_for(ne, 256), 256, 0, st>>>(sa, g.splitters, g.scal + 4, ns_cap, ne, (u64 *)g.pd, g.scal + 1);
-  return 3;
+  return n + 1;
 }
 int launch_cycle_cut(const GraphBuffers &g, uint32_t n_cyclic, cudaStream_t st) {
   u32 ne = 2 * g.n_nodes;

@@ -20,7 +20,7 @@ struct GraphBuffers {
   uint32_t *link_from, *link_to; uint32_t link_cap;
   // device scalars: [1] n_cyclic, [2] n_unitigs, [3] n_links, [4] n_splitters, [5] splitter work area too small,
   // [6] K3 lookups deferred to the second phase,
-  // [8..9] seq cursor (u64), [10..12] round flags of k_rank_solve
+  // [8..9] seq cursor (u64), [10..12] round flags of k_rank_solve, [13] K3' deferred lookups (sharded), [14] second-level splitters
   uint32_t *scal; uint64_t *seq_cursor;
   // list ranking over WEIGHTED elements (chain level of the sharded path): element e weighs w_len[e >> 1] nodes and
   // w_sum[e >> 1] k-mer counts; null = node level (weight 1, node_count)
@@ -49,6 +49,7 @@ int launch_unitig_links(const GraphBuffers &g, cudaStream_t st);
 // a larger work area).  circ may be null (first pass).
 int launch_rank_mark(const GraphBuffers &g, const uint8_t *circ, cudaStream_t st);
 size_t rank_splitter_bytes();
+uint32_t rank_splitter_guess(uint64_t n_elems);   // first guess of ns_cap for a list of n_elems elements
 int launch_rank_lists(const GraphBuffers &g, const uint8_t *circ, uint32_t ns_cap, void *work, cudaStream_t st);
 int launch_cycle_cut(const GraphBuffers &g, uint32_t n_cyclic, cudaStream_t st);
 int launch_unitig_heads(const GraphBuffers &g, int k, bool have_circ, cudaStream_t st);

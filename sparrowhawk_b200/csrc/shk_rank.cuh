@@ -31,16 +31,27 @@ namespace cg = cooperative_groups;
 namespace shk {
 
 #ifndef SHK_SPLIT_MASK
-#define SHK_SPLIT_MASK 31u
+#define SHK_SPLIT_MASK 31u          // one level
+#endif
+#ifndef SHK_SPLIT_MASK2
+#define SHK_SPLIT_MASK2 7u          // two levels: both of them
 #endif
 
 struct __align__(16) WyState { u32 ptr; u32 dist; u64 sum; };
 
-__device__ __forceinline__ bool rank_hash_splitter(u32 e) {
+// one element in (mask + 1) is a splitter (mask = 2^j - 1: 31 with one level, 7 with two)
+__device__ __forceinline__ bool rank_hash_splitter(u32 e, u32 mask) {
   u32 x = e * 0x9E3779B1u;
   x ^= x >> 15;
   x *= 0x85EBCA77u;
-  return ((x >> 13) & SHK_SPLIT_MASK) == 0;
+  return ((x >> 13) & mask) == 0;
+}
+// the same on the splitter level (another mix: a splitter index is not an element id)
+__device__ __forceinline__ bool rank_hash_splitter1(u32 i, u32 mask) {
+  u32 x = i * 0xC2B2AE3Du + 0x27D4EB2Fu;
+  x ^= x >> 16;
+  x *= 0x85EBCA77u;
+  return ((x >> 11) & mask) == 0;
 }
 // circ (nullable): 2 marks the element a cut cycle restarts from (forced head)
 __device__ __forceinline__ bool rank_is_head(const u32 *succ, const uint8_t *circ, u32 e) {
@@ -48,13 +59,13 @@ __device__ __forceinline__ bool rank_is_head(const u32 *succ, const uint8_t *cir
 }
 
 __global__ void __launch_bounds__(256)
-k_rank_mark(const u32 *__restrict__ succ, const uint8_t *__restrict__ circ, u32 n_elems, u32 *__restrict__ splitters,
+k_rank_mark(const u32 *__restrict__ succ, const uint8_t *__restrict__ circ, u32 n_elems, u32 smask, u32 *__restrict__ splitters,
             u32 *__restrict__ n_splitters) {
   __shared__ u32 wcnt[8], cta_base;
   const u32 e = blockIdx.x * blockDim.x + threadIdx.x;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   bool sp = false;
-  if (e < n_elems) sp = rank_hash_splitter(e) || rank_is_head(succ, circ, e);
+  if (e < n_elems) sp = rank_hash_splitter(e, smask) || rank_is_head(succ, circ, e);
   const u32 ball = __ballot_sync(0xffffffffu, sp);
   if (lane == 0) wcnt[warp] = __popc(ball);
   __syncthreads();
@@ -73,7 +84,7 @@ k_rank_mark(const u32 *__restrict__ succ, const uint8_t *__restrict__ circ, u32 
 __global__ void __launch_bounds__(128)
 k_rank_walk(const u32 *__restrict__ succ, const uint8_t *__restrict__ circ,
             const uint16_t *__restrict__ node_count, const u32 *__restrict__ w_len, const u64 *__restrict__ w_sum,
-            const u32 *__restrict__ splitters,
+            const u32 *__restrict__ splitters, u32 smask,
             const u32 *__restrict__ n_splitters_dev, u32 ns_cap, u64 *__restrict__ loc, u32 *__restrict__ sub_len,
             u64 *__restrict__ sub_sum, u32 *__restrict__ last_elem, u32 *__restrict__ next_elem) {
   const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -89,7 +100,7 @@ k_rank_walk(const u32 *__restrict__ succ, const uint8_t *__restrict__ circ,
     if (nxt == SHK_NONE) break;
     if (circ && circ[nxt] == 2) { nxt = SHK_NONE; break; }   // a cut cycle ends in front of its forced head
     // nxt has a predecessor (cur), so it can only be a splitter by the hash rule
-    if (rank_hash_splitter(nxt)) break;
+    if (rank_hash_splitter(nxt, smask)) break;
     cur = nxt;
   }
   sub_len[i] = r; sub_sum[i] = sum; last_elem[i] = cur; next_elem[i] = nxt;
@@ -163,6 +174,140 @@ k_rank_solve(RankSolveArgs a) {
     if (a.next_elem[i] != SHK_NONE) continue;
     const WyState v = st[i];
     if (!wy_true_head(st, v.ptr)) continue;
+    const u32 h = a.splitters[v.ptr];
+    a.tail_of[h] = a.last_elem[i];
+    a.len_of[h] = v.dist + a.sub_len[i];
+    a.sum_of[h] = v.sum + a.sub_sum[i];
+  }
+}
+
+// ---- two levels -------------------------------------------------------------------------------------------------
+// With one level the walk is a chain of dependent loads as long as the longest gap between splitters (about 400
+// elements at a rate of 1/32) and denser splitters are paid for in pointer-jumping rounds.  With two, the element
+// level uses a rate of 1/8 (gaps of at most about 110), and the list of SPLITTERS — element i weighs sub_len[i]
+// elements and sub_sum[i] counts, its successor is the splitter that starts where its sublist ends — is ranked the
+// same way once more: a 1/8 sample of the splitters (plus the list heads) walks its gaps, and only those
+// second-level splitters (an eightieth of the elements) go through pointer jumping.  The result is written in the form
+// the one-level kernels produce (state[i] = head splitter, weight in front of i), so finish and apply are shared.
+__global__ void __launch_bounds__(256)
+k_rank_link1(const u32 *__restrict__ succ, const uint8_t *__restrict__ circ, const u32 *__restrict__ splitters,
+             const u32 *__restrict__ n_splitters, u32 ns_cap, u32 smask1, const u64 *__restrict__ loc, const u32 *__restrict__ next_elem,
+             u32 *__restrict__ next1 /* bit 31: list head */, u32 *__restrict__ spl1, u32 *__restrict__ n_spl1) {
+  __shared__ u32 wcnt[8], cta_base;
+  const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+  const u32 ns = *n_splitters;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  bool sp = false;
+  if (ns <= ns_cap && i < ns) {
+    const bool head = rank_is_head(succ, circ, splitters[i]);
+    const u32 t = next_elem[i];
+    const u32 nx = t == SHK_NONE ? 0x7FFFFFFFu : (u32)(loc[t] >> 32);      // (t starts a sublist: its splitter index)
+    next1[i] = nx | (head ? 0x80000000u : 0u);
+    sp = head || rank_hash_splitter1(i, smask1);
+  }
+  const u32 ball = __ballot_sync(0xffffffffu, sp);
+  if (lane == 0) wcnt[warp] = __popc(ball);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    u32 t = 0;
+    for (int w = 0; w < 8; ++w) { const u32 c = wcnt[w]; wcnt[w] = t; t += c; }
+    cta_base = t ? atomicAdd(n_spl1, t) : 0;
+  }
+  __syncthreads();
+  if (sp) spl1[cta_base + wcnt[warp] + __popc(ball & ((1u << lane) - 1))] = i;
+}
+
+// per second-level splitter: walk the splitter list to the next one.  loc1[i] = second-level index << 32 | elements in
+// front of splitter i inside that stretch; psum1[i] = their count sum.
+__global__ void __launch_bounds__(128)
+k_rank_walk1(const u32 *__restrict__ next1, const u32 *__restrict__ sub_len, const u64 *__restrict__ sub_sum,
+             const u32 *__restrict__ spl1, const u32 *__restrict__ n_spl1, u32 ns1_cap, u32 smask1,
+             u64 *__restrict__ loc1, u64 *__restrict__ psum1, u32 *__restrict__ len1, u64 *__restrict__ sum1,
+             u32 *__restrict__ nexts1 /* the splitter (first-level index) that follows the stretch, or 0x7FFFFFFF */) {
+  const u32 j = blockIdx.x * blockDim.x + threadIdx.x;
+  const u32 n1 = *n_spl1;
+  if (n1 > ns1_cap || j >= n1) return;
+  u32 cur = spl1[j], r = 0, nx;
+  u64 s = 0;
+  for (;;) {
+    loc1[cur] = ((u64)j << 32) | r;
+    psum1[cur] = s;
+    r += sub_len[cur]; s += sub_sum[cur];
+    nx = __ldg(next1 + cur) & 0x7FFFFFFFu;
+    if (nx == 0x7FFFFFFFu) break;
+    if (rank_hash_splitter1(nx, smask1)) break;          // (nx has a predecessor: a splitter by the hash rule only)
+    cur = nx;
+  }
+  len1[j] = r; sum1[j] = s; nexts1[j] = nx;
+}
+
+struct RankSolve2Args {
+  const u32 *splitters; const u32 *n_splitters; u32 ns_cap;          // first level
+  const u32 *sub_len; const u64 *sub_sum; const u32 *last_elem; const u32 *next_elem; const u32 *next1;
+  const u64 *loc1; const u64 *psum1;
+  const u32 *spl1; const u32 *n_spl1; u32 ns1_cap;                  // second level
+  const u32 *len1; const u64 *sum1; const u32 *nexts1;
+  WyState *sa1, *sb1;                                                // second-level ping-pong
+  WyState *state0;                                                   // out: per first-level splitter, as the one-level solve leaves it
+  u32 *tail_of, *len_of; u64 *sum_of;
+  u32 *changed; u32 *overflow;
+};
+
+__global__ void __launch_bounds__(256)
+k_rank_solve2(RankSolve2Args a) {
+  cg::grid_group grid = cg::this_grid();
+  const u32 tid = blockIdx.x * blockDim.x + threadIdx.x, nthr = gridDim.x * blockDim.x;
+  const u32 ns = *a.n_splitters, n1 = *a.n_spl1;
+  if (ns > a.ns_cap || n1 > a.ns1_cap) {                   // uniform across the grid: nobody reaches a barrier
+    if (tid == 0) atomicExch(a.overflow, 1u);
+    return;
+  }
+  // ---- link the second level ----
+  for (u32 j = tid; j < n1; j += nthr) {
+    if (a.next1[a.spl1[j]] & 0x80000000u) a.sa1[j] = WyState{j, 0u, 0ull};
+    const u32 t = a.nexts1[j];
+    if (t != 0x7FFFFFFFu) a.sa1[(u32)(a.loc1[t] >> 32)] = WyState{j, a.len1[j], a.sum1[j]};
+  }
+  if (tid == 0) { a.changed[0] = 0; a.changed[1] = 0; a.changed[2] = 0; }
+  grid.sync();
+  // ---- jump ----
+  WyState *in = a.sa1, *out = a.sb1;
+  u32 max_rounds = 2;
+  for (u32 d = 1; d < n1; d <<= 1) ++max_rounds;
+  for (u32 r = 0; r < max_rounds; ++r) {
+    bool ch = false;
+    for (u32 j = tid; j < n1; j += nthr) {
+      WyState v = in[j];
+      if (v.ptr != j) {
+        const WyState vp = in[v.ptr];
+        if (vp.ptr != v.ptr) { v.ptr = vp.ptr; v.dist += vp.dist; v.sum += vp.sum; ch = true; }
+      }
+      out[j] = v;
+    }
+    if (ch) a.changed[r % 3] = 1u;
+    grid.sync();
+    const bool any = *reinterpret_cast<volatile u32 *>(a.changed + r % 3) != 0;
+    if (tid == 0) a.changed[(r + 2) % 3] = 0;
+    WyState *t = in; in = out; out = t;
+    if (!any) break;
+  }
+  const WyState *st1 = in;
+  // ---- first-level states: head splitter + weight in front (a splitter no stretch has reached lies on a cycle) ----
+  for (u32 i = tid; i < ns; i += nthr) {
+    const u64 L = a.loc1[i];
+    WyState o{i, 1u, 0ull};                                 // "not under a true head" for finish / apply
+    if (L != ~0ull) {
+      const WyState v = st1[(u32)(L >> 32)];
+      if (wy_true_head(st1, v.ptr)) o = WyState{a.spl1[v.ptr], v.dist + (u32)L, v.sum + a.psum1[i]};
+    }
+    a.state0[i] = o;
+  }
+  grid.sync();
+  // ---- finish: list tails tell their head the length, the tail element and the count sum ----
+  for (u32 i = tid; i < ns; i += nthr) {
+    if (a.next_elem[i] != SHK_NONE) continue;
+    const WyState v = a.state0[i];
+    if (!wy_true_head(a.state0, v.ptr)) continue;
     const u32 h = a.splitters[v.ptr];
     a.tail_of[h] = a.last_elem[i];
     a.len_of[h] = v.dist + a.sub_len[i];

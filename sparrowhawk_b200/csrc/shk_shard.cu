@@ -219,12 +219,13 @@ shk_status shk_shard_graph_chains(shk_asm *h, uint64_t *n_chains_out) {
   uint64_t &L = h->st.gpu_launches;
   k_unitig_links_sharded<<<(unsigned)((ne + 255) / 256), 256, 0, h->stream>>>(t, g.node_edges, g.uniq, (u32)ne, g.succ, h->xsucc.as<u32>());
   ++L;
-  uint32_t ns_cap = (uint32_t)std::min<uint64_t>(ne, std::max<uint64_t>(ne / 4 + 65536, (uint64_t)h->ns_hint + h->ns_hint / 4 + 1024));
+  uint32_t ns_cap = (uint32_t)std::min<uint64_t>(ne, std::max<uint64_t>(rank_splitter_guess(ne) + ne / 8, (uint64_t)h->ns_hint + h->ns_hint / 4 + 1024));
   const uint8_t *circ = nullptr;
   auto pass = [&]() -> shk_status {
     SHK_TRY(h->rank_work.ensure((size_t)ns_cap * rank_splitter_bytes() + 64));
     SHK_CUDA(cudaMemsetAsync(h->pd.p, 0xFF, ne * 8, h->stream));
     SHK_CUDA(cudaMemsetAsync(g.scal, 0, 52, h->stream));             // (all but [13], K3's deferred lookups)
+    SHK_CUDA(cudaMemsetAsync(g.scal + 14, 0, 8, h->stream));
     SHK_CUDA(cudaMemsetAsync(h->tail_of.p, 0xFF, ne * 4, h->stream));
     L += launch_rank_mark(g, circ, h->stream);
     L += launch_rank_lists(g, circ, ns_cap, h->rank_work.p, h->stream);
@@ -352,7 +353,7 @@ shk_status shk_shard_graph_join(shk_asm *h, const void *d_all_records, const voi
   uint64_t &L = h->st.gpu_launches;
   const unsigned cb = (C + 255) / 256, ceb = (unsigned)((ce + 255) / 256);
   k_chain_unpack<<<cb, 256, 0, h->stream>>>(recs, C, gc.succ, h->c_wlen.as<u32>(), h->c_wsum.as<u64>()); ++L;
-  uint32_t ns_cap = (uint32_t)std::min<uint64_t>(ce, std::max<uint64_t>(ce / 4 + 65536, (uint64_t)h->ns_hint_c + h->ns_hint_c / 4 + 1024));
+  uint32_t ns_cap = (uint32_t)std::min<uint64_t>(ce, std::max<uint64_t>(rank_splitter_guess(ce) + ce / 8, (uint64_t)h->ns_hint_c + h->ns_hint_c / 4 + 1024));
   u32 *kcnt = h->c_kcnt.as<u32>(); u64 *klen = h->c_klen.as<u64>();
   const uint8_t *circ_c = nullptr;
   // one pass: rank the chain-level lists, pick the kept one of each mirror pair, number the unitigs by prefix scans
