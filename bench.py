@@ -506,6 +506,12 @@ def sharded_arm(args, name, w, ctx, steps, warmup, with_e2e=True, with_cold=Fals
     barrier()
     clocks = sampler.stop()
     ms_total = ev0.elapsed_time(ev1)
+    stage_ranks = None
+    if world > 1:                                    # every rank's own stage times (rank 0's alone hide who waits for whom)
+        mine = {n: round(sum(v) / len(v), 3) for n, v in stage_acc.items() if v}
+        allm = [None] * world
+        dist.all_gather_object(allm, mine)
+        stage_ranks = {n: [m.get(n) for m in allm] for n in mine}
     st = h.stats()
     launches = st["gpu_launches"] - launches0
     t = torch.tensor([ms_total], dtype=torch.float64, device="cuda")
@@ -650,6 +656,7 @@ def sharded_arm(args, name, w, ctx, steps, warmup, with_e2e=True, with_cold=Fals
                 "stage_ms": ({n: sum(v) / len(v) for n, v in stage_acc.items() if v} if world > 1 else
                              {kname: sum(v) / len(v) for kname, v in ms_parts.items()}),
                 "stage_host_ms": {n: round(sum(v) / len(v), 3) for n, v in host_acc.items() if v} if world > 1 else None,
+                "stage_ms_ranks": stage_ranks,
                 "note": "traffic = dram bytes of one launch from the committed ncu capture (profiles/); the design "
                         "keeps the table in shared memory, so measured traffic is far below the model's bytes"}
 

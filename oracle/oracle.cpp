@@ -50,7 +50,7 @@ template <class K> struct Oracle {
   std::vector<K> dkey; std::vector<uint32_t> dcount; std::vector<uint8_t> dedge;
   uint64_t histo[SHK_NBINS];
   // nodes (sorted by key)
-  std::vector<K> nkey; std::vector<uint16_t> ncount; std::vector<uint8_t> nraw, nedge;
+  std::vector<K> nkey; std::vector<uint16_t> ncount; std::vector<uint8_t> nraw, nedge; std::vector<int64_t> nlink;
   // unitigs
   std::vector<std::string> unitigs; std::vector<float> ucov; std::vector<uint8_t> ucirc;
 
@@ -119,7 +119,10 @@ template <class K> struct Oracle {
     std::vector<std::array<uint64_t, 5>> bc(nt, std::array<uint64_t, 5>{0, 0, 0, 0, 0});
     std::vector<std::thread> th;
     for (int t = 0; t < nt; ++t)
-      th.emplace_back([&, t]() { extract(seq, qual, cut[t], cut[t + 1], loc[t], nb[t], ni[t], bc[t].data()); });
+      th.emplace_back([&, t]() {
+        for (auto &v : loc[t]) v.reserve((cut[t + 1] - cut[t]) / 256 + 64);   // (canonical keys crowd the low buckets: the others stay untouched pages)
+        extract(seq, qual, cut[t], cut[t + 1], loc[t], nb[t], ni[t], bc[t].data());
+      });
     for (auto &x : th) x.join();
     th.clear();
     for (int t = 0; t < nt; ++t) { n_bases += nb[t]; n_instances += ni[t]; for (int j = 0; j < 5; ++j) base_counts[j] += bc[t][j]; }
@@ -137,18 +140,26 @@ template <class K> struct Oracle {
   // S7/S8/S9/S10: sort + run-length, histogram, filter.
   void finish_count() {
     int nt = std::max(1, nthreads);
-    struct Part { std::vector<K> key; std::vector<uint32_t> cnt; std::vector<uint8_t> e; };
+    struct Part {
+      std::vector<K> key; std::vector<uint32_t> cnt; std::vector<uint8_t> e;
+      std::vector<K> nk; std::vector<uint16_t> nc; std::vector<uint8_t> nr;      // the survivors of the filter
+      uint64_t histo[SHK_NBINS];
+    };
     std::vector<Part> parts(256);
     auto work = [&](int t) {
       for (int b = t; b < 256; b += nt) {
         auto &v = buckets[b];
         std::sort(v.begin(), v.end(), [](const Inst<K> &x, const Inst<K> &y) { return x.key < y.key; });
         Part &p = parts[b];
+        memset(p.histo, 0, sizeof p.histo);
         for (size_t i = 0; i < v.size();) {
           size_t j = i; uint8_t e = 0;
           while (j < v.size() && v[j].key == v[i].key) { e |= v[j].e; ++j; }
           p.key.push_back(v[i].key); p.cnt.push_back((uint32_t)std::min<size_t>(j - i, 0xFFFFFFFFu));
           p.e.push_back(e);
+          uint32_t c = std::min<uint32_t>(p.cnt.back(), SHK_COUNT_MAX);
+          p.histo[shk_histo_bin(c)]++;
+          if (shk_passes(c, min_count)) { p.nk.push_back(v[i].key); p.nc.push_back((uint16_t)c); p.nr.push_back(e); }
           i = j;
         }
         std::vector<Inst<K>>().swap(v);
@@ -158,17 +169,16 @@ template <class K> struct Oracle {
     for (int t = 0; t < nt; ++t) th.emplace_back(work, t);
     for (auto &x : th) x.join();
     dkey.clear(); dcount.clear(); dedge.clear();
-    for (auto &p : parts) {
+    memset(histo, 0, sizeof histo);
+    nkey.clear(); ncount.clear(); nraw.clear();
+    for (auto &p : parts) {                 // buckets in key order: the concatenation is sorted
       dkey.insert(dkey.end(), p.key.begin(), p.key.end());
       dcount.insert(dcount.end(), p.cnt.begin(), p.cnt.end());
       dedge.insert(dedge.end(), p.e.begin(), p.e.end());
-    }
-    memset(histo, 0, sizeof histo);
-    nkey.clear(); ncount.clear(); nraw.clear();
-    for (size_t i = 0; i < dkey.size(); ++i) {
-      uint32_t c = std::min<uint32_t>(dcount[i], SHK_COUNT_MAX);
-      histo[shk_histo_bin(c)]++;
-      if (shk_passes(c, min_count)) { nkey.push_back(dkey[i]); ncount.push_back((uint16_t)c); nraw.push_back(dedge[i]); }
+      nkey.insert(nkey.end(), p.nk.begin(), p.nk.end());
+      ncount.insert(ncount.end(), p.nc.begin(), p.nc.end());
+      nraw.insert(nraw.end(), p.nr.begin(), p.nr.end());
+      for (int i = 0; i < SHK_NBINS; ++i) histo[i] += p.histo[i];
     }
   }
 
@@ -190,11 +200,13 @@ template <class K> struct Oracle {
   }
   static int side_bits(uint8_t e, int side) { return side == 0 ? (e & 15) : (e >> 4); }
   // unique mutual link leaving node i on `side`
+  // (the neighbour was found when the edge was validated: nlink keeps (index << 1 | arrival side) of the last validated
+  // edge per side, which is THE edge when the side has exactly one)
   bool link(int64_t i, int side, int64_t &w, int &s) const {
     int bits = side_bits(nedge[i], side);
     if (__builtin_popcount(bits) != 1) return false;
-    K wk; neighbour(nkey[i], side, (uint32_t)__builtin_ctz(bits), wk, s);
-    w = find(wk);
+    int64_t v = nlink[2 * i + side];
+    w = v >> 1; s = (int)(v & 1);
     if (w < 0 || w == i) return false;    // w<0 cannot happen after validation
     return __builtin_popcount(side_bits(nedge[w], s)) == 1;
   }
@@ -203,14 +215,28 @@ template <class K> struct Oracle {
   void build_graph() {
     size_t N = nkey.size();
     nedge.assign(N, 0);
-    for (size_t i = 0; i < N; ++i) {
-      uint8_t v = 0;
-      for (int bit = 0; bit < 8; ++bit)
-        if (nraw[i] >> bit & 1) {
-          K wk; int s; neighbour(nkey[i], bit >> 2, (uint32_t)(bit & 3), wk, s);
-          if (find(wk) >= 0) v |= (uint8_t)(1u << bit);
-        }
-      nedge[i] = v;
+    nlink.assign(2 * N, -2);
+    // S13: every node on its own — threads take slices
+    auto validate = [&](size_t lo, size_t hi) {
+      for (size_t i = lo; i < hi; ++i) {
+        uint8_t v = 0;
+        for (int bit = 0; bit < 8; ++bit)
+          if (nraw[i] >> bit & 1) {
+            K wk; int s; neighbour(nkey[i], bit >> 2, (uint32_t)(bit & 3), wk, s);
+            int64_t w = find(wk);
+            if (w >= 0) { v |= (uint8_t)(1u << bit); nlink[2 * i + (bit >> 2)] = (w << 1) | s; }
+          }
+        nedge[i] = v;
+      }
+    };
+    {
+      int nt = std::max(1, nthreads);
+      if (nt == 1 || N < 4096) validate(0, N);
+      else {
+        std::vector<std::thread> th;
+        for (int t = 0; t < nt; ++t) th.emplace_back(validate, N * t / nt, N * (t + 1) / nt);
+        for (auto &x : th) x.join();
+      }
     }
     unitigs.clear(); ucov.clear(); ucirc.clear();
     std::vector<uint8_t> seen(N, 0);

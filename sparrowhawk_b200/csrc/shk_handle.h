@@ -172,7 +172,7 @@ struct shk_asm {
   shk::PinBuf gpin;             // graph stage: pinned mirror of its scalars
   uint32_t ns_hint = 0;         // splitters the last graph stage on this handle needed
   uint32_t k3_hint = 0, k3_cap = 0;   // K3 lookups the last graph stage deferred to its second phase; size of the list
-  shk::DevBuf k3_work;
+  shk::DevBuf k3_work, k3_route;        // (k3_route: the sharded path's routing area, shk_shard.cuh)
 
   // ---- results / state ----
   shk_stats st;

@@ -182,17 +182,47 @@ shk_status shk_shard_graph_edges(shk_asm *h) {
   const u32 *bucket_of = h->idx_tmp.as<u32>();
   const unsigned nb = (n + 255) / 256, wb = (work_cap + 255) / 256;
   const u32 base = h->shard_node_off[h->shard_rank];
-  if (h->kw == 1) {
-    k_build_edges_fast<1><<<nb, 256, 0, h->stream>>>(ix, h->p.k, bucket_of, h->node_raw.as<uint8_t>(), n, base, edges, h->uniq.as<u32>(),
-                                                    h->k3_work.as<u32>(), work_cap, nw);
-    k_build_edges_sharded_slow<1><<<wb, 256, 0, h->stream>>>(t, h->node_lo.as<u64>(), nullptr, bucket_of, h->k3_work.as<u32>(), work_cap, nw,
-                                                            edges, h->uniq.as<u32>());
-  } else {
-    k_build_edges_fast<2><<<nb, 256, 0, h->stream>>>(ix, h->p.k, bucket_of, h->node_raw.as<uint8_t>(), n, base, edges, h->uniq.as<u32>(),
-                                                    h->k3_work.as<u32>(), work_cap, nw);
-    k_build_edges_sharded_slow<2><<<wb, 256, 0, h->stream>>>(t, h->node_lo.as<u64>(), h->node_hi.as<u64>(), bucket_of, h->k3_work.as<u32>(),
-                                                            work_cap, nw, edges, h->uniq.as<u32>());
+  // SHK_TRACE_K3=1: the two phases timed apart (printed by the next call once they are done)
+  static const bool trace = getenv("SHK_TRACE_K3") != nullptr;
+  static thread_local cudaEvent_t tev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+  static thread_local bool tev_pending = false;
+  if (trace) {
+    if (!tev[0]) for (auto &e : tev) cudaEventCreate(&e);
+    if (tev_pending && cudaEventQuery(tev[2]) == cudaSuccess) {
+      float a = 0, b = 0, c = 0, d = 0;
+      cudaEventElapsedTime(&a, tev[0], tev[1]); cudaEventElapsedTime(&b, tev[1], tev[3]);
+      cudaEventElapsedTime(&c, tev[3], tev[4]); cudaEventElapsedTime(&d, tev[4], tev[2]);
+      fprintf(stderr, "[shk] rank %u K3' fast %.3f ms, route: buckets %.3f + order %.3f ms, lookups %.3f ms (n = %u, deferred hint %u)\n",
+              h->shard_rank, a, b, c, d, n, h->k3_hint);
+    }
+    cudaEventRecord(tev[0], h->stream);
   }
+  // routing area behind the list: to_bucket [work_cap] | order [work_cap] | bin counts | bin cursors | n_routed
+  SHK_TRY(h->k3_route.ensure(((size_t)2 * work_cap + 2 * SHK_ROUTE_BINS + 4) * 4));
+  u32 *to_bucket = h->k3_route.as<u32>(), *order = to_bucket + work_cap, *bin_count = order + work_cap,
+      *bin_cursor = bin_count + SHK_ROUTE_BINS, *n_routed = bin_cursor + SHK_ROUTE_BINS;
+  SHK_CUDA(cudaMemsetAsync(bin_count, 0, (2 * SHK_ROUTE_BINS + 1) * 4, h->stream));
+  const u64 *lo = h->node_lo.as<u64>(), *hi = h->kw == 2 ? h->node_hi.as<u64>() : nullptr;
+  u32 *work = h->k3_work.as<u32>();
+  if (h->kw == 1)
+    k_build_edges_fast<1><<<nb, 256, 0, h->stream>>>(ix, h->p.k, bucket_of, h->node_raw.as<uint8_t>(), n, base, edges, h->uniq.as<u32>(),
+                                                    work, work_cap, nw);
+  else
+    k_build_edges_fast<2><<<nb, 256, 0, h->stream>>>(ix, h->p.k, bucket_of, h->node_raw.as<uint8_t>(), n, base, edges, h->uniq.as<u32>(),
+                                                    work, work_cap, nw);
+  if (trace) cudaEventRecord(tev[1], h->stream);
+  if (h->kw == 1) k_route_count<1><<<wb, 256, 0, h->stream>>>(t, lo, hi, bucket_of, work, work_cap, nw, to_bucket, bin_count);
+  else            k_route_count<2><<<wb, 256, 0, h->stream>>>(t, lo, hi, bucket_of, work, work_cap, nw, to_bucket, bin_count);
+  if (trace) cudaEventRecord(tev[3], h->stream);
+  k_route_scan<<<1, SHK_ROUTE_BINS, 0, h->stream>>>(t, bin_count, bin_cursor, n_routed);
+  k_route_scatter<<<wb, 256, 0, h->stream>>>(to_bucket, h->P, work_cap, nw, bin_cursor, order);
+  if (trace) cudaEventRecord(tev[4], h->stream);
+  if (h->kw == 1)
+    k_build_edges_sharded_slow<1><<<wb, 256, 0, h->stream>>>(t, lo, hi, work, to_bucket, order, n_routed, edges, h->uniq.as<u32>());
+  else
+    k_build_edges_sharded_slow<2><<<wb, 256, 0, h->stream>>>(t, lo, hi, work, to_bucket, order, n_routed, edges, h->uniq.as<u32>());
+  h->st.gpu_launches += 3;
+  if (trace) { cudaEventRecord(tev[2], h->stream); tev_pending = true; }
   h->st.gpu_launches += 2;
   SHK_CUDA(cudaGetLastError());
   return SHK_OK;

@@ -82,27 +82,105 @@ __device__ __forceinline__ u32 shard_find(const ShardTopo *t, typename KeyOf<KW>
 // K3' second phase (the first is k_build_edges_fast over the rank's own index, shk_edges.cuh): the lookups that missed
 // in the node's own bucket.  The neighbour's minimizer names its bucket, the bucket its owner rank; that rank's index
 // is probed in place (peer memory when it is another rank).
+//
+// The lookups are ROUTED first: sorted by the bucket they go to (SHK_ROUTE_BINS ranges of the global bucket space,
+// the owner ranks in the order rank+1, rank+2, ..., so at any moment every rank is asked by one other rank).  Probed
+// in list order the lookups of a rank scatter over the indices of ALL peers — measured on 8 GPUs (1.4 GB of peer
+// index mapped per rank): 3.85 ms for 2.1 M remote lookups, ten times the cost per lookup seen on 4 GPUs (0.6 GB),
+// which is what running out of TLB reach on the peer mappings looks like.  Routed, the grid sweeps one peer range
+// after the other and the pages in flight are a few.
+#define SHK_ROUTE_BINS 512u
+__device__ __forceinline__ u32 route_bin(u32 bucket, u32 P) { return (u32)(((u64)bucket * SHK_ROUTE_BINS) / P); }
+
+// R1: the bucket every listed lookup goes to (SHK_NONE: settled — the node's own bucket was looked up already, or the
+// owner holds no node at all), bins counted
+template <int KW>
+__global__ void __launch_bounds__(256)
+k_route_count(const ShardTopo *__restrict__ t, const u64 *__restrict__ node_lo, const u64 *__restrict__ node_hi,
+              const u32 *__restrict__ bucket_of, const u32 *__restrict__ work, u32 work_cap, const u32 *__restrict__ n_work,
+              u32 *__restrict__ to_bucket /* [work_cap] */, u32 *__restrict__ bin_count /* zeroed [SHK_ROUTE_BINS] */) {
+  typedef typename KeyOf<KW>::type K;
+  __shared__ u32 s_cnt[SHK_ROUTE_BINS];
+  const u32 nw = min(*n_work, work_cap);
+  if (blockIdx.x * blockDim.x >= nw) return;
+  for (u32 j = threadIdx.x; j < SHK_ROUTE_BINS; j += blockDim.x) s_cnt[j] = 0;
+  __syncthreads();
+  const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < nw) {
+    const u32 item = work[i], n = item >> 3, b = item & 7u;
+    K X = (K)node_lo[n];
+    if (KW == 2) X |= (K)((u128)node_hi[n] << 64);
+    int s_in;
+    const K Y = neighbour_key(X, t->k, (int)(b >> 2), b & 3u, s_in);
+    const u32 yb = minimizer_hash_of(Y, t->k) & (t->P - 1);
+    const bool look = yb != bucket_of[n] && t->peer[owner_of_bucket(yb, t->P, t->world)].n_nodes != 0;
+    to_bucket[i] = look ? yb : SHK_NONE;
+    if (look) atomicAdd(&s_cnt[route_bin(yb, t->P)], 1u);
+  }
+  __syncthreads();
+  for (u32 j = threadIdx.x; j < SHK_ROUTE_BINS; j += blockDim.x) if (s_cnt[j]) atomicAdd(bin_count + j, s_cnt[j]);
+}
+// R2 (one CTA of SHK_ROUTE_BINS threads): first position of every bin, the bins taken in rotated order — the one that
+// holds the first bucket of rank+1 comes first, this rank's own buckets last
+__global__ void __launch_bounds__(SHK_ROUTE_BINS)
+k_route_scan(const ShardTopo *__restrict__ t, const u32 *__restrict__ bin_count, u32 *__restrict__ bin_cursor, u32 *__restrict__ n_routed) {
+  __shared__ u32 s[SHK_ROUTE_BINS];
+  const u32 q = threadIdx.x;                                          // position in the rotated order
+  const u32 next = (t->rank + 1) % t->world;
+  const u32 first = route_bin((u32)(((u64)next * t->P) / t->world), t->P);
+  const u32 bin = (first + q) % SHK_ROUTE_BINS;
+  const u32 c = bin_count[bin];
+  s[q] = c;
+  __syncthreads();
+  for (u32 o = 1; o < SHK_ROUTE_BINS; o <<= 1) {
+    const u32 v = q >= o ? s[q - o] : 0u;
+    __syncthreads();
+    s[q] += v;
+    __syncthreads();
+  }
+  bin_cursor[bin] = s[q] - c;
+  if (q == SHK_ROUTE_BINS - 1) *n_routed = s[q];
+}
+// R3: the lookups in routed order (order[j] = position in the work list)
+__global__ void __launch_bounds__(256)
+k_route_scatter(const u32 *__restrict__ to_bucket, u32 P, u32 work_cap, const u32 *__restrict__ n_work,
+                u32 *__restrict__ bin_cursor, u32 *__restrict__ order) {
+  __shared__ u32 s_cnt[SHK_ROUTE_BINS], s_base[SHK_ROUTE_BINS];
+  const u32 nw = min(*n_work, work_cap);
+  if (blockIdx.x * blockDim.x >= nw) return;
+  for (u32 j = threadIdx.x; j < SHK_ROUTE_BINS; j += blockDim.x) s_cnt[j] = 0;
+  __syncthreads();
+  const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+  const u32 yb = i < nw ? to_bucket[i] : SHK_NONE;
+  u32 bin = 0, at = 0;
+  if (yb != SHK_NONE) { bin = route_bin(yb, P); at = atomicAdd(&s_cnt[bin], 1u); }
+  __syncthreads();
+  for (u32 j = threadIdx.x; j < SHK_ROUTE_BINS; j += blockDim.x) if (s_cnt[j]) s_base[j] = atomicAdd(bin_cursor + j, s_cnt[j]);
+  __syncthreads();
+  if (yb != SHK_NONE) order[s_base[bin] + at] = i;
+}
+// R4: the lookups themselves, a warp in lockstep
 template <int KW>
 __global__ void __launch_bounds__(256)
 k_build_edges_sharded_slow(const ShardTopo *__restrict__ t, const u64 *__restrict__ node_lo, const u64 *__restrict__ node_hi,
-                           const u32 *__restrict__ bucket_of, const u32 *__restrict__ work, u32 work_cap, const u32 *__restrict__ n_work,
-                           uint8_t *__restrict__ node_edges, u32 *__restrict__ nbr) {
+                           const u32 *__restrict__ work, const u32 *__restrict__ to_bucket, const u32 *__restrict__ order,
+                           const u32 *__restrict__ n_routed, uint8_t *__restrict__ node_edges, u32 *__restrict__ nbr) {
   typedef typename KeyOf<KW>::type K;
-  const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
-  const u32 nw = min(*n_work, work_cap);
-  if ((i & ~31u) >= nw) return;                           // whole warps leave together (the probes below run in lockstep)
-  const bool live = i < nw;
+  const u32 j = blockIdx.x * blockDim.x + threadIdx.x;
+  const u32 nr = *n_routed;
+  if ((j & ~31u) >= nr) return;                           // whole warps leave together (the probes below run in lockstep)
+  const bool live = j < nr;
+  const u32 i = live ? order[j] : 0u;
   const u32 item = live ? work[i] : 0u, n = item >> 3, b = item & 7u;
+  const u32 yb = live ? to_bucket[i] : 0u;
   K X = 0;
   if (live) { X = (K)node_lo[n]; if (KW == 2) X |= (K)((u128)node_hi[n] << 64); }
   int s_in;
   const K Y = neighbour_key(X, t->k, (int)(b >> 2), b & 3u, s_in);
-  const u32 yb = minimizer_hash_of(Y, t->k) & (t->P - 1);
   const u32 r = owner_of_bucket(yb, t->P, t->world);
   const PeerView pv = t->peer[r];
-  const bool look = live && yb != bucket_of[n] && pv.n_nodes != 0;   // (its own bucket was looked up already: no such node)
   NodeIndex ix{pv.slots, pv.off, pv.lo, pv.hi, t->P, t->k};
-  const u32 id = index_find_in_warp<KW>(ix, Y, yb, look);
+  const u32 id = index_find_in_warp<KW>(ix, Y, yb, live);
   if (id == SHK_NONE) return;
   atomicOr(reinterpret_cast<u32 *>(node_edges + (n & ~3u)), (1u << b) << (8u * (n & 3u)));
   nbr[2 * n + (b >> 2)] = ((t->node_off[r] + id) << 1) | (u32)s_in;

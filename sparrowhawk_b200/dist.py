@@ -272,9 +272,11 @@ def _sharded_graph(eng, group, blobs, counts, g_hist, g_inst, g_bases, used_mc, 
         # 3. K3' over the owned nodes; barrier "edges complete"
         if st == 0:
             eng.graph_edges()
-        _barrier(dev, group)
         if attempt == 0:
             mark("edges")
+        _barrier(dev, group)
+        if attempt == 0:
+            mark("edges_barrier")                    # (the wait for the slowest rank's K3' shows up here)
         # 4. K4' + local list ranking: one chain per stretch of a unitig inside this rank
         nch = eng.graph_chains() if st == 0 else -2
         chain_counts = [int(x) for x in _gather_host_ints([nch], dev, group)[:, 0]]     # (barrier "chain numbers complete")
