@@ -19,6 +19,23 @@ namespace shk {
 #ifndef SHK_CB_THREADS2
 #define SHK_CB_THREADS2 1024
 #endif
+// records a warp takes per grab on the staged decode (k > 31).  A k = 63 group is a few hundred long records
+// (about 10 k k-mer instances in ~ 25-k-mer runs): 32 per grab would leave most of the CTA's 32 warps without any
+#ifndef SHK_CB_GRAB2
+#define SHK_CB_GRAB2 8
+#endif
+// k > 31: identical super-k-mer records of a group are counted once, with their multiplicity (0: every record decoded)
+#ifndef SHK_CB_DEDUP2
+#define SHK_CB_DEDUP2 1
+#endif
+#define SHK_RT2_SLOTS 4096u        // index table of the staged records (u32 entries in the idle count array)
+#define SHK_RT2_MAXPROBE 64
+#ifndef SHK_CB_GUIDED
+#define SHK_CB_GUIDED 0
+#endif
+#ifndef SHK_CB_SPLIT2
+#define SHK_CB_SPLIT2 1
+#endif
 #define SHK_CB_MAXC 256           // record segments per group (planner splits larger groups)
 #define SHK_CB_MAXPROBE 96
 
@@ -37,7 +54,8 @@ template <int KW> __host__ __device__ constexpr size_t cb_smem_bytes() {
          + (size_t)CbCfg<KW>::WARPS * 32 * 16 * CbCfg<KW>::RECW    // record staging
          + (size_t)CbCfg<KW>::WARPS * 64 * 4                       // run-start bitmaps
          + SHK_NBINS * 4 + (SHK_CB_MAXC + 1) * 4 + 64
-         + 64 * 4;                                                  // record-length bins + cursors
+         + 64 * 4                                                   // record-length bins + cursors
+         + (KW == 2 ? (size_t)CbCfg<KW>::THREADS * 2 : 0);          // multiplicities of the staged records (k > 31)
 }
 
 // ---- shared-table insert ---------------------------------------------------
@@ -120,6 +138,30 @@ __device__ __forceinline__ bool smem_insert(U128Pair *keys, u32 *vals, int NS, u
     s = (s + 1 == (u32)NS) ? 0u : s + 1;
   }
   return false;
+}
+
+// claim halves of the two inserts above (slot or SHK_NONE), for callers that add the count after their warp has
+// re-converged (see smem_claim_at)
+__device__ __forceinline__ u32 smem_claim(u64 *keys, int NS, u64 key) {
+  const u32 s = __umulhi(slot_hash(key), (u32)NS);
+  return smem_claim_at(keys, NS, key, s, keys[s]);
+}
+__device__ __forceinline__ u32 smem_claim(U128Pair *keys, int NS, u128 key) {
+  u32 s = __umulhi(slot_hash(key), (u32)NS);
+  const u64 klo = (u64)key, khi = (u64)(key >> 64);
+  for (int probe = 0; probe < SHK_CB_MAXPROBE; ++probe) {
+    uint4 c4 = *reinterpret_cast<const uint4 *>(keys + s);
+    u64 lo = ((u64)c4.y << 32) | c4.x, hi = ((u64)c4.w << 32) | c4.z;
+    if (hi == SHK_EMPTY64) {
+      U128Pair expect{SHK_EMPTY64, SHK_EMPTY64}, want{klo, khi};
+      U128Pair old = atomicCAS(keys + s, expect, want);               // ATOMS.CAS.128
+      lo = old.lo; hi = old.hi;
+      if (hi == SHK_EMPTY64) { lo = klo; hi = khi; }
+    }
+    if (lo == klo && hi == khi) return s;
+    s = (s + 1 == (u32)NS) ? 0u : s + 1;
+  }
+  return SHK_NONE;
 }
 
 // ---- record decode ------------------------------------------------------------
@@ -211,6 +253,63 @@ __device__ __forceinline__ uint4 record_item(uint4 c, u32 j) {
   const u32 hl = (off > 0 || hasl) ? 1u : 0u, hr = (off + ne < n || hasr) ? 1u : 0u;
   c.x = (c.x & ~0xFFu) | ne | (j << 4) | (hl << 6) | (hr << 7);
   return c;
+}
+
+// ---- record-level de-duplication, k > 31 -----------------------------------------
+// A 32-byte record as four words, W[3] = the first 32 bases (left flank first) ... W[0] = the last bases and, in its low
+// byte, n | hasl << 6 | hasr << 7.  Canonical form as for k <= 31: the smaller of the payload and its reverse
+// complement, absent flanks and unused bits zeroed, the header rewritten for the strand that won.
+__device__ __forceinline__ void shl256(u64 (&W)[4], int sh) {          // W <<= sh, 0 <= sh < 256
+  const int q = sh >> 6, r = sh & 63;
+  u64 o[4];
+#pragma unroll
+  for (int i = 3; i >= 0; --i) {
+    u64 a = 0, b = 0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { if (j == i - q) a = W[j]; if (j == i - q - 1) b = W[j]; }
+    o[i] = r ? ((a << r) | (b >> (64 - r))) : a;
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) W[i] = o[i];
+}
+__device__ __forceinline__ void canon_record2(uint4 &ra, uint4 &rb, int k) {
+  u64 F[4] = {((u64)rb.y << 32) | rb.x, ((u64)rb.w << 32) | rb.z, ((u64)ra.y << 32) | ra.x, ((u64)ra.w << 32) | ra.z};
+  const u32 hd = (u32)F[0] & 0xFFu, n = hd & 63u, hasl = (hd >> 6) & 1u, hasr = (hd >> 7) & 1u;
+  const int len = (int)n + k + 1, sh = 256 - 2 * len;               // payload bases (<= 124), free bits below (>= 8)
+  const int lw = sh >> 6, lo = sh & 63;                               // the last payload base: bits lo, lo + 1 of word lw
+  // payload only
+#pragma unroll
+  for (int i = 0; i < 4; ++i) { if (i < lw) F[i] = 0; else if (i == lw) F[i] = F[i] >> lo << lo; }
+  u64 C[4] = {revcomp_word(F[3]), revcomp_word(F[2]), revcomp_word(F[1]), revcomp_word(F[0])};
+  shl256(C, sh);                                                      // its reverse complement, top aligned
+  const u64 top2 = 3ull << 62, last2 = 3ull << lo;
+  if (!hasl) {                                                        // an absent flank carries no information
+    F[3] &= ~top2;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) if (i == lw) C[i] &= ~last2;
+  }
+  if (!hasr) {
+    C[3] &= ~top2;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) if (i == lw) F[i] &= ~last2;
+  }
+  bool take_c = false, decided = false;
+#pragma unroll
+  for (int i = 3; i >= 0; --i) if (!decided && C[i] != F[i]) { take_c = C[i] < F[i]; decided = true; }
+  u64 O[4]; u32 hl, hr;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) O[i] = take_c ? C[i] : F[i];
+  if (take_c) { hl = hasr; hr = hasl; } else { hl = hasl; hr = hasr; }
+  O[0] |= (u64)(n | (hl << 6) | (hr << 7));
+  ra = make_uint4((u32)O[2], (u32)(O[2] >> 32), (u32)O[3], (u32)(O[3] >> 32));
+  rb = make_uint4((u32)O[0], (u32)(O[0] >> 32), (u32)O[1], (u32)(O[1] >> 32));
+}
+__device__ __forceinline__ u32 record_hash2(const uint4 &a, const uint4 &b) {
+  u32 h = a.x * 0x9E3779B1u ^ a.y * 0x85EBCA77u ^ a.z * 0xC2B2AE3Du ^ a.w * 0x27D4EB2Fu;
+  h = (h ^ (h >> 15)) * 0x2C1B3C6Du;
+  h ^= b.x * 0x165667B1u ^ b.y * 0xD3A2646Du ^ b.z * 0xFD7046C5u ^ b.w * 0xB55A4F09u;
+  h ^= h >> 15; h *= 0x2C1B3C6Du; h ^= h >> 13; h *= 0x297A2D39u; h ^= h >> 16;
+  return h;
 }
 
 // Self-planning mode (steady-state runs, group_start == null): CTAs take chunks of consecutive buckets (sized
@@ -501,8 +600,113 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
           key = nkey; e = ne; sl = nsl; cur = ncur;
         }
       }
+    } else if (KW == 2) {
+      // k > 31.  A group is a few hundred long records (about 10 k k-mers in runs of ~ 25): handing records to warps
+      // left most of the CTA's 32 warps idle or waiting (measured: a quarter of all warp samples at the barrier behind
+      // the decode, whatever the grab size).  So the CTA stages the records of the group TOGETHER (up to one per
+      // thread), scans their k-mer counts, and spreads the K-MERS evenly over all threads; k-mer number j finds its
+      // record by binary search in the prefix (consecutive lanes hit the same words: broadcasts).
+      u32 *pre = bitmaps;                                   // [THREADS + 1] k-mer prefix of the staged records
+      u32 *wsum = rbins;                                    // [WARPS] warp totals of the scan
+      unsigned short *wts = reinterpret_cast<unsigned short *>(rbins + 64);   // [THREADS] multiplicities of the staged records
+      for (u32 c0 = 0; c0 < total; c0 += (u32)THREADS) {
+        const u32 cn = min((u32)THREADS, total - c0);
+        u32 n = 0;
+        uint4 ra = make_uint4(0, 0, 0, 0), rb = ra;
+        if ((u32)tid < cn) {
+          const u32 f = c0 + (u32)tid;
+          u32 lo = 0, hi = snb;                             // segment with gpre[lo] <= f < gpre[lo+1]
+          while (hi - lo > 1) { u32 mid = (lo + hi) >> 1; if (gpre[mid] <= f) lo = mid; else hi = mid; }
+          const u64 sbase = seg_off ? seg_off[sb0 + lo] : (u64)(sb0 + lo) * rcap;
+          const uint4 *src = reinterpret_cast<const uint4 *>(recs + (sbase + (f - gpre[lo])));
+          ra = __ldcs(src); rb = __ldcs(src + 1);
+          if (SHK_CB_DEDUP2) canon_record2(ra, rb, k);
+          stage[2 * tid] = ra; stage[2 * tid + 1] = rb;
+          n = rb.x & 63u;
+        }
+        if (SHK_CB_DEDUP2 && c0 != 0) {
+          if ((u32)tid < cn) wts[tid] = 1;                  // (a later chunk of a very large group: the count array is in use)
+        } else if (SHK_CB_DEDUP2) {
+          // Identical records (same bases, same flanks, either strand) are counted once: the first of its kind in an
+          // index table stands for all of them, the others add to its multiplicity and contribute no k-mers.  Index
+          // and multiplicities live in the count array, which is idle and zero before the group's first k-mer goes in,
+          // and is handed back zero.
+          u32 *rt = vals, *mult = vals + SHK_RT2_SLOTS;
+          u32 myslot = SHK_NONE;
+          __syncthreads();                                  // every canonical record is staged
+          if ((u32)tid < cn) {
+            u32 sl = __umulhi(record_hash2(ra, rb), SHK_RT2_SLOTS);
+            for (int probe = 0; probe < SHK_RT2_MAXPROBE; ++probe) {
+              u32 e = rt[sl];
+              if (e == 0) { e = atomicCAS(&rt[sl], 0u, (u32)tid + 1u); if (e == 0) { myslot = sl; break; } }
+              const uint4 ga = stage[2 * (e - 1)], gb = stage[2 * (e - 1) + 1];
+              if (ga.x == ra.x && ga.y == ra.y && ga.z == ra.z && ga.w == ra.w &&
+                  gb.x == rb.x && gb.y == rb.y && gb.z == rb.z && gb.w == rb.w) {
+                atomicAdd(&mult[e - 1], 1u); n = 0; break;
+              }
+              sl = sl + 1 == SHK_RT2_SLOTS ? 0u : sl + 1;
+            }                                               // (no room in the probe window: stays a record of its own)
+          }
+          __syncthreads();
+          if ((u32)tid < cn) {
+            wts[tid] = (unsigned short)min(1u + mult[tid], 65535u);   // (counts saturate at 65535, S7)
+            mult[tid] = 0;
+            if (myslot != SHK_NONE) rt[myslot] = 0;
+          }
+        }
+        u32 incl = n;
+        for (int o = 1; o < 32; o <<= 1) { const u32 v = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += v; }
+        if (lane == 31) wsum[warp] = incl;
+        __syncthreads();
+        if (warp == 0) {
+          const u32 ws = lane < WARPS ? wsum[lane] : 0u;
+          u32 wi = ws;
+          for (int o = 1; o < 32; o <<= 1) { const u32 v = __shfl_up_sync(0xffffffffu, wi, o); if (lane >= o) wi += v; }
+          if (lane < WARPS) wsum[lane] = wi - ws;            // exclusive
+          if (lane == 31) pre[cn] = wi;                      // all k-mers of the chunk (WARPS == 32)
+        }
+        __syncthreads();
+        if ((u32)tid < cn) pre[tid] = wsum[warp] + incl - n;
+        __syncthreads();
+        // warp w takes the k-mers [w S, (w+1) S), S a multiple of 32: its lanes walk through the records in step, so
+        // the record of a k-mer is found by advancing from the one of the previous round (one binary search per warp;
+        // measured with a search per k-mer: a fifth of the kernel's instructions)
+        const u32 KT = pre[cn];
+        const u32 S = ((KT + (u32)THREADS - 1) / (u32)THREADS) * 32u;
+        u32 lo = 0;
+        {
+          const u32 j = min(warp * S + (u32)lane, KT ? KT - 1 : 0u);
+          u32 hi = cn;                                       // record with pre[lo] <= j < pre[lo+1]
+          while (hi - lo > 1) { const u32 mid = (lo + hi) >> 1; if (pre[mid] <= j) lo = mid; else hi = mid; }
+        }
+        for (u32 r0 = 0; r0 < S; r0 += 32) {                 // (every lane runs all rounds: the warp re-converges inside)
+          const u32 j = warp * S + r0 + (u32)lane;
+          K key = 0; u32 e = 0, at = SHK_NONE;
+          if (j < KT) {
+            while (pre[lo + 1] <= j) ++lo;                   // pre[cn] = KT > j: ends
+            const u32 i = j - pre[lo];
+            const u32 *rw = reinterpret_cast<const u32 *>(stage + 2 * (size_t)lo);
+            const u32 hd = rw[4], rn = hd & 63u, rl = (hd >> 6) & 1u, rr = (hd >> 7) & 1u;      // rb.x
+            K fwd; u32 a, b;
+            kmer_at(rw, (int)i, k, fwd, a, b);
+            const K rc = revcomp_key(fwd, k);
+            const bool hl = i > 0 || rl, hr = i + 1 < rn || rr;
+            if (fwd < rc) { key = fwd; e = (hr ? (1u << b) : 0u) | (hl ? (16u << a) : 0u); }
+            else { key = rc; e = (hl ? (1u << (a ^ 2u)) : 0u) | (hr ? (16u << (b ^ 2u)) : 0u); }
+            at = smem_claim(keys, NS, key);
+          }
+          __syncwarp();                  // the lanes left the probe loop at different times: add the counts together
+          if (j < KT) {
+            const u32 w = SHK_CB_DEDUP2 ? (u32)wts[lo] : 1u;
+            ndec += w;
+            if (at != SHK_NONE) slot_hit(vals + at, e, w);
+            else { table_insert(ovf, key, e, w, ovf_flag); nspill += w; }
+          }
+        }
+        if (c0 + (u32)THREADS < total) __syncthreads();     // the staging area is reused by the next chunk
+      }
     } else
-    for (;;) {
+    for (;;) {                                              // k <= 31 without the record table: a warp takes 32 records at a time
       u32 cbase = 0;
       if (lane == 0) cbase = atomicAdd(&misc[1], 32u);
       cbase = __shfl_sync(0xffffffffu, cbase, 0);
@@ -545,17 +749,22 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
         const u32 mr = __shfl_sync(0xffffffffu, meta, r & 31);
         const u32 w = DEDUP ? __shfl_sync(0xffffffffu, wgt, r & 31) : 1u;
         running += __popc(word);
+        K key = 0; u32 e = 0, at = SHK_NONE;
         if (t < T) {
           const u32 rn = mr & 0xFFu, rl = (mr >> 8) & 1u, rr = (mr >> 9) & 1u, i = t - (mr >> 16);
           K fwd; u32 a, b;
           kmer_at(reinterpret_cast<const u32 *>(wst + (size_t)(r & 31) * RECW), (int)i, k, fwd, a, b);
           const K rc = revcomp_key(fwd, k);
           const bool hl = i > 0 || rl, hr = i + 1 < rn || rr;
-          K key; u32 e;
           if (fwd < rc) { key = fwd; e = (hr ? (1u << b) : 0u) | (hl ? (16u << a) : 0u); }
           else { key = rc; e = (hl ? (1u << (a ^ 2u)) : 0u) | (hr ? (16u << (b ^ 2u)) : 0u); }
+          at = smem_claim(keys, NS, key);
+        }
+        __syncwarp();                    // the lanes left the probe loop at different times: add the counts together
+        if (t < T) {
           ndec += w;
-          if (!smem_insert(keys, vals, NS, key, e, w)) { table_insert(ovf, key, e, w, ovf_flag); nspill += w; }
+          if (at != SHK_NONE) slot_hit(vals + at, e, w);
+          else { table_insert(ovf, key, e, w, ovf_flag); nspill += w; }
         }
       }
       __syncwarp();
