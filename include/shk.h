@@ -393,6 +393,31 @@ shk_status shk_shard_graph_set_links(shk_asm *h, const void *d_from, const void 
 /* The host-side spectrum fit used by do_fit (docs/src/assembly.md:16). */
 int shk_fit_min_count(const uint64_t *histo /*[SHK_HISTO_BINS]*/, int fallback);
 
+/* ---- allocation-free entry point -----------------------------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ *
+ * The k-mer spectrum of a SMALL packed read set, with no handle and no allocation: every canonical k-mer of the
+ * stream (layout of shk_asm_preprocess_packed; d_bases / d_mask are DEVICE pointers to ceil(n_positions / 32) words
+ * each) is counted in an open-addressing table and the table is swept into the 500-bin spectrum — the same numbers
+ * shk_get_histogram / shk_get_stats report after shk_load_packed + shk_run on a handle.
+ *   d_out (device, SHK_NOALLOC_OUT_WORDS u64, written by the call): [0, SHK_HISTO_BINS) spectrum, [SHK_HISTO_BINS]
+ *   distinct k-mers, [+1] k-mer instances, [+2] 0 (non-zero: the table overflowed — cannot happen within the limit).
+ * The table lives in a fixed `static __device__` array inside the library (24 MiB, held by every GPU that loads the
+ * library until the process exits), so:
+ *   - n_positions > SHK_NOALLOC_MAX_POSITIONS, k even or outside 3..31 -> SHK_ERR_BAD_ARG, nothing queued;
+ *   - the call calls no cudaMalloc / cudaFree (or any allocating routine) and waits for nothing: clears, the count
+ *     kernel and the sweep are queued on `stream` (a cudaStream_t as void*, NULL = the default stream) of the CURRENT
+ *     device; the caller synchronises before reading d_out;
+ *   - every call on a device shares the one array and clears it first (it keeps the previous call's contents):
+ *     calls in stream order are independent, calls that OVERLAP on one GPU race — serialise them;
+ *   - the first call on a device takes the array's address (cudaGetSymbolAddress); make it outside a graph capture
+ *     (n_positions = 0 does only that and zeroes d_out). */
+#define SHK_NOALLOC_MAX_POSITIONS (1ull << 20)
+#define SHK_NOALLOC_OUT_WORDS (SHK_HISTO_BINS + 3)
+shk_status shk_spectrum_noalloc(const uint64_t *d_bases, const uint32_t *d_mask, uint64_t n_positions, int k,
+                                uint64_t *d_out, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

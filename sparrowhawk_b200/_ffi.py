@@ -111,6 +111,8 @@ SYMBOLS = {
     "shk_shard_graph_join": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_void_p]),
     "shk_shard_graph_cycle_info": (C.c_int, [_H, C.c_void_p]),
     "shk_shard_graph_set_links": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_uint64]),
+    # allocation-free spectrum of a small packed read set (fixed static device scratch; include/shk.h)
+    "shk_spectrum_noalloc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_void_p, C.c_void_p]),
 }
 
 _lib = None
