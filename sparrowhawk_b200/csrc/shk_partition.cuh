@@ -82,6 +82,12 @@ __device__ __forceinline__ u32 revcomp_m(u32 x, int m) {
 // An extra warp (threads 256..287) produces the hashes of the halo positions
 // and the A_J values of the block past the tile.
 #define SHK_PT_THREADS 288
+// resident CTAs per SM the register allocation is held to.  4 = 56 registers (156 bytes of spills) and 36 of 64 warp
+// slots; 3 = 72 registers, no spills, 27 warps: measured 1.33 ms -> 1.19 ms on config B going from 3 to 4 (the kernel
+// is issue-bound at 2.5 IPC: more warps to pick from beat a few local loads).  Five do not fit the shared memory.
+#ifndef SHK_PT_MINB
+#define SHK_PT_MINB 4
+#endif
 #define SHK_PT_WORDS 256
 #define SHK_PT_POS (SHK_PT_WORDS * 32)
 #define SHK_PT_TILE (SHK_PT_WORDS + 6)
@@ -148,7 +154,7 @@ __device__ __forceinline__ void window_min_pow2(const u32 *row, u32 (&R)[32]) {
 }
 
 template <int KW>
-__global__ void __launch_bounds__(SHK_PT_THREADS, 3)
+__global__ void __launch_bounds__(SHK_PT_THREADS, SHK_PT_MINB)
 k_minimizer_partition(const u64 *__restrict__ bases, const u32 *__restrict__ mask, u64 nwords /* of the whole stream */,
                       u64 word_begin /* first word of this launch (a multiple of SHK_PT_WORDS) */, int k, u32 P,
                       u32 rcap, typename RecOf<KW>::type *__restrict__ recs, u64 *__restrict__ bstat /* [P] records | kmers << 32 */,
