@@ -39,10 +39,17 @@ namespace shk {
 #define SHK_CB_MAXC 256           // record segments per group (planner splits larger groups)
 #define SHK_CB_MAXPROBE 96
 
+// resident CTAs per SM and table slots per CTA at k <= 31 (defaults: what fits 1024 threads and the shared memory)
+#ifndef SHK_CB_PER_SM1
+#define SHK_CB_PER_SM1 (1024 / SHK_CB_THREADS1)
+#endif
+#ifndef SHK_CB_NS1
+#define SHK_CB_NS1 (16384 / SHK_CB_PER_SM1)
+#endif
 template <int KW> struct CbCfg;
 template <> struct CbCfg<1> {
-  static const int THREADS = SHK_CB_THREADS1, PER_SM = 1024 / THREADS, WARPS = THREADS / 32;
-  static const int NS = 16384 / PER_SM; static const int KEYB = 8;  static const int RECW = 1;
+  static const int THREADS = SHK_CB_THREADS1, PER_SM = SHK_CB_PER_SM1, WARPS = THREADS / 32;
+  static const int NS = SHK_CB_NS1; static const int KEYB = 8;  static const int RECW = 1;
 };
 template <> struct CbCfg<2> {
   static const int THREADS = SHK_CB_THREADS2, PER_SM = 1024 / THREADS, WARPS = THREADS / 32;
@@ -200,7 +207,7 @@ __device__ __forceinline__ void kmer_at(const u32 *rw, int i, int k, u128 &fwd, 
 // instances vanish this way (31 % at 30x still 63 %); the result is identical
 // because a record's content fully determines its (canonical k-mer, edge) pairs and
 // those are strand-symmetric.
-#define SHK_RT_SLOTS (8192 / (1024 / SHK_CB_THREADS1))            // record-table slots (16 B key + 4 B count, time-shares the k-mer table's memory)
+#define SHK_RT_SLOTS (SHK_CB_NS1 / 2)            // record-table slots (16 B key + 4 B count, time-shares the k-mer table's memory)
 #define SHK_RT_MAXPROBE 32
 
 __device__ __forceinline__ uint4 canon_record(uint4 r, int k) {
@@ -335,17 +342,19 @@ struct CountOut {
   u64 *counters;              // [2] n_distinct, [4] spilled instances, [5] instances decoded
 };
 
-template <int KW, bool DEDUP>
+// KC != 0: k is the compile-time constant KC (see k_minimizer_partition)
+template <int KW, bool DEDUP, int KC>
 __global__ void __launch_bounds__(CbCfg<KW>::THREADS, CbCfg<KW>::PER_SM)
 k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__restrict__ bstat, u32 rcap,
                 const u64 *__restrict__ seg_off, const u32 *__restrict__ seg_cnt,
                 uint4 *__restrict__ uq_rec, u32 *__restrict__ uq_cnt, u32 uq_cap /* distinct-record list, per CTA */,
                 const u32 *__restrict__ group_start /* null: the CTAs cut their own groups (SelfPlan) */, u32 g_begin, u32 g_end,
-                SelfPlan sp, u32 *__restrict__ next_group, int k, int min_count, Table<KW> ovf, u32 *__restrict__ ovf_flag,
+                SelfPlan sp, u32 *__restrict__ next_group, int k_arg, int min_count, Table<KW> ovf, u32 *__restrict__ ovf_flag,
                 u32 *__restrict__ uq_flag /* set when a de-dup list is too small */, CountOut out,
                 const u32 *__restrict__ gate, u32 gate_want /* gate != null: run only if (*gate != 0) == gate_want — the plain and
                 the spill-aware launch are queued back to back and the device picks the one that fits what K1a did */) {
   if (gate && ((*gate != 0u) ? 1u : 0u) != gate_want) return;
+  const int k = KC ? KC : k_arg;
   typedef typename KeyOf<KW>::type K;
   typedef typename std::conditional<KW == 1, u64, U128Pair>::type SK;
   constexpr int NS = CbCfg<KW>::NS, RECW = CbCfg<KW>::RECW, THREADS = CbCfg<KW>::THREADS, WARPS = CbCfg<KW>::WARPS;

@@ -525,6 +525,12 @@ int launch_unitig_links_out(int kw, const uint64_t *slots, const uint32_t *off, 
 }
 
 // ---- two-pass counting (shk_partition.cuh / shk_count_smem.cuh) ----------------
+// k that K1a / K1b are also compiled for as a constant (0: none); the launchers pick that instantiation when the
+// run-time k matches.  31 is the UI default (AssemblyPage.vue:313) and the k of BASELINE configs A, B, D, E.
+#ifndef SHK_KSPEC
+#define SHK_KSPEC 31
+#endif
+#define SHK_KSPEC1 ((SHK_KSPEC) <= 31 ? (SHK_KSPEC) : 0)
 size_t record_bytes(int kw) { return kw == 1 ? 16 : 32; }
 int records_max_run(int kw, int k) { return rec_max_run(kw, k); }
 int count_table_slots(int kw) { return kw == 1 ? CbCfg<1>::NS : CbCfg<2>::NS; }
@@ -539,10 +545,12 @@ int launch_partition(int kw, const uint64_t *bases, const uint32_t *mask, uint64
   if (word_begin >= word_end) return 0;
   unsigned g = blocks_for(word_end - word_begin, SHK_PT_WORDS);
   const u32 scap = sp ? sp->cap : 0u; u32 *scur = sp ? sp->cursor : nullptr, *sbkt = sp ? sp->bucket : nullptr;
-  if (kw == 1)
-    k_minimizer_partition<1><<<g, SHK_PT_THREADS, 0, st>>>((const u64 *)bases, mask, nwords, word_begin, k, P, rcap, (uint4 *)recs, (u64 *)bstat, (u64 *)counters, scap, scur, sbkt);
-  else
-    k_minimizer_partition<2><<<g, SHK_PT_THREADS, 0, st>>>((const u64 *)bases, mask, nwords, word_begin, k, P, rcap, (Rec32 *)recs, (u64 *)bstat, (u64 *)counters, scap, scur, sbkt);
+#define SHK_PT_LAUNCH(KW_, KC_, REC_) \
+  k_minimizer_partition<KW_, KC_><<<g, SHK_PT_THREADS, 0, st>>>((const u64 *)bases, mask, nwords, word_begin, k, P, rcap, (REC_ *)recs, (u64 *)bstat, (u64 *)counters, scap, scur, sbkt)
+  if (kw == 1 && SHK_KSPEC1 && k == SHK_KSPEC1) SHK_PT_LAUNCH(1, SHK_KSPEC1, uint4);
+  else if (kw == 1) SHK_PT_LAUNCH(1, 0, uint4);
+  else SHK_PT_LAUNCH(2, 0, Rec32);
+#undef SHK_PT_LAUNCH
   return 1;
 }
 
@@ -625,9 +633,10 @@ int launch_count_buckets(int kw, const void *recs, const uint64_t *bstat, uint32
   static bool attr_done[SHK_MAX_DEVICES] = {false};     // function attributes belong to the device's context
   bool &attr_set = attr_done[current_device_slot()];
   if (!attr_set) {
-    cudaFuncSetAttribute(k_count_buckets<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cb_smem_bytes<1>());
-    cudaFuncSetAttribute(k_count_buckets<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cb_smem_bytes<1>());
-    cudaFuncSetAttribute(k_count_buckets<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cb_smem_bytes<2>());
+    cudaFuncSetAttribute(k_count_buckets<1, false, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cb_smem_bytes<1>());
+    cudaFuncSetAttribute(k_count_buckets<1, true, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cb_smem_bytes<1>());
+    cudaFuncSetAttribute(k_count_buckets<1, true, SHK_KSPEC1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cb_smem_bytes<1>());
+    cudaFuncSetAttribute(k_count_buckets<2, false, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cb_smem_bytes<2>());
     attr_set = true;
   }
   unsigned grid = (unsigned)count_ctas(kw);
@@ -635,15 +644,14 @@ int launch_count_buckets(int kw, const void *recs, const uint64_t *bstat, uint32
   u32 mp = (u32)(ovf_cap < 4096 ? ovf_cap : 4096);
   CountOut out{(u64 *)histo, (u64 *)node_lo, (u64 *)node_hi, node_count, node_raw, node_cap, n_nodes, (u64 *)counters};
   // record-level de-duplication needs the per-CTA list of distinct records (k <= 31 only for now)
-  if (kw == 1 && uq_rec && uq_cap)
-    k_count_buckets<1, true><<<grid, CbCfg<1>::THREADS, cb_smem_bytes<1>(), st>>>((const uint4 *)recs, (const u64 *)bstat, rcap, (const u64 *)seg_off, seg_cnt,
-        (uint4 *)uq_rec, uq_cnt, uq_cap, group_start, g_begin, g_end, sp, next_group, k, min_count, Table<1>{(Slot1 *)ovf_slots, ovf_cap, mp}, ovf_flag, uq_flag, out, gate, gate_want);
-  else if (kw == 1)
-    k_count_buckets<1, false><<<grid, CbCfg<1>::THREADS, cb_smem_bytes<1>(), st>>>((const uint4 *)recs, (const u64 *)bstat, rcap, (const u64 *)seg_off, seg_cnt,
-        nullptr, nullptr, 0, group_start, g_begin, g_end, sp, next_group, k, min_count, Table<1>{(Slot1 *)ovf_slots, ovf_cap, mp}, ovf_flag, uq_flag, out, gate, gate_want);
-  else
-    k_count_buckets<2, false><<<grid, CbCfg<2>::THREADS, cb_smem_bytes<2>(), st>>>((const Rec32 *)recs, (const u64 *)bstat, rcap, (const u64 *)seg_off, seg_cnt,
-        nullptr, nullptr, 0, group_start, g_begin, g_end, sp, next_group, k, min_count, Table<2>{(Slot2 *)ovf_slots, ovf_cap, mp}, ovf_flag, uq_flag, out, gate, gate_want);
+#define SHK_CB_LAUNCH(KW_, DD_, KC_, REC_, UQR_, UQC_, UQN_, SLOT_) \
+  k_count_buckets<KW_, DD_, KC_><<<grid, CbCfg<KW_>::THREADS, cb_smem_bytes<KW_>(), st>>>((const REC_ *)recs, (const u64 *)bstat, rcap, (const u64 *)seg_off, seg_cnt, \
+      UQR_, UQC_, UQN_, group_start, g_begin, g_end, sp, next_group, k, min_count, Table<KW_>{(SLOT_ *)ovf_slots, ovf_cap, mp}, ovf_flag, uq_flag, out, gate, gate_want)
+  if (kw == 1 && uq_rec && uq_cap && SHK_KSPEC1 && k == SHK_KSPEC1) SHK_CB_LAUNCH(1, true, SHK_KSPEC1, uint4, (uint4 *)uq_rec, uq_cnt, uq_cap, Slot1);
+  else if (kw == 1 && uq_rec && uq_cap) SHK_CB_LAUNCH(1, true, 0, uint4, (uint4 *)uq_rec, uq_cnt, uq_cap, Slot1);
+  else if (kw == 1) SHK_CB_LAUNCH(1, false, 0, uint4, nullptr, nullptr, 0, Slot1);
+  else SHK_CB_LAUNCH(2, false, 0, Rec32, nullptr, nullptr, 0, Slot2);
+#undef SHK_CB_LAUNCH
   return 1;
 }
 

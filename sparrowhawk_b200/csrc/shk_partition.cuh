@@ -153,10 +153,12 @@ __device__ __forceinline__ void window_min_pow2(const u32 *row, u32 (&R)[32]) {
   for (int i = 0; i < 32; ++i) R[i] = X[i];
 }
 
-template <int KW>
+// KC != 0: k is the compile-time constant KC (the launcher picks that instantiation when the run-time k matches):
+// window length, doubling depth and every shift by a multiple of k fold into immediates.
+template <int KW, int KC>
 __global__ void __launch_bounds__(SHK_PT_THREADS, SHK_PT_MINB)
 k_minimizer_partition(const u64 *__restrict__ bases, const u32 *__restrict__ mask, u64 nwords /* of the whole stream */,
-                      u64 word_begin /* first word of this launch (a multiple of SHK_PT_WORDS) */, int k, u32 P,
+                      u64 word_begin /* first word of this launch (a multiple of SHK_PT_WORDS) */, int k_arg, u32 P,
                       u32 rcap, typename RecOf<KW>::type *__restrict__ recs, u64 *__restrict__ bstat /* [P] records | kmers << 32 */,
                       u64 *__restrict__ counters /* [1] n_instances */,
                       u32 spill_cap, u32 *__restrict__ spill_cursor, u32 *__restrict__ spill_bkt /* spill area: see below */) {
@@ -167,6 +169,7 @@ k_minimizer_partition(const u64 *__restrict__ bases, const u32 *__restrict__ mas
   __shared__ u32 lastb[SHK_PT_WORDS];
   __shared__ u32 desc[SHK_PT_DESC];
   __shared__ u32 wsum[SHK_PT_THREADS / 32 + 1];
+  const int k = KC ? KC : k_arg;
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   const u64 w0 = word_begin + (u64)blockIdx.x * SHK_PT_WORDS;
   // tile index i holds stream word w0 - 1 + i
@@ -180,8 +183,7 @@ k_minimizer_partition(const u64 *__restrict__ bases, const u32 *__restrict__ mas
   __syncthreads();
   const int m = minimizer_len(k), wlen = k - m + 1, nmax = rec_max_run(KW, k);
   const u32 mmask = (m == 16) ? 0xFFFFFFFFu : ((1u << (2 * m)) - 1);
-  int J = 1;
-  while (2 * J <= wlen) J *= 2;
+  const int J = wlen >= 32 ? 32 : wlen >= 16 ? 16 : wlen >= 8 ? 8 : wlen >= 4 ? 4 : wlen >= 2 ? 2 : 1;   // largest power of two <= wlen (<= 53)
   const int d = wlen - J;
   u32 *row = hs + t * SHK_PT_ROW;                     // t <= 256 only
 
