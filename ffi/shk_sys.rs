@@ -71,6 +71,8 @@ pub struct shk_stats {
     pub device_planned: u32,
     pub host_qual_bits: u32,
     pub n_spilled_records: u64,
+    pub load_slices: u32,
+    pub host_packed_slices: u32,
 }
 
 /// what shk_shard_graph_join reports (include/shk.h)

@@ -155,6 +155,9 @@ typedef struct shk_stats {
   uint32_t host_qual_bits;     /* last load: 0 = the quality bytes crossed the link; else 1 + microseconds the calling
                                 * thread waited for the quality bits taken on the host (1 bit per position crossed) */
   uint64_t n_spilled_records;  /* super-k-mer records that found their bucket's region full and went through the spill area */
+  uint32_t load_slices;        /* last load: slices the host->device copy was cut into (0: one plain copy) */
+  uint32_t host_packed_slices; /* ... of which the host cores packed to 2 bits + validity bit themselves (hybrid load:
+                                * 0.375 bytes per position crossed the link for those, no K0 on the device) */
 } shk_stats;
 
 /* Use `stream` (a cudaStream_t passed as void*) for all work of this handle;

@@ -37,6 +37,7 @@ class ShkStats(C.Structure):
         ("ms_pack", C.c_float), ("ms_count", C.c_float), ("ms_filter", C.c_float), ("ms_graph", C.c_float),
         ("ms_extract", C.c_float), ("ms_count_kernel", C.c_float), ("n_spilled", C.c_uint64), ("n_records", C.c_uint64),
         ("device_planned", C.c_uint32), ("host_qual_bits", C.c_uint32), ("n_spilled_records", C.c_uint64),
+        ("load_slices", C.c_uint32), ("host_packed_slices", C.c_uint32),
     ]
 
 

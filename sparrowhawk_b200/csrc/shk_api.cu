@@ -344,6 +344,7 @@ static shk_status load_reads_overlapped(shk_asm *h, const uint8_t *seq, const ui
     const double raw_ms = (double)n / 50e6;
     if (raw_ms > 1.0 && pack_wait_ms > 1.6 * raw_ms && !getenv("SHK_QPACK")) h->qpack_ok = false;   // (small loads say nothing)
     h->st.host_qual_bits = 1u + (uint32_t)(pack_wait_ms * 1000.0);
+    h->st.load_slices = (uint32_t)S;
   }
   for (int i = 0; i < S; ++i) if ((uint64_t)(i + 1) * slice >= n) { k1a(i); break; }
   SHK_CUDA(cudaGetLastError());
@@ -353,14 +354,20 @@ static shk_status load_reads_overlapped(shk_asm *h, const uint8_t *seq, const ui
   return SHK_OK;
 }
 
+static shk_status load_reads_hybrid(shk_asm *h, const uint8_t *seq, const uint8_t *qual, size_t n, bool cut);
+static bool hpack_usable(const shk_asm *h) {
+  const char *e = getenv("SHK_HPACK");                     // 0 = never (read per call: tests flip it)
+  return qpack_usable(h) && !(e && e[0] == '0');
+}
 static shk_status load_reads_host(shk_asm *h, const uint8_t *seq, const uint8_t *qual, size_t n, int append) {
   SHK_TRY(require_device(h));
   if (!seq && n) { set_error("seq is null"); return SHK_ERR_BAD_ARG; }
   h->partition_done = false;
-  h->st.host_qual_bits = 0;
+  h->st.host_qual_bits = 0; h->st.load_slices = 0; h->st.host_packed_slices = 0;
   if (!append && qual && n >= h->overlap_min) {
     const bool cut = fast_ready_for(h, n);
     if (cut) SHK_TRY(fast_params(h, n));
+    if (hpack_usable(h)) return load_reads_hybrid(h, seq, qual, n, cut);
     if (cut || qpack_usable(h)) return load_reads_overlapped(h, seq, qual, n, cut);
   }
   SHK_CUDA(cudaEventRecord(h->ev[0], h->stream));
@@ -441,6 +448,184 @@ static void pack_range(const uint8_t *seq, const uint8_t *qual, uint64_t w0, uin
   uint64_t nb = 0;
   for (uint64_t w = w0; w < w1; ++w) { uint64_t bw; uint32_t mw; pack_word_scalar(seq, qual, w * 32, n, min_qual, bw, mw, nb); bases[w] = bw; mask[w] = mw; }
   *n_bases = nb;
+}
+
+// ---- hybrid load: the host cores pack what they can while the link carries the rest ------------------------------
+// The end-to-end call is bound by the host->device link.  load_reads_overlapped already takes the quality test on
+// the host (1.125 bytes per position cross the link instead of 2); here the host cores ALSO pack whole slices
+// (pack_range: 0.375 bytes per position, no K0 on the device) — as many as they manage while the link is busy with
+// the others.  The stream is cut into 16 slices.  The link takes slices from the FRONT as ASCII bases + host-taken
+// quality bits; the workers keep the quality bits a few slices ahead of the link and spend the rest of their time
+// packing slices from the BACK.  Nothing is decided in advance: when the two fronts meet the load is complete, so a
+// host with few or slow cores simply packs fewer slices (none: this is load_reads_overlapped).  K0 runs per ASCII
+// slice, K1a of slice i as soon as slices i and i + 1 (its halo) are on the device, in whatever order they arrive.
+static shk_status load_reads_hybrid(shk_asm *h, const uint8_t *seq, const uint8_t *qual, size_t n, bool cut) {
+  const int S = 16;
+  int LOOKAHEAD = 3;                                                  // quality bits are kept this many slices ahead of the link
+  if (const char *e = getenv("SHK_HPACK_LOOKAHEAD")) LOOKAHEAD = std::max(0, atoi(e));   // (0: the host packs its full half — tests)
+  const uint64_t tile_pos = (uint64_t)partition_tile_words() * 32;
+  const uint64_t slice = ((n + S - 1) / S + tile_pos - 1) / tile_pos * tile_pos;       // positions per slice, whole K1a tiles
+  const int NS = (int)((n + slice - 1) / slice);                                       // slices in use (<= S)
+  if (!h->copy_stream) {
+    SHK_CUDA(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+    for (auto &e : h->copy_ev) SHK_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  }
+  const uint64_t total = (n + 31) / 32;
+  const int hp_first = NS / 2;                                       // the host packs slices hp_first .. NS-1 at most
+  const uint64_t hp_w0 = (uint64_t)hp_first * slice / 32, hp_words = total - std::min(total, hp_w0);
+  // pinned staging for the packed slices; without it (host memory is short) the load goes the plain overlapped way
+  if (h->hpack_pin.ensure_host(hp_words * 12 + 64) != SHK_OK) return load_reads_overlapped(h, seq, qual, n, cut);
+  SHK_TRY(h->qbits_pin.ensure_host((total + 8) * 4)); SHK_TRY(h->qbits_dev.ensure((total + 8) * 4));
+  SHK_CUDA(cudaEventRecord(h->ev[0], h->stream));
+  SHK_TRY(h->ascii_seq.ensure(n + 64));
+  SHK_TRY(h->bases.ensure((total + 5) * 8)); SHK_TRY(h->mask.ensure((total + 5) * 4));
+  uint64_t *b = h->bases.as<uint64_t>() + 1;
+  uint32_t *m = h->mask.as<uint32_t>() + 1;
+  SHK_CUDA(cudaMemsetAsync(h->bases.p, 0, 8, h->stream));
+  SHK_CUDA(cudaMemsetAsync(h->mask.p, 0, 4, h->stream));
+  SHK_CUDA(cudaMemsetAsync(d_counters(h) + 3, 0, 8, h->stream));
+  SHK_CUDA(cudaMemsetAsync(b + total, 0, 4 * 8, h->stream));
+  SHK_CUDA(cudaMemsetAsync(m + total, 0, 4 * 4, h->stream));
+  h->nwords = total; h->n_positions = n;
+  if (cut) SHK_TRY(fast_prologue(h));
+  SHK_CUDA(cudaEventRecord(h->copy_ev[S], h->stream));
+  SHK_CUDA(cudaStreamWaitEvent(h->copy_stream, h->copy_ev[S], 0));
+  uint8_t *dseq = h->ascii_seq.as<uint8_t>();
+  uint32_t *hq = (uint32_t *)h->qbits_pin.p, *dq = h->qbits_dev.as<uint32_t>();
+  uint64_t *hpb = (uint64_t *)h->hpack_pin.p;
+  uint32_t *hpm = (uint32_t *)(hpb + hp_words);
+
+  // ---- workers: chunks of the current front job (quality bits) or back job (pack), handed out under a mutex ----
+  const uint64_t CH = 1ull << 18;                                      // positions per chunk (a multiple of 32)
+  struct Job { int slice = -1; uint64_t next = 0, end = 0; };
+  std::mutex mu;
+  Job jf, jb;
+  int front_next = 0, back_next = NS, link_done = 0;                  // (under mu)
+  std::atomic<int> mode[S], remaining[S];                             // 0 unclaimed, 1 ASCII + quality bits, 2 packed
+  for (int i = 0; i < S; ++i) { mode[i].store(0, std::memory_order_relaxed); remaining[i].store(0, std::memory_order_relaxed); }
+  std::atomic<uint64_t> host_bases{0};
+  auto start_job = [&](Job &j, int sl, int md) {                      // (under mu)
+    const uint64_t off = (uint64_t)sl * slice, end = std::min<uint64_t>(n, off + slice);
+    j.slice = sl; j.next = off; j.end = end;
+    remaining[sl].store((int)((end - off + CH - 1) / CH), std::memory_order_relaxed);
+    mode[sl].store(md, std::memory_order_release);
+  };
+  const unsigned hw = std::thread::hardware_concurrency();
+  unsigned T = std::min<unsigned>(std::max(1u, hw > 4 ? hw - 2 : hw), 16u);
+  if (const char *e = getenv("LOCAL_WORLD_SIZE")) {                   // several ranks share this host's cores (torchrun)
+    const int lws = atoi(e);
+    if (lws > 1) T = std::max(1u, std::min(T, (hw > 4 ? hw - 2 : hw) / (unsigned)lws));
+  }
+  if (const char *e = getenv("SHK_QPACK_THREADS")) T = (unsigned)std::max(1, atoi(e));
+  const int mq = h->p.min_qual;
+  std::vector<std::thread> workers;
+  for (unsigned t = 0; t < T; ++t)
+    workers.emplace_back([&, mq] {
+      for (;;) {
+        int md = 0; uint64_t p0 = 0, p1 = 0; int sl = -1;
+        {
+          std::lock_guard<std::mutex> lk(mu);
+          Job *j = nullptr;
+          if (jf.slice >= 0 && jf.next < jf.end) j = &jf;
+          else if (front_next < back_next && front_next - link_done < LOOKAHEAD) { start_job(jf, front_next++, 1); j = &jf; }
+          else if (jb.slice >= 0 && jb.next < jb.end) j = &jb;
+          else if (back_next - 1 >= front_next && back_next - 1 >= hp_first && back_next - 1 > 0) { start_job(jb, --back_next, 2); j = &jb; }
+          else if (front_next < back_next) { start_job(jf, front_next++, 1); j = &jf; }
+          else return;                                                 // every slice is claimed and both jobs are handed out
+          sl = j->slice; md = j == &jf ? 1 : 2;
+          p0 = j->next; p1 = std::min(j->end, p0 + CH); j->next = p1;
+        }
+        if (md == 1) qual_bits_range(qual, p0, p1, n, mq, hq + p0 / 32);
+        else {
+          uint64_t nb = 0;
+          pack_range(seq, qual, p0 / 32, (p1 + 31) / 32, n, mq, hpb - hp_w0, hpm - hp_w0, &nb);
+          host_bases.fetch_add(nb, std::memory_order_relaxed);
+        }
+        remaining[sl].fetch_sub(1, std::memory_order_release);
+      }
+    });
+  struct Joiner { std::vector<std::thread> &w; ~Joiner() { for (auto &t : w) if (t.joinable()) t.join(); } } joiner{workers};
+
+  // ---- the calling thread: queue every slice's copy as soon as the slice is ready; K0 / K1a behind the copies ----
+  bool arrived[S + 1] = {false}, cut_done[S] = {false};
+  bool first_k1a = true, first_k0 = true;
+  auto k1a = [&](int i) {
+    const uint64_t wb = (uint64_t)i * slice / 32, we = std::min<uint64_t>(total, (uint64_t)(i + 1) * slice / 32);
+    cut_done[i] = true;
+    if (wb >= we || !cut) return;
+    if (first_k1a) { cudaEventRecord(h->ev[8], h->stream); first_k1a = false; }
+    const SpillArgs sa = spill_args(h);
+    h->st.gpu_launches += launch_partition(h->kw, b, m, total, h->p.k, h->P, h->rcap, h->skrecs.p, h->bfill.as<uint64_t>(),
+                                           d_counters(h), h->stream, wb, we, &sa);
+  };
+  auto arrive = [&](int x, bool packed) -> shk_status {              // slice x's copy has just been queued on the copy stream
+    const uint64_t off = (uint64_t)x * slice, len = std::min<uint64_t>(slice, n - off);
+    SHK_CUDA(cudaEventRecord(h->copy_ev[x], h->copy_stream));
+    SHK_CUDA(cudaStreamWaitEvent(h->stream, h->copy_ev[x], 0));
+    if (!packed)
+      h->st.gpu_launches += launch_pack_reads(dseq + off, nullptr, len, (len + 31) / 32, h->p.min_qual, b + off / 32, m + off / 32,
+                                              d_counters(h) + 3, h->stream, dq + off / 32);
+    if (first_k0) { SHK_CUDA(cudaEventRecord(h->ev[1], h->stream)); first_k0 = false; }
+    arrived[x] = true;
+    for (int y = x - 1; y <= x + 1; ++y)                              // (K1a of slice y reads the last word of slice y - 1 and into slice y + 1)
+      if (y >= 0 && y < NS && arrived[y] && !cut_done[y] && (y == 0 || arrived[y - 1]) && (y == NS - 1 || arrived[y + 1])) k1a(y);
+    return SHK_OK;
+  };
+  int sent_front = 0, sent_back = NS, done_q = 0;                     // ASCII slices [0, sent_front) and packed slices [sent_back, NS) are queued
+  double wait_ms = 0;
+  shk_status st = SHK_OK;
+  while (sent_front < sent_back && st == SHK_OK) {
+    bool progress = false;
+    while (done_q < sent_front && cudaEventQuery(h->copy_ev[done_q]) == cudaSuccess) ++done_q;
+    { std::lock_guard<std::mutex> lk(mu); link_done = done_q; }
+    const int f = sent_front, bk = sent_back - 1;
+    if (mode[f].load(std::memory_order_acquire) == 1 && remaining[f].load(std::memory_order_acquire) == 0) {
+      const uint64_t off = (uint64_t)f * slice, len = std::min<uint64_t>(slice, n - off);
+      st = SHK_OK;
+      if (cudaMemcpyAsync(dseq + off, seq + off, len, cudaMemcpyHostToDevice, h->copy_stream) != cudaSuccess ||
+          cudaMemcpyAsync(dq + off / 32, hq + off / 32, (len + 31) / 32 * 4, cudaMemcpyHostToDevice, h->copy_stream) != cudaSuccess) {
+        st = cuda_fail(cudaGetLastError(), "hybrid load: copy of an ASCII slice");
+        break;
+      }
+      st = arrive(f, false);
+      ++sent_front; progress = true;
+    }
+    if (st == SHK_OK && sent_front < sent_back && mode[bk].load(std::memory_order_acquire) == 2 &&
+        remaining[bk].load(std::memory_order_acquire) == 0) {
+      const uint64_t w0 = (uint64_t)bk * slice / 32, w1 = std::min<uint64_t>(total, (uint64_t)(bk + 1) * slice / 32);
+      if (cudaMemcpyAsync(b + w0, hpb + (w0 - hp_w0), (w1 - w0) * 8, cudaMemcpyHostToDevice, h->copy_stream) != cudaSuccess ||
+          cudaMemcpyAsync(m + w0, hpm + (w0 - hp_w0), (w1 - w0) * 4, cudaMemcpyHostToDevice, h->copy_stream) != cudaSuccess) {
+        st = cuda_fail(cudaGetLastError(), "hybrid load: copy of a packed slice");
+        break;
+      }
+      st = arrive(bk, true);
+      --sent_back; progress = true;
+    }
+    if (!progress) {
+      // nothing ready: if the link has run dry as well, this is time the host cores cost (the speed check below)
+      const double t0 = now_ms();
+      std::this_thread::sleep_for(std::chrono::microseconds(20));
+      if (done_q == sent_front) wait_ms += now_ms() - t0;
+    }
+  }
+  if (st != SHK_OK) {
+    { std::lock_guard<std::mutex> lk(mu); front_next = back_next = 0; jf.next = jf.end; jb.next = jb.end; }   // the workers leave
+    return st;
+  }
+  for (auto &t : workers) t.join();
+  workers.clear();
+  h->st.gpu_launches += launch_add_u64(d_counters(h) + 3, host_bases.load(), h->stream);   // bases of the slices K0 never saw
+  const double raw_ms = (double)n / 50e6;
+  if (raw_ms > 1.0 && wait_ms > 1.6 * raw_ms && !getenv("SHK_QPACK")) h->qpack_ok = false;   // (see load_reads_overlapped)
+  h->st.host_qual_bits = 1u + (uint32_t)(wait_ms * 1000.0);
+  h->st.load_slices = (uint32_t)NS; h->st.host_packed_slices = (uint32_t)(NS - sent_back);
+  if (getenv("SHK_DEBUG"))
+    fprintf(stderr, "[shk] hybrid load: %d of %d slices packed by %u host threads, link idle %.2f ms\n", NS - sent_back, NS, T, wait_ms);
+  SHK_CUDA(cudaGetLastError());
+  if (cut) SHK_CUDA(cudaEventRecord(h->ev[9], h->stream));
+  h->counted = h->filtered = h->graphed = false;
+  h->partition_done = cut;
+  return SHK_OK;
 }
 
 // Sliced host->device copy of packed reads on the copy stream; on a handle that takes the K1a -> K1b path (cut), K1a

@@ -555,7 +555,7 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
       total = min(misc[6], uq_cap);
     }
     // ---- decode + insert: a warp grabs 32 records at a time (dynamic, so no warp idles at the tail) ----
-    if (DEDUP && KW == 1) {
+    if constexpr (DEDUP && KW == 1) {
       // one distinct record per lane, k-mers rolled out of registers (no re-extraction, no staging)
       const u64 km = kmask_of(k, (u64)0);
       for (;;) {
@@ -609,7 +609,7 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
           key = nkey; e = ne; sl = nsl; cur = ncur;
         }
       }
-    } else if (KW == 2) {
+    } else if constexpr (KW == 2) {
       // k > 31.  A group is a few hundred long records (about 10 k k-mers in runs of ~ 25): handing records to warps
       // left most of the CTA's 32 warps idle or waiting (measured: a quarter of all warp samples at the barrier behind
       // the decode, whatever the grab size).  So the CTA stages the records of the group TOGETHER (up to one per

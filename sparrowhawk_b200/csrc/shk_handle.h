@@ -96,7 +96,7 @@ struct shk_asm {
   cudaStream_t own_stream = nullptr, stream = nullptr;
   cudaEvent_t ev[12] = {};
   cudaStream_t copy_stream = nullptr;  // host->device slices of the overlapped load
-  cudaEvent_t copy_ev[9] = {};
+  cudaEvent_t copy_ev[18] = {};           // one per slice (8 or 16) + one "everything queued so far"
   uint64_t overlap_min = 32u << 20;    // smallest load (bytes per stream) worth slicing (SHK_OVERLAP_MIN overrides)
   bool partition_done = false;         // the resident reads are already cut into records (overlapped load)
   shk_progress_fn cb = nullptr;
@@ -110,6 +110,7 @@ struct shk_asm {
   shk::DevBuf skrecs, bfill /* u32 fill[P] | u32 kcount[P] */, groups, ovf;
   shk::PinBuf hoff /* shard_partition: dense send offsets */, hseg /* shard_count: segment offsets + counts */;
   shk::PinBuf qbits_pin /* overlapped load: quality bits taken on the host */;
+  shk::PinBuf hpack_pin /* hybrid load: the slices the host cores packed (2-bit words, then validity words) */;
   bool qpack_ok = true;                        // host cores keep ahead of the link (checked on every overlapped load)
   shk::PinBuf hfill2 /* shard_count_device falling back: the received fills on the host */;
   shk::PinBuf hsend /* shard_partition: records per owner rank + largest fill, from the device-side send plan */;

@@ -357,6 +357,13 @@ int launch_pack_reads(const uint8_t *seq, const uint8_t *qual, uint64_t n, uint6
   return 1;
 }
 
+__global__ void k_add_u64(u64 *p, u64 v) { *p += v; }
+int launch_add_u64(uint64_t *p, uint64_t v, cudaStream_t st) {
+  if (!v) return 0;
+  k_add_u64<<<1, 1, 0, st>>>((u64 *)p, (u64)v);
+  return 1;
+}
+
 __global__ void __launch_bounds__(256) k_table_clear1(Slot1 *s, u64 cap) {
   u64 stride = (u64)gridDim.x * blockDim.x;
   const uint4 v = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0u, 0u);
@@ -531,6 +538,10 @@ int launch_unitig_links_out(int kw, const uint64_t *slots, const uint32_t *off, 
 #define SHK_KSPEC 31
 #endif
 #define SHK_KSPEC1 ((SHK_KSPEC) <= 31 ? (SHK_KSPEC) : 0)
+// the same for the wide keys (31 < k <= 63): 63 is BASELINE config C
+#ifndef SHK_KSPEC2
+#define SHK_KSPEC2 63
+#endif
 size_t record_bytes(int kw) { return kw == 1 ? 16 : 32; }
 int records_max_run(int kw, int k) { return rec_max_run(kw, k); }
 int count_table_slots(int kw) { return kw == 1 ? CbCfg<1>::NS : CbCfg<2>::NS; }
@@ -547,8 +558,9 @@ int launch_partition(int kw, const uint64_t *bases, const uint32_t *mask, uint64
   const u32 scap = sp ? sp->cap : 0u; u32 *scur = sp ? sp->cursor : nullptr, *sbkt = sp ? sp->bucket : nullptr;
 #define SHK_PT_LAUNCH(KW_, KC_, REC_) \
   k_minimizer_partition<KW_, KC_><<<g, SHK_PT_THREADS, 0, st>>>((const u64 *)bases, mask, nwords, word_begin, k, P, rcap, (REC_ *)recs, (u64 *)bstat, (u64 *)counters, scap, scur, sbkt)
-  if (kw == 1 && SHK_KSPEC1 && k == SHK_KSPEC1) SHK_PT_LAUNCH(1, SHK_KSPEC1, uint4);
+  if (kw == 1 && SHK_KSPEC1 != 0 && k == SHK_KSPEC1) SHK_PT_LAUNCH(1, SHK_KSPEC1, uint4);
   else if (kw == 1) SHK_PT_LAUNCH(1, 0, uint4);
+  else if (SHK_KSPEC2 != 0 && k == SHK_KSPEC2) SHK_PT_LAUNCH(2, SHK_KSPEC2, Rec32);
   else SHK_PT_LAUNCH(2, 0, Rec32);
 #undef SHK_PT_LAUNCH
   return 1;
@@ -637,6 +649,7 @@ int launch_count_buckets(int kw, const void *recs, const uint64_t *bstat, uint32
     cudaFuncSetAttribute(k_count_buckets<1, true, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cb_smem_bytes<1>());
     cudaFuncSetAttribute(k_count_buckets<1, true, SHK_KSPEC1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cb_smem_bytes<1>());
     cudaFuncSetAttribute(k_count_buckets<2, false, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cb_smem_bytes<2>());
+    cudaFuncSetAttribute(k_count_buckets<2, false, SHK_KSPEC2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cb_smem_bytes<2>());
     attr_set = true;
   }
   unsigned grid = (unsigned)count_ctas(kw);
@@ -647,9 +660,10 @@ int launch_count_buckets(int kw, const void *recs, const uint64_t *bstat, uint32
 #define SHK_CB_LAUNCH(KW_, DD_, KC_, REC_, UQR_, UQC_, UQN_, SLOT_) \
   k_count_buckets<KW_, DD_, KC_><<<grid, CbCfg<KW_>::THREADS, cb_smem_bytes<KW_>(), st>>>((const REC_ *)recs, (const u64 *)bstat, rcap, (const u64 *)seg_off, seg_cnt, \
       UQR_, UQC_, UQN_, group_start, g_begin, g_end, sp, next_group, k, min_count, Table<KW_>{(SLOT_ *)ovf_slots, ovf_cap, mp}, ovf_flag, uq_flag, out, gate, gate_want)
-  if (kw == 1 && uq_rec && uq_cap && SHK_KSPEC1 && k == SHK_KSPEC1) SHK_CB_LAUNCH(1, true, SHK_KSPEC1, uint4, (uint4 *)uq_rec, uq_cnt, uq_cap, Slot1);
+  if (kw == 1 && uq_rec && uq_cap && SHK_KSPEC1 != 0 && k == SHK_KSPEC1) SHK_CB_LAUNCH(1, true, SHK_KSPEC1, uint4, (uint4 *)uq_rec, uq_cnt, uq_cap, Slot1);
   else if (kw == 1 && uq_rec && uq_cap) SHK_CB_LAUNCH(1, true, 0, uint4, (uint4 *)uq_rec, uq_cnt, uq_cap, Slot1);
   else if (kw == 1) SHK_CB_LAUNCH(1, false, 0, uint4, nullptr, nullptr, 0, Slot1);
+  else if (SHK_KSPEC2 != 0 && k == SHK_KSPEC2) SHK_CB_LAUNCH(2, false, SHK_KSPEC2, Rec32, nullptr, nullptr, 0, Slot2);
   else SHK_CB_LAUNCH(2, false, 0, Rec32, nullptr, nullptr, 0, Slot2);
 #undef SHK_CB_LAUNCH
   return 1;

@@ -93,7 +93,9 @@ __device__ __forceinline__ u32 revcomp_m(u32 x, int m) {
 #define SHK_PT_TILE (SHK_PT_WORDS + 6)
 #define SHK_PT_ROW 33
 #define SHK_PT_HROWS (SHK_PT_WORDS + 2)
+#ifndef SHK_PT_DESC
 #define SHK_PT_DESC 2048
+#endif
 
 // 64 bits of the staged stream starting at base index i (>= -32, relative to the tile)
 __device__ __forceinline__ u64 stream_bits64(const u64 *sb, int i) {

@@ -31,7 +31,8 @@ _Static_assert(offsetof(shk_stats, ms_pack) == 88, "ms_pack");
 _Static_assert(offsetof(shk_stats, n_spilled) == 112, "n_spilled");
 _Static_assert(offsetof(shk_stats, device_planned) == 128, "device_planned");
 _Static_assert(offsetof(shk_stats, n_spilled_records) == 136, "n_spilled_records");
-_Static_assert(sizeof(shk_stats) == 144, "shk_stats is 144 bytes");
+_Static_assert(offsetof(shk_stats, host_packed_slices) == 148, "host_packed_slices");
+_Static_assert(sizeof(shk_stats) == 152, "shk_stats is 152 bytes");
 _Static_assert(SHK_HISTO_BINS == 500, "500-bin spectrum (KmerHistogram.vue:45)");
 _Static_assert(SHK_OK == 0 && SHK_ERR_NO_DEVICE == 2 && SHK_ERR_STATE == 8, "status codes");
 

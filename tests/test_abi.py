@@ -34,7 +34,7 @@ def test_struct_layout_matches_header():
         "k", "verbose", "min_count", "min_qual", "chunk_size", "do_bloom", "do_fit", "no_bubble_collapse",
         "no_dead_end_removal"]
     assert C.sizeof(_ffi.ShkParams) == 64
-    assert C.sizeof(_ffi.ShkStats) == 10 * 8 + 2 * 4 + 6 * 4 + 2 * 8 + 2 * 4 + 8
+    assert C.sizeof(_ffi.ShkStats) == 10 * 8 + 2 * 4 + 6 * 4 + 2 * 8 + 2 * 4 + 8 + 2 * 4
 
 
 @pytest.mark.parametrize("k", [0, 2, 30, 32, 64, 65, 89])

@@ -243,6 +243,47 @@ def test_overlapped_load(k, monkeypatch):
     h.close()
 
 
+@pytest.mark.parametrize("k,lookahead", [(31, 0), (31, 3), (63, 0), (21, 1)])
+def test_hybrid_load_host_packs_slices(k, lookahead, monkeypatch):
+    """Hybrid load: the host cores pack the slices at the BACK of the stream (2 bits + validity bit, no K0) while the
+    link carries the FRONT ones as ASCII + host-taken quality bits; K1a runs per slice in arrival order.  With a
+    look-ahead of 0 the host packs its full half (deterministic); otherwise as much as it manages.  Qualities around
+    the threshold, bytes >= 128, a ragged stream end — the result must be the oracle's whatever the split."""
+    monkeypatch.setenv("SHK_OVERLAP_MIN", "1")
+    monkeypatch.setenv("SHK_QPACK", "1")
+    monkeypatch.setenv("SHK_HPACK_LOOKAHEAD", str(lookahead))
+    seq, qual = synth.reads(71, 110_000, 30.0, 0.01)
+    rng = np.random.default_rng(7)
+    qual = qual.copy()
+    body = qual != ord("\n")
+    low = body & (rng.random(qual.size) < 0.03)
+    qual[low] = rng.integers(33, 33 + 45, size=int(low.sum()), dtype=np.uint8)
+    qual[body & (rng.random(qual.size) < 0.001)] = 200
+    seq = seq.copy()
+    seq[(seq != ord("\n")) & (rng.random(seq.size) < 0.002)] = ord("N")
+    cut = seq.size - 1 - int(np.argmax(seq[::-1][1:] == ord("\n")))
+    seq, qual = seq[:cut].copy(), qual[:cut].copy()
+    assert seq.size % 32 != 0
+    h = AssemblyHelper.new(k, False, 2, 20, 0, False, False, False, False)
+    o = run_oracle(seq, qual, k, 2, 20)
+    for it in range(3):
+        h.preprocess_reads(seq, qual)
+        st = h.stats()
+        assert st["load_slices"] == 16 and st["host_qual_bits"] > 0, st
+        if lookahead == 0:
+            assert st["host_packed_slices"] == 8, st
+        assert st["n_bases"] == o.stats()["n_bases"]
+        h.assemble()
+        assert_parity(h, o, check_table=False)
+    # the same reads with the hybrid load switched off: the plain overlapped load
+    monkeypatch.setenv("SHK_HPACK", "0")
+    h.preprocess_reads(seq, qual)
+    assert h.stats()["host_packed_slices"] == 0 and h.stats()["load_slices"] == 8
+    h.assemble()
+    assert_parity(h, o, check_table=False)
+    h.close()
+
+
 @pytest.mark.parametrize("min_qual,qpack", [(2, 1), (20, 1), (37, 1), (20, 0)])
 def test_overlapped_load_quality_bits_from_host(min_qual, qpack, monkeypatch):
     """The steady-state load takes the quality test on the host cores (one bit per position crosses the link
@@ -250,6 +291,7 @@ def test_overlapped_load_quality_bits_from_host(min_qual, qpack, monkeypatch):
     a stream length that is not a multiple of 32."""
     monkeypatch.setenv("SHK_OVERLAP_MIN", "1")
     monkeypatch.setenv("SHK_QPACK", str(qpack))              # forced on / off (the library's own choice is timing-based)
+    monkeypatch.setenv("SHK_HPACK", "0")                     # (the hybrid load has its own test above)
     seq, qual = synth.reads(61, 90_000, 30.0, 0.01)
     rng = np.random.default_rng(5)
     qual = qual.copy()
