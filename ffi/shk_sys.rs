@@ -180,6 +180,7 @@ extern "C" {
                                n_total: usize, my_offset: usize, histo_global: *const u64, n_instances_global: u64,
                                n_bases_global: u64, used_min_count: c_int) -> shk_status;
     pub fn shk_fit_min_count(histo: *const u64, fallback: c_int) -> c_int;
+    pub fn shk_fastq_stats(path: *const c_char, threads: c_int, chunk_bytes: u64, bad_guesses: c_int, out4: *mut u64) -> shk_status;
     /// Allocation-free spectrum of a small packed read set (device pointers; at most 2^20 positions, k odd 3..31);
     /// no counterpart in the reference.  d_out: 503 u64 on the device.  Calls that overlap on one GPU race.
     pub fn shk_spectrum_noalloc(d_bases: *const u64, d_mask: *const u32, n_positions: u64, k: c_int, d_out: *mut u64, stream: *mut c_void) -> shk_status;

@@ -87,6 +87,15 @@ shk_status shk_asm_set_progress_cb(shk_asm *h, shk_progress_fn fn, void *user);
 shk_status shk_asm_preprocess_files(shk_asm *h, const char *path1,
                                     const char *path2_or_null);
 
+/* Host only (no device, no handle): how the file ingest of shk_asm_preprocess_files splits ONE FASTQ(.gz) file —
+ * out4 = reads, sequence characters, and two order-independent checksums (over the sequences; over sequence +
+ * quality).  threads / chunk_bytes / bad_guesses: 0 / 0 / -1 take the ingest's own choices (SHK_FASTQ_THREADS,
+ * SHK_FASTQ_CHUNK, SHK_FASTQ_BAD_GUESS); a plain file of at least two chunks is split over `threads` threads, its
+ * chunk borders guessed and then verified against the parse of the chunk in front (bad_guesses = 1 makes every
+ * guess wrong, for tests: the result must not change).  Errors as shk_asm_preprocess_files reports them.
+ * Reference analogue: the FASTQ base counts of sketchlib.rust/src/fastx_wasm.rs (tests/golden/sketchlib_fastq_kat.json). */
+shk_status shk_fastq_stats(const char *path, int threads, uint64_t chunk_bytes, int bad_guesses, uint64_t *out4);
+
 /* Streaming form of preprocess for hosts that hold bytes, not paths (model:
  * deacon-bridge/src/lib.rs:112-206 push_chunk/finish).  `bytes` is decompressed
  * FASTQ text; chunks may split records anywhere. */

@@ -103,6 +103,7 @@ SYMBOLS = {
     "shk_shard_set_nodes": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t,
                                       C.c_void_p, C.c_uint64, C.c_uint64, C.c_int]),
     "shk_fit_min_count": (C.c_int, [C.c_void_p, C.c_int]),
+    "shk_fastq_stats": (C.c_int, [C.c_char_p, C.c_int, C.c_uint64, C.c_int, C.c_void_p]),
     # sharded graph stage (peer memory)
     "shk_shard_graph_publish": (C.c_int, [_H, C.c_void_p]),
     "shk_shard_graph_connect": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_int]),

@@ -3,9 +3,14 @@
 // get_assembly().  Mirrors what stays on the host in the reference
 // (BASELINE.json north_star: "branchy graph cleaning and contig extension stay in
 // the reference's Rust host code, consuming the GPU-built graph").
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
 #include <zlib.h>
 
 #include <algorithm>
+#include <atomic>
 #include <cstdio>
 #include <cstring>
 #include <map>
@@ -116,8 +121,191 @@ struct BatchQueue {
   void done() { std::lock_guard<std::mutex> lk(mu); --producers; cv_get.notify_all(); }
 };
 
+// ---------------------------------------------------------------------------
+// ONE plain (uncompressed) FASTQ file over several threads.  The file is mapped and cut into chunks of a fixed
+// byte size; a record belongs to the chunk its '@' line starts in.  Threads take chunks in order from a counter.
+// Where a chunk's first record starts is GUESSED (the first line from the chunk border on that starts with '@',
+// whose line + 2 starts with '+', whose sequence and quality lines are equally long and which is followed by
+// another '@' line or the end of the file — a quality line may start with '@' too), the chunk is parsed from there,
+// and the batches are held back until the chunk in front has finished: its parse, which started from a verified
+// record start, ends exactly where this chunk's first record starts.  If that is not where the guess was, the chunk
+// is parsed again from the right place — so the reads are those of the serial parser whatever the guesses were, and
+// the first malformed record of the file is reported with its serial record number.  Chunks are released in file
+// order; at most one parsed chunk per thread waits in memory.
+// ---------------------------------------------------------------------------
+struct FqError { shk_status st = SHK_OK; int kind = 0; uint64_t rec = 0; size_t a = 0, b = 0; };
+struct FqChunk { std::vector<ReadBatch> batches; uint64_t reads = 0; size_t end = 0; FqError err; };
+
+static inline size_t line_end(const uint8_t *d, size_t size, size_t p) {       // position of the '\n' that ends the line at p (size: none)
+  if (p >= size) return size;
+  const uint8_t *nl = (const uint8_t *)memchr(d + p, '\n', size - p);
+  return nl ? (size_t)(nl - d) : size;
+}
+static inline size_t stripped_len(const uint8_t *d, size_t b, size_t e) { while (e > b && d[e - 1] == '\r') --e; return e - b; }
+
+// first record start at or behind `from` by the rule above (size: none found)
+static size_t guess_record_start(const uint8_t *d, size_t size, size_t from) {
+  size_t L = from;
+  if (L > 0 && d[L - 1] != '\n') { L = line_end(d, size, L); if (L >= size) return size; ++L; }
+  while (L < size) {
+    const size_t e0 = line_end(d, size, L);
+    if (d[L] == '@' && e0 < size) {
+      const size_t L1 = e0 + 1, e1 = line_end(d, size, L1);
+      if (e1 < size) {
+        const size_t L2 = e1 + 1, e2 = line_end(d, size, L2);
+        if (L2 < size && d[L2] == '+' && e2 < size) {
+          const size_t L3 = e2 + 1, e3 = line_end(d, size, L3);
+          if (stripped_len(d, L1, e1) == stripped_len(d, L3, e3)) {
+            size_t N = e3 < size ? e3 + 1 : size;                     // next line that is not blank
+            while (N < size && stripped_len(d, N, line_end(d, size, N)) == 0) N = line_end(d, size, N) + 1;
+            if (N >= size || d[N] == '@') return L;
+          }
+        }
+      }
+    }
+    if (e0 >= size) break;
+    L = e0 + 1;
+  }
+  return size;
+}
+
+// The records that start in [start, limit), by the serial parser's line state machine (decode_file below) over the
+// file with one '\n' appended — which is what that parser feeds itself at the end of a file.  `start` is a record
+// start (or lies in the blank lines in front of one); out.end = where the first record of the next chunk starts.
+static void parse_chunk(const uint8_t *d, size_t size, size_t start, size_t limit, size_t batch_bytes, FqChunk &out) {
+  out.batches.clear(); out.reads = 0; out.err = FqError();
+  ReadBatch cur;
+  int state = 0;
+  size_t p = start, sp = 0, ns = 0;
+  while (p <= size) {
+    const size_t e = line_end(d, size, p), n = stripped_len(d, p, e);
+    if (state == 0) {
+      if (n == 0) { p = e + 1; continue; }                                             // blank line between records
+      if (p >= limit) break;                                                          // the next chunk's first record
+      if (d[p] == '>') { out.err = FqError{SHK_ERR_FORMAT, 1, out.reads, 0, 0}; break; }
+      if (d[p] != '@') { out.err = FqError{SHK_ERR_FORMAT, 2, out.reads, 0, 0}; break; }
+      state = 1;
+    } else if (state == 1) {
+      sp = p; ns = n; state = 2;
+    } else if (state == 2) {
+      if (n == 0 || d[p] != '+') { out.err = FqError{SHK_ERR_FORMAT, 3, out.reads, 0, 0}; break; }
+      state = 3;
+    } else {
+      if (n != ns) { out.err = FqError{SHK_ERR_FORMAT, 4, out.reads, n, ns}; break; }
+      cur.seq.insert(cur.seq.end(), d + sp, d + sp + ns); cur.seq.push_back('\n');
+      cur.qual.insert(cur.qual.end(), d + p, d + p + n); cur.qual.push_back('\n');
+      ++cur.reads; ++out.reads; state = 0;
+      if (cur.seq.size() >= batch_bytes) { out.batches.emplace_back(std::move(cur)); cur = ReadBatch(); }
+    }
+    p = e + 1;
+  }
+  if (out.err.st == SHK_OK && state != 0) out.err = FqError{SHK_ERR_FORMAT, 5, out.reads, 0, 0};   // the file ends inside a record
+  if (cur.reads) out.batches.emplace_back(std::move(cur));
+  out.end = std::min(p, size);
+}
+
+static bool plain_file(const char *path, size_t &size) {
+  const int fd = open(path, O_RDONLY);
+  if (fd < 0) return false;
+  struct stat sb;
+  unsigned char magic[2] = {0, 0};
+  const bool ok = fstat(fd, &sb) == 0 && S_ISREG(sb.st_mode) && pread(fd, magic, 2, 0) == 2 && !(magic[0] == 0x1f && magic[1] == 0x8b);
+  close(fd);
+  size = ok ? (size_t)sb.st_size : 0;
+  return ok;
+}
+
+// false: not taken (the caller decodes the file serially); true: the file was handled here (bq->done() called)
+static bool decode_plain_parallel(const char *path, BatchQueue *bq, unsigned threads, size_t chunk_bytes, bool bad_guesses) {
+  size_t size = 0;
+  if (threads < 2 || !plain_file(path, size) || size < 2 * chunk_bytes) return false;
+  const int fd = open(path, O_RDONLY);
+  if (fd < 0) return false;
+  void *map = mmap(nullptr, size, PROT_READ, MAP_PRIVATE, fd, 0);
+  close(fd);
+  if (map == MAP_FAILED) return false;
+  madvise(map, size, MADV_SEQUENTIAL);
+  const uint8_t *d = (const uint8_t *)map;
+  const size_t nchunks = (size + chunk_bytes - 1) / chunk_bytes;
+  struct Shared {
+    std::mutex mu; std::condition_variable cv;
+    std::vector<char> done; std::vector<size_t> end; std::vector<uint64_t> reads_upto;
+    bool stop = false;
+  } sh;
+  sh.done.assign(nchunks, 0); sh.end.assign(nchunks, 0); sh.reads_upto.assign(nchunks, 0);
+  std::atomic<size_t> next{0};
+  auto fail_at = [&](const FqError &e, uint64_t reads_before) {
+    char m[400];
+    const unsigned long long rec = (unsigned long long)(reads_before + e.rec);
+    switch (e.kind) {
+      case 1: snprintf(m, sizeof m, "FASTA input in %s: the assembler needs FASTQ reads", path); break;
+      case 2: snprintf(m, sizeof m, "%s: FASTQ record %llu does not start with '@'", path, rec); break;
+      case 3: snprintf(m, sizeof m, "%s: FASTQ record %llu: missing '+' line", path, rec); break;
+      case 4: snprintf(m, sizeof m, "%s: FASTQ record %llu: %zu quality values for %zu bases", path, rec, e.a, e.b); break;
+      default: snprintf(m, sizeof m, "truncated FASTQ record at end of %s", path); break;
+    }
+    bq->fail(e.st, m);
+  };
+  auto worker = [&] {
+    FqChunk ck;
+    for (;;) {
+      const size_t c = next.fetch_add(1);
+      if (c >= nchunks) return;
+      const size_t lo = c * chunk_bytes, limit = std::min(size, lo + chunk_bytes);
+      size_t start = c == 0 ? 0 : guess_record_start(d, size, lo);
+      if (bad_guesses && c > 0 && start < size) { const size_t e = line_end(d, size, start); start = e < size ? e + 1 : size; }   // (tests: every guess is one line late)
+      parse_chunk(d, size, start, limit, 32u << 20, ck);
+      size_t true_start = 0; uint64_t reads_before = 0;
+      if (c > 0) {
+        std::unique_lock<std::mutex> lk(sh.mu);
+        sh.cv.wait(lk, [&] { return sh.done[c - 1] || sh.stop; });
+        if (sh.stop) return;
+        true_start = sh.end[c - 1]; reads_before = sh.reads_upto[c - 1];
+      }
+      // the guess was wrong: parse again from where the chunk in front really ended
+      if (c > 0 && true_start != start) parse_chunk(d, size, true_start, limit, 32u << 20, ck);
+      bool ok = ck.err.st == SHK_OK;
+      if (ok) {
+        for (auto &b : ck.batches) if (!bq->put(std::move(b))) { ok = false; break; }
+      } else {
+        fail_at(ck.err, reads_before);
+      }
+      {
+        std::lock_guard<std::mutex> lk(sh.mu);
+        if (ok) { sh.done[c] = 1; sh.end[c] = ck.end; sh.reads_upto[c] = reads_before + ck.reads; }
+        else sh.stop = true;
+      }
+      sh.cv.notify_all();
+      if (!ok) return;
+    }
+  };
+  std::vector<std::thread> th;
+  for (unsigned t = 1; t < threads; ++t) th.emplace_back(worker);
+  worker();
+  for (auto &t : th) t.join();
+  munmap(map, size);
+  if (getenv("SHK_DEBUG")) fprintf(stderr, "[shk] %s: %zu chunks of %zu bytes split by %u threads\n", path, nchunks, chunk_bytes, threads);
+  bq->done();
+  return true;
+}
+
 // one file -> batches.  limit_reads > 0: a batch per that many reads (chunked mode); else by size.
-void decode_file(const char *path, uint64_t limit_reads, BatchQueue *bq) {
+struct FastqPar { unsigned threads; size_t chunk_bytes; bool bad_guesses; };
+static FastqPar fastq_par(unsigned n_files) {
+  // threads per file for a plain FASTQ: the host's cores over the files of the run, at most 8 each (the line split runs
+  // at a few GB/s per thread; the consumer's H2D + K0 keeps up with about that many)
+  const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+  unsigned t = std::min(8u, std::max(1u, (hw > 2 ? hw - 2 : hw) / std::max(1u, n_files)));
+  size_t chunk = 64u << 20;
+  if (const char *e = getenv("SHK_FASTQ_THREADS")) t = (unsigned)std::max(1, atoi(e));
+  if (const char *e = getenv("SHK_FASTQ_CHUNK")) chunk = (size_t)std::max(64ll, atoll(e));
+  const char *bg = getenv("SHK_FASTQ_BAD_GUESS");
+  return FastqPar{t, chunk, bg && bg[0] == '1'};
+}
+
+void decode_file(const char *path, uint64_t limit_reads, BatchQueue *bq, FastqPar par) {
+  // bulk mode, a plain file: the line split runs on several threads (batches by size, any order: S2 / S8)
+  if (limit_reads == 0 && decode_plain_parallel(path, bq, par.threads, par.chunk_bytes, par.bad_guesses)) return;
   auto fail = [&](shk_status s, const char *fmt, auto... a) { char m[400]; snprintf(m, sizeof m, fmt, a...); bq->fail(s, m); bq->done(); };
   gzFile gz = gzopen(path, "rb");                // transparent for plain files, multi-member aware
   if (!gz) return fail(SHK_ERR_IO, "cannot open %s", path);
@@ -194,8 +382,9 @@ shk_status parse_fastq_files(shk_asm *h, const char *p1, const char *p2) {
   BatchQueue bq;
   std::vector<std::thread> th;
   for (int f = 0; f < 2; ++f) if (paths[f]) ++bq.producers;
+  const FastqPar par = fastq_par((unsigned)bq.producers);
   for (int f = 0; f < 2; ++f)
-    if (paths[f]) th.emplace_back(decode_file, paths[f], chunked ? (uint64_t)h->p.chunk_size : 0ull, &bq);
+    if (paths[f]) th.emplace_back(decode_file, paths[f], chunked ? (uint64_t)h->p.chunk_size : 0ull, &bq, par);
   shk_status st = SHK_OK;
   uint64_t next_tick = 500000;
   for (;;) {
@@ -396,4 +585,52 @@ shk_status build_assembly_json(shk_asm *h) {
   return SHK_OK;
 }
 
+// ---------------------------------------------------------------------------
+// Host-only: reads, bases and order-independent checksums of a FASTQ(.gz) file as the ingest above splits it
+// (include/shk.h shk_fastq_stats) — what the CPU tests compare between the serial and the multi-threaded split.
+// ---------------------------------------------------------------------------
+static inline uint64_t fnv1a(const uint8_t *p, size_t n, uint64_t h) {
+  for (size_t i = 0; i < n; ++i) { h ^= p[i]; h *= 0x100000001B3ull; }
+  return h;
+}
+shk_status fastq_stats(const char *path, int threads, uint64_t chunk_bytes, int bad_guesses, uint64_t *out) {
+  BatchQueue bq;
+  bq.producers = 1;
+  FastqPar par = fastq_par(1);
+  if (threads > 0) par.threads = (unsigned)threads;
+  if (chunk_bytes) par.chunk_bytes = (size_t)chunk_bytes;
+  if (bad_guesses >= 0) par.bad_guesses = bad_guesses != 0;
+  std::thread producer(decode_file, path, 0ull, &bq, par);
+  uint64_t reads = 0, bases = 0, cs = 0, cq = 0;
+  for (;;) {
+    ReadBatch b;
+    {
+      std::unique_lock<std::mutex> lk(bq.mu);
+      bq.cv_get.wait(lk, [&] { return !bq.q.empty() || bq.producers == 0 || bq.abort; });
+      if (bq.abort && bq.err != SHK_OK) break;
+      if (bq.q.empty()) { if (bq.producers == 0) break; continue; }
+      b = std::move(bq.q.front()); bq.q.pop_front();
+      bq.cv_put.notify_one();
+    }
+    reads += b.reads; bases += b.seq.size() - b.reads;
+    size_t ps = 0, pq = 0;
+    for (uint64_t r = 0; r < b.reads; ++r) {
+      const uint8_t *es = (const uint8_t *)memchr(b.seq.data() + ps, '\n', b.seq.size() - ps);
+      const size_t n = (size_t)(es - (b.seq.data() + ps));
+      const uint64_t hs = fnv1a(b.seq.data() + ps, n, 0xCBF29CE484222325ull), hq = fnv1a(b.qual.data() + pq, n, hs);
+      cs += hs * 0x9E3779B97F4A7C15ull; cq += (hq ^ (hq >> 29)) * 0xBF58476D1CE4E5B9ull;     // sums: the order of the reads does not matter
+      ps += n + 1; pq += n + 1;
+    }
+  }
+  producer.join();
+  if (bq.err != SHK_OK) { set_error("%s", bq.err_msg.c_str()); return bq.err; }
+  out[0] = reads; out[1] = bases; out[2] = cs; out[3] = cq;
+  return SHK_OK;
+}
+
 }  // namespace shk
+
+extern "C" shk_status shk_fastq_stats(const char *path, int threads, uint64_t chunk_bytes, int bad_guesses, uint64_t *out4) {
+  if (!path || !out4) { shk::set_error("null argument"); return SHK_ERR_BAD_ARG; }
+  return shk::fastq_stats(path, threads, chunk_bytes, bad_guesses, out4);
+}
