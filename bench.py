@@ -464,7 +464,7 @@ def sharded_arm(args, name, w, ctx, steps, warmup, with_e2e=True, with_cold=Fals
             dist.barrier()
         torch.cuda.synchronize()
 
-    stage_acc, host_acc, modes = {}, {}, []
+    stage_acc, host_acc, modes, rec_modes = {}, {}, [], []
 
     def step():
         """one pass of the hot path over the resident packed reads"""
@@ -475,6 +475,7 @@ def sharded_arm(args, name, w, ctx, steps, warmup, with_e2e=True, with_cold=Fals
         info = sharded_run(eng, timings=marks)
         step.marks = marks
         modes.append(info["graph_mode"])
+        rec_modes.append(info.get("records", "exchanged"))
 
     def harvest():
         m = getattr(step, "marks", None)
@@ -678,10 +679,13 @@ def sharded_arm(args, name, w, ctx, steps, warmup, with_e2e=True, with_cold=Fals
     sharded_graph = bool(modes) and modes[-1] == "sharded"
     multi = ("single GPU" if world == 1 else
              ("one community read set" if community else f"one read set of {world} genomes") +
-             f" sharded by read pair over {world} ranks; records routed to the owner rank by minimizer-bucket range through an "
-             "NCCL all-to-all; graph stage: " + ("every rank on its own nodes (peer memory over NVLink), unitigs joined by the "
+             f" sharded by read pair over {world} ranks; records routed to the owner rank by minimizer-bucket range: " +
+             ("the owner's K1b reads the regions of its buckets in place, out of every rank's memory (peer loads over NVLink, no "
+              "pack, no all-to-all)" if rec_modes and rec_modes[-1] == "pulled" else "packed and sent through an NCCL all-to-all") +
+             "; graph stage: " + ("every rank on its own nodes (peer memory over NVLink), unitigs joined by the "
                                                  "chain-level pointer-jumping pass" if sharded_graph else "nodes all-gathered, replicated"))
     cfg.update({"bases_per_step_this_gpu": bases, "multi_gpu": multi, "graph_mode": modes[-1] if modes else "single",
+                "records": rec_modes[-1] if rec_modes else "local",
                 "l2": "inputs larger than L2: packed reads %.0f MB + super-k-mer records %.0f MB vs 126 MB L2"
                       % (st["n_positions"] * 0.375 / 1e6, st["n_records"] * (16 if w["k"] <= 31 else 32) / 1e6),
                 "n_distinct": st["n_distinct"], "n_nodes": n_nodes_global, "n_unitigs": st["n_unitigs"],

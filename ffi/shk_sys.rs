@@ -87,6 +87,7 @@ pub struct shk_shard_join_info {
     pub n_cyclic_chain_elems: u64,
 }
 pub const SHK_PEER_BLOB_BYTES: usize = 256;
+pub const SHK_REC_BLOB_BYTES: usize = 1280;
 
 /// opaque: contigs + links produced by the host graph cleaning
 #[repr(C)]
@@ -180,6 +181,8 @@ extern "C" {
                                n_total: usize, my_offset: usize, histo_global: *const u64, n_instances_global: u64,
                                n_bases_global: u64, used_min_count: c_int) -> shk_status;
     pub fn shk_fit_min_count(histo: *const u64, fallback: c_int) -> c_int;
+    pub fn shk_shard_records_publish(h: *mut shk_asm, blob_out: *mut c_void) -> shk_status;
+    pub fn shk_shard_count_pull(h: *mut shk_asm, blobs: *const c_void, min_count: c_int, took: *mut c_int) -> shk_status;
     pub fn shk_fastq_stats(path: *const c_char, threads: c_int, chunk_bytes: u64, bad_guesses: c_int, out4: *mut u64) -> shk_status;
     /// Allocation-free spectrum of a small packed read set (device pointers; at most 2^20 positions, k odd 3..31);
     /// no counterpart in the reference.  d_out: 503 u64 on the device.  Calls that overlap on one GPU race.

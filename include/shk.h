@@ -318,6 +318,24 @@ shk_status shk_shard_count(shk_asm *h, const void *d_recv, const uint64_t *recv_
 shk_status shk_shard_count_device(shk_asm *h, const void *d_recv, const uint64_t *d_recv_fill,
                                   const uint64_t *recv_records, uint64_t n_instances,
                                   int histogram_only, int min_count);
+
+/* The record exchange WITHOUT an exchange (ranks of one box; peer memory over NVLink / NVSwitch).  After
+ * shk_shard_partition a rank publishes its record regions and their fills (blob_out: HOST, SHK_REC_BLOB_BYTES — two
+ * cudaIpc handles, the region stride, what it cut for every owner, and whether it can take the steady-state count);
+ * the host all-gathers the blobs — that collective, queued behind K1a, is also the barrier "every rank's regions are
+ * complete" — and hands all of them (HOST, world x SHK_REC_BLOB_BYTES, rank order) to shk_shard_count_pull: the
+ * owner's K1b then reads the regions of ITS buckets in place, its own and every other rank's, one coalesced load per
+ * record inside the kernel that counts it; shk_shard_pack, both all-to-alls and the receive buffer disappear.
+ * *took = 1: counted (state as after shk_shard_count_device).  *took = 0: not taken — some rank is uncalibrated or
+ * cannot export / map peer memory, or the device-side plan failed verification; nothing is lost, the host runs
+ * shk_shard_pack + the all-to-alls + shk_shard_count[_device] for this step (the decision must be the same on every
+ * rank: a rank whose count stood still takes part in the exchange and counts again).  The regions of a rank must not
+ * be rewritten (its next shk_shard_partition) before every owner's count has completed: any collective queued behind
+ * the count orders that.  SHK_SHARD_PULL=0 keeps the regions in pool memory (no export: *took is always 0).
+ * Reference analogue: none (the reference is one Web Worker, App.vue:224-226); north_star "hash-sharded over the GPUs". */
+#define SHK_REC_BLOB_BYTES 1280
+shk_status shk_shard_records_publish(shk_asm *h, void *blob_out);
+shk_status shk_shard_count_pull(shk_asm *h, const void *blobs, int min_count, int *took);
 /* Host-side quality test (S3), as the steady-state load takes it before the copy: bit j of
  * out[w] = ((int)qual[32 w + j] - 33 >= min_qual), positions past n read as 0.  out holds
  * ceil(n / 32) words.  Needs no device.  -32 <= min_qual <= 94. */

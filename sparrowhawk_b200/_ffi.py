@@ -4,6 +4,8 @@ The library is the product: if it is missing this module raises — there is no
 Python / CPU implementation to fall back to.
 """
 import ctypes as C
+
+import numpy as np
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
@@ -48,6 +50,20 @@ class ShkShardJoinInfo(C.Structure):
 
 
 PEER_BLOB_BYTES = 256
+REC_BLOB_BYTES = 1280
+
+
+def rec_blob_ready(blob):
+    """`ready` word of a record blob (csrc/shk_shard.cu RecBlob: two 64-byte handles, then eight u32)"""
+    return int(np.frombuffer(bytes(blob[128:160]), np.uint32)[5]) != 0
+
+
+def rec_blob_records_for(blob, owner):
+    return int(np.frombuffer(bytes(blob[160:160 + 64 * 8]), np.uint64)[owner])
+
+
+def rec_blob_kmers_for(blob, owner):
+    return int(np.frombuffer(bytes(blob[160 + 64 * 8:160 + 128 * 8]), np.uint64)[owner])
 PROGRESS_FN = C.CFUNCTYPE(None, C.c_char_p, C.c_void_p)
 
 # every symbol include/shk.h declares: name -> (restype, argtypes)
@@ -103,6 +119,8 @@ SYMBOLS = {
     "shk_shard_set_nodes": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t,
                                       C.c_void_p, C.c_uint64, C.c_uint64, C.c_int]),
     "shk_fit_min_count": (C.c_int, [C.c_void_p, C.c_int]),
+    "shk_shard_records_publish": (C.c_int, [_H, C.c_void_p]),
+    "shk_shard_count_pull": (C.c_int, [_H, C.c_void_p, C.c_int, C.c_void_p]),
     "shk_fastq_stats": (C.c_int, [C.c_char_p, C.c_int, C.c_uint64, C.c_int, C.c_void_p]),
     # sharded graph stage (peer memory)
     "shk_shard_graph_publish": (C.c_int, [_H, C.c_void_p]),

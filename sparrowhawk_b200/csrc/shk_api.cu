@@ -750,12 +750,12 @@ static shk_status count_impl(shk_asm *h, int /*reset*/, uint32_t P_override = 0,
     if (dev_plan) {
       uint32_t starts[65];
       for (uint32_t r = 0; r <= world; ++r) starts[r] = shard_lo(P, world, r);
-      SHK_TRY(h->pack_off.ensure((size_t)P * 8)); SHK_TRY(h->send_tot.ensure((size_t)(world + 1) * 8));
-      SHK_TRY(h->hsend.ensure_host((size_t)(world + 1) * 8));
-      SHK_CUDA(cudaMemsetAsync(h->send_tot.p, 0, (size_t)(world + 1) * 8, h->stream));
+      SHK_TRY(h->pack_off.ensure((size_t)P * 8)); SHK_TRY(h->send_tot.ensure((size_t)(2 * world + 1) * 8));
+      SHK_TRY(h->hsend.ensure_host((size_t)(2 * world + 1) * 8));
+      SHK_CUDA(cudaMemsetAsync(h->send_tot.p, 0, (size_t)(2 * world + 1) * 8, h->stream));
       h->st.gpu_launches += launch_shard_send_plan(h->bfill.as<uint64_t>(), rcap, world, starts, h->pack_off.as<uint64_t>(),
                                                    h->send_tot.as<uint64_t>(), h->stream);
-      SHK_CUDA(cudaMemcpyAsync(h->hsend.p, h->send_tot.p, (size_t)(world + 1) * 8, cudaMemcpyDeviceToHost, h->stream));
+      SHK_CUDA(cudaMemcpyAsync(h->hsend.p, h->send_tot.p, (size_t)(2 * world + 1) * 8, cudaMemcpyDeviceToHost, h->stream));
       SHK_CUDA(cudaEventRecord(h->ev[3], h->stream));
       SHK_TRY(read_scalars(h));
       const uint64_t *hs = (const uint64_t *)h->hsend.p;
@@ -1728,6 +1728,13 @@ shk_status shk_shard_partition(shk_asm *h, uint32_t n_buckets, uint32_t world, u
   if (!world || rank >= world || !send_records || n_buckets < world || (n_buckets & (n_buckets - 1))) {
     set_error("shard_partition: need a power-of-two bucket count >= world and rank < world"); return SHK_ERR_BAD_ARG;
   }
+  {
+    // the record regions and their fills are published to the other ranks of the box (shk_shard_records_publish):
+    // plain cudaMalloc, pool memory has no cudaIpc handle
+    const char *e = getenv("SHK_SHARD_PULL");
+    if (!(e && e[0] == '0'))
+      for (shk::DevBuf *b : {&h->skrecs, &h->bfill}) if (!b->plain) { b->release(); b->plain = true; }
+  }
   SHK_TRY(count_impl(h, 1, n_buckets, world));
   h->shard_world = world; h->shard_rank = rank;
   if (h->send_planned) {                       // offsets (local to the owner) and totals were cut on the device
@@ -1803,30 +1810,16 @@ shk_status shk_shard_count(shk_asm *h, const void *d_recv, const uint64_t *recv_
   return st;
 }
 
-// Steady-state form of shk_shard_count: the fills stay on the device.  The segment table is built by a kernel
-// (launch_shard_segments) and K1b's CTAs cut the bucket groups themselves from the per-bucket totals, so the host
-// walks nothing of size buckets x ranks.  Needs a handle calibrated by one host-planned sharded run (ratio,
-// de-dup list size, overflow table); everything the host planner would have guaranteed is verified after the
-// kernel, and any violation — or an uncalibrated handle — takes shk_shard_count with the fills copied to the host.
-shk_status shk_shard_count_device(shk_asm *h, const void *d_recv, const uint64_t *d_recv_fill, const uint64_t *recv_records,
-                                  uint64_t n_instances, int histogram_only, int min_count) {
-  SHK_TRY(require_device(h));
-  if (!h->counted || !h->shard_world) { set_error("shard_count before shard_partition"); return SHK_ERR_STATE; }
-  if (!d_recv_fill || !recv_records) { set_error("null recv_fill / recv_records"); return SHK_ERR_BAD_ARG; }
-  const uint32_t W = h->shard_world, lo = shard_lo(h->P, W, h->shard_rank), hi = shard_lo(h->P, W, h->shard_rank + 1), nb = hi - lo;
+}  // extern "C"
+// The steady-state owner-side count (shared by shk_shard_count_device and shk_shard_count_pull): the segment table is
+// built on the device by `build_segments` (offsets into the received records, or absolute addresses of the source
+// ranks' regions), K1b's CTAs cut the bucket groups themselves, and what the host planner would have guaranteed is
+// verified afterwards.  fast stays true when the count stands; false = run it again the host-planned way.
+template <class BuildSegments>
+static shk_status shard_count_steady(shk_asm *h, const void *d_recv, uint32_t W, uint32_t nb, uint64_t run, uint64_t n_instances,
+                                     uint64_t bound, int mc, bool dedup, BuildSegments build_segments, bool &fast) {
   const size_t nseg = (size_t)nb * W;
-  const int mc = min_count < 0 ? h->p.min_count : min_count;
-  const bool dedup = h->kw == 1 && !h->no_dedup;
-  static const bool off = [] { const char *e = getenv("SHK_NO_FAST"); return e && e[0] == '1'; }();
-  uint64_t run = 0;
-  uint64_t base[64];
-  for (uint32_t s = 0; s < W && s < 64; ++s) { base[s] = run; run += recv_records[s]; }
-  uint64_t bound = n_instances / ((uint64_t)std::max(mc, 0) + 1) + 1;
-  bool fast = !off && !histogram_only && (int)W <= std::min(64, shard_max_world()) && nb > 0 && h->ratio_est > 0 && h->ovf_cap > 0 &&
-              (!dedup || h->uq_cap > 0) && h->shard_cal_nb == nb && h->shard_cal_world == W && !h->shard_fast_banned &&
-              run <= 0xFFFFFFFFull && bound <= 0xFFFFFFF0ull && (W == 1 || (uint32_t)count_max_group() / W >= 1);
-  if (run && !d_recv) { set_error("null receive buffer"); return SHK_ERR_BAD_ARG; }
-  if (fast) {
+  {
     const uint32_t node_cap = (uint32_t)bound;
     SHK_CUDA(cudaEventRecord(h->ev[4], h->stream));
     SHK_TRY(h->seg_off.ensure(nseg * 8 + 8)); SHK_TRY(h->seg_cnt.ensure(nseg * 4 + 4)); SHK_TRY(h->shard_btot.ensure((size_t)nb * 8 + 8));
@@ -1842,8 +1835,7 @@ shk_status shk_shard_count_device(shk_asm *h, const void *d_recv, const uint64_t
       const size_t ctas = (size_t)count_ctas();
       SHK_TRY(h->uq_rec.ensure(ctas * uq_fast * 16 + 16)); SHK_TRY(h->uq_cnt.ensure(ctas * uq_fast * 4 + 16));
     }
-    h->st.gpu_launches += launch_shard_segments(d_recv_fill, nb, W, base, h->seg_off.as<uint64_t>(), h->seg_cnt.as<uint32_t>(),
-                                                h->shard_btot.as<uint64_t>(), h->stream);
+    h->st.gpu_launches += build_segments();
     SHK_CUDA(cudaMemsetAsync(d_counters(h) + 2, 0, 8, h->stream));                     // n_distinct ([1], [3]: K1a's totals stay)
     SHK_CUDA(cudaMemsetAsync(d_counters(h) + 4, 0, 4 * 8 + SHK_HISTO_BINS * 8 + 8 * 4, h->stream));   // spilled, decoded, records, spectrum, flags
     h->st.gpu_launches += launch_table_fill(h->ovf.p, h->ovf_cap, h->kw, h->stream);
@@ -1891,6 +1883,40 @@ shk_status shk_shard_count_device(shk_asm *h, const void *d_recv, const uint64_t
       return SHK_OK;
     }
   }
+  return SHK_OK;
+}
+extern "C" {
+
+// Steady-state form of shk_shard_count: the fills stay on the device.  The segment table is built by a kernel
+// (launch_shard_segments) and K1b's CTAs cut the bucket groups themselves from the per-bucket totals, so the host
+// walks nothing of size buckets x ranks.  Needs a handle calibrated by one host-planned sharded run (ratio,
+// de-dup list size, overflow table); everything the host planner would have guaranteed is verified after the
+// kernel, and any violation — or an uncalibrated handle — takes shk_shard_count with the fills copied to the host.
+shk_status shk_shard_count_device(shk_asm *h, const void *d_recv, const uint64_t *d_recv_fill, const uint64_t *recv_records,
+                                  uint64_t n_instances, int histogram_only, int min_count) {
+  SHK_TRY(require_device(h));
+  if (!h->counted || !h->shard_world) { set_error("shard_count before shard_partition"); return SHK_ERR_STATE; }
+  if (!d_recv_fill || !recv_records) { set_error("null recv_fill / recv_records"); return SHK_ERR_BAD_ARG; }
+  const uint32_t W = h->shard_world, lo = shard_lo(h->P, W, h->shard_rank), hi = shard_lo(h->P, W, h->shard_rank + 1), nb = hi - lo;
+  const size_t nseg = (size_t)nb * W;
+  const int mc = min_count < 0 ? h->p.min_count : min_count;
+  const bool dedup = h->kw == 1 && !h->no_dedup;
+  static const bool off = [] { const char *e = getenv("SHK_NO_FAST"); return e && e[0] == '1'; }();
+  uint64_t run = 0;
+  uint64_t base[64];
+  for (uint32_t s = 0; s < W && s < 64; ++s) { base[s] = run; run += recv_records[s]; }
+  uint64_t bound = n_instances / ((uint64_t)std::max(mc, 0) + 1) + 1;
+  bool fast = !off && !histogram_only && (int)W <= std::min(64, shard_max_world()) && nb > 0 && h->ratio_est > 0 && h->ovf_cap > 0 &&
+              (!dedup || h->uq_cap > 0) && h->shard_cal_nb == nb && h->shard_cal_world == W && !h->shard_fast_banned &&
+              run <= 0xFFFFFFFFull && bound <= 0xFFFFFFF0ull && (W == 1 || (uint32_t)count_max_group() / W >= 1);
+  if (run && !d_recv) { set_error("null receive buffer"); return SHK_ERR_BAD_ARG; }
+  if (fast) {
+    SHK_TRY(shard_count_steady(h, d_recv, W, nb, run, n_instances, bound, mc, dedup, [&] {
+      return launch_shard_segments(d_recv_fill, nb, W, base, h->seg_off.as<uint64_t>(), h->seg_cnt.as<uint32_t>(),
+                                   h->shard_btot.as<uint64_t>(), h->stream);
+    }, fast));
+    if (fast) return SHK_OK;
+  }
   // host-planned: fetch the fills
   SHK_TRY(h->hfill2.ensure_host(nseg * 8 + 8));
   if (nseg) SHK_CUDA(cudaMemcpyAsync(h->hfill2.p, d_recv_fill, nseg * 8, cudaMemcpyDeviceToHost, h->stream));
@@ -1900,6 +1926,31 @@ shk_status shk_shard_count_device(shk_asm *h, const void *d_recv, const uint64_t
   if (st == SHK_OK && !histogram_only) { h->shard_cal_nb = nb; h->shard_cal_world = W; }
   return st;
 }
+
+}  // extern "C"
+// what shk_shard_count_device checks before it takes the steady-state count, as far as this rank alone can tell
+bool shk_internal_shard_pull_ready(shk_asm *h, uint32_t W, uint32_t nb) {
+  static const bool off = [] { const char *e = getenv("SHK_NO_FAST"); return e && e[0] == '1'; }();
+  const bool dedup = h->kw == 1 && !h->no_dedup;
+  return !off && (int)W <= std::min(64, shard_max_world()) && nb > 0 && h->ratio_est > 0 && h->ovf_cap > 0 && (!dedup || h->uq_cap > 0) &&
+         h->shard_cal_nb == nb && h->shard_cal_world == W && !h->shard_fast_banned && (W == 1 || (uint32_t)count_max_group() / W >= 1);
+}
+shk_status shk_internal_shard_count_pull(shk_asm *h, uint32_t W, uint32_t nb, uint64_t run, uint64_t n_instances, int mc,
+                                         const uint32_t *rcap, const uint64_t *const *fill, const uint64_t *base, bool *took) {
+  const bool dedup = h->kw == 1 && !h->no_dedup;
+  const uint64_t bound = n_instances / ((uint64_t)std::max(mc, 0) + 1) + 1;
+  bool fast = shk_internal_shard_pull_ready(h, W, nb) && run <= 0xFFFFFFFFull && bound <= 0xFFFFFFF0ull;
+  if (fast) {
+    const uint32_t rb = (uint32_t)record_bytes(h->kw);
+    SHK_TRY(shard_count_steady(h, nullptr, W, nb, run, n_instances, bound, mc, dedup, [&] {
+      return launch_shard_segments_pull(W, rcap, fill, base, nb, rb, h->seg_off.as<uint64_t>(), h->seg_cnt.as<uint32_t>(),
+                                        h->shard_btot.as<uint64_t>(), h->stream);
+    }, fast));
+  }
+  *took = fast;
+  return SHK_OK;
+}
+extern "C" {
 
 shk_status shk_shard_local_nodes(shk_asm *h, void *d_lo, void *d_hi, void *d_count, void *d_raw, size_t cap) {
   SHK_TRY(require_device(h));

@@ -480,6 +480,14 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
     // the group in segment units (group_start counts segments; the self-planner counts buckets)
     const u32 sb0 = self_plan ? b0 * sp.spb : b0, snb = self_plan ? nb * sp.spb : nb;
     u32 total = gpre[snb];
+    // record idx of the group's segment lo: a bucket region of the local cut (no segment table), an offset into the
+    // received records (recs + seg_off), or — recs == null — an ABSOLUTE address: the region of a bucket this rank
+    // owns inside the memory of the rank that cut it (peer memory over NVLink; shk_shard_count_pull)
+    auto seg_rec = [&](u32 lo, u32 idx) -> const typename RecOf<KW>::type * {
+      if (!seg_off) return recs + ((u64)(sb0 + lo) * rcap + idx);
+      const u64 v = seg_off[sb0 + lo];
+      return (recs ? recs + v : reinterpret_cast<const typename RecOf<KW>::type *>(v)) + idx;
+    };
     uint4 *myrec = nullptr; u32 *mycnt = nullptr;
     if (DEDUP) {
       // ---- phase 1: distinct canonical records of the group, with multiplicities ----
@@ -490,8 +498,7 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
       auto rec_ptr = [&](u32 f) {
         u32 lo = 0, hi = snb;
         while (hi - lo > 1) { u32 mid = (lo + hi) >> 1; if (gpre[mid] <= f) lo = mid; else hi = mid; }
-        const u64 sbase = seg_off ? seg_off[sb0 + lo] : (u64)(sb0 + lo) * rcap;
-        return reinterpret_cast<const uint4 *>(recs + (sbase + (f - gpre[lo])));
+        return reinterpret_cast<const uint4 *>(seg_rec(lo, f - gpre[lo]));
       };
       auto insert_record = [&](uint4 c) {
         u32 slot;
@@ -626,8 +633,7 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
           const u32 f = c0 + (u32)tid;
           u32 lo = 0, hi = snb;                             // segment with gpre[lo] <= f < gpre[lo+1]
           while (hi - lo > 1) { u32 mid = (lo + hi) >> 1; if (gpre[mid] <= f) lo = mid; else hi = mid; }
-          const u64 sbase = seg_off ? seg_off[sb0 + lo] : (u64)(sb0 + lo) * rcap;
-          const uint4 *src = reinterpret_cast<const uint4 *>(recs + (sbase + (f - gpre[lo])));
+          const uint4 *src = reinterpret_cast<const uint4 *>(seg_rec(lo, f - gpre[lo]));
           ra = __ldcs(src); rb = __ldcs(src + 1);
           if (SHK_CB_DEDUP2) canon_record2(ra, rb, k);
           stage[2 * tid] = ra; stage[2 * tid + 1] = rb;
@@ -730,8 +736,7 @@ k_count_buckets(const typename RecOf<KW>::type *__restrict__ recs, const u64 *__
       } else if (f < total) {
         u32 lo = 0, hi = snb;                             // segment with gpre[lo] <= f < gpre[lo+1]
         while (hi - lo > 1) { u32 mid = (lo + hi) >> 1; if (gpre[mid] <= f) lo = mid; else hi = mid; }
-        const u64 sbase = seg_off ? seg_off[sb0 + lo] : (u64)(sb0 + lo) * rcap;
-        const uint4 *src = reinterpret_cast<const uint4 *>(recs + (sbase + (f - gpre[lo])));
+        const uint4 *src = reinterpret_cast<const uint4 *>(seg_rec(lo, f - gpre[lo]));
         if (KW == 1) {
           uint4 r = __ldcs(src); wst[lane] = r;
           n = r.x & 31u; hasl = (r.x >> 5) & 1u; hasr = (r.x >> 6) & 1u;

@@ -152,7 +152,9 @@ struct shk_asm {
   size_t arena_off_slots = 0, arena_off_off = 0, arena_off_edges = 0, arena_off_coh = 0, arena_off_lo = 0, arena_off_hi = 0;
   unsigned char arena_ipc[64] = {0};   // cudaIpcMemHandle_t of the arena allocation `arena_exported`
   void *arena_exported = nullptr; size_t arena_exported_cap = 0;
-  shk_peer_map peer_maps[64][1];
+  unsigned char rec_ipc[2][64] = {{0}};     // cudaIpcMemHandle_t of the record regions / their fills (shk_shard_records_publish)
+  void *rec_exported[2] = {nullptr, nullptr}; size_t rec_exported_cap[2] = {0, 0};
+  shk_peer_map peer_maps[64][3];       // [rank][0 graph arena, 1 record regions, 2 region fills]
   shk::DevBuf c_succ, c_wlen, c_wsum, c_pd, c_split, c_tail, c_len, c_sum, c_uoh, c_kcnt, c_klen, c_tmp, c_rot, c_cq, c_circ, c_mlo, c_mhi;
   // sharded steady-state count (shk_shard_count_device): calibrated by a host-planned run over this many owned buckets / ranks
   uint32_t shard_cal_nb = 0, shard_cal_world = 0;
@@ -208,3 +210,7 @@ shk_status fetch_unitigs(shk_asm *h);
 extern "C" shk_status shk_internal_flush_batch(shk_asm *h, bool final_batch);
 extern "C" shk_status shk_internal_finish_preprocess(shk_asm *h, const char *mode);
 extern "C" void shk_internal_build_pre_json(shk_asm *h);
+// owner-side count straight out of the source ranks' regions (shk_shard.cu maps them, shk_api.cu counts)
+shk_status shk_internal_shard_count_pull(shk_asm *h, uint32_t W, uint32_t nb, uint64_t run, uint64_t n_instances, int mc,
+                                         const uint32_t *rcap, const uint64_t *const *fill, const uint64_t *base, bool *took);
+bool shk_internal_shard_pull_ready(shk_asm *h, uint32_t W, uint32_t nb);

@@ -749,18 +749,22 @@ k_shard_bucket_totals(const u64 *__restrict__ fill, u32 nb, u32 W, u64 *__restri
 struct ShardRanges { u32 n; u32 start[SHK_MAX_WORLD + 1]; };
 
 __global__ void __launch_bounds__(1024)
-k_shard_send_plan(const u64 *__restrict__ fill, u32 rcap, ShardRanges rg, u64 *__restrict__ off, u64 *__restrict__ totals /* [n] + max fill */) {
+k_shard_send_plan(const u64 *__restrict__ fill, u32 rcap, ShardRanges rg, u64 *__restrict__ off,
+                  u64 *__restrict__ totals /* [n] records per owner, [n] max fill, [n + 1 ..] k-mer instances per owner */) {
   __shared__ u32 wsum[32];
   __shared__ u64 carry;
   const u32 s = blockIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const u32 b0 = rg.start[s], b1 = rg.start[s + 1];
   if (threadIdx.x == 0) carry = 0;
   u32 mx = 0;
+  u64 kk = 0;
   __syncthreads();
   for (u32 j0 = b0; j0 < b1; j0 += 1024) {
     const u32 j = j0 + threadIdx.x;
-    const u32 raw = j < b1 ? (u32)fill[j] : 0u, f = min(raw, rcap);
+    const u64 fv = j < b1 ? fill[j] : 0ull;
+    const u32 raw = (u32)fv, f = min(raw, rcap);
     mx = max(mx, raw);
+    kk += (u32)(fv >> 32);
     u32 inc = f;
     for (int o = 1; o < 32; o <<= 1) { u32 v = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += v; }
     if (lane == 31) wsum[warp] = inc;
@@ -778,7 +782,37 @@ k_shard_send_plan(const u64 *__restrict__ fill, u32 rcap, ShardRanges rg, u64 *_
   }
   for (int o = 16; o; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
   if (lane == 0 && mx) atomicMax(reinterpret_cast<u32 *>(totals + rg.n), mx);
+  for (int o = 16; o; o >>= 1) kk += __shfl_xor_sync(0xffffffffu, kk, o);
+  if (lane == 0 && kk) atomicAdd(reinterpret_cast<unsigned long long *>(totals + rg.n + 1 + s), (unsigned long long)kk);
   if (threadIdx.x == 0) totals[s] = carry;
+}
+
+// Pull form of the owner side (shk_shard_count_pull): nothing was exchanged.  Segment (owned bucket j, source s) IS
+// source s's region of that bucket, wherever it lies — this rank's own records or a peer's memory mapped over
+// NVLink: seg_off holds its absolute address, seg_cnt its fill (read from the source's fill array in place).
+struct PullSources { u32 n; u32 rcap[SHK_MAX_WORLD]; const u64 *fill[SHK_MAX_WORLD] /* the owned range of s's fills */;
+                     u64 base[SHK_MAX_WORLD] /* address of s's region of the first owned bucket */; };
+__global__ void __launch_bounds__(256)
+k_shard_segments_pull(PullSources src, u32 nb, u32 rec_bytes, u64 *__restrict__ seg_off, u32 *__restrict__ seg_cnt, u64 *__restrict__ bucket_tot) {
+  const u32 j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= nb) return;
+  u64 tr = 0, tk = 0;
+  for (u32 s = 0; s < src.n; ++s) {
+    const u64 f = __ldcg(src.fill[s] + j);
+    const u32 c = min((u32)f, src.rcap[s]);
+    seg_off[(size_t)j * src.n + s] = src.base[s] + (u64)j * src.rcap[s] * rec_bytes;
+    seg_cnt[(size_t)j * src.n + s] = c;
+    tr += c; tk += f >> 32;
+  }
+  bucket_tot[j] = tr | (tk << 32);
+}
+int launch_shard_segments_pull(uint32_t world, const uint32_t *rcap, const uint64_t *const *fill, const uint64_t *base, uint32_t nb,
+                               uint32_t rec_bytes, uint64_t *seg_off, uint32_t *seg_cnt, uint64_t *bucket_tot, cudaStream_t st) {
+  if (!nb || !world || world > SHK_MAX_WORLD) return 0;
+  PullSources src; src.n = world;
+  for (u32 i = 0; i < world; ++i) { src.rcap[i] = rcap[i]; src.fill[i] = (const u64 *)fill[i]; src.base[i] = base[i]; }
+  k_shard_segments_pull<<<blocks_for(nb, 256), 256, 0, st>>>(src, nb, rec_bytes, (u64 *)seg_off, seg_cnt, (u64 *)bucket_tot);
+  return 1;
 }
 
 int launch_shard_send_plan(const uint64_t *d_fill, uint32_t rcap, uint32_t world, const uint32_t *starts, uint64_t *off,

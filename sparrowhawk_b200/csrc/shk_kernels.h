@@ -68,6 +68,8 @@ int count_ctas(int kw = 1);   // CTAs of one K1b launch (k <= 31: also sizes the
 // (bucket[i] = their bucket, *cursor = how many — more than cap means some were dropped), then cap more for the same
 // records sorted by bucket (launch_spill_sort).  cap == 0 / null: records beyond a full region are dropped and counted.
 struct SpillArgs { uint32_t cap; uint32_t *cursor; uint32_t *bucket; };
+int launch_shard_segments_pull(uint32_t world, const uint32_t *rcap, const uint64_t *const *fill, const uint64_t *base, uint32_t nb,
+                               uint32_t rec_bytes, uint64_t *seg_off, uint32_t *seg_cnt, uint64_t *bucket_tot, cudaStream_t st);
 int launch_add_u64(uint64_t *p, uint64_t v, cudaStream_t st);   // *p += v (one thread)
 int launch_partition(int kw, const uint64_t *bases, const uint32_t *mask, uint64_t nwords, int k, uint32_t P,
                      uint32_t rcap, void *recs, uint64_t *bstat /* [P]: records | k-mers << 32 */, uint64_t *counters, cudaStream_t st,

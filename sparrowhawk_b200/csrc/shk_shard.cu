@@ -62,6 +62,83 @@ shk_status read_back(shk_asm *h, uint32_t *hs) {
 
 extern "C" {
 
+// ---- 0. the record exchange without an exchange: owners count straight out of the sources' regions ----------------
+// After K1a every rank holds, for EVERY bucket, a region of records (fixed stride rcap) and its fill.  Instead of
+// packing the regions densely, sending them through an all-to-all and counting the received copy, a rank publishes
+// its regions (two cudaIpc handles + the totals per owner) and the owner's K1b reads the regions of its buckets in
+// place — its own and, over NVLink / NVSwitch, those of every other rank: each record crosses the link once, as one
+// coalesced 16 / 32-byte load inside the kernel that consumes it, and no copy of the records is ever written.
+// The all-gather of the blobs is the barrier "every rank's K1a is complete"; the regions must stay untouched until
+// every owner's K1b has finished (any later collective of the step orders that).
+struct RecBlob {
+  cudaIpcMemHandle_t recs, fill;
+  uint32_t magic, P, rcap, kw, device, ready, world, rank;
+  uint64_t records_for[SHK_MAX_WORLD], kmers_for[SHK_MAX_WORLD];   // what this rank cut for every owner
+};
+static_assert(sizeof(RecBlob) <= SHK_REC_BLOB_BYTES, "record blob grew past its ABI size");
+const uint32_t REC_MAGIC = 0x53484B52u;   // "SHKR"
+
+shk_status shk_shard_records_publish(shk_asm *h, void *blob_out) {
+  SHK_TRY(require_device(h));
+  if (!h->counted || !h->shard_world || !blob_out) { set_error("shard_records_publish before shard_partition / null argument"); return SHK_ERR_STATE; }
+  const uint32_t W = h->shard_world, me = h->shard_rank, P = h->P;
+  RecBlob b; memset(&b, 0, sizeof b);
+  b.magic = REC_MAGIC; b.P = P; b.rcap = h->rcap; b.kw = (uint32_t)h->kw; b.device = (uint32_t)h->dev; b.world = W; b.rank = me;
+  const uint32_t nb = (uint32_t)((uint64_t)(me + 1) * P / W) - (uint32_t)((uint64_t)me * P / W);
+  bool ok = W <= SHK_MAX_WORLD && h->send_planned && h->skrecs.plain && h->bfill.plain && h->skrecs.p && h->bfill.p;
+  if (ok) {
+    shk::DevBuf *bufs[2] = {&h->skrecs, &h->bfill};
+    for (int i = 0; i < 2 && ok; ++i) {
+      if (bufs[i]->p != h->rec_exported[i] || bufs[i]->cap != h->rec_exported_cap[i]) {     // once per allocation
+        if (cudaIpcGetMemHandle((cudaIpcMemHandle_t *)h->rec_ipc[i], bufs[i]->p) != cudaSuccess) { cudaGetLastError(); ok = false; break; }
+        h->rec_exported[i] = bufs[i]->p; h->rec_exported_cap[i] = bufs[i]->cap;
+      }
+    }
+    memcpy(&b.recs, h->rec_ipc[0], 64); memcpy(&b.fill, h->rec_ipc[1], 64);
+  }
+  if (ok) {
+    const uint64_t *hs = (const uint64_t *)h->hsend.p;             // [W] records per owner, [W] max fill, [W + 1 ..] k-mers per owner
+    for (uint32_t r = 0; r < W; ++r) { b.records_for[r] = hs[r]; b.kmers_for[r] = hs[W + 1 + r]; }
+  }
+  b.ready = ok && shk_internal_shard_pull_ready(h, W, nb) ? 1u : 0u;
+  memset(blob_out, 0, SHK_REC_BLOB_BYTES);
+  memcpy(blob_out, &b, sizeof b);
+  return SHK_OK;
+}
+
+shk_status shk_shard_count_pull(shk_asm *h, const void *blobs, int min_count, int *took) {
+  SHK_TRY(require_device(h));
+  if (!h->counted || !h->shard_world || !blobs || !took) { set_error("shard_count_pull before shard_partition / null argument"); return SHK_ERR_STATE; }
+  *took = 0;
+  const uint32_t W = h->shard_world, me = h->shard_rank, P = h->P;
+  if (W > SHK_MAX_WORLD) return SHK_OK;
+  const uint32_t lo = (uint32_t)((uint64_t)me * P / W), nb = (uint32_t)((uint64_t)(me + 1) * P / W) - lo;
+  const size_t rb = record_bytes(h->kw);
+  uint32_t rcap[SHK_MAX_WORLD]; const uint64_t *fill[SHK_MAX_WORLD]; uint64_t base[SHK_MAX_WORLD];
+  uint64_t run = 0, inst = 0;
+  for (uint32_t r = 0; r < W; ++r) {
+    RecBlob b; memcpy(&b, (const uint8_t *)blobs + (size_t)r * SHK_REC_BLOB_BYTES, sizeof b);
+    if (b.magic != REC_MAGIC || b.P != P || b.kw != (uint32_t)h->kw || b.world != W || b.rank != r) {
+      set_error("record blob of rank %u does not belong to this run", r); return SHK_ERR_BAD_ARG;
+    }
+    if (!b.ready) return SHK_OK;                                     // some rank is not calibrated (or cannot export): the exchange path
+    const uint8_t *R; const uint64_t *F;
+    if (r == me) { R = (const uint8_t *)h->skrecs.p; F = h->bfill.as<uint64_t>(); }
+    else {
+      void *pr, *pf;
+      if (open_peer(h, r, 1, b.recs, &pr) != SHK_OK || open_peer(h, r, 2, b.fill, &pf) != SHK_OK) return SHK_OK;   // no peer memory: the exchange path
+      R = (const uint8_t *)pr; F = (const uint64_t *)pf;
+    }
+    rcap[r] = b.rcap; fill[r] = F + lo; base[r] = (uint64_t)(uintptr_t)(R + (size_t)lo * b.rcap * rb);
+    run += b.records_for[me]; inst += b.kmers_for[me];
+  }
+  static const bool fail_test = [] { const char *e = getenv("SHK_SHARD_PULL_FAIL"); return e && e[0] == '1'; }();
+  bool ok = false;
+  SHK_TRY(shk_internal_shard_count_pull(h, W, nb, run, inst, min_count < 0 ? h->p.min_count : min_count, rcap, fill, base, &ok));
+  *took = ok && !fail_test ? 1 : 0;
+  return SHK_OK;
+}
+
 // ---- 1. publish: this rank's index built over ITS nodes, the peer blob out -------------------------------------
 shk_status shk_shard_graph_publish(shk_asm *h, void *blob_out) {
   SHK_TRY(require_device(h));

@@ -87,6 +87,20 @@ class GpuEngine:
         check(self.lib.shk_shard_count_device(self.h._h, recv_buf.data_ptr() if recv_buf.numel() else None,
                                               recv_fill.data_ptr(), rr.ctypes.data, int(n_instances), 0, int(min_count)))
 
+    # ---- the record exchange without an exchange (include/shk.h shk_shard_records_publish / shk_shard_count_pull) ----
+    def records_publish(self):
+        blob = np.zeros(_ffi.REC_BLOB_BYTES, np.uint8)
+        check(self.lib.shk_shard_records_publish(self.h._h, blob.ctypes.data))
+        return blob
+
+    def count_pull(self, blobs, min_count):
+        """owner-side count straight out of the source ranks' regions (peer memory); False: not taken"""
+        import ctypes as C
+        b = np.ascontiguousarray(blobs, dtype=np.uint8)
+        took = C.c_int(0)
+        check(self.lib.shk_shard_count_pull(self.h._h, b.ctypes.data, int(min_count), C.byref(took)))
+        return bool(took.value)
+
     def local_counts(self):
         st = self.h.stats()
         return st["n_nodes"], int(self._instances_seen())
@@ -400,46 +414,71 @@ def sharded_run(eng, group=None, timings=None):
     lo_b, hi_b = shard_range(P, world, rank)
     n_own = hi_b - lo_b
 
-    # ---- K1a + pack ----
+    # ---- K1a ----
     send_records = eng.partition(P, world, rank)
     mark("partition")
     rw = eng.rec_words
-    send_buf = torch.empty(sum(send_records) * rw, **i64)
-    send_fill = torch.empty(P, **i64)
-    eng.pack(send_buf, send_fill)
-    mark("pack")
-
-    # ---- exchange: fills first (they size the receive buffer), then the records ----
-    fill_in = [shard_range(P, world, r)[1] - shard_range(P, world, r)[0] for r in range(world)]
-    recv_fill = torch.empty(world * n_own, **i64)
-    _a2a(recv_fill, send_fill, [n_own] * world, fill_in, group)
-    on_device = hasattr(eng, "count_device") and recv_fill.is_cuda and not eng.do_fit
-    if on_device:
-        # only the per-source sums cross to the host: records (sizes of the second all-to-all), k-mer instances
-        rf2 = recv_fill.view(world, n_own)
-        sums = torch.stack([(rf2 & 0xFFFFFFFF).sum(1), (rf2 >> 32).sum(1)]).cpu().numpy()
-        recv_records = [int(x) for x in sums[0]]
-        inst_local = int(sums[1].sum())
-        rf_host = None
-    else:
-        rf_host = recv_fill.cpu().numpy().view(np.uint64).reshape(world, n_own)
-        recv_records = [int((rf_host[s] & np.uint64(0xFFFFFFFF)).sum()) for s in range(world)]
-        inst_local = int((rf_host >> np.uint64(32)).sum())
-    recv_buf = torch.empty(sum(recv_records) * rw, **i64)
-    _a2a(recv_buf, send_buf, [n * rw for n in recv_records], [n * rw for n in send_records], group)
-    mark("all_to_all")
-
-    # ---- owner-side count, spectrum, filter ----
     used_mc = eng.min_count
-    if eng.do_fit:
-        eng.count(recv_buf, rf_host, True, 0)
-        hist = torch.from_numpy(eng.histogram().astype(np.int64)).to(dev)
-        _all_reduce(hist, group)
-        used_mc = eng.fit(hist.cpu().numpy().astype(np.uint64), eng.min_count)
-    if on_device:
-        eng.count_device(recv_buf, recv_fill, recv_records, inst_local, used_mc)
-    else:
-        eng.count(recv_buf, rf_host, False, used_mc)
+    recv_records = None
+
+    def exchange_and_count():
+        """pack -> all-to-all(fills) -> all-to-all(records) -> count on the owner (K1b/K2)"""
+        nonlocal used_mc, recv_records
+        send_buf = torch.empty(sum(send_records) * rw, **i64)
+        send_fill = torch.empty(P, **i64)
+        eng.pack(send_buf, send_fill)
+        mark("pack")
+        # fills first (they size the receive buffer), then the records
+        fill_in = [shard_range(P, world, r)[1] - shard_range(P, world, r)[0] for r in range(world)]
+        recv_fill = torch.empty(world * n_own, **i64)
+        _a2a(recv_fill, send_fill, [n_own] * world, fill_in, group)
+        on_device = hasattr(eng, "count_device") and recv_fill.is_cuda and not eng.do_fit
+        if on_device:
+            # only the per-source sums cross to the host: records (sizes of the second all-to-all), k-mer instances
+            rf2 = recv_fill.view(world, n_own)
+            sums = torch.stack([(rf2 & 0xFFFFFFFF).sum(1), (rf2 >> 32).sum(1)]).cpu().numpy()
+            recv_records = [int(x) for x in sums[0]]
+            inst_local = int(sums[1].sum())
+            rf_host = None
+        else:
+            rf_host = recv_fill.cpu().numpy().view(np.uint64).reshape(world, n_own)
+            recv_records = [int((rf_host[s] & np.uint64(0xFFFFFFFF)).sum()) for s in range(world)]
+            inst_local = int((rf_host >> np.uint64(32)).sum())
+        recv_buf = torch.empty(sum(recv_records) * rw, **i64)
+        _a2a(recv_buf, send_buf, [n * rw for n in recv_records], [n * rw for n in send_records], group)
+        mark("all_to_all")
+        # owner-side count, spectrum, filter
+        used_mc = eng.min_count
+        if eng.do_fit:
+            eng.count(recv_buf, rf_host, True, 0)
+            hist = torch.from_numpy(eng.histogram().astype(np.int64)).to(dev)
+            _all_reduce(hist, group)
+            used_mc = eng.fit(hist.cpu().numpy().astype(np.uint64), eng.min_count)
+        if on_device:
+            eng.count_device(recv_buf, recv_fill, recv_records, inst_local, used_mc)
+        else:
+            eng.count(recv_buf, rf_host, False, used_mc)
+        return inst_local
+
+    # ---- the owners count straight out of the sources' regions (peer memory over NVLink: no pack, no all-to-all, no
+    # copy of the records) when every rank is calibrated for it; the all-gather of the record blobs is the barrier
+    # "every rank's K1a is complete".  Otherwise — and on a fresh engine — pack + all-to-all + count. ----
+    pulled, pull_failed = False, 0
+    if hasattr(eng, "count_pull") and dev.type == "cuda" and not eng.do_fit and os.environ.get("SHK_SHARD_PULL", "1") != "0":
+        mine = torch.from_numpy(eng.records_publish()).to(dev)
+        flat = torch.empty(world * mine.numel(), dtype=torch.uint8, device=dev)
+        _ag_flat(flat, mine, group)
+        blobs = flat.cpu().numpy()
+        if all(_ffi.rec_blob_ready(blobs[r * _ffi.REC_BLOB_BYTES:(r + 1) * _ffi.REC_BLOB_BYTES]) for r in range(world)):
+            pulled = True
+            mark("pack"); mark("all_to_all")               # (nothing is packed or sent: "pack" = the all-gather of the blobs)
+            if eng.count_pull(blobs, used_mc):
+                inst_local = sum(_ffi.rec_blob_kmers_for(blobs[r * _ffi.REC_BLOB_BYTES:(r + 1) * _ffi.REC_BLOB_BYTES], rank) for r in range(world))
+                recv_records = [_ffi.rec_blob_records_for(blobs[r * _ffi.REC_BLOB_BYTES:(r + 1) * _ffi.REC_BLOB_BYTES], rank) for r in range(world)]
+            else:
+                pull_failed, inst_local = 1, 0             # (this rank's plan failed verification: every rank counts again, below)
+    if not pulled:
+        inst_local = exchange_and_count()
     n_local, _ = eng.local_counts()
     mark("count")
 
@@ -448,22 +487,34 @@ def sharded_run(eng, group=None, timings=None):
     # reduction is also the barrier "indices complete") ----
     peer_graph = hasattr(eng, "graph_publish") and os.environ.get("SHK_SHARD_GRAPH", "1") != "0"
     bw = _ffi.PEER_BLOB_BYTES // 8
-    red_np = np.zeros(502 + world + (world * bw if peer_graph else 0), np.int64)
-    red_np[:500] = eng.histogram().astype(np.int64)
-    red_np[500], red_np[501] = inst_local, eng.n_bases()
-    red_np[502 + rank] = n_local
-    if peer_graph:
-        red_np[502 + world + rank * bw: 502 + world + (rank + 1) * bw] = eng.graph_publish().view(np.int64)
-    red = torch.from_numpy(red_np).to(dev)
-    _all_reduce(red, group)
-    red_h = red.cpu().numpy()
+    def reduce_counts():
+        red_np = np.zeros(503 + world + (world * bw if peer_graph else 0), np.int64)
+        if not pull_failed:
+            red_np[:500] = eng.histogram().astype(np.int64)
+            red_np[500], red_np[501] = inst_local, eng.n_bases()
+            red_np[502 + rank] = n_local
+            if peer_graph:
+                red_np[503 + world + rank * bw: 503 + world + (rank + 1) * bw] = eng.graph_publish().view(np.int64)
+        red_np[502 + world] = pull_failed
+        red = torch.from_numpy(red_np).to(dev)
+        _all_reduce(red, group)
+        return red.cpu().numpy()
+
+    red_h = reduce_counts()
+    if red_h[502 + world]:
+        # some rank's in-place count did not stand: all of them take the exchange path for this step (the regions are
+        # still as K1a left them: nobody starts the next partition before this reduction)
+        pull_failed, pulled = 0, False
+        inst_local = exchange_and_count()
+        n_local, _ = eng.local_counts()
+        red_h = reduce_counts()
     g_hist = red_h[:500].astype(np.uint64)
     g_inst, g_bases = int(red_h[500]), int(red_h[501])
     counts = [int(c) for c in red_h[502:502 + world]]
     n_total = sum(counts)
     graph_mode = None
     if peer_graph:
-        blobs = np.ascontiguousarray(red_h[502 + world:]).view(np.uint8)
+        blobs = np.ascontiguousarray(red_h[503 + world:]).view(np.uint8)
         graph_mode = _sharded_graph(eng, group, blobs, counts, g_hist, g_inst, g_bases, used_mc, mark)
     if graph_mode is None:
         _replicated_graph(eng, group, counts, g_hist, g_inst, g_bases, used_mc, mark)
@@ -471,4 +522,5 @@ def sharded_run(eng, group=None, timings=None):
     return {"world": world, "n_buckets": P, "n_bases": g_bases, "n_positions": g_pos, "n_instances": g_inst,
             "n_nodes": n_total, "nodes_per_rank": counts, "used_min_count": used_mc, "histo": g_hist,
             "send_records": send_records, "recv_records": recv_records, "graph_mode": graph_mode,
+            "records": "pulled" if pulled else "exchanged",
             "a2a_bytes_out": int(sum(send_records[r] for r in range(world) if r != rank)) * rw * 8}

@@ -125,6 +125,7 @@ def main():
     opts = sys.argv[6:]
     do_fit = "fit" in opts
     expect_mode = next((x.split("=")[1] for x in opts if x.startswith("expect=")), None)
+    expect_records = next((x.split("=")[1] for x in opts if x.startswith("records=")), None)
     circular = "circular" in opts
     if mode == "nccl":
         local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -175,7 +176,8 @@ def main():
         assert ((b[a:z] >= blo) & (b[a:z] < bhi)).all() and not ((b[:a] >= blo) & (b[:a] < bhi)).any()
         assert info["recv_records"][rank] == info["send_records"][rank]
     else:
-        gpu_rank_checks(mode, rank, world, k, min_count, min_qual, seq, qual, o, so, do_fit=do_fit, expect_mode=expect_mode)
+        gpu_rank_checks(mode, rank, world, k, min_count, min_qual, seq, qual, o, so, do_fit=do_fit, expect_mode=expect_mode,
+                        expect_records=expect_records)
     dist.barrier()
     dist.destroy_process_group()
     print(f"rank {rank}/{world} ok: {so['n_nodes']} nodes, {so['n_unitigs']} unitigs")
@@ -208,7 +210,8 @@ def gathered_kmers(h, info):
     return tuple(np.concatenate([p[i] for p in parts]) for i in range(5))
 
 
-def gpu_rank_checks(mode, rank, world, k, min_count, min_qual, seq, qual, o, so, do_fit=False, expect_mode=None):
+def gpu_rank_checks(mode, rank, world, k, min_count, min_qual, seq, qual, o, so, do_fit=False, expect_mode=None,
+                    expect_records=None):
     """the real C ABI engine on this rank: mode "gpu" = gloo, every rank on cuda:0; mode "nccl" = one device per rank"""
     import json
     from parity import assert_parity, canon_link_tuples, canon_links, oracle_graph
@@ -219,10 +222,10 @@ def gpu_rank_checks(mode, rank, world, k, min_count, min_qual, seq, qual, o, so,
     h = AssemblyHelper.new(k, False, min_count, min_qual, 0, False, do_fit, False, False, device=devi)
     h.load_reads(seq, qual)
     eng = GpuEngine(h, torch.device("cuda", devi))
-    planned, modes = [], []
-    for _ in range(3):                 # the first pass calibrates (host-planned count); later ones reuse buffers and
-        info = sharded_run(eng)        # estimates and count with the fills left on the device (shk_shard_count_device)
-        planned.append(h.stats()["device_planned"]); modes.append(info["graph_mode"])
+    planned, modes, recs = [], [], []
+    for _ in range(3):                 # the first pass calibrates (pack + all-to-all + host-planned count); later ones
+        info = sharded_run(eng)        # count straight out of the source ranks' regions (shk_shard_count_pull)
+        planned.append(h.stats()["device_planned"]); modes.append(info["graph_mode"]); recs.append(info["records"])
         assert info["n_nodes"] == so["n_nodes"], (info["n_nodes"], so["n_nodes"])
         assert_parity(h, o, check_table=False, kmers=gathered_kmers(h, info))
         assert json.loads(h.get_preprocessing_info())["nkmers"] == so["n_nodes"]
@@ -231,7 +234,9 @@ def gpu_rank_checks(mode, rank, world, k, min_count, min_qual, seq, qual, o, so,
     lf, lt = h.export_links()
     ou, _okc, _oc, olinks = oracle_graph(o, k)
     assert canon_links(units, lf, lt) == canon_link_tuples(ou, olinks), "unitig links differ"
-    print(f"rank {rank}: device-planned count per pass {planned}, graph stage {modes}")
+    print(f"rank {rank}: device-planned count per pass {planned}, graph stage {modes}, records {recs}")
+    if expect_records:
+        assert recs[0] == "exchanged" and recs[-1] == expect_records, recs
     assert planned[-1] == 1 or do_fit, planned
     if expect_mode:
         assert modes == [expect_mode] * 3, modes

@@ -134,6 +134,25 @@ def test_spill_path_and_replan(monkeypatch):
     assert_parity(h, o)
 
 
+def test_preprocess_files_parallel_split(tmp_path, monkeypatch):
+    """Bulk ingest of two PLAIN FASTQ files, each split over four threads in 64 KB chunks (batches reach the device
+    in any order), with every chunk border guessed wrong as well: same k-mers, same graph."""
+    seq, qual = synth.reads(8, 30_000, 20.0, 0.01)
+    p1, p2 = str(tmp_path / "b_1.fastq"), str(tmp_path / "b_2.fastq")
+    synth.write_fastq(p1, p2, seq, qual)
+    o = run_oracle(seq, qual, 31, 2, 20)
+    monkeypatch.setenv("SHK_FASTQ_CHUNK", "65536")
+    monkeypatch.setenv("SHK_FASTQ_THREADS", "4")
+    for bad in ("0", "1"):
+        monkeypatch.setenv("SHK_FASTQ_BAD_GUESS", bad)
+        h = AssemblyHelper.new(31, False, 2, 20, 0, False, False, True, True)
+        h.preprocess(p1, p2)
+        assert h.stats()["n_bases"] == o.stats()["n_bases"]
+        h.assemble()
+        assert_parity(h, o, check_table=False)
+        h.close()
+
+
 def test_chunked_equals_bulk(tmp_path):
     seq, qual = synth.reads(6, 20_000, 20.0, 0.01)
     p1, p2 = str(tmp_path / "a_1.fastq"), str(tmp_path / "a_2.fastq.gz")

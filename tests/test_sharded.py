@@ -56,7 +56,19 @@ def test_sharded_orchestration_gloo_cpu(world, k):
 def test_sharded_gpu_matches_oracle(world, k, G):
     """gloo, every rank on cuda:0: the sharded graph stage (peer memory between the processes, chains joined by
     the chain-level ranking) must be the one that ran, and every rank must hold the oracle's graph."""
-    _launch(world, "gpu", k, 3, G, 30.0, "expect=sharded")
+    _launch(world, "gpu", k, 3, G, 30.0, "expect=sharded", "records=pulled")
+
+
+@pytest.mark.gpu
+def test_sharded_gpu_pull_falls_back_to_the_exchange(monkeypatch):
+    """the owners count straight out of the sources' regions (no pack, no all-to-all) from the second pass on; a rank
+    whose in-place count does not stand (forced here) makes every rank take the exchange path for that step; with the
+    export switched off nothing is ever pulled — same graph every time"""
+    monkeypatch.setenv("SHK_SHARD_PULL_FAIL", "1")
+    _launch(2, "gpu", 31, 3, 50000, 30.0, "expect=sharded", "records=exchanged")
+    monkeypatch.delenv("SHK_SHARD_PULL_FAIL")
+    monkeypatch.setenv("SHK_SHARD_PULL", "0")
+    _launch(2, "gpu", 31, 3, 50000, 30.0, "expect=sharded", "records=exchanged")
 
 
 @pytest.mark.gpu
@@ -93,7 +105,7 @@ def test_sharded_nccl_matches_oracle(world, k, G):
     every rank.  Needs as many devices as ranks."""
     if _n_devices() < world:
         pytest.skip(f"needs {world} devices")
-    _launch(world, "nccl", k, 3, G, 30.0, "expect=sharded")
+    _launch(world, "nccl", k, 3, G, 30.0, "expect=sharded", "records=pulled")
 
 
 @pytest.mark.gpu
