@@ -480,8 +480,12 @@ def sharded_arm(args, name, w, ctx, steps, warmup, with_e2e=True, with_cold=Fals
     def harvest():
         m = getattr(step, "marks", None)
         if m:
+            m[-1][1].synchronize()            # (the last boundary may still be in flight behind the step's final launches)
             for (_, a, _h0), (n, b, hs) in zip(m[:-1], m[1:]):
-                stage_acc.setdefault(n, []).append(a.elapsed_time(b))
+                try:
+                    stage_acc.setdefault(n, []).append(a.elapsed_time(b))
+                except RuntimeError:          # a boundary that never completed says nothing; the step time does not depend on it
+                    continue
                 host_acc.setdefault(n, []).append(hs * 1e3)
 
     # ---- device-resident arm ------------------------------------------------

@@ -463,8 +463,15 @@ def sharded_run(eng, group=None, timings=None):
     # ---- the owners count straight out of the sources' regions (peer memory over NVLink: no pack, no all-to-all, no
     # copy of the records) when every rank is calibrated for it; the all-gather of the record blobs is the barrier
     # "every rank's K1a is complete".  Otherwise — and on a fresh engine — pack + all-to-all + count. ----
+    # Measured on B200 boxes (config B per rank): at 2 ranks the in-place count costs what the local one does (2.58 vs
+    # 2.54 ms) and pack + all-to-all (1.3 ms) are gone: step 8.25 -> 7.16 ms.  At 8 ranks K1b reads 7/8 of its records
+    # out of seven peer mappings (8 GB mapped per rank) and takes 5.4 ms instead of 3.0 — more than the exchange
+    # costs (step 11.9 vs 11.4 ms): the same loss of TLB reach on peer mappings that K3' ran into.  So the records
+    # are pulled up to SHK_SHARD_PULL_MAX_WORLD ranks (default 2) and exchanged beyond.
     pulled, pull_failed = False, 0
-    if hasattr(eng, "count_pull") and dev.type == "cuda" and not eng.do_fit and os.environ.get("SHK_SHARD_PULL", "1") != "0":
+    pull_max_world = int(os.environ.get("SHK_SHARD_PULL_MAX_WORLD", "2"))
+    if (hasattr(eng, "count_pull") and dev.type == "cuda" and not eng.do_fit and os.environ.get("SHK_SHARD_PULL", "1") != "0"
+            and world <= pull_max_world):
         mine = torch.from_numpy(eng.records_publish()).to(dev)
         flat = torch.empty(world * mine.numel(), dtype=torch.uint8, device=dev)
         _ag_flat(flat, mine, group)

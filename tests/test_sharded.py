@@ -25,6 +25,7 @@ def _free_port():
 
 
 def _launch(world, *args, timeout=600):
+    os.environ.setdefault("SHK_SHARD_PULL_MAX_WORLD", "8")       # (the product pulls up to 2 ranks: the tests cover more)
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
            "--master-addr", "127.0.0.1", "--master-port", str(_free_port()), WORKER, *[str(a) for a in args]]
     env = dict(os.environ, OMP_NUM_THREADS="2")
