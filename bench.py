@@ -571,7 +571,12 @@ def sharded_arm(args, name, w, ctx, steps, warmup, with_e2e=True, with_cold=Fals
         # bytes that cross the link per step: the sequence characters, and the quality characters or — when the
         # steady-state load took the quality test on the host cores — one bit per position
         h2d = int(nbytes + (4 * ((nbytes + 31) // 32) if s2["host_qual_bits"] else nbytes))
+        # hybrid load: the slices the host cores packed themselves crossed as 0.375 bytes per position (equal slices)
+        n_sl, n_hp = int(s2.get("load_slices", 0)), int(s2.get("host_packed_slices", 0))
+        if s2["host_qual_bits"] and n_sl and n_hp:
+            h2d = int((n_sl - n_hp) / n_sl * (nbytes + nbytes / 8.0) + n_hp / n_sl * nbytes * 0.375)
         e2e = {"value": total_bases / (ms_e2e * 1e-3), "unit": "bases/s", "h2d_bytes_per_step": h2d * world,
+               "host_packed_slices": "%d of %d (last call)" % (n_hp, n_sl) if n_sl else None,
                "host_quality_bits": bool(s2["host_qual_bits"]), "host_quality_wait_ms": max(0, s2["host_qual_bits"] - 1) / 1e3,
                "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e, "calls": calls,
                "call_ms": {n: round(sum(v[1:]) / max(1, len(v) - 1), 3) for n, v in call_ms.items()},
