@@ -470,6 +470,9 @@ static shk_status load_reads_hybrid(shk_asm *h, const uint8_t *seq, const uint8_
     SHK_CUDA(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
     for (auto &e : h->copy_ev) SHK_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
   }
+  // the pinned staging areas below are rewritten by the workers at once: the copies a previous load queued out of
+  // them must have left (they have, unless the caller loads twice without ever synchronising)
+  SHK_CUDA(cudaStreamSynchronize(h->copy_stream));
   const uint64_t total = (n + 31) / 32;
   const int hp_first = NS / 2;                                       // the host packs slices hp_first .. NS-1 at most
   const uint64_t hp_w0 = (uint64_t)hp_first * slice / 32, hp_words = total - std::min(total, hp_w0);
