@@ -470,7 +470,7 @@ def sharded_run(eng, group=None, timings=None):
     # are pulled up to SHK_SHARD_PULL_MAX_WORLD ranks (default 2) and exchanged beyond.
     pulled, pull_failed = False, 0
     pull_max_world = int(os.environ.get("SHK_SHARD_PULL_MAX_WORLD", "2"))
-    if (hasattr(eng, "count_pull") and dev.type == "cuda" and not eng.do_fit and os.environ.get("SHK_SHARD_PULL", "1") != "0"
+    if (hasattr(eng, "count_pull") and not eng.do_fit and os.environ.get("SHK_SHARD_PULL", "1") != "0"
             and world <= pull_max_world):
         mine = torch.from_numpy(eng.records_publish()).to(dev)
         flat = torch.empty(world * mine.numel(), dtype=torch.uint8, device=dev)

@@ -80,6 +80,7 @@ class CpuEngine:
         send_fill.copy_(torch.from_numpy(self.fill.view(np.int64)))
 
     def count(self, recv_buf, recv_fill_host, histogram_only, min_count):
+        self.calibrated = True
         r = recv_buf.numpy().view(np.uint64).reshape(-1, 4)
         assert r.shape[0] == int((recv_fill_host & np.uint64(0xFFFFFFFF)).sum())
         acc = {}
@@ -97,6 +98,41 @@ class CpuEngine:
 
     def local_counts(self):
         return len(self.nodes[0]), 0
+
+    # ---- stand-in for the record regions published as peer memory: files in a directory every rank sees ----
+    def enable_pull(self, share_dir, rank, world, fail_on=()):
+        self.share, self.rank, self.world, self.fail_on, self.passes, self.calibrated = share_dir, rank, world, set(fail_on), 0, False
+        self.records_publish, self.count_pull = self._records_publish, self._count_pull     # (dist.py looks for count_pull)
+
+    def _records_publish(self):
+        from sparrowhawk_b200 import _ffi
+        self.passes += 1
+        P = len(self.fill)
+        blob = np.zeros(_ffi.REC_BLOB_BYTES, np.uint8)
+        blob[128:160].view(np.uint32)[5] = 1 if self.calibrated else 0
+        cnt, km = (self.fill & np.uint64(0xFFFFFFFF)), (self.fill >> np.uint64(32))
+        for r in range(self.world):
+            lo, hi = shard_range(P, self.world, r)
+            blob[160:160 + 512].view(np.uint64)[r] = cnt[lo:hi].sum()
+            blob[160 + 512:160 + 1024].view(np.uint64)[r] = km[lo:hi].sum()
+        np.save(os.path.join(self.share, f"recs_{self.rank}.npy"), self.recs)
+        np.save(os.path.join(self.share, f"fill_{self.rank}.npy"), self.fill)
+        return blob
+
+    def _count_pull(self, blobs, min_count):
+        if (self.passes, self.rank) in self.fail_on:
+            return False                              # "this rank's plan failed verification"
+        P = len(self.fill)
+        lo, hi = shard_range(P, self.world, self.rank)
+        parts, fills = [], []
+        for r in range(self.world):                   # the regions of MY buckets out of every rank's records, in place
+            recs, fill = np.load(os.path.join(self.share, f"recs_{r}.npy")), np.load(os.path.join(self.share, f"fill_{r}.npy"))
+            cnt = (fill & np.uint64(0xFFFFFFFF)).astype(np.int64)
+            off = np.concatenate([[0], np.cumsum(cnt)])
+            parts.append(recs[off[lo]:off[hi]]); fills.append(fill[lo:hi])
+        buf = torch.from_numpy(np.concatenate(parts).reshape(-1).view(np.int64).copy())
+        self.count(buf, np.stack(fills), False, min_count)
+        return True
 
     def histogram(self):
         return self.hist
@@ -159,7 +195,18 @@ def main():
     so = o.stats()
     if mode == "cpu":
         eng = CpuEngine(seq, qual, k, min_count, min_qual)
-        info = sharded_run(eng)
+        if "pull" in opts:
+            # the orchestration of the in-place count: pass 1 exchanges (nobody is calibrated), pass 2 pulls, in pass 3
+            # the count of rank 1 "fails verification" and EVERY rank must take the exchange for that step
+            eng.enable_pull(os.environ["SHK_TEST_SHARE"], rank, world, fail_on={(3, 1 % world)})
+            seen = []
+            for _ in range(3):
+                info = sharded_run(eng)
+                seen.append(info["records"])
+                assert info["n_nodes"] == so["n_nodes"] and np.array_equal(info["histo"], o.histogram()), seen
+            assert seen == ["exchanged", "pulled", "exchanged"], seen
+        else:
+            info = sharded_run(eng)
         assert info["n_bases"] == so["n_bases"] and info["n_instances"] == so["n_instances"], (info, so)
         assert np.array_equal(info["histo"], o.histogram()), "reduced spectrum differs"
         assert info["n_nodes"] == so["n_nodes"] and sum(info["nodes_per_rank"]) == so["n_nodes"]

@@ -52,6 +52,15 @@ def test_sharded_orchestration_gloo_cpu(world, k):
     _launch(world, "cpu", k, 2, 3000, 12.0)
 
 
+@pytest.mark.parametrize("world", [2, 3])
+def test_sharded_pull_orchestration_gloo_cpu(world, tmp_path, monkeypatch):
+    """dist.py's in-place count on CPU stand-ins (the published regions are files every rank sees): all ranks must
+    agree on exchanging while one is uncalibrated, pull once all are ready, and ALL fall back to the exchange in the
+    step in which ONE rank's count does not stand"""
+    monkeypatch.setenv("SHK_TEST_SHARE", str(tmp_path))
+    _launch(world, "cpu", 31, 2, 3000, 12.0, "pull")
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("world,k,G", [(2, 31, 60000), (2, 63, 40000), (3, 31, 30000), (1, 31, 30000)])
 def test_sharded_gpu_matches_oracle(world, k, G):
