@@ -183,6 +183,8 @@ extern "C" {
     pub fn shk_fit_min_count(histo: *const u64, fallback: c_int) -> c_int;
     pub fn shk_shard_records_publish(h: *mut shk_asm, blob_out: *mut c_void) -> shk_status;
     pub fn shk_shard_count_pull(h: *mut shk_asm, blobs: *const c_void, min_count: c_int, took: *mut c_int) -> shk_status;
+    pub fn shk_asm_assemble_host(h: *mut shk_asm, seq: *const c_char, offsets: *const u64, kmer_count_sum: *const u64, circular: *const u8,
+                                 n_unitigs: usize, link_from: *const u32, link_to: *const u32, n_links: usize) -> shk_status;
     pub fn shk_fastq_stats(path: *const c_char, threads: c_int, chunk_bytes: u64, bad_guesses: c_int, out4: *mut u64) -> shk_status;
     /// Allocation-free spectrum of a small packed read set (device pointers; at most 2^20 positions, k odd 3..31);
     /// no counterpart in the reference.  d_out: 503 u64 on the device.  Calls that overlap on one GPU race.

@@ -131,6 +131,16 @@ shk_status shk_asm_assemble(shk_asm *h);
  * outgfav2} — Assembler.ts:7-13,127 */
 shk_status shk_asm_get_assembly(shk_asm *h, const char **json, size_t *len);
 
+/* The host tail of shk_asm_assemble on a unitig graph the CALLER supplies — the arrays of shk_export_unitigs /
+ * shk_export_unitig_counts / shk_export_links, from this library (e.g. another rank's, or a saved run) or from
+ * anywhere else: host cleaning (the handle's no_dead_end_removal / no_bubble_collapse flags), canonical order, the
+ * four texts.  Pure host code: no device is needed or touched; the result is read with shk_asm_get_assembly /
+ * shk_asm_contigs as after shk_asm_assemble.  Reference analogue: the second half of assemble()
+ * (AssemblyPage.vue:595-603 assembly:correct_graph / collapse_graph / saving). */
+shk_status shk_asm_assemble_host(shk_asm *h, const char *seq, const uint64_t *offsets, const uint64_t *kmer_count_sum,
+                                 const uint8_t *circular, size_t n_unitigs, const uint32_t *link_from,
+                                 const uint32_t *link_to, size_t n_links);
+
 /* Thread-local message of the last failing call (reference: panic text). */
 const char *shk_last_error(void);
 int shk_abi_version(void);

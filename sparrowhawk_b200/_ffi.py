@@ -121,6 +121,7 @@ SYMBOLS = {
     "shk_fit_min_count": (C.c_int, [C.c_void_p, C.c_int]),
     "shk_shard_records_publish": (C.c_int, [_H, C.c_void_p]),
     "shk_shard_count_pull": (C.c_int, [_H, C.c_void_p, C.c_int, C.c_void_p]),
+    "shk_asm_assemble_host": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_size_t]),
     "shk_fastq_stats": (C.c_int, [C.c_char_p, C.c_int, C.c_uint64, C.c_int, C.c_void_p]),
     # sharded graph stage (peer memory)
     "shk_shard_graph_publish": (C.c_int, [_H, C.c_void_p]),

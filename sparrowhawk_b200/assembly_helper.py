@@ -149,6 +149,17 @@ class AssemblyHelper:
     def assemble(self):
         check(self._lib.shk_asm_assemble(self._h))
 
+    def assemble_host(self, seqs, kc, circ, link_from, link_to):
+        """The host tail of assemble() on a unitig graph the caller supplies (shk_asm_assemble_host): cleaning, canonical
+        order and the four texts; needs no device.  Read the result with get_assembly() / contigs()."""
+        blob = "".join(seqs).encode()
+        off = np.zeros(len(seqs) + 1, np.uint64)
+        off[1:] = np.cumsum([len(x) for x in seqs], dtype=np.uint64)
+        kc = np.ascontiguousarray(kc, np.uint64); circ = np.ascontiguousarray(circ, np.uint8)
+        lf = np.ascontiguousarray(link_from, np.uint32); lt = np.ascontiguousarray(link_to, np.uint32)
+        check(self._lib.shk_asm_assemble_host(self._h, blob, off.ctypes.data, kc.ctypes.data, circ.ctypes.data, len(seqs),
+                                              lf.ctypes.data, lt.ctypes.data, len(lf)))
+
     def get_assembly(self) -> str:
         s, n = C.c_void_p(), C.c_size_t()
         check(self._lib.shk_asm_get_assembly(self._h, C.byref(s), C.byref(n)))

@@ -630,6 +630,37 @@ shk_status fastq_stats(const char *path, int threads, uint64_t chunk_bytes, int 
 
 }  // namespace shk
 
+// The host tail of assemble() on a unitig graph the caller supplies (include/shk.h): cleaning, canonical order, the
+// four texts.  No device is touched.
+extern "C" shk_status shk_asm_assemble_host(shk_asm *h, const char *seq, const uint64_t *offsets, const uint64_t *kmer_count_sum,
+                                            const uint8_t *circular, size_t n_unitigs, const uint32_t *link_from,
+                                            const uint32_t *link_to, size_t n_links) {
+  if (!h || (n_unitigs && (!seq || !offsets || !kmer_count_sum)) || (n_links && (!link_from || !link_to))) {
+    shk::set_error("null argument"); return SHK_ERR_BAD_ARG;
+  }
+  const size_t k = (size_t)h->p.k;
+  for (size_t i = 0; i < n_unitigs; ++i)
+    if (offsets[i + 1] < offsets[i] + k) { shk::set_error("unitig %zu is shorter than k", i); return SHK_ERR_BAD_ARG; }
+  for (size_t i = 0; i < n_links; ++i)
+    if ((link_from[i] >> 1) >= n_unitigs || (link_to[i] >> 1) >= n_unitigs) { shk::set_error("link %zu names a unitig that does not exist", i); return SHK_ERR_BAD_ARG; }
+  shk::HostUnitigs &u = h->hu;
+  const size_t total = n_unitigs ? (size_t)offsets[n_unitigs] : 0;
+  u.seq.assign(seq, seq + total);
+  u.off.assign(n_unitigs + 1, 0);
+  if (n_unitigs) u.off.assign(offsets, offsets + n_unitigs + 1);
+  u.kc.assign(kmer_count_sum, kmer_count_sum + n_unitigs);
+  u.circ.assign(n_unitigs, 0);
+  if (circular) u.circ.assign(circular, circular + n_unitigs);
+  u.cov.resize(n_unitigs);
+  for (size_t i = 0; i < n_unitigs; ++i) u.cov[i] = (float)((double)u.kc[i] / (double)(u.off[i + 1] - u.off[i] - k + 1));
+  u.link_from.assign(link_from, link_from + n_links); u.link_to.assign(link_to, link_to + n_links);
+  u.valid = false;                                   // (not the device's unitigs: a later export fetches those again)
+  shk::progress(h, "assembly:start");
+  shk_status st = shk::build_assembly_json(h);
+  if (st == SHK_OK) shk::progress(h, "assembly:end");
+  return st;
+}
+
 extern "C" shk_status shk_fastq_stats(const char *path, int threads, uint64_t chunk_bytes, int bad_guesses, uint64_t *out4) {
   if (!path || !out4) { shk::set_error("null argument"); return SHK_ERR_BAD_ARG; }
   return shk::fastq_stats(path, threads, chunk_bytes, bad_guesses, out4);
