@@ -144,3 +144,47 @@ def test_bad_arguments_are_rejected():
             h.assemble_host(["A" * 30], [10], [0], [4], [0])
     finally:
         h.close()
+
+
+def layout_cases():
+    """graphs whose assemble() JSON is pinned byte for byte (tests/golden/writers_sha256.json)"""
+    cases = {}
+    for seed, k in ((1, 11), (3, 31), (5, 63)):
+        rng = random.Random(seed)
+        units, kcs, circs, links = chain_graph(rng, k, rng.randrange(3, 9))
+        cases[f"chain_{seed}_k{k}"] = (units, kcs, circs, links, k, True, True)
+        cases[f"chain_{seed}_k{k}_raw"] = (units, kcs, circs, links, k, False, False)
+    # many components: several hundred contigs, links, circular ones, a few very long
+    rng = random.Random(77)
+    k = 31
+    U, K, Z, L = [], [], [], set()
+    for c in range(120):
+        units, kcs, circs, links = chain_graph(rng, k, rng.randrange(3, 7), with_tip=c % 3 == 0, with_cycle=c % 4 == 0)
+        base = len(U)
+        U += units; K += kcs; Z += circs
+        L |= {(a + base, oa, b + base, ob) for (a, oa, b, ob) in links}
+    U.append(rand_seq(rng, 300_000)); K.append((300_000 - k + 1) * 97); Z.append(0)
+    cases["components_k31"] = (U, K, Z, L, k, True, True)
+    cases["components_k31_raw"] = (U, K, Z, L, k, False, False)
+    cases["empty"] = ([], [], [], set(), 21, True, True)
+    return cases
+
+
+def test_layout_is_pinned():
+    import hashlib
+    import os
+    gold = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "writers_sha256.json")))
+    cases = layout_cases()
+    assert set(gold) == set(cases)
+    for name, (units, kcs, circs, links, k, tips, bubbles) in cases.items():
+        lf = np.array([2 * a + oa for (a, oa, b, ob) in links], np.uint32)
+        lt = np.array([2 * b + ob for (a, oa, b, ob) in links], np.uint32)
+        h = AssemblyHelper.new(k, False, 1, 20, 0, False, False, not bubbles, not tips)
+        try:
+            h.assemble_host(units, kcs, circs, lf, lt)
+            assert hashlib.sha256(bytes(h.get_assembly_view())).hexdigest() == gold[name], name
+            if name.startswith("components"):
+                pc, pl = pyref.clean_graph(units, kcs, circs, links, k, tips=tips, bubbles=bubbles)
+                check_texts(json.loads(h.get_assembly()), h.contigs(), k, pc, pl)
+        finally:
+            h.close()
