@@ -5,6 +5,8 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <memory>
+#include <new>
 #include <string>
 #include <vector>
 
@@ -52,6 +54,28 @@ struct PinBuf {
   ~PinBuf() { release(); }
   shk_status ensure_host(size_t bytes);
   void release();
+};
+
+// grow-only text buffer whose bytes are NOT initialised on allocation (a std::string would zero-fill tens of megabytes
+// that are overwritten at once); always NUL-terminated behind size()
+struct RawText {
+  std::unique_ptr<char[]> p;
+  size_t n = 0, cap = 0;
+  bool empty() const { return n == 0; }
+  size_t size() const { return n; }
+  const char *c_str() const { return p ? p.get() : ""; }
+  char *data() { return p.get(); }
+  void clear() { n = 0; if (p) p[0] = 0; }
+  bool resize_uninit(size_t bytes) {            // false: out of memory
+    if (bytes + 1 > cap) {
+      const size_t want = bytes + bytes / 8 + 64;
+      char *q = new (std::nothrow) char[want];
+      if (!q) return false;
+      p.reset(q); cap = want;
+    }
+    n = bytes; p[n] = 0;
+    return true;
+  }
 };
 
 struct HostUnitigs {
@@ -183,7 +207,8 @@ struct shk_asm {
   bool counted = false, filtered = false, graphed = false, histo_valid = false;
   shk::HostUnitigs hu;
   shk_contigs *contigs = nullptr;     // cleaned graph of the last assemble()
-  std::string json_pre, json_asm;
+  std::string json_pre;
+  shk::RawText json_asm;      // the assemble() JSON: written in place by several threads (shk_host.cpp)
 
   // ---- FASTQ streaming parser (shk_asm_preprocess_push) ----
   std::vector<uint8_t> pend;          // bytes of an incomplete record
