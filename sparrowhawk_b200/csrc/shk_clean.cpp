@@ -32,8 +32,11 @@
 //            becomes one circular contig, rotated like S14: it starts at its
 //            minimum canonical k-mer, in that k-mer's canonical orientation.
 #include <algorithm>
+#include <atomic>
 #include <cstring>
 #include <string>
+#include <system_error>
+#include <thread>
 #include <vector>
 
 #include "shk_handle.h"
@@ -48,6 +51,25 @@ std::string revcomp_string(const std::string &s) {
   std::string r(s.size(), 'N');
   for (size_t i = 0, n = s.size(); i < n; ++i) r[i] = comp_base(s[n - 1 - i]);
   return r;
+}
+
+void parallel_for(size_t n, size_t work, const std::function<void(size_t)> &fn) {
+  const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+  const unsigned T = (unsigned)std::min<size_t>(std::min(8u, hw), n);
+  if (T < 2 || work < (4u << 20)) { for (size_t i = 0; i < n; ++i) fn(i); return; }
+  std::atomic<size_t> next{0};
+  const size_t block = std::max<size_t>(1, n / (T * 16));
+  auto body = [&] {
+    for (;;) {
+      const size_t b = next.fetch_add(block);
+      if (b >= n) return;
+      for (size_t i = b, e = std::min(n, b + block); i < e; ++i) fn(i);
+    }
+  };
+  std::vector<std::thread> th;
+  try { for (unsigned t = 1; t < T; ++t) th.emplace_back(body); } catch (const std::system_error &) {}   // (fewer threads, same result)
+  body();
+  for (auto &t : th) t.join();
 }
 
 // s < revcomp(s) without materialising the reverse complement
@@ -285,7 +307,7 @@ void clean_unitig_graph(int k, const char *seq, const uint64_t *off, const uint6
       }
     }
   }
-  for (size_t i = 0; i < n; ++i) { w.seq[i].assign(seq + off[i], seq + off[i + 1]); w.circ[i] = circ ? circ[i] : 0; }
+  parallel_for(n, n ? (size_t)(off[n] - off[0]) : 0, [&](size_t i) { w.seq[i].assign(seq + off[i], seq + off[i + 1]); w.circ[i] = circ ? circ[i] : 0; });
   for (size_t i = 0; i < nl; ++i) {
     const uint32_t x = lf[i], y = lt[i] ^ 1u;
     if ((x >> 1) >= n || (y >> 1) >= n) continue;

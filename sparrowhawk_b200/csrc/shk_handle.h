@@ -5,6 +5,7 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <functional>
 #include <memory>
 #include <new>
 #include <string>
@@ -99,6 +100,9 @@ struct CleanGraph {
 void clean_unitig_graph(int k, const char *seq, const uint64_t *off, const uint64_t *kc, const uint8_t *circ, size_t n,
                         const uint32_t *lf, const uint32_t *lt, size_t nl, bool tips, bool bubbles, CleanGraph &out);
 std::string revcomp_string(const std::string &s);
+// fn(i) for i in [0, n) on up to 8 threads when the loop is worth it (work = a rough byte count of the whole loop);
+// iterations are handed out in blocks from a counter, fn must touch only what belongs to its i
+void parallel_for(size_t n, size_t work, const std::function<void(size_t)> &fn);
 bool revcomp_is_smaller(const char *s, size_t n);
 
 }  // namespace shk

@@ -460,8 +460,11 @@ int fit_min_count(const uint64_t *histo, int fallback) {
 static void canonicalise(CleanGraph &g) {
   const size_t n = g.seq.size();
   std::vector<uint8_t> flipped(n, 0);
-  for (size_t i = 0; i < n; ++i)
+  size_t bases = 0;
+  for (size_t i = 0; i < n; ++i) bases += g.seq[i].size();
+  parallel_for(n, bases, [&](size_t i) {
     if (revcomp_is_smaller(g.seq[i].data(), g.seq[i].size())) { g.seq[i] = revcomp_string(g.seq[i]); flipped[i] = 1; }
+  });
   std::vector<uint32_t> order(n);
   std::iota(order.begin(), order.end(), 0u);
   std::sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) {
