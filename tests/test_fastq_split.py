@@ -102,3 +102,30 @@ def test_parallel_split_reports_the_serial_error(tmp_path, damage):
     assert serial[0] == "error", serial
     for threads, chunk, bad in ((4, 8192, -1), (8, 2048, -1), (4, 8192, 1)):
         assert stats(p, threads, chunk, bad) == serial, (threads, chunk, bad)
+
+
+def test_parallel_split_fuzz(tmp_path):
+    """randomly damaged files (bytes deleted / inserted / replaced, truncation): whatever the serial parser says —
+    reads and checksums, or its first error with its record number — the multi-threaded split says too"""
+    import random
+    rng = random.Random(2024)
+    p = tmp_path / "f.fastq"
+    for it in range(80):
+        eol = rng.choice([b"\n", b"\r\n"])
+        data, _, _ = make_fastq(rng.randrange(1 << 30), rng.randrange(1, 300), eol, rng.choice([0, 0, 3, 11]), rng.random() < 0.7)
+        data = bytearray(data)
+        mode = rng.randrange(5)
+        for _ in range(rng.randrange(1, 4) if mode in (1, 2, 4) else 0):
+            i = rng.randrange(len(data))
+            if mode == 1:
+                del data[i]
+            elif mode == 2:
+                data.insert(i, rng.choice(b"@+\n\rACGT>I"))
+            else:
+                data[i] = rng.choice(b"@+\n\rACGT>I")
+        if mode == 3:
+            data = data[:rng.randrange(len(data))]
+        p.write_bytes(bytes(data))
+        ref = stats(p, 1)
+        for threads, chunk, bad in ((3, 64, -1), (8, 1000, 1), (2, 5000, -1)):
+            assert stats(p, threads, chunk, bad) == ref, (it, mode, threads, chunk, bad)
